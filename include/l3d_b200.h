@@ -1,0 +1,155 @@
+/* include/l3d_b200.h -- C ABI of libl3d_b200.so: the Blackwell (sm_100a) implementation of
+ * Line3D's data-parallel matching-and-scoring path.
+ *
+ * This is the drop-in boundary.  It replaces the three C++ operator functions the
+ * reference's host code calls into its CUDA translation unit (cudawrapper.h:49-75):
+ *
+ *     compute_collinearity(...)            -> l3d_collinearity
+ *     compute_pairwise_matches(...)        -> l3d_set_views + l3d_match_view
+ *     replicator_dynamics_diffusion(...)   -> l3d_diffuse
+ *
+ * and moves onto the GPU the two pieces of the path that the reference runs in host
+ * double precision (view.cc:302-342 unprojectSegment, line3D.cc:1600-1691
+ * similarity_coll3D)                       -> l3d_unproject, l3d_affinity.
+ *
+ * Plain C: POD structs, pointers and sizes only; no STL, Eigen or torch types.  Every
+ * call returns 0 on success, non-zero on failure with a message from l3d_last_error().
+ * A context is bound to one CUDA device and one host thread; it owns all device memory,
+ * nothing is global.  Host input buffers are caller-owned and only read during the call.
+ * There is no CPU fallback: without a usable CUDA device l3d_create fails.
+ */
+#ifndef L3D_B200_H_
+#define L3D_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct l3d_ctx l3d_ctx;
+
+/* ---- lifetime ------------------------------------------------------------------------ */
+int l3d_create(int device, l3d_ctx** out);
+void l3d_destroy(l3d_ctx* ctx);
+const char* l3d_last_error(const l3d_ctx* ctx);   /* ctx may be NULL: last l3d_create error */
+
+/* ---- collinearity: replaces compute_collinearity (cudawrapper.h:49-51,
+ *      cudawrapper.cu:476-535, 833-855) and the dense N*N download + triangle scan of
+ *      segments.h:73-101.  segments: n x (p1x p1y p2x p2y).  On return *pairs points to
+ *      *count records with i < j and value > 0, sorted by (i, j); the buffer belongs to
+ *      the context and stays valid until the next l3d_collinearity call or l3d_destroy. */
+typedef struct { int32_t i, j; float value; } l3d_collin_pair;
+int l3d_collinearity(l3d_ctx* ctx, const float* segments, int n, float collin_s,
+                     const l3d_collin_pair** pairs, size_t* count);
+
+/* ---- scene tables: what line3D.cc:738-803 packs per view, uploaded once for all views.
+ *      Matrices are row-major.  The float tables are the reference's double values cast
+ *      to float (line3D.cc:745-763, 790); the double ones feed l3d_unproject. */
+typedef struct {
+    int32_t id;              /* caller's view id (reported back, not interpreted)        */
+    int32_t n_segments;
+    const float* segments;   /* n_segments x 4                                           */
+    float RtKinv[9];         /* R^T K^-1                    view.cc:26                   */
+    float C[3];              /* camera centre               view.cc:27                   */
+    float P[12];             /* K [R|t]                     view.cc:31-34                */
+    float spatial_k;         /* specificSpatialUncertaintyK(2 sigma_p), line3D.cc:820    */
+    float k_lower, k_upper;  /* view.cc:90-121                                           */
+    double RtKinv_d[9];
+    double C_d[3];
+} l3d_view;
+int l3d_set_views(l3d_ctx* ctx, int n_views, const l3d_view* views);
+
+/* ---- matching + scoring of one view: replaces compute_pairwise_matches
+ *      (cudawrapper.h:54-71, cudawrapper.cu:858-1128) together with the exchange of
+ *      reversed matches between views that the reference routes through files
+ *      (line3D.cc:838-872, view.cc:162-224).
+ *
+ *      neighbors[] lists the view's visual neighbours in ascending view id; the position
+ *      in the array is the reference's local camera id (line3D.cc:723-730).
+ *        to_be_matched  = 1: pair-test this neighbour now (line3D.cc:732-736);
+ *                         0: it was processed earlier as a mutual neighbour; the records
+ *                            it delivered to this view are consumed instead.
+ *        deliver        = 1: hand this view's filtered matches, reversed, to that
+ *                            neighbour for when it is processed (line3D.cc:844-858).
+ *      Views must be processed in the reference's order (ascending id, line3D.cc:626).
+ *      If no neighbour has to_be_matched set the reference does not score at all
+ *      (cudawrapper.cu:877-878): the delivered records come back unscored (scored = 0,
+ *      confidence 0, median_depth 1.0), sorted by (src, cam, tgt).
+ *
+ *      Results: records with score > 1 (stored score = score / 2, cudawrapper.cu:1096-1098)
+ *      in (src, cam, tgt) order, cam = position in neighbors[].  The record buffer is
+ *      context-owned pinned host memory, valid until the next l3d_match_view. */
+typedef struct {
+    int32_t view;            /* index into the l3d_set_views array                       */
+    float F[9];              /* fundamental matrix src -> this neighbour, line3D.cc:739   */
+    int32_t to_be_matched;
+    int32_t deliver;
+} l3d_neighbor;
+typedef struct {
+    int32_t src_seg;
+    int32_t cam;             /* position in neighbors[]                                   */
+    int32_t tgt_seg;
+    float confidence;
+    float depths[4];         /* src p1, src p2, tgt q1, tgt q2 (cudawrapper.cu:594-601)   */
+} l3d_match;
+typedef struct {
+    uint64_t pair_tests;     /* (src seg, tgt seg) evaluations done for this view         */
+    uint64_t n_candidates;   /* pairs the conservative pre-test passed to the exact test  */
+    uint64_t n_raw;          /* new raw matches (all four depths > 0)                     */
+    uint64_t n_delivered;    /* records consumed from earlier mutual neighbours           */
+    uint64_t n_scored;       /* n_raw + n_delivered                                       */
+    uint64_t n_filtered;
+    uint64_t score_iters;    /* sum over src segments of (matches of the segment)^2       */
+    int32_t scored;
+    float median_depth;      /* cudawrapper.cu:1066-1076                                  */
+    const l3d_match* filtered;
+} l3d_match_result;
+int l3d_match_view(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors,
+                   float sigma_p, float sigma_a, l3d_match_result* result);
+/* Forget all delivered-but-unconsumed records (a new compute3Dmodel run, line3D.cc:356). */
+int l3d_reset_matching(l3d_ctx* ctx);
+
+/* Device-only variant used for measurement: same work, but nothing is copied back except
+ * the counters; filtered is NULL. */
+int l3d_match_view_resident(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors,
+                            float sigma_p, float sigma_a, l3d_match_result* result);
+
+/* ---- hypotheses: replaces L3DView::unprojectSegment (view.cc:302-342), FP64 on device.
+ *      The n hypotheses stay resident for l3d_affinity. */
+typedef struct { int32_t view; int32_t seg; float depth1, depth2; } l3d_hypothesis_in;
+typedef struct { double P1[3], P2[3], dir[3]; } l3d_segment3d;
+int l3d_unproject(l3d_ctx* ctx, size_t n, const l3d_hypothesis_in* in, l3d_segment3d* out);
+
+/* ---- pairwise 3-D affinity: replaces Line3D::similarity_coll3D (line3D.cc:1600-1691)
+ *      for a list of candidate pairs (indices into the l3d_unproject array), in any order.
+ *      median_depth: one value per view of l3d_set_views (view.cc:353-377 cap).
+ *      out[k] = the reference's sim in [0,1] (0 where sim <= 0.01). */
+typedef struct { int32_t a, b; } l3d_pair;
+int l3d_affinity(l3d_ctx* ctx, const float* median_depth, size_t n_pairs, const l3d_pair* pairs,
+                 float sigma_a, float* out);
+
+/* ---- diffusion: replaces SparseMatrix construction (sparsematrix.cc:63-191) and
+ *      replicator_dynamics_diffusion (cudawrapper.h:74, cudawrapper.cu:1131-1191).
+ *      edges: nnz directed entries (i, j, w), unique (i, j), structurally symmetric, every
+ *      node 0..n_nodes-1 present.  out: the nnz entries of the result in the reference's
+ *      stored order (sorted by row, then column). */
+typedef struct { int32_t i, j; float w; } l3d_edge;
+int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3d_edge* out);
+
+/* ---- measurement helpers -------------------------------------------------------------- */
+/* Device time in ms of the kernels of the last l3d_match_view[_resident] call, by stage:
+ * [0] pre-test, [1] exact test, [2] assembly, [3] scoring, [4] reduce/filter/deliver,
+ * [5] whole call on the device.  Timed with CUDA events on the context's stream. */
+int l3d_last_timings(l3d_ctx* ctx, float ms[6]);
+/* FP32 FFMA throughput of the device in TFLOP/s (register-only FMA chains, CUDA events):
+ * the measured denominator for the FP32-pipe roofline. */
+int l3d_measure_fp32_peak(l3d_ctx* ctx, float* tflops);
+/* Number of kernels this library has launched on the context since creation. */
+uint64_t l3d_kernel_launches(const l3d_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* L3D_B200_H_ */

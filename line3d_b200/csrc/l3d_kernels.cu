@@ -1,0 +1,1417 @@
+// line3d_b200/csrc/l3d_kernels.cu -- sm_100a kernels and C ABI (include/l3d_b200.h) of the
+// Line3D matching-and-scoring path.  Written from scratch for B200; the reference's
+// cudawrapper.cu is cited only for the semantics each stage must reproduce.
+//
+// Per view v (l3d_match_view), everything stays on the device:
+//
+//   hoist      per neighbour, per segment: epipolar lines of the endpoints (FP64 -> FP32)
+//   pre-test   every (src, tgt) pair: conservative interval test on the four epipolar
+//              residuals q_m^T F p_n  -> 1 candidate bit per pair          [FP32-pipe bound]
+//   exact      candidates only: the reference's arithmetic, bit for bit   (l3d_device.cuh)
+//   assemble   count -> scan -> fill: the view's match list in the reference's canonical
+//              (src, cam, tgt) order, new raw matches merged with the reversed records
+//              that earlier views delivered -- no sort, no host round trip
+//   score      every match against every other match of its source segment: a 2-compare
+//              depth gate that is a superset of the reference's 3-D gate, exact
+//              evaluation of the survivors through a per-warp queue   [LDS/ALU bound]
+//   reduce     best match per segment, median depth, filter (score > 1), and the
+//              reversed hand-over lists for later views, transposed on the device
+//
+// Tensor cores are not used: nothing here is a dense contraction.
+#include "../../include/l3d_b200.h"
+#include "l3d_device.cuh"
+
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace l3d;
+
+// ------------------------------------------------------------------------------------------
+// small utilities
+// ------------------------------------------------------------------------------------------
+namespace {
+
+std::string g_create_error;
+
+#define L3D_CUDA(call)                                                                              \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess) {                                                                    \
+            char b_[512];                                                                           \
+            snprintf(b_, sizeof b_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            ctx->err = b_;                                                                          \
+            return 1;                                                                               \
+        }                                                                                           \
+    } while (0)
+
+template<class T>
+struct DBuf {                 // grow-only device buffer
+    T* p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t n)
+    {
+        if (n <= cap) return cudaSuccess;
+        size_t want = std::max(n, cap + cap / 2);
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+template<class T>
+struct HBuf {                 // grow-only pinned host buffer
+    T* p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t n)
+    {
+        if (n <= cap) return cudaSuccess;
+        size_t want = std::max(n, cap + cap / 2);
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMallocHost(&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+// per (source view, neighbour) table on the device
+struct CamTable {
+    float F[9];
+    float RtKinv[9];
+    float P[12];
+    float C[3];
+    int seg_off;        // first segment of the neighbour in the global segment array
+    int n_seg;
+    int mode;           // 0 = pair-test now, 1 = consume delivered records, 2 = nothing
+    int slot;           // index among the pair-tested neighbours (mode 0) or -1
+    int deliver;        // delivery slot (>= 0) or -1
+    const int* t_start; // mode 1: delivered records grouped by this view's segment
+    const int* t_tgt;
+    const float4* t_dep;
+};
+
+struct SrcTable {       // the source view
+    float RtKinv[9];
+    float C[3];
+    float spatial_k;
+    float cmax;         // max |C_k|
+    int seg_off, n_seg;
+};
+
+// ------------------------------------------------------------------------------------------
+// exclusive scan (int), three phases, any length up to 4096 * 4096
+// ------------------------------------------------------------------------------------------
+constexpr int SCAN_T = 1024, SCAN_ITEMS = 4, SCAN_TILE = SCAN_T * SCAN_ITEMS;
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* sh /* 32 ints */)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) sh[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        int s = (lane < (blockDim.x >> 5)) ? sh[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
+        sh[lane] = s;
+    }
+    __syncthreads();
+    int base = wid ? sh[wid - 1] : 0;
+    if (total) *total = sh[(blockDim.x >> 5) - 1];
+    __syncthreads();
+    return base + x - v;
+}
+
+__global__ void __launch_bounds__(SCAN_T) k_scan_tiles(const int* __restrict__ in, int* __restrict__ out, int* __restrict__ tile_sums, int n)
+{
+    __shared__ int sh[32];
+    const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    int v[SCAN_ITEMS], s = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) { v[k] = (base + k < n) ? in[base + k] : 0; s += v[k]; }
+    int total;
+    int ex = block_exclusive_scan(s, &total, sh);
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) { if (base + k < n) out[base + k] = ex; ex += v[k]; }
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+// scans the tile sums in one block (<= 4096 tiles) and writes the grand total to out_total
+__global__ void __launch_bounds__(SCAN_T) k_scan_sums(int* __restrict__ tile_sums, int n_tiles, int* __restrict__ out_total)
+{
+    __shared__ int sh[32];
+    const int base = threadIdx.x * SCAN_ITEMS;
+    int v[SCAN_ITEMS], s = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) { v[k] = (base + k < n_tiles) ? tile_sums[base + k] : 0; s += v[k]; }
+    int total;
+    int ex = block_exclusive_scan(s, &total, sh);
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) { if (base + k < n_tiles) tile_sums[base + k] = ex; ex += v[k]; }
+    if (threadIdx.x == 0) *out_total = total;
+}
+__global__ void __launch_bounds__(SCAN_T) k_scan_add(int* __restrict__ out, const int* __restrict__ tile_sums, int n, const int* __restrict__ total)
+{
+    const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    const int add = tile_sums[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) if (base + k < n) out[base + k] += add;
+    if (blockIdx.x == 0 && threadIdx.x == 0) out[n] = *total;       // out has n + 1 entries
+}
+
+// ------------------------------------------------------------------------------------------
+// hoist: per (pair-tested neighbour, segment) epipolar data for the pre-test
+//   src side:  A_n = F p_n (n = 1,2) and w'_n = |(A_n)_xy|
+//   tgt side:  q1, q2 and w_m = |(F^T q_m)_xy|
+// evaluated in FP64 from the FP32 tables, rounded once.
+// ------------------------------------------------------------------------------------------
+struct SrcHoist { float4 a; float4 b; };   // a = (A1x, A1y, A1z, w'1)   b = (A2x, A2y, A2z, w'2)
+struct TgtHoist { float4 q; float2 w; float2 pad; };
+
+__global__ void k_hoist(const float4* __restrict__ segs, const CamTable* __restrict__ cams, const int* __restrict__ slot_cam,
+                        SrcTable src, SrcHoist* __restrict__ sh, TgtHoist* __restrict__ th, int max_src, int max_tgt)
+{
+    const int slot = blockIdx.y;
+    const CamTable& ct = cams[slot_cam[slot]];
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    double F[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) F[k] = double(ct.F[k]);
+    if (idx < src.n_seg) {
+        float4 s = segs[src.seg_off + idx];
+        double p[2][2] = {{double(s.x), double(s.y)}, {double(s.z), double(s.w)}};
+        float o[2][4];
+#pragma unroll
+        for (int n = 0; n < 2; ++n) {
+            double ax = F[0] * p[n][0] + F[1] * p[n][1] + F[2];
+            double ay = F[3] * p[n][0] + F[4] * p[n][1] + F[5];
+            double az = F[6] * p[n][0] + F[7] * p[n][1] + F[8];
+            o[n][0] = float(ax); o[n][1] = float(ay); o[n][2] = float(az); o[n][3] = float(sqrt(ax * ax + ay * ay));
+        }
+        SrcHoist h; h.a = make_float4(o[0][0], o[0][1], o[0][2], o[0][3]); h.b = make_float4(o[1][0], o[1][1], o[1][2], o[1][3]);
+        sh[size_t(slot) * max_src + idx] = h;
+    }
+    if (idx < ct.n_seg) {
+        float4 t = segs[ct.seg_off + idx];
+        double q[2][2] = {{double(t.x), double(t.y)}, {double(t.z), double(t.w)}};
+        float w[2];
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+            double ex = F[0] * q[m][0] + F[3] * q[m][1] + F[6];
+            double ey = F[1] * q[m][0] + F[4] * q[m][1] + F[7];
+            w[m] = float(sqrt(ex * ex + ey * ey));
+        }
+        TgtHoist h; h.q = t; h.w = make_float2(w[0], w[1]); h.pad = make_float2(0.f, 0.f);
+        th[size_t(slot) * max_tgt + idx] = h;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// pre-test.  For the pair (src s = p1p2, tgt t = q1q2) let E[m][n] = q_m^T F p_n.  The
+// intersection of the src line with the epipolar line of q_m sits at parameter
+//     tau_m = E[m][1] / (E[m][1] - E[m][2])        (0 at p1, 1 at p2)
+// and the intersection of the tgt line with the epipolar line of p_n at
+//     tau'_n = E[1][n] / (E[1][n] - E[2][n]).
+// The reference's overlap value (cudawrapper.cu:209-252) is the 1-D intersection over
+// union of [0,1] with [tau_1,tau_2] (resp. tau'), or 0.  A pair is dropped here only if,
+// with every tau moved by an error bound worth L3D_PRETEST_EPS_PX pixels of intersection
+// noise, an overlap still cannot reach the reference's thresholds minus a margin; all
+// others go to the exact test.  The result is a superset of the reference's accepted set.
+// ------------------------------------------------------------------------------------------
+#define L3D_PRETEST_EPS_PX 0.25f
+#define L3D_PRETEST_LO 0.09f
+#define L3D_PRETEST_HI 0.28f
+
+__device__ __forceinline__ void side_bounds(float e1a, float e1b, float e2a, float e2b, float w1, float w2, float& I_hi, float& U_lo)
+{
+    // endpoint m: tau = ema / (ema - emb)
+    float d1 = e1a - e1b, d2 = e2a - e2b;
+    float r1 = __frcp_rn(d1), r2 = __frcp_rn(d2);
+    float t1 = e1a * r1, t2 = e2a * r2;
+    float err = L3D_PRETEST_EPS_PX * (w1 * fabsf(r1) * (1.0f + 2.0f * fabsf(t1)) + w2 * fabsf(r2) * (1.0f + 2.0f * fabsf(t2)));
+    float lo = fminf(t1, t2), hi = fmaxf(t1, t2);
+    I_hi = fminf(hi, 1.0f) - fmaxf(lo, 0.0f) + err;
+    U_lo = fmaxf(hi, 1.0f) - fminf(lo, 0.0f) - err;
+}
+
+constexpr int PT_THREADS = 128;     // rows per block
+constexpr int PT_COLS = 1024;       // columns staged per smem tile
+
+__global__ void __launch_bounds__(PT_THREADS) k_pretest(const SrcHoist* __restrict__ sh, const TgtHoist* __restrict__ th,
+                                                        const CamTable* __restrict__ cams, const int* __restrict__ slot_cam,
+                                                        int n_src, int max_src, int max_tgt, int words_per_row,
+                                                        unsigned* __restrict__ cand, int* __restrict__ cand_cnt, int n_slots)
+{
+    __shared__ float4 s_q[PT_COLS];
+    __shared__ float2 s_w[PT_COLS];
+    const int slot = blockIdx.z;
+    const int n_tgt = cams[slot_cam[slot]].n_seg;
+    const int col0 = blockIdx.y * PT_COLS;
+    if (col0 >= n_tgt) return;
+    const int ncol = min(PT_COLS, n_tgt - col0);
+    for (int k = threadIdx.x; k < PT_COLS; k += PT_THREADS) {
+        if (k < ncol) { TgtHoist h = th[size_t(slot) * max_tgt + col0 + k]; s_q[k] = h.q; s_w[k] = h.w; }
+        else { s_q[k] = make_float4(0.f, 0.f, 0.f, 0.f); s_w[k] = make_float2(0.f, 0.f); }
+    }
+    __syncthreads();
+    const int row = blockIdx.x * PT_THREADS + threadIdx.x;
+    if (row >= n_src) return;
+    const SrcHoist h = sh[size_t(slot) * max_src + row];
+    const float4 A1 = h.a, A2 = h.b;
+    int total = 0;
+    unsigned* out = cand + (size_t(slot) * max_src + row) * words_per_row + (col0 >> 5);
+    for (int w = 0; w * 32 < ncol; ++w) {
+        unsigned bits = 0, mk = 1u;
+#pragma unroll 8
+        for (int b = 0; b < 32; ++b, mk <<= 1) {
+            const float4 q = s_q[w * 32 + b];
+            const float2 ww = s_w[w * 32 + b];
+            // E[m][n] = q_m . A_n
+            float e11 = fmaf(q.x, A1.x, fmaf(q.y, A1.y, A1.z));
+            float e12 = fmaf(q.x, A2.x, fmaf(q.y, A2.y, A2.z));
+            float e21 = fmaf(q.z, A1.x, fmaf(q.w, A1.y, A1.z));
+            float e22 = fmaf(q.z, A2.x, fmaf(q.w, A2.y, A2.z));
+            float Ia, Ua, Ib, Ub;
+            side_bounds(e11, e12, e21, e22, ww.x, ww.y, Ia, Ua);      // along the src segment
+            side_bounds(e11, e21, e12, e22, A1.w, A2.w, Ib, Ub);      // along the tgt segment
+            // keep unless an overlap surely misses a threshold; NaN/inf comparisons keep
+            bool drop = (Ia < L3D_PRETEST_LO * Ua) || (Ib < L3D_PRETEST_LO * Ub) ||
+                        ((Ia < L3D_PRETEST_HI * Ua) && (Ib < L3D_PRETEST_HI * Ub));
+            if (!drop) bits |= mk;
+        }
+        if (w * 32 + 32 > ncol) { int valid = ncol - w * 32; bits &= (valid >= 32) ? 0xffffffffu : ((1u << valid) - 1u); }
+        out[w] = bits;
+        total += __popc(bits);
+    }
+    if (total) atomicAdd(&cand_cnt[row * n_slots + slot], total);
+}
+
+// ------------------------------------------------------------------------------------------
+// exact test: one warp per (row, slot); candidates are gathered in column order into a
+// per-warp queue and evaluated 32 at a time; survivors (all four depths > 0) are written,
+// still in column order, to the row's staging range.
+// ------------------------------------------------------------------------------------------
+constexpr int EX_WARPS = 8;
+constexpr int EX_QCAP = 1088;
+
+__global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restrict__ segs, const CamTable* __restrict__ cams,
+                                                         const int* __restrict__ slot_cam, SrcTable src,
+                                                         const unsigned* __restrict__ cand, const int* __restrict__ cand_off,
+                                                         int max_src, int words_per_row, int n_slots, int n_cams,
+                                                         int* __restrict__ stage_col, float4* __restrict__ stage_dep, int* __restrict__ cnt)
+{
+    __shared__ unsigned short s_queue[EX_WARPS][EX_QCAP];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row = blockIdx.x * EX_WARPS + warp;
+    const int slot = blockIdx.y;
+    if (row >= src.n_seg) return;
+    const int cam = slot_cam[slot];
+    const CamTable& ct = cams[cam];
+    const int n_cand = cand_off[row * n_slots + slot + 1] - cand_off[row * n_slots + slot];
+    if (n_cand == 0) { if (lane == 0) cnt[row * n_cams + cam] = 0; return; }
+    const int base = cand_off[row * n_slots + slot];
+    const unsigned* words = cand + (size_t(slot) * max_src + row) * words_per_row;
+    const int n_words = (ct.n_seg + 31) >> 5;
+    unsigned short* q = s_queue[warp];
+    const float4 s = segs[src.seg_off + row];
+    const V3 Cs = mk3(src.C[0], src.C[1], src.C[2]), Ct = mk3(ct.C[0], ct.C[1], ct.C[2]);
+    int qn = 0, accepted = 0;
+    auto evaluate = [&](int first, int count) {
+        // lanes [0, count) take queue entries first .. first + count - 1 (column order)
+        bool ok = false; float4 dep = make_float4(0.f, 0.f, 0.f, 0.f); int col = 0;
+        if (lane < count) {
+            col = q[first + lane];
+            ok = xpair_test(s, segs[ct.seg_off + col], ct.F, src.RtKinv, ct.RtKinv, Cs, Ct, dep);
+        }
+        unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (ok) {
+            int r = base + accepted + __popc(m & ((1u << lane) - 1u));
+            stage_col[r] = col; stage_dep[r] = dep;
+        }
+        accepted += __popc(m);
+    };
+    for (int w0 = 0; w0 < n_words; w0 += 32) {
+        unsigned bits = (w0 + lane < n_words) ? words[w0 + lane] : 0u;
+        int n = __popc(bits), ex = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, ex, o); if (lane >= o) ex += y; }
+        const int tot = __shfl_sync(0xffffffffu, ex, 31);
+        int pos = qn + ex - n;
+        while (bits) { int b = __ffs(bits) - 1; bits &= bits - 1; q[pos++] = (unsigned short)((w0 + lane) * 32 + b); }
+        qn += tot;
+        __syncwarp();
+        int head = 0;
+        while (qn - head >= 32) { evaluate(head, 32); head += 32; }
+        if (head > 0) {        // move the (< 32) leftovers to the front
+            const int rem = qn - head;
+            unsigned short v = (lane < rem) ? q[head + lane] : (unsigned short)0;
+            __syncwarp();
+            if (lane < rem) q[lane] = v;
+            qn = rem;
+            __syncwarp();
+        }
+    }
+    if (qn > 0) evaluate(0, qn);
+    if (lane == 0) cnt[row * n_cams + cam] = accepted;
+}
+
+// counts of the delivered records per (row, cam) for the cams in mode 1
+__global__ void k_delivered_counts(const CamTable* __restrict__ cams, int n_cams, int n_src, int* __restrict__ cnt)
+{
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    const int cam = blockIdx.y;
+    if (row >= n_src) return;
+    const CamTable& ct = cams[cam];
+    if (ct.mode == 1) cnt[row * n_cams + cam] = ct.t_start ? (ct.t_start[row + 1] - ct.t_start[row]) : 0;
+    else if (ct.mode == 2) cnt[row * n_cams + cam] = 0;
+}
+
+// fill: one warp per (row, cam) copies the row's records to their final place
+__global__ void k_fill(const CamTable* __restrict__ cams, int n_cams, int n_slots, int n_src,
+                       const int* __restrict__ off, const int* __restrict__ cand_off,
+                       const int* __restrict__ stage_col, const float4* __restrict__ stage_dep,
+                       int4* __restrict__ m_ids, float4* __restrict__ m_dep)
+{
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (gw >= n_src * n_cams) return;
+    const int row = gw / n_cams, cam = gw - row * n_cams;
+    const int o = off[gw], n = off[gw + 1] - o;
+    if (n == 0) return;
+    const CamTable& ct = cams[cam];
+    if (ct.mode == 0) {
+        const int b = cand_off[row * n_slots + ct.slot];
+        for (int k = lane; k < n; k += 32) { m_ids[o + k] = make_int4(row, cam, stage_col[b + k], 0); m_dep[o + k] = stage_dep[b + k]; }
+    } else if (ct.mode == 1) {
+        const int b = ct.t_start[row];
+        for (int k = lane; k < n; k += 32) { m_ids[o + k] = make_int4(row, cam, ct.t_tgt[b + k], 0); m_dep[o + k] = ct.t_dep[b + k]; }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// scoring (cudawrapper.cu:614-714).  Block = (chunk of SC_T matches of one source segment);
+// every thread owns one match y and walks the segment's other matches camera group by
+// camera group.  The reference's 3-D gate  |P-Q| > spatial_k |C-P|  (cudawrapper.cu:388-401)
+// compares two points on the same unit ray, so it can only pass when the depths differ by
+// at most spatial_k * depth (+ rounding): that 2-compare test on (d1, d2) pairs staged in
+// shared memory rejects ~97-99.8 % of the iterations; the rest are queued per warp and
+// evaluated with the reference's exact arithmetic, 32 at a time.
+// ------------------------------------------------------------------------------------------
+constexpr int SC_T = 128;
+constexpr int SC_WARPS = SC_T / 32;
+constexpr int SC_TILE = 2048;      // matches staged per smem tile
+constexpr int SC_QCAP = 96;
+
+struct ScoreParams { float sigma_p, sigma_a; };
+
+__device__ __forceinline__ void score_drain(int count, const unsigned* q, int lane, int y0,
+                                            const float2* s_yd, const float2* s_d, const int* s_tgt, int tile0,
+                                            V3 p1, V3 p2, V3 ray1, V3 ray2, V3 C, float spatial_k,
+                                            const float* P, const float4* tgt_segs, float sigma_p, float sigma_a, int* s_max)
+{
+    if (lane < count) {
+        const unsigned e = q[lane];
+        const int yl = int(e >> 16), il = int(e & 0xffffu);
+        const float2 dy = s_yd[yl], di = s_d[il];
+        // cudawrapper.cu:644-645, 671-672
+        V3 P1 = xadd3(C, xscale(dy.x, ray1)), P2 = xadd3(C, xscale(dy.y, ray2));
+        V3 Q1 = xadd3(C, xscale(di.x, ray1)), Q2 = xadd3(C, xscale(di.y, ray2));
+        V3 pr1 = xproject(P, P1), pr2 = xproject(P, P2);
+        if (pr1.z == 1.0f && pr2.z == 1.0f) {
+            float conf = xhypothesis_confidence(pr1, pr2, P1, P2, Q1, Q2, C, tgt_segs[s_tgt[il]], sigma_p, sigma_a, spatial_k);
+            if (conf > 0.5f) atomicMax(&s_max[yl], __float_as_int(conf));
+        }
+    }
+    (void)y0; (void)p1; (void)p2; (void)tile0;
+}
+
+__global__ void __launch_bounds__(SC_T) k_score(const float4* __restrict__ segs, const CamTable* __restrict__ cams, int n_cams, SrcTable src,
+                                                const int* __restrict__ off, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
+                                                ScoreParams sp, float* __restrict__ score)
+{
+    __shared__ float2 s_d[SC_TILE];
+    __shared__ int s_tgt[SC_TILE];
+    __shared__ float2 s_yd[SC_T];
+    __shared__ int s_max[SC_T];
+    __shared__ unsigned s_q[SC_WARPS][SC_QCAP];
+    const int row = blockIdx.y;
+    const int seg_start = off[row * n_cams], seg_end = off[(row + 1) * n_cams];
+    const int M = seg_end - seg_start;
+    const int y0 = blockIdx.x * SC_T;
+    if (y0 >= M) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int y = y0 + tid;
+    const bool live = y < M;
+    int my_cam = -1; float2 my_d = make_float2(0.f, 0.f);
+    if (live) { my_cam = m_ids[seg_start + y].y; float4 d = m_dep[seg_start + y]; my_d = make_float2(d.x, d.y); }
+    s_yd[tid] = my_d; s_max[tid] = 0;
+    // per-segment invariants (cudawrapper.cu:638-645)
+    const float4 sg = segs[src.seg_off + row];
+    const V3 p1 = mk3(sg.x, sg.y, 1.0f), p2 = mk3(sg.z, sg.w, 1.0f);
+    const V3 ray1 = xnormalize(xmat3(src.RtKinv, p1, false)), ray2 = xnormalize(xmat3(src.RtKinv, p2, false));
+    const V3 C = mk3(src.C[0], src.C[1], src.C[2]);
+    // superset gate:  |dy - di| <= thr  must hold for the exact gate to be able to pass
+    const float k = src.spatial_k;
+    const float thr1 = (k * fabsf(my_d.x) * 1.00001f + 2e-6f * (2.0f * fabsf(my_d.x) + src.cmax)) * 1.00001f;
+    const float thr2 = (k * fabsf(my_d.y) * 1.00001f + 2e-6f * (2.0f * fabsf(my_d.y) + src.cmax)) * 1.00001f;
+    const bool gate_on = k > 0.0f;
+    unsigned* q = s_q[warp];
+    float total = 0.0f;
+    int qn = 0;
+    for (int cam = 0; cam < n_cams; ++cam) {
+        const int g0 = off[row * n_cams + cam] - seg_start, g1 = off[row * n_cams + cam + 1] - seg_start;
+        if (g1 == g0) continue;
+        const CamTable& ct = cams[cam];
+        const bool mine = live && (cam != my_cam);
+        for (int t0 = g0; t0 < g1; t0 += SC_TILE) {
+            const int tn = min(SC_TILE, g1 - t0);
+            __syncthreads();
+            for (int i = tid; i < tn; i += SC_T) {
+                float4 d = m_dep[seg_start + t0 + i];
+                s_d[i] = make_float2(d.x, d.y);
+                s_tgt[i] = ct.seg_off + m_ids[seg_start + t0 + i].z;
+            }
+            __syncthreads();
+            for (int i0 = 0; i0 < tn; i0 += 32) {
+                // each lane tests up to 32 entries against its own hypothesis
+                unsigned hits = 0;
+                if (mine) {
+                    const int lim = min(32, tn - i0);
+                    if (gate_on) {
+#pragma unroll 8
+                        for (int b = 0; b < 32; ++b) {
+                            const float2 d = s_d[i0 + (b < lim ? b : 0)];
+                            bool pass = (fabsf(my_d.x - d.x) <= thr1) && (fabsf(my_d.y - d.y) <= thr2) && (b < lim);
+                            hits |= pass ? (1u << b) : 0u;
+                        }
+                    } else {
+                        hits = (lim >= 32) ? 0xffffffffu : ((1u << lim) - 1u);
+                    }
+                }
+                // enqueue this warp's hits, draining whenever 32 are ready
+                while (__any_sync(0xffffffffu, hits != 0u)) {
+                    int n = __popc(hits), ex = n;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { int v = __shfl_up_sync(0xffffffffu, ex, o); if (lane >= o) ex += v; }
+                    ex -= n;
+                    // take as many as fit
+                    int room = SC_QCAP - qn;
+                    int pos = qn + ex;
+                    int pushed = 0;
+                    while (hits && pos < SC_QCAP) { int b = __ffs(hits) - 1; hits &= hits - 1; q[pos++] = (unsigned(tid) << 16) | unsigned(i0 + b); ++pushed; }
+                    int tot = pushed;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+                    qn += tot;
+                    (void)room;
+                    __syncwarp();
+                    while (qn >= 32) {
+                        score_drain(32, q + (qn - 32), lane, y0, s_yd, s_d, s_tgt, t0, p1, p2, ray1, ray2, C, k, ct.P, segs, sp.sigma_p, sp.sigma_a, s_max);
+                        qn -= 32;
+                        __syncwarp();
+                    }
+                }
+            }
+            // the tile is about to be replaced: finish everything that refers to it
+            if (qn > 0) {
+                score_drain(qn, q, lane, y0, s_yd, s_d, s_tgt, t0, p1, p2, ray1, ray2, C, k, ct.P, segs, sp.sigma_p, sp.sigma_a, s_max);
+                qn = 0;
+            }
+            __syncwarp();
+        }
+        // end of this camera group: add its best confidence (cudawrapper.cu:677-687, 709)
+        __syncwarp();
+        int best = s_max[tid];
+        total = xa(total, __int_as_float(best));
+        s_max[tid] = 0;
+        __syncwarp();
+    }
+    if (live) score[seg_start + y] = total;
+}
+
+// ------------------------------------------------------------------------------------------
+// per-segment reduction (cudawrapper.cu:1028-1064, 1090-1110): best match (first maximum),
+// number of matches with score > 1, depth samples of the best if its score > 0.5
+// ------------------------------------------------------------------------------------------
+__global__ void k_seg_reduce(const int* __restrict__ off, int n_cams, int n_src, const float* __restrict__ score,
+                             const float4* __restrict__ m_dep, int* __restrict__ fcnt, float* __restrict__ dsamples,
+                             unsigned long long* __restrict__ iters)
+{
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (row >= n_src) return;
+    const int s0 = off[row * n_cams], s1 = off[(row + 1) * n_cams];
+    float best = 0.0f; int bi = 0x7fffffff, nf = 0;
+    for (int k = s0 + lane; k < s1; k += 32) {
+        float c = score[k];
+        if (c > 1.0f) ++nf;
+        if (c > best) { best = c; bi = k; }           // strict: the first maximum within this lane's stride
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        float ob = __shfl_xor_sync(0xffffffffu, best, o); int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        nf += __shfl_xor_sync(0xffffffffu, nf, o);
+        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+    }
+    if (lane == 0) {
+        fcnt[row] = nf;
+        float a = INFINITY, b = INFINITY;
+        if (best > 0.5f) { float4 d = m_dep[bi]; a = d.x; b = d.y; }
+        dsamples[2 * row] = a; dsamples[2 * row + 1] = b;
+        unsigned long long m = (unsigned long long)(s1 - s0);
+        if (m) atomicAdd(iters, m * m);
+    }
+}
+
+// median of the finite samples: sorted[count / 2], -1 if none (cudawrapper.cu:1066-1076)
+__global__ void __launch_bounds__(1024) k_median(const float* __restrict__ dsamples, int n, int n_pow2, float* __restrict__ out)
+{
+    extern __shared__ float s[];
+    __shared__ int s_cnt;
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
+    int c = 0;
+    for (int i = threadIdx.x; i < n_pow2; i += blockDim.x) { float v = (i < n) ? dsamples[i] : INFINITY; s[i] = v; if (v < INFINITY) ++c; }
+    atomicAdd(&s_cnt, c);
+    __syncthreads();
+    for (int k = 2; k <= n_pow2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < n_pow2; i += blockDim.x) {
+                int l = i ^ j;
+                if (l > i) {
+                    float a = s[i], b = s[l];
+                    bool up = ((i & k) == 0);
+                    if ((a > b) == up) { s[i] = b; s[l] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    if (threadIdx.x == 0) out[0] = s_cnt ? s[s_cnt / 2] : -1.0f;
+}
+
+// filtered records in order, one warp per segment
+__global__ void k_filter_fill(const int* __restrict__ off, int n_cams, int n_src, const float* __restrict__ score,
+                              const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, const int* __restrict__ foff,
+                              l3d_match* __restrict__ out)
+{
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (row >= n_src) return;
+    const int s0 = off[row * n_cams], s1 = off[(row + 1) * n_cams];
+    int o = foff[row];
+    if (foff[row + 1] == o) return;
+    for (int k0 = s0; k0 < s1; k0 += 32) {
+        const int k = k0 + lane;
+        float c = (k < s1) ? score[k] : 0.0f;
+        bool keep = c > 1.0f;
+        unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (keep) {
+            int r = o + __popc(m & ((1u << lane) - 1u));
+            int4 id = m_ids[k]; float4 d = m_dep[k];
+            l3d_match rec; rec.src_seg = id.x; rec.cam = id.y; rec.tgt_seg = id.z; rec.confidence = xd(c, 2.0f);
+            rec.depths[0] = d.x; rec.depths[1] = d.y; rec.depths[2] = d.z; rec.depths[3] = d.w;
+            out[r] = rec;
+        }
+        o += __popc(m);
+    }
+}
+// unscored variant (no neighbour to pair-test): all records, confidence 0
+__global__ void k_copy_unscored(const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, int M, l3d_match* __restrict__ out)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= M) return;
+    int4 id = m_ids[k]; float4 d = m_dep[k];
+    l3d_match rec; rec.src_seg = id.x; rec.cam = id.y; rec.tgt_seg = id.z; rec.confidence = 0.0f;
+    rec.depths[0] = d.x; rec.depths[1] = d.y; rec.depths[2] = d.z; rec.depths[3] = d.w;
+    out[k] = rec;
+}
+
+// ------------------------------------------------------------------------------------------
+// hand-over (line3D.cc:838-858): the filtered records towards each neighbour that asked for
+// delivery, reversed and regrouped by the neighbour's segment, target ids ascending
+// ------------------------------------------------------------------------------------------
+__global__ void k_deliver_hist(const l3d_match* __restrict__ f, int F, const CamTable* __restrict__ cams, int stride, int* __restrict__ hist)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= F) return;
+    const int d = cams[f[k].cam].deliver;
+    if (d >= 0) atomicAdd(&hist[d * stride + f[k].tgt_seg], 1);
+}
+__global__ void k_deliver_scatter(const l3d_match* __restrict__ f, int F, const CamTable* __restrict__ cams, int stride,
+                                  const int* __restrict__ start, int* __restrict__ cursor, int* __restrict__ t_tgt, float4* __restrict__ t_dep)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= F) return;
+    const l3d_match m = f[k];
+    const int d = cams[m.cam].deliver;
+    if (d < 0) return;
+    const int key = d * stride + m.tgt_seg;
+    const int pos = start[key] + atomicAdd(&cursor[key], 1);
+    t_tgt[pos] = m.src_seg;
+    t_dep[pos] = make_float4(m.depths[2], m.depths[3], m.depths[0], m.depths[1]);     // line3D.cc:852-855
+}
+// each group is tiny; order it by target id (unique within a group)
+__global__ void k_deliver_sort(const int* __restrict__ start, int n_keys, int* __restrict__ t_tgt, float4* __restrict__ t_dep)
+{
+    const int key = blockIdx.x * blockDim.x + threadIdx.x;
+    if (key >= n_keys) return;
+    const int a = start[key], b = start[key + 1];
+    for (int i = a + 1; i < b; ++i) {
+        int t = t_tgt[i]; float4 d = t_dep[i];
+        int j = i - 1;
+        while (j >= a && t_tgt[j] > t) { t_tgt[j + 1] = t_tgt[j]; t_dep[j + 1] = t_dep[j]; --j; }
+        t_tgt[j + 1] = t; t_dep[j + 1] = d;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// collinearity (cudawrapper.cu:476-535): upper triangle, compacted on the device
+// ------------------------------------------------------------------------------------------
+__global__ void k_collin_count(const float4* __restrict__ segs, int n, float sigma_sqr, int* __restrict__ cnt, unsigned* __restrict__ bits, int wpr)
+{
+    const int i = blockIdx.y;
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= wpr) return;
+    const float4 a = segs[i];
+    unsigned m = 0;
+    for (int b = 0; b < 32; ++b) {
+        const int j = w * 32 + b;
+        if (j > i && j < n && xcollinearity(a, segs[j], sigma_sqr) > 0.0f) m |= 1u << b;
+    }
+    bits[size_t(i) * wpr + w] = m;
+    if (m) atomicAdd(&cnt[i], __popc(m));
+}
+__global__ void k_collin_fill(const float4* __restrict__ segs, int n, float sigma_sqr, const int* __restrict__ off, const unsigned* __restrict__ bits,
+                              int wpr, l3d_collin_pair* __restrict__ out)
+{
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i >= n) return;
+    int o = off[i];
+    if (off[i + 1] == o) return;
+    const float4 a = segs[i];
+    for (int w0 = 0; w0 < wpr; w0 += 32) {
+        unsigned m = (w0 + lane < wpr) ? bits[size_t(i) * wpr + w0 + lane] : 0u;
+        int c = __popc(m), ex = c;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { int y = __shfl_up_sync(0xffffffffu, ex, s); if (lane >= s) ex += y; }
+        int tot = __shfl_sync(0xffffffffu, ex, 31);
+        int pos = o + ex - c;
+        while (m) {
+            int b = __ffs(m) - 1; m &= m - 1;
+            int j = (w0 + lane) * 32 + b;
+            l3d_collin_pair p; p.i = i; p.j = j; p.value = xcollinearity(a, segs[j], sigma_sqr);
+            out[pos++] = p;
+        }
+        o += tot;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// hypotheses (view.cc:302-342) and affinity (line3D.cc:1600-1691), FP64
+// ------------------------------------------------------------------------------------------
+struct ViewD { double RtKinv[9]; double C[3]; float k_lower, k_upper; int seg_off; int n_seg; };
+struct Hyp { double P1[3], P2[3], dir[3]; float d1, d2; int view; int pad; };
+
+__device__ __forceinline__ void d_normalize(double* v)
+{
+    double n = sqrt(__dadd_rn(__dadd_rn(__dmul_rn(v[0], v[0]), __dmul_rn(v[1], v[1])), __dmul_rn(v[2], v[2])));
+    v[0] = __ddiv_rn(v[0], n); v[1] = __ddiv_rn(v[1], n); v[2] = __ddiv_rn(v[2], n);
+}
+__global__ void k_unproject(const float4* __restrict__ segs, const ViewD* __restrict__ views, const l3d_hypothesis_in* __restrict__ in, size_t n,
+                            Hyp* __restrict__ hyp, l3d_segment3d* __restrict__ out)
+{
+    const size_t k = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const l3d_hypothesis_in h = in[k];
+    const ViewD& v = views[h.view];
+    const float4 s = segs[v.seg_off + h.seg];
+    const double p[2][3] = {{double(s.x), double(s.y), 1.0}, {double(s.z), double(s.w), 1.0}};
+    const double dep[2] = {double(h.depth1), double(h.depth2)};
+    Hyp o; double P[2][3];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+        double r[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            double acc = 0.0;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) acc = __dadd_rn(acc, __dmul_rn(v.RtKinv[a * 3 + c], p[e][c]));
+            r[a] = acc;
+        }
+        d_normalize(r);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) P[e][a] = __dadd_rn(v.C[a], __dmul_rn(r[a], dep[e]));
+    }
+    double d[3] = {__dsub_rn(P[1][0], P[0][0]), __dsub_rn(P[1][1], P[0][1]), __dsub_rn(P[1][2], P[0][2])};
+    d_normalize(d);
+    l3d_segment3d so;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { o.P1[a] = P[0][a]; o.P2[a] = P[1][a]; o.dir[a] = d[a]; so.P1[a] = P[0][a]; so.P2[a] = P[1][a]; so.dir[a] = d[a]; }
+    o.d1 = h.depth1; o.d2 = h.depth2; o.view = h.view; o.pad = 0;
+    hyp[k] = o; out[k] = so;
+}
+
+// line3D.cc:1684-1691: |P1 + (dir (X - P1)^T) dir - X|, the outer product evaluated first
+__device__ __forceinline__ float d_point_line(const Hyp& s, const double* X)
+{
+    double v[3] = {__dsub_rn(X[0], s.P1[0]), __dsub_rn(X[1], s.P1[1]), __dsub_rn(X[2], s.P1[2])};
+    double e[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        double acc = 0.0;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) acc = __dadd_rn(acc, __dmul_rn(__dmul_rn(s.dir[i], v[j]), s.dir[j]));
+        e[i] = __dsub_rn(__dadd_rn(s.P1[i], acc), X[i]);
+    }
+    return float(sqrt(__dadd_rn(__dadd_rn(__dmul_rn(e[0], e[0]), __dmul_rn(e[1], e[1])), __dmul_rn(e[2], e[2]))));
+}
+// view.cc:353-377
+__device__ __forceinline__ float d_sim_term(float d, float depth, float k_lower, float k_upper, float median, float neg2log)
+{
+    float lo = depth < median ? xm(k_lower, depth) : xm(k_lower, median);
+    float up = depth < median ? xm(k_upper, depth) : xm(k_upper, median);
+    if (d < lo) return 1.0f;
+    float diff = xs(up, lo);
+    float sig = xd(xm(-diff, diff), neg2log);                      // -(d2-d1)^2 / (2 logf(0.01f))
+    float t = xs(d, lo);
+    return xexpf(xd(xm(-t, t), xm(2.0f, sig)));
+}
+__global__ void k_affinity(const Hyp* __restrict__ hyp, const ViewD* __restrict__ views, const float* __restrict__ median,
+                           const l3d_pair* __restrict__ pairs, size_t n, float sigma_a, float two_log001, float* __restrict__ out)
+{
+    const size_t k = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const Hyp a = hyp[pairs[k].a], b = hyp[pairs[k].b];
+    const ViewD& va = views[a.view]; const ViewD& vb = views[b.view];
+    const float ma = median[a.view], mb = median[b.view];
+    float s1 = d_sim_term(d_point_line(b, a.P1), a.d1, va.k_lower, va.k_upper, ma, two_log001);
+    float s2 = d_sim_term(d_point_line(b, a.P2), a.d2, va.k_lower, va.k_upper, ma, two_log001);
+    float s3 = d_sim_term(d_point_line(a, b.P1), b.d1, vb.k_lower, vb.k_upper, mb, two_log001);
+    float s4 = d_sim_term(d_point_line(a, b.P2), b.d2, vb.k_lower, vb.k_upper, mb, two_log001);
+    float w_d = fminf(fminf(s1, s2), fminf(s3, s4));
+    double dt = __dadd_rn(__dadd_rn(__dmul_rn(a.dir[0], b.dir[0]), __dmul_rn(a.dir[1], b.dir[1])), __dmul_rn(a.dir[2], b.dir[2]));
+    float angle = float(acos(fmax(fmin(dt, 1.0), -1.0)) / 3.14159265358979323846 * 180.0);
+    if (angle > 90.0f) angle = xs(180.0f, angle);
+    float w_a = xexpf(xd(xm(-angle, angle), xm(xm(2.0f, sigma_a), sigma_a)));
+    float sim = fminf(w_d, w_a);
+    out[k] = (sim <= 0.01f) ? 0.0f : sim;
+}
+
+// ------------------------------------------------------------------------------------------
+// diffusion (cudawrapper.cu:717-829, 1131-1191)
+// ------------------------------------------------------------------------------------------
+// P: row-sorted entries (row, col, val); W: column-sorted.  rstart/cstart: first entry of a
+// row of P / a column of W.  tpos[y] = position in P of the entry (col_y, row_y).
+__global__ void k_rdd_normalise(const int* __restrict__ prow, float* __restrict__ pval, const int* __restrict__ rstart, int n, int nnz)
+{
+    const int y = blockIdx.x * blockDim.x + threadIdx.x;
+    if (y >= n) return;
+    const int s = rstart[y];
+    if (s < 0) return;
+    float sum = 0.0f;
+    int i = s;
+    while (i < nnz && prow[i] == y) { sum = xa(sum, pval[i]); ++i; }
+    if (sum < L3D_EPS_F) sum = L3D_EPS_F;
+    for (int k = s; k < i; ++k) pval[k] = xd(pval[k], sum);
+}
+__global__ void k_rdd_step(const int* __restrict__ prow, const int* __restrict__ pcol, const float* __restrict__ pval,
+                           const int* __restrict__ wcol, const float* __restrict__ wval,
+                           const int* __restrict__ rstart, const int* __restrict__ cstart, const int* __restrict__ tpos,
+                           float* __restrict__ pnext, int nnz)
+{
+    const int y = blockIdx.x * blockDim.x + threadIdx.x;
+    if (y >= nnz) return;
+    const int r = pcol[y], c = prow[y];                     // transposed (cudawrapper.cu:778-780)
+    float mul = 0.0f;
+    int sp = rstart[r], sw = cstart[c];
+    while (sp >= 0 && sw >= 0 && sp < nnz && sw < nnz) {    // lockstep walk (cudawrapper.cu:786-800)
+        if (prow[sp] != r || wcol[sw] != c) break;
+        mul = xa(mul, xm(pval[sp], wval[sw]));
+        ++sp; ++sw;
+    }
+    mul = xm(mul, pval[y]);
+    if (mul < L3D_EPS_F) mul = L3D_EPS_F;
+    if (tpos[y] >= 0) pnext[tpos[y]] = mul;
+}
+
+// FP32 FFMA throughput probe
+__global__ void k_fma_probe(float* out, int iters)
+{
+    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
+    const float b = 1.0000001f, c = 1e-7f;
+    for (int i = 0; i < iters; ++i) {
+        a0 = fmaf(a0, b, c); a1 = fmaf(a1, b, c); a2 = fmaf(a2, b, c); a3 = fmaf(a3, b, c);
+        a4 = fmaf(a4, b, c); a5 = fmaf(a5, b, c); a6 = fmaf(a6, b, c); a7 = fmaf(a7, b, c);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+}  // namespace
+
+// ==========================================================================================
+// context
+// ==========================================================================================
+struct Delivered {            // records a source view handed to a later view
+    int from_view = -1;
+    int count = 0;
+    int* t_start = nullptr;   // n_seg(to) + 1, points into the owning buffer
+    int* t_tgt = nullptr;
+    float4* t_dep = nullptr;
+    int owner = -1;           // index into ctx->deliver_bufs
+};
+struct DeliverBuf { int* start = nullptr; int* tgt = nullptr; float4* dep = nullptr; int refs = 0; };
+
+struct l3d_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    // views
+    int V = 0;
+    std::vector<l3d_view> views;          // host copies (segments pointer not kept)
+    std::vector<int> seg_off;
+    int total_segs = 0, max_seg = 0;
+    DBuf<float4> d_segs;
+    DBuf<ViewD> d_viewd;
+    std::vector<std::vector<Delivered> > delivered;   // per destination view
+    std::vector<DeliverBuf> deliver_bufs;
+    // scratch
+    DBuf<CamTable> d_cams; DBuf<int> d_slot_cam;
+    DBuf<SrcHoist> d_sh; DBuf<TgtHoist> d_th;
+    DBuf<unsigned> d_cand; DBuf<int> d_cand_cnt, d_cand_off, d_tile_sums, d_total;
+    DBuf<int> d_stage_col; DBuf<float4> d_stage_dep;
+    DBuf<int> d_cnt, d_off;
+    DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
+    DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
+    DBuf<l3d_match> d_filtered;
+    DBuf<int> d_hist, d_hstart, d_cursor;
+    HBuf<l3d_match> h_filtered; HBuf<CamTable> h_cams; HBuf<int> h_ints; HBuf<float> h_floats; HBuf<unsigned long long> h_u64;
+    // collinearity
+    DBuf<float4> d_csegs; DBuf<unsigned> d_cbits; DBuf<int> d_ccnt, d_coff; DBuf<l3d_collin_pair> d_cpairs; HBuf<l3d_collin_pair> h_cpairs;
+    // hypotheses
+    DBuf<Hyp> d_hyp; size_t n_hyp = 0; DBuf<l3d_hypothesis_in> d_hin; DBuf<l3d_segment3d> d_hout;
+    DBuf<l3d_pair> d_pairs; DBuf<float> d_aff, d_medians;
+    // timing
+    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    float last_ms[6] = {0, 0, 0, 0, 0, 0};
+};
+
+namespace {
+
+int scan_exclusive(l3d_ctx* ctx, const int* in, int* out /* n + 1 */, int n)
+{
+    const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    if (tiles > SCAN_TILE) { ctx->err = "scan: input too long"; return 1; }
+    L3D_CUDA(ctx->d_tile_sums.ensure(size_t(std::max(tiles, 1))));
+    L3D_CUDA(ctx->d_total.ensure(1));
+    k_scan_tiles<<<std::max(tiles, 1), SCAN_T, 0, ctx->stream>>>(in, out, ctx->d_tile_sums.p, n);
+    k_scan_sums<<<1, SCAN_T, 0, ctx->stream>>>(ctx->d_tile_sums.p, tiles, ctx->d_total.p);
+    k_scan_add<<<std::max(tiles, 1), SCAN_T, 0, ctx->stream>>>(out, ctx->d_tile_sums.p, n, ctx->d_total.p);
+    ctx->launches += 3;
+    L3D_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int fetch_int(l3d_ctx* ctx, const int* dptr, int* out)
+{
+    L3D_CUDA(ctx->h_ints.ensure(16));
+    L3D_CUDA(cudaMemcpyAsync(ctx->h_ints.p, dptr, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+    *out = ctx->h_ints.p[0];
+    return 0;
+}
+
+void release_delivered(l3d_ctx* ctx, Delivered& d)
+{
+    if (d.owner >= 0) {
+        DeliverBuf& b = ctx->deliver_bufs[d.owner];
+        if (--b.refs == 0) {
+            cudaFreeAsync(b.start, ctx->stream); cudaFreeAsync(b.tgt, ctx->stream); cudaFreeAsync(b.dep, ctx->stream);
+            b.start = nullptr; b.tgt = nullptr; b.dep = nullptr;
+        }
+    }
+    d = Delivered();
+}
+
+int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float sigma_p, float sigma_a, l3d_match_result* res, bool copy_back)
+{
+    if (!ctx) return 1;
+    if (view < 0 || view >= ctx->V) { ctx->err = "l3d_match_view: view index out of range"; return 1; }
+    if (n_nb <= 0 || !nb || !res) { ctx->err = "l3d_match_view: no neighbours / null argument"; return 1; }
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    memset(res, 0, sizeof *res);
+    cudaStream_t st = ctx->stream;
+    const l3d_view& sv = ctx->views[view];
+    const int n_src = sv.n_segments;
+
+    // ---- tables -------------------------------------------------------------------------
+    L3D_CUDA(ctx->h_cams.ensure(size_t(n_nb)));
+    L3D_CUDA(ctx->h_ints.ensure(size_t(n_nb) + 64));
+    int n_slots = 0, n_deliver = 0, max_tgt = 1, max_deliver_seg = 1;
+    uint64_t pair_tests = 0;
+    std::vector<int> slot_cam;
+    std::vector<int> consumed;                       // indices into ctx->delivered[view]
+    for (int c = 0; c < n_nb; ++c) {
+        const l3d_neighbor& n = nb[c];
+        if (n.view < 0 || n.view >= ctx->V || n.view == view) { ctx->err = "l3d_match_view: bad neighbour view index"; return 1; }
+        if (c > 0 && nb[c - 1].view >= n.view) { ctx->err = "l3d_match_view: neighbours must be in ascending view order"; return 1; }
+        const l3d_view& tv = ctx->views[n.view];
+        CamTable& ct = ctx->h_cams.p[c];
+        memcpy(ct.F, n.F, sizeof ct.F); memcpy(ct.RtKinv, tv.RtKinv, sizeof ct.RtKinv);
+        memcpy(ct.P, tv.P, sizeof ct.P); memcpy(ct.C, tv.C, sizeof ct.C);
+        ct.seg_off = ctx->seg_off[n.view]; ct.n_seg = tv.n_segments;
+        ct.t_start = nullptr; ct.t_tgt = nullptr; ct.t_dep = nullptr; ct.slot = -1; ct.deliver = -1;
+        if (n.to_be_matched) {
+            ct.mode = 0; ct.slot = n_slots++; slot_cam.push_back(c);
+            max_tgt = std::max(max_tgt, tv.n_segments);
+            pair_tests += uint64_t(n_src) * uint64_t(tv.n_segments);
+        } else {
+            ct.mode = 2;
+            std::vector<Delivered>& dl = ctx->delivered[view];
+            for (size_t k = 0; k < dl.size(); ++k)
+                if (dl[k].from_view == n.view) { ct.mode = 1; ct.t_start = dl[k].t_start; ct.t_tgt = dl[k].t_tgt; ct.t_dep = dl[k].t_dep; res->n_delivered += uint64_t(dl[k].count); consumed.push_back(int(k)); break; }
+        }
+        if (n.deliver) { ct.deliver = n_deliver++; max_deliver_seg = std::max(max_deliver_seg, tv.n_segments); }
+    }
+    res->pair_tests = pair_tests;
+    SrcTable src;
+    memcpy(src.RtKinv, sv.RtKinv, sizeof src.RtKinv); memcpy(src.C, sv.C, sizeof src.C);
+    src.spatial_k = sv.spatial_k; src.cmax = std::max(std::fabs(sv.C[0]), std::max(std::fabs(sv.C[1]), std::fabs(sv.C[2])));
+    src.seg_off = ctx->seg_off[view]; src.n_seg = n_src;
+
+    L3D_CUDA(ctx->d_cams.ensure(size_t(n_nb)));
+    L3D_CUDA(cudaMemcpyAsync(ctx->d_cams.p, ctx->h_cams.p, sizeof(CamTable) * n_nb, cudaMemcpyHostToDevice, st));
+    L3D_CUDA(ctx->d_cnt.ensure(size_t(n_src) * n_nb + 1));
+    L3D_CUDA(ctx->d_off.ensure(size_t(n_src) * n_nb + 2));
+    L3D_CUDA(cudaEventRecord(ctx->ev[0], st));
+
+    // ---- pair tests -----------------------------------------------------------------------
+    int n_cand = 0;
+    if (n_slots > 0 && n_src > 0) {
+        for (int s = 0; s < n_slots; ++s) ctx->h_ints.p[s] = slot_cam[s];
+        L3D_CUDA(ctx->d_slot_cam.ensure(size_t(n_slots)));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_slot_cam.p, ctx->h_ints.p, sizeof(int) * n_slots, cudaMemcpyHostToDevice, st));
+        const int wpr = (max_tgt + 31) / 32;
+        L3D_CUDA(ctx->d_sh.ensure(size_t(n_slots) * n_src));
+        L3D_CUDA(ctx->d_th.ensure(size_t(n_slots) * max_tgt));
+        L3D_CUDA(ctx->d_cand.ensure(size_t(n_slots) * n_src * wpr));
+        L3D_CUDA(ctx->d_cand_cnt.ensure(size_t(n_src) * n_slots + 1));
+        L3D_CUDA(ctx->d_cand_off.ensure(size_t(n_src) * n_slots + 2));
+        L3D_CUDA(cudaMemsetAsync(ctx->d_cand_cnt.p, 0, sizeof(int) * (size_t(n_src) * n_slots + 1), st));
+        L3D_CUDA(cudaMemsetAsync(ctx->d_cand.p, 0, sizeof(unsigned) * size_t(n_slots) * n_src * wpr, st));
+        const int hn = std::max(n_src, max_tgt);
+        k_hoist<<<dim3((hn + 127) / 128, n_slots), 128, 0, st>>>(ctx->d_segs.p, ctx->d_cams.p, ctx->d_slot_cam.p, src, ctx->d_sh.p, ctx->d_th.p, n_src, max_tgt);
+        k_pretest<<<dim3((n_src + PT_THREADS - 1) / PT_THREADS, (max_tgt + PT_COLS - 1) / PT_COLS, n_slots), PT_THREADS, 0, st>>>(
+            ctx->d_sh.p, ctx->d_th.p, ctx->d_cams.p, ctx->d_slot_cam.p, n_src, n_src, max_tgt, wpr, ctx->d_cand.p, ctx->d_cand_cnt.p, n_slots);
+        ctx->launches += 2;
+        L3D_CUDA(cudaGetLastError());
+        if (scan_exclusive(ctx, ctx->d_cand_cnt.p, ctx->d_cand_off.p, n_src * n_slots)) return 1;
+        L3D_CUDA(cudaEventRecord(ctx->ev[1], st));
+        if (fetch_int(ctx, ctx->d_cand_off.p + size_t(n_src) * n_slots, &n_cand)) return 1;
+        L3D_CUDA(ctx->d_stage_col.ensure(size_t(std::max(n_cand, 1))));
+        L3D_CUDA(ctx->d_stage_dep.ensure(size_t(std::max(n_cand, 1))));
+        k_exact<<<dim3((n_src + EX_WARPS - 1) / EX_WARPS, n_slots), EX_WARPS * 32, 0, st>>>(
+            ctx->d_segs.p, ctx->d_cams.p, ctx->d_slot_cam.p, src, ctx->d_cand.p, ctx->d_cand_off.p, n_src, wpr, n_slots, n_nb,
+            ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_cnt.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+    } else {
+        L3D_CUDA(cudaEventRecord(ctx->ev[1], st));
+    }
+    res->n_candidates = uint64_t(n_cand);
+    L3D_CUDA(cudaEventRecord(ctx->ev[2], st));
+
+    // ---- assemble the match list ----------------------------------------------------------
+    int M = 0;
+    if (n_src > 0) {
+        k_delivered_counts<<<dim3((n_src + 255) / 256, n_nb), 256, 0, st>>>(ctx->d_cams.p, n_nb, n_src, ctx->d_cnt.p);
+        ctx->launches += 1;
+        if (scan_exclusive(ctx, ctx->d_cnt.p, ctx->d_off.p, n_src * n_nb)) return 1;
+        if (fetch_int(ctx, ctx->d_off.p + size_t(n_src) * n_nb, &M)) return 1;
+    }
+    res->n_scored = uint64_t(M);
+    res->n_raw = uint64_t(M) - res->n_delivered;
+    if (M > 0) {
+        L3D_CUDA(ctx->d_mids.ensure(size_t(M))); L3D_CUDA(ctx->d_mdep.ensure(size_t(M))); L3D_CUDA(ctx->d_score.ensure(size_t(M)));
+        const long warps = long(n_src) * n_nb;
+        k_fill<<<unsigned((warps * 32 + 255) / 256), 256, 0, st>>>(ctx->d_cams.p, n_nb, std::max(n_slots, 1), n_src, ctx->d_off.p, ctx->d_cand_off.p,
+                                                                  ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_mids.p, ctx->d_mdep.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+    }
+    L3D_CUDA(cudaEventRecord(ctx->ev[3], st));
+
+    int F = 0;
+    float median = 1.0f;                              // line3D.cc:811
+    const bool scored = n_slots > 0;                  // cudawrapper.cu:877-878
+    res->scored = scored ? 1 : 0;
+    if (scored && M > 0) {
+        // ---- score ------------------------------------------------------------------------
+        int max_m = M;                                // upper bound on matches per segment
+        ScoreParams sp; sp.sigma_p = sigma_p; sp.sigma_a = sigma_a;
+        // grid.x covers the longest segment; shorter ones exit at once
+        L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_src) + 1)); L3D_CUDA(ctx->d_foff.ensure(size_t(n_src) + 2));
+        L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2)); L3D_CUDA(ctx->d_median.ensure(4)); L3D_CUDA(ctx->d_iters.ensure(1));
+        L3D_CUDA(cudaMemsetAsync(ctx->d_iters.p, 0, sizeof(unsigned long long), st));
+        // longest segment: take it from the count matrix on the host side cheaply via the reduce kernel's iteration count later;
+        // here bound it by the number of target segments summed over cameras
+        long bound = 0;
+        for (int c = 0; c < n_nb; ++c) bound += ctx->views[nb[c].view].n_segments;
+        max_m = int(std::min<long>(M, bound));
+        k_score<<<dim3((max_m + SC_T - 1) / SC_T, n_src), SC_T, 0, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p, sp, ctx->d_score.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+        L3D_CUDA(cudaEventRecord(ctx->ev[4], st));
+        // ---- reduce -----------------------------------------------------------------------
+        k_seg_reduce<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, ctx->d_iters.p);
+        int np2 = 2; while (np2 < 2 * n_src) np2 <<= 1;
+        if (np2 * sizeof(float) > 200 * 1024) { ctx->err = "l3d_match_view: too many segments for the median kernel"; return 1; }
+        if (np2 * sizeof(float) > 48 * 1024) L3D_CUDA(cudaFuncSetAttribute(k_median, cudaFuncAttributeMaxDynamicSharedMemorySize, int(np2 * sizeof(float))));
+        k_median<<<1, 1024, np2 * sizeof(float), st>>>(ctx->d_dsamples.p, 2 * n_src, np2, ctx->d_median.p);
+        ctx->launches += 2;
+        if (scan_exclusive(ctx, ctx->d_fcnt.p, ctx->d_foff.p, n_src)) return 1;
+        if (fetch_int(ctx, ctx->d_foff.p + n_src, &F)) return 1;
+        L3D_CUDA(ctx->h_floats.ensure(4)); L3D_CUDA(ctx->h_u64.ensure(1));
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_floats.p, ctx->d_median.p, sizeof(float), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_u64.p, ctx->d_iters.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(ctx->d_filtered.ensure(size_t(std::max(F, 1))));
+        if (F > 0) {
+            k_filter_fill<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, ctx->d_filtered.p);
+            ctx->launches += 1;
+        }
+        L3D_CUDA(cudaGetLastError());
+    } else {
+        L3D_CUDA(cudaEventRecord(ctx->ev[4], st));
+        if (!scored && M > 0) {
+            F = M;
+            L3D_CUDA(ctx->d_filtered.ensure(size_t(F)));
+            k_copy_unscored<<<(M + 255) / 256, 256, 0, st>>>(ctx->d_mids.p, ctx->d_mdep.p, M, ctx->d_filtered.p);
+            ctx->launches += 1;
+            L3D_CUDA(cudaGetLastError());
+        }
+    }
+
+    // ---- hand-over to later views ---------------------------------------------------------
+    if (n_deliver > 0 && scored) {
+        const int stride = max_deliver_seg + 1;                    // one spare key per slot keeps t_start[n_seg] addressable
+        const int n_keys = n_deliver * stride;
+        DeliverBuf buf; buf.refs = n_deliver;
+        L3D_CUDA(cudaMallocAsync(&buf.start, sizeof(int) * (size_t(n_keys) + 2), st));
+        L3D_CUDA(cudaMallocAsync(&buf.tgt, sizeof(int) * size_t(std::max(F, 1)), st));
+        L3D_CUDA(cudaMallocAsync(&buf.dep, sizeof(float4) * size_t(std::max(F, 1)), st));
+        L3D_CUDA(ctx->d_hist.ensure(size_t(n_keys) + 1)); L3D_CUDA(ctx->d_cursor.ensure(size_t(n_keys) + 1));
+        L3D_CUDA(cudaMemsetAsync(ctx->d_hist.p, 0, sizeof(int) * (size_t(n_keys) + 1), st));
+        L3D_CUDA(cudaMemsetAsync(ctx->d_cursor.p, 0, sizeof(int) * (size_t(n_keys) + 1), st));
+        if (F > 0) { k_deliver_hist<<<(F + 255) / 256, 256, 0, st>>>(ctx->d_filtered.p, F, ctx->d_cams.p, stride, ctx->d_hist.p); ctx->launches += 1; }
+        if (scan_exclusive(ctx, ctx->d_hist.p, buf.start, n_keys)) return 1;
+        if (F > 0) {
+            k_deliver_scatter<<<(F + 255) / 256, 256, 0, st>>>(ctx->d_filtered.p, F, ctx->d_cams.p, stride, buf.start, ctx->d_cursor.p, buf.tgt, buf.dep);
+            k_deliver_sort<<<(n_keys + 255) / 256, 256, 0, st>>>(buf.start, n_keys, buf.tgt, buf.dep);
+            ctx->launches += 2;
+        }
+        L3D_CUDA(cudaGetLastError());
+        // per-slot totals are needed on the host only for accounting: read the slot boundaries
+        L3D_CUDA(ctx->h_ints.ensure(size_t(n_deliver) + 17));
+        for (int d = 0; d <= n_deliver; ++d)
+            L3D_CUDA(cudaMemcpyAsync(ctx->h_ints.p + 16 + d, buf.start + size_t(d) * stride, sizeof(int), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaStreamSynchronize(st));
+        const int owner = int(ctx->deliver_bufs.size());
+        ctx->deliver_bufs.push_back(buf);
+        for (int c = 0; c < n_nb; ++c) {
+            const int d = ctx->h_cams.p[c].deliver;
+            if (d < 0) continue;
+            Delivered dl; dl.from_view = view; dl.owner = owner;
+            dl.count = ctx->h_ints.p[16 + d + 1] - ctx->h_ints.p[16 + d];
+            dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
+            ctx->delivered[nb[c].view].push_back(dl);
+        }
+    }
+    L3D_CUDA(cudaEventRecord(ctx->ev[5], st));
+
+    // ---- results --------------------------------------------------------------------------
+    if (copy_back && F > 0) {
+        L3D_CUDA(ctx->h_filtered.ensure(size_t(F)));
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_filtered.p, ctx->d_filtered.p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, st));
+    }
+    L3D_CUDA(cudaStreamSynchronize(st));
+    if (scored && M > 0) { median = ctx->h_floats.p[0]; res->score_iters = ctx->h_u64.p[0]; }
+    res->median_depth = median;
+    res->n_filtered = uint64_t(F);
+    res->filtered = (copy_back && F > 0) ? ctx->h_filtered.p : nullptr;
+    // the consumed deliveries are no longer needed
+    {
+        std::vector<Delivered>& dl = ctx->delivered[view];
+        for (size_t k = 0; k < consumed.size(); ++k) release_delivered(ctx, dl[consumed[k]]);
+        std::vector<Delivered> keep;
+        for (size_t k = 0; k < dl.size(); ++k) if (dl[k].from_view >= 0) keep.push_back(dl[k]);
+        dl.swap(keep);
+    }
+    float ms;
+    for (int k = 0; k < 5; ++k) { ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[k], ctx->ev[k + 1]); ctx->last_ms[k] = ms; }
+    ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[5]); ctx->last_ms[5] = ms;
+    return 0;
+}
+
+}  // namespace
+
+// ==========================================================================================
+// C ABI
+// ==========================================================================================
+extern "C" {
+
+int l3d_create(int device, l3d_ctx** out)
+{
+    if (!out) { g_create_error = "l3d_create: null output pointer"; return 1; }
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) { g_create_error = std::string("l3d_create: no CUDA device (") + cudaGetErrorString(e) + "); this library has no CPU path"; return 1; }
+    if (device < 0 || device >= n) { g_create_error = "l3d_create: device index out of range"; return 1; }
+    if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_error = std::string("l3d_create: cudaSetDevice: ") + cudaGetErrorString(e); return 1; }
+    l3d_ctx* ctx = new l3d_ctx();
+    ctx->device = device;
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); delete ctx; return 1; }
+    for (int k = 0; k < 8; ++k) cudaEventCreate(&ctx->ev[k]);
+    *out = ctx;
+    return 0;
+}
+
+int l3d_reset_matching(l3d_ctx* ctx)
+{
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    for (size_t v = 0; v < ctx->delivered.size(); ++v) {
+        for (size_t k = 0; k < ctx->delivered[v].size(); ++k) release_delivered(ctx, ctx->delivered[v][k]);
+        ctx->delivered[v].clear();
+    }
+    ctx->deliver_bufs.clear();
+    cudaStreamSynchronize(ctx->stream);
+    return 0;
+}
+
+void l3d_destroy(l3d_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    l3d_reset_matching(ctx);
+    ctx->d_segs.release(); ctx->d_viewd.release(); ctx->d_cams.release(); ctx->d_slot_cam.release(); ctx->d_sh.release(); ctx->d_th.release();
+    ctx->d_cand.release(); ctx->d_cand_cnt.release(); ctx->d_cand_off.release(); ctx->d_tile_sums.release(); ctx->d_total.release();
+    ctx->d_stage_col.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
+    ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
+    ctx->d_filtered.release(); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
+    ctx->h_filtered.release(); ctx->h_cams.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
+    ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
+    ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release();
+    for (int k = 0; k < 8; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* l3d_last_error(const l3d_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+uint64_t l3d_kernel_launches(const l3d_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int l3d_collinearity(l3d_ctx* ctx, const float* segments, int n, float collin_s, const l3d_collin_pair** pairs, size_t* count)
+{
+    if (!ctx) return 1;
+    if (!pairs || !count || (n > 0 && !segments)) { ctx->err = "l3d_collinearity: null argument"; return 1; }
+    *pairs = nullptr; *count = 0;
+    if (n <= 1) return 0;
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int wpr = (n + 31) / 32;
+    L3D_CUDA(ctx->d_csegs.ensure(size_t(n))); L3D_CUDA(ctx->d_cbits.ensure(size_t(n) * wpr));
+    L3D_CUDA(ctx->d_ccnt.ensure(size_t(n) + 1)); L3D_CUDA(ctx->d_coff.ensure(size_t(n) + 2));
+    L3D_CUDA(cudaMemcpyAsync(ctx->d_csegs.p, segments, sizeof(float4) * size_t(n), cudaMemcpyHostToDevice, st));
+    L3D_CUDA(cudaMemsetAsync(ctx->d_ccnt.p, 0, sizeof(int) * (size_t(n) + 1), st));
+    const float s2 = collin_s * collin_s;                                       // cudawrapper.cu:850
+    k_collin_count<<<dim3((wpr + 63) / 64, n), 64, 0, st>>>(ctx->d_csegs.p, n, s2, ctx->d_ccnt.p, ctx->d_cbits.p, wpr);
+    ctx->launches += 1;
+    L3D_CUDA(cudaGetLastError());
+    if (scan_exclusive(ctx, ctx->d_ccnt.p, ctx->d_coff.p, n)) return 1;
+    int total = 0;
+    if (fetch_int(ctx, ctx->d_coff.p + n, &total)) return 1;
+    if (total == 0) return 0;
+    L3D_CUDA(ctx->d_cpairs.ensure(size_t(total))); L3D_CUDA(ctx->h_cpairs.ensure(size_t(total)));
+    k_collin_fill<<<(n * 32 + 255) / 256, 256, 0, st>>>(ctx->d_csegs.p, n, s2, ctx->d_coff.p, ctx->d_cbits.p, wpr, ctx->d_cpairs.p);
+    ctx->launches += 1;
+    L3D_CUDA(cudaGetLastError());
+    L3D_CUDA(cudaMemcpyAsync(ctx->h_cpairs.p, ctx->d_cpairs.p, sizeof(l3d_collin_pair) * size_t(total), cudaMemcpyDeviceToHost, st));
+    L3D_CUDA(cudaStreamSynchronize(st));
+    *pairs = ctx->h_cpairs.p; *count = size_t(total);
+    return 0;
+}
+
+int l3d_set_views(l3d_ctx* ctx, int n_views, const l3d_view* views)
+{
+    if (!ctx) return 1;
+    if (n_views <= 0 || !views) { ctx->err = "l3d_set_views: no views"; return 1; }
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    l3d_reset_matching(ctx);
+    ctx->V = n_views;
+    ctx->views.assign(views, views + n_views);
+    ctx->seg_off.assign(size_t(n_views) + 1, 0);
+    ctx->max_seg = 0;
+    for (int v = 0; v < n_views; ++v) {
+        if (views[v].n_segments < 0 || (views[v].n_segments > 0 && !views[v].segments)) { ctx->err = "l3d_set_views: bad segment array"; return 1; }
+        if (views[v].n_segments > 65535) { ctx->err = "l3d_set_views: more than 65535 segments in a view"; return 1; }
+        ctx->seg_off[v + 1] = ctx->seg_off[v] + views[v].n_segments;
+        ctx->max_seg = std::max(ctx->max_seg, views[v].n_segments);
+    }
+    ctx->total_segs = ctx->seg_off[n_views];
+    L3D_CUDA(ctx->d_segs.ensure(size_t(std::max(ctx->total_segs, 1))));
+    L3D_CUDA(ctx->d_viewd.ensure(size_t(n_views)));
+    std::vector<ViewD> vd(n_views);
+    for (int v = 0; v < n_views; ++v) {
+        if (views[v].n_segments)
+            L3D_CUDA(cudaMemcpyAsync(ctx->d_segs.p + ctx->seg_off[v], views[v].segments, sizeof(float4) * size_t(views[v].n_segments), cudaMemcpyHostToDevice, ctx->stream));
+        memcpy(vd[v].RtKinv, views[v].RtKinv_d, sizeof vd[v].RtKinv); memcpy(vd[v].C, views[v].C_d, sizeof vd[v].C);
+        vd[v].k_lower = views[v].k_lower; vd[v].k_upper = views[v].k_upper; vd[v].seg_off = ctx->seg_off[v]; vd[v].n_seg = views[v].n_segments;
+        ctx->views[v].segments = nullptr;
+    }
+    L3D_CUDA(cudaMemcpyAsync(ctx->d_viewd.p, vd.data(), sizeof(ViewD) * size_t(n_views), cudaMemcpyHostToDevice, ctx->stream));
+    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->delivered.assign(size_t(n_views), std::vector<Delivered>());
+    ctx->n_hyp = 0;
+    return 0;
+}
+
+int l3d_match_view(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors, float sigma_p, float sigma_a, l3d_match_result* result)
+{
+    return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, true);
+}
+int l3d_match_view_resident(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors, float sigma_p, float sigma_a, l3d_match_result* result)
+{
+    return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, false);
+}
+
+int l3d_unproject(l3d_ctx* ctx, size_t n, const l3d_hypothesis_in* in, l3d_segment3d* out)
+{
+    if (!ctx) return 1;
+    if (n == 0) { ctx->n_hyp = 0; return 0; }
+    if (!in || !out) { ctx->err = "l3d_unproject: null argument"; return 1; }
+    for (size_t k = 0; k < n; ++k)
+        if (in[k].view < 0 || in[k].view >= ctx->V || in[k].seg < 0 || in[k].seg >= ctx->views[in[k].view].n_segments) { ctx->err = "l3d_unproject: view/segment out of range"; return 1; }
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    L3D_CUDA(ctx->d_hin.ensure(n)); L3D_CUDA(ctx->d_hout.ensure(n)); L3D_CUDA(ctx->d_hyp.ensure(n));
+    L3D_CUDA(cudaMemcpyAsync(ctx->d_hin.p, in, sizeof(l3d_hypothesis_in) * n, cudaMemcpyHostToDevice, ctx->stream));
+    k_unproject<<<unsigned((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_segs.p, ctx->d_viewd.p, ctx->d_hin.p, n, ctx->d_hyp.p, ctx->d_hout.p);
+    ctx->launches += 1;
+    L3D_CUDA(cudaGetLastError());
+    L3D_CUDA(cudaMemcpyAsync(out, ctx->d_hout.p, sizeof(l3d_segment3d) * n, cudaMemcpyDeviceToHost, ctx->stream));
+    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->n_hyp = n;
+    return 0;
+}
+
+int l3d_affinity(l3d_ctx* ctx, const float* median_depth, size_t n_pairs, const l3d_pair* pairs, float sigma_a, float* out)
+{
+    if (!ctx) return 1;
+    if (n_pairs == 0) return 0;
+    if (!median_depth || !pairs || !out) { ctx->err = "l3d_affinity: null argument"; return 1; }
+    if (ctx->n_hyp == 0) { ctx->err = "l3d_affinity: no hypotheses resident (call l3d_unproject first)"; return 1; }
+    for (size_t k = 0; k < n_pairs; ++k)
+        if (pairs[k].a < 0 || size_t(pairs[k].a) >= ctx->n_hyp || pairs[k].b < 0 || size_t(pairs[k].b) >= ctx->n_hyp) { ctx->err = "l3d_affinity: pair index out of range"; return 1; }
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    L3D_CUDA(ctx->d_pairs.ensure(n_pairs)); L3D_CUDA(ctx->d_aff.ensure(n_pairs)); L3D_CUDA(ctx->d_medians.ensure(size_t(ctx->V)));
+    L3D_CUDA(cudaMemcpyAsync(ctx->d_medians.p, median_depth, sizeof(float) * size_t(ctx->V), cudaMemcpyHostToDevice, ctx->stream));
+    L3D_CUDA(cudaMemcpyAsync(ctx->d_pairs.p, pairs, sizeof(l3d_pair) * n_pairs, cudaMemcpyHostToDevice, ctx->stream));
+    const float two_log = 2.0f * logf(0.01f);                                   // view.cc:376
+    k_affinity<<<unsigned((n_pairs + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_hyp.p, ctx->d_viewd.p, ctx->d_medians.p, ctx->d_pairs.p, n_pairs, sigma_a, two_log, ctx->d_aff.p);
+    ctx->launches += 1;
+    L3D_CUDA(cudaGetLastError());
+    L3D_CUDA(cudaMemcpyAsync(out, ctx->d_aff.p, sizeof(float) * n_pairs, cudaMemcpyDeviceToHost, ctx->stream));
+    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3d_edge* out)
+{
+    if (!ctx) return 1;
+    if (nnz == 0 || n_nodes <= 0) return 0;
+    if (!edges || !out) { ctx->err = "l3d_diffuse: null argument"; return 1; }
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int N = int(nnz);
+    for (int k = 0; k < N; ++k)
+        if (edges[k].i < 0 || edges[k].i >= n_nodes || edges[k].j < 0 || edges[k].j >= n_nodes) { ctx->err = "l3d_diffuse: node id out of range"; return 1; }
+    // W column-sorted (sparsematrix.cc:81-85), P row-sorted (sparsematrix.cc:158-161); the comparators order by the
+    // integer ids only, stable, so equal keys (none for a valid input) keep their list order
+    std::vector<int> wi(N), pi(N);
+    for (int k = 0; k < N; ++k) wi[k] = k;
+    std::stable_sort(wi.begin(), wi.end(), [&](int a, int b) { return edges[a].j < edges[b].j || (edges[a].j == edges[b].j && edges[a].i < edges[b].i); });
+    for (int k = 0; k < N; ++k) pi[k] = k;                                       // P is built from W's stored order
+    std::stable_sort(pi.begin(), pi.end(), [&](int a, int b) { const l3d_edge& x = edges[wi[a]]; const l3d_edge& y = edges[wi[b]]; return x.i < y.i || (x.i == y.i && x.j < y.j); });
+    std::vector<int> prow(N), pcol(N), wcol(N), rstart(n_nodes, -1), cstart(n_nodes, -1), tpos(N, -1);
+    std::vector<float> pval(N), wval(N);
+    for (int k = 0; k < N; ++k) { const l3d_edge& e = edges[wi[k]]; wcol[k] = e.j; wval[k] = e.w; if (cstart[e.j] < 0) cstart[e.j] = k; }
+    for (int k = 0; k < N; ++k) { const l3d_edge& e = edges[wi[pi[k]]]; prow[k] = e.i; pcol[k] = e.j; pval[k] = e.w; if (rstart[e.i] < 0) rstart[e.i] = k; }
+    for (int y = 0; y < N; ++y) {                                               // cudawrapper.cu:809-827: first entry (r, c) of row r = col_y with col == row_y
+        const int r = pcol[y], c = prow[y];
+        for (int s = rstart[r]; s >= 0 && s < N && prow[s] == r; ++s) if (pcol[s] == c) { tpos[y] = s; break; }
+    }
+    int *d_prow, *d_pcol, *d_wcol, *d_rstart, *d_cstart, *d_tpos; float *d_pa, *d_pb, *d_wval;
+    L3D_CUDA(cudaMallocAsync(&d_prow, sizeof(int) * N, st)); L3D_CUDA(cudaMallocAsync(&d_pcol, sizeof(int) * N, st)); L3D_CUDA(cudaMallocAsync(&d_wcol, sizeof(int) * N, st));
+    L3D_CUDA(cudaMallocAsync(&d_tpos, sizeof(int) * N, st)); L3D_CUDA(cudaMallocAsync(&d_rstart, sizeof(int) * n_nodes, st)); L3D_CUDA(cudaMallocAsync(&d_cstart, sizeof(int) * n_nodes, st));
+    L3D_CUDA(cudaMallocAsync(&d_pa, sizeof(float) * N, st)); L3D_CUDA(cudaMallocAsync(&d_pb, sizeof(float) * N, st)); L3D_CUDA(cudaMallocAsync(&d_wval, sizeof(float) * N, st));
+    L3D_CUDA(cudaMemcpyAsync(d_prow, prow.data(), sizeof(int) * N, cudaMemcpyHostToDevice, st)); L3D_CUDA(cudaMemcpyAsync(d_pcol, pcol.data(), sizeof(int) * N, cudaMemcpyHostToDevice, st));
+    L3D_CUDA(cudaMemcpyAsync(d_wcol, wcol.data(), sizeof(int) * N, cudaMemcpyHostToDevice, st)); L3D_CUDA(cudaMemcpyAsync(d_tpos, tpos.data(), sizeof(int) * N, cudaMemcpyHostToDevice, st));
+    L3D_CUDA(cudaMemcpyAsync(d_rstart, rstart.data(), sizeof(int) * n_nodes, cudaMemcpyHostToDevice, st)); L3D_CUDA(cudaMemcpyAsync(d_cstart, cstart.data(), sizeof(int) * n_nodes, cudaMemcpyHostToDevice, st));
+    L3D_CUDA(cudaMemcpyAsync(d_pa, pval.data(), sizeof(float) * N, cudaMemcpyHostToDevice, st)); L3D_CUDA(cudaMemcpyAsync(d_pb, pval.data(), sizeof(float) * N, cudaMemcpyHostToDevice, st));
+    L3D_CUDA(cudaMemcpyAsync(d_wval, wval.data(), sizeof(float) * N, cudaMemcpyHostToDevice, st));
+    const int rb = (n_nodes + 255) / 256, eb = (N + 255) / 256;
+    k_rdd_normalise<<<rb, 256, 0, st>>>(d_prow, d_pa, d_rstart, n_nodes, N);
+    ctx->launches += 1;
+    float* P = d_pa; float* Pn = d_pb;
+    for (int it = 0; it < 10; ++it) {                                           // L3D_RDD_MAX_ITER, cudawrapper.h:35
+        k_rdd_step<<<eb, 256, 0, st>>>(d_prow, d_pcol, P, d_wcol, d_wval, d_rstart, d_cstart, d_tpos, Pn, N);
+        std::swap(P, Pn);
+        ctx->launches += 1;
+        if (it < 9) { k_rdd_normalise<<<rb, 256, 0, st>>>(d_prow, P, d_rstart, n_nodes, N); ctx->launches += 1; }
+    }
+    L3D_CUDA(cudaGetLastError());
+    L3D_CUDA(cudaMemcpyAsync(pval.data(), P, sizeof(float) * N, cudaMemcpyDeviceToHost, st));
+    L3D_CUDA(cudaStreamSynchronize(st));
+    for (int k = 0; k < N; ++k) { out[k].i = prow[k]; out[k].j = pcol[k]; out[k].w = pval[k]; }
+    cudaFreeAsync(d_prow, st); cudaFreeAsync(d_pcol, st); cudaFreeAsync(d_wcol, st); cudaFreeAsync(d_tpos, st); cudaFreeAsync(d_rstart, st);
+    cudaFreeAsync(d_cstart, st); cudaFreeAsync(d_pa, st); cudaFreeAsync(d_pb, st); cudaFreeAsync(d_wval, st);
+    L3D_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int l3d_last_timings(l3d_ctx* ctx, float ms[6])
+{
+    if (!ctx || !ms) return 1;
+    for (int k = 0; k < 6; ++k) ms[k] = ctx->last_ms[k];
+    return 0;
+}
+
+int l3d_measure_fp32_peak(l3d_ctx* ctx, float* tflops)
+{
+    if (!ctx || !tflops) return 1;
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    cudaDeviceProp prop; L3D_CUDA(cudaGetDeviceProperties(&prop, ctx->device));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 16;
+    float* d = nullptr;
+    L3D_CUDA(cudaMalloc(&d, sizeof(float) * size_t(blocks) * threads));
+    k_fma_probe<<<blocks, threads, 0, ctx->stream>>>(d, 1024);
+    float best = 0.f;
+    for (int r = 0; r < 3; ++r) {
+        L3D_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
+        k_fma_probe<<<blocks, threads, 0, ctx->stream>>>(d, iters);
+        L3D_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+        L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+        float ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[7]);
+        double fl = double(blocks) * threads * double(iters) * 8.0 * 2.0;
+        best = std::max(best, float(fl / (double(ms) * 1e-3) / 1e12));
+    }
+    ctx->launches += 4;
+    cudaFree(d);
+    *tflops = best;
+    return 0;
+}
+
+}  // extern "C"

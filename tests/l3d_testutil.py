@@ -1,0 +1,69 @@
+"""Shared helpers for the parity tests: drive the C ABI view by view from tables dumped by
+the oracle (or the reference build), the way the host scaffold does (line3D.cc:698-885)."""
+from __future__ import annotations
+
+import os
+import tempfile
+
+import numpy as np
+
+
+def oracle_dump(scene_path, **params):
+    from oracle import oracle_py
+    d = tempfile.mkdtemp(prefix="l3d_oracle_")
+    n, tm, ct, dm = oracle_py.run_scene(scene_path, d, **params)
+    dm["_n_lines"] = n; dm["_timings"] = tm; dm["_counters"] = ct
+    return dm
+
+
+def tables_from_dump(dm, scene):
+    """views.npy columns: id, median, k_upper, k_lower, spatial_k, C(3), RtKinv(9), P(12), K(9), R(9), t(3)."""
+    vw = dm["views"]
+    ids = [int(x) for x in vw[:, 0]]
+    by_id = {v.id: v for v in scene.views}
+    views = []
+    for r in vw:
+        views.append(dict(id=int(r[0]), segs=by_id[int(r[0])].segs, k_upper=np.float32(r[2]), k_lower=np.float32(r[3]),
+                          spatial_k=np.float32(r[4]), C=r[5:8], RtKinv=r[8:17], P=r[17:29]))
+    F = {(int(r[0]), int(r[1])): r[2:11].reshape(3, 3) for r in dm["fundamentals"]}
+    vn = {}
+    for a, b in dm["visual_neighbors"]:
+        vn.setdefault(int(a), []).append(int(b))
+    return ids, views, F, vn
+
+
+def run_matching(ctx, ids, views, F, vn, sigma_p=3.5, sigma_a=10.0, resident=False):
+    """The reference's view loop (line3D.cc:620-648) with its matched_ bookkeeping (732-736, 844-845, 875-881)."""
+    index = {vid: i for i, vid in enumerate(ids)}
+    ctx.set_views(views)
+    matched = {vid: set() for vid in ids}
+    out = {}
+    for vid in sorted(vn):
+        nbs = sorted(vn[vid])
+        if not nbs:
+            continue
+        lst = []
+        for n in nbs:
+            tbm = n not in matched[vid]
+            deliver = (vid in vn.get(n, [])) and (vid not in matched[n])
+            lst.append(dict(view=index[n], F=F[(vid, n)], to_be_matched=tbm, deliver=deliver))
+        res = ctx.match_view(index[vid], lst, sigma_p, sigma_a, resident=resident)
+        res["neighbors"] = nbs
+        res["timings"] = ctx.last_timings()
+        out[vid] = res
+        for n in nbs:
+            matched[vid].add(n)
+            if vid in vn.get(n, []):
+                matched[n].add(vid)
+    return out
+
+
+def filtered_as_rows(vid, res):
+    """l3d_match records -> the (vID, seg1, cam2 global, seg2, depths x4, conf) rows of filtered_matches.npy."""
+    f = res["filtered"]
+    nbs = np.asarray(res["neighbors"], dtype=np.float64)
+    rows = np.zeros((f.shape[0], 9), dtype=np.float64)
+    rows[:, 0] = vid; rows[:, 1] = f["src_seg"]
+    rows[:, 2] = nbs[f["cam"]] if res["scored"] else f["cam"]
+    rows[:, 3] = f["tgt_seg"]; rows[:, 4:8] = f["depths"]; rows[:, 8] = f["confidence"]
+    return rows
