@@ -1,0 +1,929 @@
+// line3d_b200/csrc/line3D.cc -- host side of the Line3D API over the C ABI (l3d_b200.h).
+//
+// Fresh implementation of the reference's orchestration (line3D.cc, view.cc, segments.h,
+// clustering.cc of /root/reference; cited per function).  Containers are flat (vectors,
+// sorted arrays, hash sets) instead of the reference's nested std::map / std::list, and
+// views exchange matches through device memory instead of files; the observable behaviour
+// -- messages, guards, iteration orders, tie-breaking -- is the reference's.
+#include "line3D.h"
+
+#include "../../include/l3d_b200.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <set>
+#include <sstream>
+#include <stdexcept>
+#include <unordered_set>
+
+namespace L3D
+{
+namespace
+{
+typedef Eigen::Matrix3d M3;
+typedef Eigen::Vector3d V3;
+
+inline double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+inline uint64_t seg_key(unsigned cam, unsigned seg) { return (uint64_t(cam) << 32) | uint64_t(seg); }
+
+struct CollinEntry { unsigned other; float w; };
+
+// one image (view.h:40-153)
+struct ViewData
+{
+    unsigned id, width, height;
+    M3 K, Kinv, R, Rt, RtKinv; V3 t, C, pp; Eigen::MatrixXd P;
+    float unc_upper_px, unc_lower_px, k_upper, k_lower, median_depth;
+    std::vector<float4> segs;
+    std::vector<std::vector<CollinEntry> > collin;     // per segment, ascending partner id (segments.h:82-98)
+    int index;                                         // position in the l3d_set_views array
+
+    // view.cc:90-147: lateral 3-D displacement at depth 1 of a pixel dist_px away from the principal point
+    double shifted(float dist_px) const
+    {
+        V3 n = RtKinv * pp; n.normalize();
+        V3 Pl = C + n;
+        V3 sh(pp.x() + dist_px, pp.y(), 1.0);
+        V3 d = RtKinv * sh; d.normalize();
+        double tt = (Pl.dot(n) - n.dot(C)) / (n.dot(d));
+        V3 Q = C + tt * d;
+        return (Pl - Q).norm();
+    }
+    void defineUncertainty() { k_upper = float(shifted(unc_upper_px)); k_lower = float(shifted(unc_lower_px)); }
+    // view.cc:16-34
+    void init()
+    {
+        pp(0) = float(width) / 2.0f; pp(1) = float(height) / 2.0f; pp(2) = 1.0;
+        Kinv = K.inverse(); Rt = R.transpose(); RtKinv = Rt * Kinv; C = Rt * (-1.0 * t);
+        Eigen::MatrixXd Rpt(3, 4); Rpt.block<3, 3>(0, 0) = R; Rpt.block<3, 1>(0, 3) = t;
+        P = K * Rpt;
+        median_depth = 1.0f;
+        defineUncertainty();
+    }
+    // view.cc:227-261
+    void transform(Eigen::Matrix4d& Qinv, double scale)
+    {
+        t *= scale;
+        Eigen::MatrixXd Rtm(3, 4); Rtm.block<3, 3>(0, 0) = R; Rtm.block<3, 1>(0, 3) = t;
+        Rtm *= Qinv;
+        R = Rtm.block<3, 3>(0, 0); t = Rtm.block<3, 1>(0, 3);
+        Rt = R.transpose(); P = K * Rtm; RtKinv = Rt * Kinv; C = Rt * (-1.0 * t);
+        defineUncertainty();
+    }
+};
+
+struct BestMatch { bool has; unsigned tgt_cam, tgt_seg; float conf, d1, d2; };
+struct Hypothesis { unsigned cam, seg, tgt_cam, tgt_seg; float score; V3 P1, P2, dir; float d1, d2; };
+struct Edge { int i, j; float w; };
+
+// tiny .npy writer for debugDump (same files as oracle/ref_harness.cpp writes)
+void write_npy(const std::string& path, const char* descr, size_t elem, size_t rows, size_t cols, const void* data)
+{
+    std::ostringstream h;
+    h << "{'descr': '" << descr << "', 'fortran_order': False, 'shape': (" << rows << ", " << cols << "), }";
+    std::string hs = h.str();
+    size_t total = 10 + hs.size() + 1, pad = (64 - total % 64) % 64;
+    hs += std::string(pad, ' '); hs += "\n";
+    std::ofstream f(path.c_str(), std::ios::binary);
+    const unsigned char magic[8] = {0x93, 'N', 'U', 'M', 'P', 'Y', 1, 0};
+    f.write(reinterpret_cast<const char*>(magic), 8);
+    uint16_t hl = uint16_t(hs.size()); f.write(reinterpret_cast<const char*>(&hl), 2);
+    f.write(hs.data(), std::streamsize(hs.size()));
+    if (rows > 0 && cols > 0) f.write(static_cast<const char*>(data), std::streamsize(rows * cols * elem));
+}
+void npy_f64(const std::string& p, const std::vector<double>& v, size_t cols) { write_npy(p, "<f8", 8, v.size() / cols, cols, v.data()); }
+void npy_i32(const std::string& p, const std::vector<int32_t>& v, size_t cols) { write_npy(p, "<i4", 4, v.size() / cols, cols, v.data()); }
+void npy_f32(const std::string& p, const std::vector<float>& v, size_t cols) { write_npy(p, "<f4", 4, v.size() / cols, cols, v.data()); }
+
+std::string cacheName(const std::string& dir, unsigned id, unsigned w, unsigned h, bool collin)
+{
+    std::stringstream s;
+    s << dir << "/segments_" << id << "_" << w << "x" << h << (collin ? "_coll1.bin" : "_coll0.bin");   // line3D.cc:144-150
+    return s.str();
+}
+}  // namespace
+
+struct Line3D::Impl
+{
+    bool verbose, computation, use_collinearity, measure_only;
+    std::string prefix, separator, data_directory;
+    int matching_neighbors; float min_baseline, unc_upper, unc_lower, sigma_p, sigma_a;
+    l3d_ctx* ctx;
+
+    std::map<unsigned, ViewData*> views;
+    std::map<unsigned, unsigned> num_wps;
+    std::map<unsigned, std::map<unsigned, unsigned> > common_wps;
+    std::map<unsigned, std::map<unsigned, float> > view_sim;
+    std::map<unsigned, std::map<unsigned, bool> > wp2views;
+    std::map<unsigned, std::vector<unsigned> > vn;                 // visual neighbours, ascending
+    std::map<unsigned, std::map<unsigned, M3> > fund;
+    std::map<unsigned, std::set<unsigned> > matched;
+
+    std::map<unsigned, std::vector<BestMatch> > best;              // per view, per segment
+    std::vector<std::pair<uint64_t, uint64_t> > potential;         // symmetric pairs of segment keys
+    std::vector<Hypothesis> hyps;                                  // (cam, seg) ascending
+    std::map<uint64_t, int> hyp_of;
+
+    std::list<L3DFinalLine3D> result;
+    double tr_scale, tr_scale_inv; M3 tr_R, tr_Rinv; V3 tr_t, tr_tneg; Eigen::Matrix4d Qinv;
+
+    // dumps / stats
+    std::vector<int32_t> match_log; std::vector<float> match_median; std::vector<double> filtered_dump, edges_pre, edges_cluster;
+    int cluster_nodes;
+    L3DRunStats stats;
+
+    Impl() : ctx(0), cluster_nodes(0) { memset(&stats, 0, sizeof stats); }
+
+    void fail(const char* what)
+    {
+        std::string msg = std::string(what) + ": " + l3d_last_error(ctx);
+        std::cerr << prefix << msg << std::endl;
+        throw std::runtime_error(msg);
+    }
+    bool neighbour_of(unsigned a, unsigned b)      // b in VN(a)
+    {
+        std::map<unsigned, std::vector<unsigned> >::iterator it = vn.find(a);
+        return it != vn.end() && std::binary_search(it->second.begin(), it->second.end(), b);
+    }
+
+    // line3D.cc:1874-1935
+    void processWorldpoints(unsigned vid, std::list<unsigned>& wps)
+    {
+        num_wps[vid] = 0;
+        for (std::list<unsigned>::iterator it = wps.begin(); it != wps.end(); ++it) {
+            std::map<unsigned, bool>& seen = wp2views[*it];
+            if (seen.size() == 2) {
+                std::map<unsigned, bool>::iterator w = seen.begin();
+                unsigned v1 = w->first; ++w; unsigned v2 = w->first;
+                if (common_wps[v1].find(v2) == common_wps[v1].end()) { common_wps[v1][v2] = 1; common_wps[v2][v1] = 1; }
+                else { ++common_wps[v1][v2]; ++common_wps[v2][v1]; }
+                ++num_wps[v1]; ++num_wps[v2];
+            }
+            if (seen.size() >= 2) {
+                for (std::map<unsigned, bool>::iterator w = seen.begin(); w != seen.end(); ++w) {
+                    if (common_wps[w->first].find(vid) == common_wps[w->first].end()) { common_wps[w->first][vid] = 1; common_wps[vid][w->first] = 1; }
+                    else { ++common_wps[w->first][vid]; ++common_wps[vid][w->first]; }
+                }
+                ++num_wps[vid];
+            }
+            seen[vid] = true;
+        }
+    }
+
+    // segments.h:60-102 with the dense relation replaced by the compacted pair list
+    void buildCollinearity(ViewData* v)
+    {
+        v->collin.assign(v->segs.size(), std::vector<CollinEntry>());
+        if (!use_collinearity || v->segs.size() < 2) return;
+        const l3d_collin_pair* pairs = 0; size_t n = 0;
+        if (l3d_collinearity(ctx, reinterpret_cast<const float*>(v->segs.data()), int(v->segs.size()), L3D_DEF_COLLINEARITY_S, &pairs, &n)) fail("l3d_collinearity");
+        for (size_t k = 0; k < n; ++k) {
+            CollinEntry a = {unsigned(pairs[k].j), pairs[k].value}, b = {unsigned(pairs[k].i), pairs[k].value};
+            v->collin[pairs[k].i].push_back(a); v->collin[pairs[k].j].push_back(b);
+        }
+        for (size_t s = 0; s < v->collin.size(); ++s)
+            std::sort(v->collin[s].begin(), v->collin[s].end(), [](const CollinEntry& x, const CollinEntry& y) { return x.other < y.other; });
+    }
+
+    // common part of addImage / addImage_fixed_sim (line3D.cc:95-217, 220-342)
+    ViewData* addView(unsigned imageID, const cv::Mat& image, const M3& K, const M3& R, const V3& t, int maxImgWidth, bool loadAndStore)
+    {
+        unsigned new_width = image.cols, new_height = image.rows;
+        if (maxImgWidth > 0 && std::max(image.rows, image.cols) > maxImgWidth) {                     // line3D.cc:134-139
+            float scale = float(maxImgWidth) / fmax(image.rows, image.cols);
+            new_width = round(float(image.cols) * scale); new_height = round(float(image.rows) * scale);
+        }
+        std::cout << prefix << "adding image [" << imageID << "] [" << new_width << "x" << new_height << "]" << std::endl;
+        const std::string file = cacheName(data_directory, imageID, new_width, new_height, use_collinearity);
+        boost::filesystem::path fpath(file);
+        if (boost::filesystem::exists(fpath) && !loadAndStore) boost::filesystem::remove(fpath);     // line3D.cc:154-157
+        std::vector<float4> segs;
+        if (boost::filesystem::exists(fpath) && loadAndStore) {
+            if (verbose) std::cout << prefix << "segments data found" << std::endl;
+            if (!readSegmentCache(file, segs)) { std::cerr << prefix << "segment cache unreadable: " << file << std::endl; return 0; }
+        } else {
+            if (verbose) std::cout << prefix << "performing line segment detection..." << std::endl;
+            // line3D.cc:174-190.  2-D line detection (OpenCV LSD) is upstream of this library and not
+            // available on this image: segments have to arrive through the cache.
+            std::cerr << prefix << "no line segment detector in this build: provide " << file << " (Line3D::writeSegmentCache)" << std::endl;
+            return 0;
+        }
+        if (verbose) std::cout << prefix << "#segments: " << segs.size() << " (final)" << std::endl;
+        ViewData* v = new ViewData();
+        v->id = imageID; v->width = image.cols; v->height = image.rows;                              // line3D.cc:202-207
+        v->K = K; v->R = R; v->t = t; v->unc_upper_px = unc_upper; v->unc_lower_px = unc_lower;
+        v->segs.swap(segs); v->index = -1;
+        buildCollinearity(v);
+        v->init();
+        views[imageID] = v;
+        if (verbose) {
+            std::cout << prefix << "minimum uncertainty in depth=1: " << v->k_lower << std::endl;
+            std::cout << prefix << "maximum uncertainty in depth=1: " << v->k_upper << std::endl;
+        }
+        return v;
+    }
+
+    static bool readSegmentCache(const std::string& file, std::vector<float4>& segs)
+    {
+        std::ifstream f(file.c_str(), std::ios::binary);
+        if (!f) return false;
+        char magic[8]; f.read(magic, 8);
+        if (memcmp(magic, "L3DSEG01", 8) != 0) return false;
+        uint32_t n = 0, flags = 0; f.read(reinterpret_cast<char*>(&n), 4); f.read(reinterpret_cast<char*>(&flags), 4);
+        segs.resize(n);
+        if (n) f.read(reinterpret_cast<char*>(segs.data()), std::streamsize(size_t(n) * sizeof(float4)));
+        return bool(f);
+    }
+
+    bool guards(unsigned imageID, const cv::Mat& image, bool linked, const char* what)
+    {
+        if (computation) { std::cerr << "reconstruction already performed! cannot add more images (try reset first)" << std::endl; return false; }   // line3D.cc:101-105
+        if (views.size() == 0) std::cout << prefix << ">>> LOADING DATA <<<" << std::endl;
+        if (views.find(imageID) != views.end()) { std::cerr << prefix << "imageID already in use!" << std::endl; return false; }                   // :111-115
+        if (!linked) { std::cerr << prefix << "unlinked images cannot be added! (" << what << ")" << std::endl; return false; }                      // :116-120
+        if (image.rows == 0 || image.cols == 0) { std::cerr << prefix << "image is empty!" << std::endl; return false; }                           // :123-127
+        return true;
+    }
+
+    float baseline(unsigned a, unsigned b) { return float((views[a]->C - views[b]->C).norm()); }     // view.cc:446-449
+
+    // line3D.cc:476-549
+    void findVisualNeighbors()
+    {
+        vn.clear();
+        std::cout << prefix << separator << std::endl;
+        std::cout << prefix << ">>> FINDING VISUAL NEIGHBORS <<<" << std::endl;
+        for (std::map<unsigned, std::map<unsigned, unsigned> >::iterator it = common_wps.begin(); it != common_wps.end(); ++it) {
+            if (view_sim.find(it->first) != view_sim.end()) continue;
+            std::cout << prefix << "computing similarities for image [" << it->first << "]" << std::endl;
+            for (std::map<unsigned, unsigned>::iterator n = it->second.begin(); n != it->second.end(); ++n) {
+                float sim = 2.0f * float(n->second) / (float(num_wps[it->first] + num_wps[n->first]));
+                if (sim > L3D_EPS) view_sim[it->first][n->first] = sim;
+            }
+        }
+        for (std::map<unsigned, std::map<unsigned, float> >::iterator s = view_sim.begin(); s != view_sim.end(); ++s) {
+            std::cout << prefix << "setting VNs for image [" << s->first << "]" << std::endl;
+            std::vector<std::pair<unsigned, float> > cand;
+            for (std::map<unsigned, float>::iterator n = s->second.begin(); n != s->second.end(); ++n) {
+                if (views.find(n->first) == views.end() || views.find(s->first) == views.end()) continue;
+                if (!(baseline(s->first, n->first) > min_baseline)) continue;
+                bool ok = true;                          // baseline against the neighbours accepted so far, in id order (:514-522)
+                for (size_t e = 0; e < cand.size() && ok; ++e) if (baseline(cand[e].first, n->first) <= min_baseline) ok = false;
+                if (ok) cand.push_back(std::make_pair(n->first, n->second));
+            }
+            std::stable_sort(cand.begin(), cand.end(), [](const std::pair<unsigned, float>& a, const std::pair<unsigned, float>& b) { return a.second > b.second; });
+            if (matching_neighbors > 0 && int(cand.size()) > matching_neighbors) cand.resize(matching_neighbors);
+            std::vector<unsigned>& out = vn[s->first];
+            for (size_t e = 0; e < cand.size(); ++e) out.push_back(cand[e].first);
+            std::sort(out.begin(), out.end());
+            if (verbose) std::cout << prefix << cand.size() << " visual neighbors found" << std::endl;
+        }
+    }
+
+    // line3D.cc:552-617, 1694-1779
+    void transformGeometry()
+    {
+        std::cout << prefix << separator << std::endl;
+        std::cout << prefix << ">>> TRANSFORMING SCENE GEOMETRY <<<" << std::endl;
+        fund.clear();
+        const double size = double(views.size());
+        V3 m(0.0, 0.0, 0.0);
+        std::vector<V3> in_pts;
+        for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) { m += it->second->C; in_pts.push_back(it->second->C); }
+        m /= size;
+        double q = 0.0;
+        for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) q += (it->second->C - m).norm();
+        q /= size;
+        q = sqrtf(2.0) / q;
+        Eigen::MatrixXd T(4, 4);
+        T(0,0) = q; T(0,1) = 0.0; T(0,2) = 0.0; T(0,3) = -q * m(0);
+        T(1,0) = 0.0; T(1,1) = q; T(1,2) = 0.0; T(1,3) = -q * m(1);
+        T(2,0) = 0.0; T(2,1) = 0.0; T(2,2) = q; T(2,3) = -q * m(2);
+        T(3,0) = 0.0; T(3,1) = 0.0; T(3,2) = 0.0; T(3,3) = 1.0;
+        std::vector<V3> out_pts; V3 cog_out(0.0, 0.0, 0.0);
+        for (size_t i = 0; i < in_pts.size(); ++i) {
+            Eigen::Vector4d tv = T * Eigen::Vector4d(in_pts[i](0), in_pts[i](1), in_pts[i](2), 1.0);
+            V3 t3(tv(0), tv(1), tv(2)); cog_out += t3; out_pts.push_back(t3);
+        }
+        cog_out /= size;
+        if (verbose) {
+            std::cout << prefix << "COG_in   = [" << m.x() << " " << m.y() << " " << m.z() << "]" << std::endl;
+            std::cout << prefix << "COG_out  = [" << cog_out.x() << " " << cog_out.y() << " " << cog_out.z() << "]" << std::endl;
+            std::cout << prefix << "variance = " << q << std::endl;
+        }
+        std::cout << prefix << "computing similarity transform..." << std::endl;
+        const size_t n = in_pts.size();
+        double ssum = 0.0;
+        for (size_t i = 0; i < n; ++i) ssum += (out_pts[i] - cog_out).norm() / (in_pts[i] - m).norm();
+        tr_scale = ssum / double(n);
+        V3 cog_in = m; cog_in *= tr_scale;
+        for (size_t i = 0; i < n; ++i) in_pts[i] *= tr_scale;
+        for (size_t i = 0; i < n; ++i) { in_pts[i] -= cog_in; out_pts[i] -= cog_out; }
+        M3 H; H.setZero();
+        for (size_t i = 0; i < n; ++i) { M3 outer = out_pts[i] * in_pts[i].transpose(); H += outer; }
+        Eigen::JacobiSVD<Eigen::MatrixXd> svd(H, Eigen::ComputeThinU | Eigen::ComputeThinV);
+        M3 Vt = svd.matrixV().transpose(), U = svd.matrixU();
+        tr_R = U * Vt;
+        if (tr_R.determinant() < 0) { Vt.row(2) *= -1; tr_R = U * Vt; }
+        tr_t = cog_out - tr_R * cog_in;
+        tr_t /= tr_scale;
+        Eigen::Matrix4d Q;
+        Q << tr_R.row(0), tr_t.x() * tr_scale, tr_R.row(1), tr_t.y() * tr_scale, tr_R.row(2), tr_t.z() * tr_scale, 0.0, 0.0, 0.0, 1.0;
+        Qinv = Q.inverse();
+        tr_scale_inv = 1.0 / tr_scale; tr_Rinv = tr_R.transpose(); tr_tneg = -tr_t;
+        for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) it->second->transform(Qinv, tr_scale);
+    }
+    V3 inverseTransform(const V3& P) { return tr_Rinv * (P * tr_scale_inv + tr_tneg); }              // line3D.cc:1782-1786
+
+    // line3D.cc:1968-1993
+    M3 fundamental(unsigned a, unsigned b)
+    {
+        ViewData* v1 = views[a]; ViewData* v2 = views[b];
+        M3 R = v2->R * v1->R.transpose();
+        V3 t = v2->t - R * v1->t;
+        M3 T;
+        T(0,0) = 0.0; T(0,1) = -t.z(); T(0,2) = t.y();
+        T(1,0) = t.z(); T(1,1) = 0.0; T(1,2) = -t.x();
+        T(2,0) = -t.y(); T(2,1) = t.x(); T(2,2) = 0.0;
+        M3 E = T * R;
+        return v2->K.transpose().inverse() * E * v1->K.inverse();
+    }
+
+    void uploadViews()
+    {
+        std::vector<l3d_view> lv(views.size());
+        int idx = 0;
+        for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it, ++idx) {
+            ViewData* v = it->second; v->index = idx;
+            l3d_view& o = lv[idx];
+            memset(&o, 0, sizeof o);
+            o.id = int(v->id); o.n_segments = int(v->segs.size()); o.segments = reinterpret_cast<const float*>(v->segs.data());
+            for (int r = 0; r < 3; ++r) {
+                for (int c = 0; c < 3; ++c) { o.RtKinv[r * 3 + c] = float(v->RtKinv(r, c)); o.RtKinv_d[r * 3 + c] = v->RtKinv(r, c); }   // line3D.cc:746, 790
+                for (int c = 0; c < 4; ++c) o.P[r * 4 + c] = float(v->P(r, c));                                                            // line3D.cc:756
+                o.C[r] = float(v->C(r)); o.C_d[r] = v->C(r);                                                                               // line3D.cc:761-763, 801-803
+            }
+            o.spatial_k = float(v->shifted(2.0f * sigma_p));                                                                               // line3D.cc:820
+            o.k_lower = v->k_lower; o.k_upper = v->k_upper;
+        }
+        if (l3d_set_views(ctx, int(lv.size()), lv.data())) fail("l3d_set_views");
+    }
+
+    // line3D.cc:620-648 + 698-885
+    void matchViews()
+    {
+        std::cout << prefix << separator << std::endl;
+        std::cout << prefix << ">>> MATCHING IMAGES <<<" << std::endl;
+        for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it) {
+            const unsigned vid = it->first;
+            std::cout << prefix << "matching image [" << vid << "] with " << it->second.size() << " VNs" << std::endl;
+            if (it->second.empty()) continue;
+            ViewData* v = views[vid];
+            std::vector<l3d_neighbor> nb(it->second.size());
+            for (size_t c = 0; c < it->second.size(); ++c) {
+                const unsigned n = it->second[c];
+                if (fund[vid].find(n) == fund[vid].end()) { M3 F = fundamental(vid, n); M3 Ft = F.transpose(); fund[vid][n] = F; fund[n][vid] = Ft; }   // :1949-1965
+                const M3& F = fund[vid][n];
+                nb[c].view = views[n]->index;
+                for (int r = 0; r < 3; ++r) for (int cc = 0; cc < 3; ++cc) nb[c].F[r * 3 + cc] = float(F(r, cc));                    // :745
+                nb[c].to_be_matched = matched[vid].count(n) ? 0 : 1;                                                                 // :732-736
+                nb[c].deliver = (neighbour_of(n, vid) && !matched[n].count(vid)) ? 1 : 0;                                            // :844-845
+            }
+            l3d_match_result res;
+            const double t0 = now_s();
+            int rc = measure_only ? l3d_match_view_resident(ctx, v->index, int(nb.size()), nb.data(), sigma_p, sigma_a, &res)
+                                  : l3d_match_view(ctx, v->index, int(nb.size()), nb.data(), sigma_p, sigma_a, &res);
+            if (rc) fail("l3d_match_view");
+            stats.t_matching += now_s() - t0;
+            float ms[6]; l3d_last_timings(ctx, ms); stats.t_matching_device += double(ms[5]) * 1e-3;
+            stats.pair_tests += res.pair_tests; stats.candidates += res.n_candidates; stats.raw_matches += res.n_raw;
+            stats.scored_matches += res.n_scored; stats.filtered_matches += res.n_filtered; stats.score_iters += res.score_iters;
+            if (verbose) {
+                std::cout << prefix << "existing matches:  " << res.n_delivered << std::endl;
+                std::cout << prefix << "#raw_matches:          " << res.n_scored << std::endl;
+                std::cout << prefix << "#filtered_matches (2): " << res.n_filtered << std::endl;
+            }
+            v->median_depth = res.median_depth;                                                                                      // :835
+            size_t n_tbm = 0; for (size_t c = 0; c < nb.size(); ++c) n_tbm += nb[c].to_be_matched ? 1 : 0;
+            match_log.push_back(int32_t(vid)); match_log.push_back(int32_t(n_tbm)); match_log.push_back(int32_t(res.n_delivered)); match_log.push_back(int32_t(res.n_filtered));
+            match_median.push_back(res.median_depth);
+            // records: cam = position in nb[]; when nothing was pair-tested the reference keeps using the
+            // local id as if it were a view id (cudawrapper.cu:877-878, line3D.cc:843) -- reproduced
+            std::vector<BestMatch>& bm = best[vid];
+            bm.assign(v->segs.size(), BestMatch());
+            for (size_t s = 0; s < bm.size(); ++s) bm[s].has = false;
+            if (!measure_only)
+                for (uint64_t k = 0; k < res.n_filtered; ++k) {
+                    const l3d_match& m = res.filtered[k];
+                    const unsigned cam = res.scored ? it->second[m.cam] : unsigned(m.cam);
+                    const double row[9] = {double(vid), double(m.src_seg), double(cam), double(m.tgt_seg), m.depths[0], m.depths[1], m.depths[2], m.depths[3], m.confidence};
+                    filtered_dump.insert(filtered_dump.end(), row, row + 9);
+                    potential.push_back(std::make_pair(seg_key(vid, m.src_seg), seg_key(cam, m.tgt_seg)));                           // :861-865
+                    potential.push_back(std::make_pair(seg_key(cam, m.tgt_seg), seg_key(vid, m.src_seg)));
+                    BestMatch& b = bm[m.src_seg];                                                                                   // view.cc:165-183: first maximum
+                    if (!b.has || m.confidence > b.conf) { b.has = true; b.tgt_cam = cam; b.tgt_seg = unsigned(m.tgt_seg); b.conf = m.confidence; b.d1 = m.depths[0]; b.d2 = m.depths[1]; }
+                }
+            for (size_t c = 0; c < it->second.size(); ++c) {                                                                        // :875-881
+                const unsigned n = it->second[c];
+                matched[vid].insert(n);
+                if (neighbour_of(n, vid)) matched[n].insert(vid);
+            }
+        }
+    }
+
+    // line3D.cc:899-965 + view.cc:302-342 on the device
+    void buildHypotheses()
+    {
+        std::cout << prefix << separator << std::endl;
+        std::cout << prefix << ">>> OPTIMIZING CORRESPONDENCES (greedy) <<<" << std::endl;
+        hyps.clear(); hyp_of.clear();
+        std::vector<l3d_hypothesis_in> in;
+        for (std::map<unsigned, std::vector<BestMatch> >::iterator it = best.begin(); it != best.end(); ++it)
+            for (size_t s = 0; s < it->second.size(); ++s) {
+                const BestMatch& b = it->second[s];
+                if (!b.has) continue;
+                Hypothesis h; h.cam = it->first; h.seg = unsigned(s); h.tgt_cam = b.tgt_cam; h.tgt_seg = b.tgt_seg;
+                h.score = fminf(b.conf, 1.0f); h.d1 = b.d1; h.d2 = b.d2;                                                            // :937
+                hyp_of[seg_key(h.cam, h.seg)] = int(hyps.size());
+                hyps.push_back(h);
+                l3d_hypothesis_in hi; hi.view = views[it->first]->index; hi.seg = int(s); hi.depth1 = b.d1; hi.depth2 = b.d2;
+                in.push_back(hi);
+            }
+        std::vector<l3d_segment3d> out(in.size());
+        if (!in.empty() && l3d_unproject(ctx, in.size(), in.data(), out.data())) fail("l3d_unproject");
+        for (size_t k = 0; k < hyps.size(); ++k)
+            for (int a = 0; a < 3; ++a) { hyps[k].P1(a) = out[k].P1[a]; hyps[k].P2(a) = out[k].P2[a]; hyps[k].dir(a) = out[k].dir[a]; }
+        stats.hypotheses = hyps.size();
+        if (verbose) std::cout << prefix << "#clusterable_segments:  " << hyps.size() << std::endl;
+    }
+
+    // line3D.cc:968-1252: candidate enumeration in the reference's order, affinities on the device
+    void clusterSegments(bool perform_diffusion)
+    {
+        std::cout << prefix << separator << std::endl;
+        std::cout << prefix << ">>> CLUSTERING 2D SEGMENTS (global) <<<" << std::endl;
+        result.clear();
+        std::cout << prefix << "computing affinity matrix..." << std::endl;
+        const double t0 = now_s();
+        // potential correspondences as a sorted, de-duplicated CSR over source keys
+        std::sort(potential.begin(), potential.end());
+        potential.erase(std::unique(potential.begin(), potential.end()), potential.end());
+        struct Cand { int a, b; float mult; float thr; };
+        std::vector<Cand> cands;
+        std::unordered_set<uint64_t> used;                 // unordered pair of dense segment numbers
+        // dense numbering of every segment key that can occur
+        std::map<unsigned, uint64_t> view_base; uint64_t total = 0;
+        for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) { view_base[it->first] = total; total += it->second->segs.size(); }
+        auto dense = [&](unsigned cam, unsigned seg, uint64_t& out) -> bool {
+            std::map<unsigned, uint64_t>::iterator b = view_base.find(cam);
+            if (b == view_base.end() || seg >= views[cam]->segs.size()) return false;
+            out = b->second + seg; return true;
+        };
+        // a key outside every view can only come from the unscored-view quirk; such a target has no
+        // hypothesis and no collinear partners, so it can never produce an edge: it is skipped
+        auto mark = [&](uint64_t a, uint64_t b) -> bool {   // true if the pair was new
+            uint64_t lo = std::min(a, b), hi = std::max(a, b);
+            return used.insert(lo * total + hi).second;
+        };
+        auto hyp_index = [&](unsigned cam, unsigned seg) -> int {
+            std::map<uint64_t, int>::iterator f = hyp_of.find(seg_key(cam, seg));
+            return f == hyp_of.end() ? -1 : f->second;
+        };
+        size_t pc = 0;
+        for (size_t hidx = 0; hidx < hyps.size(); ++hidx) {
+            const Hypothesis& C = hyps[hidx];
+            uint64_t dsrc; if (!dense(C.cam, C.seg, dsrc)) continue;
+            const uint64_t skey = seg_key(C.cam, C.seg);
+            while (pc < potential.size() && potential[pc].first < skey) ++pc;
+            for (size_t k = pc; k < potential.size() && potential[k].first == skey; ++k) {                                           // :996-1138
+                const unsigned tcam = unsigned(potential[k].second >> 32), tseg = unsigned(potential[k].second & 0xffffffffu);
+                uint64_t dt; if (!dense(tcam, tseg, dt)) continue;
+                if (!mark(dsrc, dt)) continue;
+                const int ht = hyp_index(tcam, tseg);
+                if (ht < 0) continue;                                                                                               // :1007
+                Cand c = {int(hidx), ht, 1.0f, L3D_MIN_AFFINITY}; cands.push_back(c);                                               // :1014-1016
+                const std::vector<CollinEntry>& cl = views[tcam]->collin[tseg];                                                     // :1065-1135
+                for (size_t e = 0; e < cl.size(); ++e) {
+                    uint64_t dc; if (!dense(tcam, cl[e].other, dc)) continue;
+                    if (!mark(dsrc, dc)) continue;
+                    const int hc = hyp_index(tcam, cl[e].other);
+                    if (hc < 0) continue;
+                    Cand c3 = {int(hidx), hc, 1.0f, 0.01f}; cands.push_back(c3);                                                    // :1085-1087
+                }
+            }
+            const std::vector<CollinEntry>& cs = views[C.cam]->collin[C.seg];                                                       // :1141-1214
+            for (size_t e = 0; e < cs.size(); ++e) {
+                uint64_t dc; if (!dense(C.cam, cs[e].other, dc)) continue;
+                if (!mark(dsrc, dc)) continue;
+                const int hc = hyp_index(C.cam, cs[e].other);
+                if (hc < 0) continue;
+                Cand c2 = {int(hidx), hc, cs[e].w, 0.01f}; cands.push_back(c2);                                                     // :1163-1165
+            }
+        }
+        // similarities on the device (line3D.cc:1600-1691)
+        std::vector<l3d_pair> pairs(cands.size());
+        for (size_t k = 0; k < cands.size(); ++k) { pairs[k].a = cands[k].a; pairs[k].b = cands[k].b; }
+        std::vector<float> sim(cands.size());
+        std::vector<float> medians(views.size());
+        for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) medians[it->second->index] = it->second->median_depth;
+        if (!cands.empty() && l3d_affinity(ctx, medians.data(), pairs.size(), pairs.data(), sigma_a, sim.data())) fail("l3d_affinity");
+        stats.affinity_pairs = cands.size();
+        // edges and node ids in encounter order (line3D.cc:1018-1060)
+        std::vector<Edge> A;
+        std::vector<int> node_of(hyps.size(), -1); std::vector<int> hyp_of_node;
+        for (size_t k = 0; k < cands.size(); ++k) {
+            const Cand& c = cands[k];
+            // mult is the collinearity weight for same-image pairs (line3D.cc:1163) and exactly 1 otherwise
+            const float w = c.mult * 0.5f * (hyps[c.a].score + hyps[c.b].score) * sim[k];
+            if (!(w > c.thr)) continue;
+            if (node_of[c.a] < 0) { node_of[c.a] = int(hyp_of_node.size()); hyp_of_node.push_back(c.a); }
+            if (node_of[c.b] < 0) { node_of[c.b] = int(hyp_of_node.size()); hyp_of_node.push_back(c.b); }
+            Edge e = {node_of[c.a], node_of[c.b], w}; A.push_back(e);
+            Edge r = {node_of[c.b], node_of[c.a], w}; A.push_back(r);
+        }
+        stats.t_affinity += now_s() - t0;
+        const int n_nodes = int(hyp_of_node.size());
+        if (verbose) {
+            std::cout << prefix << "A: #num_entries = " << A.size() << std::endl;
+            std::cout << prefix << "A: #num_rows    = " << n_nodes << std::endl;
+        }
+        if (A.empty()) return;                                                                                                      // :1232-1233
+        if (perform_diffusion) {                                                                                                    // :1255-1303
+            std::cout << prefix << "replicator dynamics diffusion..." << std::endl;
+            const double td = now_s();
+            std::vector<l3d_edge> in(A.size()), out(A.size());
+            for (size_t k = 0; k < A.size(); ++k) { in[k].i = A[k].i; in[k].j = A[k].j; in[k].w = A[k].w; }
+            {   // W as the reference stores it (column-sorted) for the dump
+                std::vector<l3d_edge> w(in);
+                std::stable_sort(w.begin(), w.end(), [](const l3d_edge& a, const l3d_edge& b) { return a.j < b.j || (a.j == b.j && a.i < b.i); });
+                for (size_t k = 0; k < w.size(); ++k) { edges_pre.push_back(w[k].i); edges_pre.push_back(w[k].j); edges_pre.push_back(w[k].w); }
+            }
+            if (l3d_diffuse(ctx, n_nodes, in.size(), in.data(), out.data())) fail("l3d_diffuse");
+            // symmetrise with min(w_ij, w_ji) in stored order, then (i, j) order (line3D.cc:1267-1299)
+            std::map<int, std::map<int, float> > entries;
+            for (size_t k = 0; k < out.size(); ++k) {
+                const int s1 = out[k].i, s2 = out[k].j; float w12 = out[k].w, w21 = w12;
+                std::map<int, float>& row2 = entries[s2];
+                std::map<int, float>::iterator f = row2.find(s1);
+                if (f != row2.end()) w21 = f->second;
+                const float w = fminf(w12, w21);
+                entries[s1][s2] = w; entries[s2][s1] = w;
+            }
+            A.clear();
+            for (std::map<int, std::map<int, float> >::iterator a = entries.begin(); a != entries.end(); ++a)
+                for (std::map<int, float>::iterator b = a->second.begin(); b != a->second.end(); ++b) { Edge e = {a->first, b->first, b->second}; A.push_back(e); }
+            stats.t_diffusion += now_s() - td;
+        }
+        stats.edges = A.size();
+        cluster_nodes = n_nodes;
+        for (size_t k = 0; k < A.size(); ++k) { edges_cluster.push_back(A[k].i); edges_cluster.push_back(A[k].j); edges_cluster.push_back(A[k].w); }
+        std::cout << prefix << "graph clustering..." << std::endl;
+        const double tc = now_s();
+        // Felzenszwalb-Huttenlocher as the reference runs it (clustering.cc:6-47, universe.h:59-115):
+        // edges stably sorted by ascending weight, threshold w + c / size with c = 1
+        std::vector<Edge> sorted(A);
+        std::stable_sort(sorted.begin(), sorted.end(), [](const Edge& a, const Edge& b) { return a.w < b.w; });
+        std::vector<int> parent(n_nodes), rank(n_nodes, 0), sz(n_nodes, 1);
+        std::vector<float> thr(n_nodes, 1.0f);
+        for (int i = 0; i < n_nodes; ++i) parent[i] = i;
+        auto find = [&](int x) { int y = x; while (y != parent[y]) y = parent[y]; parent[x] = y; return y; };
+        for (size_t k = 0; k < sorted.size(); ++k) {
+            int a = find(sorted[k].i), b = find(sorted[k].j);
+            if (a == b) continue;
+            if (sorted[k].w <= thr[a] && sorted[k].w <= thr[b]) {
+                if (rank[a] > rank[b]) { parent[b] = a; sz[a] += sz[b]; }
+                else { parent[a] = b; sz[b] += sz[a]; if (rank[a] == rank[b]) rank[b]++; }
+                a = find(a);
+                thr[a] = sorted[k].w + 1.0f / float(sz[a]);
+            }
+        }
+        stats.t_clustering += now_s() - tc;
+        // line3D.cc:1306-1368
+        const double tl = now_s();
+        std::map<unsigned, std::vector<int> > clusters; std::map<unsigned, std::set<unsigned> > cams;
+        for (int n = 0; n < n_nodes; ++n) { unsigned cl = unsigned(find(n)); clusters[cl].push_back(hyp_of_node[n]); cams[cl].insert(hyps[hyp_of_node[n]].cam); }
+        if (verbose) std::cout << prefix << "#clusters_total:  " << clusters.size() << std::endl;
+        unsigned valid = 0;
+        for (std::map<unsigned, std::vector<int> >::iterator c = clusters.begin(); c != clusters.end(); ++c) {
+            if (cams[c->first].size() < 4) continue;
+            std::list<L3DSegment2D> s2; std::list<std::pair<V3, V3> > s3;
+            alignCluster(c->second, s3, s2);
+            if (!s3.empty()) { result.push_back(L3DFinalLine3D(s2, s3)); ++valid; }
+        }
+        if (verbose) std::cout << prefix << "#clusters_valid:  " << valid << std::endl;
+        stats.t_lines += now_s() - tl;
+        std::cout << prefix << result.size() << " 3D lines found!" << std::endl;
+    }
+
+    // line3D.cc:1371-1389, 1392-1451, 1454-1476, 1479-1597
+    void alignCluster(const std::vector<int>& members, std::list<std::pair<V3, V3> >& seg3D, std::list<L3DSegment2D>& seg2D)
+    {
+        // the reference keys the cluster's segments by (cam, seg); equal keys cannot occur
+        std::vector<int> order(members);
+        std::sort(order.begin(), order.end(), [&](int a, int b) { return seg_key(hyps[a].cam, hyps[a].seg) < seg_key(hyps[b].cam, hyps[b].seg); });
+        const int m = int(order.size());
+        if (m == 0) return;
+        std::vector<V3> A1(m), A2(m);
+        for (int k = 0; k < m; ++k) { A1[k] = inverseTransform(hyps[order[k]].P1); A2[k] = inverseTransform(hyps[order[k]].P2); }
+        V3 P(0, 0, 0);
+        const int n = m * 2;
+        Eigen::MatrixXd g(3, n);
+        double szd = 0.0;
+        for (int k = 0; k < m; ++k) {
+            P += A1[k]; P += A2[k];
+            for (int r = 0; r < 3; ++r) { g(r, 2 * k) = A1[k](r); g(r, 2 * k + 1) = A2[k](r); }
+            szd += 2.0;
+        }
+        P /= szd;
+        Eigen::MatrixXd Cm = Eigen::MatrixXd::Identity(n, n) - (1.0 / double(n)) * Eigen::MatrixXd::Constant(n, n, 1.0);
+        Eigen::MatrixXd Scat = g * Cm * g.transpose();
+        Eigen::JacobiSVD<Eigen::MatrixXd> svd(Scat, Eigen::ComputeThinU);
+        Eigen::MatrixXd U = svd.matrixU(); Eigen::VectorXd S = svd.singularValues();
+        int mp; S.maxCoeff(&mp);
+        V3 dir(U(0, mp), U(1, mp), U(2, mp)); dir.normalize();
+        struct Pt { V3 P; unsigned seg3, cam; float dist; };
+        std::vector<Pt> pts;
+        V3 min_point(0.0, 0.0, 0.0), max_point(0.0, 0.0, 0.0);
+        double min_len = 0.0, max_len = 0.0;
+        for (int k = 0; k < m; ++k) {
+            V3 pr1 = P + (dir.dot(A1[k] - P) / (dir.norm() * dir.norm())) * dir;
+            V3 pr2 = P + (dir.dot(A2[k] - P) / (dir.norm() * dir.norm())) * dir;
+            double loc1 = dir.dot(P - pr1);
+            if (loc1 <= min_len) { min_len = loc1; min_point = pr1; }
+            if (loc1 >= max_len) { max_len = loc1; max_point = pr1; }
+            double loc2 = dir.dot(P - pr2);
+            if (loc2 <= min_len) { min_len = loc2; min_point = pr2; }
+            if (loc2 >= max_len) { max_len = loc2; max_point = pr2; }
+            Pt a; a.P = A1[k]; a.seg3 = unsigned(k); a.cam = hyps[order[k]].cam; a.dist = 0; Pt b = a; b.P = A2[k];
+            pts.push_back(a); pts.push_back(b);
+        }
+        for (size_t k = 0; k < pts.size(); ++k) pts[k].dist = float((pts[k].P - min_point).norm());
+        std::stable_sort(pts.begin(), pts.end(), [](const Pt& a, const Pt& b) { return a.dist < b.dist; });
+        std::map<unsigned, unsigned> open; std::set<unsigned> open_lines;
+        bool opened = false; V3 start(0, 0, 0);
+        for (size_t k = 0; k < pts.size(); ++k) {
+            const Pt& p = pts[k];
+            if (!open_lines.count(p.seg3)) { open_lines.insert(p.seg3); ++open[p.cam]; }
+            else { open_lines.erase(p.seg3); if (--open[p.cam] == 0) open.erase(p.cam); }
+            if (opened && open.size() < 3) { seg3D.push_back(std::make_pair(start, p.P)); opened = false; }
+            else if (!opened && open.size() >= 3) { start = p.P; opened = true; }
+        }
+        for (int k = 0; k < m; ++k) seg2D.push_back(L3DSegment2D(hyps[order[k]].cam, hyps[order[k]].seg));
+    }
+};
+
+// ------------------------------------------------------------------------------------------
+// public API
+// ------------------------------------------------------------------------------------------
+Line3D::Line3D(const std::string data_directory, const int matchingNeighbors, const float uncertainty_t_upper_2D,
+               const float uncertainty_t_lower_2D, const float sigma_p, const float sigma_a, const float min_baseline,
+               bool useCollinearity, bool verbose)
+{
+    impl_ = new Impl();
+    Impl& d = *impl_;
+    d.verbose = verbose; d.prefix = "[L3D] "; d.separator = "----------------------------------------";
+    d.data_directory = data_directory; d.matching_neighbors = matchingNeighbors;
+    d.unc_upper = fabs(uncertainty_t_upper_2D); d.unc_lower = fabs(uncertainty_t_lower_2D);              // line3D.cc:18-28
+    d.computation = false; d.use_collinearity = useCollinearity; d.min_baseline = min_baseline; d.measure_only = false;
+    if (d.unc_lower < 1.0f) d.unc_lower = 1.0f;
+    if (d.unc_upper <= d.unc_lower) d.unc_upper = d.unc_lower + 1.0f;
+    d.sigma_a = sigma_a; d.sigma_p = sigma_p;
+    boost::filesystem::path dir(data_directory);
+    boost::filesystem::create_directory(dir);
+    d.tr_scale = 1.0; d.tr_scale_inv = 1.0; d.tr_R = M3::Identity(); d.tr_Rinv = M3::Identity(); d.tr_t = V3(0.0, 0.0, 0.0); d.tr_tneg = V3(0.0, 0.0, 0.0);
+    int device = 0;
+    if (const char* e = getenv("L3D_DEVICE")) device = atoi(e);
+    if (l3d_create(device, &d.ctx)) {
+        std::string msg = std::string("Line3D: cannot open the CUDA device: ") + l3d_last_error(0);
+        std::cerr << d.prefix << msg << std::endl;
+        delete impl_; impl_ = 0;
+        throw std::runtime_error(msg);
+    }
+    std::cout << d.prefix << "Line3D - http://www.icg.tugraz.at/ - AerialVisionGroup" << std::endl;
+    std::cout << d.prefix << "(c) 2015, Manuel Hofer" << std::endl;
+    std::cout << d.prefix << "(B200 matching/scoring path: line3d-b200)" << std::endl;
+    std::cout << d.prefix << d.separator << std::endl;
+}
+
+Line3D::~Line3D()
+{
+    if (!impl_) return;
+    std::cout << impl_->prefix << impl_->separator << std::endl;
+    std::cout << impl_->prefix << ">>> EXITING SYSTEM <<<" << std::endl;
+    std::cout << impl_->prefix << "cleaning up..." << std::endl;
+    reset();
+    l3d_destroy(impl_->ctx);
+    delete impl_;
+}
+
+void Line3D::reset()                                                             // line3D.cc:62-92
+{
+    Impl& d = *impl_;
+    d.num_wps.clear(); d.common_wps.clear(); d.view_sim.clear(); d.wp2views.clear(); d.vn.clear(); d.fund.clear();
+    d.matched.clear(); d.best.clear(); d.potential.clear(); d.hyps.clear(); d.hyp_of.clear(); d.result.clear();
+    for (std::map<unsigned, ViewData*>::iterator it = d.views.begin(); it != d.views.end(); ++it) delete it->second;
+    d.views.clear();
+    d.computation = false;
+    if (d.ctx) l3d_reset_matching(d.ctx);
+}
+
+void Line3D::addImage(const unsigned int imageID, const cv::Mat image, const Eigen::Matrix3d K, const Eigen::Matrix3d R,
+                      const Eigen::Vector3d t, std::list<unsigned int>& worldpointIDs, const int maxImgWidth, const bool loadAndStoreSegments)
+{
+    Impl& d = *impl_;
+    if (!d.guards(imageID, image, worldpointIDs.size() != 0, "no worldpoints")) return;
+    if (!d.addView(imageID, image, K, R, t, maxImgWidth, loadAndStoreSegments)) return;
+    if (d.verbose) std::cout << d.prefix << "updating view neighborhoods using " << worldpointIDs.size() << " wps" << std::endl;
+    d.processWorldpoints(imageID, worldpointIDs);                                 // line3D.cc:216
+}
+
+void Line3D::addImage_fixed_sim(const unsigned int imageID, const cv::Mat image, const Eigen::Matrix3d K, const Eigen::Matrix3d R,
+                                const Eigen::Vector3d t, std::map<unsigned int, float>& viewSimilarity, const int maxImgWidth,
+                                const bool loadAndStoreSegments)
+{
+    Impl& d = *impl_;
+    if (!d.guards(imageID, image, viewSimilarity.size() != 0, "no view similarities")) return;
+    if (!d.addView(imageID, image, K, R, t, maxImgWidth, loadAndStoreSegments)) return;
+    for (std::map<unsigned, float>::iterator it = viewSimilarity.begin(); it != viewSimilarity.end(); ++it)   // line3D.cc:1938-1946
+        if (it->second > 0.01f) d.view_sim[imageID][it->first] = it->second;
+}
+
+void Line3D::compute3Dmodel(bool perform_diffusion)                              // line3D.cc:345-374
+{
+    Impl& d = *impl_;
+    if (d.views.size() < 4) { std::cerr << d.prefix << "not enough images! can't compute 3D model..." << std::endl; return; }
+    d.computation = true;
+    d.matched.clear(); d.potential.clear(); d.best.clear(); d.result.clear();
+    d.match_log.clear(); d.match_median.clear(); d.filtered_dump.clear(); d.edges_pre.clear(); d.edges_cluster.clear(); d.cluster_nodes = 0;
+    memset(&d.stats, 0, sizeof d.stats);
+    const uint64_t launches0 = l3d_kernel_launches(d.ctx);
+    const double t0 = now_s();
+    d.findVisualNeighbors();
+    d.transformGeometry();
+    d.stats.t_neighbors = now_s() - t0;
+    double t1 = now_s();
+    d.uploadViews();
+    d.stats.t_upload = now_s() - t1;
+    d.matchViews();
+    if (!d.measure_only) {
+        t1 = now_s();
+        d.buildHypotheses();
+        d.stats.t_hypotheses = now_s() - t1;
+        d.clusterSegments(perform_diffusion);
+    }
+    d.stats.t_total = now_s() - t0;
+    d.stats.kernel_launches = l3d_kernel_launches(d.ctx) - launches0;
+}
+
+void Line3D::getResult(std::list<L3D::L3DFinalLine3D>& result) { result.clear(); result = impl_->result; }   // line3D.cc:377-381
+unsigned int Line3D::numCameras() { return impl_->views.size(); }
+L3DRunStats Line3D::runStats() const { return impl_->stats; }
+void Line3D::setMeasureOnly(bool on) { impl_->measure_only = on; }
+
+float4 Line3D::getSegment2D(L3D::L3DSegment2D& seg2D)                            // line3D.cc:2004-2013, view.cc:275-288
+{
+    Impl& d = *impl_;
+    float4 zero; zero.x = zero.y = zero.z = zero.w = 0.0f;
+    std::map<unsigned, ViewData*>::iterator it = d.views.find(seg2D.camID());
+    if (it == d.views.end()) { std::cerr << d.prefix << "no view with ID " << seg2D.camID() << "!" << std::endl; return zero; }
+    if (seg2D.segID() < it->second->segs.size()) return it->second->segs[seg2D.segID()];
+    return zero;
+}
+
+void Line3D::save3DLinesAsSTL(std::list<L3D::L3DFinalLine3D>& result, std::string filename)   // line3D.cc:384-430
+{
+    std::ofstream file; file.open(filename.c_str());
+    file << "solid lineModel" << std::endl;
+    for (std::list<L3DFinalLine3D>::iterator it = result.begin(); it != result.end(); ++it) {
+        std::list<std::pair<V3, V3> >* s3 = it->segments3D();
+        for (std::list<std::pair<V3, V3> >::iterator s = s3->begin(); s != s3->end(); ++s) {
+            char a[6][50];
+            sprintf(a[0], "%e", s->first.x()); sprintf(a[1], "%e", s->first.y()); sprintf(a[2], "%e", s->first.z());
+            sprintf(a[3], "%e", s->second.x()); sprintf(a[4], "%e", s->second.y()); sprintf(a[5], "%e", s->second.z());
+            file << " facet normal 1.0e+000 0.0e+000 0.0e+000" << std::endl;
+            file << "  outer loop" << std::endl;
+            file << "   vertex " << a[0] << " " << a[1] << " " << a[2] << std::endl;
+            file << "   vertex " << a[3] << " " << a[4] << " " << a[5] << std::endl;
+            file << "   vertex " << a[0] << " " << a[1] << " " << a[2] << std::endl;
+            file << "  endloop" << std::endl;
+            file << " endfacet" << std::endl;
+        }
+    }
+    file << "endsolid lineModel" << std::endl;
+    file.close();
+}
+
+void Line3D::save3DLinesAsTXT(std::list<L3D::L3DFinalLine3D>& result, std::string filename)   // line3D.cc:433-473
+{
+    std::ofstream file; file.open(filename.c_str());
+    for (std::list<L3DFinalLine3D>::iterator it = result.begin(); it != result.end(); ++it) {
+        std::list<std::pair<V3, V3> >* s3 = it->segments3D();
+        if (s3->size() == 0) continue;
+        file << s3->size() << " ";
+        for (std::list<std::pair<V3, V3> >::iterator s = s3->begin(); s != s3->end(); ++s) {
+            file << s->first.x() << " " << s->first.y() << " " << s->first.z() << " ";
+            file << s->second.x() << " " << s->second.y() << " " << s->second.z() << " ";
+        }
+        std::list<L3DSegment2D>* s2 = it->segments2D();
+        file << s2->size() << " ";
+        for (std::list<L3DSegment2D>::iterator q = s2->begin(); q != s2->end(); ++q) {
+            file << q->camID() << " " << q->segID() << " ";
+            float4 c = getSegment2D(*q);
+            file << c.x << " " << c.y << " " << c.z << " " << c.w << " ";
+        }
+        file << std::endl;
+    }
+    file.close();
+}
+
+bool Line3D::writeSegmentCache(const std::string& data_directory, unsigned int imageID, unsigned int width, unsigned int height,
+                               bool collinearity_flag, const std::vector<float4>& segments)
+{
+    std::ofstream f(cacheName(data_directory, imageID, width, height, collinearity_flag).c_str(), std::ios::binary);
+    if (!f) return false;
+    f.write("L3DSEG01", 8);
+    uint32_t n = uint32_t(segments.size()), flags = 0;
+    f.write(reinterpret_cast<const char*>(&n), 4); f.write(reinterpret_cast<const char*>(&flags), 4);
+    if (n) f.write(reinterpret_cast<const char*>(segments.data()), std::streamsize(size_t(n) * sizeof(float4)));
+    return bool(f);
+}
+
+void Line3D::debugDump(const std::string& directory)
+{
+    Impl& d = *impl_;
+    const std::string p = directory + "/";
+    std::vector<int32_t> vn;
+    for (std::map<unsigned, std::vector<unsigned> >::iterator a = d.vn.begin(); a != d.vn.end(); ++a)
+        for (size_t k = 0; k < a->second.size(); ++k) { vn.push_back(int32_t(a->first)); vn.push_back(int32_t(a->second[k])); }
+    npy_i32(p + "visual_neighbors.npy", vn, 2);
+    std::vector<double> vw;
+    for (std::map<unsigned, ViewData*>::iterator a = d.views.begin(); a != d.views.end(); ++a) {
+        ViewData* v = a->second;
+        vw.push_back(a->first); vw.push_back(v->median_depth); vw.push_back(v->k_upper); vw.push_back(v->k_lower); vw.push_back(float(v->shifted(2.0f * d.sigma_p)));
+        for (int i = 0; i < 3; ++i) vw.push_back(v->C(i));
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) vw.push_back(v->RtKinv(r, c));
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 4; ++c) vw.push_back(v->P(r, c));
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) vw.push_back(v->K(r, c));
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) vw.push_back(v->R(r, c));
+        for (int i = 0; i < 3; ++i) vw.push_back(v->t(i));
+    }
+    npy_f64(p + "views.npy", vw, 50);
+    std::vector<double> fs;
+    for (std::map<unsigned, std::map<unsigned, M3> >::iterator a = d.fund.begin(); a != d.fund.end(); ++a)
+        for (std::map<unsigned, M3>::iterator b = a->second.begin(); b != a->second.end(); ++b) {
+            fs.push_back(a->first); fs.push_back(b->first);
+            for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) fs.push_back(b->second(r, c));
+        }
+    npy_f64(p + "fundamentals.npy", fs, 11);
+    std::vector<double> co;
+    for (std::map<unsigned, ViewData*>::iterator a = d.views.begin(); a != d.views.end(); ++a)
+        for (size_t s = 0; s < a->second->collin.size(); ++s)
+            for (size_t k = 0; k < a->second->collin[s].size(); ++k) { co.push_back(a->first); co.push_back(double(s)); co.push_back(a->second->collin[s][k].other); co.push_back(a->second->collin[s][k].w); }
+    npy_f64(p + "collinearity.npy", co, 4);
+    npy_i32(p + "match_log.npy", d.match_log, 4);
+    npy_f32(p + "match_median.npy", d.match_median, 1);
+    npy_f64(p + "filtered_matches.npy", d.filtered_dump, 9);
+    std::vector<double> bm;
+    for (size_t k = 0; k < d.hyps.size(); ++k) {
+        const Hypothesis& h = d.hyps[k];
+        bm.push_back(h.cam); bm.push_back(h.seg); bm.push_back(h.tgt_cam); bm.push_back(h.tgt_seg); bm.push_back(h.score); bm.push_back(1.0);
+        for (int i = 0; i < 3; ++i) bm.push_back(h.P1(i));
+        for (int i = 0; i < 3; ++i) bm.push_back(h.P2(i));
+        for (int i = 0; i < 3; ++i) bm.push_back(h.dir(i));
+        bm.push_back(h.d1); bm.push_back(h.d2);
+    }
+    npy_f64(p + "best_match.npy", bm, 17);
+    std::vector<int32_t> pc;
+    for (size_t k = 0; k < d.potential.size(); ++k) {
+        pc.push_back(int32_t(d.potential[k].first >> 32)); pc.push_back(int32_t(d.potential[k].first & 0xffffffffu));
+        pc.push_back(int32_t(d.potential[k].second >> 32)); pc.push_back(int32_t(d.potential[k].second & 0xffffffffu));
+    }
+    npy_i32(p + "potential.npy", pc, 4);
+    npy_f64(p + "edges_pre_diffusion.npy", d.edges_pre, 3);
+    npy_f64(p + "edges_cluster.npy", d.edges_cluster, 3);
+    std::vector<int32_t> nn(1, d.cluster_nodes); npy_i32(p + "cluster_nodes.npy", nn, 1);
+    std::vector<double> s3; std::vector<int32_t> s2; int li = 0;
+    for (std::list<L3DFinalLine3D>::iterator it = d.result.begin(); it != d.result.end(); ++it, ++li) {
+        for (std::list<std::pair<V3, V3> >::iterator s = it->segments3D()->begin(); s != it->segments3D()->end(); ++s) {
+            s3.push_back(li);
+            for (int i = 0; i < 3; ++i) s3.push_back(s->first(i));
+            for (int i = 0; i < 3; ++i) s3.push_back(s->second(i));
+        }
+        for (std::list<L3DSegment2D>::iterator q = it->segments2D()->begin(); q != it->segments2D()->end(); ++q) { s2.push_back(li); s2.push_back(int32_t(q->camID())); s2.push_back(int32_t(q->segID())); }
+    }
+    npy_f64(p + "lines_seg3d.npy", s3, 7);
+    npy_i32(p + "lines_seg2d.npy", s2, 3);
+    std::vector<double> tr; tr.push_back(d.tr_scale);
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) tr.push_back(d.tr_R(r, c));
+    for (int i = 0; i < 3; ++i) tr.push_back(d.tr_t(i));
+    npy_f64(p + "transform.npy", tr, 13);
+}
+
+}  // namespace L3D

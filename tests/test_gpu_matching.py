@@ -20,6 +20,10 @@ def _compare(dm, got):
         want = exp[exp[:, 0] == vid]
         assert res["n_delivered"] == int(r[2]), (vid, res["n_delivered"], r)
         assert rows.shape == want.shape, (vid, rows.shape, want.shape)
+        if not res["scored"]:
+            # no neighbour left to pair-test: the reference returns the delivered records unscored, in
+            # delivery order (cudawrapper.cu:877-878); the C ABI returns the same set sorted by (src, cam, tgt)
+            want = want[np.lexsort((want[:, 3], want[:, 2], want[:, 1]))]
         assert np.array_equal(rows[:, :4], want[:, :4]), f"view {vid}: match set differs"
         assert np.array_equal(rows[:, 4:8], want[:, 4:8]), f"view {vid}: depths differ"
         np.testing.assert_allclose(rows[:, 8], want[:, 8], rtol=1e-6, atol=0)
