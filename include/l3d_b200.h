@@ -146,6 +146,10 @@ int l3d_last_timings(l3d_ctx* ctx, float ms[6]);
 /* FP32 FFMA throughput of the device in TFLOP/s (register-only FMA chains, CUDA events):
  * the measured denominator for the FP32-pipe roofline. */
 int l3d_measure_fp32_peak(l3d_ctx* ctx, float* tflops);
+/* The device's float exp (which = 0) / acos (which = 1) as used inside the kernels, on an
+ * array: they are written to agree bit for bit with glibc's expf / acosf, which the
+ * reference's host build calls; tests compare them against libm. */
+int l3d_debug_math(l3d_ctx* ctx, int which, int n, const float* in, float* out);
 /* Number of kernels this library has launched on the context since creation. */
 uint64_t l3d_kernel_launches(const l3d_ctx* ctx);
 

@@ -72,6 +72,7 @@ def lib():
         L.l3d_diffuse.restype = C.c_int; L.l3d_diffuse.argtypes = [vp, C.c_int, C.c_size_t, vp, vp]
         L.l3d_last_timings.restype = C.c_int; L.l3d_last_timings.argtypes = [vp, C.POINTER(C.c_float)]
         L.l3d_measure_fp32_peak.restype = C.c_int; L.l3d_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_float)]
+        L.l3d_debug_math.restype = C.c_int; L.l3d_debug_math.argtypes = [vp, C.c_int, C.c_int, vp, vp]
         L.l3d_kernel_launches.restype = C.c_uint64; L.l3d_kernel_launches.argtypes = [vp]
         _lib = L
     return _lib
@@ -79,7 +80,7 @@ def lib():
 
 EXPORTS = ["l3d_create", "l3d_destroy", "l3d_last_error", "l3d_collinearity", "l3d_set_views", "l3d_match_view",
            "l3d_match_view_resident", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
-           "l3d_last_timings", "l3d_measure_fp32_peak", "l3d_kernel_launches"]
+           "l3d_last_timings", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math"]
 
 
 class Context:
@@ -191,6 +192,12 @@ class Context:
         t = C.c_float()
         self._check(self._L.l3d_measure_fp32_peak(self._h, C.byref(t)))
         return float(t.value)
+
+    def debug_math(self, which: int, x: np.ndarray) -> np.ndarray:
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        out = np.zeros_like(x)
+        self._check(self._L.l3d_debug_math(self._h, which, x.shape[0], x.ctypes.data, out.ctypes.data))
+        return out
 
     def kernel_launches(self) -> int:
         return int(self._L.l3d_kernel_launches(self._h))

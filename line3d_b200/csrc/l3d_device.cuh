@@ -139,12 +139,78 @@ __device__ __forceinline__ V3 xproject(const float* P, V3 X)
     return mk3(0.0f, 0.0f, 0.0f);
 }
 
-// float exp / acos as the reference's host build evaluates them (glibc expf, acosf): the
-// argument is exact in double, the result is rounded once to float.  glibc's own float
-// routines are not correctly rounded, so a result can differ from this by one ulp in
-// about 0.07 % (expf) / 0.01 % (acosf near 1) of the calls -- see DESIGN.md.
-__device__ __forceinline__ float xexpf(float x) { return float(exp(double(x))); }
-__device__ __forceinline__ float xacosf(float x) { return float(acos(double(x))); }
+// expf / acosf exactly as the C library behind the reference's host build evaluates them
+// (glibc 2.39).  The oracle and the CPU build of the reference call libm; to agree with
+// them bit for bit the device runs the same two algorithms:
+//   * expf: the table-driven double-precision routine glibc adopted from ARM's optimized
+//     routines (N = 32 table of 2^(i/32), cubic polynomial, result rounded once to float);
+//     T[i] = bits(2^(i/32)) - (i << 47), regenerated here from that definition;
+//   * acosf: the fdlibm single-precision routine (rational approximation R(z) = p(z)/q(z)
+//     on three ranges), every operation individually rounded in float.
+// tests/test_device_math.py checks both against libm on random and edge inputs.
+__device__ const unsigned long long L3D_EXP2F_TAB[32] = {
+    0x3ff0000000000000ull, 0x3fefd9b0d3158574ull, 0x3fefb5586cf9890full, 0x3fef9301d0125b51ull,
+    0x3fef72b83c7d517bull, 0x3fef54873168b9aaull, 0x3fef387a6e756238ull, 0x3fef1e9df51fdee1ull,
+    0x3fef06fe0a31b715ull, 0x3feef1a7373aa9cbull, 0x3feedea64c123422ull, 0x3feece086061892dull,
+    0x3feebfdad5362a27ull, 0x3feeb42b569d4f82ull, 0x3feeab07dd485429ull, 0x3feea47eb03a5585ull,
+    0x3feea09e667f3bcdull, 0x3fee9f75e8ec5f74ull, 0x3feea11473eb0187ull, 0x3feea589994cce13ull,
+    0x3feeace5422aa0dbull, 0x3feeb737b0cdc5e5ull, 0x3feec49182a3f090ull, 0x3feed503b23e255dull,
+    0x3feee89f995ad3adull, 0x3feeff76f2fb5e47ull, 0x3fef199bdd85529cull, 0x3fef3720dcef9069ull,
+    0x3fef5818dcfba487ull, 0x3fef7c97337b9b5full, 0x3fefa4afa2a490daull, 0x3fefd0765b6e4540ull};
+__device__ __forceinline__ float xexpf(float x)
+{
+    if (x < -103.972084f) return 0.0f;                       // underflow to zero, as libm
+    const double InvLn2N = 0x1.71547652b82fep+0 * 32.0;
+    const double C0 = 0x1.c6af84b912394p-5 / 32.0 / 32.0 / 32.0, C1 = 0x1.ebfce50fac4f3p-3 / 32.0 / 32.0, C2 = 0x1.62e42ff0c52d6p-1 / 32.0;
+    const double SHIFT = 0x1.8p+52;
+    double z = __dmul_rn(InvLn2N, double(x));
+    double kd = __dadd_rn(z, SHIFT);
+    unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
+    kd = __dsub_rn(kd, SHIFT);
+    double r = __dsub_rn(z, kd);
+    unsigned long long t = L3D_EXP2F_TAB[ki & 31ull] + (ki << 47);
+    double s = __longlong_as_double((long long)t);
+    double zz = __dadd_rn(__dmul_rn(C0, r), C1);
+    double r2 = __dmul_rn(r, r);
+    double y = __dadd_rn(__dmul_rn(C2, r), 1.0);
+    y = __dadd_rn(__dmul_rn(zz, r2), y);
+    y = __dmul_rn(y, s);
+    return __double2float_rn(y);
+}
+__device__ __forceinline__ float xacos_pq(float z)
+{
+    const float pS0 = 1.6666667163e-01f, pS1 = -3.2556581497e-01f, pS2 = 2.0121252537e-01f, pS3 = -4.0055535734e-02f,
+                pS4 = 7.9153501429e-04f, pS5 = 3.4793309169e-05f;
+    const float qS1 = -2.4033949375e+00f, qS2 = 2.0209457874e+00f, qS3 = -6.8828397989e-01f, qS4 = 7.7038154006e-02f;
+    float p = xm(z, xa(pS0, xm(z, xa(pS1, xm(z, xa(pS2, xm(z, xa(pS3, xm(z, xa(pS4, xm(z, pS5)))))))))));
+    float q = xa(1.0f, xm(z, xa(qS1, xm(z, xa(qS2, xm(z, xa(qS3, xm(z, qS4))))))));
+    return xd(p, q);
+}
+__device__ inline float xacosf(float x)
+{
+    const float pio2_hi = 1.5707962513e+00f, pio2_lo = 7.5497894159e-08f, pi = 3.1415925026e+00f;
+    const unsigned ix = __float_as_uint(x) & 0x7fffffffu;
+    if (ix == 0x3f800000u) return (x > 0.0f) ? 0.0f : xa(pi, xm(2.0f, pio2_lo));
+    if (ix > 0x3f800000u) return __int_as_float(0x7fc00000);
+    if (ix < 0x3f000000u) {                                   // |x| < 0.5
+        if (ix <= 0x32800000u) return xa(pio2_hi, pio2_lo);
+        float r = xacos_pq(xm(x, x));
+        return xs(pio2_hi, xs(x, xs(pio2_lo, xm(x, r))));
+    }
+    if (x < 0.0f) {                                           // x < -0.5
+        float z = xm(xa(1.0f, x), 0.5f);
+        float r = xacos_pq(z), s = xsqrt(z);
+        float w = xs(xm(r, s), pio2_lo);
+        return xs(pi, xm(2.0f, xa(s, w)));
+    }
+    float z = xm(xs(1.0f, x), 0.5f);                          // x > 0.5
+    float s = xsqrt(z);
+    float df = __uint_as_float(__float_as_uint(s) & 0xfffff000u);
+    float c = xd(xs(z, xm(df, df)), xa(s, df));
+    float r = xacos_pq(z);
+    float w = xa(xm(r, s), c);
+    return xm(2.0f, xa(df, w));
+}
 
 // cudawrapper.cu:118-130
 __device__ inline float xangle_deg_3d(V3 P1, V3 P2, V3 Q1, V3 Q2)

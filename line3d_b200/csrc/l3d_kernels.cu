@@ -838,6 +838,14 @@ __global__ void k_rdd_step(const int* __restrict__ prow, const int* __restrict__
     if (tpos[y] >= 0) pnext[tpos[y]] = mul;
 }
 
+// libm-compatible float functions, exposed for tests
+__global__ void k_debug_math(int which, const float* __restrict__ in, float* __restrict__ out, int n)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    out[k] = which == 0 ? xexpf(in[k]) : xacosf(in[k]);
+}
+
 // FP32 FFMA throughput probe
 __global__ void k_fma_probe(float* out, int iters)
 {
@@ -1379,6 +1387,22 @@ int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3
     cudaFreeAsync(d_prow, st); cudaFreeAsync(d_pcol, st); cudaFreeAsync(d_wcol, st); cudaFreeAsync(d_tpos, st); cudaFreeAsync(d_rstart, st);
     cudaFreeAsync(d_cstart, st); cudaFreeAsync(d_pa, st); cudaFreeAsync(d_pb, st); cudaFreeAsync(d_wval, st);
     L3D_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int l3d_debug_math(l3d_ctx* ctx, int which, int n, const float* in, float* out)
+{
+    if (!ctx) return 1;
+    if (n <= 0) return 0;
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    float *d_in, *d_out;
+    L3D_CUDA(cudaMalloc(&d_in, sizeof(float) * n)); L3D_CUDA(cudaMalloc(&d_out, sizeof(float) * n));
+    L3D_CUDA(cudaMemcpyAsync(d_in, in, sizeof(float) * n, cudaMemcpyHostToDevice, ctx->stream));
+    k_debug_math<<<(n + 255) / 256, 256, 0, ctx->stream>>>(which, d_in, d_out, n);
+    ctx->launches += 1;
+    L3D_CUDA(cudaMemcpyAsync(out, d_out, sizeof(float) * n, cudaMemcpyDeviceToHost, ctx->stream));
+    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+    cudaFree(d_in); cudaFree(d_out);
     return 0;
 }
 

@@ -28,18 +28,18 @@ def _check(dm_o, n_o, dm_g, n_g):
         assert dm_o[k].shape == dm_g[k].shape, k
         assert np.array_equal(dm_o[k], dm_g[k]), k
     assert np.array_equal(dm_o["views"], dm_g["views"])
-    # match sets identical, depths bit-exact, scores within 1e-6
+    # match sets, depths and scores: bit-exact
     fo, fg = dm_o["filtered_matches"], dm_g["filtered_matches"]
     assert fo.shape == fg.shape
     key = lambda a: np.lexsort((a[:, 3], a[:, 2], a[:, 1], a[:, 0]))
     fo, fg = fo[key(fo)], fg[key(fg)]
     assert np.array_equal(fo[:, :8], fg[:, :8])
-    np.testing.assert_allclose(fg[:, 8], fo[:, 8], rtol=1e-6)
+    assert np.array_equal(fo[:, 8], fg[:, 8])
     # hypotheses: same segments, coordinates within 1e-4 relative (they are in fact ~1e-15)
     bo, bg = dm_o["best_match"], dm_g["best_match"]
     assert bo.shape == bg.shape
     assert np.array_equal(bo[:, :4], bg[:, :4])
-    np.testing.assert_allclose(bg[:, 4], bo[:, 4], rtol=1e-6)
+    assert np.array_equal(bo[:, 4], bg[:, 4])
     np.testing.assert_allclose(bg[:, 6:15], bo[:, 6:15], rtol=1e-9, atol=1e-12)
     assert np.array_equal(bo[:, 15:], bg[:, 15:])
     # affinities feeding the clustering: same edges in the same order, weights within 1e-4 relative
