@@ -102,6 +102,7 @@ typedef struct {
     uint64_t n_scored;       /* n_raw + n_delivered                                       */
     uint64_t n_filtered;
     uint64_t score_iters;    /* sum over src segments of (matches of the segment)^2       */
+    uint64_t score_iters_other_cam; /* ... minus the same-camera pairs: the scoring work unit  */
     int32_t scored;
     float median_depth;      /* cudawrapper.cu:1066-1076                                  */
     const l3d_match* filtered;
@@ -143,6 +144,8 @@ int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3
  * [0] pre-test, [1] exact test, [2] assembly, [3] scoring, [4] reduce/filter/deliver,
  * [5] whole call on the device.  Timed with CUDA events on the context's stream. */
 int l3d_last_timings(l3d_ctx* ctx, float ms[6]);
+/* Overwrites a 256 MiB scratch buffer so that nothing of the previous step is left in L2. */
+int l3d_flush_l2(l3d_ctx* ctx);
 /* FP32 FFMA throughput of the device in TFLOP/s (register-only FMA chains, CUDA events):
  * the measured denominator for the FP32-pipe roofline. */
 int l3d_measure_fp32_peak(l3d_ctx* ctx, float* tflops);

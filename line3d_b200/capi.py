@@ -43,7 +43,8 @@ PAIR_DTYPE = np.dtype([("a", "<i4"), ("b", "<i4")])
 
 class MatchResult(C.Structure):
     _fields_ = [("pair_tests", C.c_uint64), ("n_candidates", C.c_uint64), ("n_raw", C.c_uint64), ("n_delivered", C.c_uint64),
-                ("n_scored", C.c_uint64), ("n_filtered", C.c_uint64), ("score_iters", C.c_uint64), ("scored", C.c_int32),
+                ("n_scored", C.c_uint64), ("n_filtered", C.c_uint64), ("score_iters", C.c_uint64), ("score_iters_other_cam", C.c_uint64),
+                ("scored", C.c_int32),
                 ("median_depth", C.c_float), ("filtered", C.POINTER(Match))]
 
 
@@ -72,6 +73,7 @@ def lib():
         L.l3d_diffuse.restype = C.c_int; L.l3d_diffuse.argtypes = [vp, C.c_int, C.c_size_t, vp, vp]
         L.l3d_last_timings.restype = C.c_int; L.l3d_last_timings.argtypes = [vp, C.POINTER(C.c_float)]
         L.l3d_measure_fp32_peak.restype = C.c_int; L.l3d_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_float)]
+        L.l3d_flush_l2.restype = C.c_int; L.l3d_flush_l2.argtypes = [vp]
         L.l3d_debug_math.restype = C.c_int; L.l3d_debug_math.argtypes = [vp, C.c_int, C.c_int, vp, vp]
         L.l3d_kernel_launches.restype = C.c_uint64; L.l3d_kernel_launches.argtypes = [vp]
         _lib = L
@@ -80,7 +82,7 @@ def lib():
 
 EXPORTS = ["l3d_create", "l3d_destroy", "l3d_last_error", "l3d_collinearity", "l3d_set_views", "l3d_match_view",
            "l3d_match_view_resident", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
-           "l3d_last_timings", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math"]
+           "l3d_last_timings", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math", "l3d_flush_l2"]
 
 
 class Context:
@@ -151,7 +153,8 @@ class Context:
         fn = self._L.l3d_match_view_resident if resident else self._L.l3d_match_view
         self._check(fn(self._h, view, len(neighbors), nb, sigma_p, sigma_a, C.byref(res)))
         out = dict(pair_tests=res.pair_tests, n_candidates=res.n_candidates, n_raw=res.n_raw, n_delivered=res.n_delivered,
-                   n_scored=res.n_scored, n_filtered=res.n_filtered, score_iters=res.score_iters, scored=bool(res.scored),
+                   n_scored=res.n_scored, n_filtered=res.n_filtered, score_iters=res.score_iters,
+                   score_iters_other_cam=res.score_iters_other_cam, scored=bool(res.scored),
                    median_depth=float(res.median_depth), filtered=None)
         if not resident:
             if res.n_filtered:
@@ -192,6 +195,9 @@ class Context:
         t = C.c_float()
         self._check(self._L.l3d_measure_fp32_peak(self._h, C.byref(t)))
         return float(t.value)
+
+    def flush_l2(self):
+        self._check(self._L.l3d_flush_l2(self._h))
 
     def debug_math(self, which: int, x: np.ndarray) -> np.ndarray:
         x = np.ascontiguousarray(x, dtype=np.float32)

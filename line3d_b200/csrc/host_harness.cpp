@@ -34,57 +34,95 @@ bool read_scene(const char* path, std::vector<SceneView>& views)
 }
 Eigen::Matrix3d mat3(const double* m) { Eigen::Matrix3d M; for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) M(r, c) = m[r * 3 + c]; return M; }
 double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+struct Session {
+    L3D::Line3D* l3d = nullptr;
+    bool verbose = false;
+    double t_add = 0.0;
+};
+struct Quiet {      // silences std::cout for the scope unless verbose
+    std::streambuf* old = nullptr; std::ostringstream sink;
+    explicit Quiet(bool verbose) { if (!verbose) old = std::cout.rdbuf(sink.rdbuf()); }
+    ~Quiet() { if (old) std::cout.rdbuf(old); }
+};
 }
 
 extern "C" {
 
-// stats_out: 20 doubles -- pair_tests, candidates, raw, scored, filtered, score_iters, hypotheses, affinity_pairs,
-// edges, kernel_launches, t_neighbors, t_upload, t_matching, t_matching_device, t_hypotheses, t_affinity, t_diffusion,
-// t_clustering, t_lines, t_total.  timings_out: addImage total, compute3Dmodel total (seconds, host clock).
-// repeat > 1 runs compute3Dmodel several times (the reference allows that, line3D.cc:356-358) and reports the last.
-int l3dhost_run_scene(const char* scene_path, const char* data_dir, int neighbors, float unc_upper, float unc_lower,
-                      float sigma_p, float sigma_a, float min_baseline, int collinearity, int diffusion, int verbose,
-                      int measure_only, int repeat, const char* dump_dir, double* timings_out, double* stats_out)
+// Line3D(...) + addImage for every view of the scene.  Returns an opaque session or NULL.
+void* l3dhost_open(const char* scene_path, const char* data_dir, int neighbors, float unc_upper, float unc_lower,
+                   float sigma_p, float sigma_a, float min_baseline, int collinearity, int verbose)
 {
     std::vector<SceneView> sv;
-    if (!read_scene(scene_path, sv)) return -1;
-    std::streambuf* old_cout = 0; std::ostringstream sink;
-    if (!verbose) old_cout = std::cout.rdbuf(sink.rdbuf());
-    int n_lines = -2;
+    if (!read_scene(scene_path, sv)) { std::cerr << "l3dhost_open: cannot read " << scene_path << std::endl; return nullptr; }
+    Quiet q(verbose != 0);
+    Session* s = new Session();
+    s->verbose = verbose != 0;
     try {
-        L3D::Line3D l3d(data_dir, neighbors, unc_upper, unc_lower, sigma_p, sigma_a, min_baseline, collinearity != 0, verbose != 0);
-        l3d.setMeasureOnly(measure_only != 0);
+        s->l3d = new L3D::Line3D(data_dir, neighbors, unc_upper, unc_lower, sigma_p, sigma_a, min_baseline, collinearity != 0, verbose != 0);
         const double t0 = now_s();
         for (size_t i = 0; i < sv.size(); ++i) {
             SceneView& v = sv[i];
             L3D::Line3D::writeSegmentCache(data_dir, v.id, v.width, v.height, collinearity != 0, v.segs);
             cv::Mat image(int(v.height), int(v.width), CV_8UC3);
             std::list<unsigned int> wps(v.wps.begin(), v.wps.end());
-            l3d.addImage(v.id, image, mat3(v.K), mat3(v.R), Eigen::Vector3d(v.t[0], v.t[1], v.t[2]), wps, int(std::max(v.width, v.height)), true);
+            s->l3d->addImage(v.id, image, mat3(v.K), mat3(v.R), Eigen::Vector3d(v.t[0], v.t[1], v.t[2]), wps, int(std::max(v.width, v.height)), true);
         }
+        s->t_add = now_s() - t0;
+    } catch (const std::exception& e) {
+        std::cerr << "l3dhost_open: " << e.what() << std::endl;
+        delete s->l3d; delete s;
+        return nullptr;
+    }
+    return s;
+}
+
+// compute3Dmodel + getResult.  stats_out: 30 doubles (see line3d_b200/host.py STAT_NAMES).
+// Returns the number of 3-D lines or < 0.
+int l3dhost_compute(void* session, int diffusion, int measure_only, int flush_l2, double* wall_out, double* stats_out)
+{
+    Session* s = static_cast<Session*>(session);
+    if (!s || !s->l3d) return -1;
+    Quiet q(s->verbose);
+    try {
+        s->l3d->setMeasureOnly(measure_only != 0);
+        s->l3d->setFlushL2(flush_l2 != 0);
+        const double t0 = now_s();
+        s->l3d->compute3Dmodel(diffusion != 0);
         const double t1 = now_s();
-        double t2 = t1, t3 = t1;
-        for (int r = 0; r < (repeat < 1 ? 1 : repeat); ++r) { t2 = now_s(); l3d.compute3Dmodel(diffusion != 0); t3 = now_s(); }
-        if (timings_out) { timings_out[0] = t1 - t0; timings_out[1] = t3 - t2; }
+        if (wall_out) { wall_out[0] = s->t_add; wall_out[1] = t1 - t0; }
         if (stats_out) {
-            L3D::L3DRunStats s = l3d.runStats();
-            const double v[20] = {double(s.pair_tests), double(s.candidates), double(s.raw_matches), double(s.scored_matches), double(s.filtered_matches),
-                                  double(s.score_iters), double(s.hypotheses), double(s.affinity_pairs), double(s.edges), double(s.kernel_launches),
-                                  s.t_neighbors, s.t_upload, s.t_matching, s.t_matching_device, s.t_hypotheses, s.t_affinity, s.t_diffusion,
-                                  s.t_clustering, s.t_lines, s.t_total};
+            L3D::L3DRunStats st = s->l3d->runStats();
+            const double v[30] = {double(st.pair_tests), double(st.candidates), double(st.raw_matches), double(st.scored_matches), double(st.filtered_matches),
+                                  double(st.score_iters), double(st.score_iters_other_cam), double(st.hypotheses), double(st.affinity_pairs), double(st.edges),
+                                  double(st.kernel_launches), st.t_neighbors, st.t_upload, st.t_matching, st.t_matching_device, st.t_hypotheses, st.t_affinity,
+                                  st.t_diffusion, st.t_clustering, st.t_lines, st.t_total, st.t_stage[0], st.t_stage[1], st.t_stage[2], st.t_stage[3], st.t_stage[4],
+                                  double(st.h2d_bytes), double(st.d2h_bytes), 0.0, 0.0};
             std::memcpy(stats_out, v, sizeof v);
         }
-        if (dump_dir && dump_dir[0]) l3d.debugDump(dump_dir);
         std::list<L3D::L3DFinalLine3D> result;
-        l3d.getResult(result);
-        n_lines = int(result.size());
+        s->l3d->getResult(result);
+        return int(result.size());
     } catch (const std::exception& e) {
-        if (old_cout) std::cout.rdbuf(old_cout);
-        std::cerr << "l3dhost_run_scene: " << e.what() << std::endl;
+        std::cerr << "l3dhost_compute: " << e.what() << std::endl;
         return -3;
     }
-    if (old_cout) std::cout.rdbuf(old_cout);
-    return n_lines;
+}
+
+int l3dhost_dump(void* session, const char* dump_dir)
+{
+    Session* s = static_cast<Session*>(session);
+    if (!s || !s->l3d || !dump_dir) return -1;
+    s->l3d->debugDump(dump_dir);
+    return 0;
+}
+
+void l3dhost_close(void* session)
+{
+    Session* s = static_cast<Session*>(session);
+    if (!s) return;
+    { Quiet q(s->verbose); delete s->l3d; }
+    delete s;
 }
 
 }  // extern "C"

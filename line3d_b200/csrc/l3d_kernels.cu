@@ -541,7 +541,7 @@ __global__ void __launch_bounds__(SC_T) k_score(const float4* __restrict__ segs,
 // ------------------------------------------------------------------------------------------
 __global__ void k_seg_reduce(const int* __restrict__ off, int n_cams, int n_src, const float* __restrict__ score,
                              const float4* __restrict__ m_dep, int* __restrict__ fcnt, float* __restrict__ dsamples,
-                             unsigned long long* __restrict__ iters)
+                             unsigned long long* __restrict__ iters /* [0] all pairs, [1] same-camera pairs */)
 {
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (row >= n_src) return;
@@ -565,6 +565,13 @@ __global__ void k_seg_reduce(const int* __restrict__ off, int n_cams, int n_src,
         dsamples[2 * row] = a; dsamples[2 * row + 1] = b;
         unsigned long long m = (unsigned long long)(s1 - s0);
         if (m) atomicAdd(iters, m * m);
+    }
+    if (s1 > s0) {
+        unsigned long long same = 0;
+        for (int c = lane; c < n_cams; c += 32) { unsigned long long g = (unsigned long long)(off[row * n_cams + c + 1] - off[row * n_cams + c]); same += g * g; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) same += __shfl_xor_sync(0xffffffffu, same, o);
+        if (lane == 0 && same) atomicAdd(iters + 1, same);
     }
 }
 
@@ -903,6 +910,7 @@ struct l3d_ctx {
     // hypotheses
     DBuf<Hyp> d_hyp; size_t n_hyp = 0; DBuf<l3d_hypothesis_in> d_hin; DBuf<l3d_segment3d> d_hout;
     DBuf<l3d_pair> d_pairs; DBuf<float> d_aff, d_medians;
+    DBuf<unsigned char> d_flush; int flush_value = 0;
     // timing
     cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     float last_ms[6] = {0, 0, 0, 0, 0, 0};
@@ -1063,8 +1071,8 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         ScoreParams sp; sp.sigma_p = sigma_p; sp.sigma_a = sigma_a;
         // grid.x covers the longest segment; shorter ones exit at once
         L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_src) + 1)); L3D_CUDA(ctx->d_foff.ensure(size_t(n_src) + 2));
-        L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2)); L3D_CUDA(ctx->d_median.ensure(4)); L3D_CUDA(ctx->d_iters.ensure(1));
-        L3D_CUDA(cudaMemsetAsync(ctx->d_iters.p, 0, sizeof(unsigned long long), st));
+        L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2)); L3D_CUDA(ctx->d_median.ensure(4)); L3D_CUDA(ctx->d_iters.ensure(2));
+        L3D_CUDA(cudaMemsetAsync(ctx->d_iters.p, 0, 2 * sizeof(unsigned long long), st));
         // longest segment: take it from the count matrix on the host side cheaply via the reduce kernel's iteration count later;
         // here bound it by the number of target segments summed over cameras
         long bound = 0;
@@ -1083,9 +1091,9 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         ctx->launches += 2;
         if (scan_exclusive(ctx, ctx->d_fcnt.p, ctx->d_foff.p, n_src)) return 1;
         if (fetch_int(ctx, ctx->d_foff.p + n_src, &F)) return 1;
-        L3D_CUDA(ctx->h_floats.ensure(4)); L3D_CUDA(ctx->h_u64.ensure(1));
+        L3D_CUDA(ctx->h_floats.ensure(4)); L3D_CUDA(ctx->h_u64.ensure(2));
         L3D_CUDA(cudaMemcpyAsync(ctx->h_floats.p, ctx->d_median.p, sizeof(float), cudaMemcpyDeviceToHost, st));
-        L3D_CUDA(cudaMemcpyAsync(ctx->h_u64.p, ctx->d_iters.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_u64.p, ctx->d_iters.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
         L3D_CUDA(ctx->d_filtered.ensure(size_t(std::max(F, 1))));
         if (F > 0) {
             k_filter_fill<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, ctx->d_filtered.p);
@@ -1146,7 +1154,7 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         L3D_CUDA(cudaMemcpyAsync(ctx->h_filtered.p, ctx->d_filtered.p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, st));
     }
     L3D_CUDA(cudaStreamSynchronize(st));
-    if (scored && M > 0) { median = ctx->h_floats.p[0]; res->score_iters = ctx->h_u64.p[0]; }
+    if (scored && M > 0) { median = ctx->h_floats.p[0]; res->score_iters = ctx->h_u64.p[0]; res->score_iters_other_cam = ctx->h_u64.p[0] - ctx->h_u64.p[1]; }
     res->median_depth = median;
     res->n_filtered = uint64_t(F);
     res->filtered = (copy_back && F > 0) ? ctx->h_filtered.p : nullptr;
@@ -1213,7 +1221,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_filtered.release(); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_cams.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
-    ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release();
+    ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release();
     for (int k = 0; k < 8; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -1410,6 +1418,17 @@ int l3d_last_timings(l3d_ctx* ctx, float ms[6])
 {
     if (!ctx || !ms) return 1;
     for (int k = 0; k < 6; ++k) ms[k] = ctx->last_ms[k];
+    return 0;
+}
+
+int l3d_flush_l2(l3d_ctx* ctx)
+{
+    if (!ctx) return 1;
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    const size_t bytes = size_t(256) << 20;
+    L3D_CUDA(ctx->d_flush.ensure(bytes));
+    L3D_CUDA(cudaMemsetAsync(ctx->d_flush.p, ctx->flush_value++ & 0xff, bytes, ctx->stream));
+    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
 

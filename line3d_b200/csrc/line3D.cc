@@ -112,7 +112,7 @@ std::string cacheName(const std::string& dir, unsigned id, unsigned w, unsigned 
 
 struct Line3D::Impl
 {
-    bool verbose, computation, use_collinearity, measure_only;
+    bool verbose, computation, use_collinearity, measure_only, flush_l2;
     std::string prefix, separator, data_directory;
     int matching_neighbors; float min_baseline, unc_upper, unc_lower, sigma_p, sigma_a;
     l3d_ctx* ctx;
@@ -374,6 +374,7 @@ struct Line3D::Impl
             o.k_lower = v->k_lower; o.k_upper = v->k_upper;
         }
         if (l3d_set_views(ctx, int(lv.size()), lv.data())) fail("l3d_set_views");
+        for (size_t k = 0; k < lv.size(); ++k) stats.h2d_bytes += size_t(lv[k].n_segments) * 16 + sizeof(l3d_view);
     }
 
     // line3D.cc:620-648 + 698-885
@@ -403,6 +404,9 @@ struct Line3D::Impl
             if (rc) fail("l3d_match_view");
             stats.t_matching += now_s() - t0;
             float ms[6]; l3d_last_timings(ctx, ms); stats.t_matching_device += double(ms[5]) * 1e-3;
+            for (int k = 0; k < 5; ++k) stats.t_stage[k] += double(ms[k]) * 1e-3;
+            stats.score_iters_other_cam += res.score_iters_other_cam;
+            stats.h2d_bytes += nb.size() * 160; stats.d2h_bytes += (measure_only ? 0 : res.n_filtered * sizeof(l3d_match)) + 64;
             stats.pair_tests += res.pair_tests; stats.candidates += res.n_candidates; stats.raw_matches += res.n_raw;
             stats.scored_matches += res.n_scored; stats.filtered_matches += res.n_filtered; stats.score_iters += res.score_iters;
             if (verbose) {
@@ -691,7 +695,7 @@ Line3D::Line3D(const std::string data_directory, const int matchingNeighbors, co
     d.verbose = verbose; d.prefix = "[L3D] "; d.separator = "----------------------------------------";
     d.data_directory = data_directory; d.matching_neighbors = matchingNeighbors;
     d.unc_upper = fabs(uncertainty_t_upper_2D); d.unc_lower = fabs(uncertainty_t_lower_2D);              // line3D.cc:18-28
-    d.computation = false; d.use_collinearity = useCollinearity; d.min_baseline = min_baseline; d.measure_only = false;
+    d.computation = false; d.use_collinearity = useCollinearity; d.min_baseline = min_baseline; d.measure_only = false; d.flush_l2 = false;
     if (d.unc_lower < 1.0f) d.unc_lower = 1.0f;
     if (d.unc_upper <= d.unc_lower) d.unc_upper = d.unc_lower + 1.0f;
     d.sigma_a = sigma_a; d.sigma_p = sigma_p;
@@ -771,6 +775,7 @@ void Line3D::compute3Dmodel(bool perform_diffusion)                             
     double t1 = now_s();
     d.uploadViews();
     d.stats.t_upload = now_s() - t1;
+    if (d.flush_l2) l3d_flush_l2(d.ctx);
     d.matchViews();
     if (!d.measure_only) {
         t1 = now_s();
@@ -786,6 +791,7 @@ void Line3D::getResult(std::list<L3D::L3DFinalLine3D>& result) { result.clear();
 unsigned int Line3D::numCameras() { return impl_->views.size(); }
 L3DRunStats Line3D::runStats() const { return impl_->stats; }
 void Line3D::setMeasureOnly(bool on) { impl_->measure_only = on; }
+void Line3D::setFlushL2(bool on) { impl_->flush_l2 = on; }
 
 float4 Line3D::getSegment2D(L3D::L3DSegment2D& seg2D)                            // line3D.cc:2004-2013, view.cc:275-288
 {

@@ -77,9 +77,11 @@ namespace L3D
     // Counters and timers of the last compute3Dmodel() (extension; not in the reference).
     struct L3DRunStats
     {
-        unsigned long long pair_tests, candidates, raw_matches, scored_matches, filtered_matches, score_iters;
+        unsigned long long pair_tests, candidates, raw_matches, scored_matches, filtered_matches, score_iters, score_iters_other_cam;
         unsigned long long hypotheses, affinity_pairs, edges, kernel_launches;
         double t_neighbors, t_upload, t_matching, t_matching_device, t_hypotheses, t_affinity, t_diffusion, t_clustering, t_lines, t_total;
+        double t_stage[5];   // device seconds: pre-test, exact test, assembly, scoring, reduce/filter/deliver
+        unsigned long long h2d_bytes, d2h_bytes;
     };
 
     class Line3D
@@ -128,6 +130,8 @@ namespace L3D
         // run matching without copying per-view results to the host (measurement only;
         // the later stages are skipped)
         void setMeasureOnly(bool on);
+        // flush the GPU's L2 before the matching phase of every compute3Dmodel() (measurement only)
+        void setFlushL2(bool on);
 
     private:
         struct Impl;

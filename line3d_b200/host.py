@@ -6,6 +6,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import shutil
 import tempfile
 
 import numpy as np
@@ -18,9 +19,10 @@ HOST_LIB = os.path.join(_HERE, "libline3d_host.so")
 DEFAULTS = dict(neighbors=10, unc_upper=5.0, unc_lower=1.0, sigma_p=3.5, sigma_a=10.0,
                 min_baseline=0.25, collinearity=True, diffusion=False)  # commons.h:42-61
 
-STAT_NAMES = ["pair_tests", "candidates", "raw_matches", "scored_matches", "filtered_matches", "score_iters", "hypotheses",
-              "affinity_pairs", "edges", "kernel_launches", "t_neighbors", "t_upload", "t_matching", "t_matching_device",
-              "t_hypotheses", "t_affinity", "t_diffusion", "t_clustering", "t_lines", "t_total"]
+STAT_NAMES = ["pair_tests", "candidates", "raw_matches", "scored_matches", "filtered_matches", "score_iters", "score_iters_other_cam",
+              "hypotheses", "affinity_pairs", "edges", "kernel_launches", "t_neighbors", "t_upload", "t_matching", "t_matching_device",
+              "t_hypotheses", "t_affinity", "t_diffusion", "t_clustering", "t_lines", "t_total", "t_pretest", "t_exact", "t_assemble",
+              "t_score", "t_reduce", "h2d_bytes", "d2h_bytes", "_r0", "_r1"]
 
 _lib = None
 
@@ -32,26 +34,66 @@ def lib():
         if not os.path.exists(HOST_LIB):
             raise capi.L3DError(f"{HOST_LIB} is missing: build it with __graft_entry__.build()")
         L = C.CDLL(HOST_LIB)
-        L.l3dhost_run_scene.restype = C.c_int
-        L.l3dhost_run_scene.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
-                                        C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.l3dhost_open.restype = C.c_void_p
+        L.l3dhost_open.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
+        L.l3dhost_compute.restype = C.c_int
+        L.l3dhost_compute.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.l3dhost_dump.restype = C.c_int; L.l3dhost_dump.argtypes = [C.c_void_p, C.c_char_p]
+        L.l3dhost_close.restype = None; L.l3dhost_close.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
 
-def run_scene(scene_path: str, dump_dir: str | None = None, verbose: bool = False, measure_only: bool = False, repeat: int = 1, **params):
-    """Returns (n_lines, timings, stats, dumps)."""
-    p = dict(DEFAULTS); p.update(params)
-    tm = (C.c_double * 2)(); st = (C.c_double * 20)()
-    with tempfile.TemporaryDirectory(prefix="l3d_data_") as data_dir:
-        n = lib().l3dhost_run_scene(scene_path.encode(), data_dir.encode(), int(p["neighbors"]), p["unc_upper"], p["unc_lower"],
-                                    p["sigma_p"], p["sigma_a"], p["min_baseline"], int(bool(p["collinearity"])), int(bool(p["diffusion"])),
-                                    int(verbose), int(measure_only), int(repeat), (dump_dir or "").encode(), tm, st)
-    if n < 0:
-        raise capi.L3DError(f"l3dhost_run_scene failed with code {n}")
-    timings = dict(add_image=tm[0], compute3Dmodel=tm[1])
-    stats = dict(zip(STAT_NAMES, [float(x) for x in st]))
-    dumps = None
-    if dump_dir:
-        dumps = {f[:-4]: np.load(os.path.join(dump_dir, f)) for f in sorted(os.listdir(dump_dir)) if f.endswith(".npy")}
-    return n, timings, stats, dumps
+class Session:
+    """Line3D(...) + addImage for every view of a scene file; compute() = compute3Dmodel + getResult."""
+
+    def __init__(self, scene_path: str, verbose: bool = False, device: int | None = None, **params):
+        p = dict(DEFAULTS); p.update(params)
+        self.params = p
+        self._data_dir = tempfile.mkdtemp(prefix="l3d_data_")
+        if device is not None:
+            os.environ["L3D_DEVICE"] = str(device)
+        self._h = lib().l3dhost_open(scene_path.encode(), self._data_dir.encode(), int(p["neighbors"]), p["unc_upper"], p["unc_lower"],
+                                     p["sigma_p"], p["sigma_a"], p["min_baseline"], int(bool(p["collinearity"])), int(verbose))
+        if not self._h:
+            shutil.rmtree(self._data_dir, ignore_errors=True)
+            raise capi.L3DError("l3dhost_open failed (no CUDA device, or unreadable scene)")
+
+    def compute(self, measure_only: bool = False, flush_l2: bool = False, diffusion: bool | None = None):
+        wall = (C.c_double * 2)(); st = (C.c_double * 30)()
+        dif = self.params["diffusion"] if diffusion is None else diffusion
+        n = lib().l3dhost_compute(self._h, int(bool(dif)), int(measure_only), int(flush_l2), wall, st)
+        if n < 0:
+            raise capi.L3DError(f"l3dhost_compute failed with code {n}")
+        stats = dict(zip(STAT_NAMES, [float(x) for x in st]))
+        return n, dict(add_image=wall[0], compute3Dmodel=wall[1]), stats
+
+    def dump(self) -> dict:
+        d = tempfile.mkdtemp(prefix="l3d_dump_")
+        lib().l3dhost_dump(self._h, d.encode())
+        out = {f[:-4]: np.load(os.path.join(d, f)) for f in sorted(os.listdir(d)) if f.endswith(".npy")}
+        shutil.rmtree(d, ignore_errors=True)
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().l3dhost_close(self._h)
+            self._h = None
+            shutil.rmtree(self._data_dir, ignore_errors=True)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def run_scene(scene_path: str, dump_dir: str | None = None, verbose: bool = False, **params):
+    """One-shot convenience: returns (n_lines, timings, stats, dumps)."""
+    s = Session(scene_path, verbose=verbose, **params)
+    try:
+        n, tm, st = s.compute()
+        dumps = s.dump() if dump_dir is not None else None
+    finally:
+        s.close()
+    return n, tm, st, dumps

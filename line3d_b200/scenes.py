@@ -30,6 +30,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 IMG_W, IMG_H, FOCAL = 1920, 1280, 1600.0
+_REAL_COUNTS: list = []   # number of projected (non-clutter) segments of the views generated so far (diagnostics)
 MAGIC = b"L3DSCN01"
 
 
@@ -177,21 +178,35 @@ def _project_view(edges, normals, K, R, t, rng, n_target, noise=0.3, frag=0.2, m
     facing = np.einsum("ij,ij->i", normals, C[None, :] - mid) > 0.0
     E = edges[facing]
     near = 0.5
-    out = []
     Pc = (E @ R.T) + t  # (E,2,3) camera coordinates
-    for a, b in Pc:
-        if a[2] < near and b[2] < near:
-            continue
-        if a[2] < near:
-            a = a + (near - a[2]) / (b[2] - a[2]) * (b - a)
-        elif b[2] < near:
-            b = b + (near - b[2]) / (a[2] - b[2]) * (a - b)
-        pa = (K @ a); pa = pa[:2] / pa[2]
-        pb = (K @ b); pb = pb[:2] / pb[2]
-        c = _clip_2d(pa, pb, IMG_W - 1.0, IMG_H - 1.0)
-        if c is None:
-            continue
-        out.append(np.concatenate(c))
+    A, B = Pc[:, 0, :].copy(), Pc[:, 1, :].copy()
+    keep = ~((A[:, 2] < near) & (B[:, 2] < near))
+    A, B = A[keep], B[keep]
+    # clip against the near plane
+    with np.errstate(divide="ignore", invalid="ignore"):
+        fa = np.nan_to_num((near - A[:, 2]) / (B[:, 2] - A[:, 2]), nan=0.0, posinf=0.0, neginf=0.0)
+        fb = np.nan_to_num((near - B[:, 2]) / (A[:, 2] - B[:, 2]), nan=0.0, posinf=0.0, neginf=0.0)
+    ca, cb = A[:, 2] < near, B[:, 2] < near
+    A2 = np.where(ca[:, None], A + fa[:, None] * (B - A), A)
+    B2 = np.where(cb[:, None], B + fb[:, None] * (A - B), B)
+    pa = A2 @ K.T; pa = pa[:, :2] / pa[:, 2:3]
+    pb = B2 @ K.T; pb = pb[:, :2] / pb[:, 2:3]
+    # Liang-Barsky against [0, W-1] x [0, H-1], all segments at once
+    w, h = IMG_W - 1.0, IMG_H - 1.0
+    d = pb - pa
+    t0 = np.zeros(pa.shape[0]); t1 = np.ones(pa.shape[0]); ok = np.ones(pa.shape[0], dtype=bool)
+    for pi, qi in ((-d[:, 0], pa[:, 0]), (d[:, 0], w - pa[:, 0]), (-d[:, 1], pa[:, 1]), (d[:, 1], h - pa[:, 1])):
+        par = pi == 0.0
+        ok &= ~(par & (qi < 0.0))
+        with np.errstate(divide="ignore", invalid="ignore"):
+            r = np.where(par, 0.0, qi / np.where(par, 1.0, pi))
+        neg = (pi < 0.0)
+        pos = (pi > 0.0)
+        ok &= ~(neg & (r > t1)); t0 = np.where(neg & ok, np.maximum(t0, r), t0)
+        ok &= ~(pos & (r < t0)); t1 = np.where(pos & ok, np.minimum(t1, r), t1)
+    ca_ = pa + t0[:, None] * d
+    cb_ = pa + t1[:, None] * d
+    out = np.concatenate([ca_, cb_], 1)[ok]
     segs = np.array(out, dtype=np.float64).reshape(-1, 4)
     # fragmentation: split 20 % of the segments at a random interior point, small gap
     if segs.shape[0]:
@@ -206,6 +221,7 @@ def _project_view(edges, normals, K, R, t, rng, n_target, noise=0.3, frag=0.2, m
         segs = segs + rng.normal(0.0, noise, segs.shape)
         ln = np.hypot(segs[:, 0] - segs[:, 2], segs[:, 1] - segs[:, 3])
         segs = segs[ln > min_len]
+    _REAL_COUNTS.append(segs.shape[0])
     # trim (keep the longest, like the detector's cap) or pad with clutter
     if segs.shape[0] < n_target:
         k = n_target - segs.shape[0]
@@ -301,28 +317,36 @@ def urban(n_views=200, n_seg=2000, seed=1002, blocks=(4, 3)):
             buildings.append((i * pitch_x, j * pitch_y, sx, sy, sz))
     # street centre lines run between block rows: a serpentine trajectory
     path = []
-    xs0, xs1 = -10.0, bx * pitch_x - 6.0
+    xs0, xs1 = 4.0, (bx - 1) * pitch_x + 12.0     # keep the look-ahead target inside the blocks
     for j in range(by + 1):
         y = j * pitch_y - 8.0
         seg = np.linspace(xs0, xs1, 200)
         if j % 2:
             seg = seg[::-1]
         for x in seg:
-            path.append((x, y))
+            path.append((x, y, j))
     path = np.array(path)
     idx = np.linspace(0, len(path) - 1, n_views).round().astype(int)
     cams = []
     for k, i in enumerate(idx):
-        x, y = path[i]
+        x, y, street = path[i]
         side = 1.0 if (k % 2 == 0) else -1.0
+        if street == 0:
+            side = 1.0          # outer streets: only one side has buildings
+        elif street == by:
+            side = -1.0
         j = min(i + 5, len(path) - 1)
-        dx, dy = path[j] - path[i]
+        dx, dy = path[j][:2] - path[i][:2]
+        if path[j][2] != street:
+            dx, dy = path[i][:2] - path[max(i - 5, 0)][:2]
         nrm = np.hypot(dx, dy)
         if nrm < 1e-9:
             dx, dy = 1.0, 0.0; nrm = 1.0
         dx, dy = dx / nrm, dy / nrm
         # look obliquely at the facades on alternating sides of the street
-        tgt = (x + 12.0 * dx - side * 14.0 * dy, y + 12.0 * dy + side * 14.0 * dx, 9.0)
+        # street direction alternates (serpentine): "side" is meant in world +y / -y terms
+        sgn = 1.0 if dx >= 0 else -1.0
+        tgt = (x + 12.0 * dx - sgn * side * 14.0 * dy, y + 12.0 * dy + sgn * side * 14.0 * dx, 9.0)
         cams.append(((x, y, 1.7 + 0.2 * np.sin(k)), tgt))
     return _assemble("urban", buildings, cams, n_seg, seed, n_wp=20000, win=1.5)
 
