@@ -263,13 +263,14 @@ def ours(args) -> None:
                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
                config=dict(workload=f"{args.config}: {c['kw']['n_views']} views x ~{c['kw']['n_seg']} segments, k={c['k']}, no diffusion"
                                     + (f", one such district per GPU ({world} districts)" if world > 1 else ""),
-                           pair_tests_per_step=int(tot_pairs), raw_matches_per_step=int(s["raw_matches"]),
+                           pair_tests_per_step=int(tot_pairs), candidates_per_step=int(s["candidates"]), raw_matches_per_step=int(s["raw_matches"]),
                            scoring_iterations_per_step=int(s["score_iters"]), l2="flushed between steps (256 MiB memset); the per-step working set "
                            "(match lists of all views) is far larger than L2 anyway"),
                device_ms_per_step=1e3 * t_dev_max, loop_wall_s=loop_wall, clocks=clocks, gpu_launches=launches,
                e2e=dict(value=tot_pairs / t_e2e_max, unit=UNIT, h2d_bytes_per_step=int(st_e["h2d_bytes"]), d2h_bytes_per_step=int(st_e["d2h_bytes"]),
                         ms_per_step=1e3 * t_e2e_max, api="Line3D::compute3Dmodel -> l3d_set_views + l3d_match_view per view (host buffers)",
-                        compute3Dmodel_ms=1e3 * float(np.mean([tm["compute3Dmodel"] for tm, _ in e2e_stats]))),
+                        compute3Dmodel_ms=1e3 * float(np.mean([tm["compute3Dmodel"] for tm, _ in e2e_stats])),
+                        host_stages_ms={k[2:]: 1e3 * st_e[k] for k in ("t_neighbors", "t_upload", "t_matching", "t_hypotheses", "t_affinity", "t_diffusion", "t_clustering", "t_lines")}),
                roofline=roofline)
     if cb:
         out["cpu_baseline"] = cb

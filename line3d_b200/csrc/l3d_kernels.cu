@@ -242,7 +242,7 @@ __device__ __forceinline__ void side_bounds(float e1a, float e1b, float e2a, flo
 }
 
 constexpr int PT_THREADS = 128;     // rows per block
-constexpr int PT_COLS = 1024;       // columns staged per smem tile
+constexpr int PT_COLS = 256;        // columns staged per smem tile (small tiles: enough CTAs to fill 148 SMs)
 
 __global__ void __launch_bounds__(PT_THREADS) k_pretest(const SrcHoist* __restrict__ sh, const TgtHoist* __restrict__ th,
                                                         const CamTable* __restrict__ cams, const int* __restrict__ slot_cam,
@@ -406,51 +406,67 @@ __global__ void k_fill(const CamTable* __restrict__ cams, int n_cams, int n_slot
 constexpr int SC_T = 128;
 constexpr int SC_WARPS = SC_T / 32;
 constexpr int SC_TILE = 2048;      // matches staged per smem tile
-constexpr int SC_QCAP = 96;
+constexpr int SC_QCAP = 128;       // per-warp queue of gate survivors
 
 struct ScoreParams { float sigma_p, sigma_a; };
 
-__device__ __forceinline__ void score_drain(int count, const unsigned* q, int lane, int y0,
-                                            const float2* s_yd, const float2* s_d, const int* s_tgt, int tile0,
-                                            V3 p1, V3 p2, V3 ray1, V3 ray2, V3 C, float spatial_k,
-                                            const float* P, const float4* tgt_segs, float sigma_p, float sigma_a, int* s_max)
+// work items: (source segment, chunk of SC_T matches); order is irrelevant to the result
+__global__ void k_score_items(const int* __restrict__ off, int n_cams, int n_src, int* __restrict__ counter, int2* __restrict__ items)
+{
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n_src) return;
+    const int m = off[(row + 1) * n_cams] - off[row * n_cams];
+    const int n = (m + SC_T - 1) / SC_T;
+    if (n == 0) return;
+    const int base = atomicAdd(counter, n);
+    for (int k = 0; k < n; ++k) items[base + k] = make_int2(row, k);
+}
+
+// exact evaluation of queued (hypothesis y, other match i) pairs: cudawrapper.cu:662-705
+__device__ __forceinline__ void score_drain(int count, const unsigned* q, int lane, const float2* s_yd, int seg_start,
+                                            const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
+                                            V3 ray1, V3 ray2, V3 C, float spatial_k, const CamTable* __restrict__ cams,
+                                            const float4* __restrict__ segs, float sigma_p, float sigma_a, int* s_max)
 {
     if (lane < count) {
         const unsigned e = q[lane];
-        const int yl = int(e >> 16), il = int(e & 0xffffu);
-        const float2 dy = s_yd[yl], di = s_d[il];
-        // cudawrapper.cu:644-645, 671-672
-        V3 P1 = xadd3(C, xscale(dy.x, ray1)), P2 = xadd3(C, xscale(dy.y, ray2));
-        V3 Q1 = xadd3(C, xscale(di.x, ray1)), Q2 = xadd3(C, xscale(di.y, ray2));
-        V3 pr1 = xproject(P, P1), pr2 = xproject(P, P2);
+        const int yl = int(e >> 24), idx = int(e & 0xffffffu);
+        const float2 dy = s_yd[yl];
+        const int4 id = m_ids[seg_start + idx];
+        const float4 di = m_dep[seg_start + idx];
+        const CamTable& ct = cams[id.y];
+        V3 P1 = xadd3(C, xscale(dy.x, ray1)), P2 = xadd3(C, xscale(dy.y, ray2));          // cudawrapper.cu:644-645
+        V3 Q1 = xadd3(C, xscale(di.x, ray1)), Q2 = xadd3(C, xscale(di.y, ray2));          // cudawrapper.cu:671-672
+        V3 pr1 = xproject(ct.P, P1), pr2 = xproject(ct.P, P2);
         if (pr1.z == 1.0f && pr2.z == 1.0f) {
-            float conf = xhypothesis_confidence(pr1, pr2, P1, P2, Q1, Q2, C, tgt_segs[s_tgt[il]], sigma_p, sigma_a, spatial_k);
-            if (conf > 0.5f) atomicMax(&s_max[yl], __float_as_int(conf));
+            float conf = xhypothesis_confidence(pr1, pr2, P1, P2, Q1, Q2, C, segs[ct.seg_off + id.z], sigma_p, sigma_a, spatial_k);
+            if (conf > 0.5f) atomicMax(&s_max[id.y * SC_T + yl], __float_as_int(conf));
         }
     }
-    (void)y0; (void)p1; (void)p2; (void)tile0;
 }
 
 __global__ void __launch_bounds__(SC_T) k_score(const float4* __restrict__ segs, const CamTable* __restrict__ cams, int n_cams, SrcTable src,
                                                 const int* __restrict__ off, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
+                                                const int2* __restrict__ items, const int* __restrict__ n_items,
                                                 ScoreParams sp, float* __restrict__ score)
 {
+    extern __shared__ int s_max[];                 // [n_cams][SC_T] best confidence per (camera, hypothesis), as int bits
     __shared__ float2 s_d[SC_TILE];
-    __shared__ int s_tgt[SC_TILE];
     __shared__ float2 s_yd[SC_T];
-    __shared__ int s_max[SC_T];
     __shared__ unsigned s_q[SC_WARPS][SC_QCAP];
-    const int row = blockIdx.y;
+    if (int(blockIdx.x) >= *n_items) return;
+    const int2 item = items[blockIdx.x];
+    const int row = item.x;
     const int seg_start = off[row * n_cams], seg_end = off[(row + 1) * n_cams];
     const int M = seg_end - seg_start;
-    const int y0 = blockIdx.x * SC_T;
-    if (y0 >= M) return;
+    const int y0 = item.y * SC_T;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int y = y0 + tid;
     const bool live = y < M;
     int my_cam = -1; float2 my_d = make_float2(0.f, 0.f);
     if (live) { my_cam = m_ids[seg_start + y].y; float4 d = m_dep[seg_start + y]; my_d = make_float2(d.x, d.y); }
-    s_yd[tid] = my_d; s_max[tid] = 0;
+    s_yd[tid] = my_d;
+    for (int c = 0; c < n_cams; ++c) s_max[c * SC_T + tid] = 0;
     // per-segment invariants (cudawrapper.cu:638-645)
     const float4 sg = segs[src.seg_off + row];
     const V3 p1 = mk3(sg.x, sg.y, 1.0f), p2 = mk3(sg.z, sg.w, 1.0f);
@@ -462,76 +478,64 @@ __global__ void __launch_bounds__(SC_T) k_score(const float4* __restrict__ segs,
     const float thr2 = (k * fabsf(my_d.y) * 1.00001f + 2e-6f * (2.0f * fabsf(my_d.y) + src.cmax)) * 1.00001f;
     const bool gate_on = k > 0.0f;
     unsigned* q = s_q[warp];
-    float total = 0.0f;
     int qn = 0;
-    for (int cam = 0; cam < n_cams; ++cam) {
-        const int g0 = off[row * n_cams + cam] - seg_start, g1 = off[row * n_cams + cam + 1] - seg_start;
-        if (g1 == g0) continue;
-        const CamTable& ct = cams[cam];
-        const bool mine = live && (cam != my_cam);
-        for (int t0 = g0; t0 < g1; t0 += SC_TILE) {
-            const int tn = min(SC_TILE, g1 - t0);
-            __syncthreads();
-            for (int i = tid; i < tn; i += SC_T) {
-                float4 d = m_dep[seg_start + t0 + i];
-                s_d[i] = make_float2(d.x, d.y);
-                s_tgt[i] = ct.seg_off + m_ids[seg_start + t0 + i].z;
-            }
-            __syncthreads();
-            for (int i0 = 0; i0 < tn; i0 += 32) {
-                // each lane tests up to 32 entries against its own hypothesis
-                unsigned hits = 0;
-                if (mine) {
-                    const int lim = min(32, tn - i0);
-                    if (gate_on) {
+    // this thread skips its own camera's range [skip0, skip1) (cudawrapper.cu:674-675)
+    int skip0 = 0, skip1 = 0;
+    if (live) { skip0 = off[row * n_cams + my_cam] - seg_start; skip1 = off[row * n_cams + my_cam + 1] - seg_start; }
+    for (int t0 = 0; t0 < M; t0 += SC_TILE) {
+        const int tn = min(SC_TILE, M - t0);
+        __syncthreads();
+        for (int i = tid; i < tn; i += SC_T) { float4 d = m_dep[seg_start + t0 + i]; s_d[i] = make_float2(d.x, d.y); }
+        __syncthreads();
+        for (int i0 = 0; i0 < tn; i0 += 32) {
+            unsigned hits = 0;
+            if (live) {
+                const int lim = min(32, tn - i0);
+                if (gate_on) {
+                    unsigned mk = 1u;
 #pragma unroll 8
-                        for (int b = 0; b < 32; ++b) {
-                            const float2 d = s_d[i0 + (b < lim ? b : 0)];
-                            bool pass = (fabsf(my_d.x - d.x) <= thr1) && (fabsf(my_d.y - d.y) <= thr2) && (b < lim);
-                            hits |= pass ? (1u << b) : 0u;
-                        }
-                    } else {
-                        hits = (lim >= 32) ? 0xffffffffu : ((1u << lim) - 1u);
+                    for (int b = 0; b < 32; ++b, mk <<= 1) {
+                        const float2 d = s_d[i0 + b];           // beyond tn: stale but masked below
+                        bool pass = (fabsf(my_d.x - d.x) <= thr1) && (fabsf(my_d.y - d.y) <= thr2);
+                        hits |= pass ? mk : 0u;
                     }
+                    if (lim < 32) hits &= (1u << lim) - 1u;
+                } else {
+                    hits = (lim >= 32) ? 0xffffffffu : ((1u << lim) - 1u);
                 }
-                // enqueue this warp's hits, draining whenever 32 are ready
-                while (__any_sync(0xffffffffu, hits != 0u)) {
-                    int n = __popc(hits), ex = n;
+                // drop the entries of this thread's own camera
+                const int g = t0 + i0;
+                if (g < skip1 && g + 32 > skip0) {
+                    const int lo = max(skip0 - g, 0), hi = min(skip1 - g, 32);
+                    const unsigned m = ((hi >= 32) ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
+                    hits &= ~m;
+                }
+            }
+            while (__any_sync(0xffffffffu, hits != 0u)) {
+                int n = __popc(hits), ex = n;
 #pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) { int v = __shfl_up_sync(0xffffffffu, ex, o); if (lane >= o) ex += v; }
-                    ex -= n;
-                    // take as many as fit
-                    int room = SC_QCAP - qn;
-                    int pos = qn + ex;
-                    int pushed = 0;
-                    while (hits && pos < SC_QCAP) { int b = __ffs(hits) - 1; hits &= hits - 1; q[pos++] = (unsigned(tid) << 16) | unsigned(i0 + b); ++pushed; }
-                    int tot = pushed;
+                for (int o = 1; o < 32; o <<= 1) { int v = __shfl_up_sync(0xffffffffu, ex, o); if (lane >= o) ex += v; }
+                ex -= n;
+                int pos = qn + ex, pushed = 0;
+                while (hits && pos < SC_QCAP) { int b = __ffs(hits) - 1; hits &= hits - 1; q[pos++] = (unsigned(tid) << 24) | unsigned(t0 + i0 + b); ++pushed; }
+                int tot = pushed;
 #pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-                    qn += tot;
-                    (void)room;
+                for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+                qn += tot;
+                __syncwarp();
+                while (qn >= 32) {
+                    score_drain(32, q + (qn - 32), lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, k, cams, segs, sp.sigma_p, sp.sigma_a, s_max);
+                    qn -= 32;
                     __syncwarp();
-                    while (qn >= 32) {
-                        score_drain(32, q + (qn - 32), lane, y0, s_yd, s_d, s_tgt, t0, p1, p2, ray1, ray2, C, k, ct.P, segs, sp.sigma_p, sp.sigma_a, s_max);
-                        qn -= 32;
-                        __syncwarp();
-                    }
                 }
             }
-            // the tile is about to be replaced: finish everything that refers to it
-            if (qn > 0) {
-                score_drain(qn, q, lane, y0, s_yd, s_d, s_tgt, t0, p1, p2, ray1, ray2, C, k, ct.P, segs, sp.sigma_p, sp.sigma_a, s_max);
-                qn = 0;
-            }
-            __syncwarp();
         }
-        // end of this camera group: add its best confidence (cudawrapper.cu:677-687, 709)
-        __syncwarp();
-        int best = s_max[tid];
-        total = xa(total, __int_as_float(best));
-        s_max[tid] = 0;
-        __syncwarp();
     }
+    if (qn > 0) score_drain(qn, q, lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, k, cams, segs, sp.sigma_p, sp.sigma_a, s_max);
+    __syncwarp();
+    // sum of the per-camera best confidences in camera order (cudawrapper.cu:677-687, 709)
+    float total = 0.0f;
+    for (int c = 0; c < n_cams; ++c) total = xa(total, __int_as_float(s_max[c * SC_T + tid]));
     if (live) score[seg_start + y] = total;
 }
 
@@ -575,30 +579,24 @@ __global__ void k_seg_reduce(const int* __restrict__ off, int n_cams, int n_src,
     }
 }
 
-// median of the finite samples: sorted[count / 2], -1 if none (cudawrapper.cu:1066-1076)
-__global__ void __launch_bounds__(1024) k_median(const float* __restrict__ dsamples, int n, int n_pow2, float* __restrict__ out)
+// median of the finite samples: sorted[count / 2], -1 if none (cudawrapper.cu:1066-1076).
+// Selection by ranking: the sample with (#smaller) <= count/2 < (#smaller or equal) is the answer.
+__global__ void k_median_init(float* __restrict__ out) { out[0] = -1.0f; }
+__global__ void k_median(const float* __restrict__ dsamples, int n, float* __restrict__ out)
 {
-    extern __shared__ float s[];
-    __shared__ int s_cnt;
-    if (threadIdx.x == 0) s_cnt = 0;
-    __syncthreads();
-    int c = 0;
-    for (int i = threadIdx.x; i < n_pow2; i += blockDim.x) { float v = (i < n) ? dsamples[i] : INFINITY; s[i] = v; if (v < INFINITY) ++c; }
-    atomicAdd(&s_cnt, c);
-    __syncthreads();
-    for (int k = 2; k <= n_pow2; k <<= 1)
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = threadIdx.x; i < n_pow2; i += blockDim.x) {
-                int l = i ^ j;
-                if (l > i) {
-                    float a = s[i], b = s[l];
-                    bool up = ((i & k) == 0);
-                    if ((a > b) == up) { s[i] = b; s[l] = a; }
-                }
-            }
-            __syncthreads();
-        }
-    if (threadIdx.x == 0) out[0] = s_cnt ? s[s_cnt / 2] : -1.0f;
+    __shared__ float s[1024];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const float v = (i < n) ? dsamples[i] : INFINITY;
+    int less = 0, leq = 0, cnt = 0;
+    for (int t0 = 0; t0 < n; t0 += 1024) {
+        __syncthreads();
+        for (int k = threadIdx.x; k < 1024; k += blockDim.x) s[k] = (t0 + k < n) ? dsamples[t0 + k] : INFINITY;
+        __syncthreads();
+        const int tn = min(1024, n - t0);
+#pragma unroll 8
+        for (int k = 0; k < tn; ++k) { const float u = s[k]; less += (u < v); leq += (u <= v); cnt += (u < INFINITY); }
+    }
+    if (v < INFINITY) { const int r = cnt / 2; if (less <= r && r < leq) out[0] = v; }
 }
 
 // filtered records in order, one warp per segment
@@ -903,6 +901,7 @@ struct l3d_ctx {
     DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
     DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
     DBuf<l3d_match> d_filtered;
+    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024;
     DBuf<int> d_hist, d_hstart, d_cursor;
     HBuf<l3d_match> h_filtered; HBuf<CamTable> h_cams; HBuf<int> h_ints; HBuf<float> h_floats; HBuf<unsigned long long> h_u64;
     // collinearity
@@ -1067,28 +1066,27 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     res->scored = scored ? 1 : 0;
     if (scored && M > 0) {
         // ---- score ------------------------------------------------------------------------
-        int max_m = M;                                // upper bound on matches per segment
         ScoreParams sp; sp.sigma_p = sigma_p; sp.sigma_a = sigma_a;
-        // grid.x covers the longest segment; shorter ones exit at once
         L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_src) + 1)); L3D_CUDA(ctx->d_foff.ensure(size_t(n_src) + 2));
         L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2)); L3D_CUDA(ctx->d_median.ensure(4)); L3D_CUDA(ctx->d_iters.ensure(2));
         L3D_CUDA(cudaMemsetAsync(ctx->d_iters.p, 0, 2 * sizeof(unsigned long long), st));
-        // longest segment: take it from the count matrix on the host side cheaply via the reduce kernel's iteration count later;
-        // here bound it by the number of target segments summed over cameras
-        long bound = 0;
-        for (int c = 0; c < n_nb; ++c) bound += ctx->views[nb[c].view].n_segments;
-        max_m = int(std::min<long>(M, bound));
-        k_score<<<dim3((max_m + SC_T - 1) / SC_T, n_src), SC_T, 0, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p, sp, ctx->d_score.p);
-        ctx->launches += 1;
+        const int max_items = M / SC_T + n_src + 1;
+        L3D_CUDA(ctx->d_items.ensure(size_t(max_items))); L3D_CUDA(ctx->d_nitems.ensure(1));
+        L3D_CUDA(cudaMemsetAsync(ctx->d_nitems.p, 0, sizeof(int), st));
+        k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_nitems.p, ctx->d_items.p);
+        const size_t sm_bytes = size_t(n_nb) * SC_T * sizeof(int);
+        if (sm_bytes > 160 * 1024) { ctx->err = "l3d_match_view: too many neighbours for the scoring kernel's shared memory"; return 1; }
+        if (sm_bytes > ctx->score_smem) { L3D_CUDA(cudaFuncSetAttribute(k_score, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_bytes))); ctx->score_smem = sm_bytes; }
+        k_score<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
+                                                  ctx->d_items.p, ctx->d_nitems.p, sp, ctx->d_score.p);
+        ctx->launches += 2;
         L3D_CUDA(cudaGetLastError());
         L3D_CUDA(cudaEventRecord(ctx->ev[4], st));
         // ---- reduce -----------------------------------------------------------------------
         k_seg_reduce<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, ctx->d_iters.p);
-        int np2 = 2; while (np2 < 2 * n_src) np2 <<= 1;
-        if (np2 * sizeof(float) > 200 * 1024) { ctx->err = "l3d_match_view: too many segments for the median kernel"; return 1; }
-        if (np2 * sizeof(float) > 48 * 1024) L3D_CUDA(cudaFuncSetAttribute(k_median, cudaFuncAttributeMaxDynamicSharedMemorySize, int(np2 * sizeof(float))));
-        k_median<<<1, 1024, np2 * sizeof(float), st>>>(ctx->d_dsamples.p, 2 * n_src, np2, ctx->d_median.p);
-        ctx->launches += 2;
+        k_median_init<<<1, 1, 0, st>>>(ctx->d_median.p);
+        k_median<<<(2 * n_src + 255) / 256, 256, 0, st>>>(ctx->d_dsamples.p, 2 * n_src, ctx->d_median.p);
+        ctx->launches += 3;
         if (scan_exclusive(ctx, ctx->d_fcnt.p, ctx->d_foff.p, n_src)) return 1;
         if (fetch_int(ctx, ctx->d_foff.p + n_src, &F)) return 1;
         L3D_CUDA(ctx->h_floats.ensure(4)); L3D_CUDA(ctx->h_u64.ensure(2));
@@ -1218,7 +1216,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_cand.release(); ctx->d_cand_cnt.release(); ctx->d_cand_off.release(); ctx->d_tile_sums.release(); ctx->d_total.release();
     ctx->d_stage_col.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
-    ctx->d_filtered.release(); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
+    ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_cams.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
     ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release();

@@ -112,7 +112,7 @@ std::string cacheName(const std::string& dir, unsigned id, unsigned w, unsigned 
 
 struct Line3D::Impl
 {
-    bool verbose, computation, use_collinearity, measure_only, flush_l2;
+    bool verbose, computation, use_collinearity, measure_only, flush_l2, keep_debug;
     std::string prefix, separator, data_directory;
     int matching_neighbors; float min_baseline, unc_upper, unc_lower, sigma_p, sigma_a;
     l3d_ctx* ctx;
@@ -427,8 +427,10 @@ struct Line3D::Impl
                 for (uint64_t k = 0; k < res.n_filtered; ++k) {
                     const l3d_match& m = res.filtered[k];
                     const unsigned cam = res.scored ? it->second[m.cam] : unsigned(m.cam);
-                    const double row[9] = {double(vid), double(m.src_seg), double(cam), double(m.tgt_seg), m.depths[0], m.depths[1], m.depths[2], m.depths[3], m.confidence};
-                    filtered_dump.insert(filtered_dump.end(), row, row + 9);
+                    if (keep_debug) {
+                        const double row[9] = {double(vid), double(m.src_seg), double(cam), double(m.tgt_seg), m.depths[0], m.depths[1], m.depths[2], m.depths[3], m.confidence};
+                        filtered_dump.insert(filtered_dump.end(), row, row + 9);
+                    }
                     potential.push_back(std::make_pair(seg_key(vid, m.src_seg), seg_key(cam, m.tgt_seg)));                           // :861-865
                     potential.push_back(std::make_pair(seg_key(cam, m.tgt_seg), seg_key(vid, m.src_seg)));
                     BestMatch& b = bm[m.src_seg];                                                                                   // view.cc:165-183: first maximum
@@ -567,7 +569,7 @@ struct Line3D::Impl
             {   // W as the reference stores it (column-sorted) for the dump
                 std::vector<l3d_edge> w(in);
                 std::stable_sort(w.begin(), w.end(), [](const l3d_edge& a, const l3d_edge& b) { return a.j < b.j || (a.j == b.j && a.i < b.i); });
-                for (size_t k = 0; k < w.size(); ++k) { edges_pre.push_back(w[k].i); edges_pre.push_back(w[k].j); edges_pre.push_back(w[k].w); }
+                if (keep_debug) for (size_t k = 0; k < w.size(); ++k) { edges_pre.push_back(w[k].i); edges_pre.push_back(w[k].j); edges_pre.push_back(w[k].w); }
             }
             if (l3d_diffuse(ctx, n_nodes, in.size(), in.data(), out.data())) fail("l3d_diffuse");
             // symmetrise with min(w_ij, w_ji) in stored order, then (i, j) order (line3D.cc:1267-1299)
@@ -587,7 +589,7 @@ struct Line3D::Impl
         }
         stats.edges = A.size();
         cluster_nodes = n_nodes;
-        for (size_t k = 0; k < A.size(); ++k) { edges_cluster.push_back(A[k].i); edges_cluster.push_back(A[k].j); edges_cluster.push_back(A[k].w); }
+        if (keep_debug) for (size_t k = 0; k < A.size(); ++k) { edges_cluster.push_back(A[k].i); edges_cluster.push_back(A[k].j); edges_cluster.push_back(A[k].w); }
         std::cout << prefix << "graph clustering..." << std::endl;
         const double tc = now_s();
         // Felzenszwalb-Huttenlocher as the reference runs it (clustering.cc:6-47, universe.h:59-115):
@@ -695,7 +697,7 @@ Line3D::Line3D(const std::string data_directory, const int matchingNeighbors, co
     d.verbose = verbose; d.prefix = "[L3D] "; d.separator = "----------------------------------------";
     d.data_directory = data_directory; d.matching_neighbors = matchingNeighbors;
     d.unc_upper = fabs(uncertainty_t_upper_2D); d.unc_lower = fabs(uncertainty_t_lower_2D);              // line3D.cc:18-28
-    d.computation = false; d.use_collinearity = useCollinearity; d.min_baseline = min_baseline; d.measure_only = false; d.flush_l2 = false;
+    d.computation = false; d.use_collinearity = useCollinearity; d.min_baseline = min_baseline; d.measure_only = false; d.flush_l2 = false; d.keep_debug = false;
     if (d.unc_lower < 1.0f) d.unc_lower = 1.0f;
     if (d.unc_upper <= d.unc_lower) d.unc_upper = d.unc_lower + 1.0f;
     d.sigma_a = sigma_a; d.sigma_p = sigma_p;
@@ -792,6 +794,7 @@ unsigned int Line3D::numCameras() { return impl_->views.size(); }
 L3DRunStats Line3D::runStats() const { return impl_->stats; }
 void Line3D::setMeasureOnly(bool on) { impl_->measure_only = on; }
 void Line3D::setFlushL2(bool on) { impl_->flush_l2 = on; }
+void Line3D::setKeepDebug(bool on) { impl_->keep_debug = on; }
 
 float4 Line3D::getSegment2D(L3D::L3DSegment2D& seg2D)                            // line3D.cc:2004-2013, view.cc:275-288
 {

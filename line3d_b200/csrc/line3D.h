@@ -132,6 +132,8 @@ namespace L3D
         void setMeasureOnly(bool on);
         // flush the GPU's L2 before the matching phase of every compute3Dmodel() (measurement only)
         void setFlushL2(bool on);
+        // keep the per-match records debugDump() writes (off by default: they are large)
+        void setKeepDebug(bool on);
 
     private:
         struct Impl;

@@ -37,7 +37,7 @@ def lib():
         L.l3dhost_open.restype = C.c_void_p
         L.l3dhost_open.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
         L.l3dhost_compute.restype = C.c_int
-        L.l3dhost_compute.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.l3dhost_compute.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.l3dhost_dump.restype = C.c_int; L.l3dhost_dump.argtypes = [C.c_void_p, C.c_char_p]
         L.l3dhost_close.restype = None; L.l3dhost_close.argtypes = [C.c_void_p]
         _lib = L
@@ -59,10 +59,10 @@ class Session:
             shutil.rmtree(self._data_dir, ignore_errors=True)
             raise capi.L3DError("l3dhost_open failed (no CUDA device, or unreadable scene)")
 
-    def compute(self, measure_only: bool = False, flush_l2: bool = False, diffusion: bool | None = None):
+    def compute(self, measure_only: bool = False, flush_l2: bool = False, diffusion: bool | None = None, keep_debug: bool = False):
         wall = (C.c_double * 2)(); st = (C.c_double * 30)()
         dif = self.params["diffusion"] if diffusion is None else diffusion
-        n = lib().l3dhost_compute(self._h, int(bool(dif)), int(measure_only), int(flush_l2), wall, st)
+        n = lib().l3dhost_compute(self._h, int(bool(dif)), int(measure_only), int(flush_l2), int(keep_debug), wall, st)
         if n < 0:
             raise capi.L3DError(f"l3dhost_compute failed with code {n}")
         stats = dict(zip(STAT_NAMES, [float(x) for x in st]))
@@ -92,7 +92,7 @@ def run_scene(scene_path: str, dump_dir: str | None = None, verbose: bool = Fals
     """One-shot convenience: returns (n_lines, timings, stats, dumps)."""
     s = Session(scene_path, verbose=verbose, **params)
     try:
-        n, tm, st = s.compute()
+        n, tm, st = s.compute(keep_debug=dump_dir is not None)
         dumps = s.dump() if dump_dir is not None else None
     finally:
         s.close()
