@@ -109,7 +109,16 @@ typedef struct {
 } l3d_match_result;
 int l3d_match_view(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors,
                    float sigma_p, float sigma_a, l3d_match_result* result);
-/* Forget all delivered-but-unconsumed records (a new compute3Dmodel run, line3D.cc:356). */
+/* Optional: announce the whole schedule (the views in the order they will be passed to
+ * l3d_match_view, each with its neighbour array) before the first l3d_match_view call.
+ * Which neighbours get pair-tested is a static function of the neighbour graph and the view
+ * order (line3D.cc:732-736, 875-881), so the pair tests of many views can then run as a few
+ * large launches ahead of the per-view scoring, instead of one small launch per neighbour as
+ * in cudawrapper.cu:900-945.  Results are identical with or without a plan.  A call that
+ * does not follow the announced schedule voids the rest of it. */
+typedef struct { int32_t view; int32_t n_neighbors; const l3d_neighbor* neighbors; } l3d_view_plan;
+int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans);
+/* Forget all delivered-but-unconsumed records and any plan (a new compute3Dmodel run, line3D.cc:356). */
 int l3d_reset_matching(l3d_ctx* ctx);
 
 /* Device-only variant used for measurement: same work, but nothing is copied back except

@@ -90,6 +90,7 @@ struct CamTable {
     int n_seg;
     int mode;           // 0 = pair-test now, 1 = consume delivered records, 2 = nothing
     int slot;           // index among the pair-tested neighbours (mode 0) or -1
+    int row_off;        // mode 0: first global row of this (view, neighbour) job in the phase-A arrays
     int deliver;        // delivery slot (>= 0) or -1
     const int* t_start; // mode 1: delivered records grouped by this view's segment
     const int* t_tgt;
@@ -175,17 +176,40 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_add(int* __restrict__ out, cons
 struct SrcHoist { float4 a; float4 b; };   // a = (A1x, A1y, A1z, w'1)   b = (A2x, A2y, A2z, w'2)
 struct TgtHoist { float4 q; float2 w; float2 pad; };
 
-__global__ void k_hoist(const float4* __restrict__ segs, const CamTable* __restrict__ cams, const int* __restrict__ slot_cam,
-                        SrcTable src, SrcHoist* __restrict__ sh, TgtHoist* __restrict__ th, int max_src, int max_tgt)
+// one pair-tested (source view, neighbour) combination; phase A runs over an array of these
+struct JobDev {
+    float F[9], RtKinv_s[9], RtKinv_t[9], C_s[3], C_t[3];
+    int src_off, n_src, tgt_off, n_tgt;      // segment ranges in the global segment array
+    int sh_off, th_off;                      // first entry in the hoist arrays
+    long long cand_off;                      // first word in the candidate bitmask
+    int wpr;                                 // words per row
+    int row_off;                             // first global row (= source segment of this job) in the per-row arrays
+    int blk_off, col_blocks;                 // pre-test blocks of this job: blk_off + rb * col_blocks + cb
+};
+
+__device__ __forceinline__ int find_job_by_block(const JobDev* __restrict__ jobs, int n_jobs, int blk)
 {
-    const int slot = blockIdx.y;
-    const CamTable& ct = cams[slot_cam[slot]];
+    int lo = 0, hi = n_jobs - 1;
+    while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (jobs[mid].blk_off <= blk) lo = mid; else hi = mid - 1; }
+    return lo;
+}
+__device__ __forceinline__ int find_job_by_row(const JobDev* __restrict__ jobs, int n_jobs, int row)
+{
+    int lo = 0, hi = n_jobs - 1;
+    while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (jobs[mid].row_off <= row) lo = mid; else hi = mid - 1; }
+    return lo;
+}
+
+__global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, SrcHoist* __restrict__ sh, TgtHoist* __restrict__ th)
+{
+    const JobDev& jb = jobs[blockIdx.y];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= jb.n_src && idx >= jb.n_tgt) return;
     double F[9];
 #pragma unroll
-    for (int k = 0; k < 9; ++k) F[k] = double(ct.F[k]);
-    if (idx < src.n_seg) {
-        float4 s = segs[src.seg_off + idx];
+    for (int k = 0; k < 9; ++k) F[k] = double(jb.F[k]);
+    if (idx < jb.n_src) {
+        float4 s = segs[jb.src_off + idx];
         double p[2][2] = {{double(s.x), double(s.y)}, {double(s.z), double(s.w)}};
         float o[2][4];
 #pragma unroll
@@ -196,10 +220,10 @@ __global__ void k_hoist(const float4* __restrict__ segs, const CamTable* __restr
             o[n][0] = float(ax); o[n][1] = float(ay); o[n][2] = float(az); o[n][3] = float(sqrt(ax * ax + ay * ay));
         }
         SrcHoist h; h.a = make_float4(o[0][0], o[0][1], o[0][2], o[0][3]); h.b = make_float4(o[1][0], o[1][1], o[1][2], o[1][3]);
-        sh[size_t(slot) * max_src + idx] = h;
+        sh[jb.sh_off + idx] = h;
     }
-    if (idx < ct.n_seg) {
-        float4 t = segs[ct.seg_off + idx];
+    if (idx < jb.n_tgt) {
+        float4 t = segs[jb.tgt_off + idx];
         double q[2][2] = {{double(t.x), double(t.y)}, {double(t.z), double(t.w)}};
         float w[2];
 #pragma unroll
@@ -209,7 +233,7 @@ __global__ void k_hoist(const float4* __restrict__ segs, const CamTable* __restr
             w[m] = float(sqrt(ex * ex + ey * ey));
         }
         TgtHoist h; h.q = t; h.w = make_float2(w[0], w[1]); h.pad = make_float2(0.f, 0.f);
-        th[size_t(slot) * max_tgt + idx] = h;
+        th[jb.th_off + idx] = h;
     }
 }
 
@@ -245,28 +269,30 @@ constexpr int PT_THREADS = 128;     // rows per block
 constexpr int PT_COLS = 256;        // columns staged per smem tile (small tiles: enough CTAs to fill 148 SMs)
 
 __global__ void __launch_bounds__(PT_THREADS) k_pretest(const SrcHoist* __restrict__ sh, const TgtHoist* __restrict__ th,
-                                                        const CamTable* __restrict__ cams, const int* __restrict__ slot_cam,
-                                                        int n_src, int max_src, int max_tgt, int words_per_row,
-                                                        unsigned* __restrict__ cand, int* __restrict__ cand_cnt, int n_slots)
+                                                        const JobDev* __restrict__ jobs, int n_jobs,
+                                                        unsigned* __restrict__ cand, int* __restrict__ cand_cnt)
 {
     __shared__ float4 s_q[PT_COLS];
     __shared__ float2 s_w[PT_COLS];
-    const int slot = blockIdx.z;
-    const int n_tgt = cams[slot_cam[slot]].n_seg;
-    const int col0 = blockIdx.y * PT_COLS;
-    if (col0 >= n_tgt) return;
-    const int ncol = min(PT_COLS, n_tgt - col0);
+    __shared__ int s_job;
+    if (threadIdx.x == 0) s_job = find_job_by_block(jobs, n_jobs, blockIdx.x);
+    __syncthreads();
+    const JobDev& jb = jobs[s_job];
+    const int local = blockIdx.x - jb.blk_off;
+    const int rb = local / jb.col_blocks, cb = local - rb * jb.col_blocks;
+    const int col0 = cb * PT_COLS;
+    const int ncol = min(PT_COLS, jb.n_tgt - col0);
     for (int k = threadIdx.x; k < PT_COLS; k += PT_THREADS) {
-        if (k < ncol) { TgtHoist h = th[size_t(slot) * max_tgt + col0 + k]; s_q[k] = h.q; s_w[k] = h.w; }
+        if (k < ncol) { TgtHoist h = th[jb.th_off + col0 + k]; s_q[k] = h.q; s_w[k] = h.w; }
         else { s_q[k] = make_float4(0.f, 0.f, 0.f, 0.f); s_w[k] = make_float2(0.f, 0.f); }
     }
     __syncthreads();
-    const int row = blockIdx.x * PT_THREADS + threadIdx.x;
-    if (row >= n_src) return;
-    const SrcHoist h = sh[size_t(slot) * max_src + row];
+    const int row = rb * PT_THREADS + threadIdx.x;
+    if (row >= jb.n_src) return;
+    const SrcHoist h = sh[jb.sh_off + row];
     const float4 A1 = h.a, A2 = h.b;
     int total = 0;
-    unsigned* out = cand + (size_t(slot) * max_src + row) * words_per_row + (col0 >> 5);
+    unsigned* out = cand + jb.cand_off + (long long)row * jb.wpr + (col0 >> 5);
     for (int w = 0; w * 32 < ncol; ++w) {
         unsigned bits = 0, mk = 1u;
 #pragma unroll 8
@@ -290,45 +316,42 @@ __global__ void __launch_bounds__(PT_THREADS) k_pretest(const SrcHoist* __restri
         out[w] = bits;
         total += __popc(bits);
     }
-    if (total) atomicAdd(&cand_cnt[row * n_slots + slot], total);
+    if (total) atomicAdd(&cand_cnt[jb.row_off + row], total);
 }
 
 // ------------------------------------------------------------------------------------------
-// exact test: one warp per (row, slot); candidates are gathered in column order into a
-// per-warp queue and evaluated 32 at a time; survivors (all four depths > 0) are written,
-// still in column order, to the row's staging range.
+// exact test: one warp per global row (job, source segment); candidates are gathered in
+// column order into a per-warp queue and evaluated 32 at a time; survivors (all four
+// depths > 0) are written, still in column order, to the row's staging range.
 // ------------------------------------------------------------------------------------------
 constexpr int EX_WARPS = 8;
 constexpr int EX_QCAP = 1088;
 
-__global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restrict__ segs, const CamTable* __restrict__ cams,
-                                                         const int* __restrict__ slot_cam, SrcTable src,
+__global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, int n_jobs, int n_rows,
                                                          const unsigned* __restrict__ cand, const int* __restrict__ cand_off,
-                                                         int max_src, int words_per_row, int n_slots, int n_cams,
-                                                         int* __restrict__ stage_col, float4* __restrict__ stage_dep, int* __restrict__ cnt)
+                                                         int* __restrict__ stage_col, float4* __restrict__ stage_dep, int* __restrict__ raw_cnt)
 {
     __shared__ unsigned short s_queue[EX_WARPS][EX_QCAP];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int row = blockIdx.x * EX_WARPS + warp;
-    const int slot = blockIdx.y;
-    if (row >= src.n_seg) return;
-    const int cam = slot_cam[slot];
-    const CamTable& ct = cams[cam];
-    const int n_cand = cand_off[row * n_slots + slot + 1] - cand_off[row * n_slots + slot];
-    if (n_cand == 0) { if (lane == 0) cnt[row * n_cams + cam] = 0; return; }
-    const int base = cand_off[row * n_slots + slot];
-    const unsigned* words = cand + (size_t(slot) * max_src + row) * words_per_row;
-    const int n_words = (ct.n_seg + 31) >> 5;
+    const int grow = blockIdx.x * EX_WARPS + warp;
+    if (grow >= n_rows) return;
+    const int base = cand_off[grow];
+    const int n_cand = cand_off[grow + 1] - base;
+    if (n_cand == 0) { if (lane == 0) raw_cnt[grow] = 0; return; }
+    const JobDev& jb = jobs[find_job_by_row(jobs, n_jobs, grow)];
+    const int row = grow - jb.row_off;
+    const unsigned* words = cand + jb.cand_off + (long long)row * jb.wpr;
+    const int n_words = (jb.n_tgt + 31) >> 5;
     unsigned short* q = s_queue[warp];
-    const float4 s = segs[src.seg_off + row];
-    const V3 Cs = mk3(src.C[0], src.C[1], src.C[2]), Ct = mk3(ct.C[0], ct.C[1], ct.C[2]);
+    const float4 s = segs[jb.src_off + row];
+    const V3 Cs = mk3(jb.C_s[0], jb.C_s[1], jb.C_s[2]), Ct = mk3(jb.C_t[0], jb.C_t[1], jb.C_t[2]);
     int qn = 0, accepted = 0;
     auto evaluate = [&](int first, int count) {
         // lanes [0, count) take queue entries first .. first + count - 1 (column order)
         bool ok = false; float4 dep = make_float4(0.f, 0.f, 0.f, 0.f); int col = 0;
         if (lane < count) {
             col = q[first + lane];
-            ok = xpair_test(s, segs[ct.seg_off + col], ct.F, src.RtKinv, ct.RtKinv, Cs, Ct, dep);
+            ok = xpair_test(s, segs[jb.tgt_off + col], jb.F, jb.RtKinv_s, jb.RtKinv_t, Cs, Ct, dep);
         }
         unsigned m = __ballot_sync(0xffffffffu, ok);
         if (ok) {
@@ -359,22 +382,31 @@ __global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restric
         }
     }
     if (qn > 0) evaluate(0, qn);
-    if (lane == 0) cnt[row * n_cams + cam] = accepted;
+    if (lane == 0) raw_cnt[grow] = accepted;
+}
+
+// dst[k] = src[idx[k]]
+__global__ void k_gather_int(const int* __restrict__ src, const int* __restrict__ idx, int n, int* __restrict__ dst)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) dst[k] = src[idx[k]];
 }
 
 // counts of the delivered records per (row, cam) for the cams in mode 1
-__global__ void k_delivered_counts(const CamTable* __restrict__ cams, int n_cams, int n_src, int* __restrict__ cnt)
+__global__ void k_gather_counts(const CamTable* __restrict__ cams, int n_cams, int n_src, const int* __restrict__ raw_cnt, int* __restrict__ cnt)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     const int cam = blockIdx.y;
     if (row >= n_src) return;
     const CamTable& ct = cams[cam];
-    if (ct.mode == 1) cnt[row * n_cams + cam] = ct.t_start ? (ct.t_start[row + 1] - ct.t_start[row]) : 0;
-    else if (ct.mode == 2) cnt[row * n_cams + cam] = 0;
+    int c = 0;
+    if (ct.mode == 0) c = raw_cnt[ct.row_off + row];
+    else if (ct.mode == 1) c = ct.t_start ? (ct.t_start[row + 1] - ct.t_start[row]) : 0;
+    cnt[row * n_cams + cam] = c;
 }
 
 // fill: one warp per (row, cam) copies the row's records to their final place
-__global__ void k_fill(const CamTable* __restrict__ cams, int n_cams, int n_slots, int n_src,
+__global__ void k_fill(const CamTable* __restrict__ cams, int n_cams, int n_src,
                        const int* __restrict__ off, const int* __restrict__ cand_off,
                        const int* __restrict__ stage_col, const float4* __restrict__ stage_dep,
                        int4* __restrict__ m_ids, float4* __restrict__ m_dep)
@@ -386,7 +418,7 @@ __global__ void k_fill(const CamTable* __restrict__ cams, int n_cams, int n_slot
     if (n == 0) return;
     const CamTable& ct = cams[cam];
     if (ct.mode == 0) {
-        const int b = cand_off[row * n_slots + ct.slot];
+        const int b = cand_off[ct.row_off + row];
         for (int k = lane; k < n; k += 32) { m_ids[o + k] = make_int4(row, cam, stage_col[b + k], 0); m_dep[o + k] = stage_dep[b + k]; }
     } else if (ct.mode == 1) {
         const int b = ct.t_start[row];
@@ -625,10 +657,10 @@ __global__ void k_filter_fill(const int* __restrict__ off, int n_cams, int n_src
     }
 }
 // unscored variant (no neighbour to pair-test): all records, confidence 0
-__global__ void k_copy_unscored(const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, int M, l3d_match* __restrict__ out)
+__global__ void k_copy_unscored(const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, const int* __restrict__ Mptr, l3d_match* __restrict__ out)
 {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= M) return;
+    if (k >= *Mptr) return;
     int4 id = m_ids[k]; float4 d = m_dep[k];
     l3d_match rec; rec.src_seg = id.x; rec.cam = id.y; rec.tgt_seg = id.z; rec.confidence = 0.0f;
     rec.depths[0] = d.x; rec.depths[1] = d.y; rec.depths[2] = d.z; rec.depths[3] = d.w;
@@ -639,18 +671,18 @@ __global__ void k_copy_unscored(const int4* __restrict__ m_ids, const float4* __
 // hand-over (line3D.cc:838-858): the filtered records towards each neighbour that asked for
 // delivery, reversed and regrouped by the neighbour's segment, target ids ascending
 // ------------------------------------------------------------------------------------------
-__global__ void k_deliver_hist(const l3d_match* __restrict__ f, int F, const CamTable* __restrict__ cams, int stride, int* __restrict__ hist)
+__global__ void k_deliver_hist(const l3d_match* __restrict__ f, const int* __restrict__ Fptr, const CamTable* __restrict__ cams, int stride, int* __restrict__ hist)
 {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= F) return;
+    if (k >= *Fptr) return;
     const int d = cams[f[k].cam].deliver;
     if (d >= 0) atomicAdd(&hist[d * stride + f[k].tgt_seg], 1);
 }
-__global__ void k_deliver_scatter(const l3d_match* __restrict__ f, int F, const CamTable* __restrict__ cams, int stride,
+__global__ void k_deliver_scatter(const l3d_match* __restrict__ f, const int* __restrict__ Fptr, const CamTable* __restrict__ cams, int stride,
                                   const int* __restrict__ start, int* __restrict__ cursor, int* __restrict__ t_tgt, float4* __restrict__ t_dep)
 {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= F) return;
+    if (k >= *Fptr) return;
     const l3d_match m = f[k];
     const int d = cams[m.cam].deliver;
     if (d < 0) return;
@@ -878,6 +910,15 @@ struct Delivered {            // records a source view handed to a later view
 };
 struct DeliverBuf { int* start = nullptr; int* tgt = nullptr; float4* dep = nullptr; int refs = 0; };
 
+struct PlannedView {           // one entry of l3d_plan_matching
+    int view = -1;
+    std::vector<l3d_neighbor> nb;
+    uint64_t pair_tests = 0;
+    int first_job = -1;         // valid while the view's batch is resident
+    uint64_t n_candidates = 0;
+};
+struct JobHost { int src_view, tgt_view; float F[9]; };
+
 struct l3d_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -902,6 +943,14 @@ struct l3d_ctx {
     DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
     DBuf<l3d_match> d_filtered;
     DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024;
+    // phase A (pair tests) of the resident batch
+    DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
+    std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands;
+    std::vector<PlannedView> plan; size_t plan_next = 0; size_t batch_begin = 0, batch_end = 0;
+    float pa_ms[2] = {0.f, 0.f}; bool pa_ms_pending = false;
+    uint64_t pair_budget = 24000000000ull;
+    cudaEvent_t pa_ev[3] = {nullptr, nullptr, nullptr};
+    DBuf<int> d_res; HBuf<int> h_res;
     DBuf<int> d_hist, d_hstart, d_cursor;
     HBuf<l3d_match> h_filtered; HBuf<CamTable> h_cams; HBuf<int> h_ints; HBuf<float> h_floats; HBuf<unsigned long long> h_u64;
     // collinearity
@@ -952,6 +1001,80 @@ void release_delivered(l3d_ctx* ctx, Delivered& d)
     d = Delivered();
 }
 
+// Phase A for a set of (source view, neighbour) jobs: hoist, pre-test, scan, exact test.
+// Results stay on the device: d_pa_off (candidate offsets per global row = staging ranges),
+// d_pa_raw (raw matches per global row), d_stage_col / d_stage_dep.
+int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
+{
+    cudaStream_t st = ctx->stream;
+    const int n_jobs = int(jh.size());
+    ctx->jobs_host.assign(size_t(n_jobs), JobDev());
+    ctx->job_cands.assign(size_t(n_jobs), 0);
+    if (n_jobs == 0) return 0;
+    long long sh_tot = 0, th_tot = 0, words = 0, rows = 0, blocks = 0;
+    int max_n = 1;
+    for (int j = 0; j < n_jobs; ++j) {
+        const l3d_view& sv = ctx->views[jh[j].src_view]; const l3d_view& tv = ctx->views[jh[j].tgt_view];
+        JobDev& d = ctx->jobs_host[j];
+        memcpy(d.F, jh[j].F, sizeof d.F); memcpy(d.RtKinv_s, sv.RtKinv, sizeof d.RtKinv_s); memcpy(d.RtKinv_t, tv.RtKinv, sizeof d.RtKinv_t);
+        memcpy(d.C_s, sv.C, sizeof d.C_s); memcpy(d.C_t, tv.C, sizeof d.C_t);
+        d.src_off = ctx->seg_off[jh[j].src_view]; d.n_src = sv.n_segments; d.tgt_off = ctx->seg_off[jh[j].tgt_view]; d.n_tgt = tv.n_segments;
+        d.sh_off = int(sh_tot); d.th_off = int(th_tot); d.cand_off = words; d.wpr = (d.n_tgt + 31) / 32;
+        d.row_off = int(rows); d.blk_off = int(blocks); d.col_blocks = std::max((d.n_tgt + PT_COLS - 1) / PT_COLS, 1);
+        sh_tot += d.n_src; th_tot += d.n_tgt; words += (long long)d.n_src * d.wpr; rows += d.n_src;
+        blocks += (long long)((d.n_src + PT_THREADS - 1) / PT_THREADS) * d.col_blocks;
+        max_n = std::max(max_n, std::max(d.n_src, d.n_tgt));
+        if (sh_tot > 0x7fffffff || th_tot > 0x7fffffff || rows > 0x7ffffff0 || blocks > 0x7ffffff0) { ctx->err = "phase A: batch too large"; return 1; }
+    }
+    L3D_CUDA(ctx->d_jobs.ensure(size_t(n_jobs)));
+    L3D_CUDA(cudaMemcpyAsync(ctx->d_jobs.p, ctx->jobs_host.data(), sizeof(JobDev) * size_t(n_jobs), cudaMemcpyHostToDevice, st));
+    L3D_CUDA(ctx->d_sh.ensure(size_t(std::max<long long>(sh_tot, 1)))); L3D_CUDA(ctx->d_th.ensure(size_t(std::max<long long>(th_tot, 1))));
+    L3D_CUDA(ctx->d_cand.ensure(size_t(std::max<long long>(words, 1))));
+    L3D_CUDA(ctx->d_pa_cnt.ensure(size_t(rows) + 1)); L3D_CUDA(ctx->d_pa_off.ensure(size_t(rows) + 2)); L3D_CUDA(ctx->d_pa_raw.ensure(size_t(rows) + 1));
+    L3D_CUDA(cudaMemsetAsync(ctx->d_pa_cnt.p, 0, sizeof(int) * (size_t(rows) + 1), st));
+    L3D_CUDA(cudaEventRecord(ctx->pa_ev[0], st));
+    if (rows > 0 && blocks > 0) {
+        k_hoist<<<dim3((max_n + 127) / 128, n_jobs), 128, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, ctx->d_sh.p, ctx->d_th.p);
+        k_pretest<<<unsigned(blocks), PT_THREADS, 0, st>>>(ctx->d_sh.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_cand.p, ctx->d_pa_cnt.p);
+        ctx->launches += 2;
+        L3D_CUDA(cudaGetLastError());
+    }
+    if (scan_exclusive(ctx, ctx->d_pa_cnt.p, ctx->d_pa_off.p, int(rows))) return 1;
+    L3D_CUDA(cudaEventRecord(ctx->pa_ev[1], st));
+    // candidate totals per job (and overall) come back in one small copy
+    L3D_CUDA(ctx->d_pa_idx.ensure(size_t(n_jobs) + 1)); L3D_CUDA(ctx->d_pa_tot.ensure(size_t(n_jobs) + 1)); L3D_CUDA(ctx->h_res.ensure(size_t(n_jobs) + 64));
+    {
+        std::vector<int> idx(size_t(n_jobs) + 1);
+        for (int j = 0; j < n_jobs; ++j) idx[j] = ctx->jobs_host[j].row_off;
+        idx[n_jobs] = int(rows);
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_pa_idx.p, idx.data(), sizeof(int) * idx.size(), cudaMemcpyHostToDevice, st));
+        k_gather_int<<<(n_jobs + 256) / 256, 256, 0, st>>>(ctx->d_pa_off.p, ctx->d_pa_idx.p, n_jobs + 1, ctx->d_pa_tot.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p, ctx->d_pa_tot.p, sizeof(int) * (size_t(n_jobs) + 1), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaStreamSynchronize(st));        // idx is a stack vector: must be consumed before it goes away
+    }
+    for (int j = 0; j < n_jobs; ++j) ctx->job_cands[j] = uint64_t(ctx->h_res.p[j + 1] - ctx->h_res.p[j]);
+    const int n_cand = ctx->h_res.p[n_jobs];
+    L3D_CUDA(ctx->d_stage_col.ensure(size_t(std::max(n_cand, 1)))); L3D_CUDA(ctx->d_stage_dep.ensure(size_t(std::max(n_cand, 1))));
+    if (rows > 0) {
+        k_exact<<<unsigned((rows + EX_WARPS - 1) / EX_WARPS), EX_WARPS * 32, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, n_jobs, int(rows), ctx->d_cand.p, ctx->d_pa_off.p,
+                                                                                  ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_pa_raw.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+    }
+    L3D_CUDA(cudaEventRecord(ctx->pa_ev[2], st));
+    ctx->pa_ms_pending = true;
+    return 0;
+}
+
+bool same_neighbors(const std::vector<l3d_neighbor>& a, int n, const l3d_neighbor* b)
+{
+    if (int(a.size()) != n) return false;
+    for (int c = 0; c < n; ++c)
+        if (a[c].view != b[c].view || (a[c].to_be_matched != 0) != (b[c].to_be_matched != 0) || memcmp(a[c].F, b[c].F, sizeof a[c].F) != 0) return false;
+    return true;
+}
+
 int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float sigma_p, float sigma_a, l3d_match_result* res, bool copy_back)
 {
     if (!ctx) return 1;
@@ -962,27 +1085,58 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     cudaStream_t st = ctx->stream;
     const l3d_view& sv = ctx->views[view];
     const int n_src = sv.n_segments;
+    for (int c = 0; c < n_nb; ++c) {
+        if (nb[c].view < 0 || nb[c].view >= ctx->V || nb[c].view == view) { ctx->err = "l3d_match_view: bad neighbour view index"; return 1; }
+        if (c > 0 && nb[c - 1].view >= nb[c].view) { ctx->err = "l3d_match_view: neighbours must be in ascending view order"; return 1; }
+    }
+
+    // ---- phase A: from the announced schedule (batched), or for this view alone ---------------
+    int first_job = 0;
+    bool planned = false;
+    if (ctx->plan_next < ctx->plan.size() && ctx->plan[ctx->plan_next].view == view && same_neighbors(ctx->plan[ctx->plan_next].nb, n_nb, nb)) {
+        planned = true;
+        if (ctx->plan_next >= ctx->batch_end) {                 // start the next batch here
+            std::vector<JobHost> jh;
+            size_t e = ctx->plan_next; uint64_t pairs = 0;
+            while (e < ctx->plan.size() && (e == ctx->plan_next || pairs + ctx->plan[e].pair_tests <= ctx->pair_budget)) {
+                PlannedView& pv = ctx->plan[e];
+                pv.first_job = int(jh.size());
+                for (size_t c = 0; c < pv.nb.size(); ++c)
+                    if (pv.nb[c].to_be_matched) { JobHost j; j.src_view = pv.view; j.tgt_view = pv.nb[c].view; memcpy(j.F, pv.nb[c].F, sizeof j.F); jh.push_back(j); }
+                pairs += pv.pair_tests; ++e;
+            }
+            if (run_phase_a(ctx, jh)) return 1;
+            ctx->batch_begin = ctx->plan_next; ctx->batch_end = e;
+        }
+        first_job = ctx->plan[ctx->plan_next].first_job;
+        ++ctx->plan_next;
+    } else {
+        ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;      // a call off the schedule voids it
+        std::vector<JobHost> jh;
+        for (int c = 0; c < n_nb; ++c)
+            if (nb[c].to_be_matched) { JobHost j; j.src_view = view; j.tgt_view = nb[c].view; memcpy(j.F, nb[c].F, sizeof j.F); jh.push_back(j); }
+        if (run_phase_a(ctx, jh)) return 1;
+    }
+    (void)planned;
 
     // ---- tables -------------------------------------------------------------------------
     L3D_CUDA(ctx->h_cams.ensure(size_t(n_nb)));
     L3D_CUDA(ctx->h_ints.ensure(size_t(n_nb) + 64));
-    int n_slots = 0, n_deliver = 0, max_tgt = 1, max_deliver_seg = 1;
-    uint64_t pair_tests = 0;
-    std::vector<int> slot_cam;
+    int n_slots = 0, n_deliver = 0, max_deliver_seg = 1;
+    uint64_t pair_tests = 0, cand_ub = 0;
     std::vector<int> consumed;                       // indices into ctx->delivered[view]
     for (int c = 0; c < n_nb; ++c) {
         const l3d_neighbor& n = nb[c];
-        if (n.view < 0 || n.view >= ctx->V || n.view == view) { ctx->err = "l3d_match_view: bad neighbour view index"; return 1; }
-        if (c > 0 && nb[c - 1].view >= n.view) { ctx->err = "l3d_match_view: neighbours must be in ascending view order"; return 1; }
         const l3d_view& tv = ctx->views[n.view];
         CamTable& ct = ctx->h_cams.p[c];
         memcpy(ct.F, n.F, sizeof ct.F); memcpy(ct.RtKinv, tv.RtKinv, sizeof ct.RtKinv);
         memcpy(ct.P, tv.P, sizeof ct.P); memcpy(ct.C, tv.C, sizeof ct.C);
         ct.seg_off = ctx->seg_off[n.view]; ct.n_seg = tv.n_segments;
-        ct.t_start = nullptr; ct.t_tgt = nullptr; ct.t_dep = nullptr; ct.slot = -1; ct.deliver = -1;
+        ct.t_start = nullptr; ct.t_tgt = nullptr; ct.t_dep = nullptr; ct.slot = -1; ct.deliver = -1; ct.row_off = 0;
         if (n.to_be_matched) {
-            ct.mode = 0; ct.slot = n_slots++; slot_cam.push_back(c);
-            max_tgt = std::max(max_tgt, tv.n_segments);
+            const int j = first_job + n_slots;
+            ct.mode = 0; ct.slot = n_slots++; ct.row_off = ctx->jobs_host[j].row_off;
+            cand_ub += ctx->job_cands[j];
             pair_tests += uint64_t(n_src) * uint64_t(tv.n_segments);
         } else {
             ct.mode = 2;
@@ -993,84 +1147,51 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         if (n.deliver) { ct.deliver = n_deliver++; max_deliver_seg = std::max(max_deliver_seg, tv.n_segments); }
     }
     res->pair_tests = pair_tests;
+    res->n_candidates = cand_ub;
     SrcTable src;
     memcpy(src.RtKinv, sv.RtKinv, sizeof src.RtKinv); memcpy(src.C, sv.C, sizeof src.C);
     src.spatial_k = sv.spatial_k; src.cmax = std::max(std::fabs(sv.C[0]), std::max(std::fabs(sv.C[1]), std::fabs(sv.C[2])));
     src.seg_off = ctx->seg_off[view]; src.n_seg = n_src;
+    const size_t M_ub = size_t(cand_ub + res->n_delivered);          // upper bound on the number of matches to score
 
     L3D_CUDA(ctx->d_cams.ensure(size_t(n_nb)));
     L3D_CUDA(cudaMemcpyAsync(ctx->d_cams.p, ctx->h_cams.p, sizeof(CamTable) * n_nb, cudaMemcpyHostToDevice, st));
     L3D_CUDA(ctx->d_cnt.ensure(size_t(n_src) * n_nb + 1));
     L3D_CUDA(ctx->d_off.ensure(size_t(n_src) * n_nb + 2));
-    L3D_CUDA(cudaEventRecord(ctx->ev[0], st));
-
-    // ---- pair tests -----------------------------------------------------------------------
-    int n_cand = 0;
-    if (n_slots > 0 && n_src > 0) {
-        for (int s = 0; s < n_slots; ++s) ctx->h_ints.p[s] = slot_cam[s];
-        L3D_CUDA(ctx->d_slot_cam.ensure(size_t(n_slots)));
-        L3D_CUDA(cudaMemcpyAsync(ctx->d_slot_cam.p, ctx->h_ints.p, sizeof(int) * n_slots, cudaMemcpyHostToDevice, st));
-        const int wpr = (max_tgt + 31) / 32;
-        L3D_CUDA(ctx->d_sh.ensure(size_t(n_slots) * n_src));
-        L3D_CUDA(ctx->d_th.ensure(size_t(n_slots) * max_tgt));
-        L3D_CUDA(ctx->d_cand.ensure(size_t(n_slots) * n_src * wpr));
-        L3D_CUDA(ctx->d_cand_cnt.ensure(size_t(n_src) * n_slots + 1));
-        L3D_CUDA(ctx->d_cand_off.ensure(size_t(n_src) * n_slots + 2));
-        L3D_CUDA(cudaMemsetAsync(ctx->d_cand_cnt.p, 0, sizeof(int) * (size_t(n_src) * n_slots + 1), st));
-        L3D_CUDA(cudaMemsetAsync(ctx->d_cand.p, 0, sizeof(unsigned) * size_t(n_slots) * n_src * wpr, st));
-        const int hn = std::max(n_src, max_tgt);
-        k_hoist<<<dim3((hn + 127) / 128, n_slots), 128, 0, st>>>(ctx->d_segs.p, ctx->d_cams.p, ctx->d_slot_cam.p, src, ctx->d_sh.p, ctx->d_th.p, n_src, max_tgt);
-        k_pretest<<<dim3((n_src + PT_THREADS - 1) / PT_THREADS, (max_tgt + PT_COLS - 1) / PT_COLS, n_slots), PT_THREADS, 0, st>>>(
-            ctx->d_sh.p, ctx->d_th.p, ctx->d_cams.p, ctx->d_slot_cam.p, n_src, n_src, max_tgt, wpr, ctx->d_cand.p, ctx->d_cand_cnt.p, n_slots);
-        ctx->launches += 2;
-        L3D_CUDA(cudaGetLastError());
-        if (scan_exclusive(ctx, ctx->d_cand_cnt.p, ctx->d_cand_off.p, n_src * n_slots)) return 1;
-        L3D_CUDA(cudaEventRecord(ctx->ev[1], st));
-        if (fetch_int(ctx, ctx->d_cand_off.p + size_t(n_src) * n_slots, &n_cand)) return 1;
-        L3D_CUDA(ctx->d_stage_col.ensure(size_t(std::max(n_cand, 1))));
-        L3D_CUDA(ctx->d_stage_dep.ensure(size_t(std::max(n_cand, 1))));
-        k_exact<<<dim3((n_src + EX_WARPS - 1) / EX_WARPS, n_slots), EX_WARPS * 32, 0, st>>>(
-            ctx->d_segs.p, ctx->d_cams.p, ctx->d_slot_cam.p, src, ctx->d_cand.p, ctx->d_cand_off.p, n_src, wpr, n_slots, n_nb,
-            ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_cnt.p);
-        ctx->launches += 1;
-        L3D_CUDA(cudaGetLastError());
-    } else {
-        L3D_CUDA(cudaEventRecord(ctx->ev[1], st));
-    }
-    res->n_candidates = uint64_t(n_cand);
+    L3D_CUDA(ctx->d_res.ensure(8)); L3D_CUDA(ctx->h_res.ensure(64));
     L3D_CUDA(cudaEventRecord(ctx->ev[2], st));
 
     // ---- assemble the match list ----------------------------------------------------------
-    int M = 0;
+    const int* d_M = ctx->d_off.p + size_t(n_src) * n_nb;             // total number of matches, on the device
     if (n_src > 0) {
-        k_delivered_counts<<<dim3((n_src + 255) / 256, n_nb), 256, 0, st>>>(ctx->d_cams.p, n_nb, n_src, ctx->d_cnt.p);
+        k_gather_counts<<<dim3((n_src + 255) / 256, n_nb), 256, 0, st>>>(ctx->d_cams.p, n_nb, n_src, ctx->d_pa_raw.p, ctx->d_cnt.p);
         ctx->launches += 1;
         if (scan_exclusive(ctx, ctx->d_cnt.p, ctx->d_off.p, n_src * n_nb)) return 1;
-        if (fetch_int(ctx, ctx->d_off.p + size_t(n_src) * n_nb, &M)) return 1;
+    } else {
+        L3D_CUDA(cudaMemsetAsync(ctx->d_off.p, 0, sizeof(int) * 2, st));
     }
-    res->n_scored = uint64_t(M);
-    res->n_raw = uint64_t(M) - res->n_delivered;
-    if (M > 0) {
-        L3D_CUDA(ctx->d_mids.ensure(size_t(M))); L3D_CUDA(ctx->d_mdep.ensure(size_t(M))); L3D_CUDA(ctx->d_score.ensure(size_t(M)));
+    if (M_ub > 0) {
+        L3D_CUDA(ctx->d_mids.ensure(M_ub)); L3D_CUDA(ctx->d_mdep.ensure(M_ub)); L3D_CUDA(ctx->d_score.ensure(M_ub));
         const long warps = long(n_src) * n_nb;
-        k_fill<<<unsigned((warps * 32 + 255) / 256), 256, 0, st>>>(ctx->d_cams.p, n_nb, std::max(n_slots, 1), n_src, ctx->d_off.p, ctx->d_cand_off.p,
+        k_fill<<<unsigned((warps * 32 + 255) / 256), 256, 0, st>>>(ctx->d_cams.p, n_nb, n_src, ctx->d_off.p, ctx->d_pa_off.p,
                                                                   ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_mids.p, ctx->d_mdep.p);
         ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
     }
     L3D_CUDA(cudaEventRecord(ctx->ev[3], st));
 
-    int F = 0;
-    float median = 1.0f;                              // line3D.cc:811
     const bool scored = n_slots > 0;                  // cudawrapper.cu:877-878
     res->scored = scored ? 1 : 0;
-    if (scored && M > 0) {
+    const int* d_F = nullptr;                         // number of output records, on the device
+    L3D_CUDA(ctx->d_filtered.ensure(std::max<size_t>(M_ub, 1)));
+    L3D_CUDA(ctx->d_median.ensure(4)); L3D_CUDA(ctx->d_iters.ensure(2));
+    if (scored && M_ub > 0) {
         // ---- score ------------------------------------------------------------------------
         ScoreParams sp; sp.sigma_p = sigma_p; sp.sigma_a = sigma_a;
         L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_src) + 1)); L3D_CUDA(ctx->d_foff.ensure(size_t(n_src) + 2));
-        L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2)); L3D_CUDA(ctx->d_median.ensure(4)); L3D_CUDA(ctx->d_iters.ensure(2));
+        L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2));
         L3D_CUDA(cudaMemsetAsync(ctx->d_iters.p, 0, 2 * sizeof(unsigned long long), st));
-        const int max_items = M / SC_T + n_src + 1;
+        const int max_items = int(M_ub / SC_T) + n_src + 1;
         L3D_CUDA(ctx->d_items.ensure(size_t(max_items))); L3D_CUDA(ctx->d_nitems.ensure(1));
         L3D_CUDA(cudaMemsetAsync(ctx->d_nitems.p, 0, sizeof(int), st));
         k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_nitems.p, ctx->d_items.p);
@@ -1088,74 +1209,85 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         k_median<<<(2 * n_src + 255) / 256, 256, 0, st>>>(ctx->d_dsamples.p, 2 * n_src, ctx->d_median.p);
         ctx->launches += 3;
         if (scan_exclusive(ctx, ctx->d_fcnt.p, ctx->d_foff.p, n_src)) return 1;
-        if (fetch_int(ctx, ctx->d_foff.p + n_src, &F)) return 1;
-        L3D_CUDA(ctx->h_floats.ensure(4)); L3D_CUDA(ctx->h_u64.ensure(2));
-        L3D_CUDA(cudaMemcpyAsync(ctx->h_floats.p, ctx->d_median.p, sizeof(float), cudaMemcpyDeviceToHost, st));
-        L3D_CUDA(cudaMemcpyAsync(ctx->h_u64.p, ctx->d_iters.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-        L3D_CUDA(ctx->d_filtered.ensure(size_t(std::max(F, 1))));
-        if (F > 0) {
-            k_filter_fill<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, ctx->d_filtered.p);
-            ctx->launches += 1;
-        }
+        d_F = ctx->d_foff.p + n_src;
+        k_filter_fill<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, ctx->d_filtered.p);
+        ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
     } else {
         L3D_CUDA(cudaEventRecord(ctx->ev[4], st));
-        if (!scored && M > 0) {
-            F = M;
-            L3D_CUDA(ctx->d_filtered.ensure(size_t(F)));
-            k_copy_unscored<<<(M + 255) / 256, 256, 0, st>>>(ctx->d_mids.p, ctx->d_mdep.p, M, ctx->d_filtered.p);
+        d_F = d_M;
+        if (!scored && M_ub > 0) {
+            k_copy_unscored<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_mids.p, ctx->d_mdep.p, d_M, ctx->d_filtered.p);
             ctx->launches += 1;
             L3D_CUDA(cudaGetLastError());
         }
     }
 
     // ---- hand-over to later views ---------------------------------------------------------
-    if (n_deliver > 0 && scored) {
-        const int stride = max_deliver_seg + 1;                    // one spare key per slot keeps t_start[n_seg] addressable
+    DeliverBuf buf; int stride = 0;
+    const bool delivering = n_deliver > 0 && scored;
+    if (delivering) {
+        stride = max_deliver_seg + 1;                               // one spare key per slot keeps t_start[n_seg] addressable
         const int n_keys = n_deliver * stride;
-        DeliverBuf buf; buf.refs = n_deliver;
+        buf.refs = n_deliver;
         L3D_CUDA(cudaMallocAsync(&buf.start, sizeof(int) * (size_t(n_keys) + 2), st));
-        L3D_CUDA(cudaMallocAsync(&buf.tgt, sizeof(int) * size_t(std::max(F, 1)), st));
-        L3D_CUDA(cudaMallocAsync(&buf.dep, sizeof(float4) * size_t(std::max(F, 1)), st));
+        L3D_CUDA(cudaMallocAsync(&buf.tgt, sizeof(int) * std::max<size_t>(M_ub, 1), st));
+        L3D_CUDA(cudaMallocAsync(&buf.dep, sizeof(float4) * std::max<size_t>(M_ub, 1), st));
         L3D_CUDA(ctx->d_hist.ensure(size_t(n_keys) + 1)); L3D_CUDA(ctx->d_cursor.ensure(size_t(n_keys) + 1));
         L3D_CUDA(cudaMemsetAsync(ctx->d_hist.p, 0, sizeof(int) * (size_t(n_keys) + 1), st));
         L3D_CUDA(cudaMemsetAsync(ctx->d_cursor.p, 0, sizeof(int) * (size_t(n_keys) + 1), st));
-        if (F > 0) { k_deliver_hist<<<(F + 255) / 256, 256, 0, st>>>(ctx->d_filtered.p, F, ctx->d_cams.p, stride, ctx->d_hist.p); ctx->launches += 1; }
+        if (M_ub > 0) { k_deliver_hist<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, ctx->d_hist.p); ctx->launches += 1; }
         if (scan_exclusive(ctx, ctx->d_hist.p, buf.start, n_keys)) return 1;
-        if (F > 0) {
-            k_deliver_scatter<<<(F + 255) / 256, 256, 0, st>>>(ctx->d_filtered.p, F, ctx->d_cams.p, stride, buf.start, ctx->d_cursor.p, buf.tgt, buf.dep);
+        if (M_ub > 0) {
+            k_deliver_scatter<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, buf.start, ctx->d_cursor.p, buf.tgt, buf.dep);
             k_deliver_sort<<<(n_keys + 255) / 256, 256, 0, st>>>(buf.start, n_keys, buf.tgt, buf.dep);
             ctx->launches += 2;
         }
         L3D_CUDA(cudaGetLastError());
-        // per-slot totals are needed on the host only for accounting: read the slot boundaries
-        L3D_CUDA(ctx->h_ints.ensure(size_t(n_deliver) + 17));
-        for (int d = 0; d <= n_deliver; ++d)
-            L3D_CUDA(cudaMemcpyAsync(ctx->h_ints.p + 16 + d, buf.start + size_t(d) * stride, sizeof(int), cudaMemcpyDeviceToHost, st));
+        // slot boundaries (record counts per destination view) for the host's bookkeeping
+        L3D_CUDA(ctx->d_pa_idx.ensure(size_t(n_deliver) + 1)); L3D_CUDA(ctx->d_pa_tot.ensure(size_t(n_deliver) + 1));
+        for (int d = 0; d <= n_deliver; ++d) ctx->h_ints.p[d] = d * stride;
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_pa_idx.p, ctx->h_ints.p, sizeof(int) * (size_t(n_deliver) + 1), cudaMemcpyHostToDevice, st));
+        k_gather_int<<<(n_deliver + 256) / 256, 256, 0, st>>>(buf.start, ctx->d_pa_idx.p, n_deliver + 1, ctx->d_pa_tot.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p + 8, ctx->d_pa_tot.p, sizeof(int) * (size_t(n_deliver) + 1), cudaMemcpyDeviceToHost, st));
+    }
+    L3D_CUDA(cudaEventRecord(ctx->ev[5], st));
+
+    // ---- results: one small copy, one synchronise ------------------------------------------------
+    L3D_CUDA(ctx->h_floats.ensure(4)); L3D_CUDA(ctx->h_u64.ensure(2));
+    L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p, d_M, sizeof(int), cudaMemcpyDeviceToHost, st));
+    L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p + 1, d_F, sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (scored && M_ub > 0) {
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_floats.p, ctx->d_median.p, sizeof(float), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_u64.p, ctx->d_iters.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    }
+    L3D_CUDA(cudaStreamSynchronize(st));
+    const int M = ctx->h_res.p[0], F = (M_ub > 0) ? ctx->h_res.p[1] : 0;
+    float median = 1.0f;                              // line3D.cc:811
+    if (scored && M > 0) { median = ctx->h_floats.p[0]; res->score_iters = ctx->h_u64.p[0]; res->score_iters_other_cam = ctx->h_u64.p[0] - ctx->h_u64.p[1]; }
+    res->n_scored = uint64_t(M);
+    res->n_raw = uint64_t(M) - res->n_delivered;
+    res->median_depth = median;
+    res->n_filtered = uint64_t(F);
+    if (copy_back && F > 0) {
+        L3D_CUDA(ctx->h_filtered.ensure(size_t(F)));
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_filtered.p, ctx->d_filtered.p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, st));
         L3D_CUDA(cudaStreamSynchronize(st));
+    }
+    res->filtered = (copy_back && F > 0) ? ctx->h_filtered.p : nullptr;
+    if (delivering) {
         const int owner = int(ctx->deliver_bufs.size());
         ctx->deliver_bufs.push_back(buf);
         for (int c = 0; c < n_nb; ++c) {
             const int d = ctx->h_cams.p[c].deliver;
             if (d < 0) continue;
             Delivered dl; dl.from_view = view; dl.owner = owner;
-            dl.count = ctx->h_ints.p[16 + d + 1] - ctx->h_ints.p[16 + d];
+            dl.count = ctx->h_res.p[8 + d + 1] - ctx->h_res.p[8 + d];
             dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
             ctx->delivered[nb[c].view].push_back(dl);
         }
     }
-    L3D_CUDA(cudaEventRecord(ctx->ev[5], st));
-
-    // ---- results --------------------------------------------------------------------------
-    if (copy_back && F > 0) {
-        L3D_CUDA(ctx->h_filtered.ensure(size_t(F)));
-        L3D_CUDA(cudaMemcpyAsync(ctx->h_filtered.p, ctx->d_filtered.p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, st));
-    }
-    L3D_CUDA(cudaStreamSynchronize(st));
-    if (scored && M > 0) { median = ctx->h_floats.p[0]; res->score_iters = ctx->h_u64.p[0]; res->score_iters_other_cam = ctx->h_u64.p[0] - ctx->h_u64.p[1]; }
-    res->median_depth = median;
-    res->n_filtered = uint64_t(F);
-    res->filtered = (copy_back && F > 0) ? ctx->h_filtered.p : nullptr;
     // the consumed deliveries are no longer needed
     {
         std::vector<Delivered>& dl = ctx->delivered[view];
@@ -1165,8 +1297,14 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         dl.swap(keep);
     }
     float ms;
-    for (int k = 0; k < 5; ++k) { ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[k], ctx->ev[k + 1]); ctx->last_ms[k] = ms; }
-    ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[5]); ctx->last_ms[5] = ms;
+    ctx->last_ms[0] = ctx->last_ms[1] = 0.f;
+    if (ctx->pa_ms_pending) {                          // phase A of a whole batch is booked on the call that ran it
+        ms = 0.f; cudaEventElapsedTime(&ms, ctx->pa_ev[0], ctx->pa_ev[1]); ctx->last_ms[0] = ms;
+        ms = 0.f; cudaEventElapsedTime(&ms, ctx->pa_ev[1], ctx->pa_ev[2]); ctx->last_ms[1] = ms;
+        ctx->pa_ms_pending = false;
+    }
+    for (int k = 2; k < 5; ++k) { ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[k], ctx->ev[k + 1]); ctx->last_ms[k] = ms; }
+    ctx->last_ms[5] = ctx->last_ms[0] + ctx->last_ms[1] + ctx->last_ms[2] + ctx->last_ms[3] + ctx->last_ms[4];
     return 0;
 }
 
@@ -1190,6 +1328,7 @@ int l3d_create(int device, l3d_ctx** out)
     ctx->device = device;
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); delete ctx; return 1; }
     for (int k = 0; k < 8; ++k) cudaEventCreate(&ctx->ev[k]);
+    for (int k = 0; k < 3; ++k) cudaEventCreate(&ctx->pa_ev[k]);
     *out = ctx;
     return 0;
 }
@@ -1203,6 +1342,7 @@ int l3d_reset_matching(l3d_ctx* ctx)
         ctx->delivered[v].clear();
     }
     ctx->deliver_bufs.clear();
+    ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;
     cudaStreamSynchronize(ctx->stream);
     return 0;
 }
@@ -1216,7 +1356,9 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_cand.release(); ctx->d_cand_cnt.release(); ctx->d_cand_off.release(); ctx->d_tile_sums.release(); ctx->d_total.release();
     ctx->d_stage_col.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
-    ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
+    ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release();
+    ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->h_res.release();
+    for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_cams.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
     ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release();
@@ -1290,6 +1432,25 @@ int l3d_set_views(l3d_ctx* ctx, int n_views, const l3d_view* views)
     L3D_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->delivered.assign(size_t(n_views), std::vector<Delivered>());
     ctx->n_hyp = 0;
+    return 0;
+}
+
+int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
+{
+    if (!ctx) return 1;
+    ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;
+    if (n_views <= 0) return 0;
+    if (!plans) { ctx->err = "l3d_plan_matching: null argument"; return 1; }
+    for (int k = 0; k < n_views; ++k) {
+        const l3d_view_plan& p = plans[k];
+        if (p.view < 0 || p.view >= ctx->V || p.n_neighbors <= 0 || !p.neighbors) { ctx->plan.clear(); ctx->err = "l3d_plan_matching: bad entry"; return 1; }
+        PlannedView pv; pv.view = p.view; pv.nb.assign(p.neighbors, p.neighbors + p.n_neighbors);
+        for (int c = 0; c < p.n_neighbors; ++c) {
+            if (p.neighbors[c].view < 0 || p.neighbors[c].view >= ctx->V || p.neighbors[c].view == p.view) { ctx->plan.clear(); ctx->err = "l3d_plan_matching: bad neighbour"; return 1; }
+            if (p.neighbors[c].to_be_matched) pv.pair_tests += uint64_t(ctx->views[p.view].n_segments) * uint64_t(ctx->views[p.neighbors[c].view].n_segments);
+        }
+        ctx->plan.push_back(pv);
+    }
     return 0;
 }
 

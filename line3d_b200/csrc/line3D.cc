@@ -382,21 +382,45 @@ struct Line3D::Impl
     {
         std::cout << prefix << separator << std::endl;
         std::cout << prefix << ">>> MATCHING IMAGES <<<" << std::endl;
+        // Which neighbours a view pair-tests and to which it hands its matches depends only on the
+        // neighbour graph and the view order (line3D.cc:732-736, 844-845, 875-881): work the whole
+        // schedule out first and announce it, so the library can batch the pair tests.
+        std::map<unsigned, std::vector<l3d_neighbor> > schedule;
+        {
+            std::map<unsigned, std::set<unsigned> > done;
+            for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it) {
+                const unsigned vid = it->first;
+                if (it->second.empty()) continue;
+                std::vector<l3d_neighbor>& nb = schedule[vid];
+                nb.resize(it->second.size());
+                for (size_t c = 0; c < it->second.size(); ++c) {
+                    const unsigned n = it->second[c];
+                    if (fund[vid].find(n) == fund[vid].end()) { M3 F = fundamental(vid, n); M3 Ft = F.transpose(); fund[vid][n] = F; fund[n][vid] = Ft; }   // :1949-1965
+                    const M3& F = fund[vid][n];
+                    nb[c].view = views[n]->index;
+                    for (int r = 0; r < 3; ++r) for (int cc = 0; cc < 3; ++cc) nb[c].F[r * 3 + cc] = float(F(r, cc));                    // :745
+                    nb[c].to_be_matched = done[vid].count(n) ? 0 : 1;                                                                    // :732-736
+                    nb[c].deliver = (neighbour_of(n, vid) && !done[n].count(vid)) ? 1 : 0;                                               // :844-845
+                }
+                for (size_t c = 0; c < it->second.size(); ++c) {                                                                         // :875-881
+                    const unsigned n = it->second[c];
+                    done[vid].insert(n);
+                    if (neighbour_of(n, vid)) done[n].insert(vid);
+                }
+            }
+            std::vector<l3d_view_plan> plans;
+            for (std::map<unsigned, std::vector<l3d_neighbor> >::iterator it = schedule.begin(); it != schedule.end(); ++it) {
+                l3d_view_plan p; p.view = views[it->first]->index; p.n_neighbors = int(it->second.size()); p.neighbors = it->second.data();
+                plans.push_back(p);
+            }
+            if (l3d_plan_matching(ctx, int(plans.size()), plans.data())) fail("l3d_plan_matching");
+        }
         for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it) {
             const unsigned vid = it->first;
             std::cout << prefix << "matching image [" << vid << "] with " << it->second.size() << " VNs" << std::endl;
             if (it->second.empty()) continue;
             ViewData* v = views[vid];
-            std::vector<l3d_neighbor> nb(it->second.size());
-            for (size_t c = 0; c < it->second.size(); ++c) {
-                const unsigned n = it->second[c];
-                if (fund[vid].find(n) == fund[vid].end()) { M3 F = fundamental(vid, n); M3 Ft = F.transpose(); fund[vid][n] = F; fund[n][vid] = Ft; }   // :1949-1965
-                const M3& F = fund[vid][n];
-                nb[c].view = views[n]->index;
-                for (int r = 0; r < 3; ++r) for (int cc = 0; cc < 3; ++cc) nb[c].F[r * 3 + cc] = float(F(r, cc));                    // :745
-                nb[c].to_be_matched = matched[vid].count(n) ? 0 : 1;                                                                 // :732-736
-                nb[c].deliver = (neighbour_of(n, vid) && !matched[n].count(vid)) ? 1 : 0;                                            // :844-845
-            }
+            std::vector<l3d_neighbor>& nb = schedule[vid];
             l3d_match_result res;
             const double t0 = now_s();
             int rc = measure_only ? l3d_match_view_resident(ctx, v->index, int(nb.size()), nb.data(), sigma_p, sigma_a, &res)
