@@ -265,58 +265,112 @@ __device__ __forceinline__ void side_bounds(float e1a, float e1b, float e2a, flo
     U_lo = fmaxf(hi, 1.0f) - fminf(lo, 0.0f) - err;
 }
 
-constexpr int PT_THREADS = 128;     // rows per block
-constexpr int PT_COLS = 256;        // columns staged per smem tile (small tiles: enough CTAs to fill 148 SMs)
+// Two levels inside the kernel.  Level 1 is a sign test on the four residuals: the src
+// segment lies entirely on one side of an epipolar line when E[m][1] and E[m][2] have the
+// same sign; if that holds for both target endpoints, by more than L3D_PRETEST_EPS_PX pixels,
+// and both intersections fall beyond the same end of the segment, the overlap is zero
+// whatever the rounding (same for the target side).  About 93 % of all pairs end here.
+// Survivors are compacted through a per-warp queue and get the interval test (level 2).
+constexpr int PT_ROWS = 128;        // source segments per block tile
+constexpr int PT_COLS = 256;        // target segments per block tile: 8 warps x 32 lanes
+constexpr int PT_BLOCK = 256;
+constexpr int PT_Q = 96;
 
-__global__ void __launch_bounds__(PT_THREADS) k_pretest(const SrcHoist* __restrict__ sh, const TgtHoist* __restrict__ th,
-                                                        const JobDev* __restrict__ jobs, int n_jobs,
-                                                        unsigned* __restrict__ cand, int* __restrict__ cand_cnt)
+__device__ __forceinline__ bool pretest_level1_reject(float e11, float e12, float e21, float e22, float tq1, float tq2, float tp1, float tp2)
 {
+    // along the src segment: endpoint m of the target gives (e_m1, e_m2); tq_m = eps * |(F^T q_m)_xy|
+    const float a11 = fabsf(e11), a12 = fabsf(e12), a21 = fabsf(e21), a22 = fabsf(e22);
+    const bool sA = (e11 * e12 > 0.0f) && (e21 * e22 > 0.0f) && (fminf(a11, a12) > tq1) && (fminf(a21, a22) > tq2) && ((a11 < a12) == (a21 < a22));
+    // along the tgt segment: endpoint n of the source gives (e_1n, e_2n); tp_n = eps * |(F p_n)_xy|
+    const bool sB = (e11 * e21 > 0.0f) && (e12 * e22 > 0.0f) && (fminf(a11, a21) > tp1) && (fminf(a12, a22) > tp2) && ((a11 < a21) == (a12 < a22));
+    return sA || sB;
+}
+
+__global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict__ sh, const TgtHoist* __restrict__ th,
+                                                      const JobDev* __restrict__ jobs, int n_jobs,
+                                                      unsigned* __restrict__ cand, int* __restrict__ cand_cnt)
+{
+    __shared__ float4 s_a[PT_ROWS], s_b[PT_ROWS];
     __shared__ float4 s_q[PT_COLS];
     __shared__ float2 s_w[PT_COLS];
+    __shared__ unsigned s_bits[PT_ROWS][PT_COLS / 32];
+    __shared__ unsigned short s_queue[PT_BLOCK / 32][PT_Q];
     __shared__ int s_job;
     if (threadIdx.x == 0) s_job = find_job_by_block(jobs, n_jobs, blockIdx.x);
     __syncthreads();
     const JobDev& jb = jobs[s_job];
     const int local = blockIdx.x - jb.blk_off;
     const int rb = local / jb.col_blocks, cb = local - rb * jb.col_blocks;
-    const int col0 = cb * PT_COLS;
-    const int ncol = min(PT_COLS, jb.n_tgt - col0);
-    for (int k = threadIdx.x; k < PT_COLS; k += PT_THREADS) {
-        if (k < ncol) { TgtHoist h = th[jb.th_off + col0 + k]; s_q[k] = h.q; s_w[k] = h.w; }
-        else { s_q[k] = make_float4(0.f, 0.f, 0.f, 0.f); s_w[k] = make_float2(0.f, 0.f); }
+    const int col0 = cb * PT_COLS, row0 = rb * PT_ROWS;
+    const int ncol = min(PT_COLS, jb.n_tgt - col0), nrow = min(PT_ROWS, jb.n_src - row0);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        if (tid < ncol) { TgtHoist h = th[jb.th_off + col0 + tid]; s_q[tid] = h.q; s_w[tid] = h.w; }
+        else { s_q[tid] = make_float4(0.f, 0.f, 0.f, 0.f); s_w[tid] = make_float2(0.f, 0.f); }
+        if (tid < PT_ROWS) {
+            if (tid < nrow) { SrcHoist h = sh[jb.sh_off + row0 + tid]; s_a[tid] = h.a; s_b[tid] = h.b; }
+            else { s_a[tid] = make_float4(0.f, 0.f, 0.f, 0.f); s_b[tid] = make_float4(0.f, 0.f, 0.f, 0.f); }
+        }
+        for (int k = tid; k < PT_ROWS * (PT_COLS / 32); k += PT_BLOCK) (&s_bits[0][0])[k] = 0u;
     }
     __syncthreads();
-    const int row = rb * PT_THREADS + threadIdx.x;
-    if (row >= jb.n_src) return;
-    const SrcHoist h = sh[jb.sh_off + row];
-    const float4 A1 = h.a, A2 = h.b;
-    int total = 0;
-    unsigned* out = cand + jb.cand_off + (long long)row * jb.wpr + (col0 >> 5);
-    for (int w = 0; w * 32 < ncol; ++w) {
-        unsigned bits = 0, mk = 1u;
-#pragma unroll 8
-        for (int b = 0; b < 32; ++b, mk <<= 1) {
-            const float4 q = s_q[w * 32 + b];
-            const float2 ww = s_w[w * 32 + b];
-            // E[m][n] = q_m . A_n
-            float e11 = fmaf(q.x, A1.x, fmaf(q.y, A1.y, A1.z));
-            float e12 = fmaf(q.x, A2.x, fmaf(q.y, A2.y, A2.z));
-            float e21 = fmaf(q.z, A1.x, fmaf(q.w, A1.y, A1.z));
-            float e22 = fmaf(q.z, A2.x, fmaf(q.w, A2.y, A2.z));
+    const bool valid = tid < ncol;
+    const float4 q = s_q[tid];
+    const float2 wq = s_w[tid];
+    const float tq1 = L3D_PRETEST_EPS_PX * wq.x, tq2 = L3D_PRETEST_EPS_PX * wq.y;
+    unsigned short* queue = s_queue[warp];
+    int qn = 0;
+    auto level2 = [&](int first, int count) {
+        if (lane < count) {
+            const unsigned e = queue[first + lane];
+            const int r = int(e >> 5), l = int(e & 31u);
+            const float4 A1 = s_a[r], A2 = s_b[r];
+            const float4 qq = s_q[warp * 32 + l];
+            const float2 ww = s_w[warp * 32 + l];
+            float e11 = fmaf(qq.x, A1.x, fmaf(qq.y, A1.y, A1.z));
+            float e12 = fmaf(qq.x, A2.x, fmaf(qq.y, A2.y, A2.z));
+            float e21 = fmaf(qq.z, A1.x, fmaf(qq.w, A1.y, A1.z));
+            float e22 = fmaf(qq.z, A2.x, fmaf(qq.w, A2.y, A2.z));
             float Ia, Ua, Ib, Ub;
             side_bounds(e11, e12, e21, e22, ww.x, ww.y, Ia, Ua);      // along the src segment
             side_bounds(e11, e21, e12, e22, A1.w, A2.w, Ib, Ub);      // along the tgt segment
             // keep unless an overlap surely misses a threshold; NaN/inf comparisons keep
-            bool drop = (Ia < L3D_PRETEST_LO * Ua) || (Ib < L3D_PRETEST_LO * Ub) ||
-                        ((Ia < L3D_PRETEST_HI * Ua) && (Ib < L3D_PRETEST_HI * Ub));
-            if (!drop) bits |= mk;
+            const bool drop = (Ia < L3D_PRETEST_LO * Ua) || (Ib < L3D_PRETEST_LO * Ub) ||
+                              ((Ia < L3D_PRETEST_HI * Ua) && (Ib < L3D_PRETEST_HI * Ub));
+            if (!drop) atomicOr(&s_bits[r][warp], 1u << l);
         }
-        if (w * 32 + 32 > ncol) { int valid = ncol - w * 32; bits &= (valid >= 32) ? 0xffffffffu : ((1u << valid) - 1u); }
-        out[w] = bits;
-        total += __popc(bits);
+    };
+#pragma unroll 4
+    for (int r = 0; r < nrow; ++r) {
+        const float4 A1 = s_a[r], A2 = s_b[r];          // broadcast
+        // E[m][n] = q_m . A_n
+        const float e11 = fmaf(q.x, A1.x, fmaf(q.y, A1.y, A1.z));
+        const float e12 = fmaf(q.x, A2.x, fmaf(q.y, A2.y, A2.z));
+        const float e21 = fmaf(q.z, A1.x, fmaf(q.w, A1.y, A1.z));
+        const float e22 = fmaf(q.z, A2.x, fmaf(q.w, A2.y, A2.z));
+        const bool pass = valid && !pretest_level1_reject(e11, e12, e21, e22, tq1, tq2, L3D_PRETEST_EPS_PX * A1.w, L3D_PRETEST_EPS_PX * A2.w);
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        if (m) {
+            if (pass) queue[qn + __popc(m & ((1u << lane) - 1u))] = (unsigned short)((r << 5) | lane);
+            qn += __popc(m);
+            __syncwarp();
+            if (qn >= 32) { level2(qn - 32, 32); qn -= 32; __syncwarp(); }
+        }
     }
-    if (total) atomicAdd(&cand_cnt[jb.row_off + row], total);
+    if (qn > 0) level2(0, qn);
+    __syncthreads();
+    // write the tile's bitmask rows and count the candidates per row
+    const int wpt = PT_COLS / 32;                        // 8 words per row
+    for (int k = tid; k < nrow * wpt; k += PT_BLOCK) {
+        const int r = k / wpt, w = k - r * wpt;
+        if (col0 + w * 32 < jb.n_tgt) cand[jb.cand_off + (long long)(row0 + r) * jb.wpr + (col0 >> 5) + w] = s_bits[r][w];
+    }
+    if (tid < nrow) {
+        int total = 0;
+#pragma unroll
+        for (int w = 0; w < wpt; ++w) total += __popc(s_bits[tid][w]);
+        if (total) atomicAdd(&cand_cnt[jb.row_off + row0 + tid], total);
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1022,7 +1076,7 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
         d.sh_off = int(sh_tot); d.th_off = int(th_tot); d.cand_off = words; d.wpr = (d.n_tgt + 31) / 32;
         d.row_off = int(rows); d.blk_off = int(blocks); d.col_blocks = std::max((d.n_tgt + PT_COLS - 1) / PT_COLS, 1);
         sh_tot += d.n_src; th_tot += d.n_tgt; words += (long long)d.n_src * d.wpr; rows += d.n_src;
-        blocks += (long long)((d.n_src + PT_THREADS - 1) / PT_THREADS) * d.col_blocks;
+        blocks += (long long)((d.n_src + PT_ROWS - 1) / PT_ROWS) * d.col_blocks;
         max_n = std::max(max_n, std::max(d.n_src, d.n_tgt));
         if (sh_tot > 0x7fffffff || th_tot > 0x7fffffff || rows > 0x7ffffff0 || blocks > 0x7ffffff0) { ctx->err = "phase A: batch too large"; return 1; }
     }
@@ -1035,7 +1089,7 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     L3D_CUDA(cudaEventRecord(ctx->pa_ev[0], st));
     if (rows > 0 && blocks > 0) {
         k_hoist<<<dim3((max_n + 127) / 128, n_jobs), 128, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, ctx->d_sh.p, ctx->d_th.p);
-        k_pretest<<<unsigned(blocks), PT_THREADS, 0, st>>>(ctx->d_sh.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_cand.p, ctx->d_pa_cnt.p);
+        k_pretest<<<unsigned(blocks), PT_BLOCK, 0, st>>>(ctx->d_sh.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_cand.p, ctx->d_pa_cnt.p);
         ctx->launches += 2;
         L3D_CUDA(cudaGetLastError());
     }

@@ -21,7 +21,7 @@
 #include <set>
 #include <sstream>
 #include <stdexcept>
-#include <unordered_set>
+#include <thread>
 
 namespace L3D
 {
@@ -127,9 +127,12 @@ struct Line3D::Impl
     std::map<unsigned, std::set<unsigned> > matched;
 
     std::map<unsigned, std::vector<BestMatch> > best;              // per view, per segment
-    std::vector<std::pair<uint64_t, uint64_t> > potential;         // symmetric pairs of segment keys
+    struct PC { unsigned seg, tcam, tseg; };                          // (this view, seg) <-> (tcam, tseg), line3D.cc:861-865
+    std::vector<std::vector<PC> > pc_fwd, pc_rev, pc;                // per view index: as produced / as received / merged, sorted, unique
+    std::vector<ViewData*> view_at;                                  // view index -> view
+    std::vector<int> id2idx;                                         // view id -> view index or -1
     std::vector<Hypothesis> hyps;                                  // (cam, seg) ascending
-    std::map<uint64_t, int> hyp_of;
+    std::vector<std::vector<int> > hyp_of;                            // [view index][segment] -> hypothesis or -1
 
     std::list<L3DFinalLine3D> result;
     double tr_scale, tr_scale_inv; M3 tr_R, tr_Rinv; V3 tr_t, tr_tneg; Eigen::Matrix4d Qinv;
@@ -360,8 +363,11 @@ struct Line3D::Impl
     {
         std::vector<l3d_view> lv(views.size());
         int idx = 0;
+        view_at.assign(views.size(), (ViewData*)0);
+        id2idx.assign(views.empty() ? 0 : size_t(views.rbegin()->first) + 1, -1);
+        pc_fwd.assign(views.size(), std::vector<PC>()); pc_rev.assign(views.size(), std::vector<PC>()); pc.assign(views.size(), std::vector<PC>());
         for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it, ++idx) {
-            ViewData* v = it->second; v->index = idx;
+            ViewData* v = it->second; v->index = idx; view_at[idx] = v; id2idx[it->first] = idx;
             l3d_view& o = lv[idx];
             memset(&o, 0, sizeof o);
             o.id = int(v->id); o.n_segments = int(v->segs.size()); o.segments = reinterpret_cast<const float*>(v->segs.data());
@@ -455,8 +461,9 @@ struct Line3D::Impl
                         const double row[9] = {double(vid), double(m.src_seg), double(cam), double(m.tgt_seg), m.depths[0], m.depths[1], m.depths[2], m.depths[3], m.confidence};
                         filtered_dump.insert(filtered_dump.end(), row, row + 9);
                     }
-                    potential.push_back(std::make_pair(seg_key(vid, m.src_seg), seg_key(cam, m.tgt_seg)));                           // :861-865
-                    potential.push_back(std::make_pair(seg_key(cam, m.tgt_seg), seg_key(vid, m.src_seg)));
+                    PC f = {unsigned(m.src_seg), cam, unsigned(m.tgt_seg)};                                                         // :861-865
+                    pc_fwd[v->index].push_back(f);
+                    if (cam < id2idx.size() && id2idx[cam] >= 0) { PC r = {unsigned(m.tgt_seg), vid, unsigned(m.src_seg)}; pc_rev[id2idx[cam]].push_back(r); }
                     BestMatch& b = bm[m.src_seg];                                                                                   // view.cc:165-183: first maximum
                     if (!b.has || m.confidence > b.conf) { b.has = true; b.tgt_cam = cam; b.tgt_seg = unsigned(m.tgt_seg); b.conf = m.confidence; b.d1 = m.depths[0]; b.d2 = m.depths[1]; }
                 }
@@ -473,7 +480,8 @@ struct Line3D::Impl
     {
         std::cout << prefix << separator << std::endl;
         std::cout << prefix << ">>> OPTIMIZING CORRESPONDENCES (greedy) <<<" << std::endl;
-        hyps.clear(); hyp_of.clear();
+        hyps.clear(); hyp_of.assign(views.size(), std::vector<int>());
+        for (size_t k = 0; k < view_at.size(); ++k) hyp_of[k].assign(view_at[k]->segs.size(), -1);
         std::vector<l3d_hypothesis_in> in;
         for (std::map<unsigned, std::vector<BestMatch> >::iterator it = best.begin(); it != best.end(); ++it)
             for (size_t s = 0; s < it->second.size(); ++s) {
@@ -481,7 +489,7 @@ struct Line3D::Impl
                 if (!b.has) continue;
                 Hypothesis h; h.cam = it->first; h.seg = unsigned(s); h.tgt_cam = b.tgt_cam; h.tgt_seg = b.tgt_seg;
                 h.score = fminf(b.conf, 1.0f); h.d1 = b.d1; h.d2 = b.d2;                                                            // :937
-                hyp_of[seg_key(h.cam, h.seg)] = int(hyps.size());
+                hyp_of[views[it->first]->index][s] = int(hyps.size());
                 hyps.push_back(h);
                 l3d_hypothesis_in hi; hi.view = views[it->first]->index; hi.seg = int(s); hi.depth1 = b.d1; hi.depth2 = b.d2;
                 in.push_back(hi);
@@ -502,61 +510,91 @@ struct Line3D::Impl
         result.clear();
         std::cout << prefix << "computing affinity matrix..." << std::endl;
         const double t0 = now_s();
-        // potential correspondences as a sorted, de-duplicated CSR over source keys
-        std::sort(potential.begin(), potential.end());
-        potential.erase(std::unique(potential.begin(), potential.end()), potential.end());
+        // potential correspondences per view: the records a view produced are already in (seg, cam, seg) order,
+        // the ones it received are sorted here; both are merged and de-duplicated (a std::map in the reference)
+        {
+            const size_t nv = view_at.size();
+            auto work = [&](size_t v0, size_t step) {
+                auto less = [](const PC& a, const PC& b) { return a.seg != b.seg ? a.seg < b.seg : (a.tcam != b.tcam ? a.tcam < b.tcam : a.tseg < b.tseg); };
+                auto same = [](const PC& a, const PC& b) { return a.seg == b.seg && a.tcam == b.tcam && a.tseg == b.tseg; };
+                for (size_t v = v0; v < nv; v += step) {
+                    std::vector<PC>& f = pc_fwd[v]; std::vector<PC>& r = pc_rev[v]; std::vector<PC>& o = pc[v];
+                    if (!std::is_sorted(f.begin(), f.end(), less)) std::sort(f.begin(), f.end(), less);
+                    std::sort(r.begin(), r.end(), less);
+                    o.resize(f.size() + r.size());
+                    std::merge(f.begin(), f.end(), r.begin(), r.end(), o.begin(), less);
+                    o.erase(std::unique(o.begin(), o.end(), same), o.end());
+                    std::vector<PC>().swap(f); std::vector<PC>().swap(r);
+                }
+            };
+            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), 16));
+            std::vector<std::thread> pool;
+            for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t, nt);
+            work(0, nt);
+            for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
+        }
         struct Cand { int a, b; float mult; float thr; };
         std::vector<Cand> cands;
-        std::unordered_set<uint64_t> used;                 // unordered pair of dense segment numbers
-        // dense numbering of every segment key that can occur
-        std::map<unsigned, uint64_t> view_base; uint64_t total = 0;
-        for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) { view_base[it->first] = total; total += it->second->segs.size(); }
-        auto dense = [&](unsigned cam, unsigned seg, uint64_t& out) -> bool {
-            std::map<unsigned, uint64_t>::iterator b = view_base.find(cam);
-            if (b == view_base.end() || seg >= views[cam]->segs.size()) return false;
-            out = b->second + seg; return true;
-        };
+        // dense numbering of every segment, for the "used" pair set
+        std::vector<uint64_t> view_base(view_at.size() + 1, 0);
+        for (size_t k = 0; k < view_at.size(); ++k) view_base[k + 1] = view_base[k] + view_at[k]->segs.size();
+        const uint64_t total = view_base[view_at.size()];
         // a key outside every view can only come from the unscored-view quirk; such a target has no
         // hypothesis and no collinear partners, so it can never produce an edge: it is skipped
+        auto dense = [&](unsigned cam, unsigned seg, int& vidx, uint64_t& out) -> bool {
+            if (cam >= id2idx.size() || id2idx[cam] < 0) return false;
+            vidx = id2idx[cam];
+            if (seg >= view_at[vidx]->segs.size()) return false;
+            out = view_base[vidx] + seg; return true;
+        };
+        // set of unordered segment pairs already looked at (line3D.cc:980, 1001-1005): open addressing
+        std::vector<uint64_t> used(size_t(1) << 16, ~uint64_t(0)); size_t used_n = 0;
         auto mark = [&](uint64_t a, uint64_t b) -> bool {   // true if the pair was new
-            uint64_t lo = std::min(a, b), hi = std::max(a, b);
-            return used.insert(lo * total + hi).second;
+            const uint64_t key = std::min(a, b) * total + std::max(a, b);
+            if ((used_n + 1) * 2 > used.size()) {
+                std::vector<uint64_t> bigger(used.size() * 4, ~uint64_t(0));
+                for (size_t k = 0; k < used.size(); ++k) if (used[k] != ~uint64_t(0)) {
+                    size_t h = size_t((used[k] * 0x9E3779B97F4A7C15ull) >> 20) & (bigger.size() - 1);
+                    while (bigger[h] != ~uint64_t(0)) h = (h + 1) & (bigger.size() - 1);
+                    bigger[h] = used[k];
+                }
+                used.swap(bigger);
+            }
+            size_t h = size_t((key * 0x9E3779B97F4A7C15ull) >> 20) & (used.size() - 1);
+            while (used[h] != ~uint64_t(0)) { if (used[h] == key) return false; h = (h + 1) & (used.size() - 1); }
+            used[h] = key; ++used_n; return true;
         };
-        auto hyp_index = [&](unsigned cam, unsigned seg) -> int {
-            std::map<uint64_t, int>::iterator f = hyp_of.find(seg_key(cam, seg));
-            return f == hyp_of.end() ? -1 : f->second;
-        };
-        size_t pc = 0;
+        std::vector<size_t> cursor(view_at.size(), 0);
         for (size_t hidx = 0; hidx < hyps.size(); ++hidx) {
             const Hypothesis& C = hyps[hidx];
-            uint64_t dsrc; if (!dense(C.cam, C.seg, dsrc)) continue;
-            const uint64_t skey = seg_key(C.cam, C.seg);
-            while (pc < potential.size() && potential[pc].first < skey) ++pc;
-            for (size_t k = pc; k < potential.size() && potential[k].first == skey; ++k) {                                           // :996-1138
-                const unsigned tcam = unsigned(potential[k].second >> 32), tseg = unsigned(potential[k].second & 0xffffffffu);
-                uint64_t dt; if (!dense(tcam, tseg, dt)) continue;
+            int svi; uint64_t dsrc; if (!dense(C.cam, C.seg, svi, dsrc)) continue;
+            const std::vector<PC>& list = pc[svi];
+            size_t& cur = cursor[svi];
+            while (cur < list.size() && list[cur].seg < C.seg) ++cur;
+            for (size_t k = cur; k < list.size() && list[k].seg == C.seg; ++k) {                                                    // :996-1138
+                const unsigned tcam = list[k].tcam, tseg = list[k].tseg;
+                int tvi; uint64_t dt; if (!dense(tcam, tseg, tvi, dt)) continue;
                 if (!mark(dsrc, dt)) continue;
-                const int ht = hyp_index(tcam, tseg);
+                const int ht = hyp_of[tvi][tseg];
                 if (ht < 0) continue;                                                                                               // :1007
                 Cand c = {int(hidx), ht, 1.0f, L3D_MIN_AFFINITY}; cands.push_back(c);                                               // :1014-1016
-                const std::vector<CollinEntry>& cl = views[tcam]->collin[tseg];                                                     // :1065-1135
+                const std::vector<CollinEntry>& cl = view_at[tvi]->collin[tseg];                                                    // :1065-1135
                 for (size_t e = 0; e < cl.size(); ++e) {
-                    uint64_t dc; if (!dense(tcam, cl[e].other, dc)) continue;
-                    if (!mark(dsrc, dc)) continue;
-                    const int hc = hyp_index(tcam, cl[e].other);
+                    if (!mark(dsrc, view_base[tvi] + cl[e].other)) continue;
+                    const int hc = hyp_of[tvi][cl[e].other];
                     if (hc < 0) continue;
                     Cand c3 = {int(hidx), hc, 1.0f, 0.01f}; cands.push_back(c3);                                                    // :1085-1087
                 }
             }
-            const std::vector<CollinEntry>& cs = views[C.cam]->collin[C.seg];                                                       // :1141-1214
+            const std::vector<CollinEntry>& cs = view_at[svi]->collin[C.seg];                                                       // :1141-1214
             for (size_t e = 0; e < cs.size(); ++e) {
-                uint64_t dc; if (!dense(C.cam, cs[e].other, dc)) continue;
-                if (!mark(dsrc, dc)) continue;
-                const int hc = hyp_index(C.cam, cs[e].other);
+                if (!mark(dsrc, view_base[svi] + cs[e].other)) continue;
+                const int hc = hyp_of[svi][cs[e].other];
                 if (hc < 0) continue;
                 Cand c2 = {int(hidx), hc, cs[e].w, 0.01f}; cands.push_back(c2);                                                     // :1163-1165
             }
         }
+        std::vector<uint64_t>().swap(used);
         // similarities on the device (line3D.cc:1600-1691)
         std::vector<l3d_pair> pairs(cands.size());
         for (size_t k = 0; k < cands.size(); ++k) { pairs[k].a = cands[k].a; pairs[k].b = cands[k].b; }
@@ -757,7 +795,7 @@ void Line3D::reset()                                                            
 {
     Impl& d = *impl_;
     d.num_wps.clear(); d.common_wps.clear(); d.view_sim.clear(); d.wp2views.clear(); d.vn.clear(); d.fund.clear();
-    d.matched.clear(); d.best.clear(); d.potential.clear(); d.hyps.clear(); d.hyp_of.clear(); d.result.clear();
+    d.matched.clear(); d.best.clear(); d.pc_fwd.clear(); d.pc_rev.clear(); d.pc.clear(); d.hyps.clear(); d.hyp_of.clear(); d.result.clear();
     for (std::map<unsigned, ViewData*>::iterator it = d.views.begin(); it != d.views.end(); ++it) delete it->second;
     d.views.clear();
     d.computation = false;
@@ -790,7 +828,7 @@ void Line3D::compute3Dmodel(bool perform_diffusion)                             
     Impl& d = *impl_;
     if (d.views.size() < 4) { std::cerr << d.prefix << "not enough images! can't compute 3D model..." << std::endl; return; }
     d.computation = true;
-    d.matched.clear(); d.potential.clear(); d.best.clear(); d.result.clear();
+    d.matched.clear(); d.best.clear(); d.result.clear();
     d.match_log.clear(); d.match_median.clear(); d.filtered_dump.clear(); d.edges_pre.clear(); d.edges_cluster.clear(); d.cluster_nodes = 0;
     memset(&d.stats, 0, sizeof d.stats);
     const uint64_t launches0 = l3d_kernel_launches(d.ctx);
@@ -934,10 +972,11 @@ void Line3D::debugDump(const std::string& directory)
     }
     npy_f64(p + "best_match.npy", bm, 17);
     std::vector<int32_t> pc;
-    for (size_t k = 0; k < d.potential.size(); ++k) {
-        pc.push_back(int32_t(d.potential[k].first >> 32)); pc.push_back(int32_t(d.potential[k].first & 0xffffffffu));
-        pc.push_back(int32_t(d.potential[k].second >> 32)); pc.push_back(int32_t(d.potential[k].second & 0xffffffffu));
-    }
+    for (size_t v = 0; v < d.pc.size(); ++v)
+        for (size_t k = 0; k < d.pc[v].size(); ++k) {
+            pc.push_back(int32_t(d.view_at[v]->id)); pc.push_back(int32_t(d.pc[v][k].seg));
+            pc.push_back(int32_t(d.pc[v][k].tcam)); pc.push_back(int32_t(d.pc[v][k].tseg));
+        }
     npy_i32(p + "potential.npy", pc, 4);
     npy_f64(p + "edges_pre_diffusion.npy", d.edges_pre, 3);
     npy_f64(p + "edges_cluster.npy", d.edges_cluster, 3);
