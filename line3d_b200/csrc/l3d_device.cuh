@@ -99,9 +99,10 @@ __device__ inline float xtri_depth(V3 p1, V3 p2, V3 C1, V3 C2, const float* RtKi
     return -1.0f;
 }
 
-// cudawrapper.cu:538-611.  Returns true when all four depths are > 0 (cudawrapper.cu:931).
-__device__ inline bool xpair_test(float4 s, float4 t, const float* F, const float* RtKinv_s, const float* RtKinv_t,
-                                  V3 C_s, V3 C_t, float4& depths)
+// cudawrapper.cu:546-588: the overlap part of the pair test.  On acceptance the four intersection
+// points (x, y of l2_p1, l2_p2, l1_q1, l1_q2) are returned for the triangulation.
+struct PairIsect { float ax, ay, bx, by, cx, cy, dx, dy; };
+__device__ inline bool xpair_overlap(float4 s, float4 t, const float* F, PairIsect& is)
 {
     V3 p1 = mk3(s.x, s.y, 1.0f), p2 = mk3(s.z, s.w, 1.0f), line1 = xcross(p1, p2);
     V3 q1 = mk3(t.x, t.y, 1.0f), q2 = mk3(t.z, t.w, 1.0f), line2 = xcross(q1, q2);
@@ -112,11 +113,28 @@ __device__ inline bool xpair_test(float4 s, float4 t, const float* F, const floa
     if (l2_p1.z == 0.0f || l2_p2.z == 0.0f || l1_q1.z == 0.0f || l1_q2.z == 0.0f) return false;
     float o1 = xoverlap(p1, p2, l1_q1, l1_q2), o2 = xoverlap(q1, q2, l2_p1, l2_p2);
     if (!(fminf(o1, o2) > L3D_OVERLAP_LO && fmaxf(o1, o2) > L3D_OVERLAP_HI)) return false;
+    is.ax = l2_p1.x; is.ay = l2_p1.y; is.bx = l2_p2.x; is.by = l2_p2.y;
+    is.cx = l1_q1.x; is.cy = l1_q1.y; is.dx = l1_q2.x; is.dy = l1_q2.y;
+    return true;
+}
+// cudawrapper.cu:590-601 + :931: the four depths; true when all are > 0
+__device__ inline bool xpair_depths(float4 s, float4 t, const PairIsect& is, const float* RtKinv_s, const float* RtKinv_t, V3 C_s, V3 C_t, float4& depths)
+{
+    V3 p1 = mk3(s.x, s.y, 1.0f), p2 = mk3(s.z, s.w, 1.0f), q1 = mk3(t.x, t.y, 1.0f), q2 = mk3(t.z, t.w, 1.0f);
+    V3 l2_p1 = mk3(is.ax, is.ay, 1.0f), l2_p2 = mk3(is.bx, is.by, 1.0f), l1_q1 = mk3(is.cx, is.cy, 1.0f), l1_q2 = mk3(is.dx, is.dy, 1.0f);
     depths.x = xtri_depth(p1, l2_p1, C_s, C_t, RtKinv_s, RtKinv_t, true);
     depths.y = xtri_depth(p2, l2_p2, C_s, C_t, RtKinv_s, RtKinv_t, true);
     depths.z = xtri_depth(l1_q1, q1, C_s, C_t, RtKinv_s, RtKinv_t, false);
     depths.w = xtri_depth(l1_q2, q2, C_s, C_t, RtKinv_s, RtKinv_t, false);
     return depths.x > 0.0f && depths.y > 0.0f && depths.z > 0.0f && depths.w > 0.0f;
+}
+// cudawrapper.cu:538-611.  Returns true when all four depths are > 0 (cudawrapper.cu:931).
+__device__ inline bool xpair_test(float4 s, float4 t, const float* F, const float* RtKinv_s, const float* RtKinv_t,
+                                  V3 C_s, V3 C_t, float4& depths)
+{
+    PairIsect is;
+    if (!xpair_overlap(s, t, F, is)) return false;
+    return xpair_depths(s, t, is, RtKinv_s, RtKinv_t, C_s, C_t, depths);
 }
 
 // cudawrapper.cu:58-61

@@ -158,6 +158,29 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_sums(int* __restrict__ tile_sum
     for (int k = 0; k < SCAN_ITEMS; ++k) { if (base + k < n_tiles) tile_sums[base + k] = ex; ex += v[k]; }
     if (threadIdx.x == 0) *out_total = total;
 }
+// whole scan in one block for inputs up to SCAN_SMALL elements (most per-view scans): one launch instead of three
+constexpr int SCAN_SMALL = 64 * 1024;
+__global__ void __launch_bounds__(SCAN_T) k_scan_small(const int* __restrict__ in, int* __restrict__ out /* n + 1 */, int n)
+{
+    __shared__ int sh[32];
+    __shared__ int s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (int base0 = 0; base0 < n; base0 += SCAN_TILE) {
+        const int base = base0 + threadIdx.x * SCAN_ITEMS;
+        int v[SCAN_ITEMS], s = 0;
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; ++k) { v[k] = (base + k < n) ? in[base + k] : 0; s += v[k]; }
+        int total;
+        int ex = block_exclusive_scan(s, &total, sh) + s_carry;
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; ++k) { if (base + k < n) out[base + k] = ex; ex += v[k]; }
+        __syncthreads();
+        if (threadIdx.x == 0) s_carry += total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[n] = s_carry;
+}
 __global__ void __launch_bounds__(SCAN_T) k_scan_add(int* __restrict__ out, const int* __restrict__ tile_sums, int n, const int* __restrict__ total)
 {
     const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
@@ -380,12 +403,16 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
 // ------------------------------------------------------------------------------------------
 constexpr int EX_WARPS = 8;
 constexpr int EX_QCAP = 1088;
+constexpr int EX_Q2 = 64;          // second queue: pairs that passed the overlap test, waiting for triangulation
+
+struct ExQueue2 { int col[EX_Q2]; float f[8][EX_Q2]; };
 
 __global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, int n_jobs, int n_rows,
                                                          const unsigned* __restrict__ cand, const int* __restrict__ cand_off,
                                                          int* __restrict__ stage_col, float4* __restrict__ stage_dep, int* __restrict__ raw_cnt)
 {
     __shared__ unsigned short s_queue[EX_WARPS][EX_QCAP];
+    __shared__ ExQueue2 s_q2[EX_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int grow = blockIdx.x * EX_WARPS + warp;
     if (grow >= n_rows) return;
@@ -397,22 +424,53 @@ __global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restric
     const unsigned* words = cand + jb.cand_off + (long long)row * jb.wpr;
     const int n_words = (jb.n_tgt + 31) >> 5;
     unsigned short* q = s_queue[warp];
+    ExQueue2& q2 = s_q2[warp];
     const float4 s = segs[jb.src_off + row];
     const V3 Cs = mk3(jb.C_s[0], jb.C_s[1], jb.C_s[2]), Ct = mk3(jb.C_t[0], jb.C_t[1], jb.C_t[2]);
-    int qn = 0, accepted = 0;
-    auto evaluate = [&](int first, int count) {
-        // lanes [0, count) take queue entries first .. first + count - 1 (column order)
+    int qn = 0, q2n = 0, accepted = 0;
+    // stage 2: triangulate `count` queued pairs (FIFO order = column order) and write the survivors
+    auto triangulate = [&](int count) {
         bool ok = false; float4 dep = make_float4(0.f, 0.f, 0.f, 0.f); int col = 0;
         if (lane < count) {
-            col = q[first + lane];
-            ok = xpair_test(s, segs[jb.tgt_off + col], jb.F, jb.RtKinv_s, jb.RtKinv_t, Cs, Ct, dep);
+            col = q2.col[lane];
+            PairIsect is;
+            is.ax = q2.f[0][lane]; is.ay = q2.f[1][lane]; is.bx = q2.f[2][lane]; is.by = q2.f[3][lane];
+            is.cx = q2.f[4][lane]; is.cy = q2.f[5][lane]; is.dx = q2.f[6][lane]; is.dy = q2.f[7][lane];
+            ok = xpair_depths(s, segs[jb.tgt_off + col], is, jb.RtKinv_s, jb.RtKinv_t, Cs, Ct, dep);
         }
-        unsigned m = __ballot_sync(0xffffffffu, ok);
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
         if (ok) {
-            int r = base + accepted + __popc(m & ((1u << lane) - 1u));
+            const int r = base + accepted + __popc(m & ((1u << lane) - 1u));
             stage_col[r] = col; stage_dep[r] = dep;
         }
         accepted += __popc(m);
+        // drop the processed head of the queue
+        __syncwarp();
+        const int rem = q2n - count;
+        int c2 = 0; float v[8];
+        if (lane < rem) { c2 = q2.col[count + lane]; for (int k = 0; k < 8; ++k) v[k] = q2.f[k][count + lane]; }
+        __syncwarp();
+        if (lane < rem) { q2.col[lane] = c2; for (int k = 0; k < 8; ++k) q2.f[k][lane] = v[k]; }
+        q2n = rem;
+        __syncwarp();
+    };
+    // stage 1: overlap test of `count` candidates starting at queue position `first`
+    auto overlap = [&](int first, int count) {
+        bool ok = false; int col = 0; PairIsect is;
+        if (lane < count) {
+            col = q[first + lane];
+            ok = xpair_overlap(s, segs[jb.tgt_off + col], jb.F, is);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (ok) {
+            const int r = q2n + __popc(m & ((1u << lane) - 1u));
+            q2.col[r] = col;
+            q2.f[0][r] = is.ax; q2.f[1][r] = is.ay; q2.f[2][r] = is.bx; q2.f[3][r] = is.by;
+            q2.f[4][r] = is.cx; q2.f[5][r] = is.cy; q2.f[6][r] = is.dx; q2.f[7][r] = is.dy;
+        }
+        q2n += __popc(m);
+        __syncwarp();
+        if (q2n >= 32) triangulate(32);
     };
     for (int w0 = 0; w0 < n_words; w0 += 32) {
         unsigned bits = (w0 + lane < n_words) ? words[w0 + lane] : 0u;
@@ -425,7 +483,7 @@ __global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restric
         qn += tot;
         __syncwarp();
         int head = 0;
-        while (qn - head >= 32) { evaluate(head, 32); head += 32; }
+        while (qn - head >= 32) { overlap(head, 32); head += 32; }
         if (head > 0) {        // move the (< 32) leftovers to the front
             const int rem = qn - head;
             unsigned short v = (lane < rem) ? q[head + lane] : (unsigned short)0;
@@ -435,7 +493,8 @@ __global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restric
             __syncwarp();
         }
     }
-    if (qn > 0) evaluate(0, qn);
+    if (qn > 0) overlap(0, qn);
+    while (q2n > 0) triangulate(min(q2n, 32));
     if (lane == 0) raw_cnt[grow] = accepted;
 }
 
@@ -667,22 +726,37 @@ __global__ void k_seg_reduce(const int* __restrict__ off, int n_cams, int n_src,
 
 // median of the finite samples: sorted[count / 2], -1 if none (cudawrapper.cu:1066-1076).
 // Selection by ranking: the sample with (#smaller) <= count/2 < (#smaller or equal) is the answer.
-__global__ void k_median_init(float* __restrict__ out) { out[0] = -1.0f; }
-__global__ void k_median(const float* __restrict__ dsamples, int n, float* __restrict__ out)
+// Pass 1 (2-D grid: samples x chunks of the comparison loop) accumulates, for every sample, how many
+// samples are smaller / smaller-or-equal, and (block row 0) how many are finite; pass 2 picks the answer.
+constexpr int MED_CHUNK = 512;
+__global__ void k_median_rank(const float* __restrict__ dsamples, int n, int* __restrict__ less, int* __restrict__ leq, int* __restrict__ cnt)
 {
-    __shared__ float s[1024];
+    __shared__ float s[MED_CHUNK];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const float v = (i < n) ? dsamples[i] : INFINITY;
-    int less = 0, leq = 0, cnt = 0;
-    for (int t0 = 0; t0 < n; t0 += 1024) {
-        __syncthreads();
-        for (int k = threadIdx.x; k < 1024; k += blockDim.x) s[k] = (t0 + k < n) ? dsamples[t0 + k] : INFINITY;
-        __syncthreads();
-        const int tn = min(1024, n - t0);
+    const int t0 = blockIdx.y * MED_CHUNK;
+    const int tn = min(MED_CHUNK, n - t0);
+    for (int k = threadIdx.x; k < MED_CHUNK; k += blockDim.x) s[k] = (k < tn) ? dsamples[t0 + k] : INFINITY;
+    __syncthreads();
+    if (i >= n) return;
+    const float v = dsamples[i];
+    if (!(v < INFINITY)) return;
+    int a = 0, b = 0;
 #pragma unroll 8
-        for (int k = 0; k < tn; ++k) { const float u = s[k]; less += (u < v); leq += (u <= v); cnt += (u < INFINITY); }
-    }
-    if (v < INFINITY) { const int r = cnt / 2; if (less <= r && r < leq) out[0] = v; }
+    for (int k = 0; k < MED_CHUNK; ++k) { const float u = s[k]; a += (u < v); b += (u <= v); }
+    if (a) atomicAdd(&less[i], a);
+    if (b) atomicAdd(&leq[i], b);
+    if (blockIdx.y == 0) atomicAdd(cnt, 1);
+}
+__global__ void k_median_pick(const float* __restrict__ dsamples, int n, const int* __restrict__ less, const int* __restrict__ leq,
+                              const int* __restrict__ cnt, float* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0 && *cnt == 0) out[0] = -1.0f;
+    if (i >= n) return;
+    const float v = dsamples[i];
+    if (!(v < INFINITY)) return;
+    const int r = *cnt / 2;
+    if (less[i] <= r && r < leq[i]) out[0] = v;
 }
 
 // filtered records in order, one warp per segment
@@ -996,7 +1070,7 @@ struct l3d_ctx {
     DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
     DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
     DBuf<l3d_match> d_filtered;
-    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024;
+    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; DBuf<int> d_medrank;
     // phase A (pair tests) of the resident batch
     DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
     std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands;
@@ -1022,6 +1096,12 @@ namespace {
 
 int scan_exclusive(l3d_ctx* ctx, const int* in, int* out /* n + 1 */, int n)
 {
+    if (n <= SCAN_SMALL) {
+        k_scan_small<<<1, SCAN_T, 0, ctx->stream>>>(in, out, n);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+        return 0;
+    }
     const int tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     if (tiles > SCAN_TILE) { ctx->err = "scan: input too long"; return 1; }
     L3D_CUDA(ctx->d_tile_sums.ensure(size_t(std::max(tiles, 1))));
@@ -1259,8 +1339,14 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         L3D_CUDA(cudaEventRecord(ctx->ev[4], st));
         // ---- reduce -----------------------------------------------------------------------
         k_seg_reduce<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, ctx->d_iters.p);
-        k_median_init<<<1, 1, 0, st>>>(ctx->d_median.p);
-        k_median<<<(2 * n_src + 255) / 256, 256, 0, st>>>(ctx->d_dsamples.p, 2 * n_src, ctx->d_median.p);
+        {
+            const int ns = 2 * n_src;
+            L3D_CUDA(ctx->d_medrank.ensure(size_t(2 * ns) + 1));
+            L3D_CUDA(cudaMemsetAsync(ctx->d_medrank.p, 0, sizeof(int) * (size_t(2 * ns) + 1), st));
+            int* less = ctx->d_medrank.p; int* leq = less + ns; int* cnt = leq + ns;
+            k_median_rank<<<dim3((ns + 127) / 128, (ns + MED_CHUNK - 1) / MED_CHUNK), 128, 0, st>>>(ctx->d_dsamples.p, ns, less, leq, cnt);
+            k_median_pick<<<(ns + 255) / 256, 256, 0, st>>>(ctx->d_dsamples.p, ns, less, leq, cnt, ctx->d_median.p);
+        }
         ctx->launches += 3;
         if (scan_exclusive(ctx, ctx->d_fcnt.p, ctx->d_foff.p, n_src)) return 1;
         d_F = ctx->d_foff.p + n_src;
@@ -1381,6 +1467,10 @@ int l3d_create(int device, l3d_ctx** out)
     l3d_ctx* ctx = new l3d_ctx();
     ctx->device = device;
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); delete ctx; return 1; }
+    {   // keep stream-ordered allocations cached across synchronisations (hand-over buffers are allocated per view)
+        cudaMemPool_t pool; unsigned long long keep = ~0ull;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
     for (int k = 0; k < 8; ++k) cudaEventCreate(&ctx->ev[k]);
     for (int k = 0; k < 3; ++k) cudaEventCreate(&ctx->pa_ev[k]);
     *out = ctx;
@@ -1410,7 +1500,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_cand.release(); ctx->d_cand_cnt.release(); ctx->d_cand_off.release(); ctx->d_tile_sums.release(); ctx->d_total.release();
     ctx->d_stage_col.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
-    ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release();
+    ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release();
     ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->h_res.release();
     for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_cams.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
