@@ -403,16 +403,12 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
 // ------------------------------------------------------------------------------------------
 constexpr int EX_WARPS = 8;
 constexpr int EX_QCAP = 1088;
-constexpr int EX_Q2 = 64;          // second queue: pairs that passed the overlap test, waiting for triangulation
-
-struct ExQueue2 { int col[EX_Q2]; float f[8][EX_Q2]; };
 
 __global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, int n_jobs, int n_rows,
                                                          const unsigned* __restrict__ cand, const int* __restrict__ cand_off,
                                                          int* __restrict__ stage_col, float4* __restrict__ stage_dep, int* __restrict__ raw_cnt)
 {
     __shared__ unsigned short s_queue[EX_WARPS][EX_QCAP];
-    __shared__ ExQueue2 s_q2[EX_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int grow = blockIdx.x * EX_WARPS + warp;
     if (grow >= n_rows) return;
@@ -424,53 +420,22 @@ __global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restric
     const unsigned* words = cand + jb.cand_off + (long long)row * jb.wpr;
     const int n_words = (jb.n_tgt + 31) >> 5;
     unsigned short* q = s_queue[warp];
-    ExQueue2& q2 = s_q2[warp];
     const float4 s = segs[jb.src_off + row];
     const V3 Cs = mk3(jb.C_s[0], jb.C_s[1], jb.C_s[2]), Ct = mk3(jb.C_t[0], jb.C_t[1], jb.C_t[2]);
-    int qn = 0, q2n = 0, accepted = 0;
-    // stage 2: triangulate `count` queued pairs (FIFO order = column order) and write the survivors
-    auto triangulate = [&](int count) {
+    int qn = 0, accepted = 0;
+    auto evaluate = [&](int first, int count) {
+        // lanes [0, count) take queue entries first .. first + count - 1 (column order)
         bool ok = false; float4 dep = make_float4(0.f, 0.f, 0.f, 0.f); int col = 0;
         if (lane < count) {
-            col = q2.col[lane];
-            PairIsect is;
-            is.ax = q2.f[0][lane]; is.ay = q2.f[1][lane]; is.bx = q2.f[2][lane]; is.by = q2.f[3][lane];
-            is.cx = q2.f[4][lane]; is.cy = q2.f[5][lane]; is.dx = q2.f[6][lane]; is.dy = q2.f[7][lane];
-            ok = xpair_depths(s, segs[jb.tgt_off + col], is, jb.RtKinv_s, jb.RtKinv_t, Cs, Ct, dep);
+            col = q[first + lane];
+            ok = xpair_test(s, segs[jb.tgt_off + col], jb.F, jb.RtKinv_s, jb.RtKinv_t, Cs, Ct, dep);
         }
-        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        unsigned m = __ballot_sync(0xffffffffu, ok);
         if (ok) {
-            const int r = base + accepted + __popc(m & ((1u << lane) - 1u));
+            int r = base + accepted + __popc(m & ((1u << lane) - 1u));
             stage_col[r] = col; stage_dep[r] = dep;
         }
         accepted += __popc(m);
-        // drop the processed head of the queue
-        __syncwarp();
-        const int rem = q2n - count;
-        int c2 = 0; float v[8];
-        if (lane < rem) { c2 = q2.col[count + lane]; for (int k = 0; k < 8; ++k) v[k] = q2.f[k][count + lane]; }
-        __syncwarp();
-        if (lane < rem) { q2.col[lane] = c2; for (int k = 0; k < 8; ++k) q2.f[k][lane] = v[k]; }
-        q2n = rem;
-        __syncwarp();
-    };
-    // stage 1: overlap test of `count` candidates starting at queue position `first`
-    auto overlap = [&](int first, int count) {
-        bool ok = false; int col = 0; PairIsect is;
-        if (lane < count) {
-            col = q[first + lane];
-            ok = xpair_overlap(s, segs[jb.tgt_off + col], jb.F, is);
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, ok);
-        if (ok) {
-            const int r = q2n + __popc(m & ((1u << lane) - 1u));
-            q2.col[r] = col;
-            q2.f[0][r] = is.ax; q2.f[1][r] = is.ay; q2.f[2][r] = is.bx; q2.f[3][r] = is.by;
-            q2.f[4][r] = is.cx; q2.f[5][r] = is.cy; q2.f[6][r] = is.dx; q2.f[7][r] = is.dy;
-        }
-        q2n += __popc(m);
-        __syncwarp();
-        if (q2n >= 32) triangulate(32);
     };
     for (int w0 = 0; w0 < n_words; w0 += 32) {
         unsigned bits = (w0 + lane < n_words) ? words[w0 + lane] : 0u;
@@ -483,7 +448,7 @@ __global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restric
         qn += tot;
         __syncwarp();
         int head = 0;
-        while (qn - head >= 32) { overlap(head, 32); head += 32; }
+        while (qn - head >= 32) { evaluate(head, 32); head += 32; }
         if (head > 0) {        // move the (< 32) leftovers to the front
             const int rem = qn - head;
             unsigned short v = (lane < rem) ? q[head + lane] : (unsigned short)0;
@@ -493,8 +458,7 @@ __global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restric
             __syncwarp();
         }
     }
-    if (qn > 0) overlap(0, qn);
-    while (q2n > 0) triangulate(min(q2n, 32));
+    if (qn > 0) evaluate(0, qn);
     if (lane == 0) raw_cnt[grow] = accepted;
 }
 
