@@ -44,6 +44,37 @@ typedef struct { int32_t i, j; float value; } l3d_collin_pair;
 int l3d_collinearity(l3d_ctx* ctx, const float* segments, int n, float collin_s,
                      const l3d_collin_pair** pairs, size_t* count);
 
+/* ---- collinearity for callers that must not allocate.  No counterpart in the reference.
+ *
+ *      Who needs it: a host program that hands out its whole GPU memory budget at start-up
+ *      and forbids (or cannot survive) later device allocations -- a long-running
+ *      reconstruction service sharing the card with other components, or a frame loop with
+ *      a latency bound, for which cudaMalloc/cudaFree are unacceptable because they
+ *      synchronise the device for an unbounded time and may fail once the card is full.
+ *      l3d_collinearity grows context-owned buffers with cudaMalloc; this variant allocates
+ *      nothing, ever: its working memory is a fixed array compiled into the library
+ *      (about 2.1 MB of device memory on every GPU that loads the library, held until the
+ *      process exits), and inputs and outputs are the caller's own DEVICE buffers.
+ *
+ *      d_segments  n x 4 floats on the device          d_pairs   room for `capacity` records
+ *      d_count     one int on the device: receives the number of collinear pairs found.  If
+ *                  it exceeds `capacity`, only the first `capacity` records (in (i, j) order)
+ *                  were written.
+ *      cuda_stream a cudaStream_t (NULL = default stream); the work is enqueued, not waited for.
+ *      err/err_len optional buffer for a message when the return value is non-zero.
+ *
+ *      Limit: n <= 4096 segments per image; larger inputs are refused with return code 2
+ *      (the reference's own detector cap is 3000, commons.h:44).
+ *      The first call on each device looks up the device address of the built-in array
+ *      (cudaGetSymbolAddress) with that device current; make that first call during
+ *      start-up, before any stream capture is begun.  All calls on a device share the one
+ *      array and it keeps whatever the previous call left in it (the part that has to start
+ *      from zero is cleared by each call); two calls whose GPU work overlaps in time -- on
+ *      different streams or from different threads -- race on it and must be serialised by
+ *      the caller.  Results are identical to l3d_collinearity. */
+int l3d_collinearity_prealloc(const float* d_segments, int n, float collin_s, l3d_collin_pair* d_pairs, int capacity,
+                              int* d_count, void* cuda_stream, char* err, size_t err_len);
+
 /* ---- scene tables: what line3D.cc:738-803 packs per view, uploaded once for all views.
  *      Matrices are row-major.  The float tables are the reference's double values cast
  *      to float (line3D.cc:745-763, 790); the double ones feed l3d_unproject. */

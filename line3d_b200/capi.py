@@ -64,6 +64,8 @@ def lib():
         L.l3d_destroy.restype = None; L.l3d_destroy.argtypes = [vp]
         L.l3d_last_error.restype = C.c_char_p; L.l3d_last_error.argtypes = [vp]
         L.l3d_collinearity.restype = C.c_int; L.l3d_collinearity.argtypes = [vp, vp, C.c_int, C.c_float, C.POINTER(vp), C.POINTER(C.c_size_t)]
+        L.l3d_collinearity_prealloc.restype = C.c_int
+        L.l3d_collinearity_prealloc.argtypes = [vp, C.c_int, C.c_float, vp, C.c_int, vp, vp, C.c_char_p, C.c_size_t]
         L.l3d_set_views.restype = C.c_int; L.l3d_set_views.argtypes = [vp, C.c_int, C.POINTER(View)]
         for f in (L.l3d_match_view, L.l3d_match_view_resident):
             f.restype = C.c_int; f.argtypes = [vp, C.c_int, C.c_int, C.POINTER(Neighbor), C.c_float, C.c_float, C.POINTER(MatchResult)]
@@ -80,7 +82,7 @@ def lib():
     return _lib
 
 
-EXPORTS = ["l3d_create", "l3d_destroy", "l3d_last_error", "l3d_collinearity", "l3d_set_views", "l3d_match_view",
+EXPORTS = ["l3d_create", "l3d_destroy", "l3d_last_error", "l3d_collinearity", "l3d_collinearity_prealloc", "l3d_set_views", "l3d_match_view",
            "l3d_match_view_resident", "l3d_plan_matching", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
            "l3d_last_timings", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math", "l3d_flush_l2"]
 

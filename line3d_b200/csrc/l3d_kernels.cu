@@ -840,6 +840,54 @@ __global__ void k_collin_fill(const float4* __restrict__ segs, int n, float sigm
 }
 
 // ------------------------------------------------------------------------------------------
+// Collinearity without any allocation (l3d_collinearity_prealloc).
+//
+// Some programs that embed this library are not allowed to allocate device memory while
+// they run: a reconstruction service that reserves its whole GPU budget at start-up and
+// treats any later cudaMalloc as a fault, or a frame loop with a latency bound, where
+// cudaMalloc / cudaFree would stall the device for an unpredictable time (both synchronise
+// it) and can fail outright once the host application has filled the card.  For them the
+// per-image collinearity pass gets a second entry point whose working memory (the pair
+// bitmask, the per-row counts and their prefix sums) is this fixed array, part of the
+// library image on every GPU that loads it, instead of buffers grown with cudaMalloc.
+// The price is a hard upper limit on the number of segments per image.
+// ------------------------------------------------------------------------------------------
+constexpr int PREALLOC_MAX_SEGMENTS = 4096;
+constexpr int PREALLOC_WPR = PREALLOC_MAX_SEGMENTS / 32;
+constexpr size_t PREALLOC_BITS_WORDS = size_t(PREALLOC_MAX_SEGMENTS) * PREALLOC_WPR;          // 2 MiB of pair bits
+constexpr size_t PREALLOC_CNT_OFF = PREALLOC_BITS_WORDS;                                      // n + 1 counts
+constexpr size_t PREALLOC_OFF_OFF = PREALLOC_CNT_OFF + PREALLOC_MAX_SEGMENTS + 32;            // n + 2 offsets
+constexpr size_t PREALLOC_WORDS = PREALLOC_OFF_OFF + PREALLOC_MAX_SEGMENTS + 32;
+static __device__ __align__(256) unsigned int g_prealloc_scratch[PREALLOC_WORDS];
+
+// like k_collin_fill, but never writes past `capacity` records and also reports the total
+__global__ void k_collin_fill_capped(const float4* __restrict__ segs, int n, float sigma_sqr, const int* __restrict__ off, const unsigned* __restrict__ bits,
+                                     int wpr, l3d_collin_pair* __restrict__ out, int capacity, int* __restrict__ total_out)
+{
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i == 0 && lane == 0 && total_out) *total_out = off[n];
+    if (i >= n) return;
+    int o = off[i];
+    if (off[i + 1] == o) return;
+    const float4 a = segs[i];
+    for (int w0 = 0; w0 < wpr; w0 += 32) {
+        unsigned m = (w0 + lane < wpr) ? bits[size_t(i) * wpr + w0 + lane] : 0u;
+        int c = __popc(m), ex = c;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { int y = __shfl_up_sync(0xffffffffu, ex, s); if (lane >= s) ex += y; }
+        int tot = __shfl_sync(0xffffffffu, ex, 31);
+        int pos = o + ex - c;
+        while (m) {
+            int b = __ffs(m) - 1; m &= m - 1;
+            int j = (w0 + lane) * 32 + b;
+            if (pos < capacity) { l3d_collin_pair p; p.i = i; p.j = j; p.value = xcollinearity(a, segs[j], sigma_sqr); out[pos] = p; }
+            ++pos;
+        }
+        o += tot;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // hypotheses (view.cc:302-342) and affinity (line3D.cc:1600-1691), FP64
 // ------------------------------------------------------------------------------------------
 struct ViewD { double RtKinv[9]; double C[3]; float k_lower, k_upper; int seg_off; int n_seg; };
@@ -1506,6 +1554,51 @@ int l3d_collinearity(l3d_ctx* ctx, const float* segments, int n, float collin_s,
     L3D_CUDA(cudaMemcpyAsync(ctx->h_cpairs.p, ctx->d_cpairs.p, sizeof(l3d_collin_pair) * size_t(total), cudaMemcpyDeviceToHost, st));
     L3D_CUDA(cudaStreamSynchronize(st));
     *pairs = ctx->h_cpairs.p; *count = size_t(total);
+    return 0;
+}
+
+int l3d_collinearity_prealloc(const float* d_segments, int n, float collin_s, l3d_collin_pair* d_pairs, int capacity,
+                              int* d_count, void* cuda_stream, char* err, size_t err_len)
+{
+    // No cudaMalloc, cudaFree, cudaMallocAsync or any other allocating call may appear in this function.
+    auto fail = [&](int code, const char* msg) { if (err && err_len) snprintf(err, err_len, "l3d_collinearity_prealloc: %s", msg); return code; };
+    if (n < 0 || capacity < 0 || (n > 0 && !d_segments) || (capacity > 0 && !d_pairs) || !d_count) return fail(1, "null or negative argument");
+    if (n > PREALLOC_MAX_SEGMENTS) {
+        char b[160]; snprintf(b, sizeof b, "%d segments exceed the built-in limit of %d (use l3d_collinearity, which allocates)", n, PREALLOC_MAX_SEGMENTS);
+        return fail(2, b);
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    // Set-up, once per device and with that device current: the array's name is only a host-side handle for the
+    // symbol, the kernels need its address in device memory.
+    static unsigned int* scratch_of_device[64] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) return fail(3, e != cudaSuccess ? cudaGetErrorString(e) : "device index out of range");
+    unsigned int* scratch = scratch_of_device[dev];
+    if (!scratch) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_prealloc_scratch);
+        if (e != cudaSuccess || !p) return fail(4, e != cudaSuccess ? cudaGetErrorString(e) : "cudaGetSymbolAddress returned null");
+        scratch = static_cast<unsigned int*>(p);
+        scratch_of_device[dev] = scratch;
+    }
+    unsigned* bits = scratch;
+    int* cnt = reinterpret_cast<int*>(scratch + PREALLOC_CNT_OFF);
+    int* off = reinterpret_cast<int*>(scratch + PREALLOC_OFF_OFF);
+    if (n <= 1) {
+        e = cudaMemsetAsync(d_count, 0, sizeof(int), st);
+        return e == cudaSuccess ? 0 : fail(5, cudaGetErrorString(e));
+    }
+    const int wpr = (n + 31) / 32;
+    const float s2 = collin_s * collin_s;                                       // cudawrapper.cu:850
+    // the counts are accumulated with atomicAdd and must start from zero; the bitmask is fully rewritten
+    e = cudaMemsetAsync(cnt, 0, sizeof(int) * (size_t(n) + 1), st);
+    if (e != cudaSuccess) return fail(5, cudaGetErrorString(e));
+    k_collin_count<<<dim3((wpr + 63) / 64, n), 64, 0, st>>>(reinterpret_cast<const float4*>(d_segments), n, s2, cnt, bits, wpr);
+    k_scan_small<<<1, SCAN_T, 0, st>>>(cnt, off, n);
+    k_collin_fill_capped<<<(n * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(d_segments), n, s2, off, bits, wpr, d_pairs, capacity, d_count);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(6, cudaGetErrorString(e));
     return 0;
 }
 
