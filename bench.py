@@ -64,6 +64,16 @@ def scene_file(config: str, rank: int = 0) -> str:
     return path
 
 
+def multi_scene_file(config: str, n: int) -> str:
+    """n districts of the config in one scene (one connected component each): the job that is sharded over n GPUs."""
+    path = os.path.join(tempfile.gettempdir(), f"l3d_scene_{config}_x{n}.scn")
+    if not os.path.exists(path):
+        tmp = path + f".{os.getpid()}.tmp"
+        scenes.write_scene(scenes.multi_district(config, n), tmp)
+        os.replace(tmp, path)
+    return path
+
+
 def sample_scene_file(config: str) -> tuple[str, dict]:
     s = CPU_SAMPLE[config]
     full = scenes.read_scene(scene_file(config))
@@ -176,9 +186,16 @@ def ours(args) -> None:
     from line3d_b200 import capi, host
 
     c = scenes.CONFIGS[args.config]
-    path = scene_file(args.config, rank)
+    if world > 1:
+        if rank == 0:
+            multi_scene_file(args.config, world)      # written once, read by every rank
+        dist.barrier()
+        path = multi_scene_file(args.config, world)
+    else:
+        path = scene_file(args.config)
     params = dict(neighbors=c["k"], collinearity=False, diffusion=False)
     sess = host.Session(path, device=local, **params)
+    sess.set_shard(rank, world)                       # this rank's connected components of the neighbour graph
 
     def barrier():
         if dist is not None:
@@ -262,7 +279,7 @@ def ours(args) -> None:
     out = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * t_max,
                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
                config=dict(workload=f"{args.config}: {c['kw']['n_views']} views x ~{c['kw']['n_seg']} segments, k={c['k']}, no diffusion"
-                                    + (f", one such district per GPU ({world} districts)" if world > 1 else ""),
+                                    + (f"; {world} such districts in one scene, sharded by connected component over {world} GPUs" if world > 1 else ""),
                            pair_tests_per_step=int(tot_pairs), candidates_per_step=int(s["candidates"]), raw_matches_per_step=int(s["raw_matches"]),
                            scoring_iterations_per_step=int(s["score_iters"]), l2="flushed between steps (256 MiB memset); the per-step working set "
                            "(match lists of all views) is far larger than L2 anyway"),

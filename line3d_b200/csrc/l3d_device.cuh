@@ -255,13 +255,14 @@ __device__ inline float xhypothesis_confidence(V3 p1, V3 p2, V3 P1, V3 P2, V3 Q1
     float d1 = fmaxf(xdist_p2l(line2, p1), xdist_p2l(line2, p2));
     float d2 = fmaxf(xdist_p2l(line1, q1), xdist_p2l(line1, q2));
     float dist = fmaxf(d1, d2);
-    float angle = xangle_deg_3d(P1, P2, Q1, Q2);
     float sigma_sqr_a = xm(sigma_a, sigma_a), sigma_sqr_d = xm(sigma_p, sigma_p);
     // callers only use the value when it exceeds 0.5 (cudawrapper.cu:699); exp(-0.7) < 0.4966,
-    // so an exponent below -0.7 can never get there and the exponentials are skipped
+    // so an exponent below -0.7 can never get there: the angle and the exponentials are skipped
     float arg_d = xd(xm(-dist, dist), xm(2.0f, sigma_sqr_d));
+    if (arg_d < -0.7f) return 0.0f;
+    float angle = xangle_deg_3d(P1, P2, Q1, Q2);
     float arg_a = xd(xm(-angle, angle), xm(2.0f, sigma_sqr_a));
-    if (arg_d < -0.7f || arg_a < -0.7f) return 0.0f;
+    if (arg_a < -0.7f) return 0.0f;
     return fminf(xexpf(arg_d), xexpf(arg_a));
 }
 

@@ -520,11 +520,12 @@ constexpr int SC_QCAP = 128;       // per-warp queue of gate survivors
 struct ScoreParams { float sigma_p, sigma_a; };
 
 // work items: (source segment, chunk of SC_T matches); order is irrelevant to the result
-__global__ void k_score_items(const int* __restrict__ off, int n_cams, int n_src, int* __restrict__ counter, int2* __restrict__ items)
+__global__ void k_score_items(const int* __restrict__ off, int n_cams, int n_src, int m_lo, int m_hi, int* __restrict__ counter, int2* __restrict__ items)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n_src) return;
-    const int m = off[(row + 1) * n_cams] - off[row * n_cams];
+    int m = off[(row + 1) * n_cams] - off[row * n_cams];
+    if (m <= m_lo || m > m_hi) m = 0;        // not in this list's range
     const int n = (m + SC_T - 1) / SC_T;
     if (n == 0) return;
     const int base = atomicAdd(counter, n);
@@ -535,7 +536,7 @@ __global__ void k_score_items(const int* __restrict__ off, int n_cams, int n_src
 __device__ __forceinline__ void score_drain(int count, const unsigned* q, int lane, const float2* s_yd, int seg_start,
                                             const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
                                             V3 ray1, V3 ray2, V3 C, float spatial_k, const CamTable* __restrict__ cams,
-                                            const float4* __restrict__ segs, float sigma_p, float sigma_a, int* s_max)
+                                            const float4* __restrict__ segs, float sigma_p, float sigma_a, int* s_max, int stride = SC_T)
 {
     if (lane < count) {
         const unsigned e = q[lane];
@@ -549,7 +550,7 @@ __device__ __forceinline__ void score_drain(int count, const unsigned* q, int la
         V3 pr1 = xproject(ct.P, P1), pr2 = xproject(ct.P, P2);
         if (pr1.z == 1.0f && pr2.z == 1.0f) {
             float conf = xhypothesis_confidence(pr1, pr2, P1, P2, Q1, Q2, C, segs[ct.seg_off + id.z], sigma_p, sigma_a, spatial_k);
-            if (conf > 0.5f) atomicMax(&s_max[id.y * SC_T + yl], __float_as_int(conf));
+            if (conf > 0.5f) atomicMax(&s_max[id.y * stride + yl], __float_as_int(conf));
         }
     }
 }
@@ -646,6 +647,128 @@ __global__ void __launch_bounds__(SC_T) k_score(const float4* __restrict__ segs,
     float total = 0.0f;
     for (int c = 0; c < n_cams; ++c) total = xa(total, __int_as_float(s_max[c * SC_T + tid]));
     if (live) score[seg_start + y] = total;
+}
+
+// ------------------------------------------------------------------------------------------
+// scoring, sorted-window variant.  The superset gate of k_score is |d1_y - d1_i| <= thr1(y) and
+// |d2_y - d2_i| <= thr2(y).  If the segment's matches are sorted by d1, the partners of y that can
+// pass the first condition are one contiguous window, found by binary search: the quadratic walk
+// over all (y, i) pairs becomes O(M log M) + the window contents.  The set of pairs handed to the
+// exact evaluation is the same as in k_score (the same two fabsf tests are applied inside the
+// window), so the scores are bit-identical; only the order of evaluation changes, and the result
+// is a per-camera maximum, which does not depend on it.
+// One CTA per source segment with lo < M <= MP matches; the segment is sorted once in shared
+// memory (bitonic, key d1, payload d2 + camera + original index).
+// ------------------------------------------------------------------------------------------
+constexpr int SS_T = 256;
+
+// sorts the matches of every segment with m_lo < M <= MP by d1 and writes (d1, d2, camera << 20 | index)
+// to global arrays at the segment's own offsets
+template<int MP>
+__global__ void __launch_bounds__(SS_T) k_sort_segments(const int* __restrict__ off, int n_cams, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
+                                                        int m_lo, float* __restrict__ g_k, float* __restrict__ g_d2, unsigned* __restrict__ g_pl)
+{
+    extern __shared__ int s_sort[];
+    float* s_k = reinterpret_cast<float*>(s_sort);
+    float* s_d2 = s_k + MP;
+    unsigned* s_pl = reinterpret_cast<unsigned*>(s_d2 + MP);
+    const int row = blockIdx.x;
+    const int seg_start = off[row * n_cams], M = off[(row + 1) * n_cams] - seg_start;
+    if (M <= m_lo || M > MP) return;
+    const int tid = threadIdx.x;
+    int mp = 32; while (mp < M) mp <<= 1;
+    for (int i = tid; i < mp; i += SS_T) {
+        if (i < M) { float4 d = m_dep[seg_start + i]; s_k[i] = d.x; s_d2[i] = d.y; s_pl[i] = (unsigned(m_ids[seg_start + i].y) << 20) | unsigned(i); }
+        else { s_k[i] = INFINITY; s_d2[i] = 0.f; s_pl[i] = 0xffffffffu; }
+    }
+    __syncthreads();
+    for (int k = 2; k <= mp; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < mp; i += SS_T) {
+                const int l = i ^ j;
+                if (l > i) {
+                    const float a = s_k[i], b = s_k[l];
+                    const bool up = ((i & k) == 0);
+                    if ((a > b) == up) {
+                        s_k[i] = b; s_k[l] = a;
+                        const float t = s_d2[i]; s_d2[i] = s_d2[l]; s_d2[l] = t;
+                        const unsigned u = s_pl[i]; s_pl[i] = s_pl[l]; s_pl[l] = u;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    for (int i = tid; i < M; i += SS_T) { g_k[seg_start + i] = s_k[i]; g_d2[seg_start + i] = s_d2[i]; g_pl[seg_start + i] = s_pl[i]; }
+}
+
+// work items (segment, chunk of SC_T hypotheses) as in k_score; the partners of a hypothesis are the
+// window of the segment's d1-sorted list found by binary search
+__global__ void __launch_bounds__(SC_T) k_score_window(const float4* __restrict__ segs, const CamTable* __restrict__ cams, int n_cams, SrcTable src,
+                                                       const int* __restrict__ off, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
+                                                       const float* __restrict__ g_k, const float* __restrict__ g_d2, const unsigned* __restrict__ g_pl,
+                                                       const int2* __restrict__ items, const int* __restrict__ n_items,
+                                                       ScoreParams sp, float* __restrict__ score)
+{
+    extern __shared__ int s_max[];                 // [n_cams][SC_T]
+    __shared__ float2 s_yd[SC_T];
+    __shared__ unsigned s_q[SC_WARPS][SC_QCAP];
+    if (int(blockIdx.x) >= *n_items) return;
+    const int2 item = items[blockIdx.x];
+    const int row = item.x;
+    const int seg_start = off[row * n_cams], M = off[(row + 1) * n_cams] - seg_start;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int y = item.y * SC_T + tid;
+    const bool live = y < M;
+    int my_cam = -1; float2 my_d = make_float2(0.f, 0.f);
+    if (live) { my_cam = m_ids[seg_start + y].y; float4 d = m_dep[seg_start + y]; my_d = make_float2(d.x, d.y); }
+    s_yd[tid] = my_d;
+    for (int c = 0; c < n_cams; ++c) s_max[c * SC_T + tid] = 0;
+    const float4 sg = segs[src.seg_off + row];
+    const V3 p1 = mk3(sg.x, sg.y, 1.0f), p2 = mk3(sg.z, sg.w, 1.0f);
+    const V3 ray1 = xnormalize(xmat3(src.RtKinv, p1, false)), ray2 = xnormalize(xmat3(src.RtKinv, p2, false));
+    const V3 C = mk3(src.C[0], src.C[1], src.C[2]);
+    const float kk = src.spatial_k;
+    const float thr1 = (kk * fabsf(my_d.x) * 1.00001f + 2e-6f * (2.0f * fabsf(my_d.x) + src.cmax)) * 1.00001f;
+    const float thr2 = (kk * fabsf(my_d.y) * 1.00001f + 2e-6f * (2.0f * fabsf(my_d.y) + src.cmax)) * 1.00001f;
+    const float* K = g_k + seg_start; const float* D2 = g_d2 + seg_start; const unsigned* PL = g_pl + seg_start;
+    int j = 0, jend = 0;
+    if (live) {        // slightly widened window; the exact fabsf tests follow
+        const float lo = my_d.x - thr1 * 1.001f - 1e-30f, hi = my_d.x + thr1 * 1.001f + 1e-30f;
+        int a = 0, b = M;
+        while (a < b) { const int mid = (a + b) >> 1; if (K[mid] < lo) a = mid + 1; else b = mid; }
+        j = a; b = M;
+        while (a < b) { const int mid = (a + b) >> 1; if (K[mid] <= hi) a = mid + 1; else b = mid; }
+        jend = a;
+    }
+    __syncwarp();
+    unsigned* q = s_q[warp];
+    int qn = 0;
+    while (__any_sync(0xffffffffu, j < jend)) {
+        bool hit = false; unsigned pl = 0;
+        if (j < jend) {
+            pl = PL[j];
+            hit = (fabsf(my_d.x - K[j]) <= thr1) && (fabsf(my_d.y - D2[j]) <= thr2) && (int(pl >> 20) != my_cam);
+            ++j;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (m) {
+            if (hit) q[qn + __popc(m & ((1u << lane) - 1u))] = (unsigned(tid) << 24) | (pl & 0xfffffu);
+            qn += __popc(m);
+            __syncwarp();
+            if (qn >= 32) {
+                score_drain(32, q + (qn - 32), lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, kk, cams, segs, sp.sigma_p, sp.sigma_a, s_max);
+                qn -= 32;
+                __syncwarp();
+            }
+        }
+    }
+    if (qn > 0) score_drain(qn, q, lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, kk, cams, segs, sp.sigma_p, sp.sigma_a, s_max);
+    __syncwarp();
+    if (live) {        // sum of the per-camera best confidences in camera order (cudawrapper.cu:677-687, 709)
+        float total = 0.0f;
+        for (int c = 0; c < n_cams; ++c) total = xa(total, __int_as_float(s_max[c * SC_T + tid]));
+        score[seg_start + y] = total;
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1082,7 +1205,7 @@ struct l3d_ctx {
     DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
     DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
     DBuf<l3d_match> d_filtered;
-    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; DBuf<int> d_medrank;
+    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; bool sort_attr_set = false; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl;
     // phase A (pair tests) of the resident batch
     DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
     std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands;
@@ -1337,16 +1460,40 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_src) + 1)); L3D_CUDA(ctx->d_foff.ensure(size_t(n_src) + 2));
         L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2));
         L3D_CUDA(cudaMemsetAsync(ctx->d_iters.p, 0, 2 * sizeof(unsigned long long), st));
+        // segments with up to SORT_MAX matches are sorted by depth and scored through windows; longer ones
+        // (and everything when the 3-D gate is switched off) go through the tiled quadratic kernel
+        const int SORT_SMALL = 1024, SORT_MAX = 8192;
+        const bool windowed = src.spatial_k > 0.0f;
         const int max_items = int(M_ub / SC_T) + n_src + 1;
-        L3D_CUDA(ctx->d_items.ensure(size_t(max_items))); L3D_CUDA(ctx->d_nitems.ensure(1));
-        L3D_CUDA(cudaMemsetAsync(ctx->d_nitems.p, 0, sizeof(int), st));
-        k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_nitems.p, ctx->d_items.p);
+        L3D_CUDA(ctx->d_items.ensure(size_t(2 * max_items))); L3D_CUDA(ctx->d_nitems.ensure(2));
+        L3D_CUDA(cudaMemsetAsync(ctx->d_nitems.p, 0, 2 * sizeof(int), st));
         const size_t sm_bytes = size_t(n_nb) * SC_T * sizeof(int);
         if (sm_bytes > 160 * 1024) { ctx->err = "l3d_match_view: too many neighbours for the scoring kernel's shared memory"; return 1; }
-        if (sm_bytes > ctx->score_smem) { L3D_CUDA(cudaFuncSetAttribute(k_score, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_bytes))); ctx->score_smem = sm_bytes; }
-        k_score<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
-                                                  ctx->d_items.p, ctx->d_nitems.p, sp, ctx->d_score.p);
-        ctx->launches += 2;
+        if (sm_bytes > ctx->score_smem) {
+            L3D_CUDA(cudaFuncSetAttribute(k_score, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_bytes)));
+            L3D_CUDA(cudaFuncSetAttribute(k_score_window, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_bytes)));
+            ctx->score_smem = sm_bytes;
+        }
+        if (windowed) {
+            L3D_CUDA(ctx->d_sk.ensure(M_ub)); L3D_CUDA(ctx->d_sd2.ensure(M_ub)); L3D_CUDA(ctx->d_spl.ensure(M_ub));
+            if (!ctx->sort_attr_set) { L3D_CUDA(cudaFuncSetAttribute(k_sort_segments<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 12)); ctx->sort_attr_set = true; }
+            k_sort_segments<1024><<<n_src, SS_T, 1024 * 12, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, 0, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
+            ctx->launches += 1;
+            if (M_ub > size_t(SORT_SMALL)) {
+                k_sort_segments<8192><<<n_src, SS_T, 8192 * 12, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_SMALL, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
+                ctx->launches += 1;
+            }
+            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, 0, SORT_MAX, ctx->d_nitems.p, ctx->d_items.p);
+            k_score_window<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
+                                                             ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_items.p, ctx->d_nitems.p, sp, ctx->d_score.p);
+            ctx->launches += 2;
+        }
+        if (!windowed || M_ub > size_t(SORT_MAX)) {
+            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, windowed ? SORT_MAX : 0, 0x7fffffff, ctx->d_nitems.p + 1, ctx->d_items.p + max_items);
+            k_score<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
+                                                      ctx->d_items.p + max_items, ctx->d_nitems.p + 1, sp, ctx->d_score.p);
+            ctx->launches += 2;
+        }
         L3D_CUDA(cudaGetLastError());
         L3D_CUDA(cudaEventRecord(ctx->ev[4], st));
         // ---- reduce -----------------------------------------------------------------------
@@ -1512,7 +1659,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_cand.release(); ctx->d_cand_cnt.release(); ctx->d_cand_off.release(); ctx->d_tile_sums.release(); ctx->d_total.release();
     ctx->d_stage_col.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
-    ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release();
+    ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release();
     ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->h_res.release();
     for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_cams.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();

@@ -115,6 +115,7 @@ struct Line3D::Impl
     bool verbose, computation, use_collinearity, measure_only, flush_l2, keep_debug;
     std::string prefix, separator, data_directory;
     int matching_neighbors; float min_baseline, unc_upper, unc_lower, sigma_p, sigma_a;
+    int shard_rank, shard_world; std::set<unsigned> my_views;
     l3d_ctx* ctx;
 
     std::map<unsigned, ViewData*> views;
@@ -142,7 +143,7 @@ struct Line3D::Impl
     int cluster_nodes;
     L3DRunStats stats;
 
-    Impl() : ctx(0), cluster_nodes(0) { memset(&stats, 0, sizeof stats); }
+    Impl() : shard_rank(0), shard_world(1), ctx(0), cluster_nodes(0) { memset(&stats, 0, sizeof stats); }
 
     void fail(const char* what)
     {
@@ -290,6 +291,38 @@ struct Line3D::Impl
         }
     }
 
+    // Deal the connected components of the (undirected) neighbour graph out to the ranks.
+    void assignShard()
+    {
+        my_views.clear();
+        std::map<unsigned, std::set<unsigned> > adj;
+        for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it)
+            for (size_t k = 0; k < it->second.size(); ++k) { adj[it->first].insert(it->second[k]); adj[it->second[k]].insert(it->first); }
+        std::map<unsigned, int> comp; std::vector<double> cost; std::vector<std::vector<unsigned> > members;
+        for (std::map<unsigned, std::set<unsigned> >::iterator it = adj.begin(); it != adj.end(); ++it) {
+            if (comp.count(it->first)) continue;
+            const int c = int(cost.size()); cost.push_back(0.0); members.push_back(std::vector<unsigned>());
+            std::vector<unsigned> stack(1, it->first); comp[it->first] = c;
+            while (!stack.empty()) {
+                const unsigned v = stack.back(); stack.pop_back();
+                members[c].push_back(v);
+                std::map<unsigned, std::vector<unsigned> >::iterator nv = vn.find(v);
+                if (nv != vn.end()) for (size_t k = 0; k < nv->second.size(); ++k) cost[c] += double(views[v]->segs.size()) * double(views[nv->second[k]]->segs.size());
+                for (std::set<unsigned>::iterator n = adj[v].begin(); n != adj[v].end(); ++n) if (!comp.count(*n)) { comp[*n] = c; stack.push_back(*n); }
+            }
+        }
+        std::vector<int> order(cost.size());
+        for (size_t c = 0; c < order.size(); ++c) order[c] = int(c);
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return cost[a] > cost[b]; });
+        std::vector<double> load(size_t(std::max(shard_world, 1)), 0.0);
+        for (size_t k = 0; k < order.size(); ++k) {
+            size_t best = 0;
+            for (size_t r = 1; r < load.size(); ++r) if (load[r] < load[best]) best = r;
+            load[best] += cost[order[k]];
+            if (int(best) == shard_rank) my_views.insert(members[order[k]].begin(), members[order[k]].end());
+        }
+    }
+
     // line3D.cc:552-617, 1694-1779
     void transformGeometry()
     {
@@ -396,7 +429,7 @@ struct Line3D::Impl
             std::map<unsigned, std::set<unsigned> > done;
             for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it) {
                 const unsigned vid = it->first;
-                if (it->second.empty()) continue;
+                if (it->second.empty() || !my_views.count(vid)) continue;
                 std::vector<l3d_neighbor>& nb = schedule[vid];
                 nb.resize(it->second.size());
                 for (size_t c = 0; c < it->second.size(); ++c) {
@@ -424,7 +457,7 @@ struct Line3D::Impl
         for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it) {
             const unsigned vid = it->first;
             std::cout << prefix << "matching image [" << vid << "] with " << it->second.size() << " VNs" << std::endl;
-            if (it->second.empty()) continue;
+            if (it->second.empty() || !my_views.count(vid)) continue;
             ViewData* v = views[vid];
             std::vector<l3d_neighbor>& nb = schedule[vid];
             l3d_match_result res;
@@ -834,6 +867,7 @@ void Line3D::compute3Dmodel(bool perform_diffusion)                             
     const uint64_t launches0 = l3d_kernel_launches(d.ctx);
     const double t0 = now_s();
     d.findVisualNeighbors();
+    d.assignShard();
     d.transformGeometry();
     d.stats.t_neighbors = now_s() - t0;
     double t1 = now_s();
@@ -857,6 +891,7 @@ L3DRunStats Line3D::runStats() const { return impl_->stats; }
 void Line3D::setMeasureOnly(bool on) { impl_->measure_only = on; }
 void Line3D::setFlushL2(bool on) { impl_->flush_l2 = on; }
 void Line3D::setKeepDebug(bool on) { impl_->keep_debug = on; }
+void Line3D::setShard(int rank, int world) { impl_->shard_world = world < 1 ? 1 : world; impl_->shard_rank = (rank < 0 || rank >= impl_->shard_world) ? 0 : rank; }
 
 float4 Line3D::getSegment2D(L3D::L3DSegment2D& seg2D)                            // line3D.cc:2004-2013, view.cc:275-288
 {

@@ -132,6 +132,10 @@ namespace L3D
         void setMeasureOnly(bool on);
         // flush the GPU's L2 before the matching phase of every compute3Dmodel() (measurement only)
         void setFlushL2(bool on);
+        // Multi-GPU: process only this rank's share of the views.  The neighbour graph's connected components are
+        // independent of each other, so they are dealt out whole (largest first, to the least loaded rank); all ranks
+        // must have added the same images.  rank 0 / world 1 = everything.
+        void setShard(int rank, int world);
         // keep the per-match records debugDump() writes (off by default: they are large)
         void setKeepDebug(bool on);
 

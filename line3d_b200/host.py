@@ -38,6 +38,7 @@ def lib():
         L.l3dhost_open.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
         L.l3dhost_compute.restype = C.c_int
         L.l3dhost_compute.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.l3dhost_set_shard.restype = C.c_int; L.l3dhost_set_shard.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.l3dhost_dump.restype = C.c_int; L.l3dhost_dump.argtypes = [C.c_void_p, C.c_char_p]
         L.l3dhost_close.restype = None; L.l3dhost_close.argtypes = [C.c_void_p]
         _lib = L
@@ -67,6 +68,9 @@ class Session:
             raise capi.L3DError(f"l3dhost_compute failed with code {n}")
         stats = dict(zip(STAT_NAMES, [float(x) for x in st]))
         return n, dict(add_image=wall[0], compute3Dmodel=wall[1]), stats
+
+    def set_shard(self, rank: int, world: int):
+        lib().l3dhost_set_shard(self._h, int(rank), int(world))
 
     def dump(self) -> dict:
         d = tempfile.mkdtemp(prefix="l3d_dump_")

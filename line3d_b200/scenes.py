@@ -383,6 +383,24 @@ CONFIGS = {
 }
 
 
+def multi_district(config: str, n: int, spacing: float = 260.0) -> Scene:
+    """n independent districts of the named configuration in one scene: district d is generated with its own
+    seed, moved by a world-space offset (cameras only; image measurements are unchanged by a rigid move of the
+    whole district), its view ids are offset by d * V and its worldpoint ids by d * 10^6, so the districts share
+    no worldpoints and form separate connected components of the neighbour graph."""
+    c = CONFIGS[config]
+    out = Scene(name=f"{config}x{n}")
+    for d in range(n):
+        kw = dict(c["kw"]); kw["seed"] = kw["seed"] + 100 * d
+        sc = c["fn"](**kw)
+        T = np.array([spacing * (d % 4), spacing * (d // 4), 0.0])
+        nv = len(sc.views)
+        for v in sc.views:
+            t = v.t - v.R @ T                      # C' = C + T  ->  t' = -R C'
+            out.views.append(View(v.id + d * nv, v.width, v.height, v.K, v.R, t, v.segs, (v.wps.astype(np.uint64) + d * 1000000).astype(np.uint32)))
+    return out
+
+
 def make(config: str) -> Scene:
     c = CONFIGS[config]
     return c["fn"](**c["kw"])

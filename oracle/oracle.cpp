@@ -16,6 +16,7 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
+#include <functional>
 #include <list>
 #include <map>
 #include <set>
@@ -945,15 +946,42 @@ struct Pipeline {
         for (std::map<Seg2D, std::pair<V3, V3> >::iterator it = t3.begin(); it != t3.end(); ++it) fl.s2.push_back(it->first);
     }
 
+    // Not in the reference: multi-process sharding by connected component of the neighbour graph (DESIGN.md
+    // section 5).  Components are dealt out whole, most expensive first, to the least loaded rank.
+    int shard_rank = 0, shard_world = 1;
+    std::set<unsigned> shard_views()
+    {
+        std::map<unsigned, unsigned> root;                                   // union-find over view ids
+        std::function<unsigned(unsigned)> find = [&](unsigned x) { while (root[x] != x) x = root[x] = root[root[x]]; return x; };
+        for (auto& a : vn) { if (!root.count(a.first)) root[a.first] = a.first; for (auto& b : a.second) if (!root.count(b.first)) root[b.first] = b.first; }
+        for (auto& a : vn) for (auto& b : a.second) { unsigned x = find(a.first), y = find(b.first); if (x != y) root[std::max(x, y)] = std::min(x, y); }
+        std::map<unsigned, double> cost; std::map<unsigned, std::vector<unsigned> > members;   // keyed by smallest view id of the component
+        for (auto& r : root) members[find(r.first)].push_back(r.first);
+        for (auto& a : vn) for (auto& b : a.second) cost[find(a.first)] += double(views[a.first]->segs.size()) * double(views[b.first]->segs.size());
+        std::vector<unsigned> order;
+        for (auto& m : members) order.push_back(m.first);
+        std::stable_sort(order.begin(), order.end(), [&](unsigned a, unsigned b) { return cost[a] > cost[b]; });
+        std::vector<double> load(size_t(shard_world), 0.0);
+        std::set<unsigned> mine;
+        for (unsigned c : order) {
+            size_t best = 0;
+            for (size_t r = 1; r < load.size(); ++r) if (load[r] < load[best]) best = r;
+            load[best] += cost[c];
+            if (int(best) == shard_rank) mine.insert(members[c].begin(), members[c].end());
+        }
+        return mine;
+    }
+
     // line3D.cc:345-374, 620-648, 888-896
     void compute_3d_model()
     {
         if (views.size() < 4) return;
         matched.clear(); potential.clear(); result.clear();
         find_visual_neighbors();
+        const std::set<unsigned> mine = shard_views();
         transform_geometry();
         for (std::map<unsigned, std::map<unsigned, bool> >::iterator it = vn.begin(); it != vn.end(); ++it) {
-            if (it->second.empty()) continue;
+            if (it->second.empty() || !mine.count(it->first)) continue;
             compute_fundamentals(it->first);
             perform_matching(it->first);
         }
@@ -1004,7 +1032,11 @@ void npy_f32(const std::string& p, const std::vector<float>& v, size_t cols) { w
 
 }  // namespace
 
+static int g_shard_rank = 0, g_shard_world = 1;
+
 extern "C" {
+
+void oracle_set_shard(int rank, int world) { g_shard_world = world < 1 ? 1 : world; g_shard_rank = (rank < 0 || rank >= g_shard_world) ? 0 : rank; }
 
 int oracle_run_scene(const char* scene_path, int neighbors, float unc_upper, float unc_lower, float sigma_p, float sigma_a,
                      float min_baseline, int collinearity, int diffusion, const char* dump_dir, int threads, double* timings, double* counters)
@@ -1019,6 +1051,7 @@ int oracle_run_scene(const char* scene_path, int neighbors, float unc_upper, flo
     if (pl.unc_upper <= pl.unc_lower) pl.unc_upper = pl.unc_lower + 1.0f;
     pl.sigma_p = sigma_p; pl.sigma_a = sigma_a; pl.min_baseline = min_baseline; pl.collin = collinearity != 0; pl.diffusion = diffusion != 0;
     pl.threads = threads < 1 ? 1 : threads;
+    pl.shard_rank = g_shard_rank; pl.shard_world = g_shard_world;
     auto t0 = std::chrono::steady_clock::now();
     for (size_t i = 0; i < sv.size(); ++i) pl.add_image(sv[i].id, sv[i].width, sv[i].height, sv[i].K, sv[i].R, sv[i].t, sv[i].segs, sv[i].wps);
     auto t1 = std::chrono::steady_clock::now();

@@ -29,6 +29,10 @@ int oracle_run_scene(const char* scene_path, int neighbors, float unc_upper, flo
                      float sigma_p, float sigma_a, float min_baseline, int collinearity, int diffusion,
                      const char* dump_dir, int threads, double* timings, double* counters);
 
+/* Multi-process sharding for the next oracle_run_scene calls: only the views of this rank's connected
+ * components of the neighbour graph are matched (not in the reference; mirrors Line3D::setShard). */
+void oracle_set_shard(int rank, int world);
+
 /* One pair test (cudawrapper.cu:538-611).  seg = p1x p1y p2x p2y; F, RtKinv row-major 3x3.
  * out[0..3] = depths (0 if rejected); out[4], out[5] = the two overlap values, or -1 if an
  * intersection was invalid.  Returns 1 if the overlap test accepted the pair. */

@@ -33,6 +33,7 @@ def lib():
         L.oracle_run_scene.restype = ctypes.c_int
         L.oracle_run_scene.argtypes = [ctypes.c_char_p, ctypes.c_int, _f, _f, _f, _f, _f, ctypes.c_int, ctypes.c_int,
                                        ctypes.c_char_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+        L.oracle_set_shard.restype = None; L.oracle_set_shard.argtypes = [ctypes.c_int, ctypes.c_int]
         L.oracle_pair_test.restype = ctypes.c_int
         L.oracle_pair_test.argtypes = [_vp] * 8
         L.oracle_match_pair.restype = ctypes.c_long
@@ -57,8 +58,9 @@ def _f32(a):
     return np.ascontiguousarray(a, dtype=np.float32)
 
 
-def run_scene(scene_path, dump_dir=None, threads=1, **params):
+def run_scene(scene_path, dump_dir=None, threads=1, shard=(0, 1), **params):
     p = dict(DEFAULTS); p.update(params)
+    lib().oracle_set_shard(int(shard[0]), int(shard[1]))
     tm = (ctypes.c_double * 5)(); ct = (ctypes.c_double * 5)()
     n = lib().oracle_run_scene(scene_path.encode(), int(p["neighbors"]), p["unc_upper"], p["unc_lower"], p["sigma_p"], p["sigma_a"],
                                p["min_baseline"], int(bool(p["collinearity"])), int(bool(p["diffusion"])),
