@@ -1,0 +1,89 @@
+"""GPU parity on the shapes of BASELINE.json's configs: C1 at full size against the oracle,
+the dense-neighbour (k = -1) and urban shapes at reduced size, and size-independent
+properties at a larger size where the oracle would take too long: run-to-run determinism and
+equality of the batched (l3d_plan_matching) and the view-by-view execution."""
+import tempfile
+
+import numpy as np
+import pytest
+
+import l3d_testutil as util
+
+pytestmark = pytest.mark.gpu
+
+
+def _pipeline_equal(scene_path, threads=16, **params):
+    from line3d_b200 import host
+    dm_o = util.oracle_dump(scene_path, threads=threads, **params)
+    n_g, tm, st, dm_g = host.run_scene(scene_path, tempfile.mkdtemp(), **params)
+    assert n_g == dm_o["_n_lines"]
+    for k in ("visual_neighbors", "match_log", "match_median", "best_match", "potential", "edges_cluster", "lines_seg2d"):
+        assert dm_o[k].shape == dm_g[k].shape, k
+        assert np.array_equal(dm_o[k], dm_g[k]), k
+    # a view with nothing left to pair-test returns its delivered records unscored: in delivery order in the reference
+    # (cudawrapper.cu:877-878), sorted by (src, cam, tgt) here -- compare as sets
+    fo, fg = dm_o["filtered_matches"], dm_g["filtered_matches"]
+    assert fo.shape == fg.shape
+    key = lambda a: np.lexsort((a[:, 3], a[:, 2], a[:, 1], a[:, 0]))
+    assert np.array_equal(fo[key(fo)], fg[key(fg)])
+    np.testing.assert_allclose(dm_g["lines_seg3d"], dm_o["lines_seg3d"], rtol=1e-9, atol=1e-9)
+    return n_g, st
+
+
+def test_c1_full_size(tmp_path):
+    """BASELINE.json configs[0]: 24 views, ~800 segments/view, k = 12 -- whole pipeline identical to the oracle."""
+    from line3d_b200 import scenes
+    p = str(tmp_path / "c1.scn")
+    scenes.write_scene(scenes.make("C1"), p)
+    n, st = _pipeline_equal(p, neighbors=12)
+    assert n > 50 and st["pair_tests"] > 5e7
+
+
+def test_dense_neighbours_reduced(tmp_path):
+    """configs[4] shape (all co-visible views are neighbours, k = -1) at 14 views x ~250 segments."""
+    from line3d_b200 import scenes
+    p = str(tmp_path / "dome.scn")
+    scenes.write_scene(scenes.dense_dome(n_views=14, n_seg=250, seed=1005), p)
+    _pipeline_equal(p, neighbors=-1)
+
+
+def test_urban_reduced_with_diffusion(tmp_path):
+    """configs[1]/[2] shape at 16 views x ~500 segments, with the diffusion step."""
+    from line3d_b200 import scenes
+    p = str(tmp_path / "urban.scn")
+    scenes.write_scene(scenes.urban(n_views=16, n_seg=500, seed=1002, blocks=(1, 1)), p)
+    _pipeline_equal(p, neighbors=6, diffusion=True)
+
+
+def test_batched_equals_view_by_view_and_is_deterministic(tmp_path):
+    """Larger urban slice (no oracle): the scaffold announces the schedule (batched pair tests), the plain C-ABI loop
+    does not; both must give the same filtered matches, and a second run the same again."""
+    from line3d_b200 import capi, host, scenes
+    p = str(tmp_path / "u.scn")
+    sc = scenes.urban(n_views=24, n_seg=1500, seed=1002, blocks=(2, 1))
+    scenes.write_scene(sc, p)
+    s = host.Session(p, neighbors=8, collinearity=False)
+    n1, _, st1 = s.compute(keep_debug=True); d1 = s.dump()
+    n2, _, st2 = s.compute(keep_debug=True); d2 = s.dump()
+    s.close()
+    # (a second compute3Dmodel re-normalises the already normalised scene, as in the reference, line3D.cc:364: the
+    # final lines then come back in the normalised frame -- only the matching results are compared between the runs)
+    assert n1 == n2 and np.array_equal(d1["filtered_matches"], d2["filtered_matches"]) and np.array_equal(d1["lines_seg2d"], d2["lines_seg2d"])
+    ids, views, F, vn = util.tables_from_dump(d1, sc)
+    ctx = capi.Context(0)
+    got = util.run_matching(ctx, ids, views, F, vn)
+    ctx.close()
+    rows = np.concatenate([util.filtered_as_rows(v, got[v]) for v in sorted(got)])
+    assert np.array_equal(rows, d1["filtered_matches"])
+    assert [got[v]["median_depth"] for v in sorted(got)] == [float(x) for x in d1["match_median"].ravel()]
+    assert sum(r["pair_tests"] for r in got.values()) == st1["pair_tests"]
+    # a raw match (v,i)->(n,j) delivered to n must show up there with mirrored depths if it survives: every filtered
+    # record of a view whose camera was processed earlier as a mutual neighbour stems from that view's filtered list
+    f = d1["filtered_matches"]
+    keys = {(int(r[0]), int(r[1]), int(r[2]), int(r[3])): r[4:8] for r in f}
+    checked = 0
+    for (v, i, n, j), dep in list(keys.items())[:20000]:
+        if n < v and (n, j, v, i) in keys:
+            assert np.array_equal(keys[(n, j, v, i)][[2, 3, 0, 1]], dep)
+            checked += 1
+    assert checked > 0
