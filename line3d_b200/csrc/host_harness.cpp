@@ -110,6 +110,14 @@ int l3dhost_compute(void* session, int diffusion, int measure_only, int flush_l2
     }
 }
 
+int l3dhost_reset_geometry(void* session)
+{
+    Session* s = static_cast<Session*>(session);
+    if (!s || !s->l3d) return -1;
+    s->l3d->resetGeometry();
+    return 0;
+}
+
 int l3dhost_set_shard(void* session, int rank, int world)
 {
     Session* s = static_cast<Session*>(session);

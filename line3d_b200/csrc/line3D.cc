@@ -39,7 +39,7 @@ struct CollinEntry { unsigned other; float w; };
 struct ViewData
 {
     unsigned id, width, height;
-    M3 K, Kinv, R, Rt, RtKinv; V3 t, C, pp; Eigen::MatrixXd P;
+    M3 K, Kinv, R, Rt, RtKinv, R0; V3 t, C, pp, t0; Eigen::MatrixXd P;
     float unc_upper_px, unc_lower_px, k_upper, k_lower, median_depth;
     std::vector<float4> segs;
     std::vector<std::vector<CollinEntry> > collin;     // per segment, ascending partner id (segments.h:82-98)
@@ -222,7 +222,7 @@ struct Line3D::Impl
         if (verbose) std::cout << prefix << "#segments: " << segs.size() << " (final)" << std::endl;
         ViewData* v = new ViewData();
         v->id = imageID; v->width = image.cols; v->height = image.rows;                              // line3D.cc:202-207
-        v->K = K; v->R = R; v->t = t; v->unc_upper_px = unc_upper; v->unc_lower_px = unc_lower;
+        v->K = K; v->R = R; v->t = t; v->R0 = R; v->t0 = t; v->unc_upper_px = unc_upper; v->unc_lower_px = unc_lower;
         v->segs.swap(segs); v->index = -1;
         buildCollinearity(v);
         v->init();
@@ -543,6 +543,7 @@ struct Line3D::Impl
         result.clear();
         std::cout << prefix << "computing affinity matrix..." << std::endl;
         const double t0 = now_s();
+        const bool prof = getenv("L3D_PROFILE") != 0; double tp = now_s();
         // potential correspondences per view: the records a view produced are already in (seg, cam, seg) order,
         // the ones it received are sorted here; both are merged and de-duplicated (a std::map in the reference)
         {
@@ -566,6 +567,7 @@ struct Line3D::Impl
             work(0, nt);
             for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
         }
+        if (prof) { std::cerr << "[prof] pc merge " << now_s() - tp << std::endl; tp = now_s(); }
         struct Cand { int a, b; float mult; float thr; };
         std::vector<Cand> cands;
         // dense numbering of every segment, for the "used" pair set
@@ -628,6 +630,7 @@ struct Line3D::Impl
             }
         }
         std::vector<uint64_t>().swap(used);
+        if (prof) { std::cerr << "[prof] enumerate " << now_s() - tp << " cands " << cands.size() << std::endl; tp = now_s(); }
         // similarities on the device (line3D.cc:1600-1691)
         std::vector<l3d_pair> pairs(cands.size());
         for (size_t k = 0; k < cands.size(); ++k) { pairs[k].a = cands[k].a; pairs[k].b = cands[k].b; }
@@ -636,6 +639,7 @@ struct Line3D::Impl
         for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) medians[it->second->index] = it->second->median_depth;
         if (!cands.empty() && l3d_affinity(ctx, medians.data(), pairs.size(), pairs.data(), sigma_a, sim.data())) fail("l3d_affinity");
         stats.affinity_pairs = cands.size();
+        if (prof) { std::cerr << "[prof] l3d_affinity " << now_s() - tp << std::endl; tp = now_s(); }
         // edges and node ids in encounter order (line3D.cc:1018-1060)
         std::vector<Edge> A;
         std::vector<int> node_of(hyps.size(), -1); std::vector<int> hyp_of_node;
@@ -649,6 +653,7 @@ struct Line3D::Impl
             Edge e = {node_of[c.a], node_of[c.b], w}; A.push_back(e);
             Edge r = {node_of[c.b], node_of[c.a], w}; A.push_back(r);
         }
+        if (prof) { std::cerr << "[prof] edges " << now_s() - tp << " A " << A.size() << std::endl; }
         stats.t_affinity += now_s() - t0;
         const int n_nodes = int(hyp_of_node.size());
         if (verbose) {
@@ -891,6 +896,10 @@ L3DRunStats Line3D::runStats() const { return impl_->stats; }
 void Line3D::setMeasureOnly(bool on) { impl_->measure_only = on; }
 void Line3D::setFlushL2(bool on) { impl_->flush_l2 = on; }
 void Line3D::setKeepDebug(bool on) { impl_->keep_debug = on; }
+void Line3D::resetGeometry()
+{
+    for (std::map<unsigned, ViewData*>::iterator it = impl_->views.begin(); it != impl_->views.end(); ++it) { it->second->R = it->second->R0; it->second->t = it->second->t0; it->second->init(); }
+}
 void Line3D::setShard(int rank, int world) { impl_->shard_world = world < 1 ? 1 : world; impl_->shard_rank = (rank < 0 || rank >= impl_->shard_world) ? 0 : rank; }
 
 float4 Line3D::getSegment2D(L3D::L3DSegment2D& seg2D)                            // line3D.cc:2004-2013, view.cc:275-288

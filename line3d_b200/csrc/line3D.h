@@ -132,6 +132,10 @@ namespace L3D
         void setMeasureOnly(bool on);
         // flush the GPU's L2 before the matching phase of every compute3Dmodel() (measurement only)
         void setFlushL2(bool on);
+        // Put every camera back to the pose it was added with.  compute3Dmodel() normalises the scene in place
+        // (line3D.cc:364) and, as in the reference, a second call would normalise the normalised scene again (with
+        // min_baseline then meaning something else); call this in between to repeat a run on identical input.
+        void resetGeometry();
         // Multi-GPU: process only this rank's share of the views.  The neighbour graph's connected components are
         // independent of each other, so they are dealt out whole (largest first, to the least loaded rank); all ranks
         // must have added the same images.  rank 0 / world 1 = everything.
