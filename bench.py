@@ -193,7 +193,7 @@ def ours(args) -> None:
         path = multi_scene_file(args.config, world)
     else:
         path = scene_file(args.config)
-    params = dict(neighbors=c["k"], collinearity=False, diffusion=False)
+    params = dict(neighbors=c["k"], collinearity=True, diffusion=c["diffusion"])      # the reference's defaults (commons.h:49, 61)
     sess = host.Session(path, device=local, **params)
     sess.set_shard(rank, world)                       # this rank's connected components of the neighbour graph
 

@@ -163,23 +163,27 @@ constexpr int SCAN_SMALL = 64 * 1024;
 __global__ void __launch_bounds__(SCAN_T) k_scan_small(const int* __restrict__ in, int* __restrict__ out /* n + 1 */, int n)
 {
     __shared__ int sh[32];
-    __shared__ int s_carry;
-    if (threadIdx.x == 0) s_carry = 0;
-    __syncthreads();
-    for (int base0 = 0; base0 < n; base0 += SCAN_TILE) {
-        const int base = base0 + threadIdx.x * SCAN_ITEMS;
-        int v[SCAN_ITEMS], s = 0;
+    int carry = 0;
+    // tiles of SCAN_TILE elements; the next tile's values are loaded before the current one is scanned
+    int v[SCAN_ITEMS], nx[SCAN_ITEMS];
+    int base = threadIdx.x * SCAN_ITEMS;
 #pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; ++k) { v[k] = (base + k < n) ? in[base + k] : 0; s += v[k]; }
+    for (int k = 0; k < SCAN_ITEMS; ++k) nx[k] = (base + k < n) ? in[base + k] : 0;
+    for (int base0 = 0; base0 < n; base0 += SCAN_TILE) {
+        base = base0 + threadIdx.x * SCAN_ITEMS;
+        int s = 0;
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; ++k) { v[k] = nx[k]; s += v[k]; }
+        const int nb = base + SCAN_TILE;
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; ++k) nx[k] = (nb + k < n) ? in[nb + k] : 0;
         int total;
-        int ex = block_exclusive_scan(s, &total, sh) + s_carry;
+        int ex = block_exclusive_scan(s, &total, sh) + carry;
 #pragma unroll
         for (int k = 0; k < SCAN_ITEMS; ++k) { if (base + k < n) out[base + k] = ex; ex += v[k]; }
-        __syncthreads();
-        if (threadIdx.x == 0) s_carry += total;
-        __syncthreads();
+        carry += total;
     }
-    if (threadIdx.x == 0) out[n] = s_carry;
+    if (threadIdx.x == 0) out[n] = carry;
 }
 __global__ void __launch_bounds__(SCAN_T) k_scan_add(int* __restrict__ out, const int* __restrict__ tile_sums, int n, const int* __restrict__ total)
 {
@@ -520,12 +524,13 @@ constexpr int SC_QCAP = 128;       // per-warp queue of gate survivors
 struct ScoreParams { float sigma_p, sigma_a; };
 
 // work items: (source segment, chunk of SC_T matches); order is irrelevant to the result
-__global__ void k_score_items(const int* __restrict__ off, int n_cams, int n_src, int m_lo, int m_hi, int* __restrict__ counter, int2* __restrict__ items)
+__global__ void k_score_items(const int* __restrict__ off, int n_cams, int n_src, int m_lo, int m_hi, int outside, int* __restrict__ counter, int2* __restrict__ items)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n_src) return;
     int m = off[(row + 1) * n_cams] - off[row * n_cams];
-    if (m <= m_lo || m > m_hi) m = 0;        // not in this list's range
+    const bool inside = m > m_lo && m <= m_hi;
+    if (inside == (outside != 0)) m = 0;     // this list takes the segments inside (m_lo, m_hi], or those outside it
     const int n = (m + SC_T - 1) / SC_T;
     if (n == 0) return;
     const int base = atomicAdd(counter, n);
@@ -846,7 +851,7 @@ __global__ void k_median_pick(const float* __restrict__ dsamples, int n, const i
     if (less[i] <= r && r < leq[i]) out[0] = v;
 }
 
-// filtered records in order, one warp per segment
+// filtered records in order, one warp per segment; four 32-match chunks per iteration keep several loads in flight
 __global__ void k_filter_fill(const int* __restrict__ off, int n_cams, int n_src, const float* __restrict__ score,
                               const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, const int* __restrict__ foff,
                               l3d_match* __restrict__ out)
@@ -856,19 +861,24 @@ __global__ void k_filter_fill(const int* __restrict__ off, int n_cams, int n_src
     const int s0 = off[row * n_cams], s1 = off[(row + 1) * n_cams];
     int o = foff[row];
     if (foff[row + 1] == o) return;
-    for (int k0 = s0; k0 < s1; k0 += 32) {
-        const int k = k0 + lane;
-        float c = (k < s1) ? score[k] : 0.0f;
-        bool keep = c > 1.0f;
-        unsigned m = __ballot_sync(0xffffffffu, keep);
-        if (keep) {
-            int r = o + __popc(m & ((1u << lane) - 1u));
-            int4 id = m_ids[k]; float4 d = m_dep[k];
-            l3d_match rec; rec.src_seg = id.x; rec.cam = id.y; rec.tgt_seg = id.z; rec.confidence = xd(c, 2.0f);
-            rec.depths[0] = d.x; rec.depths[1] = d.y; rec.depths[2] = d.z; rec.depths[3] = d.w;
-            out[r] = rec;
+    for (int k0 = s0; k0 < s1; k0 += 128) {
+        float c[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { const int k = k0 + 32 * u + lane; c[u] = (k < s1) ? score[k] : 0.0f; }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int k = k0 + 32 * u + lane;
+            const bool keep = c[u] > 1.0f;
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            if (keep) {
+                const int r = o + __popc(m & ((1u << lane) - 1u));
+                const int4 id = m_ids[k]; const float4 d = m_dep[k];
+                l3d_match rec; rec.src_seg = id.x; rec.cam = id.y; rec.tgt_seg = id.z; rec.confidence = xd(c[u], 2.0f);
+                rec.depths[0] = d.x; rec.depths[1] = d.y; rec.depths[2] = d.z; rec.depths[3] = d.w;
+                out[r] = rec;
+            }
+            o += __popc(m);
         }
-        o += __popc(m);
     }
 }
 // unscored variant (no neighbour to pair-test): all records, confidence 0
@@ -906,18 +916,23 @@ __global__ void k_deliver_scatter(const l3d_match* __restrict__ f, const int* __
     t_tgt[pos] = m.src_seg;
     t_dep[pos] = make_float4(m.depths[2], m.depths[3], m.depths[0], m.depths[1]);     // line3D.cc:852-855
 }
-// each group is tiny; order it by target id (unique within a group)
-__global__ void k_deliver_sort(const int* __restrict__ start, int n_keys, int* __restrict__ t_tgt, float4* __restrict__ t_dep)
+// the scatter above is unordered within a group; every record finds its place by counting the group members with a
+// smaller target id (ids are unique within a group, groups are tiny) and is copied to the final arrays
+__global__ void k_deliver_place(const int* __restrict__ start, int n_keys, const int* __restrict__ tmp_tgt, const float4* __restrict__ tmp_dep,
+                                int* __restrict__ t_tgt, float4* __restrict__ t_dep)
 {
-    const int key = blockIdx.x * blockDim.x + threadIdx.x;
-    if (key >= n_keys) return;
-    const int a = start[key], b = start[key + 1];
-    for (int i = a + 1; i < b; ++i) {
-        int t = t_tgt[i]; float4 d = t_dep[i];
-        int j = i - 1;
-        while (j >= a && t_tgt[j] > t) { t_tgt[j + 1] = t_tgt[j]; t_dep[j + 1] = t_dep[j]; --j; }
-        t_tgt[j + 1] = t; t_dep[j + 1] = d;
-    }
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    const int total = start[n_keys];
+    if (k >= total) return;
+    // group of record k: largest key with start[key] <= k
+    int lo = 0, hi = n_keys - 1;
+    while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (start[mid] <= k) lo = mid; else hi = mid - 1; }
+    const int a = start[lo], b = start[lo + 1];
+    const int me = tmp_tgt[k];
+    int rank = 0;
+    for (int i = a; i < b; ++i) rank += (tmp_tgt[i] < me);
+    t_tgt[a + rank] = me;
+    t_dep[a + rank] = tmp_dep[k];
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1205,7 +1220,7 @@ struct l3d_ctx {
     DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
     DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
     DBuf<l3d_match> d_filtered;
-    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; bool sort_attr_set = false; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl;
+    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; bool sort_attr_set = false; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl; DBuf<int> d_dl_tgt; DBuf<float4> d_dl_dep;
     // phase A (pair tests) of the resident batch
     DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
     std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands;
@@ -1460,9 +1475,10 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_src) + 1)); L3D_CUDA(ctx->d_foff.ensure(size_t(n_src) + 2));
         L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2));
         L3D_CUDA(cudaMemsetAsync(ctx->d_iters.p, 0, 2 * sizeof(unsigned long long), st));
-        // segments with up to SORT_MAX matches are sorted by depth and scored through windows; longer ones
-        // (and everything when the 3-D gate is switched off) go through the tiled quadratic kernel
-        const int SORT_SMALL = 1024, SORT_MAX = 8192;
+        // Segments with SORT_MIN < M <= SORT_MAX matches are sorted by depth and scored through windows; shorter ones
+        // (a sort costs more than their few pairs), longer ones (do not fit the sort's shared memory) and everything
+        // when the 3-D gate is switched off go through the tiled quadratic kernel.
+        const int SORT_MIN = 0, SORT_SMALL = 1024, SORT_MAX = 8192;
         const bool windowed = src.spatial_k > 0.0f;
         const int max_items = int(M_ub / SC_T) + n_src + 1;
         L3D_CUDA(ctx->d_items.ensure(size_t(2 * max_items))); L3D_CUDA(ctx->d_nitems.ensure(2));
@@ -1474,22 +1490,23 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
             L3D_CUDA(cudaFuncSetAttribute(k_score_window, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_bytes)));
             ctx->score_smem = sm_bytes;
         }
-        if (windowed) {
+        if (windowed && M_ub > size_t(SORT_MIN)) {
             L3D_CUDA(ctx->d_sk.ensure(M_ub)); L3D_CUDA(ctx->d_sd2.ensure(M_ub)); L3D_CUDA(ctx->d_spl.ensure(M_ub));
             if (!ctx->sort_attr_set) { L3D_CUDA(cudaFuncSetAttribute(k_sort_segments<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 12)); ctx->sort_attr_set = true; }
-            k_sort_segments<1024><<<n_src, SS_T, 1024 * 12, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, 0, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
+            k_sort_segments<1024><<<n_src, SS_T, 1024 * 12, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_MIN, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
             ctx->launches += 1;
             if (M_ub > size_t(SORT_SMALL)) {
                 k_sort_segments<8192><<<n_src, SS_T, 8192 * 12, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_SMALL, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
                 ctx->launches += 1;
             }
-            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, 0, SORT_MAX, ctx->d_nitems.p, ctx->d_items.p);
+            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, SORT_MIN, SORT_MAX, 0, ctx->d_nitems.p, ctx->d_items.p);
             k_score_window<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
                                                              ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_items.p, ctx->d_nitems.p, sp, ctx->d_score.p);
             ctx->launches += 2;
         }
-        if (!windowed || M_ub > size_t(SORT_MAX)) {
-            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, windowed ? SORT_MAX : 0, 0x7fffffff, ctx->d_nitems.p + 1, ctx->d_items.p + max_items);
+        {
+            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, windowed ? SORT_MIN : 0x7fffffff, windowed ? SORT_MAX : 0x7fffffff, 1,
+                                                              ctx->d_nitems.p + 1, ctx->d_items.p + max_items);
             k_score<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
                                                       ctx->d_items.p + max_items, ctx->d_nitems.p + 1, sp, ctx->d_score.p);
             ctx->launches += 2;
@@ -1538,8 +1555,9 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         if (M_ub > 0) { k_deliver_hist<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, ctx->d_hist.p); ctx->launches += 1; }
         if (scan_exclusive(ctx, ctx->d_hist.p, buf.start, n_keys)) return 1;
         if (M_ub > 0) {
-            k_deliver_scatter<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, buf.start, ctx->d_cursor.p, buf.tgt, buf.dep);
-            k_deliver_sort<<<(n_keys + 255) / 256, 256, 0, st>>>(buf.start, n_keys, buf.tgt, buf.dep);
+            L3D_CUDA(ctx->d_dl_tgt.ensure(M_ub)); L3D_CUDA(ctx->d_dl_dep.ensure(M_ub));
+            k_deliver_scatter<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, buf.start, ctx->d_cursor.p, ctx->d_dl_tgt.p, ctx->d_dl_dep.p);
+            k_deliver_place<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(buf.start, n_keys, ctx->d_dl_tgt.p, ctx->d_dl_dep.p, buf.tgt, buf.dep);
             ctx->launches += 2;
         }
         L3D_CUDA(cudaGetLastError());
@@ -1659,7 +1677,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_cand.release(); ctx->d_cand_cnt.release(); ctx->d_cand_off.release(); ctx->d_tile_sums.release(); ctx->d_total.release();
     ctx->d_stage_col.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
-    ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release();
+    ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release();
     ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->h_res.release();
     for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_cams.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();

@@ -583,11 +583,15 @@ struct Line3D::Impl
             out = view_base[vidx] + seg; return true;
         };
         // set of unordered segment pairs already looked at (line3D.cc:980, 1001-1005): open addressing
-        std::vector<uint64_t> used(size_t(1) << 16, ~uint64_t(0)); size_t used_n = 0;
+        size_t pc_total = 0;
+        for (size_t v = 0; v < pc.size(); ++v) pc_total += pc[v].size();
+        size_t cap = size_t(1) << 16;
+        while (cap < pc_total * 3) cap <<= 1;
+        std::vector<uint64_t> used(cap, ~uint64_t(0)); size_t used_n = 0;
         auto mark = [&](uint64_t a, uint64_t b) -> bool {   // true if the pair was new
             const uint64_t key = std::min(a, b) * total + std::max(a, b);
             if ((used_n + 1) * 2 > used.size()) {
-                std::vector<uint64_t> bigger(used.size() * 4, ~uint64_t(0));
+                std::vector<uint64_t> bigger(used.size() * 2, ~uint64_t(0));
                 for (size_t k = 0; k < used.size(); ++k) if (used[k] != ~uint64_t(0)) {
                     size_t h = size_t((used[k] * 0x9E3779B97F4A7C15ull) >> 20) & (bigger.size() - 1);
                     while (bigger[h] != ~uint64_t(0)) h = (h + 1) & (bigger.size() - 1);
@@ -600,12 +604,29 @@ struct Line3D::Impl
             used[h] = key; ++used_n; return true;
         };
         std::vector<size_t> cursor(view_at.size(), 0);
+        auto slot_of = [&](uint64_t a, uint64_t b) -> size_t {
+            const uint64_t key = std::min(a, b) * total + std::max(a, b);
+            return size_t((key * 0x9E3779B97F4A7C15ull) >> 20) & (used.size() - 1);
+        };
         for (size_t hidx = 0; hidx < hyps.size(); ++hidx) {
             const Hypothesis& C = hyps[hidx];
             int svi; uint64_t dsrc; if (!dense(C.cam, C.seg, svi, dsrc)) continue;
             const std::vector<PC>& list = pc[svi];
             size_t& cur = cursor[svi];
             while (cur < list.size() && list[cur].seg < C.seg) ++cur;
+            // the pair set is far larger than the caches: touch the slots this turn may need before walking them in order
+            for (size_t k = cur; k < list.size() && list[k].seg == C.seg; ++k) {
+                int tvi; uint64_t dt;
+                if (!dense(list[k].tcam, list[k].tseg, tvi, dt)) continue;
+                __builtin_prefetch(&used[slot_of(dsrc, dt)]);
+                if (hyp_of[tvi][list[k].tseg] < 0) continue;
+                const std::vector<CollinEntry>& cl = view_at[tvi]->collin[list[k].tseg];
+                for (size_t e = 0; e < cl.size(); ++e) __builtin_prefetch(&used[slot_of(dsrc, view_base[tvi] + cl[e].other)]);
+            }
+            {
+                const std::vector<CollinEntry>& cs0 = view_at[svi]->collin[C.seg];
+                for (size_t e = 0; e < cs0.size(); ++e) __builtin_prefetch(&used[slot_of(dsrc, view_base[svi] + cs0[e].other)]);
+            }
             for (size_t k = cur; k < list.size() && list[k].seg == C.seg; ++k) {                                                    // :996-1138
                 const unsigned tcam = list[k].tcam, tseg = list[k].tseg;
                 int tvi; uint64_t dt; if (!dense(tcam, tseg, tvi, dt)) continue;
