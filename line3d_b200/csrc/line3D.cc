@@ -582,61 +582,60 @@ struct Line3D::Impl
             if (seg >= view_at[vidx]->segs.size()) return false;
             out = view_base[vidx] + seg; return true;
         };
-        // set of unordered segment pairs already looked at (line3D.cc:980, 1001-1005): open addressing
-        size_t pc_total = 0;
-        for (size_t v = 0; v < pc.size(); ++v) pc_total += pc[v].size();
-        size_t cap = size_t(1) << 16;
-        while (cap < pc_total * 3) cap <<= 1;
-        std::vector<uint64_t> used(cap, ~uint64_t(0)); size_t used_n = 0;
-        auto mark = [&](uint64_t a, uint64_t b) -> bool {   // true if the pair was new
-            const uint64_t key = std::min(a, b) * total + std::max(a, b);
-            if ((used_n + 1) * 2 > used.size()) {
-                std::vector<uint64_t> bigger(used.size() * 2, ~uint64_t(0));
-                for (size_t k = 0; k < used.size(); ++k) if (used[k] != ~uint64_t(0)) {
-                    size_t h = size_t((used[k] * 0x9E3779B97F4A7C15ull) >> 20) & (bigger.size() - 1);
-                    while (bigger[h] != ~uint64_t(0)) h = (h + 1) & (bigger.size() - 1);
-                    bigger[h] = used[k];
+        // Set of unordered segment pairs already looked at (line3D.cc:980, 1001-1005).  Pairs only ever join segments of
+        // two neighbouring views (or of one view), so the set is kept as one bit matrix per view pair, created on first
+        // use and dropped once the later of its two views has had its turns: a few MB are live at any time and the
+        // accesses are nearly sequential, where a hash set of 10^7..10^8 keys misses the caches on every probe.
+        struct PairBits { std::vector<uint64_t> w; size_t pitch; };
+        std::map<uint64_t, PairBits> bitmaps;                     // key = min view index * V + max view index
+        std::vector<std::vector<uint64_t> > drop_after(view_at.size());
+        std::vector<PairBits*> cur_bits(view_at.size(), (PairBits*)0);
+        int cur_view = -1;
+        const uint64_t nviews = view_at.size();
+        auto enter_view = [&](int v) {
+            if (v == cur_view) return;
+            if (cur_view >= 0) { for (size_t k = 0; k < drop_after[cur_view].size(); ++k) bitmaps.erase(drop_after[cur_view][k]); drop_after[cur_view].clear(); }
+            std::fill(cur_bits.begin(), cur_bits.end(), (PairBits*)0);
+            cur_view = v;
+        };
+        auto mark = [&](int sv, unsigned sseg, int tv, unsigned tseg) -> bool {   // true if the pair was new
+            PairBits*& pb = cur_bits[tv];
+            const int lo = std::min(sv, tv), hi = std::max(sv, tv);
+            if (!pb) {
+                const uint64_t key = uint64_t(lo) * nviews + uint64_t(hi);
+                std::map<uint64_t, PairBits>::iterator f = bitmaps.find(key);
+                if (f == bitmaps.end()) {
+                    PairBits nb; nb.pitch = (view_at[hi]->segs.size() + 63) / 64; nb.w.assign(view_at[lo]->segs.size() * nb.pitch, 0);
+                    f = bitmaps.insert(std::make_pair(key, PairBits())).first; f->second.w.swap(nb.w); f->second.pitch = nb.pitch;
+                    drop_after[hi].push_back(key);
                 }
-                used.swap(bigger);
+                pb = &f->second;
             }
-            size_t h = size_t((key * 0x9E3779B97F4A7C15ull) >> 20) & (used.size() - 1);
-            while (used[h] != ~uint64_t(0)) { if (used[h] == key) return false; h = (h + 1) & (used.size() - 1); }
-            used[h] = key; ++used_n; return true;
+            unsigned r, c;                                          // row: segment of the lower view, column: of the higher
+            if (sv < tv) { r = sseg; c = tseg; } else if (sv > tv) { r = tseg; c = sseg; } else { r = std::min(sseg, tseg); c = std::max(sseg, tseg); }
+            uint64_t& word = pb->w[size_t(r) * pb->pitch + (c >> 6)];
+            const uint64_t bit = uint64_t(1) << (c & 63);
+            if (word & bit) return false;
+            word |= bit; return true;
         };
         std::vector<size_t> cursor(view_at.size(), 0);
-        auto slot_of = [&](uint64_t a, uint64_t b) -> size_t {
-            const uint64_t key = std::min(a, b) * total + std::max(a, b);
-            return size_t((key * 0x9E3779B97F4A7C15ull) >> 20) & (used.size() - 1);
-        };
         for (size_t hidx = 0; hidx < hyps.size(); ++hidx) {
             const Hypothesis& C = hyps[hidx];
             int svi; uint64_t dsrc; if (!dense(C.cam, C.seg, svi, dsrc)) continue;
+            enter_view(svi);
             const std::vector<PC>& list = pc[svi];
             size_t& cur = cursor[svi];
             while (cur < list.size() && list[cur].seg < C.seg) ++cur;
-            // the pair set is far larger than the caches: touch the slots this turn may need before walking them in order
-            for (size_t k = cur; k < list.size() && list[k].seg == C.seg; ++k) {
-                int tvi; uint64_t dt;
-                if (!dense(list[k].tcam, list[k].tseg, tvi, dt)) continue;
-                __builtin_prefetch(&used[slot_of(dsrc, dt)]);
-                if (hyp_of[tvi][list[k].tseg] < 0) continue;
-                const std::vector<CollinEntry>& cl = view_at[tvi]->collin[list[k].tseg];
-                for (size_t e = 0; e < cl.size(); ++e) __builtin_prefetch(&used[slot_of(dsrc, view_base[tvi] + cl[e].other)]);
-            }
-            {
-                const std::vector<CollinEntry>& cs0 = view_at[svi]->collin[C.seg];
-                for (size_t e = 0; e < cs0.size(); ++e) __builtin_prefetch(&used[slot_of(dsrc, view_base[svi] + cs0[e].other)]);
-            }
             for (size_t k = cur; k < list.size() && list[k].seg == C.seg; ++k) {                                                    // :996-1138
                 const unsigned tcam = list[k].tcam, tseg = list[k].tseg;
                 int tvi; uint64_t dt; if (!dense(tcam, tseg, tvi, dt)) continue;
-                if (!mark(dsrc, dt)) continue;
+                if (!mark(svi, C.seg, tvi, tseg)) continue;
                 const int ht = hyp_of[tvi][tseg];
                 if (ht < 0) continue;                                                                                               // :1007
                 Cand c = {int(hidx), ht, 1.0f, L3D_MIN_AFFINITY}; cands.push_back(c);                                               // :1014-1016
                 const std::vector<CollinEntry>& cl = view_at[tvi]->collin[tseg];                                                    // :1065-1135
                 for (size_t e = 0; e < cl.size(); ++e) {
-                    if (!mark(dsrc, view_base[tvi] + cl[e].other)) continue;
+                    if (!mark(svi, C.seg, tvi, cl[e].other)) continue;
                     const int hc = hyp_of[tvi][cl[e].other];
                     if (hc < 0) continue;
                     Cand c3 = {int(hidx), hc, 1.0f, 0.01f}; cands.push_back(c3);                                                    // :1085-1087
@@ -644,13 +643,13 @@ struct Line3D::Impl
             }
             const std::vector<CollinEntry>& cs = view_at[svi]->collin[C.seg];                                                       // :1141-1214
             for (size_t e = 0; e < cs.size(); ++e) {
-                if (!mark(dsrc, view_base[svi] + cs[e].other)) continue;
+                if (!mark(svi, C.seg, svi, cs[e].other)) continue;
                 const int hc = hyp_of[svi][cs[e].other];
                 if (hc < 0) continue;
                 Cand c2 = {int(hidx), hc, cs[e].w, 0.01f}; cands.push_back(c2);                                                     // :1163-1165
             }
         }
-        std::vector<uint64_t>().swap(used);
+        bitmaps.clear();
         if (prof) { std::cerr << "[prof] enumerate " << now_s() - tp << " cands " << cands.size() << std::endl; tp = now_s(); }
         // similarities on the device (line3D.cc:1600-1691)
         std::vector<l3d_pair> pairs(cands.size());
