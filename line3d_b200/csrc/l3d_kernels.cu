@@ -401,69 +401,80 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
 }
 
 // ------------------------------------------------------------------------------------------
-// exact test: one warp per global row (job, source segment); candidates are gathered in
-// column order into a per-warp queue and evaluated 32 at a time; survivors (all four
-// depths > 0) are written, still in column order, to the row's staging range.
+// exact test.  Candidates of a row rarely fill whole warps and most of them fail the overlap test, so a
+// row-per-warp kernel (the first version, see profiles/r1_v1_kernels.md) idled more than half of its lanes.
+// Here every candidate is its own thread:
+//   k_expand      warp per row: the row's candidate columns, in order, into a flat list (+ the row of each)
+//   k_exact_flat  thread per candidate: overlap test; the block compacts the survivors through shared memory
+//                 and its first threads triangulate them (idle warps cost no issue slots); results are written
+//                 at the candidate's own index: ok flag, 4 depths; raw matches per row are counted with atomics
+// k_fill then copies the ok candidates of a row, in order, to their final position.
 // ------------------------------------------------------------------------------------------
-constexpr int EX_WARPS = 8;
-constexpr int EX_QCAP = 1088;
-
-__global__ void __launch_bounds__(EX_WARPS * 32) k_exact(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, int n_jobs, int n_rows,
-                                                         const unsigned* __restrict__ cand, const int* __restrict__ cand_off,
-                                                         int* __restrict__ stage_col, float4* __restrict__ stage_dep, int* __restrict__ raw_cnt)
+__global__ void k_expand(const JobDev* __restrict__ jobs, int n_jobs, int n_rows, const unsigned* __restrict__ cand, const int* __restrict__ cand_off,
+                         int* __restrict__ c_col, int* __restrict__ c_row)
 {
-    __shared__ unsigned short s_queue[EX_WARPS][EX_QCAP];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int grow = blockIdx.x * EX_WARPS + warp;
+    const int grow = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (grow >= n_rows) return;
-    const int base = cand_off[grow];
-    const int n_cand = cand_off[grow + 1] - base;
-    if (n_cand == 0) { if (lane == 0) raw_cnt[grow] = 0; return; }
+    int o = cand_off[grow];
+    if (cand_off[grow + 1] == o) return;
     const JobDev& jb = jobs[find_job_by_row(jobs, n_jobs, grow)];
-    const int row = grow - jb.row_off;
-    const unsigned* words = cand + jb.cand_off + (long long)row * jb.wpr;
+    const unsigned* words = cand + jb.cand_off + (long long)(grow - jb.row_off) * jb.wpr;
     const int n_words = (jb.n_tgt + 31) >> 5;
-    unsigned short* q = s_queue[warp];
-    const float4 s = segs[jb.src_off + row];
-    const V3 Cs = mk3(jb.C_s[0], jb.C_s[1], jb.C_s[2]), Ct = mk3(jb.C_t[0], jb.C_t[1], jb.C_t[2]);
-    int qn = 0, accepted = 0;
-    auto evaluate = [&](int first, int count) {
-        // lanes [0, count) take queue entries first .. first + count - 1 (column order)
-        bool ok = false; float4 dep = make_float4(0.f, 0.f, 0.f, 0.f); int col = 0;
-        if (lane < count) {
-            col = q[first + lane];
-            ok = xpair_test(s, segs[jb.tgt_off + col], jb.F, jb.RtKinv_s, jb.RtKinv_t, Cs, Ct, dep);
-        }
-        unsigned m = __ballot_sync(0xffffffffu, ok);
-        if (ok) {
-            int r = base + accepted + __popc(m & ((1u << lane) - 1u));
-            stage_col[r] = col; stage_dep[r] = dep;
-        }
-        accepted += __popc(m);
-    };
     for (int w0 = 0; w0 < n_words; w0 += 32) {
         unsigned bits = (w0 + lane < n_words) ? words[w0 + lane] : 0u;
         int n = __popc(bits), ex = n;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, ex, o); if (lane >= o) ex += y; }
+        for (int s = 1; s < 32; s <<= 1) { int y = __shfl_up_sync(0xffffffffu, ex, s); if (lane >= s) ex += y; }
         const int tot = __shfl_sync(0xffffffffu, ex, 31);
-        int pos = qn + ex - n;
-        while (bits) { int b = __ffs(bits) - 1; bits &= bits - 1; q[pos++] = (unsigned short)((w0 + lane) * 32 + b); }
-        qn += tot;
-        __syncwarp();
-        int head = 0;
-        while (qn - head >= 32) { evaluate(head, 32); head += 32; }
-        if (head > 0) {        // move the (< 32) leftovers to the front
-            const int rem = qn - head;
-            unsigned short v = (lane < rem) ? q[head + lane] : (unsigned short)0;
-            __syncwarp();
-            if (lane < rem) q[lane] = v;
-            qn = rem;
-            __syncwarp();
-        }
+        int pos = o + ex - n;
+        while (bits) { int b = __ffs(bits) - 1; bits &= bits - 1; c_col[pos] = (w0 + lane) * 32 + b; c_row[pos] = grow; ++pos; }
+        o += tot;
     }
-    if (qn > 0) evaluate(0, qn);
-    if (lane == 0) raw_cnt[grow] = accepted;
+}
+
+constexpr int EF_T = 256;
+__global__ void __launch_bounds__(EF_T) k_exact_flat(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, int n_jobs, int n_cand,
+                                                     const int* __restrict__ c_col, const int* __restrict__ c_row,
+                                                     unsigned char* __restrict__ c_ok, float4* __restrict__ c_dep, int* __restrict__ raw_cnt)
+{
+    __shared__ float s_is[8][EF_T];
+    __shared__ int s_who[EF_T];               // candidate (block-local) of each overlap survivor
+    __shared__ int s_warp_n[EF_T / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int c = blockIdx.x * EF_T + tid;
+    bool ok1 = false; PairIsect is;
+    if (c < n_cand) {
+        const int grow = c_row[c];
+        const JobDev& jb = jobs[find_job_by_row(jobs, n_jobs, grow)];
+        ok1 = xpair_overlap(segs[jb.src_off + (grow - jb.row_off)], segs[jb.tgt_off + c_col[c]], jb.F, is);
+        c_ok[c] = 0;
+    }
+    // block-wide ordered compaction of the survivors
+    const unsigned m = __ballot_sync(0xffffffffu, ok1);
+    if (lane == 0) s_warp_n[warp] = __popc(m);
+    __syncthreads();
+    int base = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < EF_T / 32; ++w) { const int n = s_warp_n[w]; if (w < warp) base += n; total += n; }
+    if (ok1) {
+        const int p = base + __popc(m & ((1u << lane) - 1u));
+        s_who[p] = tid;
+        s_is[0][p] = is.ax; s_is[1][p] = is.ay; s_is[2][p] = is.bx; s_is[3][p] = is.by;
+        s_is[4][p] = is.cx; s_is[5][p] = is.cy; s_is[6][p] = is.dx; s_is[7][p] = is.dy;
+    }
+    __syncthreads();
+    if (tid < total) {
+        const int cc = blockIdx.x * EF_T + s_who[tid];
+        const int grow = c_row[cc];
+        const JobDev& jb = jobs[find_job_by_row(jobs, n_jobs, grow)];
+        PairIsect i2;
+        i2.ax = s_is[0][tid]; i2.ay = s_is[1][tid]; i2.bx = s_is[2][tid]; i2.by = s_is[3][tid];
+        i2.cx = s_is[4][tid]; i2.cy = s_is[5][tid]; i2.dx = s_is[6][tid]; i2.dy = s_is[7][tid];
+        float4 dep;
+        const bool ok = xpair_depths(segs[jb.src_off + (grow - jb.row_off)], segs[jb.tgt_off + c_col[cc]], i2, jb.RtKinv_s, jb.RtKinv_t,
+                                     mk3(jb.C_s[0], jb.C_s[1], jb.C_s[2]), mk3(jb.C_t[0], jb.C_t[1], jb.C_t[2]), dep);
+        if (ok) { c_ok[cc] = 1; c_dep[cc] = dep; atomicAdd(&raw_cnt[grow], 1); }
+    }
 }
 
 // dst[k] = src[idx[k]]
@@ -489,7 +500,7 @@ __global__ void k_gather_counts(const CamTable* __restrict__ cams, int n_cams, i
 // fill: one warp per (row, cam) copies the row's records to their final place
 __global__ void k_fill(const CamTable* __restrict__ cams, int n_cams, int n_src,
                        const int* __restrict__ off, const int* __restrict__ cand_off,
-                       const int* __restrict__ stage_col, const float4* __restrict__ stage_dep,
+                       const int* __restrict__ stage_col, const float4* __restrict__ stage_dep, const unsigned char* __restrict__ stage_ok,
                        int4* __restrict__ m_ids, float4* __restrict__ m_dep)
 {
     const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -499,8 +510,15 @@ __global__ void k_fill(const CamTable* __restrict__ cams, int n_cams, int n_src,
     if (n == 0) return;
     const CamTable& ct = cams[cam];
     if (ct.mode == 0) {
-        const int b = cand_off[ct.row_off + row];
-        for (int k = lane; k < n; k += 32) { m_ids[o + k] = make_int4(row, cam, stage_col[b + k], 0); m_dep[o + k] = stage_dep[b + k]; }
+        const int b = cand_off[ct.row_off + row], e = cand_off[ct.row_off + row + 1];
+        int w = o;
+        for (int k0 = b; k0 < e; k0 += 32) {
+            const int k = k0 + lane;
+            const bool ok = k < e && stage_ok[k] != 0;
+            const unsigned m = __ballot_sync(0xffffffffu, ok);
+            if (ok) { const int r = w + __popc(m & ((1u << lane) - 1u)); m_ids[r] = make_int4(row, cam, stage_col[k], 0); m_dep[r] = stage_dep[k]; }
+            w += __popc(m);
+        }
     } else if (ct.mode == 1) {
         const int b = ct.t_start[row];
         for (int k = lane; k < n; k += 32) { m_ids[o + k] = make_int4(row, cam, ct.t_tgt[b + k], 0); m_dep[o + k] = ct.t_dep[b + k]; }
@@ -1215,7 +1233,7 @@ struct l3d_ctx {
     DBuf<CamTable> d_cams; DBuf<int> d_slot_cam;
     DBuf<SrcHoist> d_sh; DBuf<TgtHoist> d_th;
     DBuf<unsigned> d_cand; DBuf<int> d_cand_cnt, d_cand_off, d_tile_sums, d_total;
-    DBuf<int> d_stage_col; DBuf<float4> d_stage_dep;
+    DBuf<int> d_stage_col, d_stage_row; DBuf<float4> d_stage_dep; DBuf<unsigned char> d_stage_ok;
     DBuf<int> d_cnt, d_off;
     DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
     DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
@@ -1340,10 +1358,13 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     for (int j = 0; j < n_jobs; ++j) ctx->job_cands[j] = uint64_t(ctx->h_res.p[j + 1] - ctx->h_res.p[j]);
     const int n_cand = ctx->h_res.p[n_jobs];
     L3D_CUDA(ctx->d_stage_col.ensure(size_t(std::max(n_cand, 1)))); L3D_CUDA(ctx->d_stage_dep.ensure(size_t(std::max(n_cand, 1))));
-    if (rows > 0) {
-        k_exact<<<unsigned((rows + EX_WARPS - 1) / EX_WARPS), EX_WARPS * 32, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, n_jobs, int(rows), ctx->d_cand.p, ctx->d_pa_off.p,
-                                                                                  ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_pa_raw.p);
-        ctx->launches += 1;
+    L3D_CUDA(ctx->d_stage_row.ensure(size_t(std::max(n_cand, 1)))); L3D_CUDA(ctx->d_stage_ok.ensure(size_t(std::max(n_cand, 1))));
+    L3D_CUDA(cudaMemsetAsync(ctx->d_pa_raw.p, 0, sizeof(int) * (size_t(rows) + 1), st));
+    if (rows > 0 && n_cand > 0) {
+        k_expand<<<unsigned((rows * 32 + 255) / 256), 256, 0, st>>>(ctx->d_jobs.p, n_jobs, int(rows), ctx->d_cand.p, ctx->d_pa_off.p, ctx->d_stage_col.p, ctx->d_stage_row.p);
+        k_exact_flat<<<unsigned((n_cand + EF_T - 1) / EF_T), EF_T, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, n_jobs, n_cand, ctx->d_stage_col.p, ctx->d_stage_row.p,
+                                                                          ctx->d_stage_ok.p, ctx->d_stage_dep.p, ctx->d_pa_raw.p);
+        ctx->launches += 2;
         L3D_CUDA(cudaGetLastError());
     }
     L3D_CUDA(cudaEventRecord(ctx->pa_ev[2], st));
@@ -1458,7 +1479,7 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         L3D_CUDA(ctx->d_mids.ensure(M_ub)); L3D_CUDA(ctx->d_mdep.ensure(M_ub)); L3D_CUDA(ctx->d_score.ensure(M_ub));
         const long warps = long(n_src) * n_nb;
         k_fill<<<unsigned((warps * 32 + 255) / 256), 256, 0, st>>>(ctx->d_cams.p, n_nb, n_src, ctx->d_off.p, ctx->d_pa_off.p,
-                                                                  ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_mids.p, ctx->d_mdep.p);
+                                                                  ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_stage_ok.p, ctx->d_mids.p, ctx->d_mdep.p);
         ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
     }
@@ -1675,7 +1696,7 @@ void l3d_destroy(l3d_ctx* ctx)
     l3d_reset_matching(ctx);
     ctx->d_segs.release(); ctx->d_viewd.release(); ctx->d_cams.release(); ctx->d_slot_cam.release(); ctx->d_sh.release(); ctx->d_th.release();
     ctx->d_cand.release(); ctx->d_cand_cnt.release(); ctx->d_cand_off.release(); ctx->d_tile_sums.release(); ctx->d_total.release();
-    ctx->d_stage_col.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
+    ctx->d_stage_col.release(); ctx->d_stage_row.release(); ctx->d_stage_ok.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
     ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release();
     ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->h_res.release();
