@@ -477,6 +477,26 @@ __global__ void __launch_bounds__(EF_T) k_exact_flat(const float4* __restrict__ 
     }
 }
 
+// out[b] = max over i in [begin[b], begin[b] + len[b]) of (diff ? v[i + 1] - v[i] : v[i]); one block per b.
+// Used for upper bounds on the number of matches of a single segment (which scoring kernels are needed).
+__global__ void k_range_max(const int* __restrict__ v, const int* __restrict__ begin, const int* __restrict__ len, int diff, int* __restrict__ out)
+{
+    __shared__ int sh[32];
+    const int b0 = begin[blockIdx.x], n = len[blockIdx.x];
+    int m = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) m = max(m, diff ? v[b0 + i + 1] - v[b0 + i] : v[b0 + i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        m = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (threadIdx.x == 0) out[blockIdx.x] = m;
+    }
+}
+
 // dst[k] = src[idx[k]]
 __global__ void k_gather_int(const int* __restrict__ src, const int* __restrict__ idx, int n, int* __restrict__ dst)
 {
@@ -685,43 +705,40 @@ __global__ void __launch_bounds__(SC_T) k_score(const float4* __restrict__ segs,
 // ------------------------------------------------------------------------------------------
 constexpr int SS_T = 256;
 
-// sorts the matches of every segment with m_lo < M <= MP by d1 and writes (d1, d2, camera << 20 | index)
-// to global arrays at the segment's own offsets
+// sorts the matches of every segment with m_lo < M <= MP by d1 and writes (d1, d2, camera << 20 | index) to global
+// arrays at the segment's own offsets.  Sorted in shared memory as one 64-bit word per match: the bits of d1 (positive
+// floats order like unsigned integers) above the match's index within the segment.
 template<int MP>
 __global__ void __launch_bounds__(SS_T) k_sort_segments(const int* __restrict__ off, int n_cams, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
                                                         int m_lo, float* __restrict__ g_k, float* __restrict__ g_d2, unsigned* __restrict__ g_pl)
 {
-    extern __shared__ int s_sort[];
-    float* s_k = reinterpret_cast<float*>(s_sort);
-    float* s_d2 = s_k + MP;
-    unsigned* s_pl = reinterpret_cast<unsigned*>(s_d2 + MP);
+    extern __shared__ unsigned long long s_key[];
     const int row = blockIdx.x;
     const int seg_start = off[row * n_cams], M = off[(row + 1) * n_cams] - seg_start;
     if (M <= m_lo || M > MP) return;
     const int tid = threadIdx.x;
     int mp = 32; while (mp < M) mp <<= 1;
-    for (int i = tid; i < mp; i += SS_T) {
-        if (i < M) { float4 d = m_dep[seg_start + i]; s_k[i] = d.x; s_d2[i] = d.y; s_pl[i] = (unsigned(m_ids[seg_start + i].y) << 20) | unsigned(i); }
-        else { s_k[i] = INFINITY; s_d2[i] = 0.f; s_pl[i] = 0xffffffffu; }
-    }
+    for (int i = tid; i < mp; i += SS_T)
+        s_key[i] = (i < M) ? ((unsigned long long)__float_as_uint(m_dep[seg_start + i].x) << 32) | (unsigned)i : ~0ull;
     __syncthreads();
     for (int k = 2; k <= mp; k <<= 1)
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = tid; i < mp; i += SS_T) {
-                const int l = i ^ j;
-                if (l > i) {
-                    const float a = s_k[i], b = s_k[l];
-                    const bool up = ((i & k) == 0);
-                    if ((a > b) == up) {
-                        s_k[i] = b; s_k[l] = a;
-                        const float t = s_d2[i]; s_d2[i] = s_d2[l]; s_d2[l] = t;
-                        const unsigned u = s_pl[i]; s_pl[i] = s_pl[l]; s_pl[l] = u;
-                    }
-                }
+            for (int t = tid; t < (mp >> 1); t += SS_T) {
+                // t-th compare-exchange pair of this step: i has bit j clear
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), l = i | j;
+                const unsigned long long a = s_key[i], b = s_key[l];
+                const bool up = ((i & k) == 0);
+                if ((a > b) == up) { s_key[i] = b; s_key[l] = a; }
             }
             __syncthreads();
         }
-    for (int i = tid; i < M; i += SS_T) { g_k[seg_start + i] = s_k[i]; g_d2[seg_start + i] = s_d2[i]; g_pl[seg_start + i] = s_pl[i]; }
+    for (int i = tid; i < M; i += SS_T) {
+        const unsigned long long kv = s_key[i];
+        const unsigned idx = unsigned(kv & 0xffffffffu);
+        g_k[seg_start + i] = __uint_as_float(unsigned(kv >> 32));
+        g_d2[seg_start + i] = m_dep[seg_start + idx].y;
+        g_pl[seg_start + i] = (unsigned(m_ids[seg_start + idx].y) << 20) | idx;
+    }
 }
 
 // work items (segment, chunk of SC_T hypotheses) as in k_score; the partners of a hypothesis are the
@@ -1203,6 +1220,7 @@ struct Delivered {            // records a source view handed to a later view
     int* t_tgt = nullptr;
     float4* t_dep = nullptr;
     int owner = -1;           // index into ctx->deliver_bufs
+    int max_group = 0;        // most records delivered to a single segment
 };
 struct DeliverBuf { int* start = nullptr; int* tgt = nullptr; float4* dep = nullptr; int refs = 0; };
 
@@ -1241,7 +1259,7 @@ struct l3d_ctx {
     DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; bool sort_attr_set = false; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl; DBuf<int> d_dl_tgt; DBuf<float4> d_dl_dep;
     // phase A (pair tests) of the resident batch
     DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
-    std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands;
+    std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands; std::vector<int> job_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
     std::vector<PlannedView> plan; size_t plan_next = 0; size_t batch_begin = 0, batch_end = 0;
     float pa_ms[2] = {0.f, 0.f}; bool pa_ms_pending = false;
     uint64_t pair_budget = 24000000000ull;
@@ -1312,6 +1330,7 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     const int n_jobs = int(jh.size());
     ctx->jobs_host.assign(size_t(n_jobs), JobDev());
     ctx->job_cands.assign(size_t(n_jobs), 0);
+    ctx->job_rowmax.assign(size_t(n_jobs), 0);
     if (n_jobs == 0) return 0;
     long long sh_tot = 0, th_tot = 0, words = 0, rows = 0, blocks = 0;
     int max_n = 1;
@@ -1344,7 +1363,7 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     if (scan_exclusive(ctx, ctx->d_pa_cnt.p, ctx->d_pa_off.p, int(rows))) return 1;
     L3D_CUDA(cudaEventRecord(ctx->pa_ev[1], st));
     // candidate totals per job (and overall) come back in one small copy
-    L3D_CUDA(ctx->d_pa_idx.ensure(size_t(n_jobs) + 1)); L3D_CUDA(ctx->d_pa_tot.ensure(size_t(n_jobs) + 1)); L3D_CUDA(ctx->h_res.ensure(size_t(n_jobs) + 64));
+    L3D_CUDA(ctx->d_pa_idx.ensure(size_t(n_jobs) + 1)); L3D_CUDA(ctx->d_pa_tot.ensure(size_t(n_jobs) + 1)); L3D_CUDA(ctx->h_res.ensure(2 * size_t(n_jobs) + 64));
     {
         std::vector<int> idx(size_t(n_jobs) + 1);
         for (int j = 0; j < n_jobs; ++j) idx[j] = ctx->jobs_host[j].row_off;
@@ -1353,9 +1372,19 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
         k_gather_int<<<(n_jobs + 256) / 256, 256, 0, st>>>(ctx->d_pa_off.p, ctx->d_pa_idx.p, n_jobs + 1, ctx->d_pa_tot.p);
         ctx->launches += 1;
         L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p, ctx->d_pa_tot.p, sizeof(int) * (size_t(n_jobs) + 1), cudaMemcpyDeviceToHost, st));
-        L3D_CUDA(cudaStreamSynchronize(st));        // idx is a stack vector: must be consumed before it goes away
+        // largest candidate count of a single row, per job
+        std::vector<int> lens(static_cast<size_t>(n_jobs));
+        for (int j = 0; j < n_jobs; ++j) lens[j] = ctx->jobs_host[j].n_src;
+        L3D_CUDA(ctx->d_rm_begin.ensure(size_t(n_jobs))); L3D_CUDA(ctx->d_rm_len.ensure(size_t(n_jobs))); L3D_CUDA(ctx->d_rm_out.ensure(size_t(n_jobs)));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_rm_begin.p, idx.data(), sizeof(int) * size_t(n_jobs), cudaMemcpyHostToDevice, st));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_rm_len.p, lens.data(), sizeof(int) * size_t(n_jobs), cudaMemcpyHostToDevice, st));
+        k_range_max<<<n_jobs, 256, 0, st>>>(ctx->d_pa_cnt.p, ctx->d_rm_begin.p, ctx->d_rm_len.p, 0, ctx->d_rm_out.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p + n_jobs + 1, ctx->d_rm_out.p, sizeof(int) * size_t(n_jobs), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaStreamSynchronize(st));        // idx / lens are stack vectors: must be consumed before they go away
     }
     for (int j = 0; j < n_jobs; ++j) ctx->job_cands[j] = uint64_t(ctx->h_res.p[j + 1] - ctx->h_res.p[j]);
+    for (int j = 0; j < n_jobs; ++j) ctx->job_rowmax[j] = ctx->h_res.p[n_jobs + 1 + j];
     const int n_cand = ctx->h_res.p[n_jobs];
     L3D_CUDA(ctx->d_stage_col.ensure(size_t(std::max(n_cand, 1)))); L3D_CUDA(ctx->d_stage_dep.ensure(size_t(std::max(n_cand, 1))));
     L3D_CUDA(ctx->d_stage_row.ensure(size_t(std::max(n_cand, 1)))); L3D_CUDA(ctx->d_stage_ok.ensure(size_t(std::max(n_cand, 1))));
@@ -1426,9 +1455,10 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
 
     // ---- tables -------------------------------------------------------------------------
     L3D_CUDA(ctx->h_cams.ensure(size_t(n_nb)));
-    L3D_CUDA(ctx->h_ints.ensure(size_t(n_nb) + 64));
+    L3D_CUDA(ctx->h_ints.ensure(2 * size_t(n_nb) + 64));
     int n_slots = 0, n_deliver = 0, max_deliver_seg = 1;
     uint64_t pair_tests = 0, cand_ub = 0;
+    size_t seg_ub = 0;                               // upper bound on the matches of one source segment
     std::vector<int> consumed;                       // indices into ctx->delivered[view]
     for (int c = 0; c < n_nb; ++c) {
         const l3d_neighbor& n = nb[c];
@@ -1441,13 +1471,13 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         if (n.to_be_matched) {
             const int j = first_job + n_slots;
             ct.mode = 0; ct.slot = n_slots++; ct.row_off = ctx->jobs_host[j].row_off;
-            cand_ub += ctx->job_cands[j];
+            cand_ub += ctx->job_cands[j]; seg_ub += size_t(ctx->job_rowmax[j]);
             pair_tests += uint64_t(n_src) * uint64_t(tv.n_segments);
         } else {
             ct.mode = 2;
             std::vector<Delivered>& dl = ctx->delivered[view];
             for (size_t k = 0; k < dl.size(); ++k)
-                if (dl[k].from_view == n.view) { ct.mode = 1; ct.t_start = dl[k].t_start; ct.t_tgt = dl[k].t_tgt; ct.t_dep = dl[k].t_dep; res->n_delivered += uint64_t(dl[k].count); consumed.push_back(int(k)); break; }
+                if (dl[k].from_view == n.view) { ct.mode = 1; ct.t_start = dl[k].t_start; ct.t_tgt = dl[k].t_tgt; ct.t_dep = dl[k].t_dep; res->n_delivered += uint64_t(dl[k].count); seg_ub += size_t(dl[k].max_group); consumed.push_back(int(k)); break; }
         }
         if (n.deliver) { ct.deliver = n_deliver++; max_deliver_seg = std::max(max_deliver_seg, tv.n_segments); }
     }
@@ -1463,7 +1493,7 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     L3D_CUDA(cudaMemcpyAsync(ctx->d_cams.p, ctx->h_cams.p, sizeof(CamTable) * n_nb, cudaMemcpyHostToDevice, st));
     L3D_CUDA(ctx->d_cnt.ensure(size_t(n_src) * n_nb + 1));
     L3D_CUDA(ctx->d_off.ensure(size_t(n_src) * n_nb + 2));
-    L3D_CUDA(ctx->d_res.ensure(8)); L3D_CUDA(ctx->h_res.ensure(64));
+    L3D_CUDA(ctx->d_res.ensure(8)); L3D_CUDA(ctx->h_res.ensure(2 * size_t(n_nb) + 64));
     L3D_CUDA(cudaEventRecord(ctx->ev[2], st));
 
     // ---- assemble the match list ----------------------------------------------------------
@@ -1499,7 +1529,7 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         // Segments with SORT_MIN < M <= SORT_MAX matches are sorted by depth and scored through windows; shorter ones
         // (a sort costs more than their few pairs), longer ones (do not fit the sort's shared memory) and everything
         // when the 3-D gate is switched off go through the tiled quadratic kernel.
-        const int SORT_MIN = 0, SORT_SMALL = 1024, SORT_MAX = 8192;
+        const int SORT_MIN = 0, SORT_SMALL = 2048, SORT_MAX = 8192;
         const bool windowed = src.spatial_k > 0.0f;
         const int max_items = int(M_ub / SC_T) + n_src + 1;
         L3D_CUDA(ctx->d_items.ensure(size_t(2 * max_items))); L3D_CUDA(ctx->d_nitems.ensure(2));
@@ -1513,11 +1543,11 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         }
         if (windowed && M_ub > size_t(SORT_MIN)) {
             L3D_CUDA(ctx->d_sk.ensure(M_ub)); L3D_CUDA(ctx->d_sd2.ensure(M_ub)); L3D_CUDA(ctx->d_spl.ensure(M_ub));
-            if (!ctx->sort_attr_set) { L3D_CUDA(cudaFuncSetAttribute(k_sort_segments<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 12)); ctx->sort_attr_set = true; }
-            k_sort_segments<1024><<<n_src, SS_T, 1024 * 12, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_MIN, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
+            if (!ctx->sort_attr_set) { L3D_CUDA(cudaFuncSetAttribute(k_sort_segments<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8)); ctx->sort_attr_set = true; }
+            k_sort_segments<2048><<<n_src, SS_T, 2048 * 8, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_MIN, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
             ctx->launches += 1;
-            if (M_ub > size_t(SORT_SMALL)) {
-                k_sort_segments<8192><<<n_src, SS_T, 8192 * 12, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_SMALL, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
+            if (seg_ub > size_t(SORT_SMALL)) {
+                k_sort_segments<8192><<<n_src, SS_T, 8192 * 8, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_SMALL, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
                 ctx->launches += 1;
             }
             k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, SORT_MIN, SORT_MAX, 0, ctx->d_nitems.p, ctx->d_items.p);
@@ -1525,7 +1555,7 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
                                                              ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_items.p, ctx->d_nitems.p, sp, ctx->d_score.p);
             ctx->launches += 2;
         }
-        {
+        if (!windowed || seg_ub > size_t(SORT_MAX) || SORT_MIN > 0) {
             k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, windowed ? SORT_MIN : 0x7fffffff, windowed ? SORT_MAX : 0x7fffffff, 1,
                                                               ctx->d_nitems.p + 1, ctx->d_items.p + max_items);
             k_score<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
@@ -1589,6 +1619,13 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         k_gather_int<<<(n_deliver + 256) / 256, 256, 0, st>>>(buf.start, ctx->d_pa_idx.p, n_deliver + 1, ctx->d_pa_tot.p);
         ctx->launches += 1;
         L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p + 8, ctx->d_pa_tot.p, sizeof(int) * (size_t(n_deliver) + 1), cudaMemcpyDeviceToHost, st));
+        // largest group (records for one destination segment) per slot: bounds the destination's segment sizes
+        L3D_CUDA(ctx->d_rm_len.ensure(size_t(n_deliver))); L3D_CUDA(ctx->d_rm_out.ensure(size_t(n_deliver)));
+        for (int d = 0; d < n_deliver; ++d) ctx->h_ints.p[n_deliver + 1 + d] = max_deliver_seg;
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_rm_len.p, ctx->h_ints.p + n_deliver + 1, sizeof(int) * size_t(n_deliver), cudaMemcpyHostToDevice, st));
+        k_range_max<<<n_deliver, 256, 0, st>>>(buf.start, ctx->d_pa_idx.p, ctx->d_rm_len.p, 1, ctx->d_rm_out.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p + 8 + n_deliver + 1, ctx->d_rm_out.p, sizeof(int) * size_t(n_deliver), cudaMemcpyDeviceToHost, st));
     }
     L3D_CUDA(cudaEventRecord(ctx->ev[5], st));
 
@@ -1622,6 +1659,7 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
             if (d < 0) continue;
             Delivered dl; dl.from_view = view; dl.owner = owner;
             dl.count = ctx->h_res.p[8 + d + 1] - ctx->h_res.p[8 + d];
+            dl.max_group = ctx->h_res.p[8 + n_deliver + 1 + d];
             dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
             ctx->delivered[nb[c].view].push_back(dl);
         }
@@ -1699,7 +1737,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_stage_col.release(); ctx->d_stage_row.release(); ctx->d_stage_ok.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
     ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release();
-    ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->h_res.release();
+    ctx->d_rm_begin.release(); ctx->d_rm_len.release(); ctx->d_rm_out.release(); ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->h_res.release();
     for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_cams.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
