@@ -497,6 +497,36 @@ __global__ void k_range_max(const int* __restrict__ v, const int* __restrict__ b
     }
 }
 
+// All the small per-view results in one buffer, so that one copy brings them to the host:
+// out[0] = matches, out[1] = output records, out[2] = median depth (float bits), out[4..7] = two 64-bit iteration
+// counters, out[8 + d] = records handed to delivery slot d, out[8 + n_deliver + d] = the largest group of that slot.
+// One block per slot (at least one block).
+__global__ void k_pack_results(const int* __restrict__ M, const int* __restrict__ F, const float* __restrict__ median,
+                               const unsigned long long* __restrict__ iters, const int* __restrict__ start, int stride, int n_deliver, int seg_max,
+                               int* __restrict__ out)
+{
+    __shared__ int sh[32];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        out[0] = *M; out[1] = *F; out[2] = median ? __float_as_int(*median) : 0; out[3] = 0;
+        unsigned long long a = iters ? iters[0] : 0ull, b = iters ? iters[1] : 0ull;
+        out[4] = int(a & 0xffffffffull); out[5] = int(a >> 32); out[6] = int(b & 0xffffffffull); out[7] = int(b >> 32);
+    }
+    if (int(blockIdx.x) >= n_deliver) return;
+    const int b0 = blockIdx.x * stride;
+    int m = 0;
+    for (int i = threadIdx.x; i < seg_max; i += blockDim.x) m = max(m, start[b0 + i + 1] - start[b0 + i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        m = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (threadIdx.x == 0) { out[8 + blockIdx.x] = start[b0 + stride] - start[b0]; out[8 + n_deliver + blockIdx.x] = m; }
+    }
+}
+
 // dst[k] = src[idx[k]]
 __global__ void k_gather_int(const int* __restrict__ src, const int* __restrict__ idx, int n, int* __restrict__ dst)
 {
@@ -1264,7 +1294,7 @@ struct l3d_ctx {
     float pa_ms[2] = {0.f, 0.f}; bool pa_ms_pending = false;
     uint64_t pair_budget = 24000000000ull;
     cudaEvent_t pa_ev[3] = {nullptr, nullptr, nullptr};
-    DBuf<int> d_res; HBuf<int> h_res;
+    DBuf<int> d_res, d_zero; HBuf<int> h_res;
     DBuf<int> d_hist, d_hstart, d_cursor;
     HBuf<l3d_match> h_filtered; HBuf<CamTable> h_cams; HBuf<int> h_ints; HBuf<float> h_floats; HBuf<unsigned long long> h_u64;
     // collinearity
@@ -1519,21 +1549,30 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     res->scored = scored ? 1 : 0;
     const int* d_F = nullptr;                         // number of output records, on the device
     L3D_CUDA(ctx->d_filtered.ensure(std::max<size_t>(M_ub, 1)));
-    L3D_CUDA(ctx->d_median.ensure(4)); L3D_CUDA(ctx->d_iters.ensure(2));
+    L3D_CUDA(ctx->d_median.ensure(4));
+    // everything that has to start from zero lives in one buffer and is cleared with one memset per view
+    const bool delivering = n_deliver > 0 && scored;
+    const int stride = max_deliver_seg + 1;                         // one spare key per slot keeps t_start[n_seg] addressable
+    const int n_keys = delivering ? n_deliver * stride : 0;
+    const int ns = 2 * n_src;
+    const size_t z_items = 0, z_iters = 4, z_rank = 8, z_hist = z_rank + size_t(2 * ns) + 2, z_cursor = z_hist + size_t(n_keys) + 2, z_end = z_cursor + size_t(n_keys) + 2;
+    L3D_CUDA(ctx->d_zero.ensure(z_end));
+    L3D_CUDA(cudaMemsetAsync(ctx->d_zero.p, 0, sizeof(int) * z_end, st));
+    int* d_nitems = ctx->d_zero.p + z_items;
+    unsigned long long* d_iters = reinterpret_cast<unsigned long long*>(ctx->d_zero.p + z_iters);
+    int* d_hist = ctx->d_zero.p + z_hist; int* d_cursor = ctx->d_zero.p + z_cursor;
     if (scored && M_ub > 0) {
         // ---- score ------------------------------------------------------------------------
         ScoreParams sp; sp.sigma_p = sigma_p; sp.sigma_a = sigma_a;
         L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_src) + 1)); L3D_CUDA(ctx->d_foff.ensure(size_t(n_src) + 2));
         L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2));
-        L3D_CUDA(cudaMemsetAsync(ctx->d_iters.p, 0, 2 * sizeof(unsigned long long), st));
-        // Segments with SORT_MIN < M <= SORT_MAX matches are sorted by depth and scored through windows; shorter ones
-        // (a sort costs more than their few pairs), longer ones (do not fit the sort's shared memory) and everything
-        // when the 3-D gate is switched off go through the tiled quadratic kernel.
-        const int SORT_MIN = 0, SORT_SMALL = 2048, SORT_MAX = 8192;
+        // Segments with up to SORT_MAX matches are sorted by depth and scored through windows; longer ones (they do
+        // not fit the sort's shared memory) and everything when the 3-D gate is switched off go through the tiled
+        // quadratic kernel.
+        const int SORT_SMALL = 2048, SORT_MAX = 8192;
         const bool windowed = src.spatial_k > 0.0f;
         const int max_items = int(M_ub / SC_T) + n_src + 1;
-        L3D_CUDA(ctx->d_items.ensure(size_t(2 * max_items))); L3D_CUDA(ctx->d_nitems.ensure(2));
-        L3D_CUDA(cudaMemsetAsync(ctx->d_nitems.p, 0, 2 * sizeof(int), st));
+        L3D_CUDA(ctx->d_items.ensure(size_t(2 * max_items)));
         const size_t sm_bytes = size_t(n_nb) * SC_T * sizeof(int);
         if (sm_bytes > 160 * 1024) { ctx->err = "l3d_match_view: too many neighbours for the scoring kernel's shared memory"; return 1; }
         if (sm_bytes > ctx->score_smem) {
@@ -1541,36 +1580,33 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
             L3D_CUDA(cudaFuncSetAttribute(k_score_window, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_bytes)));
             ctx->score_smem = sm_bytes;
         }
-        if (windowed && M_ub > size_t(SORT_MIN)) {
+        if (windowed) {
             L3D_CUDA(ctx->d_sk.ensure(M_ub)); L3D_CUDA(ctx->d_sd2.ensure(M_ub)); L3D_CUDA(ctx->d_spl.ensure(M_ub));
             if (!ctx->sort_attr_set) { L3D_CUDA(cudaFuncSetAttribute(k_sort_segments<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8)); ctx->sort_attr_set = true; }
-            k_sort_segments<2048><<<n_src, SS_T, 2048 * 8, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_MIN, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
+            k_sort_segments<2048><<<n_src, SS_T, 2048 * 8, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, 0, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
             ctx->launches += 1;
             if (seg_ub > size_t(SORT_SMALL)) {
                 k_sort_segments<8192><<<n_src, SS_T, 8192 * 8, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_SMALL, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
                 ctx->launches += 1;
             }
-            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, SORT_MIN, SORT_MAX, 0, ctx->d_nitems.p, ctx->d_items.p);
+            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, 0, SORT_MAX, 0, d_nitems, ctx->d_items.p);
             k_score_window<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
-                                                             ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_items.p, ctx->d_nitems.p, sp, ctx->d_score.p);
+                                                             ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_items.p, d_nitems, sp, ctx->d_score.p);
             ctx->launches += 2;
         }
-        if (!windowed || seg_ub > size_t(SORT_MAX) || SORT_MIN > 0) {
-            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, windowed ? SORT_MIN : 0x7fffffff, windowed ? SORT_MAX : 0x7fffffff, 1,
-                                                              ctx->d_nitems.p + 1, ctx->d_items.p + max_items);
+        if (!windowed || seg_ub > size_t(SORT_MAX)) {
+            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, windowed ? 0 : 0x7fffffff, windowed ? SORT_MAX : 0x7fffffff, 1,
+                                                              d_nitems + 1, ctx->d_items.p + max_items);
             k_score<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
-                                                      ctx->d_items.p + max_items, ctx->d_nitems.p + 1, sp, ctx->d_score.p);
+                                                      ctx->d_items.p + max_items, d_nitems + 1, sp, ctx->d_score.p);
             ctx->launches += 2;
         }
         L3D_CUDA(cudaGetLastError());
         L3D_CUDA(cudaEventRecord(ctx->ev[4], st));
         // ---- reduce -----------------------------------------------------------------------
-        k_seg_reduce<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, ctx->d_iters.p);
+        k_seg_reduce<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, d_iters);
         {
-            const int ns = 2 * n_src;
-            L3D_CUDA(ctx->d_medrank.ensure(size_t(2 * ns) + 1));
-            L3D_CUDA(cudaMemsetAsync(ctx->d_medrank.p, 0, sizeof(int) * (size_t(2 * ns) + 1), st));
-            int* less = ctx->d_medrank.p; int* leq = less + ns; int* cnt = leq + ns;
+            int* less = ctx->d_zero.p + z_rank; int* leq = less + ns; int* cnt = leq + ns;
             k_median_rank<<<dim3((ns + 127) / 128, (ns + MED_CHUNK - 1) / MED_CHUNK), 128, 0, st>>>(ctx->d_dsamples.p, ns, less, leq, cnt);
             k_median_pick<<<(ns + 255) / 256, 256, 0, st>>>(ctx->d_dsamples.p, ns, less, leq, cnt, ctx->d_median.p);
         }
@@ -1591,56 +1627,40 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     }
 
     // ---- hand-over to later views ---------------------------------------------------------
-    DeliverBuf buf; int stride = 0;
-    const bool delivering = n_deliver > 0 && scored;
+    DeliverBuf buf;
     if (delivering) {
-        stride = max_deliver_seg + 1;                               // one spare key per slot keeps t_start[n_seg] addressable
-        const int n_keys = n_deliver * stride;
         buf.refs = n_deliver;
         L3D_CUDA(cudaMallocAsync(&buf.start, sizeof(int) * (size_t(n_keys) + 2), st));
         L3D_CUDA(cudaMallocAsync(&buf.tgt, sizeof(int) * std::max<size_t>(M_ub, 1), st));
         L3D_CUDA(cudaMallocAsync(&buf.dep, sizeof(float4) * std::max<size_t>(M_ub, 1), st));
-        L3D_CUDA(ctx->d_hist.ensure(size_t(n_keys) + 1)); L3D_CUDA(ctx->d_cursor.ensure(size_t(n_keys) + 1));
-        L3D_CUDA(cudaMemsetAsync(ctx->d_hist.p, 0, sizeof(int) * (size_t(n_keys) + 1), st));
-        L3D_CUDA(cudaMemsetAsync(ctx->d_cursor.p, 0, sizeof(int) * (size_t(n_keys) + 1), st));
-        if (M_ub > 0) { k_deliver_hist<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, ctx->d_hist.p); ctx->launches += 1; }
-        if (scan_exclusive(ctx, ctx->d_hist.p, buf.start, n_keys)) return 1;
+        if (M_ub > 0) { k_deliver_hist<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, d_hist); ctx->launches += 1; }
+        if (scan_exclusive(ctx, d_hist, buf.start, n_keys)) return 1;
         if (M_ub > 0) {
             L3D_CUDA(ctx->d_dl_tgt.ensure(M_ub)); L3D_CUDA(ctx->d_dl_dep.ensure(M_ub));
-            k_deliver_scatter<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, buf.start, ctx->d_cursor.p, ctx->d_dl_tgt.p, ctx->d_dl_dep.p);
+            k_deliver_scatter<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, buf.start, d_cursor, ctx->d_dl_tgt.p, ctx->d_dl_dep.p);
             k_deliver_place<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(buf.start, n_keys, ctx->d_dl_tgt.p, ctx->d_dl_dep.p, buf.tgt, buf.dep);
             ctx->launches += 2;
         }
         L3D_CUDA(cudaGetLastError());
-        // slot boundaries (record counts per destination view) for the host's bookkeeping
-        L3D_CUDA(ctx->d_pa_idx.ensure(size_t(n_deliver) + 1)); L3D_CUDA(ctx->d_pa_tot.ensure(size_t(n_deliver) + 1));
-        for (int d = 0; d <= n_deliver; ++d) ctx->h_ints.p[d] = d * stride;
-        L3D_CUDA(cudaMemcpyAsync(ctx->d_pa_idx.p, ctx->h_ints.p, sizeof(int) * (size_t(n_deliver) + 1), cudaMemcpyHostToDevice, st));
-        k_gather_int<<<(n_deliver + 256) / 256, 256, 0, st>>>(buf.start, ctx->d_pa_idx.p, n_deliver + 1, ctx->d_pa_tot.p);
-        ctx->launches += 1;
-        L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p + 8, ctx->d_pa_tot.p, sizeof(int) * (size_t(n_deliver) + 1), cudaMemcpyDeviceToHost, st));
-        // largest group (records for one destination segment) per slot: bounds the destination's segment sizes
-        L3D_CUDA(ctx->d_rm_len.ensure(size_t(n_deliver))); L3D_CUDA(ctx->d_rm_out.ensure(size_t(n_deliver)));
-        for (int d = 0; d < n_deliver; ++d) ctx->h_ints.p[n_deliver + 1 + d] = max_deliver_seg;
-        L3D_CUDA(cudaMemcpyAsync(ctx->d_rm_len.p, ctx->h_ints.p + n_deliver + 1, sizeof(int) * size_t(n_deliver), cudaMemcpyHostToDevice, st));
-        k_range_max<<<n_deliver, 256, 0, st>>>(buf.start, ctx->d_pa_idx.p, ctx->d_rm_len.p, 1, ctx->d_rm_out.p);
-        ctx->launches += 1;
-        L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p + 8 + n_deliver + 1, ctx->d_rm_out.p, sizeof(int) * size_t(n_deliver), cudaMemcpyDeviceToHost, st));
     }
+    // ---- results: one kernel packs them, one copy, one synchronise -------------------------------------
+    const int n_res = 8 + 2 * std::max(n_deliver, 1);
+    L3D_CUDA(ctx->d_res.ensure(size_t(n_res)));
+    k_pack_results<<<std::max(delivering ? n_deliver : 0, 1), 256, 0, st>>>(d_M, d_F, (scored && M_ub > 0) ? ctx->d_median.p : nullptr, (scored && M_ub > 0) ? d_iters : nullptr,
+                                                                          delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, max_deliver_seg, ctx->d_res.p);
+    ctx->launches += 1;
+    L3D_CUDA(cudaGetLastError());
     L3D_CUDA(cudaEventRecord(ctx->ev[5], st));
-
-    // ---- results: one small copy, one synchronise ------------------------------------------------
-    L3D_CUDA(ctx->h_floats.ensure(4)); L3D_CUDA(ctx->h_u64.ensure(2));
-    L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p, d_M, sizeof(int), cudaMemcpyDeviceToHost, st));
-    L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p + 1, d_F, sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (scored && M_ub > 0) {
-        L3D_CUDA(cudaMemcpyAsync(ctx->h_floats.p, ctx->d_median.p, sizeof(float), cudaMemcpyDeviceToHost, st));
-        L3D_CUDA(cudaMemcpyAsync(ctx->h_u64.p, ctx->d_iters.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-    }
+    L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p, ctx->d_res.p, sizeof(int) * size_t(n_res), cudaMemcpyDeviceToHost, st));
     L3D_CUDA(cudaStreamSynchronize(st));
     const int M = ctx->h_res.p[0], F = (M_ub > 0) ? ctx->h_res.p[1] : 0;
     float median = 1.0f;                              // line3D.cc:811
-    if (scored && M > 0) { median = ctx->h_floats.p[0]; res->score_iters = ctx->h_u64.p[0]; res->score_iters_other_cam = ctx->h_u64.p[0] - ctx->h_u64.p[1]; }
+    if (scored && M > 0) {
+        memcpy(&median, &ctx->h_res.p[2], sizeof(float));
+        const unsigned long long all = (unsigned long long)(unsigned)ctx->h_res.p[4] | ((unsigned long long)(unsigned)ctx->h_res.p[5] << 32);
+        const unsigned long long same = (unsigned long long)(unsigned)ctx->h_res.p[6] | ((unsigned long long)(unsigned)ctx->h_res.p[7] << 32);
+        res->score_iters = all; res->score_iters_other_cam = all - same;
+    }
     res->n_scored = uint64_t(M);
     res->n_raw = uint64_t(M) - res->n_delivered;
     res->median_depth = median;
@@ -1658,8 +1678,8 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
             const int d = ctx->h_cams.p[c].deliver;
             if (d < 0) continue;
             Delivered dl; dl.from_view = view; dl.owner = owner;
-            dl.count = ctx->h_res.p[8 + d + 1] - ctx->h_res.p[8 + d];
-            dl.max_group = ctx->h_res.p[8 + n_deliver + 1 + d];
+            dl.count = ctx->h_res.p[8 + d];
+            dl.max_group = ctx->h_res.p[8 + n_deliver + d];
             dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
             ctx->delivered[nb[c].view].push_back(dl);
         }
@@ -1737,7 +1757,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_stage_col.release(); ctx->d_stage_row.release(); ctx->d_stage_ok.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
     ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release();
-    ctx->d_rm_begin.release(); ctx->d_rm_len.release(); ctx->d_rm_out.release(); ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->h_res.release();
+    ctx->d_rm_begin.release(); ctx->d_rm_len.release(); ctx->d_rm_out.release(); ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->d_zero.release(); ctx->h_res.release();
     for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_cams.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
