@@ -200,8 +200,8 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_add(int* __restrict__ out, cons
 //   tgt side:  q1, q2 and w_m = |(F^T q_m)_xy|
 // evaluated in FP64 from the FP32 tables, rounded once.
 // ------------------------------------------------------------------------------------------
-struct SrcHoist { float4 a; float4 b; };   // a = (A1x, A1y, A1z, w'1)   b = (A2x, A2y, A2z, w'2)
-struct TgtHoist { float4 q; float2 w; float2 pad; };
+struct SrcHoist { float4 a; float4 b; };   // a = (A1x, A1y, A1z, T1)   b = (A2x, A2y, A2z, T2),  A_n = F p_n,  T_n = 2 eps |(A_n)_xy|
+struct TgtHoist { float4 q; float2 w; float2 pad; };   // w_m = 2 eps |(F^T q_m)_xy|
 
 // one pair-tested (source view, neighbour) combination; phase A runs over an array of these
 struct JobDev {
@@ -227,6 +227,10 @@ __device__ __forceinline__ int find_job_by_row(const JobDev* __restrict__ jobs, 
     return lo;
 }
 
+#define L3D_PRETEST_EPS_PX 0.25f
+#define L3D_PRETEST_LO 0.09f
+#define L3D_PRETEST_HI 0.28f
+
 __global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, SrcHoist* __restrict__ sh, TgtHoist* __restrict__ th)
 {
     const JobDev& jb = jobs[blockIdx.y];
@@ -244,7 +248,10 @@ __global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restric
             double ax = F[0] * p[n][0] + F[1] * p[n][1] + F[2];
             double ay = F[3] * p[n][0] + F[4] * p[n][1] + F[5];
             double az = F[6] * p[n][0] + F[7] * p[n][1] + F[8];
-            o[n][0] = float(ax); o[n][1] = float(ay); o[n][2] = float(az); o[n][3] = float(sqrt(ax * ax + ay * ay));
+            o[n][0] = float(ax); o[n][1] = float(ay); o[n][2] = float(az); o[n][3] = float(2.0 * L3D_PRETEST_EPS_PX * sqrt(ax * ax + ay * ay));
+            // values the float tests cannot handle (non-finite, or so large that products overflow) switch the
+            // pre-test off for this endpoint: zero residuals and an infinite margin keep every pair
+            if (!(fabsf(o[n][0]) < 1e15f && fabsf(o[n][1]) < 1e15f && fabsf(o[n][2]) < 1e15f)) { o[n][0] = o[n][1] = o[n][2] = 0.f; o[n][3] = __int_as_float(0x7f800000); }
         }
         SrcHoist h; h.a = make_float4(o[0][0], o[0][1], o[0][2], o[0][3]); h.b = make_float4(o[1][0], o[1][1], o[1][2], o[1][3]);
         sh[jb.sh_off + idx] = h;
@@ -257,8 +264,9 @@ __global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restric
         for (int m = 0; m < 2; ++m) {
             double ex = F[0] * q[m][0] + F[3] * q[m][1] + F[6];
             double ey = F[1] * q[m][0] + F[4] * q[m][1] + F[7];
-            w[m] = float(sqrt(ex * ex + ey * ey));
+            w[m] = float(2.0 * L3D_PRETEST_EPS_PX * sqrt(ex * ex + ey * ey));
         }
+        if (!(fabsf(t.x) < 1e15f && fabsf(t.y) < 1e15f && fabsf(t.z) < 1e15f && fabsf(t.w) < 1e15f)) { t = make_float4(0.f, 0.f, 0.f, 0.f); w[0] = w[1] = __int_as_float(0x7f800000); }
         TgtHoist h; h.q = t; h.w = make_float2(w[0], w[1]); h.pad = make_float2(0.f, 0.f);
         th[jb.th_off + idx] = h;
     }
@@ -276,9 +284,6 @@ __global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restric
 // noise, an overlap still cannot reach the reference's thresholds minus a margin; all
 // others go to the exact test.  The result is a superset of the reference's accepted set.
 // ------------------------------------------------------------------------------------------
-#define L3D_PRETEST_EPS_PX 0.25f
-#define L3D_PRETEST_LO 0.09f
-#define L3D_PRETEST_HI 0.28f
 
 __device__ __forceinline__ void side_bounds(float e1a, float e1b, float e2a, float e2b, float w1, float w2, float& I_hi, float& U_lo)
 {
@@ -286,7 +291,7 @@ __device__ __forceinline__ void side_bounds(float e1a, float e1b, float e2a, flo
     float d1 = e1a - e1b, d2 = e2a - e2b;
     float r1 = __frcp_rn(d1), r2 = __frcp_rn(d2);
     float t1 = e1a * r1, t2 = e2a * r2;
-    float err = L3D_PRETEST_EPS_PX * (w1 * fabsf(r1) * (1.0f + 2.0f * fabsf(t1)) + w2 * fabsf(r2) * (1.0f + 2.0f * fabsf(t2)));
+    float err = 0.5f * (w1 * fabsf(r1) * (1.0f + 2.0f * fabsf(t1)) + w2 * fabsf(r2) * (1.0f + 2.0f * fabsf(t2)));
     float lo = fminf(t1, t2), hi = fmaxf(t1, t2);
     I_hi = fminf(hi, 1.0f) - fmaxf(lo, 0.0f) + err;
     U_lo = fmaxf(hi, 1.0f) - fminf(lo, 0.0f) - err;
@@ -303,14 +308,22 @@ constexpr int PT_COLS = 256;        // target segments per block tile: 8 warps x
 constexpr int PT_BLOCK = 256;
 constexpr int PT_Q = 96;
 
-__device__ __forceinline__ bool pretest_level1_reject(float e11, float e12, float e21, float e22, float tq1, float tq2, float tp1, float tp2)
+// Sign bit of the result set = the pair survives level 1.  With two residuals a, b of one epipolar line,
+// |a + b| - ||a| - |b|| is twice the smaller magnitude when they share a sign and zero when they do not, so one
+// subtraction of the margin T = 2 eps |.| tests "same side, by more than eps pixels"; |a| - |b| tells beyond which
+// end the intersection falls.  Everything but the final bit operations runs on the FMA pipe; the kernel used to be
+// bound by the ALU pipe (compares, min/max, predicate logic).
+__device__ __forceinline__ int pretest_level1(float e11, float e12, float e21, float e22, float Tq1, float Tq2, float Tp1, float Tp2)
 {
-    // along the src segment: endpoint m of the target gives (e_m1, e_m2); tq_m = eps * |(F^T q_m)_xy|
-    const float a11 = fabsf(e11), a12 = fabsf(e12), a21 = fabsf(e21), a22 = fabsf(e22);
-    const bool sA = (e11 * e12 > 0.0f) && (e21 * e22 > 0.0f) && (fminf(a11, a12) > tq1) && (fminf(a21, a22) > tq2) && ((a11 < a12) == (a21 < a22));
-    // along the tgt segment: endpoint n of the source gives (e_1n, e_2n); tp_n = eps * |(F p_n)_xy|
-    const bool sB = (e11 * e21 > 0.0f) && (e12 * e22 > 0.0f) && (fminf(a11, a21) > tp1) && (fminf(a12, a22) > tp2) && ((a11 < a21) == (a12 < a22));
-    return sA || sB;
+    // along the src segment: endpoint m of the target gives (e_m1, e_m2)
+    const float da1 = fabsf(e11) - fabsf(e12), da2 = fabsf(e21) - fabsf(e22);
+    const float xa1 = (fabsf(e11 + e12) - fabsf(da1)) - Tq1, xa2 = (fabsf(e21 + e22) - fabsf(da2)) - Tq2;
+    const int A = __float_as_int(xa1) | __float_as_int(xa2) | __float_as_int(da1 * da2);     // >= 0: surely no overlap on the src side
+    // along the tgt segment: endpoint n of the source gives (e_1n, e_2n)
+    const float db1 = fabsf(e11) - fabsf(e21), db2 = fabsf(e12) - fabsf(e22);
+    const float xb1 = (fabsf(e11 + e21) - fabsf(db1)) - Tp1, xb2 = (fabsf(e12 + e22) - fabsf(db2)) - Tp2;
+    const int B = __float_as_int(xb1) | __float_as_int(xb2) | __float_as_int(db1 * db2);
+    return A & B;
 }
 
 __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict__ sh, const TgtHoist* __restrict__ th,
@@ -344,7 +357,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
     const bool valid = tid < ncol;
     const float4 q = s_q[tid];
     const float2 wq = s_w[tid];
-    const float tq1 = L3D_PRETEST_EPS_PX * wq.x, tq2 = L3D_PRETEST_EPS_PX * wq.y;
+    const unsigned vmask = __ballot_sync(0xffffffffu, valid);
     unsigned short* queue = s_queue[warp];
     int qn = 0;
     auto level2 = [&](int first, int count) {
@@ -375,10 +388,10 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
         const float e12 = fmaf(q.x, A2.x, fmaf(q.y, A2.y, A2.z));
         const float e21 = fmaf(q.z, A1.x, fmaf(q.w, A1.y, A1.z));
         const float e22 = fmaf(q.z, A2.x, fmaf(q.w, A2.y, A2.z));
-        const bool pass = valid && !pretest_level1_reject(e11, e12, e21, e22, tq1, tq2, L3D_PRETEST_EPS_PX * A1.w, L3D_PRETEST_EPS_PX * A2.w);
-        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        const bool pass = pretest_level1(e11, e12, e21, e22, wq.x, wq.y, A1.w, A2.w) < 0;
+        const unsigned m = __ballot_sync(0xffffffffu, pass) & vmask;
         if (m) {
-            if (pass) queue[qn + __popc(m & ((1u << lane) - 1u))] = (unsigned short)((r << 5) | lane);
+            if ((m >> lane) & 1u) queue[qn + __popc(m & ((1u << lane) - 1u))] = (unsigned short)((r << 5) | lane);
             qn += __popc(m);
             __syncwarp();
             if (qn >= 32) { level2(qn - 32, 32); qn -= 32; __syncwarp(); }
