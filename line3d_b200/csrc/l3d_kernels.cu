@@ -306,7 +306,7 @@ __device__ __forceinline__ void side_bounds(float e1a, float e1b, float e2a, flo
 constexpr int PT_ROWS = 128;        // source segments per block tile
 constexpr int PT_COLS = 256;        // target segments per block tile: 8 warps x 32 lanes
 constexpr int PT_BLOCK = 256;
-constexpr int PT_Q = 96;
+constexpr int PT_Q = 1024 + 32;     // a 32-row chunk can leave up to 1024 survivors on top of 31 waiting ones
 
 // Sign bit of the result set = the pair survives level 1.  With two residuals a, b of one epipolar line,
 // |a + b| - ||a| - |b|| is twice the smaller magnitude when they share a sign and zero when they do not, so one
@@ -357,7 +357,6 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
     const bool valid = tid < ncol;
     const float4 q = s_q[tid];
     const float2 wq = s_w[tid];
-    const unsigned vmask = __ballot_sync(0xffffffffu, valid);
     unsigned short* queue = s_queue[warp];
     int qn = 0;
     auto level2 = [&](int first, int count) {
@@ -380,22 +379,38 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
             if (!drop) atomicOr(&s_bits[r][warp], 1u << l);
         }
     };
-#pragma unroll 4
-    for (int r = 0; r < nrow; ++r) {
-        const float4 A1 = s_a[r], A2 = s_b[r];          // broadcast
-        // E[m][n] = q_m . A_n
-        const float e11 = fmaf(q.x, A1.x, fmaf(q.y, A1.y, A1.z));
-        const float e12 = fmaf(q.x, A2.x, fmaf(q.y, A2.y, A2.z));
-        const float e21 = fmaf(q.z, A1.x, fmaf(q.w, A1.y, A1.z));
-        const float e22 = fmaf(q.z, A2.x, fmaf(q.w, A2.y, A2.z));
-        const bool pass = pretest_level1(e11, e12, e21, e22, wq.x, wq.y, A1.w, A2.w) < 0;
-        const unsigned m = __ballot_sync(0xffffffffu, pass) & vmask;
-        if (m) {
-            if ((m >> lane) & 1u) queue[qn + __popc(m & ((1u << lane) - 1u))] = (unsigned short)((r << 5) | lane);
-            qn += __popc(m);
-            __syncwarp();
-            if (qn >= 32) { level2(qn - 32, 32); qn -= 32; __syncwarp(); }
+    // Level 1 over 32 rows at a time: every lane shifts its verdicts into a register (no vote, no branch in the
+    // loop); the warp then compacts its up to 1024 survivors into the queue and runs level 2 on full warps.
+    for (int c = 0; c < nrow; c += 32) {
+        unsigned acc = 0u;
+#pragma unroll 8
+        for (int rr = 0; rr < 32; ++rr) {
+            const float4 A1 = s_a[c + rr], A2 = s_b[c + rr];          // broadcast
+            // E[m][n] = q_m . A_n
+            const float e11 = fmaf(q.x, A1.x, fmaf(q.y, A1.y, A1.z));
+            const float e12 = fmaf(q.x, A2.x, fmaf(q.y, A2.y, A2.z));
+            const float e21 = fmaf(q.z, A1.x, fmaf(q.w, A1.y, A1.z));
+            const float e22 = fmaf(q.z, A2.x, fmaf(q.w, A2.y, A2.z));
+            acc = __funnelshift_l(unsigned(pretest_level1(e11, e12, e21, e22, wq.x, wq.y, A1.w, A2.w)), acc, 1);   // row c + rr ends at bit 31 - rr
         }
+        const int left = nrow - c;
+        if (left < 32) acc &= ~((1u << (32 - left)) - 1u);
+        if (!valid) acc = 0u;
+        const int n = __popc(acc);
+        int pre = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += t; }
+        const int total = __shfl_sync(0xffffffffu, pre, 31);
+        pre += qn - n;
+        while (acc) {
+            const int bit = 31 - __clz(acc);
+            acc &= ~(1u << bit);
+            queue[pre++] = (unsigned short)(((c + 31 - bit) << 5) | lane);
+        }
+        qn += total;
+        __syncwarp();
+        while (qn >= 32) { level2(qn - 32, 32); qn -= 32; }
+        __syncwarp();
     }
     if (qn > 0) level2(0, qn);
     __syncthreads();
