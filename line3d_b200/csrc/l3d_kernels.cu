@@ -220,18 +220,12 @@ __device__ __forceinline__ int find_job_by_block(const JobDev* __restrict__ jobs
     while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (jobs[mid].blk_off <= blk) lo = mid; else hi = mid - 1; }
     return lo;
 }
-__device__ __forceinline__ int find_job_by_row(const JobDev* __restrict__ jobs, int n_jobs, int row)
-{
-    int lo = 0, hi = n_jobs - 1;
-    while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (jobs[mid].row_off <= row) lo = mid; else hi = mid - 1; }
-    return lo;
-}
 
 #define L3D_PRETEST_EPS_PX 0.25f
 #define L3D_PRETEST_LO 0.09f
 #define L3D_PRETEST_HI 0.28f
 
-__global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, SrcHoist* __restrict__ sh, TgtHoist* __restrict__ th)
+__global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, SrcHoist* __restrict__ sh, TgtHoist* __restrict__ th, int* __restrict__ row_job)
 {
     const JobDev& jb = jobs[blockIdx.y];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -255,6 +249,7 @@ __global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restric
         }
         SrcHoist h; h.a = make_float4(o[0][0], o[0][1], o[0][2], o[0][3]); h.b = make_float4(o[1][0], o[1][1], o[1][2], o[1][3]);
         sh[jb.sh_off + idx] = h;
+        row_job[jb.row_off + idx] = blockIdx.y;          // row -> job, so that later kernels need no search
     }
     if (idx < jb.n_tgt) {
         float4 t = segs[jb.tgt_off + idx];
@@ -438,14 +433,14 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
 //                 at the candidate's own index: ok flag, 4 depths; raw matches per row are counted with atomics
 // k_fill then copies the ok candidates of a row, in order, to their final position.
 // ------------------------------------------------------------------------------------------
-__global__ void k_expand(const JobDev* __restrict__ jobs, int n_jobs, int n_rows, const unsigned* __restrict__ cand, const int* __restrict__ cand_off,
+__global__ void k_expand(const JobDev* __restrict__ jobs, const int* __restrict__ row_job, int n_rows, const unsigned* __restrict__ cand, const int* __restrict__ cand_off,
                          int* __restrict__ c_col, int* __restrict__ c_row)
 {
     const int grow = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (grow >= n_rows) return;
     int o = cand_off[grow];
     if (cand_off[grow + 1] == o) return;
-    const JobDev& jb = jobs[find_job_by_row(jobs, n_jobs, grow)];
+    const JobDev& jb = jobs[row_job[grow]];
     const unsigned* words = cand + jb.cand_off + (long long)(grow - jb.row_off) * jb.wpr;
     const int n_words = (jb.n_tgt + 31) >> 5;
     for (int w0 = 0; w0 < n_words; w0 += 32) {
@@ -461,19 +456,20 @@ __global__ void k_expand(const JobDev* __restrict__ jobs, int n_jobs, int n_rows
 }
 
 constexpr int EF_T = 256;
-__global__ void __launch_bounds__(EF_T) k_exact_flat(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, int n_jobs, int n_cand,
+__global__ void __launch_bounds__(EF_T) k_exact_flat(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, const int* __restrict__ row_job, int n_cand,
                                                      const int* __restrict__ c_col, const int* __restrict__ c_row,
                                                      unsigned char* __restrict__ c_ok, float4* __restrict__ c_dep, int* __restrict__ raw_cnt)
 {
     __shared__ float s_is[8][EF_T];
-    __shared__ int s_who[EF_T];               // candidate (block-local) of each overlap survivor
+    __shared__ int s_who[EF_T];               // candidate (block-local, low 8 bits) and job of each overlap survivor
     __shared__ int s_warp_n[EF_T / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = blockIdx.x * EF_T + tid;
-    bool ok1 = false; PairIsect is;
+    bool ok1 = false; PairIsect is; int job = 0;
     if (c < n_cand) {
         const int grow = c_row[c];
-        const JobDev& jb = jobs[find_job_by_row(jobs, n_jobs, grow)];
+        job = row_job[grow];
+        const JobDev& jb = jobs[job];
         ok1 = xpair_overlap(segs[jb.src_off + (grow - jb.row_off)], segs[jb.tgt_off + c_col[c]], jb.F, is);
         c_ok[c] = 0;
     }
@@ -486,15 +482,15 @@ __global__ void __launch_bounds__(EF_T) k_exact_flat(const float4* __restrict__ 
     for (int w = 0; w < EF_T / 32; ++w) { const int n = s_warp_n[w]; if (w < warp) base += n; total += n; }
     if (ok1) {
         const int p = base + __popc(m & ((1u << lane) - 1u));
-        s_who[p] = tid;
+        s_who[p] = tid | (job << 8);
         s_is[0][p] = is.ax; s_is[1][p] = is.ay; s_is[2][p] = is.bx; s_is[3][p] = is.by;
         s_is[4][p] = is.cx; s_is[5][p] = is.cy; s_is[6][p] = is.dx; s_is[7][p] = is.dy;
     }
     __syncthreads();
     if (tid < total) {
-        const int cc = blockIdx.x * EF_T + s_who[tid];
+        const int cc = blockIdx.x * EF_T + (s_who[tid] & (EF_T - 1));
         const int grow = c_row[cc];
-        const JobDev& jb = jobs[find_job_by_row(jobs, n_jobs, grow)];
+        const JobDev& jb = jobs[s_who[tid] >> 8];
         PairIsect i2;
         i2.ax = s_is[0][tid]; i2.ay = s_is[1][tid]; i2.bx = s_is[2][tid]; i2.by = s_is[3][tid];
         i2.cx = s_is[4][tid]; i2.cy = s_is[5][tid]; i2.dx = s_is[6][tid]; i2.dy = s_is[7][tid];
@@ -1307,7 +1303,7 @@ struct l3d_ctx {
     std::vector<DeliverBuf> deliver_bufs;
     // scratch
     DBuf<CamTable> d_cams; DBuf<int> d_slot_cam;
-    DBuf<SrcHoist> d_sh; DBuf<TgtHoist> d_th;
+    DBuf<SrcHoist> d_sh; DBuf<TgtHoist> d_th; DBuf<int> d_row_job;
     DBuf<unsigned> d_cand; DBuf<int> d_cand_cnt, d_cand_off, d_tile_sums, d_total;
     DBuf<int> d_stage_col, d_stage_row; DBuf<float4> d_stage_dep; DBuf<unsigned char> d_stage_ok;
     DBuf<int> d_cnt, d_off;
@@ -1408,12 +1404,12 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     L3D_CUDA(ctx->d_jobs.ensure(size_t(n_jobs)));
     L3D_CUDA(cudaMemcpyAsync(ctx->d_jobs.p, ctx->jobs_host.data(), sizeof(JobDev) * size_t(n_jobs), cudaMemcpyHostToDevice, st));
     L3D_CUDA(ctx->d_sh.ensure(size_t(std::max<long long>(sh_tot, 1)))); L3D_CUDA(ctx->d_th.ensure(size_t(std::max<long long>(th_tot, 1))));
-    L3D_CUDA(ctx->d_cand.ensure(size_t(std::max<long long>(words, 1))));
+    L3D_CUDA(ctx->d_cand.ensure(size_t(std::max<long long>(words, 1)))); L3D_CUDA(ctx->d_row_job.ensure(size_t(rows) + 1));
     L3D_CUDA(ctx->d_pa_cnt.ensure(size_t(rows) + 1)); L3D_CUDA(ctx->d_pa_off.ensure(size_t(rows) + 2)); L3D_CUDA(ctx->d_pa_raw.ensure(size_t(rows) + 1));
     L3D_CUDA(cudaMemsetAsync(ctx->d_pa_cnt.p, 0, sizeof(int) * (size_t(rows) + 1), st));
     L3D_CUDA(cudaEventRecord(ctx->pa_ev[0], st));
     if (rows > 0 && blocks > 0) {
-        k_hoist<<<dim3((max_n + 127) / 128, n_jobs), 128, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, ctx->d_sh.p, ctx->d_th.p);
+        k_hoist<<<dim3((max_n + 127) / 128, n_jobs), 128, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, ctx->d_sh.p, ctx->d_th.p, ctx->d_row_job.p);
         k_pretest<<<unsigned(blocks), PT_BLOCK, 0, st>>>(ctx->d_sh.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_cand.p, ctx->d_pa_cnt.p);
         ctx->launches += 2;
         L3D_CUDA(cudaGetLastError());
@@ -1448,8 +1444,8 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     L3D_CUDA(ctx->d_stage_row.ensure(size_t(std::max(n_cand, 1)))); L3D_CUDA(ctx->d_stage_ok.ensure(size_t(std::max(n_cand, 1))));
     L3D_CUDA(cudaMemsetAsync(ctx->d_pa_raw.p, 0, sizeof(int) * (size_t(rows) + 1), st));
     if (rows > 0 && n_cand > 0) {
-        k_expand<<<unsigned((rows * 32 + 255) / 256), 256, 0, st>>>(ctx->d_jobs.p, n_jobs, int(rows), ctx->d_cand.p, ctx->d_pa_off.p, ctx->d_stage_col.p, ctx->d_stage_row.p);
-        k_exact_flat<<<unsigned((n_cand + EF_T - 1) / EF_T), EF_T, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, n_jobs, n_cand, ctx->d_stage_col.p, ctx->d_stage_row.p,
+        k_expand<<<unsigned((rows * 32 + 255) / 256), 256, 0, st>>>(ctx->d_jobs.p, ctx->d_row_job.p, int(rows), ctx->d_cand.p, ctx->d_pa_off.p, ctx->d_stage_col.p, ctx->d_stage_row.p);
+        k_exact_flat<<<unsigned((n_cand + EF_T - 1) / EF_T), EF_T, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, ctx->d_row_job.p, n_cand, ctx->d_stage_col.p, ctx->d_stage_row.p,
                                                                           ctx->d_stage_ok.p, ctx->d_stage_dep.p, ctx->d_pa_raw.p);
         ctx->launches += 2;
         L3D_CUDA(cudaGetLastError());
@@ -1780,7 +1776,7 @@ void l3d_destroy(l3d_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     l3d_reset_matching(ctx);
-    ctx->d_segs.release(); ctx->d_viewd.release(); ctx->d_cams.release(); ctx->d_slot_cam.release(); ctx->d_sh.release(); ctx->d_th.release();
+    ctx->d_segs.release(); ctx->d_viewd.release(); ctx->d_cams.release(); ctx->d_slot_cam.release(); ctx->d_sh.release(); ctx->d_th.release(); ctx->d_row_job.release();
     ctx->d_cand.release(); ctx->d_cand_cnt.release(); ctx->d_cand_off.release(); ctx->d_tile_sums.release(); ctx->d_total.release();
     ctx->d_stage_col.release(); ctx->d_stage_row.release(); ctx->d_stage_ok.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
