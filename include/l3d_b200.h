@@ -140,13 +140,22 @@ typedef struct {
 } l3d_match_result;
 int l3d_match_view(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors,
                    float sigma_p, float sigma_a, l3d_match_result* result);
+/* Optional: with on != 0, l3d_match_result::filtered of every following l3d_match_view call stays valid until
+ * l3d_reset_matching / l3d_set_views / l3d_destroy instead of until the next call (the records of all views are kept
+ * in pinned host memory, 32 bytes each, reused after a reset).  A caller that files the records into its own
+ * structures (view.cc:162-224 in the reference) can then do so after the loop, off the GPU's critical path.
+ * No counterpart in the reference. */
+int l3d_retain_results(l3d_ctx* ctx, int on);
 /* Optional: announce the whole schedule (the views in the order they will be passed to
  * l3d_match_view, each with its neighbour array) before the first l3d_match_view call.
  * Which neighbours get pair-tested is a static function of the neighbour graph and the view
  * order (line3D.cc:732-736, 875-881), so the pair tests of many views can then run as a few
  * large launches ahead of the per-view scoring, instead of one small launch per neighbour as
- * in cudawrapper.cu:900-945.  Results are identical with or without a plan.  A call that
- * does not follow the announced schedule voids the rest of it. */
+ * in cudawrapper.cu:900-945, and the scoring of the next announced view is put on the GPU before the
+ * host waits for the current one.  Results are identical with or without a plan.  Because of that run-ahead the
+ * announced views must then be asked for in order, with the announced neighbours and the same sigmas throughout:
+ * a call that deviates before the schedule has started voids the schedule, one that deviates while a view is
+ * already running ahead fails (l3d_last_error says so; l3d_reset_matching starts over). */
 typedef struct { int32_t view; int32_t n_neighbors; const l3d_neighbor* neighbors; } l3d_view_plan;
 int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans);
 /* Forget all delivered-but-unconsumed records and any plan (a new compute3Dmodel run, line3D.cc:356). */

@@ -98,7 +98,7 @@ int l3dhost_compute(void* session, int diffusion, int measure_only, int flush_l2
                                   double(st.score_iters), double(st.score_iters_other_cam), double(st.hypotheses), double(st.affinity_pairs), double(st.edges),
                                   double(st.kernel_launches), st.t_neighbors, st.t_upload, st.t_matching, st.t_matching_device, st.t_hypotheses, st.t_affinity,
                                   st.t_diffusion, st.t_clustering, st.t_lines, st.t_total, st.t_stage[0], st.t_stage[1], st.t_stage[2], st.t_stage[3], st.t_stage[4],
-                                  double(st.h2d_bytes), double(st.d2h_bytes), 0.0, 0.0};
+                                  double(st.h2d_bytes), double(st.d2h_bytes), st.t_matching_calls, 0.0};
             std::memcpy(stats_out, v, sizeof v);
         }
         std::list<L3D::L3DFinalLine3D> result;

@@ -1275,8 +1275,9 @@ struct Delivered {            // records a source view handed to a later view
     float4* t_dep = nullptr;
     int owner = -1;           // index into ctx->deliver_bufs
     int max_group = 0;        // most records delivered to a single segment
+    int slot = 0;             // position among the owner's deliveries
 };
-struct DeliverBuf { int* start = nullptr; int* tgt = nullptr; float4* dep = nullptr; int refs = 0; };
+struct DeliverBuf { int* start = nullptr; int* tgt = nullptr; float4* dep = nullptr; int refs = 0; std::vector<int> counts, maxg; };   // counts/maxg: per slot, bounds until the owner is collected
 
 struct PlannedView {           // one entry of l3d_plan_matching
     int view = -1;
@@ -1286,6 +1287,17 @@ struct PlannedView {           // one entry of l3d_plan_matching
     uint64_t n_candidates = 0;
 };
 struct JobHost { int src_view, tgt_view; float F[9]; };
+struct ViewJob {                 // phase B of one view: on the stream, not yet collected
+    bool active = false;
+    int view = -1, parity = 0;
+    std::vector<l3d_neighbor> nb;
+    float sigma_p = 0.f, sigma_a = 0.f;
+    uint64_t pair_tests = 0, cand_ub = 0;
+    size_t M_ub = 0;
+    bool scored = false, delivering = false;
+    int n_deliver = 0, owner = -1;
+    std::vector<std::pair<int, int> > consumed;      // (deliver buffer, slot) of every delivery the view took in
+};
 
 struct l3d_ctx {
     int device = 0;
@@ -1309,7 +1321,6 @@ struct l3d_ctx {
     DBuf<int> d_cnt, d_off;
     DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
     DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
-    DBuf<l3d_match> d_filtered;
     DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; bool sort_attr_set = false; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl; DBuf<int> d_dl_tgt; DBuf<float4> d_dl_dep;
     // phase A (pair tests) of the resident batch
     DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
@@ -1319,8 +1330,15 @@ struct l3d_ctx {
     uint64_t pair_budget = 24000000000ull;
     cudaEvent_t pa_ev[3] = {nullptr, nullptr, nullptr};
     DBuf<int> d_res, d_zero; HBuf<int> h_res;
+    // two views in flight: everything the host or the copy stream touches while the next view runs exists twice
+    ViewJob vjob[2]; int pending = -1, vnext = 0;
+    DBuf<int> d_vres[2]; HBuf<int> h_vres[2]; HBuf<CamTable> h_cams2[2]; DBuf<l3d_match> d_filtered2[2];
+    cudaEvent_t vev[2][6] = {{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+    cudaStream_t copy_stream = nullptr;
+    // retained results (l3d_retain_results): pinned chunks that are never moved, handed out front to back
+    bool retain = false; std::vector<std::pair<l3d_match*, size_t> > arena; size_t arena_chunk = 0, arena_used = 0;
     DBuf<int> d_hist, d_hstart, d_cursor;
-    HBuf<l3d_match> h_filtered; HBuf<CamTable> h_cams; HBuf<int> h_ints; HBuf<float> h_floats; HBuf<unsigned long long> h_u64;
+    HBuf<l3d_match> h_filtered; HBuf<int> h_ints; HBuf<float> h_floats; HBuf<unsigned long long> h_u64;
     // collinearity
     DBuf<float4> d_csegs; DBuf<unsigned> d_cbits; DBuf<int> d_ccnt, d_coff; DBuf<l3d_collin_pair> d_cpairs; HBuf<l3d_collin_pair> h_cpairs;
     // hypotheses
@@ -1463,61 +1481,37 @@ bool same_neighbors(const std::vector<l3d_neighbor>& a, int n, const l3d_neighbo
     return true;
 }
 
-int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float sigma_p, float sigma_a, l3d_match_result* res, bool copy_back)
+// Phase B of one view is split in two so that the next view of an announced schedule can be put on the stream
+// before the host waits for this one: enqueue_view launches everything (sizes come from upper bounds, the real
+// counts stay on the device), finish_view waits for the view's small result record and fetches its output.
+int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float sigma_p, float sigma_a, int first_job, ViewJob& job)
 {
-    if (!ctx) return 1;
     if (view < 0 || view >= ctx->V) { ctx->err = "l3d_match_view: view index out of range"; return 1; }
-    if (n_nb <= 0 || !nb || !res) { ctx->err = "l3d_match_view: no neighbours / null argument"; return 1; }
-    L3D_CUDA(cudaSetDevice(ctx->device));
-    memset(res, 0, sizeof *res);
-    cudaStream_t st = ctx->stream;
-    const l3d_view& sv = ctx->views[view];
-    const int n_src = sv.n_segments;
     for (int c = 0; c < n_nb; ++c) {
         if (nb[c].view < 0 || nb[c].view >= ctx->V || nb[c].view == view) { ctx->err = "l3d_match_view: bad neighbour view index"; return 1; }
         if (c > 0 && nb[c - 1].view >= nb[c].view) { ctx->err = "l3d_match_view: neighbours must be in ascending view order"; return 1; }
     }
-
-    // ---- phase A: from the announced schedule (batched), or for this view alone ---------------
-    int first_job = 0;
-    bool planned = false;
-    if (ctx->plan_next < ctx->plan.size() && ctx->plan[ctx->plan_next].view == view && same_neighbors(ctx->plan[ctx->plan_next].nb, n_nb, nb)) {
-        planned = true;
-        if (ctx->plan_next >= ctx->batch_end) {                 // start the next batch here
-            std::vector<JobHost> jh;
-            size_t e = ctx->plan_next; uint64_t pairs = 0;
-            while (e < ctx->plan.size() && (e == ctx->plan_next || pairs + ctx->plan[e].pair_tests <= ctx->pair_budget)) {
-                PlannedView& pv = ctx->plan[e];
-                pv.first_job = int(jh.size());
-                for (size_t c = 0; c < pv.nb.size(); ++c)
-                    if (pv.nb[c].to_be_matched) { JobHost j; j.src_view = pv.view; j.tgt_view = pv.nb[c].view; memcpy(j.F, pv.nb[c].F, sizeof j.F); jh.push_back(j); }
-                pairs += pv.pair_tests; ++e;
-            }
-            if (run_phase_a(ctx, jh)) return 1;
-            ctx->batch_begin = ctx->plan_next; ctx->batch_end = e;
-        }
-        first_job = ctx->plan[ctx->plan_next].first_job;
-        ++ctx->plan_next;
-    } else {
-        ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;      // a call off the schedule voids it
-        std::vector<JobHost> jh;
-        for (int c = 0; c < n_nb; ++c)
-            if (nb[c].to_be_matched) { JobHost j; j.src_view = view; j.tgt_view = nb[c].view; memcpy(j.F, nb[c].F, sizeof j.F); jh.push_back(j); }
-        if (run_phase_a(ctx, jh)) return 1;
-    }
-    (void)planned;
+    cudaStream_t st = ctx->stream;
+    const l3d_view& sv = ctx->views[view];
+    const int n_src = sv.n_segments;
+    const int par = job.parity;
+    HBuf<CamTable>& hc = ctx->h_cams2[par];
+    DBuf<l3d_match>& dfil = ctx->d_filtered2[par];
+    cudaEvent_t* ev = ctx->vev[par];
+    job.view = view; job.nb.assign(nb, nb + n_nb); job.sigma_p = sigma_p; job.sigma_a = sigma_a;
+    job.consumed.clear(); job.owner = -1;
 
     // ---- tables -------------------------------------------------------------------------
-    L3D_CUDA(ctx->h_cams.ensure(size_t(n_nb)));
-    L3D_CUDA(ctx->h_ints.ensure(2 * size_t(n_nb) + 64));
+    L3D_CUDA(hc.ensure(size_t(n_nb)));
     int n_slots = 0, n_deliver = 0, max_deliver_seg = 1;
     uint64_t pair_tests = 0, cand_ub = 0;
     size_t seg_ub = 0;                               // upper bound on the matches of one source segment
     std::vector<int> consumed;                       // indices into ctx->delivered[view]
+    uint64_t delivered_ub = 0;
     for (int c = 0; c < n_nb; ++c) {
         const l3d_neighbor& n = nb[c];
         const l3d_view& tv = ctx->views[n.view];
-        CamTable& ct = ctx->h_cams.p[c];
+        CamTable& ct = hc.p[c];
         memcpy(ct.F, n.F, sizeof ct.F); memcpy(ct.RtKinv, tv.RtKinv, sizeof ct.RtKinv);
         memcpy(ct.P, tv.P, sizeof ct.P); memcpy(ct.C, tv.C, sizeof ct.C);
         ct.seg_off = ctx->seg_off[n.view]; ct.n_seg = tv.n_segments;
@@ -1531,24 +1525,22 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
             ct.mode = 2;
             std::vector<Delivered>& dl = ctx->delivered[view];
             for (size_t k = 0; k < dl.size(); ++k)
-                if (dl[k].from_view == n.view) { ct.mode = 1; ct.t_start = dl[k].t_start; ct.t_tgt = dl[k].t_tgt; ct.t_dep = dl[k].t_dep; res->n_delivered += uint64_t(dl[k].count); seg_ub += size_t(dl[k].max_group); consumed.push_back(int(k)); break; }
+                if (dl[k].from_view == n.view) { ct.mode = 1; ct.t_start = dl[k].t_start; ct.t_tgt = dl[k].t_tgt; ct.t_dep = dl[k].t_dep; delivered_ub += uint64_t(dl[k].count); seg_ub += size_t(dl[k].max_group); consumed.push_back(int(k)); job.consumed.push_back(std::make_pair(dl[k].owner, dl[k].slot)); break; }
         }
         if (n.deliver) { ct.deliver = n_deliver++; max_deliver_seg = std::max(max_deliver_seg, tv.n_segments); }
     }
-    res->pair_tests = pair_tests;
-    res->n_candidates = cand_ub;
+    job.pair_tests = pair_tests; job.cand_ub = cand_ub;
     SrcTable src;
     memcpy(src.RtKinv, sv.RtKinv, sizeof src.RtKinv); memcpy(src.C, sv.C, sizeof src.C);
     src.spatial_k = sv.spatial_k; src.cmax = std::max(std::fabs(sv.C[0]), std::max(std::fabs(sv.C[1]), std::fabs(sv.C[2])));
     src.seg_off = ctx->seg_off[view]; src.n_seg = n_src;
-    const size_t M_ub = size_t(cand_ub + res->n_delivered);          // upper bound on the number of matches to score
+    const size_t M_ub = size_t(cand_ub + delivered_ub);          // upper bound on the number of matches to score
 
     L3D_CUDA(ctx->d_cams.ensure(size_t(n_nb)));
-    L3D_CUDA(cudaMemcpyAsync(ctx->d_cams.p, ctx->h_cams.p, sizeof(CamTable) * n_nb, cudaMemcpyHostToDevice, st));
+    L3D_CUDA(cudaMemcpyAsync(ctx->d_cams.p, hc.p, sizeof(CamTable) * n_nb, cudaMemcpyHostToDevice, st));
     L3D_CUDA(ctx->d_cnt.ensure(size_t(n_src) * n_nb + 1));
     L3D_CUDA(ctx->d_off.ensure(size_t(n_src) * n_nb + 2));
-    L3D_CUDA(ctx->d_res.ensure(8)); L3D_CUDA(ctx->h_res.ensure(2 * size_t(n_nb) + 64));
-    L3D_CUDA(cudaEventRecord(ctx->ev[2], st));
+    L3D_CUDA(cudaEventRecord(ev[2], st));
 
     // ---- assemble the match list ----------------------------------------------------------
     const int* d_M = ctx->d_off.p + size_t(n_src) * n_nb;             // total number of matches, on the device
@@ -1567,12 +1559,11 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
     }
-    L3D_CUDA(cudaEventRecord(ctx->ev[3], st));
+    L3D_CUDA(cudaEventRecord(ev[3], st));
 
     const bool scored = n_slots > 0;                  // cudawrapper.cu:877-878
-    res->scored = scored ? 1 : 0;
     const int* d_F = nullptr;                         // number of output records, on the device
-    L3D_CUDA(ctx->d_filtered.ensure(std::max<size_t>(M_ub, 1)));
+    L3D_CUDA(dfil.ensure(std::max<size_t>(M_ub, 1)));
     L3D_CUDA(ctx->d_median.ensure(4));
     // everything that has to start from zero lives in one buffer and is cleared with one memset per view
     const bool delivering = n_deliver > 0 && scored;
@@ -1626,7 +1617,7 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
             ctx->launches += 2;
         }
         L3D_CUDA(cudaGetLastError());
-        L3D_CUDA(cudaEventRecord(ctx->ev[4], st));
+        L3D_CUDA(cudaEventRecord(ev[4], st));
         // ---- reduce -----------------------------------------------------------------------
         k_seg_reduce<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, d_iters);
         {
@@ -1637,14 +1628,14 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         ctx->launches += 3;
         if (scan_exclusive(ctx, ctx->d_fcnt.p, ctx->d_foff.p, n_src)) return 1;
         d_F = ctx->d_foff.p + n_src;
-        k_filter_fill<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, ctx->d_filtered.p);
+        k_filter_fill<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, dfil.p);
         ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
     } else {
-        L3D_CUDA(cudaEventRecord(ctx->ev[4], st));
+        L3D_CUDA(cudaEventRecord(ev[4], st));
         d_F = d_M;
         if (!scored && M_ub > 0) {
-            k_copy_unscored<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_mids.p, ctx->d_mdep.p, d_M, ctx->d_filtered.p);
+            k_copy_unscored<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_mids.p, ctx->d_mdep.p, d_M, dfil.p);
             ctx->launches += 1;
             L3D_CUDA(cudaGetLastError());
         }
@@ -1657,58 +1648,44 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         L3D_CUDA(cudaMallocAsync(&buf.start, sizeof(int) * (size_t(n_keys) + 2), st));
         L3D_CUDA(cudaMallocAsync(&buf.tgt, sizeof(int) * std::max<size_t>(M_ub, 1), st));
         L3D_CUDA(cudaMallocAsync(&buf.dep, sizeof(float4) * std::max<size_t>(M_ub, 1), st));
-        if (M_ub > 0) { k_deliver_hist<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, d_hist); ctx->launches += 1; }
+        if (M_ub > 0) { k_deliver_hist<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(dfil.p, d_F, ctx->d_cams.p, stride, d_hist); ctx->launches += 1; }
         if (scan_exclusive(ctx, d_hist, buf.start, n_keys)) return 1;
         if (M_ub > 0) {
             L3D_CUDA(ctx->d_dl_tgt.ensure(M_ub)); L3D_CUDA(ctx->d_dl_dep.ensure(M_ub));
-            k_deliver_scatter<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_filtered.p, d_F, ctx->d_cams.p, stride, buf.start, d_cursor, ctx->d_dl_tgt.p, ctx->d_dl_dep.p);
+            k_deliver_scatter<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(dfil.p, d_F, ctx->d_cams.p, stride, buf.start, d_cursor, ctx->d_dl_tgt.p, ctx->d_dl_dep.p);
             k_deliver_place<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(buf.start, n_keys, ctx->d_dl_tgt.p, ctx->d_dl_dep.p, buf.tgt, buf.dep);
             ctx->launches += 2;
         }
         L3D_CUDA(cudaGetLastError());
     }
-    // ---- results: one kernel packs them, one copy, one synchronise -------------------------------------
+    // ---- results: one kernel packs them, one copy; the host collects them in finish_view ----------------
     const int n_res = 8 + 2 * std::max(n_deliver, 1);
-    L3D_CUDA(ctx->d_res.ensure(size_t(n_res)));
+    L3D_CUDA(ctx->d_vres[par].ensure(size_t(n_res))); L3D_CUDA(ctx->h_vres[par].ensure(size_t(n_res)));
     k_pack_results<<<std::max(delivering ? n_deliver : 0, 1), 256, 0, st>>>(d_M, d_F, (scored && M_ub > 0) ? ctx->d_median.p : nullptr, (scored && M_ub > 0) ? d_iters : nullptr,
-                                                                          delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, max_deliver_seg, ctx->d_res.p);
+                                                                          delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, max_deliver_seg, ctx->d_vres[par].p);
     ctx->launches += 1;
     L3D_CUDA(cudaGetLastError());
-    L3D_CUDA(cudaEventRecord(ctx->ev[5], st));
-    L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p, ctx->d_res.p, sizeof(int) * size_t(n_res), cudaMemcpyDeviceToHost, st));
-    L3D_CUDA(cudaStreamSynchronize(st));
-    const int M = ctx->h_res.p[0], F = (M_ub > 0) ? ctx->h_res.p[1] : 0;
-    float median = 1.0f;                              // line3D.cc:811
-    if (scored && M > 0) {
-        memcpy(&median, &ctx->h_res.p[2], sizeof(float));
-        const unsigned long long all = (unsigned long long)(unsigned)ctx->h_res.p[4] | ((unsigned long long)(unsigned)ctx->h_res.p[5] << 32);
-        const unsigned long long same = (unsigned long long)(unsigned)ctx->h_res.p[6] | ((unsigned long long)(unsigned)ctx->h_res.p[7] << 32);
-        res->score_iters = all; res->score_iters_other_cam = all - same;
-    }
-    res->n_scored = uint64_t(M);
-    res->n_raw = uint64_t(M) - res->n_delivered;
-    res->median_depth = median;
-    res->n_filtered = uint64_t(F);
-    if (copy_back && F > 0) {
-        L3D_CUDA(ctx->h_filtered.ensure(size_t(F)));
-        L3D_CUDA(cudaMemcpyAsync(ctx->h_filtered.p, ctx->d_filtered.p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, st));
-        L3D_CUDA(cudaStreamSynchronize(st));
-    }
-    res->filtered = (copy_back && F > 0) ? ctx->h_filtered.p : nullptr;
+    L3D_CUDA(cudaEventRecord(ev[5], st));
+    L3D_CUDA(cudaMemcpyAsync(ctx->h_vres[par].p, ctx->d_vres[par].p, sizeof(int) * size_t(n_res), cudaMemcpyDeviceToHost, st));
+    L3D_CUDA(cudaEventRecord(ev[0], st));
+    job.M_ub = M_ub; job.scored = scored; job.delivering = delivering; job.n_deliver = n_deliver;
+    // the hand-over records exist from now on (stream order); until this view is collected their sizes are bounds
     if (delivering) {
-        const int owner = int(ctx->deliver_bufs.size());
-        ctx->deliver_bufs.push_back(buf);
+        job.owner = int(ctx->deliver_bufs.size());
+        buf.counts.assign(size_t(n_deliver), 0); buf.maxg.assign(size_t(n_deliver), 0);
         for (int c = 0; c < n_nb; ++c) {
-            const int d = ctx->h_cams.p[c].deliver;
+            const int d = hc.p[c].deliver;
             if (d < 0) continue;
-            Delivered dl; dl.from_view = view; dl.owner = owner;
-            dl.count = ctx->h_res.p[8 + d];
-            dl.max_group = ctx->h_res.p[8 + n_deliver + d];
+            const uint64_t ub = std::min<uint64_t>(hc.p[c].slot >= 0 ? ctx->job_cands[first_job + hc.p[c].slot] : uint64_t(M_ub), 0x7fffffffull);
+            Delivered dl; dl.from_view = view; dl.owner = job.owner; dl.slot = d;
+            dl.count = int(ub); dl.max_group = int(std::min<uint64_t>(ub, uint64_t(n_src)));      // a source segment matches a target segment once
             dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
+            buf.counts[d] = dl.count; buf.maxg[d] = dl.max_group;
             ctx->delivered[nb[c].view].push_back(dl);
         }
+        ctx->deliver_bufs.push_back(buf);
     }
-    // the consumed deliveries are no longer needed
+    // the consumed deliveries are no longer needed (freed in stream order)
     {
         std::vector<Delivered>& dl = ctx->delivered[view];
         for (size_t k = 0; k < consumed.size(); ++k) release_delivered(ctx, dl[consumed[k]]);
@@ -1716,16 +1693,137 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         for (size_t k = 0; k < dl.size(); ++k) if (dl[k].from_view >= 0) keep.push_back(dl[k]);
         dl.swap(keep);
     }
+    job.active = true;
+    return 0;
+}
+
+// n records of pinned host memory that stay where they are until l3d_reset_matching
+int arena_take(l3d_ctx* ctx, size_t n, l3d_match** out)
+{
+    while (ctx->arena_chunk < ctx->arena.size() && ctx->arena_used + n > ctx->arena[ctx->arena_chunk].second) { ++ctx->arena_chunk; ctx->arena_used = 0; }
+    if (ctx->arena_chunk == ctx->arena.size()) {
+        const size_t cap = std::max<size_t>(n, size_t(4) << 20);          // 128 MiB chunks
+        l3d_match* p = nullptr;
+        L3D_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&p), cap * sizeof(l3d_match), cudaHostAllocDefault));
+        ctx->arena.push_back(std::make_pair(p, cap)); ctx->arena_used = 0;
+    }
+    *out = ctx->arena[ctx->arena_chunk].first + ctx->arena_used;
+    ctx->arena_used += n;
+    return 0;
+}
+
+int finish_view(l3d_ctx* ctx, ViewJob& job, l3d_match_result* res, bool copy_back)
+{
+    const int par = job.parity;
+    job.active = false;
+    L3D_CUDA(cudaEventSynchronize(ctx->vev[par][0]));
+    const int* hr = ctx->h_vres[par].p;
+    memset(res, 0, sizeof *res);
+    res->pair_tests = job.pair_tests; res->n_candidates = job.cand_ub; res->scored = job.scored ? 1 : 0;
+    const int M = hr[0], F = (job.M_ub > 0) ? hr[1] : 0;
+    float median = 1.0f;                              // line3D.cc:811
+    if (job.scored && M > 0) {
+        memcpy(&median, &hr[2], sizeof(float));
+        const unsigned long long all = (unsigned long long)(unsigned)hr[4] | ((unsigned long long)(unsigned)hr[5] << 32);
+        const unsigned long long same = (unsigned long long)(unsigned)hr[6] | ((unsigned long long)(unsigned)hr[7] << 32);
+        res->score_iters = all; res->score_iters_other_cam = all - same;
+    }
+    if (job.delivering) {                              // exact sizes of what this view handed over
+        DeliverBuf& b = ctx->deliver_bufs[job.owner];
+        for (int d = 0; d < job.n_deliver; ++d) { b.counts[d] = hr[8 + d]; b.maxg[d] = hr[8 + job.n_deliver + d]; }
+        for (size_t c = 0; c < job.nb.size(); ++c) {
+            if (!job.nb[c].deliver) continue;
+            std::vector<Delivered>& dl = ctx->delivered[job.nb[c].view];
+            for (size_t k = 0; k < dl.size(); ++k)
+                if (dl[k].owner == job.owner) { dl[k].count = b.counts[dl[k].slot]; dl[k].max_group = b.maxg[dl[k].slot]; }
+        }
+    }
+    for (size_t k = 0; k < job.consumed.size(); ++k) res->n_delivered += uint64_t(ctx->deliver_bufs[job.consumed[k].first].counts[job.consumed[k].second]);
+    res->n_scored = uint64_t(M);
+    res->n_raw = uint64_t(M) - res->n_delivered;
+    res->median_depth = median;
+    res->n_filtered = uint64_t(F);
+    l3d_match* dst = nullptr;
+    if (copy_back && F > 0) {                          // on its own stream: the next view may already be running
+        if (ctx->retain) { if (arena_take(ctx, size_t(F), &dst)) return 1; }
+        else { L3D_CUDA(ctx->h_filtered.ensure(size_t(F))); dst = ctx->h_filtered.p; }
+        L3D_CUDA(cudaMemcpyAsync(dst, ctx->d_filtered2[par].p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, ctx->copy_stream));
+        L3D_CUDA(cudaStreamSynchronize(ctx->copy_stream));
+    }
+    res->filtered = dst;
     float ms;
     ctx->last_ms[0] = ctx->last_ms[1] = 0.f;
-    if (ctx->pa_ms_pending) {                          // phase A of a whole batch is booked on the call that ran it
+    if (ctx->pa_ms_pending) {                          // phase A of a whole batch is booked on the first view collected after it
         ms = 0.f; cudaEventElapsedTime(&ms, ctx->pa_ev[0], ctx->pa_ev[1]); ctx->last_ms[0] = ms;
         ms = 0.f; cudaEventElapsedTime(&ms, ctx->pa_ev[1], ctx->pa_ev[2]); ctx->last_ms[1] = ms;
         ctx->pa_ms_pending = false;
     }
-    for (int k = 2; k < 5; ++k) { ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[k], ctx->ev[k + 1]); ctx->last_ms[k] = ms; }
+    for (int k = 2; k < 5; ++k) { ms = 0.f; cudaEventElapsedTime(&ms, ctx->vev[par][k], ctx->vev[par][k + 1]); ctx->last_ms[k] = ms; }
     ctx->last_ms[5] = ctx->last_ms[0] + ctx->last_ms[1] + ctx->last_ms[2] + ctx->last_ms[3] + ctx->last_ms[4];
     return 0;
+}
+
+// Collects a view that was put on the stream ahead of its call and is not going to be asked for.
+void drain_pending(l3d_ctx* ctx)
+{
+    if (ctx->pending >= 0) { l3d_match_result dummy; finish_view(ctx, ctx->vjob[ctx->pending], &dummy, false); ctx->pending = -1; }
+}
+
+int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float sigma_p, float sigma_a, l3d_match_result* res, bool copy_back)
+{
+    if (!ctx) return 1;
+    if (n_nb <= 0 || !nb || !res) { ctx->err = "l3d_match_view: no neighbours / null argument"; return 1; }
+    if (view < 0 || view >= ctx->V) { ctx->err = "l3d_match_view: view index out of range"; return 1; }
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    memset(res, 0, sizeof *res);
+    int ci;
+    if (ctx->pending >= 0) {
+        // this view is already running: the call must be the one the schedule announced
+        ViewJob& p = ctx->vjob[ctx->pending];
+        if (p.view != view || !same_neighbors(p.nb, n_nb, nb) || p.sigma_p != sigma_p || p.sigma_a != sigma_a) {
+            ctx->err = "l3d_match_view: the call does not follow the schedule announced with l3d_plan_matching (same views, neighbours and sigmas, in order); call l3d_reset_matching to start over";
+            return 1;
+        }
+        ci = ctx->pending; ctx->pending = -1;
+    } else {
+        // ---- phase A: from the announced schedule (batched), or for this view alone -----------
+        int first_job = 0;
+        if (ctx->plan_next < ctx->plan.size() && ctx->plan[ctx->plan_next].view == view && same_neighbors(ctx->plan[ctx->plan_next].nb, n_nb, nb)) {
+            if (ctx->plan_next >= ctx->batch_end) {                 // start the next batch here
+                std::vector<JobHost> jh;
+                size_t e = ctx->plan_next; uint64_t pairs = 0;
+                while (e < ctx->plan.size() && (e == ctx->plan_next || pairs + ctx->plan[e].pair_tests <= ctx->pair_budget)) {
+                    PlannedView& pv = ctx->plan[e];
+                    pv.first_job = int(jh.size());
+                    for (size_t c = 0; c < pv.nb.size(); ++c)
+                        if (pv.nb[c].to_be_matched) { JobHost j; j.src_view = pv.view; j.tgt_view = pv.nb[c].view; memcpy(j.F, pv.nb[c].F, sizeof j.F); jh.push_back(j); }
+                    pairs += pv.pair_tests; ++e;
+                }
+                if (run_phase_a(ctx, jh)) return 1;
+                ctx->batch_begin = ctx->plan_next; ctx->batch_end = e;
+            }
+            first_job = ctx->plan[ctx->plan_next].first_job;
+            ++ctx->plan_next;
+        } else {
+            ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;      // a call off the schedule voids it
+            std::vector<JobHost> jh;
+            for (int c = 0; c < n_nb; ++c)
+                if (nb[c].to_be_matched) { JobHost j; j.src_view = view; j.tgt_view = nb[c].view; memcpy(j.F, nb[c].F, sizeof j.F); jh.push_back(j); }
+            if (run_phase_a(ctx, jh)) return 1;
+        }
+        ci = ctx->vnext; ctx->vnext ^= 1;
+        ctx->vjob[ci].parity = ci;
+        if (enqueue_view(ctx, view, n_nb, nb, sigma_p, sigma_a, first_job, ctx->vjob[ci])) return 1;
+    }
+    // put the schedule's next view on the stream before waiting for this one (its pair tests must be resident)
+    if (ctx->plan_next < ctx->batch_end) {
+        PlannedView& pv = ctx->plan[ctx->plan_next];
+        const int ni = ci ^ 1;
+        ctx->vjob[ni].parity = ni;
+        if (enqueue_view(ctx, pv.view, int(pv.nb.size()), pv.nb.data(), sigma_p, sigma_a, pv.first_job, ctx->vjob[ni])) { finish_view(ctx, ctx->vjob[ci], res, false); return 1; }
+        ++ctx->plan_next; ctx->pending = ni; ctx->vnext = ci;
+    }
+    return finish_view(ctx, ctx->vjob[ci], res, copy_back);
 }
 
 }  // namespace
@@ -1752,6 +1850,8 @@ int l3d_create(int device, l3d_ctx** out)
         if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
     }
     for (int k = 0; k < 8; ++k) cudaEventCreate(&ctx->ev[k]);
+    for (int q = 0; q < 2; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->vev[q][k]);
+    if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); cudaStreamDestroy(ctx->stream); delete ctx; return 1; }
     for (int k = 0; k < 3; ++k) cudaEventCreate(&ctx->pa_ev[k]);
     *out = ctx;
     return 0;
@@ -1761,12 +1861,14 @@ int l3d_reset_matching(l3d_ctx* ctx)
 {
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
+    drain_pending(ctx);
     for (size_t v = 0; v < ctx->delivered.size(); ++v) {
         for (size_t k = 0; k < ctx->delivered[v].size(); ++k) release_delivered(ctx, ctx->delivered[v][k]);
         ctx->delivered[v].clear();
     }
     ctx->deliver_bufs.clear();
     ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;
+    ctx->arena_chunk = 0; ctx->arena_used = 0;           // retained results are given up, their memory is reused
     cudaStreamSynchronize(ctx->stream);
     return 0;
 }
@@ -1780,10 +1882,13 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_cand.release(); ctx->d_cand_cnt.release(); ctx->d_cand_off.release(); ctx->d_tile_sums.release(); ctx->d_total.release();
     ctx->d_stage_col.release(); ctx->d_stage_row.release(); ctx->d_stage_ok.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
-    ctx->d_filtered.release(); ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release();
+    for (int q = 0; q < 2; ++q) { ctx->d_filtered2[q].release(); ctx->d_vres[q].release(); ctx->h_vres[q].release(); ctx->h_cams2[q].release(); for (int k = 0; k < 6; ++k) if (ctx->vev[q][k]) cudaEventDestroy(ctx->vev[q][k]); }
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    for (size_t k = 0; k < ctx->arena.size(); ++k) cudaFreeHost(ctx->arena[k].first);
+    ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release();
     ctx->d_rm_begin.release(); ctx->d_rm_len.release(); ctx->d_rm_out.release(); ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->d_zero.release(); ctx->h_res.release();
     for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
-    ctx->h_filtered.release(); ctx->h_cams.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
+    ctx->h_filtered.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
     ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release();
     for (int k = 0; k < 8; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
@@ -1907,6 +2012,8 @@ int l3d_set_views(l3d_ctx* ctx, int n_views, const l3d_view* views)
 int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
 {
     if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    drain_pending(ctx);
     ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;
     if (n_views <= 0) return 0;
     if (!plans) { ctx->err = "l3d_plan_matching: null argument"; return 1; }
@@ -1920,6 +2027,13 @@ int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
         }
         ctx->plan.push_back(pv);
     }
+    return 0;
+}
+
+int l3d_retain_results(l3d_ctx* ctx, int on)
+{
+    if (!ctx) return 1;
+    ctx->retain = on != 0;
     return 0;
 }
 

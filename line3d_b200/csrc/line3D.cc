@@ -421,6 +421,9 @@ struct Line3D::Impl
     {
         std::cout << prefix << separator << std::endl;
         std::cout << prefix << ">>> MATCHING IMAGES <<<" << std::endl;
+        // t_matching is the wall time of this whole function: the library runs a view ahead of the host, so the time
+        // spent inside the calls alone (t_matching_calls) would leave out the host's own share of the loop
+        const double t_match0 = now_s();
         // Which neighbours a view pair-tests and to which it hands its matches depends only on the
         // neighbour graph and the view order (line3D.cc:732-736, 844-845, 875-881): work the whole
         // schedule out first and announce it, so the library can batch the pair tests.
@@ -452,6 +455,8 @@ struct Line3D::Impl
                 l3d_view_plan p; p.view = views[it->first]->index; p.n_neighbors = int(it->second.size()); p.neighbors = it->second.data();
                 plans.push_back(p);
             }
+            view_records.clear();
+            if (l3d_retain_results(ctx, measure_only ? 0 : 1)) fail("l3d_retain_results");
             if (l3d_plan_matching(ctx, int(plans.size()), plans.data())) fail("l3d_plan_matching");
         }
         for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it) {
@@ -465,7 +470,7 @@ struct Line3D::Impl
             int rc = measure_only ? l3d_match_view_resident(ctx, v->index, int(nb.size()), nb.data(), sigma_p, sigma_a, &res)
                                   : l3d_match_view(ctx, v->index, int(nb.size()), nb.data(), sigma_p, sigma_a, &res);
             if (rc) fail("l3d_match_view");
-            stats.t_matching += now_s() - t0;
+            stats.t_matching_calls += now_s() - t0;
             float ms[6]; l3d_last_timings(ctx, ms); stats.t_matching_device += double(ms[5]) * 1e-3;
             for (int k = 0; k < 5; ++k) stats.t_stage[k] += double(ms[k]) * 1e-3;
             stats.score_iters_other_cam += res.score_iters_other_cam;
@@ -481,31 +486,96 @@ struct Line3D::Impl
             size_t n_tbm = 0; for (size_t c = 0; c < nb.size(); ++c) n_tbm += nb[c].to_be_matched ? 1 : 0;
             match_log.push_back(int32_t(vid)); match_log.push_back(int32_t(n_tbm)); match_log.push_back(int32_t(res.n_delivered)); match_log.push_back(int32_t(res.n_filtered));
             match_median.push_back(res.median_depth);
-            // records: cam = position in nb[]; when nothing was pair-tested the reference keeps using the
-            // local id as if it were a view id (cudawrapper.cu:877-878, line3D.cc:843) -- reproduced
-            std::vector<BestMatch>& bm = best[vid];
-            bm.assign(v->segs.size(), BestMatch());
-            for (size_t s = 0; s < bm.size(); ++s) bm[s].has = false;
-            if (!measure_only)
-                for (uint64_t k = 0; k < res.n_filtered; ++k) {
-                    const l3d_match& m = res.filtered[k];
-                    const unsigned cam = res.scored ? it->second[m.cam] : unsigned(m.cam);
-                    if (keep_debug) {
-                        const double row[9] = {double(vid), double(m.src_seg), double(cam), double(m.tgt_seg), m.depths[0], m.depths[1], m.depths[2], m.depths[3], m.confidence};
-                        filtered_dump.insert(filtered_dump.end(), row, row + 9);
-                    }
-                    PC f = {unsigned(m.src_seg), cam, unsigned(m.tgt_seg)};                                                         // :861-865
-                    pc_fwd[v->index].push_back(f);
-                    if (cam < id2idx.size() && id2idx[cam] >= 0) { PC r = {unsigned(m.tgt_seg), vid, unsigned(m.src_seg)}; pc_rev[id2idx[cam]].push_back(r); }
-                    BestMatch& b = bm[m.src_seg];                                                                                   // view.cc:165-183: first maximum
-                    if (!b.has || m.confidence > b.conf) { b.has = true; b.tgt_cam = cam; b.tgt_seg = unsigned(m.tgt_seg); b.conf = m.confidence; b.d1 = m.depths[0]; b.d2 = m.depths[1]; }
-                }
+            // the records stay in the library's pinned memory (l3d_retain_results) and are filed after the loop, on
+            // all cores, while nothing else waits for them: the GPU is not held up by the host's bookkeeping
+            if (!measure_only) { ViewRecords vr = {vid, v->index, res.scored != 0, res.filtered, res.n_filtered, &it->second}; view_records.push_back(vr); }
+            else { std::vector<BestMatch>& bm = best[vid]; bm.assign(v->segs.size(), BestMatch()); for (size_t s = 0; s < bm.size(); ++s) bm[s].has = false; }
             for (size_t c = 0; c < it->second.size(); ++c) {                                                                        // :875-881
                 const unsigned n = it->second[c];
                 matched[vid].insert(n);
                 if (neighbour_of(n, vid)) matched[n].insert(vid);
             }
         }
+        stats.t_matching += now_s() - t_match0;
+    }
+
+    // view.cc:162-224 (a view takes in its matches: best match per segment) and the potential-correspondence
+    // lists of line3D.cc:861-871, from the records the matching loop left in place.  Pass 1 (per source view):
+    // best matches, the view's own list, and its records grouped by target camera.  Pass 2 (per target view):
+    // the received records in ascending source-view order, as a sequential loop would have appended them.
+    struct ViewRecords { unsigned vid; int index; bool scored; const l3d_match* recs; uint64_t n; const std::vector<unsigned>* cams; };
+    std::vector<ViewRecords> view_records;
+    void fileRecords()
+    {
+        const size_t nr = view_records.size();
+        for (size_t k = 0; k < nr; ++k) best[view_records[k].vid];                    // create the map nodes before the threads run
+        std::vector<std::vector<PC> > grouped(nr);                                    // reversed records of a source view, by local camera
+        std::vector<std::vector<size_t> > group_off(nr);
+        std::vector<std::vector<std::pair<size_t, size_t> > > sources(view_at.size());   // target view index -> (source record set, local camera)
+        for (size_t k = 0; k < nr; ++k) {
+            const ViewRecords& vr = view_records[k];
+            for (size_t c = 0; c < vr.cams->size(); ++c) {
+                const unsigned cam = vr.scored ? (*vr.cams)[c] : unsigned(c);         // cudawrapper.cu:877-878, line3D.cc:843 -- reproduced
+                if (cam < id2idx.size() && id2idx[cam] >= 0) sources[id2idx[cam]].push_back(std::make_pair(k, c));
+            }
+        }
+        auto pass1 = [&](size_t t, size_t nt) {
+            for (size_t k = t; k < nr; k += nt) {
+                const ViewRecords& vr = view_records[k];
+                std::vector<BestMatch>& bm = best.find(vr.vid)->second;
+                bm.assign(view_at[vr.index]->segs.size(), BestMatch());
+                for (size_t s = 0; s < bm.size(); ++s) bm[s].has = false;
+                const size_t nc = vr.cams->size();
+                std::vector<size_t>& off = group_off[k]; off.assign(nc + 1, 0);
+                std::vector<PC>& fwd = pc_fwd[vr.index]; fwd.resize(vr.n);
+                for (uint64_t i = 0; i < vr.n; ++i) {
+                    const l3d_match& m = vr.recs[i];
+                    const unsigned cam = vr.scored ? (*vr.cams)[m.cam] : unsigned(m.cam);
+                    PC f = {unsigned(m.src_seg), cam, unsigned(m.tgt_seg)};                                                         // :861-865
+                    fwd[i] = f;
+                    ++off[size_t(m.cam) + 1];
+                    BestMatch& b = bm[m.src_seg];                                                                                   // view.cc:165-183: first maximum
+                    if (!b.has || m.confidence > b.conf) { b.has = true; b.tgt_cam = cam; b.tgt_seg = unsigned(m.tgt_seg); b.conf = m.confidence; b.d1 = m.depths[0]; b.d2 = m.depths[1]; }
+                }
+                for (size_t c = 0; c < nc; ++c) off[c + 1] += off[c];
+                std::vector<size_t> cur(off.begin(), off.end() - 1);
+                std::vector<PC>& g = grouped[k]; g.resize(vr.n);
+                for (uint64_t i = 0; i < vr.n; ++i) {
+                    const l3d_match& m = vr.recs[i];
+                    PC r = {unsigned(m.tgt_seg), vr.vid, unsigned(m.src_seg)};
+                    g[cur[m.cam]++] = r;
+                }
+            }
+        };
+        auto pass2 = [&](size_t t, size_t nt) {
+            for (size_t w = t; w < sources.size(); w += nt) {
+                size_t total = 0;
+                for (size_t q = 0; q < sources[w].size(); ++q) { const std::vector<size_t>& off = group_off[sources[w][q].first]; total += off[sources[w][q].second + 1] - off[sources[w][q].second]; }
+                std::vector<PC>& rev = pc_rev[w]; rev.reserve(total);
+                for (size_t q = 0; q < sources[w].size(); ++q) {
+                    const size_t k = sources[w][q].first, c = sources[w][q].second;
+                    rev.insert(rev.end(), grouped[k].begin() + group_off[k][c], grouped[k].begin() + group_off[k][c + 1]);
+                }
+            }
+        };
+        const size_t nt = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), 16));
+        for (int pass = 1; pass <= 2; ++pass) {
+            std::vector<std::thread> pool;
+            for (size_t t = 1; t < nt; ++t) { if (pass == 1) pool.emplace_back(pass1, t, nt); else pool.emplace_back(pass2, t, nt); }
+            if (pass == 1) pass1(0, nt); else pass2(0, nt);
+            for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
+        }
+        if (keep_debug)
+            for (size_t k = 0; k < nr; ++k) {
+                const ViewRecords& vr = view_records[k];
+                for (uint64_t i = 0; i < vr.n; ++i) {
+                    const l3d_match& m = vr.recs[i];
+                    const unsigned cam = vr.scored ? (*vr.cams)[m.cam] : unsigned(m.cam);
+                    const double row[9] = {double(vr.vid), double(m.src_seg), double(cam), double(m.tgt_seg), m.depths[0], m.depths[1], m.depths[2], m.depths[3], m.confidence};
+                    filtered_dump.insert(filtered_dump.end(), row, row + 9);
+                }
+            }
+        view_records.clear();
     }
 
     // line3D.cc:899-965 + view.cc:302-342 on the device
@@ -513,6 +583,7 @@ struct Line3D::Impl
     {
         std::cout << prefix << separator << std::endl;
         std::cout << prefix << ">>> OPTIMIZING CORRESPONDENCES (greedy) <<<" << std::endl;
+        fileRecords();
         hyps.clear(); hyp_of.assign(views.size(), std::vector<int>());
         for (size_t k = 0; k < view_at.size(); ++k) hyp_of[k].assign(view_at[k]->segs.size(), -1);
         std::vector<l3d_hypothesis_in> in;

@@ -22,7 +22,7 @@ DEFAULTS = dict(neighbors=10, unc_upper=5.0, unc_lower=1.0, sigma_p=3.5, sigma_a
 STAT_NAMES = ["pair_tests", "candidates", "raw_matches", "scored_matches", "filtered_matches", "score_iters", "score_iters_other_cam",
               "hypotheses", "affinity_pairs", "edges", "kernel_launches", "t_neighbors", "t_upload", "t_matching", "t_matching_device",
               "t_hypotheses", "t_affinity", "t_diffusion", "t_clustering", "t_lines", "t_total", "t_pretest", "t_exact", "t_assemble",
-              "t_score", "t_reduce", "h2d_bytes", "d2h_bytes", "_r0", "_r1"]
+              "t_score", "t_reduce", "h2d_bytes", "d2h_bytes", "t_matching_calls", "_r1"]
 
 _lib = None
 
