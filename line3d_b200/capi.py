@@ -29,6 +29,10 @@ class Neighbor(C.Structure):
     _fields_ = [("view", C.c_int32), ("F", C.c_float * 9), ("to_be_matched", C.c_int32), ("deliver", C.c_int32)]
 
 
+class ViewPlan(C.Structure):
+    _fields_ = [("view", C.c_int32), ("n_neighbors", C.c_int32), ("neighbors", C.POINTER(Neighbor))]
+
+
 class Match(C.Structure):
     _fields_ = [("src_seg", C.c_int32), ("cam", C.c_int32), ("tgt_seg", C.c_int32), ("confidence", C.c_float), ("depths", C.c_float * 4)]
 
@@ -145,12 +149,29 @@ class Context:
     def reset_matching(self):
         self._check(self._L.l3d_reset_matching(self._h))
 
-    def match_view(self, view: int, neighbors: list[dict], sigma_p: float = 3.5, sigma_a: float = 10.0, resident: bool = False):
-        """neighbors: dicts with view, F (3,3) float64, to_be_matched, deliver; ascending view order."""
+    @staticmethod
+    def _neighbors(neighbors):
         nb = (Neighbor * len(neighbors))()
         for i, n in enumerate(neighbors):
             nb[i].view = int(n["view"]); nb[i].to_be_matched = int(bool(n["to_be_matched"])); nb[i].deliver = int(bool(n["deliver"]))
             nb[i].F[:] = [float(np.float32(x)) for x in np.asarray(n["F"], dtype=np.float64).reshape(9)]
+        return nb
+
+    def plan_matching(self, schedule: list[tuple[int, list[dict]]]):
+        """schedule: (view, neighbors) in the order the views will be passed to match_view."""
+        keep = [self._neighbors(nbs) for _, nbs in schedule]
+        plans = (ViewPlan * max(len(schedule), 1))()
+        for k, (view, nbs) in enumerate(schedule):
+            plans[k].view = int(view); plans[k].n_neighbors = len(nbs); plans[k].neighbors = C.cast(keep[k], C.POINTER(Neighbor))
+        self._check(self._L.l3d_plan_matching(self._h, len(schedule), plans))
+
+    def retain_results(self, on: bool):
+        self._check(self._L.l3d_retain_results(self._h, int(bool(on))))
+
+    def match_view(self, view: int, neighbors: list[dict], sigma_p: float = 3.5, sigma_a: float = 10.0, resident: bool = False, copy: bool = True):
+        """neighbors: dicts with view, F (3,3) float64, to_be_matched, deliver; ascending view order.
+        copy=False returns a numpy view of the library's own buffer (what `filtered` points to)."""
+        nb = self._neighbors(neighbors)
         res = MatchResult()
         fn = self._L.l3d_match_view_resident if resident else self._L.l3d_match_view
         self._check(fn(self._h, view, len(neighbors), nb, sigma_p, sigma_a, C.byref(res)))
@@ -161,7 +182,9 @@ class Context:
         if not resident:
             if res.n_filtered:
                 buf = (C.c_char * (res.n_filtered * MATCH_DTYPE.itemsize)).from_address(C.addressof(res.filtered.contents))
-                out["filtered"] = np.frombuffer(buf, dtype=MATCH_DTYPE).copy()
+                out["filtered"] = np.frombuffer(buf, dtype=MATCH_DTYPE)
+                if copy:
+                    out["filtered"] = out["filtered"].copy()
             else:
                 out["filtered"] = np.zeros(0, MATCH_DTYPE)
         return out

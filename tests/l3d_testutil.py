@@ -32,12 +32,12 @@ def tables_from_dump(dm, scene):
     return ids, views, F, vn
 
 
-def run_matching(ctx, ids, views, F, vn, sigma_p=3.5, sigma_a=10.0, resident=False):
-    """The reference's view loop (line3D.cc:620-648) with its matched_ bookkeeping (732-736, 844-845, 875-881)."""
+def schedule_of(ids, F, vn):
+    """The reference's matched_ bookkeeping (line3D.cc:732-736, 844-845, 875-881) as a static schedule:
+    [(view id, neighbour ids, neighbour dicts)] in matching order."""
     index = {vid: i for i, vid in enumerate(ids)}
-    ctx.set_views(views)
     matched = {vid: set() for vid in ids}
-    out = {}
+    sched = []
     for vid in sorted(vn):
         nbs = sorted(vn[vid])
         if not nbs:
@@ -47,14 +47,32 @@ def run_matching(ctx, ids, views, F, vn, sigma_p=3.5, sigma_a=10.0, resident=Fal
             tbm = n not in matched[vid]
             deliver = (vid in vn.get(n, [])) and (vid not in matched[n])
             lst.append(dict(view=index[n], F=F[(vid, n)], to_be_matched=tbm, deliver=deliver))
-        res = ctx.match_view(index[vid], lst, sigma_p, sigma_a, resident=resident)
-        res["neighbors"] = nbs
-        res["timings"] = ctx.last_timings()
-        out[vid] = res
+        sched.append((vid, nbs, lst))
         for n in nbs:
             matched[vid].add(n)
             if vid in vn.get(n, []):
                 matched[n].add(vid)
+    return sched
+
+
+def run_matching(ctx, ids, views, F, vn, sigma_p=3.5, sigma_a=10.0, resident=False, plan=False, retain=False):
+    """The reference's view loop (line3D.cc:620-648).  plan: announce the schedule first (l3d_plan_matching);
+    retain: keep every view's records in the library's memory (l3d_retain_results) and read them after the loop."""
+    index = {vid: i for i, vid in enumerate(ids)}
+    ctx.set_views(views)
+    sched = schedule_of(ids, F, vn)
+    ctx.retain_results(retain)
+    if plan:
+        ctx.plan_matching([(index[vid], lst) for vid, _, lst in sched])
+    out = {}
+    for vid, nbs, lst in sched:
+        res = ctx.match_view(index[vid], lst, sigma_p, sigma_a, resident=resident, copy=not retain)
+        res["neighbors"] = nbs
+        res["timings"] = ctx.last_timings()
+        out[vid] = res
+    if retain and not resident:
+        for res in out.values():
+            res["filtered"] = res["filtered"].copy()      # only now: the buffers must have survived the later calls
     return out
 
 

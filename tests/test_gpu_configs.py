@@ -85,3 +85,39 @@ def test_batched_equals_view_by_view_and_is_deterministic(tmp_path):
             assert np.array_equal(keys[(n, j, v, i)][[2, 3, 0, 1]], dep)
             checked += 1
     assert checked > 0
+
+
+def test_plan_run_ahead_and_retained_results(tmp_path):
+    """C ABI only: with an announced schedule the library scores one view ahead of the caller, and with
+    l3d_retain_results every view's records stay readable after the loop; both must not change a single record.
+    A call that leaves the schedule while a view is running ahead is refused."""
+    from line3d_b200 import capi, scenes
+    sc = scenes.urban(n_views=16, n_seg=900, seed=77, blocks=(2, 1))
+    p = str(tmp_path / "u.scn")
+    scenes.write_scene(sc, p)
+    dm = util.oracle_dump(p, neighbors=6, collinearity=False)
+    ids, views, F, vn = util.tables_from_dump(dm, sc)
+    ctx = capi.Context(0)
+    plain = util.run_matching(ctx, ids, views, F, vn)
+    for plan, retain in ((True, False), (True, True), (False, True)):
+        got = util.run_matching(ctx, ids, views, F, vn, plan=plan, retain=retain)
+        assert sorted(got) == sorted(plain)
+        for v in plain:
+            assert np.array_equal(got[v]["filtered"], plain[v]["filtered"]), (plan, retain, v)
+            for k in ("pair_tests", "n_raw", "n_delivered", "n_scored", "n_filtered", "score_iters", "score_iters_other_cam", "median_depth", "scored"):
+                assert got[v][k] == plain[v][k], (plan, retain, v, k)
+    rows = np.concatenate([util.filtered_as_rows(v, plain[v]) for v in sorted(plain)])
+    key = lambda a: np.lexsort((a[:, 3], a[:, 2], a[:, 1], a[:, 0]))
+    assert np.array_equal(rows[key(rows)], dm["filtered_matches"][key(dm["filtered_matches"])])
+    # leaving the schedule: the second announced view is already on the GPU when the first call returns
+    index = {vid: i for i, vid in enumerate(ids)}
+    sched = util.schedule_of(ids, F, vn)
+    ctx.set_views(views)
+    ctx.plan_matching([(index[vid], lst) for vid, _, lst in sched])
+    ctx.match_view(index[sched[0][0]], sched[0][2])
+    with pytest.raises(capi.L3DError, match="schedule"):
+        ctx.match_view(index[sched[2][0]], sched[2][2])
+    ctx.reset_matching()
+    again = util.run_matching(ctx, ids, views, F, vn, plan=True)
+    assert all(np.array_equal(again[v]["filtered"], plain[v]["filtered"]) for v in plain)
+    ctx.close()
