@@ -193,6 +193,9 @@ int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3
  * [0] pre-test, [1] exact test, [2] assembly, [3] scoring, [4] reduce/filter/deliver,
  * [5] whole call on the device.  Timed with CUDA events on the context's stream. */
 int l3d_last_timings(l3d_ctx* ctx, float ms[6]);
+/* Duration in ms of the two large launches of the last batch of pair tests alone: [0] the pre-test kernel,
+ * [1] the exact-test kernel (valid after the l3d_last_timings call that reported a non-zero ms[0]). */
+int l3d_last_kernel_timings(l3d_ctx* ctx, float ms[2]);
 /* Overwrites a 256 MiB scratch buffer so that nothing of the previous step is left in L2. */
 int l3d_flush_l2(l3d_ctx* ctx);
 /* FP32 FFMA throughput of the device in TFLOP/s (register-only FMA chains, CUDA events):

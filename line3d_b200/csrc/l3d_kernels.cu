@@ -1329,6 +1329,8 @@ struct l3d_ctx {
     float pa_ms[2] = {0.f, 0.f}; bool pa_ms_pending = false;
     uint64_t pair_budget = 24000000000ull;
     cudaEvent_t pa_ev[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t pa_kev[4] = {nullptr, nullptr, nullptr, nullptr};   // around the k_pretest and k_exact_flat launches
+    float pa_kernel_ms[2] = {0.f, 0.f}; bool pa_kev_set[2] = {false, false};
     DBuf<int> d_res, d_zero; HBuf<int> h_res;
     // two views in flight: everything the host or the copy stream touches while the next view runs exists twice
     ViewJob vjob[2]; int pending = -1, vnext = 0;
@@ -1403,6 +1405,7 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     ctx->jobs_host.assign(size_t(n_jobs), JobDev());
     ctx->job_cands.assign(size_t(n_jobs), 0);
     ctx->job_rowmax.assign(size_t(n_jobs), 0);
+    ctx->pa_kev_set[0] = ctx->pa_kev_set[1] = false;
     if (n_jobs == 0) return 0;
     long long sh_tot = 0, th_tot = 0, words = 0, rows = 0, blocks = 0;
     int max_n = 1;
@@ -1428,7 +1431,10 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     L3D_CUDA(cudaEventRecord(ctx->pa_ev[0], st));
     if (rows > 0 && blocks > 0) {
         k_hoist<<<dim3((max_n + 127) / 128, n_jobs), 128, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, ctx->d_sh.p, ctx->d_th.p, ctx->d_row_job.p);
+        L3D_CUDA(cudaEventRecord(ctx->pa_kev[0], st));
         k_pretest<<<unsigned(blocks), PT_BLOCK, 0, st>>>(ctx->d_sh.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_cand.p, ctx->d_pa_cnt.p);
+        L3D_CUDA(cudaEventRecord(ctx->pa_kev[1], st));
+        ctx->pa_kev_set[0] = true;
         ctx->launches += 2;
         L3D_CUDA(cudaGetLastError());
     }
@@ -1463,8 +1469,11 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     L3D_CUDA(cudaMemsetAsync(ctx->d_pa_raw.p, 0, sizeof(int) * (size_t(rows) + 1), st));
     if (rows > 0 && n_cand > 0) {
         k_expand<<<unsigned((rows * 32 + 255) / 256), 256, 0, st>>>(ctx->d_jobs.p, ctx->d_row_job.p, int(rows), ctx->d_cand.p, ctx->d_pa_off.p, ctx->d_stage_col.p, ctx->d_stage_row.p);
+        L3D_CUDA(cudaEventRecord(ctx->pa_kev[2], st));
         k_exact_flat<<<unsigned((n_cand + EF_T - 1) / EF_T), EF_T, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, ctx->d_row_job.p, n_cand, ctx->d_stage_col.p, ctx->d_stage_row.p,
                                                                           ctx->d_stage_ok.p, ctx->d_stage_dep.p, ctx->d_pa_raw.p);
+        L3D_CUDA(cudaEventRecord(ctx->pa_kev[3], st));
+        ctx->pa_kev_set[1] = true;
         ctx->launches += 2;
         L3D_CUDA(cudaGetLastError());
     }
@@ -1756,6 +1765,7 @@ int finish_view(l3d_ctx* ctx, ViewJob& job, l3d_match_result* res, bool copy_bac
     if (ctx->pa_ms_pending) {                          // phase A of a whole batch is booked on the first view collected after it
         ms = 0.f; cudaEventElapsedTime(&ms, ctx->pa_ev[0], ctx->pa_ev[1]); ctx->last_ms[0] = ms;
         ms = 0.f; cudaEventElapsedTime(&ms, ctx->pa_ev[1], ctx->pa_ev[2]); ctx->last_ms[1] = ms;
+        for (int k = 0; k < 2; ++k) { ms = 0.f; if (ctx->pa_kev_set[k]) cudaEventElapsedTime(&ms, ctx->pa_kev[2 * k], ctx->pa_kev[2 * k + 1]); ctx->pa_kernel_ms[k] = ms; }
         ctx->pa_ms_pending = false;
     }
     for (int k = 2; k < 5; ++k) { ms = 0.f; cudaEventElapsedTime(&ms, ctx->vev[par][k], ctx->vev[par][k + 1]); ctx->last_ms[k] = ms; }
@@ -1853,6 +1863,7 @@ int l3d_create(int device, l3d_ctx** out)
     for (int q = 0; q < 2; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->vev[q][k]);
     if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); cudaStreamDestroy(ctx->stream); delete ctx; return 1; }
     for (int k = 0; k < 3; ++k) cudaEventCreate(&ctx->pa_ev[k]);
+    for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->pa_kev[k]);
     *out = ctx;
     return 0;
 }
@@ -1887,7 +1898,8 @@ void l3d_destroy(l3d_ctx* ctx)
     for (size_t k = 0; k < ctx->arena.size(); ++k) cudaFreeHost(ctx->arena[k].first);
     ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release();
     ctx->d_rm_begin.release(); ctx->d_rm_len.release(); ctx->d_rm_out.release(); ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->d_zero.release(); ctx->h_res.release();
-    for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
+    for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]);
+    for (int k = 0; k < 4; ++k) if (ctx->pa_kev[k]) cudaEventDestroy(ctx->pa_kev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
     ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release();
@@ -2160,6 +2172,13 @@ int l3d_last_timings(l3d_ctx* ctx, float ms[6])
 {
     if (!ctx || !ms) return 1;
     for (int k = 0; k < 6; ++k) ms[k] = ctx->last_ms[k];
+    return 0;
+}
+
+int l3d_last_kernel_timings(l3d_ctx* ctx, float ms[2])
+{
+    if (!ctx || !ms) return 1;
+    ms[0] = ctx->pa_kernel_ms[0]; ms[1] = ctx->pa_kernel_ms[1];
     return 0;
 }
 

@@ -473,6 +473,7 @@ struct Line3D::Impl
             stats.t_matching_calls += now_s() - t0;
             float ms[6]; l3d_last_timings(ctx, ms); stats.t_matching_device += double(ms[5]) * 1e-3;
             for (int k = 0; k < 5; ++k) stats.t_stage[k] += double(ms[k]) * 1e-3;
+            if (ms[0] > 0.f) { float km[2]; l3d_last_kernel_timings(ctx, km); stats.t_k_pretest += double(km[0]) * 1e-3; stats.t_k_exact += double(km[1]) * 1e-3; }
             stats.score_iters_other_cam += res.score_iters_other_cam;
             stats.h2d_bytes += nb.size() * 160; stats.d2h_bytes += (measure_only ? 0 : res.n_filtered * sizeof(l3d_match)) + 64;
             stats.pair_tests += res.pair_tests; stats.candidates += res.n_candidates; stats.raw_matches += res.n_raw;

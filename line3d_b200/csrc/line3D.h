@@ -82,6 +82,7 @@ namespace L3D
         double t_neighbors, t_upload, t_matching, t_matching_device, t_hypotheses, t_affinity, t_diffusion, t_clustering, t_lines, t_total;
         double t_stage[5];   // device seconds: pre-test, exact test, assembly, scoring, reduce/filter/deliver
         unsigned long long h2d_bytes, d2h_bytes;
+        double t_k_pretest, t_k_exact;   // device seconds of the pre-test and exact-test kernels alone
         double t_matching_calls;   // part of t_matching spent inside l3d_match_view (the rest is the host's bookkeeping between the calls)
     };
 
