@@ -257,10 +257,10 @@ def ours(args) -> None:
     t_kp = float(np.mean([x["t_k_pretest"] for x in stats])); t_ke = float(np.mean([x["t_k_exact"] for x in stats]))
     # The largest single kernel is k_pretest (one launch per step on this workload): it is arithmetic-bound (HBM traffic
     # under 1 % of peak in profiles/), so its roof is the FP32 rate.  Algorithmic work per pair test:
-    # 8 FFMA for the four residuals + 16 FADD + 2 FMUL for the two sign tests = 26 FMA-pipe instructions = 34 flops;
+    # 8 FFMA for the four residuals + 8 FADD + 1 FMUL for the sign test = 17 FMA-pipe instructions = 25 flops;
     # the interval test of the ~2 % survivors is left out (lower bound).  The peak is an all-FFMA figure, so this
-    # instruction mix cannot exceed 34 / (2 * 26) = 65 % of it: issue_frac is the same measurement in instructions.
-    PRETEST_FLOPS, PRETEST_INSTR = 34.0, 26.0
+    # instruction mix cannot exceed 25 / (2 * 17) = 74 % of it: issue_frac is the same measurement in instructions.
+    PRETEST_FLOPS, PRETEST_INSTR = 25.0, 17.0
     achieved = PRETEST_FLOPS * s["pair_tests"] / max(t_kp, 1e-12) / 1e12
     # reference arithmetic per unit: matching 104 + 420 a flops per pair test with a = raw / pair tests;
     # scoring 30 flops per inner iteration on another camera (lower bounds)

@@ -296,7 +296,7 @@ __device__ __forceinline__ void side_bounds(float e1a, float e1b, float e2a, flo
 // segment lies entirely on one side of an epipolar line when E[m][1] and E[m][2] have the
 // same sign; if that holds for both target endpoints, by more than L3D_PRETEST_EPS_PX pixels,
 // and both intersections fall beyond the same end of the segment, the overlap is zero
-// whatever the rounding (same for the target side).  About 93 % of all pairs end here.
+// whatever the rounding.  About 96 % of all pairs end here.
 // Survivors are compacted through a per-warp queue and get the interval test (level 2).
 constexpr int PT_ROWS = 128;        // source segments per block tile
 constexpr int PT_COLS = 256;        // target segments per block tile: 8 warps x 32 lanes
@@ -306,19 +306,15 @@ constexpr int PT_Q = 1024 + 32;     // a 32-row chunk can leave up to 1024 survi
 // Sign bit of the result set = the pair survives level 1.  With two residuals a, b of one epipolar line,
 // |a + b| - ||a| - |b|| is twice the smaller magnitude when they share a sign and zero when they do not, so one
 // subtraction of the margin T = 2 eps |.| tests "same side, by more than eps pixels"; |a| - |b| tells beyond which
-// end the intersection falls.  Everything but the final bit operations runs on the FMA pipe; the kernel used to be
-// bound by the ALU pipe (compares, min/max, predicate logic).
-__device__ __forceinline__ int pretest_level1(float e11, float e12, float e21, float e22, float Tq1, float Tq2, float Tp1, float Tp2)
+// end the intersection falls.  Everything but the final bit operation runs on the FMA pipe.  Only the source side
+// is tested here: on the frozen scenes it rejects 95.8 % of all pairs and the mirrored test on the target side
+// would add 0.4 % for as many instructions again -- level 2 covers both sides anyway.
+__device__ __forceinline__ int pretest_level1(float e11, float e12, float e21, float e22, float Tq1, float Tq2)
 {
     // along the src segment: endpoint m of the target gives (e_m1, e_m2)
     const float da1 = fabsf(e11) - fabsf(e12), da2 = fabsf(e21) - fabsf(e22);
     const float xa1 = (fabsf(e11 + e12) - fabsf(da1)) - Tq1, xa2 = (fabsf(e21 + e22) - fabsf(da2)) - Tq2;
-    const int A = __float_as_int(xa1) | __float_as_int(xa2) | __float_as_int(da1 * da2);     // >= 0: surely no overlap on the src side
-    // along the tgt segment: endpoint n of the source gives (e_1n, e_2n)
-    const float db1 = fabsf(e11) - fabsf(e21), db2 = fabsf(e12) - fabsf(e22);
-    const float xb1 = (fabsf(e11 + e21) - fabsf(db1)) - Tp1, xb2 = (fabsf(e12 + e22) - fabsf(db2)) - Tp2;
-    const int B = __float_as_int(xb1) | __float_as_int(xb2) | __float_as_int(db1 * db2);
-    return A & B;
+    return __float_as_int(xa1) | __float_as_int(xa2) | __float_as_int(da1 * da2);     // >= 0: surely no overlap on the src side
 }
 
 __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict__ sh, const TgtHoist* __restrict__ th,
@@ -386,7 +382,7 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
             const float e12 = fmaf(q.x, A2.x, fmaf(q.y, A2.y, A2.z));
             const float e21 = fmaf(q.z, A1.x, fmaf(q.w, A1.y, A1.z));
             const float e22 = fmaf(q.z, A2.x, fmaf(q.w, A2.y, A2.z));
-            acc = __funnelshift_l(unsigned(pretest_level1(e11, e12, e21, e22, wq.x, wq.y, A1.w, A2.w)), acc, 1);   // row c + rr ends at bit 31 - rr
+            acc = __funnelshift_l(unsigned(pretest_level1(e11, e12, e21, e22, wq.x, wq.y)), acc, 1);   // row c + rr ends at bit 31 - rr
         }
         const int left = nrow - c;
         if (left < 32) acc &= ~((1u << (32 - left)) - 1u);
