@@ -280,11 +280,15 @@ __global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restric
 // others go to the exact test.  The result is a superset of the reference's accepted set.
 // ------------------------------------------------------------------------------------------
 
+__device__ __forceinline__ float fast_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
 __device__ __forceinline__ void side_bounds(float e1a, float e1b, float e2a, float e2b, float w1, float w2, float& I_hi, float& U_lo)
 {
     // endpoint m: tau = ema / (ema - emb)
     float d1 = e1a - e1b, d2 = e2a - e2b;
-    float r1 = __frcp_rn(d1), r2 = __frcp_rn(d2);
+    // approximate reciprocals (one MUFU each, 1 ulp): the thresholds below keep a 10 % margin; a zero or denormal
+    // denominator gives inf, then NaN/inf bounds, and those comparisons keep the pair
+    float r1 = fast_rcp(d1), r2 = fast_rcp(d2);
     float t1 = e1a * r1, t2 = e2a * r2;
     float err = 0.5f * (w1 * fabsf(r1) * (1.0f + 2.0f * fabsf(t1)) + w2 * fabsf(r2) * (1.0f + 2.0f * fabsf(t2)));
     float lo = fminf(t1, t2), hi = fmaxf(t1, t2);
