@@ -191,11 +191,19 @@ int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3
 /* ---- measurement helpers -------------------------------------------------------------- */
 /* Device time in ms of the kernels of the last l3d_match_view[_resident] call, by stage:
  * [0] pre-test, [1] exact test, [2] assembly, [3] scoring, [4] reduce/filter/deliver,
- * [5] whole call on the device.  Timed with CUDA events on the context's stream. */
+ * [5] their sum.  Timed with CUDA events on the context's stream.  [0] and [1] are reported on the first call
+ * after a batch of pair tests ran; [2]..[4] only with l3d_set_stage_timing(ctx, 1), zero otherwise: the events
+ * between the stages keep consecutive kernels from overlapping (programmatic dependent launch) and cost about
+ * 13 % of a step, so they are off unless asked for. */
 int l3d_last_timings(l3d_ctx* ctx, float ms[6]);
 /* Duration in ms of the two large launches of the last batch of pair tests alone: [0] the pre-test kernel,
  * [1] the exact-test kernel (valid after the l3d_last_timings call that reported a non-zero ms[0]). */
 int l3d_last_kernel_timings(l3d_ctx* ctx, float ms[2]);
+int l3d_set_stage_timing(l3d_ctx* ctx, int on);
+/* Two CUDA events on the context's stream for timing any span of calls on the device: l3d_mark(ctx, 0) before,
+ * l3d_mark(ctx, 1) after, l3d_marks_elapsed waits for the second and returns the milliseconds between them. */
+int l3d_mark(l3d_ctx* ctx, int which);
+int l3d_marks_elapsed(l3d_ctx* ctx, float* ms);
 /* Overwrites a 256 MiB scratch buffer so that nothing of the previous step is left in L2. */
 int l3d_flush_l2(l3d_ctx* ctx);
 /* FP32 FFMA throughput of the device in TFLOP/s (register-only FMA chains, CUDA events):

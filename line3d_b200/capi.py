@@ -88,7 +88,7 @@ def lib():
 
 EXPORTS = ["l3d_create", "l3d_destroy", "l3d_last_error", "l3d_collinearity", "l3d_collinearity_prealloc", "l3d_set_views", "l3d_match_view",
            "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
-           "l3d_last_timings", "l3d_last_kernel_timings", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math", "l3d_flush_l2"]
+           "l3d_last_timings", "l3d_last_kernel_timings", "l3d_set_stage_timing", "l3d_mark", "l3d_marks_elapsed", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math", "l3d_flush_l2"]
 
 
 class Context:
@@ -145,6 +145,9 @@ class Context:
             a.spatial_k = float(v["spatial_k"]); a.k_lower = float(v["k_lower"]); a.k_upper = float(v["k_upper"])
         self._check(self._L.l3d_set_views(self._h, len(views), arr))
         self._n_views = len(views)
+
+    def set_stage_timing(self, on: bool):
+        self._check(self._L.l3d_set_stage_timing(self._h, int(bool(on))))
 
     def reset_matching(self):
         self._check(self._L.l3d_reset_matching(self._h))

@@ -79,7 +79,7 @@ void* l3dhost_open(const char* scene_path, const char* data_dir, int neighbors, 
 
 // compute3Dmodel + getResult.  stats_out: 32 doubles (see line3d_b200/host.py STAT_NAMES).
 // Returns the number of 3-D lines or < 0.
-int l3dhost_compute(void* session, int diffusion, int measure_only, int flush_l2, int keep_debug, double* wall_out, double* stats_out)
+int l3dhost_compute(void* session, int diffusion, int measure_only, int flush_l2, int keep_debug, int stage_timing, double* wall_out, double* stats_out)
 {
     Session* s = static_cast<Session*>(session);
     if (!s || !s->l3d) return -1;
@@ -88,6 +88,7 @@ int l3dhost_compute(void* session, int diffusion, int measure_only, int flush_l2
         s->l3d->setMeasureOnly(measure_only != 0);
         s->l3d->setFlushL2(flush_l2 != 0);
         s->l3d->setKeepDebug(keep_debug != 0);
+        s->l3d->setStageTiming(stage_timing != 0);
         const double t0 = now_s();
         s->l3d->compute3Dmodel(diffusion != 0);
         const double t1 = now_s();

@@ -131,8 +131,16 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* total, int* sh /
     return base + x - v;
 }
 
+// Programmatic dependent launch: every kernel of the per-view chain starts with L3D_PDL_PROLOGUE and is launched with
+// pdl_launch, so the blocks of kernel N+1 are set up on the SMs while the last blocks of kernel N still run and start
+// the moment N has finished (griddepcontrol.wait returns when the preceding grid is complete and its writes are
+// visible).  No kernel touches global memory before the prologue; launched the ordinary way the two instructions
+// do nothing.
+#define L3D_PDL_PROLOGUE() do { asm volatile("griddepcontrol.wait;" ::: "memory"); asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); } while (0)
+
 __global__ void __launch_bounds__(SCAN_T) k_scan_tiles(const int* __restrict__ in, int* __restrict__ out, int* __restrict__ tile_sums, int n)
 {
+    L3D_PDL_PROLOGUE();
     __shared__ int sh[32];
     const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
     int v[SCAN_ITEMS], s = 0;
@@ -147,6 +155,7 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_tiles(const int* __restrict__ i
 // scans the tile sums in one block (<= 4096 tiles) and writes the grand total to out_total
 __global__ void __launch_bounds__(SCAN_T) k_scan_sums(int* __restrict__ tile_sums, int n_tiles, int* __restrict__ out_total)
 {
+    L3D_PDL_PROLOGUE();
     __shared__ int sh[32];
     const int base = threadIdx.x * SCAN_ITEMS;
     int v[SCAN_ITEMS], s = 0;
@@ -162,6 +171,7 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_sums(int* __restrict__ tile_sum
 constexpr int SCAN_SMALL = 64 * 1024;
 __global__ void __launch_bounds__(SCAN_T) k_scan_small(const int* __restrict__ in, int* __restrict__ out /* n + 1 */, int n)
 {
+    L3D_PDL_PROLOGUE();
     __shared__ int sh[32];
     int carry = 0;
     // tiles of SCAN_TILE elements; the next tile's values are loaded before the current one is scanned
@@ -187,6 +197,7 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_small(const int* __restrict__ i
 }
 __global__ void __launch_bounds__(SCAN_T) k_scan_add(int* __restrict__ out, const int* __restrict__ tile_sums, int n, const int* __restrict__ total)
 {
+    L3D_PDL_PROLOGUE();
     const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
     const int add = tile_sums[blockIdx.x];
 #pragma unroll
@@ -529,6 +540,7 @@ __global__ void k_pack_results(const int* __restrict__ M, const int* __restrict_
                                const unsigned long long* __restrict__ iters, const int* __restrict__ start, int stride, int n_deliver, int seg_max,
                                int* __restrict__ out)
 {
+    L3D_PDL_PROLOGUE();
     __shared__ int sh[32];
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         out[0] = *M; out[1] = *F; out[2] = median ? __float_as_int(*median) : 0; out[3] = 0;
@@ -561,6 +573,7 @@ __global__ void k_gather_int(const int* __restrict__ src, const int* __restrict_
 // counts of the delivered records per (row, cam) for the cams in mode 1
 __global__ void k_gather_counts(const CamTable* __restrict__ cams, int n_cams, int n_src, const int* __restrict__ raw_cnt, int* __restrict__ cnt)
 {
+    L3D_PDL_PROLOGUE();
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     const int cam = blockIdx.y;
     if (row >= n_src) return;
@@ -577,6 +590,7 @@ __global__ void k_fill(const CamTable* __restrict__ cams, int n_cams, int n_src,
                        const int* __restrict__ stage_col, const float4* __restrict__ stage_dep, const unsigned char* __restrict__ stage_ok,
                        int4* __restrict__ m_ids, float4* __restrict__ m_dep)
 {
+    L3D_PDL_PROLOGUE();
     const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (gw >= n_src * n_cams) return;
     const int row = gw / n_cams, cam = gw - row * n_cams;
@@ -618,6 +632,7 @@ struct ScoreParams { float sigma_p, sigma_a; };
 // work items: (source segment, chunk of SC_T matches); order is irrelevant to the result
 __global__ void k_score_items(const int* __restrict__ off, int n_cams, int n_src, int m_lo, int m_hi, int outside, int* __restrict__ counter, int2* __restrict__ items)
 {
+    L3D_PDL_PROLOGUE();
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n_src) return;
     int m = off[(row + 1) * n_cams] - off[row * n_cams];
@@ -657,6 +672,7 @@ __global__ void __launch_bounds__(SC_T) k_score(const float4* __restrict__ segs,
                                                 const int2* __restrict__ items, const int* __restrict__ n_items,
                                                 ScoreParams sp, float* __restrict__ score)
 {
+    L3D_PDL_PROLOGUE();
     extern __shared__ int s_max[];                 // [n_cams][SC_T] best confidence per (camera, hypothesis), as int bits
     __shared__ float2 s_d[SC_TILE];
     __shared__ float2 s_yd[SC_T];
@@ -766,6 +782,7 @@ template<int MP>
 __global__ void __launch_bounds__(SS_T) k_sort_segments(const int* __restrict__ off, int n_cams, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
                                                         int m_lo, float* __restrict__ g_k, float* __restrict__ g_d2, unsigned* __restrict__ g_pl)
 {
+    L3D_PDL_PROLOGUE();
     extern __shared__ unsigned long long s_key[];
     const int row = blockIdx.x;
     const int seg_start = off[row * n_cams], M = off[(row + 1) * n_cams] - seg_start;
@@ -803,6 +820,7 @@ __global__ void __launch_bounds__(SC_T) k_score_window(const float4* __restrict_
                                                        const int2* __restrict__ items, const int* __restrict__ n_items,
                                                        ScoreParams sp, float* __restrict__ score)
 {
+    L3D_PDL_PROLOGUE();
     extern __shared__ int s_max[];                 // [n_cams][SC_T]
     __shared__ float2 s_yd[SC_T];
     __shared__ unsigned s_q[SC_WARPS][SC_QCAP];
@@ -873,6 +891,7 @@ __global__ void k_seg_reduce(const int* __restrict__ off, int n_cams, int n_src,
                              const float4* __restrict__ m_dep, int* __restrict__ fcnt, float* __restrict__ dsamples,
                              unsigned long long* __restrict__ iters /* [0] all pairs, [1] same-camera pairs */)
 {
+    L3D_PDL_PROLOGUE();
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (row >= n_src) return;
     const int s0 = off[row * n_cams], s1 = off[(row + 1) * n_cams];
@@ -912,6 +931,7 @@ __global__ void k_seg_reduce(const int* __restrict__ off, int n_cams, int n_src,
 constexpr int MED_CHUNK = 512;
 __global__ void k_median_rank(const float* __restrict__ dsamples, int n, int* __restrict__ less, int* __restrict__ leq, int* __restrict__ cnt)
 {
+    L3D_PDL_PROLOGUE();
     __shared__ float s[MED_CHUNK];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int t0 = blockIdx.y * MED_CHUNK;
@@ -931,6 +951,7 @@ __global__ void k_median_rank(const float* __restrict__ dsamples, int n, int* __
 __global__ void k_median_pick(const float* __restrict__ dsamples, int n, const int* __restrict__ less, const int* __restrict__ leq,
                               const int* __restrict__ cnt, float* __restrict__ out)
 {
+    L3D_PDL_PROLOGUE();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0 && *cnt == 0) out[0] = -1.0f;
     if (i >= n) return;
@@ -945,6 +966,7 @@ __global__ void k_filter_fill(const int* __restrict__ off, int n_cams, int n_src
                               const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, const int* __restrict__ foff,
                               l3d_match* __restrict__ out)
 {
+    L3D_PDL_PROLOGUE();
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (row >= n_src) return;
     const int s0 = off[row * n_cams], s1 = off[(row + 1) * n_cams];
@@ -973,6 +995,7 @@ __global__ void k_filter_fill(const int* __restrict__ off, int n_cams, int n_src
 // unscored variant (no neighbour to pair-test): all records, confidence 0
 __global__ void k_copy_unscored(const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, const int* __restrict__ Mptr, l3d_match* __restrict__ out)
 {
+    L3D_PDL_PROLOGUE();
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= *Mptr) return;
     int4 id = m_ids[k]; float4 d = m_dep[k];
@@ -987,6 +1010,7 @@ __global__ void k_copy_unscored(const int4* __restrict__ m_ids, const float4* __
 // ------------------------------------------------------------------------------------------
 __global__ void k_deliver_hist(const l3d_match* __restrict__ f, const int* __restrict__ Fptr, const CamTable* __restrict__ cams, int stride, int* __restrict__ hist)
 {
+    L3D_PDL_PROLOGUE();
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= *Fptr) return;
     const int d = cams[f[k].cam].deliver;
@@ -995,6 +1019,7 @@ __global__ void k_deliver_hist(const l3d_match* __restrict__ f, const int* __res
 __global__ void k_deliver_scatter(const l3d_match* __restrict__ f, const int* __restrict__ Fptr, const CamTable* __restrict__ cams, int stride,
                                   const int* __restrict__ start, int* __restrict__ cursor, int* __restrict__ t_tgt, float4* __restrict__ t_dep)
 {
+    L3D_PDL_PROLOGUE();
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= *Fptr) return;
     const l3d_match m = f[k];
@@ -1010,6 +1035,7 @@ __global__ void k_deliver_scatter(const l3d_match* __restrict__ f, const int* __
 __global__ void k_deliver_place(const int* __restrict__ start, int n_keys, const int* __restrict__ tmp_tgt, const float4* __restrict__ tmp_dep,
                                 int* __restrict__ t_tgt, float4* __restrict__ t_dep)
 {
+    L3D_PDL_PROLOGUE();
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     const int total = start[n_keys];
     if (k >= total) return;
@@ -1337,6 +1363,8 @@ struct l3d_ctx {
     DBuf<int> d_vres[2]; HBuf<int> h_vres[2]; HBuf<CamTable> h_cams2[2]; DBuf<l3d_match> d_filtered2[2];
     cudaEvent_t vev[2][6] = {{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
     cudaStream_t copy_stream = nullptr;
+    bool stage_events = false;         // per-stage CUDA events inside a view (l3d_set_stage_timing): they separate kernels that otherwise overlap
+    cudaEvent_t mark_ev[2] = {nullptr, nullptr};
     // retained results (l3d_retain_results): pinned chunks that are never moved, handed out front to back
     bool retain = false; std::vector<std::pair<l3d_match*, size_t> > arena; size_t arena_chunk = 0, arena_used = 0;
     DBuf<int> d_hist, d_hstart, d_cursor;
@@ -1354,10 +1382,23 @@ struct l3d_ctx {
 
 namespace {
 
+template <typename K, typename... Args>
+inline cudaError_t pdl_launch(K kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
 int scan_exclusive(l3d_ctx* ctx, const int* in, int* out /* n + 1 */, int n)
 {
     if (n <= SCAN_SMALL) {
-        k_scan_small<<<1, SCAN_T, 0, ctx->stream>>>(in, out, n);
+        L3D_CUDA(pdl_launch(k_scan_small, dim3(1), dim3(SCAN_T), 0, ctx->stream, in, out, n));
         ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
         return 0;
@@ -1366,9 +1407,9 @@ int scan_exclusive(l3d_ctx* ctx, const int* in, int* out /* n + 1 */, int n)
     if (tiles > SCAN_TILE) { ctx->err = "scan: input too long"; return 1; }
     L3D_CUDA(ctx->d_tile_sums.ensure(size_t(std::max(tiles, 1))));
     L3D_CUDA(ctx->d_total.ensure(1));
-    k_scan_tiles<<<std::max(tiles, 1), SCAN_T, 0, ctx->stream>>>(in, out, ctx->d_tile_sums.p, n);
-    k_scan_sums<<<1, SCAN_T, 0, ctx->stream>>>(ctx->d_tile_sums.p, tiles, ctx->d_total.p);
-    k_scan_add<<<std::max(tiles, 1), SCAN_T, 0, ctx->stream>>>(out, ctx->d_tile_sums.p, n, ctx->d_total.p);
+    L3D_CUDA(pdl_launch(k_scan_tiles, dim3(std::max(tiles, 1)), dim3(SCAN_T), 0, ctx->stream, in, out, ctx->d_tile_sums.p, n));
+    L3D_CUDA(pdl_launch(k_scan_sums, dim3(1), dim3(SCAN_T), 0, ctx->stream, ctx->d_tile_sums.p, tiles, ctx->d_total.p));
+    L3D_CUDA(pdl_launch(k_scan_add, dim3(std::max(tiles, 1)), dim3(SCAN_T), 0, ctx->stream, out, ctx->d_tile_sums.p, n, ctx->d_total.p));
     ctx->launches += 3;
     L3D_CUDA(cudaGetLastError());
     return 0;
@@ -1549,12 +1590,12 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     L3D_CUDA(cudaMemcpyAsync(ctx->d_cams.p, hc.p, sizeof(CamTable) * n_nb, cudaMemcpyHostToDevice, st));
     L3D_CUDA(ctx->d_cnt.ensure(size_t(n_src) * n_nb + 1));
     L3D_CUDA(ctx->d_off.ensure(size_t(n_src) * n_nb + 2));
-    L3D_CUDA(cudaEventRecord(ev[2], st));
+    if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[2], st));
 
     // ---- assemble the match list ----------------------------------------------------------
     const int* d_M = ctx->d_off.p + size_t(n_src) * n_nb;             // total number of matches, on the device
     if (n_src > 0) {
-        k_gather_counts<<<dim3((n_src + 255) / 256, n_nb), 256, 0, st>>>(ctx->d_cams.p, n_nb, n_src, ctx->d_pa_raw.p, ctx->d_cnt.p);
+        L3D_CUDA(pdl_launch(k_gather_counts, dim3(dim3((n_src + 255) / 256, n_nb)), dim3(256), 0, st, ctx->d_cams.p, n_nb, n_src, ctx->d_pa_raw.p, ctx->d_cnt.p));
         ctx->launches += 1;
         if (scan_exclusive(ctx, ctx->d_cnt.p, ctx->d_off.p, n_src * n_nb)) return 1;
     } else {
@@ -1563,12 +1604,12 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     if (M_ub > 0) {
         L3D_CUDA(ctx->d_mids.ensure(M_ub)); L3D_CUDA(ctx->d_mdep.ensure(M_ub)); L3D_CUDA(ctx->d_score.ensure(M_ub));
         const long warps = long(n_src) * n_nb;
-        k_fill<<<unsigned((warps * 32 + 255) / 256), 256, 0, st>>>(ctx->d_cams.p, n_nb, n_src, ctx->d_off.p, ctx->d_pa_off.p,
-                                                                  ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_stage_ok.p, ctx->d_mids.p, ctx->d_mdep.p);
+        L3D_CUDA(pdl_launch(k_fill, dim3(unsigned((warps * 32 + 255) / 256)), dim3(256), 0, st, ctx->d_cams.p, n_nb, n_src, ctx->d_off.p, ctx->d_pa_off.p,
+                                                                  ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_stage_ok.p, ctx->d_mids.p, ctx->d_mdep.p));
         ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
     }
-    L3D_CUDA(cudaEventRecord(ev[3], st));
+    if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[3], st));
 
     const bool scored = n_slots > 0;                  // cudawrapper.cu:877-878
     const int* d_F = nullptr;                         // number of output records, on the device
@@ -1607,44 +1648,44 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         if (windowed) {
             L3D_CUDA(ctx->d_sk.ensure(M_ub)); L3D_CUDA(ctx->d_sd2.ensure(M_ub)); L3D_CUDA(ctx->d_spl.ensure(M_ub));
             if (!ctx->sort_attr_set) { L3D_CUDA(cudaFuncSetAttribute(k_sort_segments<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8)); ctx->sort_attr_set = true; }
-            k_sort_segments<2048><<<n_src, SS_T, 2048 * 8, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, 0, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
+            L3D_CUDA(pdl_launch(k_sort_segments<2048>, dim3(n_src), dim3(SS_T), 2048 * 8, st, ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, 0, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p));
             ctx->launches += 1;
             if (seg_ub > size_t(SORT_SMALL)) {
-                k_sort_segments<8192><<<n_src, SS_T, 8192 * 8, st>>>(ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_SMALL, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p);
+                L3D_CUDA(pdl_launch(k_sort_segments<8192>, dim3(n_src), dim3(SS_T), 8192 * 8, st, ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_SMALL, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p));
                 ctx->launches += 1;
             }
-            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, 0, SORT_MAX, 0, d_nitems, ctx->d_items.p);
-            k_score_window<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
-                                                             ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_items.p, d_nitems, sp, ctx->d_score.p);
+            L3D_CUDA(pdl_launch(k_score_items, dim3((n_src + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, 0, SORT_MAX, 0, d_nitems, ctx->d_items.p));
+            L3D_CUDA(pdl_launch(k_score_window, dim3(max_items), dim3(SC_T), sm_bytes, st, ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
+                                                             ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_items.p, d_nitems, sp, ctx->d_score.p));
             ctx->launches += 2;
         }
         if (!windowed || seg_ub > size_t(SORT_MAX)) {
-            k_score_items<<<(n_src + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, windowed ? 0 : 0x7fffffff, windowed ? SORT_MAX : 0x7fffffff, 1,
-                                                              d_nitems + 1, ctx->d_items.p + max_items);
-            k_score<<<max_items, SC_T, sm_bytes, st>>>(ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
-                                                      ctx->d_items.p + max_items, d_nitems + 1, sp, ctx->d_score.p);
+            L3D_CUDA(pdl_launch(k_score_items, dim3((n_src + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, windowed ? 0 : 0x7fffffff, windowed ? SORT_MAX : 0x7fffffff, 1,
+                                                              d_nitems + 1, ctx->d_items.p + max_items));
+            L3D_CUDA(pdl_launch(k_score, dim3(max_items), dim3(SC_T), sm_bytes, st, ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
+                                                      ctx->d_items.p + max_items, d_nitems + 1, sp, ctx->d_score.p));
             ctx->launches += 2;
         }
         L3D_CUDA(cudaGetLastError());
-        L3D_CUDA(cudaEventRecord(ev[4], st));
+        if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[4], st));
         // ---- reduce -----------------------------------------------------------------------
-        k_seg_reduce<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, d_iters);
+        L3D_CUDA(pdl_launch(k_seg_reduce, dim3((n_src * 32 + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, d_iters));
         {
             int* less = ctx->d_zero.p + z_rank; int* leq = less + ns; int* cnt = leq + ns;
-            k_median_rank<<<dim3((ns + 127) / 128, (ns + MED_CHUNK - 1) / MED_CHUNK), 128, 0, st>>>(ctx->d_dsamples.p, ns, less, leq, cnt);
-            k_median_pick<<<(ns + 255) / 256, 256, 0, st>>>(ctx->d_dsamples.p, ns, less, leq, cnt, ctx->d_median.p);
+            L3D_CUDA(pdl_launch(k_median_rank, dim3(dim3((ns + 127) / 128, (ns + MED_CHUNK - 1) / MED_CHUNK)), dim3(128), 0, st, ctx->d_dsamples.p, ns, less, leq, cnt));
+            L3D_CUDA(pdl_launch(k_median_pick, dim3((ns + 255) / 256), dim3(256), 0, st, ctx->d_dsamples.p, ns, less, leq, cnt, ctx->d_median.p));
         }
         ctx->launches += 3;
         if (scan_exclusive(ctx, ctx->d_fcnt.p, ctx->d_foff.p, n_src)) return 1;
         d_F = ctx->d_foff.p + n_src;
-        k_filter_fill<<<(n_src * 32 + 255) / 256, 256, 0, st>>>(ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, dfil.p);
+        L3D_CUDA(pdl_launch(k_filter_fill, dim3((n_src * 32 + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, dfil.p));
         ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
     } else {
-        L3D_CUDA(cudaEventRecord(ev[4], st));
+        if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[4], st));
         d_F = d_M;
         if (!scored && M_ub > 0) {
-            k_copy_unscored<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(ctx->d_mids.p, ctx->d_mdep.p, d_M, dfil.p);
+            L3D_CUDA(pdl_launch(k_copy_unscored, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, ctx->d_mids.p, ctx->d_mdep.p, d_M, dfil.p));
             ctx->launches += 1;
             L3D_CUDA(cudaGetLastError());
         }
@@ -1657,12 +1698,12 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         L3D_CUDA(cudaMallocAsync(&buf.start, sizeof(int) * (size_t(n_keys) + 2), st));
         L3D_CUDA(cudaMallocAsync(&buf.tgt, sizeof(int) * std::max<size_t>(M_ub, 1), st));
         L3D_CUDA(cudaMallocAsync(&buf.dep, sizeof(float4) * std::max<size_t>(M_ub, 1), st));
-        if (M_ub > 0) { k_deliver_hist<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(dfil.p, d_F, ctx->d_cams.p, stride, d_hist); ctx->launches += 1; }
+        if (M_ub > 0) { L3D_CUDA(pdl_launch(k_deliver_hist, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, dfil.p, d_F, ctx->d_cams.p, stride, d_hist)); ctx->launches += 1; }
         if (scan_exclusive(ctx, d_hist, buf.start, n_keys)) return 1;
         if (M_ub > 0) {
             L3D_CUDA(ctx->d_dl_tgt.ensure(M_ub)); L3D_CUDA(ctx->d_dl_dep.ensure(M_ub));
-            k_deliver_scatter<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(dfil.p, d_F, ctx->d_cams.p, stride, buf.start, d_cursor, ctx->d_dl_tgt.p, ctx->d_dl_dep.p);
-            k_deliver_place<<<unsigned((M_ub + 255) / 256), 256, 0, st>>>(buf.start, n_keys, ctx->d_dl_tgt.p, ctx->d_dl_dep.p, buf.tgt, buf.dep);
+            L3D_CUDA(pdl_launch(k_deliver_scatter, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, dfil.p, d_F, ctx->d_cams.p, stride, buf.start, d_cursor, ctx->d_dl_tgt.p, ctx->d_dl_dep.p));
+            L3D_CUDA(pdl_launch(k_deliver_place, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, buf.start, n_keys, ctx->d_dl_tgt.p, ctx->d_dl_dep.p, buf.tgt, buf.dep));
             ctx->launches += 2;
         }
         L3D_CUDA(cudaGetLastError());
@@ -1670,11 +1711,11 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     // ---- results: one kernel packs them, one copy; the host collects them in finish_view ----------------
     const int n_res = 8 + 2 * std::max(n_deliver, 1);
     L3D_CUDA(ctx->d_vres[par].ensure(size_t(n_res))); L3D_CUDA(ctx->h_vres[par].ensure(size_t(n_res)));
-    k_pack_results<<<std::max(delivering ? n_deliver : 0, 1), 256, 0, st>>>(d_M, d_F, (scored && M_ub > 0) ? ctx->d_median.p : nullptr, (scored && M_ub > 0) ? d_iters : nullptr,
-                                                                          delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, max_deliver_seg, ctx->d_vres[par].p);
+    L3D_CUDA(pdl_launch(k_pack_results, dim3(std::max(delivering ? n_deliver : 0, 1)), dim3(256), 0, st, d_M, d_F, (scored && M_ub > 0) ? ctx->d_median.p : nullptr, (scored && M_ub > 0) ? d_iters : nullptr,
+                                                                          delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, max_deliver_seg, ctx->d_vres[par].p));
     ctx->launches += 1;
     L3D_CUDA(cudaGetLastError());
-    L3D_CUDA(cudaEventRecord(ev[5], st));
+    if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[5], st));
     L3D_CUDA(cudaMemcpyAsync(ctx->h_vres[par].p, ctx->d_vres[par].p, sizeof(int) * size_t(n_res), cudaMemcpyDeviceToHost, st));
     L3D_CUDA(cudaEventRecord(ev[0], st));
     job.M_ub = M_ub; job.scored = scored; job.delivering = delivering; job.n_deliver = n_deliver;
@@ -1768,7 +1809,7 @@ int finish_view(l3d_ctx* ctx, ViewJob& job, l3d_match_result* res, bool copy_bac
         for (int k = 0; k < 2; ++k) { ms = 0.f; if (ctx->pa_kev_set[k]) cudaEventElapsedTime(&ms, ctx->pa_kev[2 * k], ctx->pa_kev[2 * k + 1]); ctx->pa_kernel_ms[k] = ms; }
         ctx->pa_ms_pending = false;
     }
-    for (int k = 2; k < 5; ++k) { ms = 0.f; cudaEventElapsedTime(&ms, ctx->vev[par][k], ctx->vev[par][k + 1]); ctx->last_ms[k] = ms; }
+    for (int k = 2; k < 5; ++k) { ms = 0.f; if (ctx->stage_events) cudaEventElapsedTime(&ms, ctx->vev[par][k], ctx->vev[par][k + 1]); ctx->last_ms[k] = ms; }
     ctx->last_ms[5] = ctx->last_ms[0] + ctx->last_ms[1] + ctx->last_ms[2] + ctx->last_ms[3] + ctx->last_ms[4];
     return 0;
 }
@@ -1863,6 +1904,7 @@ int l3d_create(int device, l3d_ctx** out)
     for (int q = 0; q < 2; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->vev[q][k]);
     if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); cudaStreamDestroy(ctx->stream); delete ctx; return 1; }
     for (int k = 0; k < 3; ++k) cudaEventCreate(&ctx->pa_ev[k]);
+    for (int k = 0; k < 2; ++k) cudaEventCreate(&ctx->mark_ev[k]);
     for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->pa_kev[k]);
     *out = ctx;
     return 0;
@@ -1899,6 +1941,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release();
     ctx->d_rm_begin.release(); ctx->d_rm_len.release(); ctx->d_rm_out.release(); ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->d_zero.release(); ctx->h_res.release();
     for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]);
+    for (int k = 0; k < 2; ++k) if (ctx->mark_ev[k]) cudaEventDestroy(ctx->mark_ev[k]);
     for (int k = 0; k < 4; ++k) if (ctx->pa_kev[k]) cudaEventDestroy(ctx->pa_kev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
@@ -2172,6 +2215,32 @@ int l3d_last_timings(l3d_ctx* ctx, float ms[6])
 {
     if (!ctx || !ms) return 1;
     for (int k = 0; k < 6; ++k) ms[k] = ctx->last_ms[k];
+    return 0;
+}
+
+int l3d_set_stage_timing(l3d_ctx* ctx, int on)
+{
+    if (!ctx) return 1;
+    cudaSetDevice(ctx->device);
+    drain_pending(ctx);
+    ctx->stage_events = on != 0;
+    return 0;
+}
+
+int l3d_mark(l3d_ctx* ctx, int which)
+{
+    if (!ctx || which < 0 || which > 1) return 1;
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    L3D_CUDA(cudaEventRecord(ctx->mark_ev[which], ctx->stream));
+    return 0;
+}
+
+int l3d_marks_elapsed(l3d_ctx* ctx, float* ms)
+{
+    if (!ctx || !ms) return 1;
+    L3D_CUDA(cudaSetDevice(ctx->device));
+    L3D_CUDA(cudaEventSynchronize(ctx->mark_ev[1]));
+    L3D_CUDA(cudaEventElapsedTime(ms, ctx->mark_ev[0], ctx->mark_ev[1]));
     return 0;
 }
 

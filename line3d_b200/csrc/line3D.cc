@@ -112,7 +112,7 @@ std::string cacheName(const std::string& dir, unsigned id, unsigned w, unsigned 
 
 struct Line3D::Impl
 {
-    bool verbose, computation, use_collinearity, measure_only, flush_l2, keep_debug;
+    bool verbose, computation, use_collinearity, measure_only, flush_l2, keep_debug, stage_timing;
     std::string prefix, separator, data_directory;
     int matching_neighbors; float min_baseline, unc_upper, unc_lower, sigma_p, sigma_a;
     int shard_rank, shard_world; std::set<unsigned> my_views;
@@ -424,6 +424,7 @@ struct Line3D::Impl
         // t_matching is the wall time of this whole function: the library runs a view ahead of the host, so the time
         // spent inside the calls alone (t_matching_calls) would leave out the host's own share of the loop
         const double t_match0 = now_s();
+        if (l3d_set_stage_timing(ctx, stage_timing ? 1 : 0) || l3d_mark(ctx, 0)) fail("l3d_set_stage_timing");
         // Which neighbours a view pair-tests and to which it hands its matches depends only on the
         // neighbour graph and the view order (line3D.cc:732-736, 844-845, 875-881): work the whole
         // schedule out first and announce it, so the library can batch the pair tests.
@@ -471,7 +472,7 @@ struct Line3D::Impl
                                   : l3d_match_view(ctx, v->index, int(nb.size()), nb.data(), sigma_p, sigma_a, &res);
             if (rc) fail("l3d_match_view");
             stats.t_matching_calls += now_s() - t0;
-            float ms[6]; l3d_last_timings(ctx, ms); stats.t_matching_device += double(ms[5]) * 1e-3;
+            float ms[6]; l3d_last_timings(ctx, ms);
             for (int k = 0; k < 5; ++k) stats.t_stage[k] += double(ms[k]) * 1e-3;
             if (ms[0] > 0.f) { float km[2]; l3d_last_kernel_timings(ctx, km); stats.t_k_pretest += double(km[0]) * 1e-3; stats.t_k_exact += double(km[1]) * 1e-3; }
             stats.score_iters_other_cam += res.score_iters_other_cam;
@@ -497,6 +498,7 @@ struct Line3D::Impl
                 if (neighbour_of(n, vid)) matched[n].insert(vid);
             }
         }
+        { float span = 0.f; if (l3d_mark(ctx, 1) || l3d_marks_elapsed(ctx, &span)) fail("l3d_mark"); stats.t_matching_device += double(span) * 1e-3; }   // CUDA events around the whole loop
         stats.t_matching += now_s() - t_match0;
     }
 
@@ -889,7 +891,7 @@ Line3D::Line3D(const std::string data_directory, const int matchingNeighbors, co
     d.verbose = verbose; d.prefix = "[L3D] "; d.separator = "----------------------------------------";
     d.data_directory = data_directory; d.matching_neighbors = matchingNeighbors;
     d.unc_upper = fabs(uncertainty_t_upper_2D); d.unc_lower = fabs(uncertainty_t_lower_2D);              // line3D.cc:18-28
-    d.computation = false; d.use_collinearity = useCollinearity; d.min_baseline = min_baseline; d.measure_only = false; d.flush_l2 = false; d.keep_debug = false;
+    d.computation = false; d.use_collinearity = useCollinearity; d.min_baseline = min_baseline; d.measure_only = false; d.flush_l2 = false; d.keep_debug = false; d.stage_timing = false;
     if (d.unc_lower < 1.0f) d.unc_lower = 1.0f;
     if (d.unc_upper <= d.unc_lower) d.unc_upper = d.unc_lower + 1.0f;
     d.sigma_a = sigma_a; d.sigma_p = sigma_p;
@@ -987,6 +989,7 @@ unsigned int Line3D::numCameras() { return impl_->views.size(); }
 L3DRunStats Line3D::runStats() const { return impl_->stats; }
 void Line3D::setMeasureOnly(bool on) { impl_->measure_only = on; }
 void Line3D::setFlushL2(bool on) { impl_->flush_l2 = on; }
+void Line3D::setStageTiming(bool on) { impl_->stage_timing = on; }
 void Line3D::setKeepDebug(bool on) { impl_->keep_debug = on; }
 void Line3D::resetGeometry()
 {

@@ -144,6 +144,7 @@ namespace L3D
         void setShard(int rank, int world);
         // keep the per-match records debugDump() writes (off by default: they are large)
         void setKeepDebug(bool on);
+        void setStageTiming(bool on);   // per-stage device times in runStats().t_stage (slows matching by about 13 %)
 
     private:
         struct Impl;

@@ -37,7 +37,7 @@ def lib():
         L.l3dhost_open.restype = C.c_void_p
         L.l3dhost_open.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int]
         L.l3dhost_compute.restype = C.c_int
-        L.l3dhost_compute.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.l3dhost_compute.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.l3dhost_reset_geometry.restype = C.c_int; L.l3dhost_reset_geometry.argtypes = [C.c_void_p]
         L.l3dhost_set_shard.restype = C.c_int; L.l3dhost_set_shard.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.l3dhost_dump.restype = C.c_int; L.l3dhost_dump.argtypes = [C.c_void_p, C.c_char_p]
@@ -61,14 +61,14 @@ class Session:
             shutil.rmtree(self._data_dir, ignore_errors=True)
             raise capi.L3DError("l3dhost_open failed (no CUDA device, or unreadable scene)")
 
-    def compute(self, measure_only: bool = False, flush_l2: bool = False, diffusion: bool | None = None, keep_debug: bool = False, fresh: bool = True):
+    def compute(self, measure_only: bool = False, flush_l2: bool = False, diffusion: bool | None = None, keep_debug: bool = False, fresh: bool = True, stage_timing: bool = False):
         """fresh: put the cameras back to their original poses first, so that every call sees the same input (a repeated
         compute3Dmodel otherwise re-normalises the normalised scene, as the reference does)."""
         if fresh:
             lib().l3dhost_reset_geometry(self._h)
         wall = (C.c_double * 2)(); st = (C.c_double * 32)()
         dif = self.params["diffusion"] if diffusion is None else diffusion
-        n = lib().l3dhost_compute(self._h, int(bool(dif)), int(measure_only), int(flush_l2), int(keep_debug), wall, st)
+        n = lib().l3dhost_compute(self._h, int(bool(dif)), int(measure_only), int(flush_l2), int(keep_debug), int(stage_timing), wall, st)
         if n < 0:
             raise capi.L3DError(f"l3dhost_compute failed with code {n}")
         stats = dict(zip(STAT_NAMES, [float(x) for x in st]))
