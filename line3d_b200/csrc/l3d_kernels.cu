@@ -773,50 +773,78 @@ __global__ void __launch_bounds__(SC_T) k_score(const float4* __restrict__ segs,
 // One CTA per source segment with lo < M <= MP matches; the segment is sorted once in shared
 // memory (bitonic, key d1, payload d2 + camera + original index).
 // ------------------------------------------------------------------------------------------
-constexpr int SS_T = 256;
+// Grouping the matches of a segment by depth, for the windowed scoring.  A hypothesis can only be supported by matches
+// whose first depth lies within a small relative window of its own (the 3-D gate, see k_score_window), so each
+// segment's matches are distributed over BK_B buckets by d1 -- a counting sort: three barriers per segment whatever
+// its length, where a comparison sort of the longest segments took 66 barrier-separated steps and set the kernel's
+// duration.  The bucket of a depth is linear in the bit pattern of the float between the segment's smallest and
+// largest d1 (positive floats order like unsigned integers, and the pattern is a piecewise-linear log2, which suits
+// a window that is relative): monotonic, so the buckets a window touches are the buckets of its two ends.  The
+// order inside a bucket is whatever the atomics give; the scores do not depend on it (per-camera maxima).
+// Output: (d1, d2, camera << 20 | index) at the segment's own offsets in bucket order, the bucket boundaries, and
+// (bits of min d1, bits of max d1, scale) per segment.
+constexpr int BK_T = 128;
+constexpr int BK_B = 128;
+__device__ __forceinline__ int depth_bucket(unsigned bits, unsigned bits_min, float scale)
+{
+    return min(BK_B - 1, int(float(bits - bits_min) * scale));
+}
 
-// sorts the matches of every segment with m_lo < M <= MP by d1 and writes (d1, d2, camera << 20 | index) to global
-// arrays at the segment's own offsets.  Sorted in shared memory as one 64-bit word per match: the bits of d1 (positive
-// floats order like unsigned integers) above the match's index within the segment.
-template<int MP>
-__global__ void __launch_bounds__(SS_T) k_sort_segments(const int* __restrict__ off, int n_cams, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
-                                                        int m_lo, float* __restrict__ g_k, float* __restrict__ g_d2, unsigned* __restrict__ g_pl)
+__global__ void __launch_bounds__(BK_T) k_bucket_segments(const int* __restrict__ off, int n_cams, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
+                                                          float* __restrict__ g_k, float* __restrict__ g_d2, unsigned* __restrict__ g_pl,
+                                                          int* __restrict__ g_boff /* [n_src][BK_B + 1] */, uint4* __restrict__ g_brange)
 {
     L3D_PDL_PROLOGUE();
-    extern __shared__ unsigned long long s_key[];
-    const int row = blockIdx.x;
+    __shared__ int s_cnt[BK_B], s_start[BK_B + 1];
+    __shared__ unsigned s_lo[BK_T / 32], s_hi[BK_T / 32];
+    const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int seg_start = off[row * n_cams], M = off[(row + 1) * n_cams] - seg_start;
-    if (M <= m_lo || M > MP) return;
-    const int tid = threadIdx.x;
-    int mp = 32; while (mp < M) mp <<= 1;
-    for (int i = tid; i < mp; i += SS_T)
-        s_key[i] = (i < M) ? ((unsigned long long)__float_as_uint(m_dep[seg_start + i].x) << 32) | (unsigned)i : ~0ull;
+    if (M <= 0) return;
+    unsigned lo = 0xffffffffu, hi = 0u;
+    for (int i = tid; i < M; i += BK_T) { const unsigned b = __float_as_uint(m_dep[seg_start + i].x); lo = min(lo, b); hi = max(hi, b); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+    if (lane == 0) { s_lo[warp] = lo; s_hi[warp] = hi; }
+    s_cnt[tid] = 0;
     __syncthreads();
-    for (int k = 2; k <= mp; k <<= 1)
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = tid; t < (mp >> 1); t += SS_T) {
-                // t-th compare-exchange pair of this step: i has bit j clear
-                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), l = i | j;
-                const unsigned long long a = s_key[i], b = s_key[l];
-                const bool up = ((i & k) == 0);
-                if ((a > b) == up) { s_key[i] = b; s_key[l] = a; }
-            }
-            __syncthreads();
-        }
-    for (int i = tid; i < M; i += SS_T) {
-        const unsigned long long kv = s_key[i];
-        const unsigned idx = unsigned(kv & 0xffffffffu);
-        g_k[seg_start + i] = __uint_as_float(unsigned(kv >> 32));
-        g_d2[seg_start + i] = m_dep[seg_start + idx].y;
-        g_pl[seg_start + i] = (unsigned(m_ids[seg_start + idx].y) << 20) | idx;
+#pragma unroll
+    for (int w = 0; w < BK_T / 32; ++w) { lo = min(lo, s_lo[w]); hi = max(hi, s_hi[w]); }
+    const float scale = float(BK_B) / (float(hi - lo) + 1.0f);
+    for (int i = tid; i < M; i += BK_T) atomicAdd(&s_cnt[depth_bucket(__float_as_uint(m_dep[seg_start + i].x), lo, scale)], 1);
+    __syncthreads();
+    if (warp == 0) {                               // exclusive scan of the BK_B counts: 4 per lane
+        int c[BK_B / 32], sum = 0;
+#pragma unroll
+        for (int r = 0; r < BK_B / 32; ++r) { c[r] = s_cnt[lane * (BK_B / 32) + r]; sum += c[r]; }
+        int ex = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, ex, o); if (lane >= o) ex += t; }
+        ex -= sum;
+#pragma unroll
+        for (int r = 0; r < BK_B / 32; ++r) { s_start[lane * (BK_B / 32) + r] = ex; ex += c[r]; }
+        if (lane == 31) s_start[BK_B] = ex;
+    }
+    __syncthreads();
+    int* boff = g_boff + size_t(row) * (BK_B + 1);
+    boff[tid] = s_start[tid];
+    if (tid == 0) { boff[BK_B] = s_start[BK_B]; g_brange[row] = make_uint4(lo, hi, __float_as_uint(scale), 0u); }
+    s_cnt[tid] = 0;                                // now the fill cursors
+    __syncthreads();
+    for (int i = tid; i < M; i += BK_T) {
+        const float4 d = m_dep[seg_start + i];
+        const int bk = depth_bucket(__float_as_uint(d.x), lo, scale);
+        const int pos = seg_start + s_start[bk] + atomicAdd(&s_cnt[bk], 1);
+        g_k[pos] = d.x; g_d2[pos] = d.y;
+        g_pl[pos] = (unsigned(m_ids[seg_start + i].y) << 20) | unsigned(i);
     }
 }
 
-// work items (segment, chunk of SC_T hypotheses) as in k_score; the partners of a hypothesis are the
-// window of the segment's d1-sorted list found by binary search
+// work items (segment, chunk of SC_T hypotheses) as in k_score; the partners of a hypothesis are looked for in the
+// depth buckets its window touches
 __global__ void __launch_bounds__(SC_T) k_score_window(const float4* __restrict__ segs, const CamTable* __restrict__ cams, int n_cams, SrcTable src,
                                                        const int* __restrict__ off, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
                                                        const float* __restrict__ g_k, const float* __restrict__ g_d2, const unsigned* __restrict__ g_pl,
+                                                       const int* __restrict__ g_boff, const uint4* __restrict__ g_brange,
                                                        const int2* __restrict__ items, const int* __restrict__ n_items,
                                                        ScoreParams sp, float* __restrict__ score)
 {
@@ -846,11 +874,13 @@ __global__ void __launch_bounds__(SC_T) k_score_window(const float4* __restrict_
     int j = 0, jend = 0;
     if (live) {        // slightly widened window; the exact fabsf tests follow
         const float lo = my_d.x - thr1 * 1.001f - 1e-30f, hi = my_d.x + thr1 * 1.001f + 1e-30f;
-        int a = 0, b = M;
-        while (a < b) { const int mid = (a + b) >> 1; if (K[mid] < lo) a = mid + 1; else b = mid; }
-        j = a; b = M;
-        while (a < b) { const int mid = (a + b) >> 1; if (K[mid] <= hi) a = mid + 1; else b = mid; }
-        jend = a;
+        const uint4 br = g_brange[row];
+        const float dmin = __uint_as_float(br.x), dmax = __uint_as_float(br.y), scale = __uint_as_float(br.z);
+        if (hi >= dmin && lo <= dmax) {
+            const int* boff = g_boff + size_t(row) * (BK_B + 1);
+            j = boff[depth_bucket(__float_as_uint(fmaxf(lo, dmin)), br.x, scale)];
+            jend = boff[depth_bucket(__float_as_uint(fminf(hi, dmax)), br.x, scale) + 1];
+        }
     }
     __syncwarp();
     unsigned* q = s_q[warp];
@@ -1347,7 +1377,7 @@ struct l3d_ctx {
     DBuf<int> d_cnt, d_off;
     DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
     DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
-    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; bool sort_attr_set = false; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl; DBuf<int> d_dl_tgt; DBuf<float4> d_dl_dep;
+    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl; DBuf<int> d_dl_tgt; DBuf<float4> d_dl_dep; DBuf<int> d_boff; DBuf<uint4> d_brange; int n_sm = 148;
     // phase A (pair tests) of the resident batch
     DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
     std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands; std::vector<int> job_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
@@ -1631,10 +1661,9 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         ScoreParams sp; sp.sigma_p = sigma_p; sp.sigma_a = sigma_a;
         L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_src) + 1)); L3D_CUDA(ctx->d_foff.ensure(size_t(n_src) + 2));
         L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2));
-        // Segments with up to SORT_MAX matches are sorted by depth and scored through windows; longer ones (they do
-        // not fit the sort's shared memory) and everything when the 3-D gate is switched off go through the tiled
-        // quadratic kernel.
-        const int SORT_SMALL = 2048, SORT_MAX = 8192;
+        // Segments are grouped by depth and scored through windows; the tiled quadratic kernel takes everything when
+        // the 3-D gate is switched off, and segments with more matches than the window kernel's 20-bit index can hold.
+        const int SORT_MAX = 1 << 20;
         const bool windowed = src.spatial_k > 0.0f;
         const int max_items = int(M_ub / SC_T) + n_src + 1;
         L3D_CUDA(ctx->d_items.ensure(size_t(2 * max_items)));
@@ -1647,16 +1676,13 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         }
         if (windowed) {
             L3D_CUDA(ctx->d_sk.ensure(M_ub)); L3D_CUDA(ctx->d_sd2.ensure(M_ub)); L3D_CUDA(ctx->d_spl.ensure(M_ub));
-            if (!ctx->sort_attr_set) { L3D_CUDA(cudaFuncSetAttribute(k_sort_segments<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8)); ctx->sort_attr_set = true; }
-            L3D_CUDA(pdl_launch(k_sort_segments<2048>, dim3(n_src), dim3(SS_T), 2048 * 8, st, ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, 0, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p));
+            L3D_CUDA(ctx->d_boff.ensure(size_t(n_src) * (BK_B + 1))); L3D_CUDA(ctx->d_brange.ensure(size_t(n_src)));
+            L3D_CUDA(pdl_launch(k_bucket_segments, dim3(n_src), dim3(BK_T), 0, st, ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p,
+                                ctx->d_boff.p, ctx->d_brange.p));
             ctx->launches += 1;
-            if (seg_ub > size_t(SORT_SMALL)) {
-                L3D_CUDA(pdl_launch(k_sort_segments<8192>, dim3(n_src), dim3(SS_T), 8192 * 8, st, ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, SORT_SMALL, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p));
-                ctx->launches += 1;
-            }
             L3D_CUDA(pdl_launch(k_score_items, dim3((n_src + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, 0, SORT_MAX, 0, d_nitems, ctx->d_items.p));
             L3D_CUDA(pdl_launch(k_score_window, dim3(max_items), dim3(SC_T), sm_bytes, st, ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
-                                                             ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_items.p, d_nitems, sp, ctx->d_score.p));
+                                                             ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_boff.p, ctx->d_brange.p, ctx->d_items.p, d_nitems, sp, ctx->d_score.p));
             ctx->launches += 2;
         }
         if (!windowed || seg_ub > size_t(SORT_MAX)) {
@@ -1895,6 +1921,7 @@ int l3d_create(int device, l3d_ctx** out)
     if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_error = std::string("l3d_create: cudaSetDevice: ") + cudaGetErrorString(e); return 1; }
     l3d_ctx* ctx = new l3d_ctx();
     ctx->device = device;
+    { int sm = 0; if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && sm > 0) ctx->n_sm = sm; }
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); delete ctx; return 1; }
     {   // keep stream-ordered allocations cached across synchronisations (hand-over buffers are allocated per view)
         cudaMemPool_t pool; unsigned long long keep = ~0ull;
@@ -1938,7 +1965,7 @@ void l3d_destroy(l3d_ctx* ctx)
     for (int q = 0; q < 2; ++q) { ctx->d_filtered2[q].release(); ctx->d_vres[q].release(); ctx->h_vres[q].release(); ctx->h_cams2[q].release(); for (int k = 0; k < 6; ++k) if (ctx->vev[q][k]) cudaEventDestroy(ctx->vev[q][k]); }
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (size_t k = 0; k < ctx->arena.size(); ++k) cudaFreeHost(ctx->arena[k].first);
-    ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release();
+    ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release(); ctx->d_boff.release(); ctx->d_brange.release();
     ctx->d_rm_begin.release(); ctx->d_rm_len.release(); ctx->d_rm_out.release(); ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->d_zero.release(); ctx->h_res.release();
     for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]);
     for (int k = 0; k < 2; ++k) if (ctx->mark_ev[k]) cudaEventDestroy(ctx->mark_ev[k]);
