@@ -799,14 +799,19 @@ __device__ __forceinline__ int depth_bucket(unsigned bits, unsigned bits_min, fl
 
 __global__ void __launch_bounds__(BK_T) k_bucket_segments(const int* __restrict__ off, int n_cams, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
                                                           float* __restrict__ g_k, float* __restrict__ g_d2, unsigned* __restrict__ g_pl,
-                                                          int* __restrict__ g_boff /* [n_src][BK_B + 1] */, uint4* __restrict__ g_brange)
+                                                          int* __restrict__ g_boff /* [n_src][BK_B + 1] */, uint4* __restrict__ g_brange,
+                                                          int m_hi, int chunk, int* __restrict__ n_items, int2* __restrict__ items)
 {
     L3D_PDL_PROLOGUE();
     __shared__ int s_cnt[BK_B], s_start[BK_B + 1];
     __shared__ unsigned s_lo[BK_T / 32], s_hi[BK_T / 32];
+    __shared__ int s_item0;
     const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int seg_start = off[row * n_cams], M = off[(row + 1) * n_cams] - seg_start;
-    if (M <= 0) return;
+    if (M <= 0 || M > m_hi) return;
+    // the scoring kernel's work items of this segment: (segment, chunk of `chunk` hypotheses); their order is irrelevant
+    const int n_chunks = (M + chunk - 1) / chunk;
+    if (tid == 0) s_item0 = atomicAdd(n_items, n_chunks);
     unsigned lo = 0xffffffffu, hi = 0u;
     for (int i = tid; i < M; i += BK_T) { const unsigned b = __float_as_uint(m_dep[seg_start + i].x); lo = min(lo, b); hi = max(hi, b); }
 #pragma unroll
@@ -835,6 +840,7 @@ __global__ void __launch_bounds__(BK_T) k_bucket_segments(const int* __restrict_
     int* boff = g_boff + size_t(row) * (BK_B + 1);
     boff[tid] = s_start[tid];
     if (tid == 0) { boff[BK_B] = s_start[BK_B]; g_brange[row] = make_uint4(lo, hi, __float_as_uint(scale), 0u); }
+    for (int c = tid; c < n_chunks; c += BK_T) items[s_item0 + c] = make_int2(row, c);
     s_cnt[tid] = 0;                                // now the fill cursors
     __syncthreads();
     for (int i = tid; i < M; i += BK_T) {
@@ -962,46 +968,64 @@ __global__ void k_seg_reduce(const int* __restrict__ off, int n_cams, int n_src,
 }
 
 // median of the finite samples: sorted[count / 2], -1 if none (cudawrapper.cu:1066-1076).
-// Selection by ranking: the sample with (#smaller) <= count/2 < (#smaller or equal) is the answer.
-// Pass 1 (2-D grid: samples x chunks of the comparison loop) accumulates, for every sample, how many
-// samples are smaller / smaller-or-equal, and (block row 0) how many are finite; pass 2 picks the answer.
-constexpr int MED_CHUNK = 512;
-__global__ void k_median_rank(const float* __restrict__ dsamples, int n, int* __restrict__ less, int* __restrict__ leq, int* __restrict__ cnt)
+// Radix select in one block: the samples are positive floats or +inf (no sample), so their bit patterns order like
+// unsigned integers; four passes of an 8-bit histogram over the samples that still match the prefix found so far
+// narrow the wanted rank down to one value.
+constexpr int MS_T = 1024;
+__global__ void __launch_bounds__(MS_T) k_median_select(const float* __restrict__ dsamples, int n, float* __restrict__ out)
 {
     L3D_PDL_PROLOGUE();
-    __shared__ float s[MED_CHUNK];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int t0 = blockIdx.y * MED_CHUNK;
-    const int tn = min(MED_CHUNK, n - t0);
-    for (int k = threadIdx.x; k < MED_CHUNK; k += blockDim.x) s[k] = (k < tn) ? dsamples[t0 + k] : INFINITY;
+    __shared__ int s_hist[256];
+    __shared__ int s_cnt[MS_T / 32];
+    __shared__ unsigned s_prefix; __shared__ int s_rank;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int finite = 0;
+    for (int i = tid; i < n; i += MS_T) finite += (dsamples[i] < INFINITY);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) finite += __shfl_xor_sync(0xffffffffu, finite, o);
+    if (lane == 0) s_cnt[warp] = finite;
+    if (tid < 256) s_hist[tid] = 0;
     __syncthreads();
-    if (i >= n) return;
-    const float v = dsamples[i];
-    if (!(v < INFINITY)) return;
-    int a = 0, b = 0;
-#pragma unroll 8
-    for (int k = 0; k < MED_CHUNK; ++k) { const float u = s[k]; a += (u < v); b += (u <= v); }
-    if (a) atomicAdd(&less[i], a);
-    if (b) atomicAdd(&leq[i], b);
-    if (blockIdx.y == 0) atomicAdd(cnt, 1);
-}
-__global__ void k_median_pick(const float* __restrict__ dsamples, int n, const int* __restrict__ less, const int* __restrict__ leq,
-                              const int* __restrict__ cnt, float* __restrict__ out)
-{
-    L3D_PDL_PROLOGUE();
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0 && *cnt == 0) out[0] = -1.0f;
-    if (i >= n) return;
-    const float v = dsamples[i];
-    if (!(v < INFINITY)) return;
-    const int r = *cnt / 2;
-    if (less[i] <= r && r < leq[i]) out[0] = v;
+    int count = 0;
+#pragma unroll
+    for (int w = 0; w < MS_T / 32; ++w) count += s_cnt[w];
+    if (count == 0) { if (tid == 0) out[0] = -1.0f; return; }
+    if (tid == 0) { s_prefix = 0u; s_rank = count / 2; }
+    unsigned prefix = 0u, mask = 0u;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int i = tid; i < n; i += MS_T) {       // the samples are re-read every pass (16 KB, L1/L2)
+            const float x = dsamples[i];
+            const unsigned v = __float_as_uint(x);
+            if (x < INFINITY && (v & mask) == prefix) atomicAdd(&s_hist[(v >> shift) & 255u], 1);
+        }
+        __syncthreads();
+        if (warp == 0) {                            // the bin in which the cumulative count passes the wanted rank
+            int c[8], sum = 0;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) { c[r] = s_hist[lane * 8 + r]; sum += c[r]; }
+            int inc = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+            const int rank = s_rank;
+            int ex = inc - sum;
+            if (ex <= rank && rank < inc) {
+#pragma unroll
+                for (int r = 0; r < 8; ++r) { if (rank < ex + c[r]) { s_prefix = prefix | (unsigned(lane * 8 + r) << shift); s_rank = rank - ex; break; } ex += c[r]; }
+            }
+        }
+        __syncthreads();
+        prefix = s_prefix; mask |= 255u << shift;
+        if (tid < 256) s_hist[tid] = 0;
+        __syncthreads();
+    }
+    if (tid == 0) out[0] = __uint_as_float(prefix);
 }
 
-// filtered records in order, one warp per segment; four 32-match chunks per iteration keep several loads in flight
+// filtered records in order, one warp per segment; four 32-match chunks per iteration keep several loads in flight.
+// Also counts the records per hand-over group (destination view's segment), the first step of the regrouping below.
 __global__ void k_filter_fill(const int* __restrict__ off, int n_cams, int n_src, const float* __restrict__ score,
                               const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, const int* __restrict__ foff,
-                              l3d_match* __restrict__ out)
+                              l3d_match* __restrict__ out, const CamTable* __restrict__ cams, int stride, int* __restrict__ hist /* or null */)
 {
     L3D_PDL_PROLOGUE();
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -1024,6 +1048,7 @@ __global__ void k_filter_fill(const int* __restrict__ off, int n_cams, int n_src
                 l3d_match rec; rec.src_seg = id.x; rec.cam = id.y; rec.tgt_seg = id.z; rec.confidence = xd(c[u], 2.0f);
                 rec.depths[0] = d.x; rec.depths[1] = d.y; rec.depths[2] = d.z; rec.depths[3] = d.w;
                 out[r] = rec;
+                if (hist) { const int dl = cams[id.y].deliver; if (dl >= 0) atomicAdd(&hist[dl * stride + id.z], 1); }     // hand-over group sizes
             }
             o += __popc(m);
         }
@@ -1045,14 +1070,6 @@ __global__ void k_copy_unscored(const int4* __restrict__ m_ids, const float4* __
 // hand-over (line3D.cc:838-858): the filtered records towards each neighbour that asked for
 // delivery, reversed and regrouped by the neighbour's segment, target ids ascending
 // ------------------------------------------------------------------------------------------
-__global__ void k_deliver_hist(const l3d_match* __restrict__ f, const int* __restrict__ Fptr, const CamTable* __restrict__ cams, int stride, int* __restrict__ hist)
-{
-    L3D_PDL_PROLOGUE();
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= *Fptr) return;
-    const int d = cams[f[k].cam].deliver;
-    if (d >= 0) atomicAdd(&hist[d * stride + f[k].tgt_seg], 1);
-}
 __global__ void k_deliver_scatter(const l3d_match* __restrict__ f, const int* __restrict__ Fptr, const CamTable* __restrict__ cams, int stride,
                                   const int* __restrict__ start, int* __restrict__ cursor, int* __restrict__ t_tgt, float4* __restrict__ t_dep)
 {
@@ -1685,9 +1702,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
             L3D_CUDA(ctx->d_sk.ensure(M_ub)); L3D_CUDA(ctx->d_sd2.ensure(M_ub)); L3D_CUDA(ctx->d_spl.ensure(M_ub));
             L3D_CUDA(ctx->d_boff.ensure(size_t(n_src) * (BK_B + 1))); L3D_CUDA(ctx->d_brange.ensure(size_t(n_src)));
             L3D_CUDA(pdl_launch(k_bucket_segments, dim3(n_src), dim3(BK_T), 0, st, ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p,
-                                ctx->d_boff.p, ctx->d_brange.p));
-            ctx->launches += 1;
-            L3D_CUDA(pdl_launch(k_score_items, dim3((n_src + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, 0, SORT_MAX, 0, d_nitems, ctx->d_items.p));
+                                ctx->d_boff.p, ctx->d_brange.p, SORT_MAX, SC_T, d_nitems, ctx->d_items.p));
             L3D_CUDA(pdl_launch(k_score_window, dim3(max_items), dim3(SC_T), sm_bytes, st, ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
                                                              ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_boff.p, ctx->d_brange.p, ctx->d_items.p, d_nitems, sp, ctx->d_score.p));
             ctx->launches += 2;
@@ -1703,15 +1718,11 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[4], st));
         // ---- reduce -----------------------------------------------------------------------
         L3D_CUDA(pdl_launch(k_seg_reduce, dim3((n_src * 32 + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, d_iters));
-        {
-            int* less = ctx->d_zero.p + z_rank; int* leq = less + ns; int* cnt = leq + ns;
-            L3D_CUDA(pdl_launch(k_median_rank, dim3(dim3((ns + 127) / 128, (ns + MED_CHUNK - 1) / MED_CHUNK)), dim3(128), 0, st, ctx->d_dsamples.p, ns, less, leq, cnt));
-            L3D_CUDA(pdl_launch(k_median_pick, dim3((ns + 255) / 256), dim3(256), 0, st, ctx->d_dsamples.p, ns, less, leq, cnt, ctx->d_median.p));
-        }
-        ctx->launches += 3;
+        L3D_CUDA(pdl_launch(k_median_select, dim3(1), dim3(MS_T), 0, st, ctx->d_dsamples.p, ns, ctx->d_median.p));
+        ctx->launches += 2;
         if (scan_exclusive(ctx, ctx->d_fcnt.p, ctx->d_foff.p, n_src)) return 1;
         d_F = ctx->d_foff.p + n_src;
-        L3D_CUDA(pdl_launch(k_filter_fill, dim3((n_src * 32 + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, dfil.p));
+        L3D_CUDA(pdl_launch(k_filter_fill, dim3((n_src * 32 + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, dfil.p, ctx->d_cams.p, stride, delivering ? d_hist : nullptr));
         ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
     } else {
@@ -1731,7 +1742,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         L3D_CUDA(cudaMallocAsync(&buf.start, sizeof(int) * (size_t(n_keys) + 2), st));
         L3D_CUDA(cudaMallocAsync(&buf.tgt, sizeof(int) * std::max<size_t>(M_ub, 1), st));
         L3D_CUDA(cudaMallocAsync(&buf.dep, sizeof(float4) * std::max<size_t>(M_ub, 1), st));
-        if (M_ub > 0) { L3D_CUDA(pdl_launch(k_deliver_hist, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, dfil.p, d_F, ctx->d_cams.p, stride, d_hist)); ctx->launches += 1; }
+        // (the group sizes were counted by k_filter_fill)
         if (scan_exclusive(ctx, d_hist, buf.start, n_keys)) return 1;
         if (M_ub > 0) {
             L3D_CUDA(ctx->d_dl_tgt.ensure(M_ub)); L3D_CUDA(ctx->d_dl_dep.ensure(M_ub));
