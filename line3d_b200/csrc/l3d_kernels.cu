@@ -519,6 +519,26 @@ __global__ void __launch_bounds__(EF_T) k_exact_flat(const float4* __restrict__ 
     }
 }
 
+// out_sum[b], out_max[b] over v[begin[b] .. begin[b] + len[b]); one block per b.  After the exact test: raw matches
+// per job and the most raw matches of a single row, which bound every per-view buffer and grid.
+__global__ void k_range_sum_max(const int* __restrict__ v, const int* __restrict__ begin, const int* __restrict__ len, int* __restrict__ out_sum, int* __restrict__ out_max)
+{
+    __shared__ int sh_s[32], sh_m[32];
+    const int b0 = begin[blockIdx.x], n = len[blockIdx.x];
+    int s = 0, m = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { const int x = v[b0 + i]; s += x; m = max(m, x); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); m = max(m, __shfl_xor_sync(0xffffffffu, m, o)); }
+    if ((threadIdx.x & 31) == 0) { sh_s[threadIdx.x >> 5] = s; sh_m[threadIdx.x >> 5] = m; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        s = (threadIdx.x < (blockDim.x >> 5)) ? sh_s[threadIdx.x] : 0; m = (threadIdx.x < (blockDim.x >> 5)) ? sh_m[threadIdx.x] : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); m = max(m, __shfl_xor_sync(0xffffffffu, m, o)); }
+        if (threadIdx.x == 0) { out_sum[blockIdx.x] = s; out_max[blockIdx.x] = m; }
+    }
+}
+
 // out[b] = max over i in [begin[b], begin[b] + len[b]) of (diff ? v[i + 1] - v[i] : v[i]); one block per b.
 // Used for upper bounds on the number of matches of a single segment (which scoring kernels are needed).
 __global__ void k_range_max(const int* __restrict__ v, const int* __restrict__ begin, const int* __restrict__ len, int diff, int* __restrict__ out)
@@ -1404,7 +1424,7 @@ struct l3d_ctx {
     DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl; DBuf<int> d_dl_tgt; DBuf<float4> d_dl_dep; DBuf<int> d_boff; DBuf<uint4> d_brange; int n_sm = 148;
     // phase A (pair tests) of the resident batch
     DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
-    std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands; std::vector<int> job_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
+    std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands, job_raw; std::vector<int> job_rowmax, job_raw_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
     std::vector<PlannedView> plan; size_t plan_next = 0; size_t batch_begin = 0, batch_end = 0;
     float pa_ms[2] = {0.f, 0.f}; bool pa_ms_pending = false;
     uint64_t pair_budget = 24000000000ull;
@@ -1500,6 +1520,7 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     ctx->jobs_host.assign(size_t(n_jobs), JobDev());
     ctx->job_cands.assign(size_t(n_jobs), 0);
     ctx->job_rowmax.assign(size_t(n_jobs), 0);
+    ctx->job_raw.assign(size_t(n_jobs), 0); ctx->job_raw_rowmax.assign(size_t(n_jobs), 0);
     ctx->pa_kev_set[0] = ctx->pa_kev_set[1] = false;
     if (n_jobs == 0) return 0;
     long long sh_tot = 0, th_tot = 0, words = 0, rows = 0, blocks = 0;
@@ -1574,6 +1595,17 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     }
     L3D_CUDA(cudaEventRecord(ctx->pa_ev[2], st));
     ctx->pa_ms_pending = true;
+    // raw matches per job and per row: tight bounds for the per-view work (the candidate counts are 2.5x larger).
+    // Waiting for them here costs one idle gap per batch, not per view.
+    if (rows > 0 && n_cand > 0) {
+        L3D_CUDA(ctx->d_pa_idx.ensure(2 * size_t(n_jobs) + 2));
+        k_range_sum_max<<<n_jobs, 256, 0, st>>>(ctx->d_pa_raw.p, ctx->d_rm_begin.p, ctx->d_rm_len.p, ctx->d_pa_idx.p, ctx->d_pa_idx.p + n_jobs);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p, ctx->d_pa_idx.p, sizeof(int) * 2 * size_t(n_jobs), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaStreamSynchronize(st));
+        for (int j = 0; j < n_jobs; ++j) { ctx->job_raw[j] = uint64_t(ctx->h_res.p[j]); ctx->job_raw_rowmax[j] = ctx->h_res.p[n_jobs + j]; }
+    }
     return 0;
 }
 
@@ -1608,7 +1640,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     // ---- tables -------------------------------------------------------------------------
     L3D_CUDA(hc.ensure(size_t(n_nb)));
     int n_slots = 0, n_deliver = 0, max_deliver_seg = 1;
-    uint64_t pair_tests = 0, cand_ub = 0;
+    uint64_t pair_tests = 0, cand_ub = 0, raw_ub = 0;
     size_t seg_ub = 0;                               // upper bound on the matches of one source segment
     std::vector<int> consumed;                       // indices into ctx->delivered[view]
     uint64_t delivered_ub = 0;
@@ -1623,7 +1655,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         if (n.to_be_matched) {
             const int j = first_job + n_slots;
             ct.mode = 0; ct.slot = n_slots++; ct.row_off = ctx->jobs_host[j].row_off;
-            cand_ub += ctx->job_cands[j]; seg_ub += size_t(ctx->job_rowmax[j]);
+            cand_ub += ctx->job_cands[j]; raw_ub += ctx->job_raw[j]; seg_ub += size_t(ctx->job_raw_rowmax[j]);
             pair_tests += uint64_t(n_src) * uint64_t(tv.n_segments);
         } else {
             ct.mode = 2;
@@ -1638,7 +1670,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     memcpy(src.RtKinv, sv.RtKinv, sizeof src.RtKinv); memcpy(src.C, sv.C, sizeof src.C);
     src.spatial_k = sv.spatial_k; src.cmax = std::max(std::fabs(sv.C[0]), std::max(std::fabs(sv.C[1]), std::fabs(sv.C[2])));
     src.seg_off = ctx->seg_off[view]; src.n_seg = n_src;
-    const size_t M_ub = size_t(cand_ub + delivered_ub);          // upper bound on the number of matches to score
+    const size_t M_ub = size_t(raw_ub + delivered_ub);          // upper bound on the number of matches to score
 
     L3D_CUDA(ctx->d_cams.ensure(size_t(n_nb)));
     L3D_CUDA(cudaMemcpyAsync(ctx->d_cams.p, hc.p, sizeof(CamTable) * n_nb, cudaMemcpyHostToDevice, st));
@@ -1770,7 +1802,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         for (int c = 0; c < n_nb; ++c) {
             const int d = hc.p[c].deliver;
             if (d < 0) continue;
-            const uint64_t ub = std::min<uint64_t>(hc.p[c].slot >= 0 ? ctx->job_cands[first_job + hc.p[c].slot] : uint64_t(M_ub), 0x7fffffffull);
+            const uint64_t ub = std::min<uint64_t>(hc.p[c].slot >= 0 ? ctx->job_raw[first_job + hc.p[c].slot] : uint64_t(M_ub), 0x7fffffffull);
             Delivered dl; dl.from_view = view; dl.owner = job.owner; dl.slot = d;
             dl.count = int(ub); dl.max_group = int(std::min<uint64_t>(ub, uint64_t(n_src)));      // a source segment matches a target segment once
             dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
