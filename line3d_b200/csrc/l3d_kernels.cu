@@ -635,8 +635,15 @@ __global__ void k_fill(const CamTable* __restrict__ cams, int n_cams, int n_src,
             w += __popc(m);
         }
     } else if (ct.mode == 1) {
+        // delivered records of one segment arrive in the order of the sender's atomics; they go out in ascending
+        // target id (ids are unique within a group and groups are tiny: each record counts the smaller ones)
         const int b = ct.t_start[row];
-        for (int k = lane; k < n; k += 32) { m_ids[o + k] = make_int4(row, cam, ct.t_tgt[b + k], 0); m_dep[o + k] = ct.t_dep[b + k]; }
+        for (int k = lane; k < n; k += 32) {
+            const int me = ct.t_tgt[b + k];
+            int rank = 0;
+            for (int i = 0; i < n; ++i) rank += (ct.t_tgt[b + i] < me);
+            m_ids[o + rank] = make_int4(row, cam, me, 0); m_dep[o + rank] = ct.t_dep[b + k];
+        }
     }
 }
 
@@ -1104,26 +1111,6 @@ __global__ void k_deliver_scatter(const l3d_match* __restrict__ f, const int* __
     t_tgt[pos] = m.src_seg;
     t_dep[pos] = make_float4(m.depths[2], m.depths[3], m.depths[0], m.depths[1]);     // line3D.cc:852-855
 }
-// the scatter above is unordered within a group; every record finds its place by counting the group members with a
-// smaller target id (ids are unique within a group, groups are tiny) and is copied to the final arrays
-__global__ void k_deliver_place(const int* __restrict__ start, int n_keys, const int* __restrict__ tmp_tgt, const float4* __restrict__ tmp_dep,
-                                int* __restrict__ t_tgt, float4* __restrict__ t_dep)
-{
-    L3D_PDL_PROLOGUE();
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    const int total = start[n_keys];
-    if (k >= total) return;
-    // group of record k: largest key with start[key] <= k
-    int lo = 0, hi = n_keys - 1;
-    while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (start[mid] <= k) lo = mid; else hi = mid - 1; }
-    const int a = start[lo], b = start[lo + 1];
-    const int me = tmp_tgt[k];
-    int rank = 0;
-    for (int i = a; i < b; ++i) rank += (tmp_tgt[i] < me);
-    t_tgt[a + rank] = me;
-    t_dep[a + rank] = tmp_dep[k];
-}
-
 // ------------------------------------------------------------------------------------------
 // collinearity (cudawrapper.cu:476-535): upper triangle, compacted on the device
 // ------------------------------------------------------------------------------------------
@@ -1421,7 +1408,7 @@ struct l3d_ctx {
     DBuf<int> d_cnt, d_off;
     DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
     DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
-    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl; DBuf<int> d_dl_tgt; DBuf<float4> d_dl_dep; DBuf<int> d_boff; DBuf<uint4> d_brange; int n_sm = 148;
+    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl; DBuf<int> d_boff; DBuf<uint4> d_brange; int n_sm = 148;
     // phase A (pair tests) of the resident batch
     DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
     std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands, job_raw; std::vector<int> job_rowmax, job_raw_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
@@ -1777,10 +1764,9 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         // (the group sizes were counted by k_filter_fill)
         if (scan_exclusive(ctx, d_hist, buf.start, n_keys)) return 1;
         if (M_ub > 0) {
-            L3D_CUDA(ctx->d_dl_tgt.ensure(M_ub)); L3D_CUDA(ctx->d_dl_dep.ensure(M_ub));
-            L3D_CUDA(pdl_launch(k_deliver_scatter, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, dfil.p, d_F, ctx->d_cams.p, stride, buf.start, d_cursor, ctx->d_dl_tgt.p, ctx->d_dl_dep.p));
-            L3D_CUDA(pdl_launch(k_deliver_place, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, buf.start, n_keys, ctx->d_dl_tgt.p, ctx->d_dl_dep.p, buf.tgt, buf.dep));
-            ctx->launches += 2;
+            // records land in their group in the order of the atomics; the receiving view's k_fill orders them
+            L3D_CUDA(pdl_launch(k_deliver_scatter, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, dfil.p, d_F, ctx->d_cams.p, stride, buf.start, d_cursor, buf.tgt, buf.dep));
+            ctx->launches += 1;
         }
         L3D_CUDA(cudaGetLastError());
     }
@@ -2015,7 +2001,7 @@ void l3d_destroy(l3d_ctx* ctx)
     for (int q = 0; q < 2; ++q) { ctx->d_filtered2[q].release(); ctx->d_vres[q].release(); ctx->h_vres[q].release(); ctx->h_cams2[q].release(); for (int k = 0; k < 6; ++k) if (ctx->vev[q][k]) cudaEventDestroy(ctx->vev[q][k]); }
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (size_t k = 0; k < ctx->arena.size(); ++k) cudaFreeHost(ctx->arena[k].first);
-    ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_dl_tgt.release(); ctx->d_dl_dep.release(); ctx->d_boff.release(); ctx->d_brange.release();
+    ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_boff.release(); ctx->d_brange.release();
     ctx->d_rm_begin.release(); ctx->d_rm_len.release(); ctx->d_rm_out.release(); ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->d_zero.release(); ctx->h_res.release();
     for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]);
     for (int k = 0; k < 2; ++k) if (ctx->mark_ev[k]) cudaEventDestroy(ctx->mark_ev[k]);
