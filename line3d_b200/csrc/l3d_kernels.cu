@@ -559,37 +559,6 @@ __global__ void k_range_max(const int* __restrict__ v, const int* __restrict__ b
     }
 }
 
-// All the small per-view results in one buffer, so that one copy brings them to the host:
-// out[0] = matches, out[1] = output records, out[2] = median depth (float bits), out[4..7] = two 64-bit iteration
-// counters, out[8 + d] = records handed to delivery slot d, out[8 + n_deliver + d] = the largest group of that slot.
-// One block per slot (at least one block).
-__global__ void k_pack_results(const int* __restrict__ M, const int* __restrict__ F, const float* __restrict__ median,
-                               const unsigned long long* __restrict__ iters, const int* __restrict__ start, int stride, int n_deliver, int seg_max,
-                               int* __restrict__ out)
-{
-    L3D_PDL_PROLOGUE();
-    __shared__ int sh[32];
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        out[0] = *M; out[1] = *F; out[2] = median ? __float_as_int(*median) : 0; out[3] = 0;
-        unsigned long long a = iters ? iters[0] : 0ull, b = iters ? iters[1] : 0ull;
-        out[4] = int(a & 0xffffffffull); out[5] = int(a >> 32); out[6] = int(b & 0xffffffffull); out[7] = int(b >> 32);
-    }
-    if (int(blockIdx.x) >= n_deliver) return;
-    const int b0 = blockIdx.x * stride;
-    int m = 0;
-    for (int i = threadIdx.x; i < seg_max; i += blockDim.x) m = max(m, start[b0 + i + 1] - start[b0 + i]);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        m = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
-        if (threadIdx.x == 0) { out[8 + blockIdx.x] = start[b0 + stride] - start[b0]; out[8 + n_deliver + blockIdx.x] = m; }
-    }
-}
-
 // dst[k] = src[idx[k]]
 __global__ void k_gather_int(const int* __restrict__ src, const int* __restrict__ idx, int n, int* __restrict__ dst)
 {
@@ -999,9 +968,8 @@ __global__ void k_seg_reduce(const int* __restrict__ off, int n_cams, int n_src,
 // unsigned integers; four passes of an 8-bit histogram over the samples that still match the prefix found so far
 // narrow the wanted rank down to one value.
 constexpr int MS_T = 1024;
-__global__ void __launch_bounds__(MS_T) k_median_select(const float* __restrict__ dsamples, int n, float* __restrict__ out)
+__device__ float block_median_select(const float* __restrict__ dsamples, int n)
 {
-    L3D_PDL_PROLOGUE();
     __shared__ int s_hist[256];
     __shared__ int s_cnt[MS_T / 32];
     __shared__ unsigned s_prefix; __shared__ int s_rank;
@@ -1016,7 +984,7 @@ __global__ void __launch_bounds__(MS_T) k_median_select(const float* __restrict_
     int count = 0;
 #pragma unroll
     for (int w = 0; w < MS_T / 32; ++w) count += s_cnt[w];
-    if (count == 0) { if (tid == 0) out[0] = -1.0f; return; }
+    if (count == 0) return -1.0f;                   // (the same for every thread of the block)
     if (tid == 0) { s_prefix = 0u; s_rank = count / 2; }
     unsigned prefix = 0u, mask = 0u;
     for (int shift = 24; shift >= 0; shift -= 8) {
@@ -1045,7 +1013,24 @@ __global__ void __launch_bounds__(MS_T) k_median_select(const float* __restrict_
         if (tid < 256) s_hist[tid] = 0;
         __syncthreads();
     }
-    if (tid == 0) out[0] = __uint_as_float(prefix);
+    return __uint_as_float(prefix);
+}
+
+// The last kernel of a view: the median depth, and all the small results in one buffer so that one copy brings
+// them to the host: out[0] = matches, out[1] = output records, out[2] = median depth (float bits), out[4..7] = two
+// 64-bit iteration counters, out[8 + d] = records handed to delivery slot d.  One block.
+__global__ void __launch_bounds__(MS_T) k_finish_view(const float* __restrict__ dsamples, int n_samples, const int* __restrict__ M, const int* __restrict__ F,
+                                                      const unsigned long long* __restrict__ iters, const int* __restrict__ start, int stride, int n_deliver,
+                                                      int* __restrict__ out)
+{
+    L3D_PDL_PROLOGUE();
+    const float median = (n_samples > 0) ? block_median_select(dsamples, n_samples) : 0.0f;
+    if (threadIdx.x == 0) {
+        out[0] = *M; out[1] = *F; out[2] = __float_as_int(median); out[3] = 0;
+        const unsigned long long a = iters ? iters[0] : 0ull, b = iters ? iters[1] : 0ull;
+        out[4] = int(a & 0xffffffffull); out[5] = int(a >> 32); out[6] = int(b & 0xffffffffull); out[7] = int(b >> 32);
+    }
+    for (int d = threadIdx.x; d < n_deliver; d += blockDim.x) out[8 + d] = start[(d + 1) * stride] - start[d * stride];
 }
 
 // filtered records in order, one warp per segment; four 32-match chunks per iteration keep several loads in flight.
@@ -1737,8 +1722,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[4], st));
         // ---- reduce -----------------------------------------------------------------------
         L3D_CUDA(pdl_launch(k_seg_reduce, dim3((n_src * 32 + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, d_iters));
-        L3D_CUDA(pdl_launch(k_median_select, dim3(1), dim3(MS_T), 0, st, ctx->d_dsamples.p, ns, ctx->d_median.p));
-        ctx->launches += 2;
+        ctx->launches += 1;
         if (scan_exclusive(ctx, ctx->d_fcnt.p, ctx->d_foff.p, n_src)) return 1;
         d_F = ctx->d_foff.p + n_src;
         L3D_CUDA(pdl_launch(k_filter_fill, dim3((n_src * 32 + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, dfil.p, ctx->d_cams.p, stride, delivering ? d_hist : nullptr));
@@ -1771,10 +1755,10 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         L3D_CUDA(cudaGetLastError());
     }
     // ---- results: one kernel packs them, one copy; the host collects them in finish_view ----------------
-    const int n_res = 8 + 2 * std::max(n_deliver, 1);
+    const int n_res = 8 + std::max(n_deliver, 1);
     L3D_CUDA(ctx->d_vres[par].ensure(size_t(n_res))); L3D_CUDA(ctx->h_vres[par].ensure(size_t(n_res)));
-    L3D_CUDA(pdl_launch(k_pack_results, dim3(std::max(delivering ? n_deliver : 0, 1)), dim3(256), 0, st, d_M, d_F, (scored && M_ub > 0) ? ctx->d_median.p : nullptr, (scored && M_ub > 0) ? d_iters : nullptr,
-                                                                          delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, max_deliver_seg, ctx->d_vres[par].p));
+    L3D_CUDA(pdl_launch(k_finish_view, dim3(1), dim3(MS_T), 0, st, ctx->d_dsamples.p, (scored && M_ub > 0) ? ns : 0, d_M, d_F, (scored && M_ub > 0) ? d_iters : nullptr,
+                        delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, ctx->d_vres[par].p));
     ctx->launches += 1;
     L3D_CUDA(cudaGetLastError());
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[5], st));
@@ -1842,7 +1826,7 @@ int finish_view(l3d_ctx* ctx, ViewJob& job, l3d_match_result* res, bool copy_bac
     }
     if (job.delivering) {                              // exact sizes of what this view handed over
         DeliverBuf& b = ctx->deliver_bufs[job.owner];
-        for (int d = 0; d < job.n_deliver; ++d) { b.counts[d] = hr[8 + d]; b.maxg[d] = hr[8 + job.n_deliver + d]; }
+        for (int d = 0; d < job.n_deliver; ++d) { b.counts[d] = hr[8 + d]; b.maxg[d] = std::min(b.maxg[d], hr[8 + d]); }
         for (size_t c = 0; c < job.nb.size(); ++c) {
             if (!job.nb[c].deliver) continue;
             std::vector<Delivered>& dl = ctx->delivered[job.nb[c].view];
