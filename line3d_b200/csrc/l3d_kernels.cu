@@ -787,7 +787,7 @@ __global__ void __launch_bounds__(SC_T) k_score(const float4* __restrict__ segs,
 // Output: (d1, d2, camera << 20 | index) at the segment's own offsets in bucket order, the bucket boundaries, and
 // (bits of min d1, bits of max d1, scale) per segment.
 constexpr int BK_T = 128;
-constexpr int BK_B = 128;
+constexpr int BK_B = 512;
 __device__ __forceinline__ int depth_bucket(unsigned bits, unsigned bits_min, float scale)
 {
     return min(BK_B - 1, int(float(bits - bits_min) * scale));
@@ -813,7 +813,7 @@ __global__ void __launch_bounds__(BK_T) k_bucket_segments(const int* __restrict_
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
     if (lane == 0) { s_lo[warp] = lo; s_hi[warp] = hi; }
-    s_cnt[tid] = 0;
+    for (int b = tid; b < BK_B; b += BK_T) s_cnt[b] = 0;
     __syncthreads();
 #pragma unroll
     for (int w = 0; w < BK_T / 32; ++w) { lo = min(lo, s_lo[w]); hi = max(hi, s_hi[w]); }
@@ -834,10 +834,10 @@ __global__ void __launch_bounds__(BK_T) k_bucket_segments(const int* __restrict_
     }
     __syncthreads();
     int* boff = g_boff + size_t(row) * (BK_B + 1);
-    boff[tid] = s_start[tid];
+    for (int b = tid; b < BK_B; b += BK_T) boff[b] = s_start[b];
     if (tid == 0) { boff[BK_B] = s_start[BK_B]; g_brange[row] = make_uint4(lo, hi, __float_as_uint(scale), 0u); }
     for (int c = tid; c < n_chunks; c += BK_T) items[s_item0 + c] = make_int2(row, c);
-    s_cnt[tid] = 0;                                // now the fill cursors
+    for (int b = tid; b < BK_B; b += BK_T) s_cnt[b] = 0;      // now the fill cursors
     __syncthreads();
     for (int i = tid; i < M; i += BK_T) {
         const float4 d = m_dep[seg_start + i];
@@ -897,8 +897,8 @@ __global__ void __launch_bounds__(SC_T) k_score_window(const float4* __restrict_
     while (__any_sync(0xffffffffu, j < jend)) {
         bool hit = false; unsigned pl = 0;
         if (j < jend) {
-            pl = PL[j];
-            hit = (fabsf(my_d.x - K[j]) <= thr1) && (fabsf(my_d.y - D2[j]) <= thr2) && (int(pl >> 20) != my_cam);
+            hit = (fabsf(my_d.x - K[j]) <= thr1) && (fabsf(my_d.y - D2[j]) <= thr2);
+            if (hit) { pl = PL[j]; hit = int(pl >> 20) != my_cam; }
             ++j;
         }
         const unsigned m = __ballot_sync(0xffffffffu, hit);
