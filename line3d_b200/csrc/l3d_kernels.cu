@@ -923,43 +923,44 @@ __global__ void __launch_bounds__(SC_T) k_score_window(const float4* __restrict_
 }
 
 // ------------------------------------------------------------------------------------------
-// per-segment reduction (cudawrapper.cu:1028-1064, 1090-1110): best match (first maximum),
-// number of matches with score > 1, depth samples of the best if its score > 0.5
+// per-segment reduction (cudawrapper.cu:1028-1064, 1090-1110): best match of every segment (first maximum) and
+// the matches with score > 1.  One thread per match, all loads independent (a warp per segment walking its matches
+// was a chain of dependent loads as long as the longest segment): the best match is a 64-bit atomicMax on
+// (score bits, ~match index) -- scores are positive, so their bits order like the values, and among equal scores the
+// smaller index wins as in the reference's strict '>' scan --, the kept matches are counted per CTA for the ordered
+// compaction in k_filter_compact, and the two iteration counters are summed on the way.
 // ------------------------------------------------------------------------------------------
-__global__ void k_seg_reduce(const int* __restrict__ off, int n_cams, int n_src, const float* __restrict__ score,
-                             const float4* __restrict__ m_dep, int* __restrict__ fcnt, float* __restrict__ dsamples,
-                             unsigned long long* __restrict__ iters /* [0] all pairs, [1] same-camera pairs */)
+constexpr int RM_T = 1024;
+__global__ void __launch_bounds__(RM_T) k_reduce_matches(const int* __restrict__ Mptr, const int* __restrict__ off, int n_cams, const float* __restrict__ score,
+                                                         const int4* __restrict__ m_ids, unsigned long long* __restrict__ best /* [n_src], zeroed */,
+                                                         int* __restrict__ cta_kept, unsigned long long* __restrict__ iters /* [0] all pairs, [1] same-camera pairs */)
 {
     L3D_PDL_PROLOGUE();
-    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (row >= n_src) return;
-    const int s0 = off[row * n_cams], s1 = off[(row + 1) * n_cams];
-    float best = 0.0f; int bi = 0x7fffffff, nf = 0;
-    for (int k = s0 + lane; k < s1; k += 32) {
-        float c = score[k];
-        if (c > 1.0f) ++nf;
-        if (c > best) { best = c; bi = k; }           // strict: the first maximum within this lane's stride
+    __shared__ int s_k[RM_T / 32];
+    __shared__ unsigned long long s_a[RM_T / 32], s_b[RM_T / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int k = blockIdx.x * RM_T + tid, M = *Mptr;
+    int keep = 0; unsigned long long all = 0ull, same = 0ull;
+    if (k < M) {
+        const float c = score[k]; const int4 id = m_ids[k];
+        keep = c > 1.0f;
+        const int* o = off + id.x * n_cams;
+        all = (unsigned long long)(o[n_cams] - o[0]);                 // sum over the matches of their segment's size = sum of squares
+        same = (unsigned long long)(o[id.y + 1] - o[id.y]);
+        if (c > 0.0f) {
+            const unsigned long long key = ((unsigned long long)__float_as_uint(c) << 32) | (unsigned long long)(0xffffffffu - unsigned(k));
+            if (key > best[id.x]) atomicMax(&best[id.x], key);
+        }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        float ob = __shfl_xor_sync(0xffffffffu, best, o); int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        nf += __shfl_xor_sync(0xffffffffu, nf, o);
-        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
-    }
-    if (lane == 0) {
-        fcnt[row] = nf;
-        float a = INFINITY, b = INFINITY;
-        if (best > 0.5f) { float4 d = m_dep[bi]; a = d.x; b = d.y; }
-        dsamples[2 * row] = a; dsamples[2 * row + 1] = b;
-        unsigned long long m = (unsigned long long)(s1 - s0);
-        if (m) atomicAdd(iters, m * m);
-    }
-    if (s1 > s0) {
-        unsigned long long same = 0;
-        for (int c = lane; c < n_cams; c += 32) { unsigned long long g = (unsigned long long)(off[row * n_cams + c + 1] - off[row * n_cams + c]); same += g * g; }
+    for (int o = 16; o > 0; o >>= 1) { keep += __shfl_xor_sync(0xffffffffu, keep, o); all += __shfl_xor_sync(0xffffffffu, all, o); same += __shfl_xor_sync(0xffffffffu, same, o); }
+    if (lane == 0) { s_k[warp] = keep; s_a[warp] = all; s_b[warp] = same; }
+    __syncthreads();
+    if (warp == 0) {
+        keep = s_k[lane]; all = s_a[lane]; same = s_b[lane];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) same += __shfl_xor_sync(0xffffffffu, same, o);
-        if (lane == 0 && same) atomicAdd(iters + 1, same);
+        for (int o = 16; o > 0; o >>= 1) { keep += __shfl_xor_sync(0xffffffffu, keep, o); all += __shfl_xor_sync(0xffffffffu, all, o); same += __shfl_xor_sync(0xffffffffu, same, o); }
+        if (lane == 0) { cta_kept[blockIdx.x] = keep; if (all) atomicAdd(iters, all); if (same) atomicAdd(iters + 1, same); }
     }
 }
 
@@ -1019,11 +1020,20 @@ __device__ float block_median_select(const float* __restrict__ dsamples, int n)
 // The last kernel of a view: the median depth, and all the small results in one buffer so that one copy brings
 // them to the host: out[0] = matches, out[1] = output records, out[2] = median depth (float bits), out[4..7] = two
 // 64-bit iteration counters, out[8 + d] = records handed to delivery slot d.  One block.
-__global__ void __launch_bounds__(MS_T) k_finish_view(const float* __restrict__ dsamples, int n_samples, const int* __restrict__ M, const int* __restrict__ F,
+__global__ void __launch_bounds__(MS_T) k_finish_view(float* __restrict__ dsamples, int n_samples, const unsigned long long* __restrict__ best, const float4* __restrict__ m_dep,
+                                                      const int* __restrict__ M, const int* __restrict__ F,
                                                       const unsigned long long* __restrict__ iters, const int* __restrict__ start, int stride, int n_deliver,
                                                       int* __restrict__ out)
 {
     L3D_PDL_PROLOGUE();
+    // depth samples: both depths of every segment's best match if its score exceeds 0.5 (cudawrapper.cu:1090-1110)
+    for (int row = threadIdx.x; 2 * row < n_samples; row += MS_T) {
+        const unsigned long long key = best[row];
+        float a = INFINITY, b = INFINITY;
+        if (__uint_as_float(unsigned(key >> 32)) > 0.5f) { const float4 d = m_dep[0xffffffffu - unsigned(key & 0xffffffffull)]; a = d.x; b = d.y; }
+        dsamples[2 * row] = a; dsamples[2 * row + 1] = b;
+    }
+    __syncthreads();
     const float median = (n_samples > 0) ? block_median_select(dsamples, n_samples) : 0.0f;
     if (threadIdx.x == 0) {
         out[0] = *M; out[1] = *F; out[2] = __float_as_int(median); out[3] = 0;
@@ -1033,38 +1043,45 @@ __global__ void __launch_bounds__(MS_T) k_finish_view(const float* __restrict__ 
     for (int d = threadIdx.x; d < n_deliver; d += blockDim.x) out[8 + d] = start[(d + 1) * stride] - start[d * stride];
 }
 
-// filtered records in order, one warp per segment; four 32-match chunks per iteration keep several loads in flight.
-// Also counts the records per hand-over group (destination view's segment), the first step of the regrouping below.
-__global__ void k_filter_fill(const int* __restrict__ off, int n_cams, int n_src, const float* __restrict__ score,
-                              const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, const int* __restrict__ foff,
-                              l3d_match* __restrict__ out, const CamTable* __restrict__ cams, int stride, int* __restrict__ hist /* or null */)
+// filtered records (score > 1) in match order = the reference's order: an ordered compaction of the whole match list.
+// CTA b keeps cta_kept[b] records (k_reduce_matches), so it starts at the sum of the counts before it; inside the CTA
+// a ballot/prefix gives every kept match its place.  Also counts the records per hand-over group (destination
+// view's segment), the first step of the regrouping below.
+__global__ void __launch_bounds__(RM_T) k_filter_compact(const int* __restrict__ Mptr, const float* __restrict__ score, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
+                                                         const int* __restrict__ cta_kept, l3d_match* __restrict__ out, int* __restrict__ Fout,
+                                                         const CamTable* __restrict__ cams, int stride, int* __restrict__ hist /* or null */)
 {
     L3D_PDL_PROLOGUE();
-    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (row >= n_src) return;
-    const int s0 = off[row * n_cams], s1 = off[(row + 1) * n_cams];
-    int o = foff[row];
-    if (foff[row + 1] == o) return;
-    for (int k0 = s0; k0 < s1; k0 += 128) {
-        float c[4];
+    __shared__ int s_w[RM_T / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int k = blockIdx.x * RM_T + tid, M = *Mptr;
+    int part = 0;
+    for (int i = tid; i < int(blockIdx.x); i += RM_T) part += cta_kept[i];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { const int k = k0 + 32 * u + lane; c[u] = (k < s1) ? score[k] : 0.0f; }
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if (lane == 0) s_w[warp] = part;
+    __syncthreads();
+    int base = 0;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int k = k0 + 32 * u + lane;
-            const bool keep = c[u] > 1.0f;
-            const unsigned m = __ballot_sync(0xffffffffu, keep);
-            if (keep) {
-                const int r = o + __popc(m & ((1u << lane) - 1u));
-                const int4 id = m_ids[k]; const float4 d = m_dep[k];
-                l3d_match rec; rec.src_seg = id.x; rec.cam = id.y; rec.tgt_seg = id.z; rec.confidence = xd(c[u], 2.0f);
-                rec.depths[0] = d.x; rec.depths[1] = d.y; rec.depths[2] = d.z; rec.depths[3] = d.w;
-                out[r] = rec;
-                if (hist) { const int dl = cams[id.y].deliver; if (dl >= 0) atomicAdd(&hist[dl * stride + id.z], 1); }     // hand-over group sizes
-            }
-            o += __popc(m);
-        }
+    for (int w = 0; w < RM_T / 32; ++w) base += s_w[w];
+    __syncthreads();
+    const float c = (k < M) ? score[k] : 0.0f;
+    const bool keep = c > 1.0f;
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_w[warp] = __popc(m);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < RM_T / 32; ++w) { const int n = s_w[w]; if (w < warp) before += n; total += n; }
+    if (keep) {
+        const int r = base + before + __popc(m & ((1u << lane) - 1u));
+        const int4 id = m_ids[k]; const float4 d = m_dep[k];
+        l3d_match rec; rec.src_seg = id.x; rec.cam = id.y; rec.tgt_seg = id.z; rec.confidence = xd(c, 2.0f);
+        rec.depths[0] = d.x; rec.depths[1] = d.y; rec.depths[2] = d.z; rec.depths[3] = d.w;
+        out[r] = rec;
+        if (hist) { const int dl = cams[id.y].deliver; if (dl >= 0) atomicAdd(&hist[dl * stride + id.z], 1); }     // hand-over group sizes
     }
+    if (blockIdx.x == gridDim.x - 1 && tid == 0) *Fout = base + total;
 }
 // unscored variant (no neighbour to pair-test): all records, confidence 0
 __global__ void k_copy_unscored(const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, const int* __restrict__ Mptr, l3d_match* __restrict__ out)
@@ -1684,10 +1701,11 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     int* d_nitems = ctx->d_zero.p + z_items;
     unsigned long long* d_iters = reinterpret_cast<unsigned long long*>(ctx->d_zero.p + z_iters);
     int* d_hist = ctx->d_zero.p + z_hist; int* d_cursor = ctx->d_zero.p + z_cursor;
+    unsigned long long* d_best = reinterpret_cast<unsigned long long*>(ctx->d_zero.p + z_rank);     // [n_src], 8-byte aligned (z_rank is even)
     if (scored && M_ub > 0) {
         // ---- score ------------------------------------------------------------------------
         ScoreParams sp; sp.sigma_p = sigma_p; sp.sigma_a = sigma_a;
-        L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_src) + 1)); L3D_CUDA(ctx->d_foff.ensure(size_t(n_src) + 2));
+        L3D_CUDA(ctx->d_foff.ensure(4));
         L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2));
         // Segments are grouped by depth and scored through windows; the tiled quadratic kernel takes everything when
         // the 3-D gate is switched off, and segments with more matches than the window kernel's 20-bit index can hold.
@@ -1721,12 +1739,13 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         L3D_CUDA(cudaGetLastError());
         if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[4], st));
         // ---- reduce -----------------------------------------------------------------------
-        L3D_CUDA(pdl_launch(k_seg_reduce, dim3((n_src * 32 + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mdep.p, ctx->d_fcnt.p, ctx->d_dsamples.p, d_iters));
-        ctx->launches += 1;
-        if (scan_exclusive(ctx, ctx->d_fcnt.p, ctx->d_foff.p, n_src)) return 1;
-        d_F = ctx->d_foff.p + n_src;
-        L3D_CUDA(pdl_launch(k_filter_fill, dim3((n_src * 32 + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_foff.p, dfil.p, ctx->d_cams.p, stride, delivering ? d_hist : nullptr));
-        ctx->launches += 1;
+        const unsigned n_cta = unsigned((M_ub + RM_T - 1) / RM_T);
+        L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_cta) + 1));                       // kept matches per CTA
+        L3D_CUDA(pdl_launch(k_reduce_matches, dim3(n_cta), dim3(RM_T), 0, st, d_M, ctx->d_off.p, n_nb, ctx->d_score.p, ctx->d_mids.p, d_best, ctx->d_fcnt.p, d_iters));
+        d_F = ctx->d_foff.p;
+        L3D_CUDA(pdl_launch(k_filter_compact, dim3(n_cta), dim3(RM_T), 0, st, d_M, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_fcnt.p, dfil.p, ctx->d_foff.p,
+                            ctx->d_cams.p, stride, delivering ? d_hist : nullptr));
+        ctx->launches += 2;
         L3D_CUDA(cudaGetLastError());
     } else {
         if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[4], st));
@@ -1757,7 +1776,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     // ---- results: one kernel packs them, one copy; the host collects them in finish_view ----------------
     const int n_res = 8 + std::max(n_deliver, 1);
     L3D_CUDA(ctx->d_vres[par].ensure(size_t(n_res))); L3D_CUDA(ctx->h_vres[par].ensure(size_t(n_res)));
-    L3D_CUDA(pdl_launch(k_finish_view, dim3(1), dim3(MS_T), 0, st, ctx->d_dsamples.p, (scored && M_ub > 0) ? ns : 0, d_M, d_F, (scored && M_ub > 0) ? d_iters : nullptr,
+    L3D_CUDA(pdl_launch(k_finish_view, dim3(1), dim3(MS_T), 0, st, ctx->d_dsamples.p, (scored && M_ub > 0) ? ns : 0, d_best, ctx->d_mdep.p, d_M, d_F, (scored && M_ub > 0) ? d_iters : nullptr,
                         delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, ctx->d_vres[par].p));
     ctx->launches += 1;
     L3D_CUDA(cudaGetLastError());
