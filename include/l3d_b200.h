@@ -158,6 +158,9 @@ int l3d_retain_results(l3d_ctx* ctx, int on);
  * already running ahead fails (l3d_last_error says so; l3d_reset_matching starts over). */
 typedef struct { int32_t view; int32_t n_neighbors; const l3d_neighbor* neighbors; } l3d_view_plan;
 int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans);
+/* Tests only: pair tests per batch of the next announced schedules (0 = automatic: about an eighth of the schedule,
+ * at least 2.5e8, at most 2.4e10).  Small values force many batches on small scenes. */
+int l3d_debug_set_batch_pairs(l3d_ctx* ctx, uint64_t pairs);
 /* Forget all delivered-but-unconsumed records and any plan (a new compute3Dmodel run, line3D.cc:356). */
 int l3d_reset_matching(l3d_ctx* ctx);
 

@@ -87,7 +87,7 @@ def lib():
 
 
 EXPORTS = ["l3d_create", "l3d_destroy", "l3d_last_error", "l3d_collinearity", "l3d_collinearity_prealloc", "l3d_set_views", "l3d_match_view",
-           "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
+           "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_debug_set_batch_pairs", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
            "l3d_last_timings", "l3d_last_kernel_timings", "l3d_set_stage_timing", "l3d_mark", "l3d_marks_elapsed", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math", "l3d_flush_l2"]
 
 
@@ -167,6 +167,10 @@ class Context:
         for k, (view, nbs) in enumerate(schedule):
             plans[k].view = int(view); plans[k].n_neighbors = len(nbs); plans[k].neighbors = C.cast(keep[k], C.POINTER(Neighbor))
         self._check(self._L.l3d_plan_matching(self._h, len(schedule), plans))
+
+    def debug_set_batch_pairs(self, pairs: int):
+        self._L.l3d_debug_set_batch_pairs.argtypes = [C.c_void_p, C.c_uint64]
+        self._check(self._L.l3d_debug_set_batch_pairs(self._h, int(pairs)))
 
     def retain_results(self, on: bool):
         self._check(self._L.l3d_retain_results(self._h, int(bool(on))))

@@ -27,6 +27,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace l3d;
@@ -1388,6 +1389,36 @@ struct ViewJob {                 // phase B of one view: on the stream, not yet 
     std::vector<std::pair<int, int> > consumed;      // (deliver buffer, slot) of every delivery the view took in
 };
 
+// Everything one batch of pair tests (phase A) produces and needs: two of these exist, so that a helper thread can
+// run the next batch's pair tests on a second stream while the per-view work (phase B) of the current batch, which
+// leaves most of the GPU idle, goes on.
+struct PhaseASet {
+    cudaStream_t stream = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    size_t begin = 0, end = 0;                 // plan entries covered
+    DBuf<SrcHoist> d_sh; DBuf<TgtHoist> d_th; DBuf<int> d_row_job;
+    DBuf<unsigned> d_cand; DBuf<int> d_tile_sums, d_total;
+    DBuf<int> d_stage_col, d_stage_row; DBuf<float4> d_stage_dep; DBuf<unsigned char> d_stage_ok;
+    DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
+    std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands, job_raw; std::vector<int> job_rowmax, job_raw_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
+    bool pa_ms_pending = false;
+    cudaEvent_t pa_ev[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t pa_kev[4] = {nullptr, nullptr, nullptr, nullptr};   // around the k_pretest and k_exact_flat launches
+    bool pa_kev_set[2] = {false, false};
+    HBuf<int> h_res;
+    void release()
+    {
+        d_sh.release(); d_th.release(); d_row_job.release(); d_cand.release(); d_tile_sums.release(); d_total.release();
+        d_stage_col.release(); d_stage_row.release(); d_stage_dep.release(); d_stage_ok.release(); d_jobs.release();
+        d_pa_cnt.release(); d_pa_off.release(); d_pa_raw.release(); d_pa_idx.release(); d_pa_tot.release();
+        d_rm_begin.release(); d_rm_len.release(); d_rm_out.release(); h_res.release();
+        for (int k = 0; k < 3; ++k) if (pa_ev[k]) { cudaEventDestroy(pa_ev[k]); pa_ev[k] = nullptr; }
+        for (int k = 0; k < 4; ++k) if (pa_kev[k]) { cudaEventDestroy(pa_kev[k]); pa_kev[k] = nullptr; }
+        if (stream) { cudaStreamDestroy(stream); stream = nullptr; }
+    }
+};
+
 struct l3d_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -1404,23 +1435,20 @@ struct l3d_ctx {
     std::vector<DeliverBuf> deliver_bufs;
     // scratch
     DBuf<CamTable> d_cams; DBuf<int> d_slot_cam;
-    DBuf<SrcHoist> d_sh; DBuf<TgtHoist> d_th; DBuf<int> d_row_job;
-    DBuf<unsigned> d_cand; DBuf<int> d_cand_cnt, d_cand_off, d_tile_sums, d_total;
-    DBuf<int> d_stage_col, d_stage_row; DBuf<float4> d_stage_dep; DBuf<unsigned char> d_stage_ok;
+    DBuf<int> d_tile_sums, d_total;
     DBuf<int> d_cnt, d_off;
     DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
     DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
     DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl; DBuf<int> d_boff; DBuf<uint4> d_brange; int n_sm = 148;
-    // phase A (pair tests) of the resident batch
-    DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
-    std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands, job_raw; std::vector<int> job_rowmax, job_raw_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
+    // phase A (pair tests): the batch the per-view work reads (pa[cur]) and the one a helper thread prepares meanwhile
+    PhaseASet pa[2]; int cur = 0;
+    std::thread pa_worker; bool pa_worker_active = false; int pa_worker_rc = 0;
     std::vector<PlannedView> plan; size_t plan_next = 0; size_t batch_begin = 0, batch_end = 0;
-    float pa_ms[2] = {0.f, 0.f}; bool pa_ms_pending = false;
-    uint64_t pair_budget = 24000000000ull;
-    cudaEvent_t pa_ev[3] = {nullptr, nullptr, nullptr};
-    cudaEvent_t pa_kev[4] = {nullptr, nullptr, nullptr, nullptr};   // around the k_pretest and k_exact_flat launches
-    float pa_kernel_ms[2] = {0.f, 0.f}; bool pa_kev_set[2] = {false, false};
-    DBuf<int> d_res, d_zero; HBuf<int> h_res;
+    uint64_t pair_budget = 24000000000ull;          // most pair tests of one batch (3 GB of candidate bits)
+    uint64_t batch_pairs = 24000000000ull;          // pair tests per batch of the announced schedule (l3d_plan_matching)
+    uint64_t batch_override = 0;                    // l3d_debug_set_batch_pairs
+    float pa_kernel_ms[2] = {0.f, 0.f};
+    DBuf<int> d_res, d_zero;
     // two views in flight: everything the host or the copy stream touches while the next view runs exists twice
     ViewJob vjob[2]; int pending = -1, vnext = 0;
     DBuf<int> d_vres[2]; HBuf<int> h_vres[2]; HBuf<CamTable> h_cams2[2]; DBuf<l3d_match> d_filtered2[2];
@@ -1458,7 +1486,8 @@ inline cudaError_t pdl_launch(K kernel, dim3 grid, dim3 block, size_t smem, cuda
     return cudaLaunchKernelEx(&cfg, kernel, args...);
 }
 
-int scan_exclusive(l3d_ctx* ctx, const int* in, int* out /* n + 1 */, int n)
+template <typename C>
+int scan_exclusive(C* ctx, const int* in, int* out /* n + 1 */, int n)
 {
     if (n <= SCAN_SMALL) {
         L3D_CUDA(pdl_launch(k_scan_small, dim3(1), dim3(SCAN_T), 0, ctx->stream, in, out, n));
@@ -1502,8 +1531,9 @@ void release_delivered(l3d_ctx* ctx, Delivered& d)
 // Phase A for a set of (source view, neighbour) jobs: hoist, pre-test, scan, exact test.
 // Results stay on the device: d_pa_off (candidate offsets per global row = staging ranges),
 // d_pa_raw (raw matches per global row), d_stage_col / d_stage_dep.
-int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
+int run_phase_a(l3d_ctx* cx, PhaseASet* ctx, const std::vector<JobHost>& jh)   // ctx: the set being filled (the error macro writes ctx->err)
 {
+    L3D_CUDA(cudaSetDevice(cx->device));
     cudaStream_t st = ctx->stream;
     const int n_jobs = int(jh.size());
     ctx->jobs_host.assign(size_t(n_jobs), JobDev());
@@ -1515,11 +1545,11 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     long long sh_tot = 0, th_tot = 0, words = 0, rows = 0, blocks = 0;
     int max_n = 1;
     for (int j = 0; j < n_jobs; ++j) {
-        const l3d_view& sv = ctx->views[jh[j].src_view]; const l3d_view& tv = ctx->views[jh[j].tgt_view];
+        const l3d_view& sv = cx->views[jh[j].src_view]; const l3d_view& tv = cx->views[jh[j].tgt_view];
         JobDev& d = ctx->jobs_host[j];
         memcpy(d.F, jh[j].F, sizeof d.F); memcpy(d.RtKinv_s, sv.RtKinv, sizeof d.RtKinv_s); memcpy(d.RtKinv_t, tv.RtKinv, sizeof d.RtKinv_t);
         memcpy(d.C_s, sv.C, sizeof d.C_s); memcpy(d.C_t, tv.C, sizeof d.C_t);
-        d.src_off = ctx->seg_off[jh[j].src_view]; d.n_src = sv.n_segments; d.tgt_off = ctx->seg_off[jh[j].tgt_view]; d.n_tgt = tv.n_segments;
+        d.src_off = cx->seg_off[jh[j].src_view]; d.n_src = sv.n_segments; d.tgt_off = cx->seg_off[jh[j].tgt_view]; d.n_tgt = tv.n_segments;
         d.sh_off = int(sh_tot); d.th_off = int(th_tot); d.cand_off = words; d.wpr = (d.n_tgt + 31) / 32;
         d.row_off = int(rows); d.blk_off = int(blocks); d.col_blocks = std::max((d.n_tgt + PT_COLS - 1) / PT_COLS, 1);
         sh_tot += d.n_src; th_tot += d.n_tgt; words += (long long)d.n_src * d.wpr; rows += d.n_src;
@@ -1535,7 +1565,7 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     L3D_CUDA(cudaMemsetAsync(ctx->d_pa_cnt.p, 0, sizeof(int) * (size_t(rows) + 1), st));
     L3D_CUDA(cudaEventRecord(ctx->pa_ev[0], st));
     if (rows > 0 && blocks > 0) {
-        k_hoist<<<dim3((max_n + 127) / 128, n_jobs), 128, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, ctx->d_sh.p, ctx->d_th.p, ctx->d_row_job.p);
+        k_hoist<<<dim3((max_n + 127) / 128, n_jobs), 128, 0, st>>>(cx->d_segs.p, ctx->d_jobs.p, ctx->d_sh.p, ctx->d_th.p, ctx->d_row_job.p);
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[0], st));
         k_pretest<<<unsigned(blocks), PT_BLOCK, 0, st>>>(ctx->d_sh.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_cand.p, ctx->d_pa_cnt.p);
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[1], st));
@@ -1575,7 +1605,7 @@ int run_phase_a(l3d_ctx* ctx, const std::vector<JobHost>& jh)
     if (rows > 0 && n_cand > 0) {
         k_expand<<<unsigned((rows * 32 + 255) / 256), 256, 0, st>>>(ctx->d_jobs.p, ctx->d_row_job.p, int(rows), ctx->d_cand.p, ctx->d_pa_off.p, ctx->d_stage_col.p, ctx->d_stage_row.p);
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[2], st));
-        k_exact_flat<<<unsigned((n_cand + EF_T - 1) / EF_T), EF_T, 0, st>>>(ctx->d_segs.p, ctx->d_jobs.p, ctx->d_row_job.p, n_cand, ctx->d_stage_col.p, ctx->d_stage_row.p,
+        k_exact_flat<<<unsigned((n_cand + EF_T - 1) / EF_T), EF_T, 0, st>>>(cx->d_segs.p, ctx->d_jobs.p, ctx->d_row_job.p, n_cand, ctx->d_stage_col.p, ctx->d_stage_row.p,
                                                                           ctx->d_stage_ok.p, ctx->d_stage_dep.p, ctx->d_pa_raw.p);
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[3], st));
         ctx->pa_kev_set[1] = true;
@@ -1617,6 +1647,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         if (c > 0 && nb[c - 1].view >= nb[c].view) { ctx->err = "l3d_match_view: neighbours must be in ascending view order"; return 1; }
     }
     cudaStream_t st = ctx->stream;
+    PhaseASet& pa = ctx->pa[ctx->cur];
     const l3d_view& sv = ctx->views[view];
     const int n_src = sv.n_segments;
     const int par = job.parity;
@@ -1643,8 +1674,8 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         ct.t_start = nullptr; ct.t_tgt = nullptr; ct.t_dep = nullptr; ct.slot = -1; ct.deliver = -1; ct.row_off = 0;
         if (n.to_be_matched) {
             const int j = first_job + n_slots;
-            ct.mode = 0; ct.slot = n_slots++; ct.row_off = ctx->jobs_host[j].row_off;
-            cand_ub += ctx->job_cands[j]; raw_ub += ctx->job_raw[j]; seg_ub += size_t(ctx->job_raw_rowmax[j]);
+            ct.mode = 0; ct.slot = n_slots++; ct.row_off = pa.jobs_host[j].row_off;
+            cand_ub += pa.job_cands[j]; raw_ub += pa.job_raw[j]; seg_ub += size_t(pa.job_raw_rowmax[j]);
             pair_tests += uint64_t(n_src) * uint64_t(tv.n_segments);
         } else {
             ct.mode = 2;
@@ -1670,7 +1701,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     // ---- assemble the match list ----------------------------------------------------------
     const int* d_M = ctx->d_off.p + size_t(n_src) * n_nb;             // total number of matches, on the device
     if (n_src > 0) {
-        L3D_CUDA(pdl_launch(k_gather_counts, dim3(dim3((n_src + 255) / 256, n_nb)), dim3(256), 0, st, ctx->d_cams.p, n_nb, n_src, ctx->d_pa_raw.p, ctx->d_cnt.p));
+        L3D_CUDA(pdl_launch(k_gather_counts, dim3(dim3((n_src + 255) / 256, n_nb)), dim3(256), 0, st, ctx->d_cams.p, n_nb, n_src, pa.d_pa_raw.p, ctx->d_cnt.p));
         ctx->launches += 1;
         if (scan_exclusive(ctx, ctx->d_cnt.p, ctx->d_off.p, n_src * n_nb)) return 1;
     } else {
@@ -1679,8 +1710,8 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     if (M_ub > 0) {
         L3D_CUDA(ctx->d_mids.ensure(M_ub)); L3D_CUDA(ctx->d_mdep.ensure(M_ub)); L3D_CUDA(ctx->d_score.ensure(M_ub));
         const long warps = long(n_src) * n_nb;
-        L3D_CUDA(pdl_launch(k_fill, dim3(unsigned((warps * 32 + 255) / 256)), dim3(256), 0, st, ctx->d_cams.p, n_nb, n_src, ctx->d_off.p, ctx->d_pa_off.p,
-                                                                  ctx->d_stage_col.p, ctx->d_stage_dep.p, ctx->d_stage_ok.p, ctx->d_mids.p, ctx->d_mdep.p));
+        L3D_CUDA(pdl_launch(k_fill, dim3(unsigned((warps * 32 + 255) / 256)), dim3(256), 0, st, ctx->d_cams.p, n_nb, n_src, ctx->d_off.p, pa.d_pa_off.p,
+                                                                  pa.d_stage_col.p, pa.d_stage_dep.p, pa.d_stage_ok.p, ctx->d_mids.p, ctx->d_mdep.p));
         ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
     }
@@ -1791,7 +1822,7 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         for (int c = 0; c < n_nb; ++c) {
             const int d = hc.p[c].deliver;
             if (d < 0) continue;
-            const uint64_t ub = std::min<uint64_t>(hc.p[c].slot >= 0 ? ctx->job_raw[first_job + hc.p[c].slot] : uint64_t(M_ub), 0x7fffffffull);
+            const uint64_t ub = std::min<uint64_t>(hc.p[c].slot >= 0 ? pa.job_raw[first_job + hc.p[c].slot] : uint64_t(M_ub), 0x7fffffffull);
             Delivered dl; dl.from_view = view; dl.owner = job.owner; dl.slot = d;
             dl.count = int(ub); dl.max_group = int(std::min<uint64_t>(ub, uint64_t(n_src)));      // a source segment matches a target segment once
             dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
@@ -1868,21 +1899,60 @@ int finish_view(l3d_ctx* ctx, ViewJob& job, l3d_match_result* res, bool copy_bac
     res->filtered = dst;
     float ms;
     ctx->last_ms[0] = ctx->last_ms[1] = 0.f;
-    if (ctx->pa_ms_pending) {                          // phase A of a whole batch is booked on the first view collected after it
-        ms = 0.f; cudaEventElapsedTime(&ms, ctx->pa_ev[0], ctx->pa_ev[1]); ctx->last_ms[0] = ms;
-        ms = 0.f; cudaEventElapsedTime(&ms, ctx->pa_ev[1], ctx->pa_ev[2]); ctx->last_ms[1] = ms;
-        for (int k = 0; k < 2; ++k) { ms = 0.f; if (ctx->pa_kev_set[k]) cudaEventElapsedTime(&ms, ctx->pa_kev[2 * k], ctx->pa_kev[2 * k + 1]); ctx->pa_kernel_ms[k] = ms; }
-        ctx->pa_ms_pending = false;
+    PhaseASet& pa = ctx->pa[ctx->cur];
+    if (pa.pa_ms_pending) {                            // phase A of a whole batch is booked on the first view collected after it
+        ms = 0.f; cudaEventElapsedTime(&ms, pa.pa_ev[0], pa.pa_ev[1]); ctx->last_ms[0] = ms;
+        ms = 0.f; cudaEventElapsedTime(&ms, pa.pa_ev[1], pa.pa_ev[2]); ctx->last_ms[1] = ms;
+        for (int k = 0; k < 2; ++k) { ms = 0.f; if (pa.pa_kev_set[k]) cudaEventElapsedTime(&ms, pa.pa_kev[2 * k], pa.pa_kev[2 * k + 1]); ctx->pa_kernel_ms[k] = ms; }
+        pa.pa_ms_pending = false;
     }
     for (int k = 2; k < 5; ++k) { ms = 0.f; if (ctx->stage_events) cudaEventElapsedTime(&ms, ctx->vev[par][k], ctx->vev[par][k + 1]); ctx->last_ms[k] = ms; }
     ctx->last_ms[5] = ctx->last_ms[0] + ctx->last_ms[1] + ctx->last_ms[2] + ctx->last_ms[3] + ctx->last_ms[4];
     return 0;
 }
 
-// Collects a view that was put on the stream ahead of its call and is not going to be asked for.
+int join_worker(l3d_ctx* ctx);
+
+// Collects a view that was put on the stream ahead of its call and is not going to be asked for (and the helper thread).
 void drain_pending(l3d_ctx* ctx)
 {
+    join_worker(ctx);
     if (ctx->pending >= 0) { l3d_match_result dummy; finish_view(ctx, ctx->vjob[ctx->pending], &dummy, false); ctx->pending = -1; }
+}
+
+// The batch of the announced schedule that starts at plan entry `from`: its job list, and where it ends.
+size_t plan_batch(l3d_ctx* ctx, size_t from, std::vector<JobHost>& jh)
+{
+    size_t e = from; uint64_t pairs = 0;
+    while (e < ctx->plan.size() && (e == from || pairs + ctx->plan[e].pair_tests <= ctx->batch_pairs)) {
+        PlannedView& pv = ctx->plan[e];
+        pv.first_job = int(jh.size());
+        for (size_t c = 0; c < pv.nb.size(); ++c)
+            if (pv.nb[c].to_be_matched) { JobHost j; j.src_view = pv.view; j.tgt_view = pv.nb[c].view; memcpy(j.F, pv.nb[c].F, sizeof j.F); jh.push_back(j); }
+        pairs += pv.pair_tests; ++e;
+    }
+    return e;
+}
+
+// Pair tests of the batch starting at `from`, on the helper thread and the second stream, into the set that is not
+// in use.  The per-view work of a batch keeps only a fraction of the SMs busy (short dependent kernels); the pair
+// tests of the next batch fill the rest.
+void start_worker(l3d_ctx* ctx, size_t from)
+{
+    PhaseASet* set = &ctx->pa[ctx->cur ^ 1];
+    std::vector<JobHost> jh;
+    set->begin = from; set->end = plan_batch(ctx, from, jh);
+    ctx->pa_worker_rc = 0;
+    ctx->pa_worker = std::thread([ctx, set, jh]() { ctx->pa_worker_rc = run_phase_a(ctx, set, jh); });
+    ctx->pa_worker_active = true;
+}
+
+int join_worker(l3d_ctx* ctx)
+{
+    if (!ctx->pa_worker_active) return 0;
+    ctx->pa_worker.join();
+    ctx->pa_worker_active = false;
+    return ctx->pa_worker_rc;
 }
 
 int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float sigma_p, float sigma_a, l3d_match_result* res, bool copy_back)
@@ -1905,27 +1975,34 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         // ---- phase A: from the announced schedule (batched), or for this view alone -----------
         int first_job = 0;
         if (ctx->plan_next < ctx->plan.size() && ctx->plan[ctx->plan_next].view == view && same_neighbors(ctx->plan[ctx->plan_next].nb, n_nb, nb)) {
-            if (ctx->plan_next >= ctx->batch_end) {                 // start the next batch here
-                std::vector<JobHost> jh;
-                size_t e = ctx->plan_next; uint64_t pairs = 0;
-                while (e < ctx->plan.size() && (e == ctx->plan_next || pairs + ctx->plan[e].pair_tests <= ctx->pair_budget)) {
-                    PlannedView& pv = ctx->plan[e];
-                    pv.first_job = int(jh.size());
-                    for (size_t c = 0; c < pv.nb.size(); ++c)
-                        if (pv.nb[c].to_be_matched) { JobHost j; j.src_view = pv.view; j.tgt_view = pv.nb[c].view; memcpy(j.F, pv.nb[c].F, sizeof j.F); jh.push_back(j); }
-                    pairs += pv.pair_tests; ++e;
+            if (ctx->plan_next >= ctx->batch_end) {                 // the next batch starts here
+                if (ctx->pa_worker_active) {                         // its pair tests were started while the previous batch was scored
+                    PhaseASet& nx = ctx->pa[ctx->cur ^ 1];
+                    if (join_worker(ctx)) { ctx->err = nx.err; return 1; }
+                    if (nx.begin != ctx->plan_next) { ctx->err = "l3d_match_view: internal error (batch out of step)"; return 1; }
+                    ctx->cur ^= 1;
+                } else {
+                    std::vector<JobHost> jh;
+                    PhaseASet& set = ctx->pa[ctx->cur];
+                    set.begin = ctx->plan_next; set.end = plan_batch(ctx, ctx->plan_next, jh);
+                    if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
                 }
-                if (run_phase_a(ctx, jh)) return 1;
-                ctx->batch_begin = ctx->plan_next; ctx->batch_end = e;
+                PhaseASet& set = ctx->pa[ctx->cur];
+                ctx->batch_begin = set.begin; ctx->batch_end = set.end;
+                ctx->launches += set.launches; set.launches = 0;
+                if (ctx->batch_end < ctx->plan.size()) start_worker(ctx, ctx->batch_end);     // the following batch, meanwhile
             }
             first_job = ctx->plan[ctx->plan_next].first_job;
             ++ctx->plan_next;
         } else {
+            join_worker(ctx);
             ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;      // a call off the schedule voids it
             std::vector<JobHost> jh;
             for (int c = 0; c < n_nb; ++c)
                 if (nb[c].to_be_matched) { JobHost j; j.src_view = view; j.tgt_view = nb[c].view; memcpy(j.F, nb[c].F, sizeof j.F); jh.push_back(j); }
-            if (run_phase_a(ctx, jh)) return 1;
+            PhaseASet& set = ctx->pa[ctx->cur];
+            if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
+            ctx->launches += set.launches; set.launches = 0;
         }
         ci = ctx->vnext; ctx->vnext ^= 1;
         ctx->vjob[ci].parity = ci;
@@ -1961,7 +2038,9 @@ int l3d_create(int device, l3d_ctx** out)
     l3d_ctx* ctx = new l3d_ctx();
     ctx->device = device;
     { int sm = 0; if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && sm > 0) ctx->n_sm = sm; }
-    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); delete ctx; return 1; }
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);        // the per-view chain is latency-bound: it goes first
+    if ((e = cudaStreamCreateWithPriority(&ctx->stream, cudaStreamNonBlocking, prio_hi)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); delete ctx; return 1; }
     {   // keep stream-ordered allocations cached across synchronisations (hand-over buffers are allocated per view)
         cudaMemPool_t pool; unsigned long long keep = ~0ull;
         if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
@@ -1969,9 +2048,13 @@ int l3d_create(int device, l3d_ctx** out)
     for (int k = 0; k < 8; ++k) cudaEventCreate(&ctx->ev[k]);
     for (int q = 0; q < 2; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->vev[q][k]);
     if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); cudaStreamDestroy(ctx->stream); delete ctx; return 1; }
-    for (int k = 0; k < 3; ++k) cudaEventCreate(&ctx->pa_ev[k]);
+    for (int q = 0; q < 2; ++q) {
+        PhaseASet& set = ctx->pa[q];
+        if ((e = cudaStreamCreateWithPriority(&set.stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); l3d_destroy(ctx); return 1; }
+        for (int k = 0; k < 3; ++k) cudaEventCreate(&set.pa_ev[k]);
+        for (int k = 0; k < 4; ++k) cudaEventCreate(&set.pa_kev[k]);
+    }
     for (int k = 0; k < 2; ++k) cudaEventCreate(&ctx->mark_ev[k]);
-    for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->pa_kev[k]);
     *out = ctx;
     return 0;
 }
@@ -1997,18 +2080,17 @@ void l3d_destroy(l3d_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     l3d_reset_matching(ctx);
-    ctx->d_segs.release(); ctx->d_viewd.release(); ctx->d_cams.release(); ctx->d_slot_cam.release(); ctx->d_sh.release(); ctx->d_th.release(); ctx->d_row_job.release();
-    ctx->d_cand.release(); ctx->d_cand_cnt.release(); ctx->d_cand_off.release(); ctx->d_tile_sums.release(); ctx->d_total.release();
-    ctx->d_stage_col.release(); ctx->d_stage_row.release(); ctx->d_stage_ok.release(); ctx->d_stage_dep.release(); ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
+    ctx->d_segs.release(); ctx->d_viewd.release(); ctx->d_cams.release(); ctx->d_slot_cam.release(); ctx->pa[0].release(); ctx->pa[1].release();
+    ctx->d_tile_sums.release(); ctx->d_total.release();
+    ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
     ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
     for (int q = 0; q < 2; ++q) { ctx->d_filtered2[q].release(); ctx->d_vres[q].release(); ctx->h_vres[q].release(); ctx->h_cams2[q].release(); for (int k = 0; k < 6; ++k) if (ctx->vev[q][k]) cudaEventDestroy(ctx->vev[q][k]); }
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (size_t k = 0; k < ctx->arena.size(); ++k) cudaFreeHost(ctx->arena[k].first);
     ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_boff.release(); ctx->d_brange.release();
-    ctx->d_rm_begin.release(); ctx->d_rm_len.release(); ctx->d_rm_out.release(); ctx->d_jobs.release(); ctx->d_pa_cnt.release(); ctx->d_pa_off.release(); ctx->d_pa_raw.release(); ctx->d_pa_idx.release(); ctx->d_pa_tot.release(); ctx->d_res.release(); ctx->d_zero.release(); ctx->h_res.release();
-    for (int k = 0; k < 3; ++k) if (ctx->pa_ev[k]) cudaEventDestroy(ctx->pa_ev[k]);
+    ctx->d_res.release(); ctx->d_zero.release();
     for (int k = 0; k < 2; ++k) if (ctx->mark_ev[k]) cudaEventDestroy(ctx->mark_ev[k]);
-    for (int k = 0; k < 4; ++k) if (ctx->pa_kev[k]) cudaEventDestroy(ctx->pa_kev[k]); ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
+    ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
     ctx->h_filtered.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
     ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release();
@@ -2148,6 +2230,18 @@ int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
         }
         ctx->plan.push_back(pv);
     }
+    // Batches: the pair tests of batch i + 1 run beside the per-view work of batch i, so the schedule is cut into
+    // about eight of them (not smaller than 2.5e8 pair tests: a batch has fixed costs), none above the memory budget.
+    uint64_t total = 0;
+    for (size_t k = 0; k < ctx->plan.size(); ++k) total += ctx->plan[k].pair_tests;
+    ctx->batch_pairs = ctx->batch_override ? ctx->batch_override : std::min<uint64_t>(ctx->pair_budget, std::max<uint64_t>(total / 8, 250000000ull));
+    return 0;
+}
+
+int l3d_debug_set_batch_pairs(l3d_ctx* ctx, uint64_t pairs)
+{
+    if (!ctx) return 1;
+    ctx->batch_override = pairs;
     return 0;
 }
 

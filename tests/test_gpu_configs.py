@@ -106,6 +106,15 @@ def test_plan_run_ahead_and_retained_results(tmp_path):
             assert np.array_equal(got[v]["filtered"], plain[v]["filtered"]), (plan, retain, v)
             for k in ("pair_tests", "n_raw", "n_delivered", "n_scored", "n_filtered", "score_iters", "score_iters_other_cam", "median_depth", "scored"):
                 assert got[v][k] == plain[v][k], (plan, retain, v, k)
+    # many small batches: the pair tests of each batch run on a helper thread and a second stream while the views of the
+    # batch before it are scored
+    for pairs in (1, 3_000_000, 20_000_000):
+        ctx.debug_set_batch_pairs(pairs)
+        got = util.run_matching(ctx, ids, views, F, vn, plan=True, retain=(pairs == 1))
+        for v in plain:
+            assert np.array_equal(got[v]["filtered"], plain[v]["filtered"]), (pairs, v)
+            assert got[v]["median_depth"] == plain[v]["median_depth"] and got[v]["n_delivered"] == plain[v]["n_delivered"], (pairs, v)
+    ctx.debug_set_batch_pairs(0)
     rows = np.concatenate([util.filtered_as_rows(v, plain[v]) for v in sorted(plain)])
     key = lambda a: np.lexsort((a[:, 3], a[:, 2], a[:, 1], a[:, 0]))
     assert np.array_equal(rows[key(rows)], dm["filtered_matches"][key(dm["filtered_matches"])])
