@@ -1388,6 +1388,27 @@ struct ViewJob {                 // phase B of one view: on the stream, not yet 
     int n_deliver = 0, owner = -1;
     std::vector<std::pair<int, int> > consumed;      // (deliver buffer, slot) of every delivery the view took in
 };
+// The hand-over between views is a dependency graph, not a chain (C2: 200 views, longest chain 50), so several views
+// are on the GPU at once: VS_W slots, each with its own scratch buffers, on VS_S streams; a view waits for the events
+// of the views whose records it receives.  The caller still gets its results in the order of its calls.
+constexpr int VS_W = 8, VS_S = 4;
+struct ViewSlot {
+    ViewJob job;
+    cudaStream_t stream = nullptr;                   // one of l3d_ctx::vstream
+    std::string err; uint64_t launches = 0; DBuf<int> d_tile_sums, d_total;      // what scan_exclusive wants from its context
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [0] results on the host, [2..5] stage boundaries
+    DBuf<CamTable> d_cams; HBuf<CamTable> h_cams;
+    DBuf<int> d_cnt, d_off, d_fcnt, d_foff, d_boff, d_zero, d_vres; HBuf<int> h_vres;
+    DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score, d_dsamples, d_sk, d_sd2; DBuf<unsigned> d_spl;
+    DBuf<int2> d_items; DBuf<uint4> d_brange; DBuf<l3d_match> d_filtered;
+    void release()
+    {
+        d_cams.release(); h_cams.release(); d_cnt.release(); d_off.release(); d_fcnt.release(); d_foff.release(); d_boff.release(); d_zero.release();
+        d_vres.release(); h_vres.release(); d_mids.release(); d_mdep.release(); d_score.release(); d_dsamples.release(); d_sk.release(); d_sd2.release();
+        d_spl.release(); d_items.release(); d_brange.release(); d_filtered.release(); d_tile_sums.release(); d_total.release();
+        for (int k = 0; k < 6; ++k) if (ev[k]) { cudaEventDestroy(ev[k]); ev[k] = nullptr; }
+    }
+};
 
 // Everything one batch of pair tests (phase A) produces and needs: two of these exist, so that a helper thread can
 // run the next batch's pair tests on a second stream while the per-view work (phase B) of the current batch, which
@@ -1434,12 +1455,8 @@ struct l3d_ctx {
     std::vector<std::vector<Delivered> > delivered;   // per destination view
     std::vector<DeliverBuf> deliver_bufs;
     // scratch
-    DBuf<CamTable> d_cams; DBuf<int> d_slot_cam;
     DBuf<int> d_tile_sums, d_total;
-    DBuf<int> d_cnt, d_off;
-    DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score;
-    DBuf<int> d_fcnt, d_foff; DBuf<float> d_dsamples, d_median; DBuf<unsigned long long> d_iters;
-    DBuf<int2> d_items; DBuf<int> d_nitems; size_t score_smem = 48 * 1024; DBuf<int> d_medrank; DBuf<float> d_sk, d_sd2; DBuf<unsigned> d_spl; DBuf<int> d_boff; DBuf<uint4> d_brange; int n_sm = 148;
+    size_t score_smem = 48 * 1024; int n_sm = 148;
     // phase A (pair tests): the batch the per-view work reads (pa[cur]) and the one a helper thread prepares meanwhile
     PhaseASet pa[2]; int cur = 0;
     std::thread pa_worker; bool pa_worker_active = false; int pa_worker_rc = 0;
@@ -1449,10 +1466,11 @@ struct l3d_ctx {
     uint64_t batch_override = 0;                    // l3d_debug_set_batch_pairs
     float pa_kernel_ms[2] = {0.f, 0.f};
     DBuf<int> d_res, d_zero;
-    // two views in flight: everything the host or the copy stream touches while the next view runs exists twice
-    ViewJob vjob[2]; int pending = -1, vnext = 0;
-    DBuf<int> d_vres[2]; HBuf<int> h_vres[2]; HBuf<CamTable> h_cams2[2]; DBuf<l3d_match> d_filtered2[2];
-    cudaEvent_t vev[2][6] = {{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}};
+    // views in flight: plan entries [fly_begin, fly_end) are on the GPU, entry i in slot i % VS_W on stream i % VS_S
+    ViewSlot vs[VS_W]; cudaStream_t vstream[VS_S] = {nullptr, nullptr, nullptr, nullptr};
+    size_t fly_begin = 0, fly_end = 0; std::vector<int> inflight_slot;   // per view: its slot while in flight, else -1
+    float run_sigma_p = 0.f, run_sigma_a = 0.f;
+    cudaEvent_t join_ev = nullptr;
     cudaStream_t copy_stream = nullptr;
     bool stage_events = false;         // per-stage CUDA events inside a view (l3d_set_stage_timing): they separate kernels that otherwise overlap
     cudaEvent_t mark_ev[2] = {nullptr, nullptr};
@@ -1639,21 +1657,21 @@ bool same_neighbors(const std::vector<l3d_neighbor>& a, int n, const l3d_neighbo
 // Phase B of one view is split in two so that the next view of an announced schedule can be put on the stream
 // before the host waits for this one: enqueue_view launches everything (sizes come from upper bounds, the real
 // counts stay on the device), finish_view waits for the view's small result record and fetches its output.
-int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float sigma_p, float sigma_a, int first_job, ViewJob& job)
+int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float sigma_p, float sigma_a, int first_job, ViewSlot& sl)
 {
     if (view < 0 || view >= ctx->V) { ctx->err = "l3d_match_view: view index out of range"; return 1; }
     for (int c = 0; c < n_nb; ++c) {
         if (nb[c].view < 0 || nb[c].view >= ctx->V || nb[c].view == view) { ctx->err = "l3d_match_view: bad neighbour view index"; return 1; }
         if (c > 0 && nb[c - 1].view >= nb[c].view) { ctx->err = "l3d_match_view: neighbours must be in ascending view order"; return 1; }
     }
-    cudaStream_t st = ctx->stream;
+    cudaStream_t st = sl.stream;
+    ViewJob& job = sl.job;
     PhaseASet& pa = ctx->pa[ctx->cur];
     const l3d_view& sv = ctx->views[view];
     const int n_src = sv.n_segments;
-    const int par = job.parity;
-    HBuf<CamTable>& hc = ctx->h_cams2[par];
-    DBuf<l3d_match>& dfil = ctx->d_filtered2[par];
-    cudaEvent_t* ev = ctx->vev[par];
+    HBuf<CamTable>& hc = sl.h_cams;
+    DBuf<l3d_match>& dfil = sl.d_filtered;
+    cudaEvent_t* ev = sl.ev;
     job.view = view; job.nb.assign(nb, nb + n_nb); job.sigma_p = sigma_p; job.sigma_a = sigma_a;
     job.consumed.clear(); job.owner = -1;
 
@@ -1681,7 +1699,11 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
             ct.mode = 2;
             std::vector<Delivered>& dl = ctx->delivered[view];
             for (size_t k = 0; k < dl.size(); ++k)
-                if (dl[k].from_view == n.view) { ct.mode = 1; ct.t_start = dl[k].t_start; ct.t_tgt = dl[k].t_tgt; ct.t_dep = dl[k].t_dep; delivered_ub += uint64_t(dl[k].count); seg_ub += size_t(dl[k].max_group); consumed.push_back(int(k)); job.consumed.push_back(std::make_pair(dl[k].owner, dl[k].slot)); break; }
+                if (dl[k].from_view == n.view) {
+                    // the records come from a view that may still be running on another stream
+                    const int ps = ctx->inflight_slot[dl[k].from_view];
+                    if (ps >= 0 && ctx->vs[ps].stream != st) L3D_CUDA(cudaStreamWaitEvent(st, ctx->vs[ps].ev[0], 0));
+                    ct.mode = 1; ct.t_start = dl[k].t_start; ct.t_tgt = dl[k].t_tgt; ct.t_dep = dl[k].t_dep; delivered_ub += uint64_t(dl[k].count); seg_ub += size_t(dl[k].max_group); consumed.push_back(int(k)); job.consumed.push_back(std::make_pair(dl[k].owner, dl[k].slot)); break; }
         }
         if (n.deliver) { ct.deliver = n_deliver++; max_deliver_seg = std::max(max_deliver_seg, tv.n_segments); }
     }
@@ -1692,26 +1714,26 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     src.seg_off = ctx->seg_off[view]; src.n_seg = n_src;
     const size_t M_ub = size_t(raw_ub + delivered_ub);          // upper bound on the number of matches to score
 
-    L3D_CUDA(ctx->d_cams.ensure(size_t(n_nb)));
-    L3D_CUDA(cudaMemcpyAsync(ctx->d_cams.p, hc.p, sizeof(CamTable) * n_nb, cudaMemcpyHostToDevice, st));
-    L3D_CUDA(ctx->d_cnt.ensure(size_t(n_src) * n_nb + 1));
-    L3D_CUDA(ctx->d_off.ensure(size_t(n_src) * n_nb + 2));
+    L3D_CUDA(sl.d_cams.ensure(size_t(n_nb)));
+    L3D_CUDA(cudaMemcpyAsync(sl.d_cams.p, hc.p, sizeof(CamTable) * n_nb, cudaMemcpyHostToDevice, st));
+    L3D_CUDA(sl.d_cnt.ensure(size_t(n_src) * n_nb + 1));
+    L3D_CUDA(sl.d_off.ensure(size_t(n_src) * n_nb + 2));
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[2], st));
 
     // ---- assemble the match list ----------------------------------------------------------
-    const int* d_M = ctx->d_off.p + size_t(n_src) * n_nb;             // total number of matches, on the device
+    const int* d_M = sl.d_off.p + size_t(n_src) * n_nb;             // total number of matches, on the device
     if (n_src > 0) {
-        L3D_CUDA(pdl_launch(k_gather_counts, dim3(dim3((n_src + 255) / 256, n_nb)), dim3(256), 0, st, ctx->d_cams.p, n_nb, n_src, pa.d_pa_raw.p, ctx->d_cnt.p));
+        L3D_CUDA(pdl_launch(k_gather_counts, dim3(dim3((n_src + 255) / 256, n_nb)), dim3(256), 0, st, sl.d_cams.p, n_nb, n_src, pa.d_pa_raw.p, sl.d_cnt.p));
         ctx->launches += 1;
-        if (scan_exclusive(ctx, ctx->d_cnt.p, ctx->d_off.p, n_src * n_nb)) return 1;
+        if (scan_exclusive(&sl, sl.d_cnt.p, sl.d_off.p, n_src * n_nb)) { ctx->err = sl.err; return 1; }
     } else {
-        L3D_CUDA(cudaMemsetAsync(ctx->d_off.p, 0, sizeof(int) * 2, st));
+        L3D_CUDA(cudaMemsetAsync(sl.d_off.p, 0, sizeof(int) * 2, st));
     }
     if (M_ub > 0) {
-        L3D_CUDA(ctx->d_mids.ensure(M_ub)); L3D_CUDA(ctx->d_mdep.ensure(M_ub)); L3D_CUDA(ctx->d_score.ensure(M_ub));
+        L3D_CUDA(sl.d_mids.ensure(M_ub)); L3D_CUDA(sl.d_mdep.ensure(M_ub)); L3D_CUDA(sl.d_score.ensure(M_ub));
         const long warps = long(n_src) * n_nb;
-        L3D_CUDA(pdl_launch(k_fill, dim3(unsigned((warps * 32 + 255) / 256)), dim3(256), 0, st, ctx->d_cams.p, n_nb, n_src, ctx->d_off.p, pa.d_pa_off.p,
-                                                                  pa.d_stage_col.p, pa.d_stage_dep.p, pa.d_stage_ok.p, ctx->d_mids.p, ctx->d_mdep.p));
+        L3D_CUDA(pdl_launch(k_fill, dim3(unsigned((warps * 32 + 255) / 256)), dim3(256), 0, st, sl.d_cams.p, n_nb, n_src, sl.d_off.p, pa.d_pa_off.p,
+                                                                  pa.d_stage_col.p, pa.d_stage_dep.p, pa.d_stage_ok.p, sl.d_mids.p, sl.d_mdep.p));
         ctx->launches += 1;
         L3D_CUDA(cudaGetLastError());
     }
@@ -1720,30 +1742,29 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
     const bool scored = n_slots > 0;                  // cudawrapper.cu:877-878
     const int* d_F = nullptr;                         // number of output records, on the device
     L3D_CUDA(dfil.ensure(std::max<size_t>(M_ub, 1)));
-    L3D_CUDA(ctx->d_median.ensure(4));
     // everything that has to start from zero lives in one buffer and is cleared with one memset per view
     const bool delivering = n_deliver > 0 && scored;
     const int stride = max_deliver_seg + 1;                         // one spare key per slot keeps t_start[n_seg] addressable
     const int n_keys = delivering ? n_deliver * stride : 0;
     const int ns = 2 * n_src;
     const size_t z_items = 0, z_iters = 4, z_rank = 8, z_hist = z_rank + size_t(2 * ns) + 2, z_cursor = z_hist + size_t(n_keys) + 2, z_end = z_cursor + size_t(n_keys) + 2;
-    L3D_CUDA(ctx->d_zero.ensure(z_end));
-    L3D_CUDA(cudaMemsetAsync(ctx->d_zero.p, 0, sizeof(int) * z_end, st));
-    int* d_nitems = ctx->d_zero.p + z_items;
-    unsigned long long* d_iters = reinterpret_cast<unsigned long long*>(ctx->d_zero.p + z_iters);
-    int* d_hist = ctx->d_zero.p + z_hist; int* d_cursor = ctx->d_zero.p + z_cursor;
-    unsigned long long* d_best = reinterpret_cast<unsigned long long*>(ctx->d_zero.p + z_rank);     // [n_src], 8-byte aligned (z_rank is even)
+    L3D_CUDA(sl.d_zero.ensure(z_end));
+    L3D_CUDA(cudaMemsetAsync(sl.d_zero.p, 0, sizeof(int) * z_end, st));
+    int* d_nitems = sl.d_zero.p + z_items;
+    unsigned long long* d_iters = reinterpret_cast<unsigned long long*>(sl.d_zero.p + z_iters);
+    int* d_hist = sl.d_zero.p + z_hist; int* d_cursor = sl.d_zero.p + z_cursor;
+    unsigned long long* d_best = reinterpret_cast<unsigned long long*>(sl.d_zero.p + z_rank);     // [n_src], 8-byte aligned (z_rank is even)
     if (scored && M_ub > 0) {
         // ---- score ------------------------------------------------------------------------
         ScoreParams sp; sp.sigma_p = sigma_p; sp.sigma_a = sigma_a;
-        L3D_CUDA(ctx->d_foff.ensure(4));
-        L3D_CUDA(ctx->d_dsamples.ensure(size_t(n_src) * 2));
+        L3D_CUDA(sl.d_foff.ensure(4));
+        L3D_CUDA(sl.d_dsamples.ensure(size_t(n_src) * 2));
         // Segments are grouped by depth and scored through windows; the tiled quadratic kernel takes everything when
         // the 3-D gate is switched off, and segments with more matches than the window kernel's 20-bit index can hold.
         const int SORT_MAX = 1 << 20;
         const bool windowed = src.spatial_k > 0.0f;
         const int max_items = int(M_ub / SC_T) + n_src + 1;
-        L3D_CUDA(ctx->d_items.ensure(size_t(2 * max_items)));
+        L3D_CUDA(sl.d_items.ensure(size_t(2 * max_items)));
         const size_t sm_bytes = size_t(n_nb) * SC_T * sizeof(int);
         if (sm_bytes > 160 * 1024) { ctx->err = "l3d_match_view: too many neighbours for the scoring kernel's shared memory"; return 1; }
         if (sm_bytes > ctx->score_smem) {
@@ -1752,37 +1773,37 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
             ctx->score_smem = sm_bytes;
         }
         if (windowed) {
-            L3D_CUDA(ctx->d_sk.ensure(M_ub)); L3D_CUDA(ctx->d_sd2.ensure(M_ub)); L3D_CUDA(ctx->d_spl.ensure(M_ub));
-            L3D_CUDA(ctx->d_boff.ensure(size_t(n_src) * (BK_B + 1))); L3D_CUDA(ctx->d_brange.ensure(size_t(n_src)));
-            L3D_CUDA(pdl_launch(k_bucket_segments, dim3(n_src), dim3(BK_T), 0, st, ctx->d_off.p, n_nb, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p,
-                                ctx->d_boff.p, ctx->d_brange.p, SORT_MAX, SC_T, d_nitems, ctx->d_items.p));
-            L3D_CUDA(pdl_launch(k_score_window, dim3(max_items), dim3(SC_T), sm_bytes, st, ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
-                                                             ctx->d_sk.p, ctx->d_sd2.p, ctx->d_spl.p, ctx->d_boff.p, ctx->d_brange.p, ctx->d_items.p, d_nitems, sp, ctx->d_score.p));
+            L3D_CUDA(sl.d_sk.ensure(M_ub)); L3D_CUDA(sl.d_sd2.ensure(M_ub)); L3D_CUDA(sl.d_spl.ensure(M_ub));
+            L3D_CUDA(sl.d_boff.ensure(size_t(n_src) * (BK_B + 1))); L3D_CUDA(sl.d_brange.ensure(size_t(n_src)));
+            L3D_CUDA(pdl_launch(k_bucket_segments, dim3(n_src), dim3(BK_T), 0, st, sl.d_off.p, n_nb, sl.d_mids.p, sl.d_mdep.p, sl.d_sk.p, sl.d_sd2.p, sl.d_spl.p,
+                                sl.d_boff.p, sl.d_brange.p, SORT_MAX, SC_T, d_nitems, sl.d_items.p));
+            L3D_CUDA(pdl_launch(k_score_window, dim3(max_items), dim3(SC_T), sm_bytes, st, ctx->d_segs.p, sl.d_cams.p, n_nb, src, sl.d_off.p, sl.d_mids.p, sl.d_mdep.p,
+                                                             sl.d_sk.p, sl.d_sd2.p, sl.d_spl.p, sl.d_boff.p, sl.d_brange.p, sl.d_items.p, d_nitems, sp, sl.d_score.p));
             ctx->launches += 2;
         }
         if (!windowed || seg_ub > size_t(SORT_MAX)) {
-            L3D_CUDA(pdl_launch(k_score_items, dim3((n_src + 255) / 256), dim3(256), 0, st, ctx->d_off.p, n_nb, n_src, windowed ? 0 : 0x7fffffff, windowed ? SORT_MAX : 0x7fffffff, 1,
-                                                              d_nitems + 1, ctx->d_items.p + max_items));
-            L3D_CUDA(pdl_launch(k_score, dim3(max_items), dim3(SC_T), sm_bytes, st, ctx->d_segs.p, ctx->d_cams.p, n_nb, src, ctx->d_off.p, ctx->d_mids.p, ctx->d_mdep.p,
-                                                      ctx->d_items.p + max_items, d_nitems + 1, sp, ctx->d_score.p));
+            L3D_CUDA(pdl_launch(k_score_items, dim3((n_src + 255) / 256), dim3(256), 0, st, sl.d_off.p, n_nb, n_src, windowed ? 0 : 0x7fffffff, windowed ? SORT_MAX : 0x7fffffff, 1,
+                                                              d_nitems + 1, sl.d_items.p + max_items));
+            L3D_CUDA(pdl_launch(k_score, dim3(max_items), dim3(SC_T), sm_bytes, st, ctx->d_segs.p, sl.d_cams.p, n_nb, src, sl.d_off.p, sl.d_mids.p, sl.d_mdep.p,
+                                                      sl.d_items.p + max_items, d_nitems + 1, sp, sl.d_score.p));
             ctx->launches += 2;
         }
         L3D_CUDA(cudaGetLastError());
         if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[4], st));
         // ---- reduce -----------------------------------------------------------------------
         const unsigned n_cta = unsigned((M_ub + RM_T - 1) / RM_T);
-        L3D_CUDA(ctx->d_fcnt.ensure(size_t(n_cta) + 1));                       // kept matches per CTA
-        L3D_CUDA(pdl_launch(k_reduce_matches, dim3(n_cta), dim3(RM_T), 0, st, d_M, ctx->d_off.p, n_nb, ctx->d_score.p, ctx->d_mids.p, d_best, ctx->d_fcnt.p, d_iters));
-        d_F = ctx->d_foff.p;
-        L3D_CUDA(pdl_launch(k_filter_compact, dim3(n_cta), dim3(RM_T), 0, st, d_M, ctx->d_score.p, ctx->d_mids.p, ctx->d_mdep.p, ctx->d_fcnt.p, dfil.p, ctx->d_foff.p,
-                            ctx->d_cams.p, stride, delivering ? d_hist : nullptr));
+        L3D_CUDA(sl.d_fcnt.ensure(size_t(n_cta) + 1));                       // kept matches per CTA
+        L3D_CUDA(pdl_launch(k_reduce_matches, dim3(n_cta), dim3(RM_T), 0, st, d_M, sl.d_off.p, n_nb, sl.d_score.p, sl.d_mids.p, d_best, sl.d_fcnt.p, d_iters));
+        d_F = sl.d_foff.p;
+        L3D_CUDA(pdl_launch(k_filter_compact, dim3(n_cta), dim3(RM_T), 0, st, d_M, sl.d_score.p, sl.d_mids.p, sl.d_mdep.p, sl.d_fcnt.p, dfil.p, sl.d_foff.p,
+                            sl.d_cams.p, stride, delivering ? d_hist : nullptr));
         ctx->launches += 2;
         L3D_CUDA(cudaGetLastError());
     } else {
         if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[4], st));
         d_F = d_M;
         if (!scored && M_ub > 0) {
-            L3D_CUDA(pdl_launch(k_copy_unscored, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, ctx->d_mids.p, ctx->d_mdep.p, d_M, dfil.p));
+            L3D_CUDA(pdl_launch(k_copy_unscored, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, sl.d_mids.p, sl.d_mdep.p, d_M, dfil.p));
             ctx->launches += 1;
             L3D_CUDA(cudaGetLastError());
         }
@@ -1796,23 +1817,23 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         L3D_CUDA(cudaMallocAsync(&buf.tgt, sizeof(int) * std::max<size_t>(M_ub, 1), st));
         L3D_CUDA(cudaMallocAsync(&buf.dep, sizeof(float4) * std::max<size_t>(M_ub, 1), st));
         // (the group sizes were counted by k_filter_fill)
-        if (scan_exclusive(ctx, d_hist, buf.start, n_keys)) return 1;
+        if (scan_exclusive(&sl, d_hist, buf.start, n_keys)) { ctx->err = sl.err; return 1; }
         if (M_ub > 0) {
             // records land in their group in the order of the atomics; the receiving view's k_fill orders them
-            L3D_CUDA(pdl_launch(k_deliver_scatter, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, dfil.p, d_F, ctx->d_cams.p, stride, buf.start, d_cursor, buf.tgt, buf.dep));
+            L3D_CUDA(pdl_launch(k_deliver_scatter, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, dfil.p, d_F, sl.d_cams.p, stride, buf.start, d_cursor, buf.tgt, buf.dep));
             ctx->launches += 1;
         }
         L3D_CUDA(cudaGetLastError());
     }
     // ---- results: one kernel packs them, one copy; the host collects them in finish_view ----------------
     const int n_res = 8 + std::max(n_deliver, 1);
-    L3D_CUDA(ctx->d_vres[par].ensure(size_t(n_res))); L3D_CUDA(ctx->h_vres[par].ensure(size_t(n_res)));
-    L3D_CUDA(pdl_launch(k_finish_view, dim3(1), dim3(MS_T), 0, st, ctx->d_dsamples.p, (scored && M_ub > 0) ? ns : 0, d_best, ctx->d_mdep.p, d_M, d_F, (scored && M_ub > 0) ? d_iters : nullptr,
-                        delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, ctx->d_vres[par].p));
+    L3D_CUDA(sl.d_vres.ensure(size_t(n_res))); L3D_CUDA(sl.h_vres.ensure(size_t(n_res)));
+    L3D_CUDA(pdl_launch(k_finish_view, dim3(1), dim3(MS_T), 0, st, sl.d_dsamples.p, (scored && M_ub > 0) ? ns : 0, d_best, sl.d_mdep.p, d_M, d_F, (scored && M_ub > 0) ? d_iters : nullptr,
+                        delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, sl.d_vres.p));
     ctx->launches += 1;
     L3D_CUDA(cudaGetLastError());
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[5], st));
-    L3D_CUDA(cudaMemcpyAsync(ctx->h_vres[par].p, ctx->d_vres[par].p, sizeof(int) * size_t(n_res), cudaMemcpyDeviceToHost, st));
+    L3D_CUDA(cudaMemcpyAsync(sl.h_vres.p, sl.d_vres.p, sizeof(int) * size_t(n_res), cudaMemcpyDeviceToHost, st));
     L3D_CUDA(cudaEventRecord(ev[0], st));
     job.M_ub = M_ub; job.scored = scored; job.delivering = delivering; job.n_deliver = n_deliver;
     // the hand-over records exist from now on (stream order); until this view is collected their sizes are bounds
@@ -1831,14 +1852,15 @@ int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float
         }
         ctx->deliver_bufs.push_back(buf);
     }
-    // the consumed deliveries are no longer needed (freed in stream order)
+    // the consumed deliveries leave the list; their memory is given back when this view has been collected
     {
         std::vector<Delivered>& dl = ctx->delivered[view];
-        for (size_t k = 0; k < consumed.size(); ++k) release_delivered(ctx, dl[consumed[k]]);
+        for (size_t k = 0; k < consumed.size(); ++k) dl[consumed[k]].from_view = -1;
         std::vector<Delivered> keep;
         for (size_t k = 0; k < dl.size(); ++k) if (dl[k].from_view >= 0) keep.push_back(dl[k]);
         dl.swap(keep);
     }
+    ctx->inflight_slot[view] = int(&sl - ctx->vs);
     job.active = true;
     return 0;
 }
@@ -1858,12 +1880,12 @@ int arena_take(l3d_ctx* ctx, size_t n, l3d_match** out)
     return 0;
 }
 
-int finish_view(l3d_ctx* ctx, ViewJob& job, l3d_match_result* res, bool copy_back)
+int finish_view(l3d_ctx* ctx, ViewSlot& sl, l3d_match_result* res, bool copy_back)
 {
-    const int par = job.parity;
+    ViewJob& job = sl.job;
     job.active = false;
-    L3D_CUDA(cudaEventSynchronize(ctx->vev[par][0]));
-    const int* hr = ctx->h_vres[par].p;
+    L3D_CUDA(cudaEventSynchronize(sl.ev[0]));
+    const int* hr = sl.h_vres.p;
     memset(res, 0, sizeof *res);
     res->pair_tests = job.pair_tests; res->n_candidates = job.cand_ub; res->scored = job.scored ? 1 : 0;
     const int M = hr[0], F = (job.M_ub > 0) ? hr[1] : 0;
@@ -1884,7 +1906,16 @@ int finish_view(l3d_ctx* ctx, ViewJob& job, l3d_match_result* res, bool copy_bac
                 if (dl[k].owner == job.owner) { dl[k].count = b.counts[dl[k].slot]; dl[k].max_group = b.maxg[dl[k].slot]; }
         }
     }
-    for (size_t k = 0; k < job.consumed.size(); ++k) res->n_delivered += uint64_t(ctx->deliver_bufs[job.consumed[k].first].counts[job.consumed[k].second]);
+    for (size_t k = 0; k < job.consumed.size(); ++k) {
+        DeliverBuf& b = ctx->deliver_bufs[job.consumed[k].first];
+        res->n_delivered += uint64_t(b.counts[job.consumed[k].second]);
+        if (--b.refs == 0) {                           // the last receiver has been collected: nothing on any stream reads it any more
+            cudaFreeAsync(b.start, ctx->stream); cudaFreeAsync(b.tgt, ctx->stream); cudaFreeAsync(b.dep, ctx->stream);
+            b.start = nullptr; b.tgt = nullptr; b.dep = nullptr;
+        }
+    }
+    ctx->inflight_slot[job.view] = -1;
+    ctx->launches += sl.launches; sl.launches = 0;
     res->n_scored = uint64_t(M);
     res->n_raw = uint64_t(M) - res->n_delivered;
     res->median_depth = median;
@@ -1893,7 +1924,7 @@ int finish_view(l3d_ctx* ctx, ViewJob& job, l3d_match_result* res, bool copy_bac
     if (copy_back && F > 0) {                          // on its own stream: the next view may already be running
         if (ctx->retain) { if (arena_take(ctx, size_t(F), &dst)) return 1; }
         else { L3D_CUDA(ctx->h_filtered.ensure(size_t(F))); dst = ctx->h_filtered.p; }
-        L3D_CUDA(cudaMemcpyAsync(dst, ctx->d_filtered2[par].p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, ctx->copy_stream));
+        L3D_CUDA(cudaMemcpyAsync(dst, sl.d_filtered.p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, ctx->copy_stream));
         L3D_CUDA(cudaStreamSynchronize(ctx->copy_stream));
     }
     res->filtered = dst;
@@ -1906,18 +1937,19 @@ int finish_view(l3d_ctx* ctx, ViewJob& job, l3d_match_result* res, bool copy_bac
         for (int k = 0; k < 2; ++k) { ms = 0.f; if (pa.pa_kev_set[k]) cudaEventElapsedTime(&ms, pa.pa_kev[2 * k], pa.pa_kev[2 * k + 1]); ctx->pa_kernel_ms[k] = ms; }
         pa.pa_ms_pending = false;
     }
-    for (int k = 2; k < 5; ++k) { ms = 0.f; if (ctx->stage_events) cudaEventElapsedTime(&ms, ctx->vev[par][k], ctx->vev[par][k + 1]); ctx->last_ms[k] = ms; }
+    for (int k = 2; k < 5; ++k) { ms = 0.f; if (ctx->stage_events) cudaEventElapsedTime(&ms, sl.ev[k], sl.ev[k + 1]); ctx->last_ms[k] = ms; }
     ctx->last_ms[5] = ctx->last_ms[0] + ctx->last_ms[1] + ctx->last_ms[2] + ctx->last_ms[3] + ctx->last_ms[4];
     return 0;
 }
 
 int join_worker(l3d_ctx* ctx);
 
-// Collects a view that was put on the stream ahead of its call and is not going to be asked for (and the helper thread).
+// Collects the views that were put on the GPU ahead of their calls and are not going to be asked for (and the helper thread).
 void drain_pending(l3d_ctx* ctx)
 {
     join_worker(ctx);
-    if (ctx->pending >= 0) { l3d_match_result dummy; finish_view(ctx, ctx->vjob[ctx->pending], &dummy, false); ctx->pending = -1; }
+    while (ctx->fly_begin < ctx->fly_end) { l3d_match_result dummy; finish_view(ctx, ctx->vs[ctx->fly_begin % VS_W], &dummy, false); ++ctx->fly_begin; }
+    ctx->fly_begin = ctx->fly_end = 0;
 }
 
 // The batch of the announced schedule that starts at plan entry `from`: its job list, and where it ends.
@@ -1962,61 +1994,62 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     if (view < 0 || view >= ctx->V) { ctx->err = "l3d_match_view: view index out of range"; return 1; }
     L3D_CUDA(cudaSetDevice(ctx->device));
     memset(res, 0, sizeof *res);
-    int ci;
-    if (ctx->pending >= 0) {
-        // this view is already running: the call must be the one the schedule announced
-        ViewJob& p = ctx->vjob[ctx->pending];
-        if (p.view != view || !same_neighbors(p.nb, n_nb, nb) || p.sigma_p != sigma_p || p.sigma_a != sigma_a) {
+    const size_t depth = ctx->stage_events ? 1 : size_t(VS_W);      // per-stage timing wants one view at a time
+    if (ctx->fly_begin < ctx->fly_end) {
+        // this view is already on the GPU: the call must be the one the schedule announced
+        const PlannedView& pv = ctx->plan[ctx->fly_begin];
+        if (pv.view != view || !same_neighbors(pv.nb, n_nb, nb) || ctx->run_sigma_p != sigma_p || ctx->run_sigma_a != sigma_a) {
             ctx->err = "l3d_match_view: the call does not follow the schedule announced with l3d_plan_matching (same views, neighbours and sigmas, in order); call l3d_reset_matching to start over";
             return 1;
         }
-        ci = ctx->pending; ctx->pending = -1;
-    } else {
-        // ---- phase A: from the announced schedule (batched), or for this view alone -----------
-        int first_job = 0;
-        if (ctx->plan_next < ctx->plan.size() && ctx->plan[ctx->plan_next].view == view && same_neighbors(ctx->plan[ctx->plan_next].nb, n_nb, nb)) {
-            if (ctx->plan_next >= ctx->batch_end) {                 // the next batch starts here
-                if (ctx->pa_worker_active) {                         // its pair tests were started while the previous batch was scored
-                    PhaseASet& nx = ctx->pa[ctx->cur ^ 1];
-                    if (join_worker(ctx)) { ctx->err = nx.err; return 1; }
-                    if (nx.begin != ctx->plan_next) { ctx->err = "l3d_match_view: internal error (batch out of step)"; return 1; }
-                    ctx->cur ^= 1;
-                } else {
-                    std::vector<JobHost> jh;
-                    PhaseASet& set = ctx->pa[ctx->cur];
-                    set.begin = ctx->plan_next; set.end = plan_batch(ctx, ctx->plan_next, jh);
-                    if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
-                }
+    } else if (ctx->plan_next < ctx->plan.size() && ctx->plan[ctx->plan_next].view == view && same_neighbors(ctx->plan[ctx->plan_next].nb, n_nb, nb)) {
+        // ---- the next view of the announced schedule ------------------------------------------
+        if (ctx->plan_next >= ctx->batch_end) {                 // the next batch starts here (nothing is in flight)
+            if (ctx->pa_worker_active) {                         // its pair tests were started while the previous batch was scored
+                PhaseASet& nx = ctx->pa[ctx->cur ^ 1];
+                if (join_worker(ctx)) { ctx->err = nx.err; return 1; }
+                if (nx.begin != ctx->plan_next) { ctx->err = "l3d_match_view: internal error (batch out of step)"; return 1; }
+                ctx->cur ^= 1;
+            } else {
+                std::vector<JobHost> jh;
                 PhaseASet& set = ctx->pa[ctx->cur];
-                ctx->batch_begin = set.begin; ctx->batch_end = set.end;
-                ctx->launches += set.launches; set.launches = 0;
-                if (ctx->batch_end < ctx->plan.size()) start_worker(ctx, ctx->batch_end);     // the following batch, meanwhile
+                set.begin = ctx->plan_next; set.end = plan_batch(ctx, ctx->plan_next, jh);
+                if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
             }
-            first_job = ctx->plan[ctx->plan_next].first_job;
-            ++ctx->plan_next;
-        } else {
-            join_worker(ctx);
-            ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;      // a call off the schedule voids it
-            std::vector<JobHost> jh;
-            for (int c = 0; c < n_nb; ++c)
-                if (nb[c].to_be_matched) { JobHost j; j.src_view = view; j.tgt_view = nb[c].view; memcpy(j.F, nb[c].F, sizeof j.F); jh.push_back(j); }
             PhaseASet& set = ctx->pa[ctx->cur];
-            if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
+            ctx->batch_begin = set.begin; ctx->batch_end = set.end;
             ctx->launches += set.launches; set.launches = 0;
+            if (ctx->batch_end < ctx->plan.size()) start_worker(ctx, ctx->batch_end);     // the following batch, meanwhile
         }
-        ci = ctx->vnext; ctx->vnext ^= 1;
-        ctx->vjob[ci].parity = ci;
-        if (enqueue_view(ctx, view, n_nb, nb, sigma_p, sigma_a, first_job, ctx->vjob[ci])) return 1;
+        ctx->fly_begin = ctx->fly_end = ctx->plan_next;
+        ctx->run_sigma_p = sigma_p; ctx->run_sigma_a = sigma_a;
+    } else {
+        // ---- a call off the schedule voids it: this view alone --------------------------------
+        join_worker(ctx);
+        ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0; ctx->fly_begin = ctx->fly_end = 0;
+        std::vector<JobHost> jh;
+        for (int c = 0; c < n_nb; ++c)
+            if (nb[c].to_be_matched) { JobHost j; j.src_view = view; j.tgt_view = nb[c].view; memcpy(j.F, nb[c].F, sizeof j.F); jh.push_back(j); }
+        PhaseASet& set = ctx->pa[ctx->cur];
+        if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
+        ctx->launches += set.launches; set.launches = 0;
+        ViewSlot& sl = ctx->vs[0];
+        sl.stream = ctx->vstream[0];
+        if (enqueue_view(ctx, view, n_nb, nb, sigma_p, sigma_a, 0, sl)) return 1;
+        return finish_view(ctx, sl, res, copy_back);
     }
-    // put the schedule's next view on the stream before waiting for this one (its pair tests must be resident)
-    if (ctx->plan_next < ctx->batch_end) {
-        PlannedView& pv = ctx->plan[ctx->plan_next];
-        const int ni = ci ^ 1;
-        ctx->vjob[ni].parity = ni;
-        if (enqueue_view(ctx, pv.view, int(pv.nb.size()), pv.nb.data(), sigma_p, sigma_a, pv.first_job, ctx->vjob[ni])) { finish_view(ctx, ctx->vjob[ci], res, false); return 1; }
-        ++ctx->plan_next; ctx->pending = ni; ctx->vnext = ci;
+    // put the schedule's next views on the GPU before waiting for this one (their pair tests must be resident)
+    while (ctx->fly_end < ctx->batch_end && ctx->fly_end - ctx->fly_begin < depth) {
+        PlannedView& pv = ctx->plan[ctx->fly_end];
+        ViewSlot& sl = ctx->vs[ctx->fly_end % VS_W];
+        sl.stream = ctx->vstream[ctx->fly_end % VS_S];
+        if (enqueue_view(ctx, pv.view, int(pv.nb.size()), pv.nb.data(), ctx->run_sigma_p, ctx->run_sigma_a, pv.first_job, sl)) { drain_pending(ctx); return 1; }
+        ++ctx->fly_end;
+        ctx->plan_next = ctx->fly_end;
     }
-    return finish_view(ctx, ctx->vjob[ci], res, copy_back);
+    const int rc = finish_view(ctx, ctx->vs[ctx->fly_begin % VS_W], res, copy_back);
+    ++ctx->fly_begin;
+    return rc;
 }
 
 }  // namespace
@@ -2046,7 +2079,10 @@ int l3d_create(int device, l3d_ctx** out)
         if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
     }
     for (int k = 0; k < 8; ++k) cudaEventCreate(&ctx->ev[k]);
-    for (int q = 0; q < 2; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->vev[q][k]);
+    for (int q = 0; q < VS_S; ++q)
+        if ((e = cudaStreamCreateWithPriority(&ctx->vstream[q], cudaStreamNonBlocking, prio_hi)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); l3d_destroy(ctx); return 1; }
+    for (int q = 0; q < VS_W; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->vs[q].ev[k]);
+    cudaEventCreateWithFlags(&ctx->join_ev, cudaEventDisableTiming);
     if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); cudaStreamDestroy(ctx->stream); delete ctx; return 1; }
     for (int q = 0; q < 2; ++q) {
         PhaseASet& set = ctx->pa[q];
@@ -2064,11 +2100,13 @@ int l3d_reset_matching(l3d_ctx* ctx)
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
     drain_pending(ctx);
-    for (size_t v = 0; v < ctx->delivered.size(); ++v) {
-        for (size_t k = 0; k < ctx->delivered[v].size(); ++k) release_delivered(ctx, ctx->delivered[v][k]);
-        ctx->delivered[v].clear();
+    for (size_t v = 0; v < ctx->delivered.size(); ++v) ctx->delivered[v].clear();
+    for (size_t k = 0; k < ctx->deliver_bufs.size(); ++k) {          // handed over and never taken, or not yet given back
+        DeliverBuf& b = ctx->deliver_bufs[k];
+        if (b.start) { cudaFreeAsync(b.start, ctx->stream); cudaFreeAsync(b.tgt, ctx->stream); cudaFreeAsync(b.dep, ctx->stream); }
     }
     ctx->deliver_bufs.clear();
+    ctx->inflight_slot.assign(size_t(std::max(ctx->V, 0)), -1);
     ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;
     ctx->arena_chunk = 0; ctx->arena_used = 0;           // retained results are given up, their memory is reused
     cudaStreamSynchronize(ctx->stream);
@@ -2080,14 +2118,13 @@ void l3d_destroy(l3d_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     l3d_reset_matching(ctx);
-    ctx->d_segs.release(); ctx->d_viewd.release(); ctx->d_cams.release(); ctx->d_slot_cam.release(); ctx->pa[0].release(); ctx->pa[1].release();
+    ctx->d_segs.release(); ctx->d_viewd.release(); ctx->pa[0].release(); ctx->pa[1].release();
     ctx->d_tile_sums.release(); ctx->d_total.release();
-    ctx->d_cnt.release(); ctx->d_off.release(); ctx->d_mids.release(); ctx->d_mdep.release();
-    ctx->d_score.release(); ctx->d_fcnt.release(); ctx->d_foff.release(); ctx->d_dsamples.release(); ctx->d_median.release(); ctx->d_iters.release();
-    for (int q = 0; q < 2; ++q) { ctx->d_filtered2[q].release(); ctx->d_vres[q].release(); ctx->h_vres[q].release(); ctx->h_cams2[q].release(); for (int k = 0; k < 6; ++k) if (ctx->vev[q][k]) cudaEventDestroy(ctx->vev[q][k]); }
+    for (int q = 0; q < VS_W; ++q) ctx->vs[q].release();
+    for (int q = 0; q < VS_S; ++q) if (ctx->vstream[q]) cudaStreamDestroy(ctx->vstream[q]);
+    if (ctx->join_ev) cudaEventDestroy(ctx->join_ev);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (size_t k = 0; k < ctx->arena.size(); ++k) cudaFreeHost(ctx->arena[k].first);
-    ctx->d_items.release(); ctx->d_nitems.release(); ctx->d_medrank.release(); ctx->d_sk.release(); ctx->d_sd2.release(); ctx->d_spl.release(); ctx->d_boff.release(); ctx->d_brange.release();
     ctx->d_res.release(); ctx->d_zero.release();
     for (int k = 0; k < 2; ++k) if (ctx->mark_ev[k]) cudaEventDestroy(ctx->mark_ev[k]);
     ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
@@ -2185,6 +2222,7 @@ int l3d_set_views(l3d_ctx* ctx, int n_views, const l3d_view* views)
     L3D_CUDA(cudaSetDevice(ctx->device));
     l3d_reset_matching(ctx);
     ctx->V = n_views;
+    ctx->inflight_slot.assign(size_t(n_views), -1);
     ctx->views.assign(views, views + n_views);
     ctx->seg_off.assign(size_t(n_views) + 1, 0);
     ctx->max_seg = 0;
@@ -2391,7 +2429,11 @@ int l3d_mark(l3d_ctx* ctx, int which)
 {
     if (!ctx || which < 0 || which > 1) return 1;
     L3D_CUDA(cudaSetDevice(ctx->device));
+    for (int q = 0; q < VS_S; ++q) {                 // the mark comes after (before) everything on the view streams too
+        if (which == 1) { L3D_CUDA(cudaEventRecord(ctx->join_ev, ctx->vstream[q])); L3D_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->join_ev, 0)); }
+    }
     L3D_CUDA(cudaEventRecord(ctx->mark_ev[which], ctx->stream));
+    if (which == 0) for (int q = 0; q < VS_S; ++q) L3D_CUDA(cudaStreamWaitEvent(ctx->vstream[q], ctx->mark_ev[0], 0));
     return 0;
 }
 
