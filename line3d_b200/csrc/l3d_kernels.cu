@@ -1460,13 +1460,18 @@ struct l3d_ctx {
     // phase A (pair tests): the batch the per-view work reads (pa[cur]) and the one a helper thread prepares meanwhile
     PhaseASet pa[2]; int cur = 0;
     std::thread pa_worker; bool pa_worker_active = false; int pa_worker_rc = 0;
-    std::vector<PlannedView> plan; size_t plan_next = 0; size_t batch_begin = 0, batch_end = 0;
+    std::vector<PlannedView> plan;                  // as announced (the order of the caller's calls)
+    std::vector<size_t> order;                      // plan entries in the order they are executed: by dependency level
+    struct Stashed { l3d_match_result res; bool ready; float ms[6], kms[2]; };
+    std::vector<Stashed> results;                   // per plan entry, until the caller asks for it
+    size_t call_next = 0; bool plan_started = false, run_copy_back = true;
+    size_t batch_begin = 0, batch_end = 0;          // positions in `order` whose pair tests are resident
     uint64_t pair_budget = 24000000000ull;          // most pair tests of one batch (3 GB of candidate bits)
     uint64_t batch_pairs = 24000000000ull;          // pair tests per batch of the announced schedule (l3d_plan_matching)
     uint64_t batch_override = 0;                    // l3d_debug_set_batch_pairs
     float pa_kernel_ms[2] = {0.f, 0.f};
     DBuf<int> d_res, d_zero;
-    // views in flight: plan entries [fly_begin, fly_end) are on the GPU, entry i in slot i % VS_W on stream i % VS_S
+    // views in flight: positions [fly_begin, fly_end) of `order` are on the GPU, position i in slot i % VS_W on stream i % VS_S
     ViewSlot vs[VS_W]; cudaStream_t vstream[VS_S] = {nullptr, nullptr, nullptr, nullptr};
     size_t fly_begin = 0, fly_end = 0; std::vector<int> inflight_slot;   // per view: its slot while in flight, else -1
     float run_sigma_p = 0.f, run_sigma_a = 0.f;
@@ -1922,7 +1927,7 @@ int finish_view(l3d_ctx* ctx, ViewSlot& sl, l3d_match_result* res, bool copy_bac
     res->n_filtered = uint64_t(F);
     l3d_match* dst = nullptr;
     if (copy_back && F > 0) {                          // on its own stream: the next view may already be running
-        if (ctx->retain) { if (arena_take(ctx, size_t(F), &dst)) return 1; }
+        if (ctx->retain || ctx->plan_started) { if (arena_take(ctx, size_t(F), &dst)) return 1; }     // results of a schedule are collected ahead of their calls
         else { L3D_CUDA(ctx->h_filtered.ensure(size_t(F))); dst = ctx->h_filtered.p; }
         L3D_CUDA(cudaMemcpyAsync(dst, sl.d_filtered.p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, ctx->copy_stream));
         L3D_CUDA(cudaStreamSynchronize(ctx->copy_stream));
@@ -1952,12 +1957,13 @@ void drain_pending(l3d_ctx* ctx)
     ctx->fly_begin = ctx->fly_end = 0;
 }
 
-// The batch of the announced schedule that starts at plan entry `from`: its job list, and where it ends.
+// The batch of the announced schedule that starts at position `from` of the execution order: its job list, and
+// where it ends.
 size_t plan_batch(l3d_ctx* ctx, size_t from, std::vector<JobHost>& jh)
 {
     size_t e = from; uint64_t pairs = 0;
-    while (e < ctx->plan.size() && (e == from || pairs + ctx->plan[e].pair_tests <= ctx->batch_pairs)) {
-        PlannedView& pv = ctx->plan[e];
+    while (e < ctx->order.size() && (e == from || pairs + ctx->plan[ctx->order[e]].pair_tests <= ctx->batch_pairs)) {
+        PlannedView& pv = ctx->plan[ctx->order[e]];
         pv.first_job = int(jh.size());
         for (size_t c = 0; c < pv.nb.size(); ++c)
             if (pv.nb[c].to_be_matched) { JobHost j; j.src_view = pv.view; j.tgt_view = pv.nb[c].view; memcpy(j.F, pv.nb[c].F, sizeof j.F); jh.push_back(j); }
@@ -1987,6 +1993,39 @@ int join_worker(l3d_ctx* ctx)
     return ctx->pa_worker_rc;
 }
 
+// More views of the schedule onto the GPU, in execution order, as far as slots and resident pair tests allow; starts
+// the next batch when the current one has been collected completely.
+int top_up(l3d_ctx* ctx)
+{
+    if (ctx->fly_end >= ctx->batch_end) {
+        if (ctx->fly_begin < ctx->fly_end || ctx->fly_end >= ctx->order.size()) return 0;
+        if (ctx->pa_worker_active) {                             // its pair tests were started while the previous batch was scored
+            PhaseASet& nx = ctx->pa[ctx->cur ^ 1];
+            if (join_worker(ctx)) { ctx->err = nx.err; return 1; }
+            if (nx.begin != ctx->fly_end) { ctx->err = "l3d_match_view: internal error (batch out of step)"; return 1; }
+            ctx->cur ^= 1;
+        } else {
+            std::vector<JobHost> jh;
+            PhaseASet& set = ctx->pa[ctx->cur];
+            set.begin = ctx->fly_end; set.end = plan_batch(ctx, ctx->fly_end, jh);
+            if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
+        }
+        PhaseASet& set = ctx->pa[ctx->cur];
+        ctx->batch_begin = set.begin; ctx->batch_end = set.end;
+        ctx->launches += set.launches; set.launches = 0;
+        if (ctx->batch_end < ctx->order.size()) start_worker(ctx, ctx->batch_end);      // the following batch, meanwhile
+    }
+    const size_t depth = ctx->stage_events ? 1 : size_t(VS_W);      // per-stage timing wants one view at a time
+    while (ctx->fly_end < ctx->batch_end && ctx->fly_end - ctx->fly_begin < depth) {
+        PlannedView& pv = ctx->plan[ctx->order[ctx->fly_end]];
+        ViewSlot& sl = ctx->vs[ctx->fly_end % VS_W];
+        sl.stream = ctx->vstream[ctx->fly_end % VS_S];
+        if (enqueue_view(ctx, pv.view, int(pv.nb.size()), pv.nb.data(), ctx->run_sigma_p, ctx->run_sigma_a, pv.first_job, sl)) return 1;
+        ++ctx->fly_end;
+    }
+    return 0;
+}
+
 int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float sigma_p, float sigma_a, l3d_match_result* res, bool copy_back)
 {
     if (!ctx) return 1;
@@ -1994,62 +2033,45 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     if (view < 0 || view >= ctx->V) { ctx->err = "l3d_match_view: view index out of range"; return 1; }
     L3D_CUDA(cudaSetDevice(ctx->device));
     memset(res, 0, sizeof *res);
-    const size_t depth = ctx->stage_events ? 1 : size_t(VS_W);      // per-stage timing wants one view at a time
-    if (ctx->fly_begin < ctx->fly_end) {
-        // this view is already on the GPU: the call must be the one the schedule announced
-        const PlannedView& pv = ctx->plan[ctx->fly_begin];
-        if (pv.view != view || !same_neighbors(pv.nb, n_nb, nb) || ctx->run_sigma_p != sigma_p || ctx->run_sigma_a != sigma_a) {
-            ctx->err = "l3d_match_view: the call does not follow the schedule announced with l3d_plan_matching (same views, neighbours and sigmas, in order); call l3d_reset_matching to start over";
-            return 1;
-        }
-    } else if (ctx->plan_next < ctx->plan.size() && ctx->plan[ctx->plan_next].view == view && same_neighbors(ctx->plan[ctx->plan_next].nb, n_nb, nb)) {
-        // ---- the next view of the announced schedule ------------------------------------------
-        if (ctx->plan_next >= ctx->batch_end) {                 // the next batch starts here (nothing is in flight)
-            if (ctx->pa_worker_active) {                         // its pair tests were started while the previous batch was scored
-                PhaseASet& nx = ctx->pa[ctx->cur ^ 1];
-                if (join_worker(ctx)) { ctx->err = nx.err; return 1; }
-                if (nx.begin != ctx->plan_next) { ctx->err = "l3d_match_view: internal error (batch out of step)"; return 1; }
-                ctx->cur ^= 1;
-            } else {
-                std::vector<JobHost> jh;
-                PhaseASet& set = ctx->pa[ctx->cur];
-                set.begin = ctx->plan_next; set.end = plan_batch(ctx, ctx->plan_next, jh);
-                if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
-            }
-            PhaseASet& set = ctx->pa[ctx->cur];
-            ctx->batch_begin = set.begin; ctx->batch_end = set.end;
-            ctx->launches += set.launches; set.launches = 0;
-            if (ctx->batch_end < ctx->plan.size()) start_worker(ctx, ctx->batch_end);     // the following batch, meanwhile
-        }
-        ctx->fly_begin = ctx->fly_end = ctx->plan_next;
-        ctx->run_sigma_p = sigma_p; ctx->run_sigma_a = sigma_a;
-    } else {
-        // ---- a call off the schedule voids it: this view alone --------------------------------
-        join_worker(ctx);
-        ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0; ctx->fly_begin = ctx->fly_end = 0;
-        std::vector<JobHost> jh;
-        for (int c = 0; c < n_nb; ++c)
-            if (nb[c].to_be_matched) { JobHost j; j.src_view = view; j.tgt_view = nb[c].view; memcpy(j.F, nb[c].F, sizeof j.F); jh.push_back(j); }
-        PhaseASet& set = ctx->pa[ctx->cur];
-        if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
-        ctx->launches += set.launches; set.launches = 0;
-        ViewSlot& sl = ctx->vs[0];
-        sl.stream = ctx->vstream[0];
-        if (enqueue_view(ctx, view, n_nb, nb, sigma_p, sigma_a, 0, sl)) return 1;
-        return finish_view(ctx, sl, res, copy_back);
+    const bool on_plan = ctx->call_next < ctx->plan.size() && ctx->plan[ctx->call_next].view == view && same_neighbors(ctx->plan[ctx->call_next].nb, n_nb, nb);
+    if (ctx->plan_started && !(on_plan && ctx->run_sigma_p == sigma_p && ctx->run_sigma_a == sigma_a && ctx->run_copy_back == copy_back)) {
+        ctx->err = "l3d_match_view: the call does not follow the schedule announced with l3d_plan_matching (same views, neighbours, sigmas and entry point, in order); call l3d_reset_matching to start over";
+        return 1;
     }
-    // put the schedule's next views on the GPU before waiting for this one (their pair tests must be resident)
-    while (ctx->fly_end < ctx->batch_end && ctx->fly_end - ctx->fly_begin < depth) {
-        PlannedView& pv = ctx->plan[ctx->fly_end];
-        ViewSlot& sl = ctx->vs[ctx->fly_end % VS_W];
-        sl.stream = ctx->vstream[ctx->fly_end % VS_S];
-        if (enqueue_view(ctx, pv.view, int(pv.nb.size()), pv.nb.data(), ctx->run_sigma_p, ctx->run_sigma_a, pv.first_job, sl)) { drain_pending(ctx); return 1; }
-        ++ctx->fly_end;
-        ctx->plan_next = ctx->fly_end;
+    if (on_plan) {
+        // ---- the next view of the announced schedule: the library works through the schedule in its own order
+        // (by dependency level) and ahead of the caller; wait until this view's result has been collected
+        if (!ctx->plan_started) { ctx->plan_started = true; ctx->run_sigma_p = sigma_p; ctx->run_sigma_a = sigma_a; ctx->run_copy_back = copy_back; }
+        const size_t p = ctx->call_next;
+        while (!ctx->results[p].ready) {
+            if (top_up(ctx)) { drain_pending(ctx); return 1; }
+            if (ctx->fly_begin >= ctx->fly_end) { ctx->err = "l3d_match_view: internal error (schedule exhausted)"; return 1; }
+            const size_t q = ctx->order[ctx->fly_begin];
+            const int rc = finish_view(ctx, ctx->vs[ctx->fly_begin % VS_W], &ctx->results[q].res, ctx->run_copy_back);
+            ++ctx->fly_begin;
+            if (rc) { drain_pending(ctx); return 1; }
+            ctx->results[q].ready = true;
+            memcpy(ctx->results[q].ms, ctx->last_ms, sizeof ctx->last_ms); memcpy(ctx->results[q].kms, ctx->pa_kernel_ms, sizeof ctx->pa_kernel_ms);
+        }
+        *res = ctx->results[p].res;
+        memcpy(ctx->last_ms, ctx->results[p].ms, sizeof ctx->last_ms); memcpy(ctx->pa_kernel_ms, ctx->results[p].kms, sizeof ctx->pa_kernel_ms);
+        ++ctx->call_next;
+        if (top_up(ctx)) { drain_pending(ctx); return 1; }       // keep the GPU busy while the caller works
+        return 0;
     }
-    const int rc = finish_view(ctx, ctx->vs[ctx->fly_begin % VS_W], res, copy_back);
-    ++ctx->fly_begin;
-    return rc;
+    // ---- a call off the schedule (before it started) voids it: this view alone -------------------
+    drain_pending(ctx);
+    ctx->plan.clear(); ctx->order.clear(); ctx->results.clear(); ctx->call_next = 0; ctx->batch_begin = ctx->batch_end = 0; ctx->fly_begin = ctx->fly_end = 0;
+    std::vector<JobHost> jh;
+    for (int c = 0; c < n_nb; ++c)
+        if (nb[c].to_be_matched) { JobHost j; j.src_view = view; j.tgt_view = nb[c].view; memcpy(j.F, nb[c].F, sizeof j.F); jh.push_back(j); }
+    PhaseASet& set = ctx->pa[ctx->cur];
+    if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
+    ctx->launches += set.launches; set.launches = 0;
+    ViewSlot& sl = ctx->vs[0];
+    sl.stream = ctx->vstream[0];
+    if (enqueue_view(ctx, view, n_nb, nb, sigma_p, sigma_a, 0, sl)) return 1;
+    return finish_view(ctx, sl, res, copy_back);
 }
 
 }  // namespace
@@ -2107,7 +2129,7 @@ int l3d_reset_matching(l3d_ctx* ctx)
     }
     ctx->deliver_bufs.clear();
     ctx->inflight_slot.assign(size_t(std::max(ctx->V, 0)), -1);
-    ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;
+    ctx->plan.clear(); ctx->order.clear(); ctx->results.clear(); ctx->call_next = 0; ctx->plan_started = false; ctx->batch_begin = ctx->batch_end = 0; ctx->fly_begin = ctx->fly_end = 0;
     ctx->arena_chunk = 0; ctx->arena_used = 0;           // retained results are given up, their memory is reused
     cudaStreamSynchronize(ctx->stream);
     return 0;
@@ -2255,7 +2277,7 @@ int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
     if (!ctx) return 1;
     cudaSetDevice(ctx->device);
     drain_pending(ctx);
-    ctx->plan.clear(); ctx->plan_next = 0; ctx->batch_begin = ctx->batch_end = 0;
+    ctx->plan.clear(); ctx->order.clear(); ctx->results.clear(); ctx->call_next = 0; ctx->plan_started = false; ctx->batch_begin = ctx->batch_end = 0; ctx->fly_begin = ctx->fly_end = 0;
     if (n_views <= 0) return 0;
     if (!plans) { ctx->err = "l3d_plan_matching: null argument"; return 1; }
     for (int k = 0; k < n_views; ++k) {
@@ -2267,6 +2289,26 @@ int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
             if (p.neighbors[c].to_be_matched) pv.pair_tests += uint64_t(ctx->views[p.view].n_segments) * uint64_t(ctx->views[p.neighbors[c].view].n_segments);
         }
         ctx->plan.push_back(pv);
+    }
+    // Execution order.  View b needs view a first only if a hands records over to b (a comes earlier and marks b
+    // "deliver"), so the schedule is a dependency graph, usually of a few independent chains (views along a street;
+    // C2: 200 views, longest chain 50).  The library works through it level by level -- the views of one level do not
+    // depend on each other and run side by side -- and hands the results out in the order of the calls.
+    {
+        const size_t n = ctx->plan.size();
+        std::vector<int> at(size_t(ctx->V), -1), level(n, 1);
+        for (size_t k = 0; k < n; ++k) at[ctx->plan[k].view] = int(k);
+        for (size_t k = 0; k < n; ++k)
+            for (size_t c = 0; c < ctx->plan[k].nb.size(); ++c) {
+                const l3d_neighbor& nbr = ctx->plan[k].nb[c];
+                const int to = at[nbr.view];
+                if (nbr.deliver && to > int(k)) level[to] = std::max(level[to], level[k] + 1);
+            }
+        ctx->order.resize(n);
+        for (size_t k = 0; k < n; ++k) ctx->order[k] = k;
+        std::stable_sort(ctx->order.begin(), ctx->order.end(), [&level](size_t a, size_t b) { return level[a] < level[b]; });
+        l3d_ctx::Stashed empty; memset(&empty, 0, sizeof empty);
+        ctx->results.assign(n, empty);
     }
     // Batches: the pair tests of batch i + 1 run beside the per-view work of batch i, so the schedule is cut into
     // about eight of them (not smaller than 2.5e8 pair tests: a batch has fixed costs), none above the memory budget.
