@@ -173,9 +173,8 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_sums(int* __restrict__ tile_sum
 // warp totals gives each warp its base, pass 2 re-reads the chunk (L1/L2) and scans it 32 elements at a time with
 // a running carry.  One block-wide barrier in total; the tiled version this replaces had three per 4096 elements.
 constexpr int SCAN_SMALL = 64 * 1024;
-__global__ void __launch_bounds__(SCAN_T) k_scan_small(const int* __restrict__ in, int* __restrict__ out /* n + 1 */, int n)
+__device__ __forceinline__ void block_scan_global(const int* __restrict__ in, int* __restrict__ out /* n + 1 */, int n)      // blocks of SCAN_T threads
 {
-    L3D_PDL_PROLOGUE();
     __shared__ int s_tot[32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int chunk = (((n + 31) >> 5) + 31) & ~31;              // elements per warp, a multiple of 32
@@ -202,6 +201,11 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_small(const int* __restrict__ i
         if (i < end) out[i] = carry + x - v;
         carry += __shfl_sync(0xffffffffu, x, 31);
     }
+}
+__global__ void __launch_bounds__(SCAN_T) k_scan_small(const int* __restrict__ in, int* __restrict__ out /* n + 1 */, int n)
+{
+    L3D_PDL_PROLOGUE();
+    block_scan_global(in, out, n);
 }
 __global__ void __launch_bounds__(SCAN_T) k_scan_add(int* __restrict__ out, const int* __restrict__ tile_sums, int n, const int* __restrict__ total)
 {
@@ -568,9 +572,8 @@ __global__ void k_gather_int(const int* __restrict__ src, const int* __restrict_
 }
 
 // counts of the delivered records per (row, cam) for the cams in mode 1
-__global__ void k_gather_counts(const CamTable* __restrict__ cams, int n_cams, int n_src, const int* __restrict__ raw_cnt, int* __restrict__ cnt)
+__device__ __forceinline__ void b_gather_counts(const CamTable* __restrict__ cams, int n_cams, int n_src, const int* __restrict__ raw_cnt, int* __restrict__ cnt)
 {
-    L3D_PDL_PROLOGUE();
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     const int cam = blockIdx.y;
     if (row >= n_src) return;
@@ -582,12 +585,11 @@ __global__ void k_gather_counts(const CamTable* __restrict__ cams, int n_cams, i
 }
 
 // fill: one warp per (row, cam) copies the row's records to their final place
-__global__ void k_fill(const CamTable* __restrict__ cams, int n_cams, int n_src,
+__device__ __forceinline__ void b_fill(const CamTable* __restrict__ cams, int n_cams, int n_src,
                        const int* __restrict__ off, const int* __restrict__ cand_off,
                        const int* __restrict__ stage_col, const float4* __restrict__ stage_dep, const unsigned char* __restrict__ stage_ok,
                        int4* __restrict__ m_ids, float4* __restrict__ m_dep)
 {
-    L3D_PDL_PROLOGUE();
     const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (gw >= n_src * n_cams) return;
     const int row = gw / n_cams, cam = gw - row * n_cams;
@@ -634,9 +636,8 @@ constexpr int SC_QCAP = 128;       // per-warp queue of gate survivors
 struct ScoreParams { float sigma_p, sigma_a; };
 
 // work items: (source segment, chunk of SC_T matches); order is irrelevant to the result
-__global__ void k_score_items(const int* __restrict__ off, int n_cams, int n_src, int m_lo, int m_hi, int outside, int* __restrict__ counter, int2* __restrict__ items)
+__device__ __forceinline__ void b_score_items(const int* __restrict__ off, int n_cams, int n_src, int m_lo, int m_hi, int outside, int* __restrict__ counter, int2* __restrict__ items)
 {
-    L3D_PDL_PROLOGUE();
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n_src) return;
     int m = off[(row + 1) * n_cams] - off[row * n_cams];
@@ -671,12 +672,11 @@ __device__ __forceinline__ void score_drain(int count, const unsigned* q, int la
     }
 }
 
-__global__ void __launch_bounds__(SC_T) k_score(const float4* __restrict__ segs, const CamTable* __restrict__ cams, int n_cams, SrcTable src,
+__device__ __forceinline__ void b_score(const float4* __restrict__ segs, const CamTable* __restrict__ cams, int n_cams, SrcTable src,
                                                 const int* __restrict__ off, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
                                                 const int2* __restrict__ items, const int* __restrict__ n_items,
                                                 ScoreParams sp, float* __restrict__ score)
 {
-    L3D_PDL_PROLOGUE();
     extern __shared__ int s_max[];                 // [n_cams][SC_T] best confidence per (camera, hypothesis), as int bits
     __shared__ float2 s_d[SC_TILE];
     __shared__ float2 s_yd[SC_T];
@@ -794,12 +794,11 @@ __device__ __forceinline__ int depth_bucket(unsigned bits, unsigned bits_min, fl
     return min(BK_B - 1, int(float(bits - bits_min) * scale));
 }
 
-__global__ void __launch_bounds__(BK_T) k_bucket_segments(const int* __restrict__ off, int n_cams, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
+__device__ __forceinline__ void b_bucket_segments(const int* __restrict__ off, int n_cams, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
                                                           float* __restrict__ g_k, float* __restrict__ g_d2, unsigned* __restrict__ g_pl,
                                                           int* __restrict__ g_boff /* [n_src][BK_B + 1] */, uint4* __restrict__ g_brange,
                                                           int m_hi, int chunk, int* __restrict__ n_items, int2* __restrict__ items)
 {
-    L3D_PDL_PROLOGUE();
     __shared__ int s_cnt[BK_B], s_start[BK_B + 1];
     __shared__ unsigned s_lo[BK_T / 32], s_hi[BK_T / 32];
     __shared__ int s_item0;
@@ -851,14 +850,13 @@ __global__ void __launch_bounds__(BK_T) k_bucket_segments(const int* __restrict_
 
 // work items (segment, chunk of SC_T hypotheses) as in k_score; the partners of a hypothesis are looked for in the
 // depth buckets its window touches
-__global__ void __launch_bounds__(SC_T) k_score_window(const float4* __restrict__ segs, const CamTable* __restrict__ cams, int n_cams, SrcTable src,
+__device__ __forceinline__ void b_score_window(const float4* __restrict__ segs, const CamTable* __restrict__ cams, int n_cams, SrcTable src,
                                                        const int* __restrict__ off, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
                                                        const float* __restrict__ g_k, const float* __restrict__ g_d2, const unsigned* __restrict__ g_pl,
                                                        const int* __restrict__ g_boff, const uint4* __restrict__ g_brange,
                                                        const int2* __restrict__ items, const int* __restrict__ n_items,
                                                        ScoreParams sp, float* __restrict__ score)
 {
-    L3D_PDL_PROLOGUE();
     extern __shared__ int s_max[];                 // [n_cams][SC_T]
     __shared__ float2 s_yd[SC_T];
     __shared__ unsigned s_q[SC_WARPS][SC_QCAP];
@@ -932,11 +930,10 @@ __global__ void __launch_bounds__(SC_T) k_score_window(const float4* __restrict_
 // compaction in k_filter_compact, and the two iteration counters are summed on the way.
 // ------------------------------------------------------------------------------------------
 constexpr int RM_T = 1024;
-__global__ void __launch_bounds__(RM_T) k_reduce_matches(const int* __restrict__ Mptr, const int* __restrict__ off, int n_cams, const float* __restrict__ score,
+__device__ __forceinline__ void b_reduce_matches(const int* __restrict__ Mptr, const int* __restrict__ off, int n_cams, const float* __restrict__ score,
                                                          const int4* __restrict__ m_ids, unsigned long long* __restrict__ best /* [n_src], zeroed */,
                                                          int* __restrict__ cta_kept, unsigned long long* __restrict__ iters /* [0] all pairs, [1] same-camera pairs */)
 {
-    L3D_PDL_PROLOGUE();
     __shared__ int s_k[RM_T / 32];
     __shared__ unsigned long long s_a[RM_T / 32], s_b[RM_T / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1021,12 +1018,11 @@ __device__ float block_median_select(const float* __restrict__ dsamples, int n)
 // The last kernel of a view: the median depth, and all the small results in one buffer so that one copy brings
 // them to the host: out[0] = matches, out[1] = output records, out[2] = median depth (float bits), out[4..7] = two
 // 64-bit iteration counters, out[8 + d] = records handed to delivery slot d.  One block.
-__global__ void __launch_bounds__(MS_T) k_finish_view(float* __restrict__ dsamples, int n_samples, const unsigned long long* __restrict__ best, const float4* __restrict__ m_dep,
+__device__ __forceinline__ void b_finish_view(float* __restrict__ dsamples, int n_samples, const unsigned long long* __restrict__ best, const float4* __restrict__ m_dep,
                                                       const int* __restrict__ M, const int* __restrict__ F,
                                                       const unsigned long long* __restrict__ iters, const int* __restrict__ start, int stride, int n_deliver,
                                                       int* __restrict__ out)
 {
-    L3D_PDL_PROLOGUE();
     // depth samples: both depths of every segment's best match if its score exceeds 0.5 (cudawrapper.cu:1090-1110)
     for (int row = threadIdx.x; 2 * row < n_samples; row += MS_T) {
         const unsigned long long key = best[row];
@@ -1048,11 +1044,10 @@ __global__ void __launch_bounds__(MS_T) k_finish_view(float* __restrict__ dsampl
 // CTA b keeps cta_kept[b] records (k_reduce_matches), so it starts at the sum of the counts before it; inside the CTA
 // a ballot/prefix gives every kept match its place.  Also counts the records per hand-over group (destination
 // view's segment), the first step of the regrouping below.
-__global__ void __launch_bounds__(RM_T) k_filter_compact(const int* __restrict__ Mptr, const float* __restrict__ score, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
+__device__ __forceinline__ void b_filter_compact(const int* __restrict__ Mptr, const float* __restrict__ score, const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
                                                          const int* __restrict__ cta_kept, l3d_match* __restrict__ out, int* __restrict__ Fout,
-                                                         const CamTable* __restrict__ cams, int stride, int* __restrict__ hist /* or null */)
+                                                         const CamTable* __restrict__ cams, int stride, int* __restrict__ hist /* or null */, int n_cta)
 {
-    L3D_PDL_PROLOGUE();
     __shared__ int s_w[RM_T / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int k = blockIdx.x * RM_T + tid, M = *Mptr;
@@ -1082,13 +1077,11 @@ __global__ void __launch_bounds__(RM_T) k_filter_compact(const int* __restrict__
         out[r] = rec;
         if (hist) { const int dl = cams[id.y].deliver; if (dl >= 0) atomicAdd(&hist[dl * stride + id.z], 1); }     // hand-over group sizes
     }
-    if (blockIdx.x == gridDim.x - 1 && tid == 0) *Fout = base + total;
+    if (int(blockIdx.x) == n_cta - 1 && tid == 0) *Fout = base + total;
 }
 // unscored variant (no neighbour to pair-test): all records, confidence 0
-__global__ void k_copy_unscored(const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, const int* __restrict__ Mptr, l3d_match* __restrict__ out)
+__device__ __forceinline__ void b_copy_unscored_at(const int4* __restrict__ m_ids, const float4* __restrict__ m_dep, const int* __restrict__ Mptr, l3d_match* __restrict__ out, int k)
 {
-    L3D_PDL_PROLOGUE();
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= *Mptr) return;
     int4 id = m_ids[k]; float4 d = m_dep[k];
     l3d_match rec; rec.src_seg = id.x; rec.cam = id.y; rec.tgt_seg = id.z; rec.confidence = 0.0f;
@@ -1100,10 +1093,9 @@ __global__ void k_copy_unscored(const int4* __restrict__ m_ids, const float4* __
 // hand-over (line3D.cc:838-858): the filtered records towards each neighbour that asked for
 // delivery, reversed and regrouped by the neighbour's segment, target ids ascending
 // ------------------------------------------------------------------------------------------
-__global__ void k_deliver_scatter(const l3d_match* __restrict__ f, const int* __restrict__ Fptr, const CamTable* __restrict__ cams, int stride,
+__device__ __forceinline__ void b_deliver_scatter(const l3d_match* __restrict__ f, const int* __restrict__ Fptr, const CamTable* __restrict__ cams, int stride,
                                   const int* __restrict__ start, int* __restrict__ cursor, int* __restrict__ t_tgt, float4* __restrict__ t_dep)
 {
-    L3D_PDL_PROLOGUE();
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= *Fptr) return;
     const l3d_match m = f[k];
@@ -1114,6 +1106,106 @@ __global__ void k_deliver_scatter(const l3d_match* __restrict__ f, const int* __
     t_tgt[pos] = m.src_seg;
     t_dep[pos] = make_float4(m.depths[2], m.depths[3], m.depths[0], m.depths[1]);     // line3D.cc:852-855
 }
+// ------------------------------------------------------------------------------------------
+// The per-view kernels run on GROUPS of views.  Which view needs which other view first (the hand-over of filtered
+// matches) is a dependency graph, usually a few independent chains (views along a street; C2: 200 views, longest
+// chain 50), and the views of one dependency level are independent.  One launch of each kernel below covers all views
+// of a level: blockIdx.y (z for k_gather_counts) picks the view, whose buffers and sizes come from a VArgs record, and
+// the grid's x extent is the largest any view of the group needs.  Per level, not per view: the host's launch work
+// (it was the bottleneck at ~95 us per view) and the GPU's chain of short dependent kernels.
+// ------------------------------------------------------------------------------------------
+struct VArgs {
+    // tables of the view
+    const CamTable* cams; int n_cams, n_src; SrcTable src; ScoreParams sp;
+    // pair-test results of the view's batch
+    const int* raw_cnt; const int* cand_off; const int* stage_col; const float4* stage_dep; const unsigned char* stage_ok;
+    // match list
+    int* cnt; int* off; int4* mids; float4* mdep; float* score;
+    // scoring
+    float* sk; float* sd2; unsigned* spl; int* boff; uint4* brange; int2* items; int max_items; int scored, windowed, quadratic, m_hi;
+    // zeroed per view
+    int* nitems; unsigned long long* iters; unsigned long long* best; int* hist; int* cursor;
+    // reduce, filter
+    int* cta_kept; int n_cta; int* Fout; l3d_match* filtered; float* dsamples;
+    // hand-over
+    int delivering, stride, n_keys, n_deliver; int* dl_start; int* dl_tgt; float4* dl_dep;
+    int* vres;
+};
+#define L3D_VIEW(dim) L3D_PDL_PROLOGUE(); const VArgs& va = all[blockIdx.dim]
+
+__global__ void k_gather_counts(const VArgs* __restrict__ all)
+{
+    L3D_VIEW(z);
+    if (int(blockIdx.y) >= va.n_cams) return;
+    b_gather_counts(va.cams, va.n_cams, va.n_src, va.raw_cnt, va.cnt);
+}
+// which = 0: count matrix -> offsets; 1: hand-over group sizes -> group starts.  One block per view.
+__global__ void __launch_bounds__(SCAN_T) k_scan_views(const VArgs* __restrict__ all, int which)
+{
+    L3D_VIEW(y);
+    if (which == 0) block_scan_global(va.cnt, va.off, va.n_src * va.n_cams);
+    else if (va.delivering) block_scan_global(va.hist, va.dl_start, va.n_keys);
+}
+__global__ void k_fill(const VArgs* __restrict__ all, const float4* __restrict__ segs)
+{
+    L3D_VIEW(y);
+    (void)segs;
+    b_fill(va.cams, va.n_cams, va.n_src, va.off, va.cand_off, va.stage_col, va.stage_dep, va.stage_ok, va.mids, va.mdep);
+}
+__global__ void __launch_bounds__(BK_T) k_bucket_segments(const VArgs* __restrict__ all)
+{
+    L3D_VIEW(y);
+    if (!va.scored || !va.windowed || int(blockIdx.x) >= va.n_src) return;
+    b_bucket_segments(va.off, va.n_cams, va.mids, va.mdep, va.sk, va.sd2, va.spl, va.boff, va.brange, va.m_hi, SC_T, va.nitems, va.items);
+}
+__global__ void __launch_bounds__(SC_T) k_score_window(const VArgs* __restrict__ all, const float4* __restrict__ segs)
+{
+    L3D_VIEW(y);
+    if (!va.scored || !va.windowed) return;
+    b_score_window(segs, va.cams, va.n_cams, va.src, va.off, va.mids, va.mdep, va.sk, va.sd2, va.spl, va.boff, va.brange, va.items, va.nitems, va.sp, va.score);
+}
+// the quadratic path: views without the 3-D gate, and segments too long for the window kernel's index
+__global__ void k_score_items(const VArgs* __restrict__ all)
+{
+    L3D_VIEW(y);
+    if (!va.scored || !va.quadratic) return;
+    b_score_items(va.off, va.n_cams, va.n_src, va.windowed ? 0 : 0x7fffffff, va.windowed ? va.m_hi : 0x7fffffff, 1, va.nitems + 1, va.items + va.max_items);
+}
+__global__ void __launch_bounds__(SC_T) k_score(const VArgs* __restrict__ all, const float4* __restrict__ segs)
+{
+    L3D_VIEW(y);
+    if (!va.scored || !va.quadratic) return;
+    b_score(segs, va.cams, va.n_cams, va.src, va.off, va.mids, va.mdep, va.items + va.max_items, va.nitems + 1, va.sp, va.score);
+}
+__global__ void __launch_bounds__(RM_T) k_reduce_matches(const VArgs* __restrict__ all)
+{
+    L3D_VIEW(y);
+    if (!va.scored || int(blockIdx.x) >= va.n_cta) return;
+    b_reduce_matches(va.off + va.n_src * va.n_cams, va.off, va.n_cams, va.score, va.mids, va.best, va.cta_kept, va.iters);
+}
+__global__ void __launch_bounds__(RM_T) k_filter_compact(const VArgs* __restrict__ all)
+{
+    L3D_VIEW(y);
+    if (int(blockIdx.x) >= va.n_cta) return;
+    if (va.scored) b_filter_compact(va.off + va.n_src * va.n_cams, va.score, va.mids, va.mdep, va.cta_kept, va.filtered, va.Fout, va.cams, va.stride, va.delivering ? va.hist : nullptr, va.n_cta);
+    else {          // no neighbour was pair-tested (cudawrapper.cu:877-878): all records, unscored; RM_T / 256 chunks of 256 per block
+        b_copy_unscored_at(va.mids, va.mdep, va.off + va.n_src * va.n_cams, va.filtered, blockIdx.x * RM_T + threadIdx.x);
+    }
+}
+__global__ void k_deliver_scatter(const VArgs* __restrict__ all)
+{
+    L3D_VIEW(y);
+    if (!va.delivering) return;
+    b_deliver_scatter(va.filtered, va.Fout, va.cams, va.stride, va.dl_start, va.cursor, va.dl_tgt, va.dl_dep);
+}
+__global__ void __launch_bounds__(MS_T) k_finish_view(const VArgs* __restrict__ all)
+{
+    L3D_VIEW(y);
+    const int* Mptr = va.off + va.n_src * va.n_cams;
+    b_finish_view(va.dsamples, va.scored ? 2 * va.n_src : 0, va.best, va.mdep, Mptr, va.scored ? va.Fout : Mptr, va.scored ? va.iters : nullptr,
+                  va.delivering ? va.dl_start : nullptr, va.stride, va.delivering ? va.n_deliver : 0, va.vres);
+}
+
 // ------------------------------------------------------------------------------------------
 // collinearity (cudawrapper.cu:476-535): upper triangle, compacted on the device
 // ------------------------------------------------------------------------------------------
@@ -1388,26 +1480,61 @@ struct ViewJob {                 // phase B of one view: on the stream, not yet 
     int n_deliver = 0, owner = -1;
     std::vector<std::pair<int, int> > consumed;      // (deliver buffer, slot) of every delivery the view took in
 };
-// The hand-over between views is a dependency graph, not a chain (C2: 200 views, longest chain 50), so several views
-// are on the GPU at once: VS_W slots, each with its own scratch buffers, on VS_S streams; a view waits for the events
-// of the views whose records it receives.  The caller still gets its results in the order of its calls.
-constexpr int VS_W = 8, VS_S = 4;
+// The per-view work runs on groups of views (see VArgs): a slot holds one view's buffers, a group up to VG_MAX
+// slots plus what the group's views share (one upload of tables and arguments, one memset, one result download).
+// Two groups exist: the host prepares and launches the next one while the GPU works on the current one.
+constexpr int VG_MAX = 8;
 struct ViewSlot {
     ViewJob job;
-    cudaStream_t stream = nullptr;                   // one of l3d_ctx::vstream
-    std::string err; uint64_t launches = 0; DBuf<int> d_tile_sums, d_total;      // what scan_exclusive wants from its context
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [0] results on the host, [2..5] stage boundaries
-    DBuf<CamTable> d_cams; HBuf<CamTable> h_cams;
-    DBuf<int> d_cnt, d_off, d_fcnt, d_foff, d_boff, d_zero, d_vres; HBuf<int> h_vres;
+    size_t plan_index = 0;
+    DBuf<int> d_cnt, d_off, d_cta, d_F, d_boff;
     DBuf<int4> d_mids; DBuf<float4> d_mdep; DBuf<float> d_score, d_dsamples, d_sk, d_sd2; DBuf<unsigned> d_spl;
     DBuf<int2> d_items; DBuf<uint4> d_brange; DBuf<l3d_match> d_filtered;
     void release()
     {
-        d_cams.release(); h_cams.release(); d_cnt.release(); d_off.release(); d_fcnt.release(); d_foff.release(); d_boff.release(); d_zero.release();
-        d_vres.release(); h_vres.release(); d_mids.release(); d_mdep.release(); d_score.release(); d_dsamples.release(); d_sk.release(); d_sd2.release();
-        d_spl.release(); d_items.release(); d_brange.release(); d_filtered.release(); d_tile_sums.release(); d_total.release();
+        d_cnt.release(); d_off.release(); d_cta.release(); d_F.release(); d_boff.release(); d_mids.release(); d_mdep.release(); d_score.release();
+        d_dsamples.release(); d_sk.release(); d_sd2.release(); d_spl.release(); d_items.release(); d_brange.release(); d_filtered.release();
+    }
+};
+constexpr int VG_RES = 8 + 64;           // result ints per view: 8 scalars + one count per hand-over slot (checked against n_deliver)
+struct ViewGroup {
+    int count = 0; size_t pos0 = 0;      // positions [pos0, pos0 + count) of the execution order
+    ViewSlot slot[VG_MAX];
+    HBuf<VArgs> h_args; DBuf<VArgs> d_args;
+    HBuf<CamTable> h_cams; DBuf<CamTable> d_cams; size_t cam_off[VG_MAX + 1];
+    DBuf<int> d_zero; DBuf<int> d_vres; HBuf<int> h_vres;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [0] results on the host, [2..5] stage boundaries
+    void release()
+    {
+        for (int k = 0; k < VG_MAX; ++k) slot[k].release();
+        h_args.release(); d_args.release(); h_cams.release(); d_cams.release(); d_zero.release(); d_vres.release(); h_vres.release();
         for (int k = 0; k < 6; ++k) if (ev[k]) { cudaEventDestroy(ev[k]); ev[k] = nullptr; }
     }
+};
+// Device memory for the hand-over buffers, recycled on the host: a buffer goes back when the last receiving view has
+// been collected, so nothing on the GPU can still be reading it (stream-ordered allocation across streams cost 10 us
+// per call here).
+struct DevPool {
+    struct Block { void* p; size_t cap; bool free; };
+    std::vector<Block> blocks;
+    cudaError_t get(size_t bytes, void** out)
+    {
+        size_t best = blocks.size();
+        for (size_t k = 0; k < blocks.size(); ++k)
+            if (blocks[k].free && blocks[k].cap >= bytes && blocks[k].cap <= 4 * std::max<size_t>(bytes, 4096) && (best == blocks.size() || blocks[k].cap < blocks[best].cap)) best = k;
+        if (best == blocks.size()) {
+            size_t cap = 4096; while (cap < bytes) cap <<= 1;
+            void* p = nullptr;
+            cudaError_t e = cudaMalloc(&p, cap);
+            if (e != cudaSuccess) return e;
+            Block b = {p, cap, true}; blocks.push_back(b);
+        }
+        blocks[best].free = false; *out = blocks[best].p;
+        return cudaSuccess;
+    }
+    void put(void* p) { for (size_t k = 0; k < blocks.size(); ++k) if (blocks[k].p == p) { blocks[k].free = true; return; } }
+    void put_all() { for (size_t k = 0; k < blocks.size(); ++k) blocks[k].free = true; }
+    void release() { for (size_t k = 0; k < blocks.size(); ++k) cudaFree(blocks[k].p); blocks.clear(); }
 };
 
 // Everything one batch of pair tests (phase A) produces and needs: two of these exist, so that a helper thread can
@@ -1471,11 +1598,11 @@ struct l3d_ctx {
     uint64_t batch_override = 0;                    // l3d_debug_set_batch_pairs
     float pa_kernel_ms[2] = {0.f, 0.f};
     DBuf<int> d_res, d_zero;
-    // views in flight: positions [fly_begin, fly_end) of `order` are on the GPU, position i in slot i % VS_W on stream i % VS_S
-    ViewSlot vs[VS_W]; cudaStream_t vstream[VS_S] = {nullptr, nullptr, nullptr, nullptr};
-    size_t fly_begin = 0, fly_end = 0; std::vector<int> inflight_slot;   // per view: its slot while in flight, else -1
+    // views in flight: positions [fly_begin, fly_end) of `order` are on the GPU, as the groups [grp_begin, grp_end)
+    ViewGroup grp[2]; size_t grp_begin = 0, grp_end = 0;
+    size_t fly_begin = 0, fly_end = 0; std::vector<int> level;
     float run_sigma_p = 0.f, run_sigma_a = 0.f;
-    cudaEvent_t join_ev = nullptr;
+    DevPool pool;
     cudaStream_t copy_stream = nullptr;
     bool stage_events = false;         // per-stage CUDA events inside a view (l3d_set_stage_timing): they separate kernels that otherwise overlap
     cudaEvent_t mark_ev[2] = {nullptr, nullptr};
@@ -1537,18 +1664,6 @@ int fetch_int(l3d_ctx* ctx, const int* dptr, int* out)
     L3D_CUDA(cudaStreamSynchronize(ctx->stream));
     *out = ctx->h_ints.p[0];
     return 0;
-}
-
-void release_delivered(l3d_ctx* ctx, Delivered& d)
-{
-    if (d.owner >= 0) {
-        DeliverBuf& b = ctx->deliver_bufs[d.owner];
-        if (--b.refs == 0) {
-            cudaFreeAsync(b.start, ctx->stream); cudaFreeAsync(b.tgt, ctx->stream); cudaFreeAsync(b.dep, ctx->stream);
-            b.start = nullptr; b.tgt = nullptr; b.dep = nullptr;
-        }
-    }
-    d = Delivered();
 }
 
 // Phase A for a set of (source view, neighbour) jobs: hoist, pre-test, scan, exact test.
@@ -1659,214 +1774,207 @@ bool same_neighbors(const std::vector<l3d_neighbor>& a, int n, const l3d_neighbo
     return true;
 }
 
-// Phase B of one view is split in two so that the next view of an announced schedule can be put on the stream
-// before the host waits for this one: enqueue_view launches everything (sizes come from upper bounds, the real
-// counts stay on the device), finish_view waits for the view's small result record and fetches its output.
-int enqueue_view(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, float sigma_p, float sigma_a, int first_job, ViewSlot& sl)
+// Phase B of a group of views (all of one dependency level, see VArgs), split in two so that the next group can be
+// put on the stream before the host waits for this one: enqueue_group does the host's bookkeeping for every view,
+// uploads the group's tables and arguments once and launches every kernel once (sizes come from upper bounds, the
+// real counts stay on the device); finish_group waits for the group's result records and fetches the views' output.
+struct GroupView { int view; int n_nb; const l3d_neighbor* nb; int first_job; size_t plan_index; };
+
+int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, float sigma_p, float sigma_a)
 {
-    if (view < 0 || view >= ctx->V) { ctx->err = "l3d_match_view: view index out of range"; return 1; }
-    for (int c = 0; c < n_nb; ++c) {
-        if (nb[c].view < 0 || nb[c].view >= ctx->V || nb[c].view == view) { ctx->err = "l3d_match_view: bad neighbour view index"; return 1; }
-        if (c > 0 && nb[c - 1].view >= nb[c].view) { ctx->err = "l3d_match_view: neighbours must be in ascending view order"; return 1; }
-    }
-    cudaStream_t st = sl.stream;
-    ViewJob& job = sl.job;
+    cudaStream_t st = ctx->stream;
     PhaseASet& pa = ctx->pa[ctx->cur];
-    const l3d_view& sv = ctx->views[view];
-    const int n_src = sv.n_segments;
-    HBuf<CamTable>& hc = sl.h_cams;
-    DBuf<l3d_match>& dfil = sl.d_filtered;
-    cudaEvent_t* ev = sl.ev;
-    job.view = view; job.nb.assign(nb, nb + n_nb); job.sigma_p = sigma_p; job.sigma_a = sigma_a;
-    job.consumed.clear(); job.owner = -1;
-
-    // ---- tables -------------------------------------------------------------------------
-    L3D_CUDA(hc.ensure(size_t(n_nb)));
-    int n_slots = 0, n_deliver = 0, max_deliver_seg = 1;
-    uint64_t pair_tests = 0, cand_ub = 0, raw_ub = 0;
-    size_t seg_ub = 0;                               // upper bound on the matches of one source segment
-    std::vector<int> consumed;                       // indices into ctx->delivered[view]
-    uint64_t delivered_ub = 0;
-    for (int c = 0; c < n_nb; ++c) {
-        const l3d_neighbor& n = nb[c];
-        const l3d_view& tv = ctx->views[n.view];
-        CamTable& ct = hc.p[c];
-        memcpy(ct.F, n.F, sizeof ct.F); memcpy(ct.RtKinv, tv.RtKinv, sizeof ct.RtKinv);
-        memcpy(ct.P, tv.P, sizeof ct.P); memcpy(ct.C, tv.C, sizeof ct.C);
-        ct.seg_off = ctx->seg_off[n.view]; ct.n_seg = tv.n_segments;
-        ct.t_start = nullptr; ct.t_tgt = nullptr; ct.t_dep = nullptr; ct.slot = -1; ct.deliver = -1; ct.row_off = 0;
-        if (n.to_be_matched) {
-            const int j = first_job + n_slots;
-            ct.mode = 0; ct.slot = n_slots++; ct.row_off = pa.jobs_host[j].row_off;
-            cand_ub += pa.job_cands[j]; raw_ub += pa.job_raw[j]; seg_ub += size_t(pa.job_raw_rowmax[j]);
-            pair_tests += uint64_t(n_src) * uint64_t(tv.n_segments);
-        } else {
-            ct.mode = 2;
-            std::vector<Delivered>& dl = ctx->delivered[view];
-            for (size_t k = 0; k < dl.size(); ++k)
-                if (dl[k].from_view == n.view) {
-                    // the records come from a view that may still be running on another stream
-                    const int ps = ctx->inflight_slot[dl[k].from_view];
-                    if (ps >= 0 && ctx->vs[ps].stream != st) L3D_CUDA(cudaStreamWaitEvent(st, ctx->vs[ps].ev[0], 0));
-                    ct.mode = 1; ct.t_start = dl[k].t_start; ct.t_tgt = dl[k].t_tgt; ct.t_dep = dl[k].t_dep; delivered_ub += uint64_t(dl[k].count); seg_ub += size_t(dl[k].max_group); consumed.push_back(int(k)); job.consumed.push_back(std::make_pair(dl[k].owner, dl[k].slot)); break; }
+    gr.count = count;
+    L3D_CUDA(gr.h_args.ensure(VG_MAX)); L3D_CUDA(gr.d_args.ensure(VG_MAX));
+    L3D_CUDA(gr.d_vres.ensure(size_t(VG_MAX) * VG_RES)); L3D_CUDA(gr.h_vres.ensure(size_t(VG_MAX) * VG_RES));
+    size_t cams_total = 0;
+    for (int g = 0; g < count; ++g) {
+        if (gv[g].view < 0 || gv[g].view >= ctx->V) { ctx->err = "l3d_match_view: view index out of range"; return 1; }
+        for (int c = 0; c < gv[g].n_nb; ++c) {
+            if (gv[g].nb[c].view < 0 || gv[g].nb[c].view >= ctx->V || gv[g].nb[c].view == gv[g].view) { ctx->err = "l3d_match_view: bad neighbour view index"; return 1; }
+            if (c > 0 && gv[g].nb[c - 1].view >= gv[g].nb[c].view) { ctx->err = "l3d_match_view: neighbours must be in ascending view order"; return 1; }
         }
-        if (n.deliver) { ct.deliver = n_deliver++; max_deliver_seg = std::max(max_deliver_seg, tv.n_segments); }
+        gr.cam_off[g] = cams_total; cams_total += size_t(gv[g].n_nb);
     }
-    job.pair_tests = pair_tests; job.cand_ub = cand_ub;
-    SrcTable src;
-    memcpy(src.RtKinv, sv.RtKinv, sizeof src.RtKinv); memcpy(src.C, sv.C, sizeof src.C);
-    src.spatial_k = sv.spatial_k; src.cmax = std::max(std::fabs(sv.C[0]), std::max(std::fabs(sv.C[1]), std::fabs(sv.C[2])));
-    src.seg_off = ctx->seg_off[view]; src.n_seg = n_src;
-    const size_t M_ub = size_t(raw_ub + delivered_ub);          // upper bound on the number of matches to score
+    gr.cam_off[count] = cams_total;
+    L3D_CUDA(gr.h_cams.ensure(cams_total)); L3D_CUDA(gr.d_cams.ensure(cams_total));
 
-    L3D_CUDA(sl.d_cams.ensure(size_t(n_nb)));
-    L3D_CUDA(cudaMemcpyAsync(sl.d_cams.p, hc.p, sizeof(CamTable) * n_nb, cudaMemcpyHostToDevice, st));
-    L3D_CUDA(sl.d_cnt.ensure(size_t(n_src) * n_nb + 1));
-    L3D_CUDA(sl.d_off.ensure(size_t(n_src) * n_nb + 2));
-    if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[2], st));
-
-    // ---- assemble the match list ----------------------------------------------------------
-    const int* d_M = sl.d_off.p + size_t(n_src) * n_nb;             // total number of matches, on the device
-    if (n_src > 0) {
-        L3D_CUDA(pdl_launch(k_gather_counts, dim3(dim3((n_src + 255) / 256, n_nb)), dim3(256), 0, st, sl.d_cams.p, n_nb, n_src, pa.d_pa_raw.p, sl.d_cnt.p));
-        ctx->launches += 1;
-        if (scan_exclusive(&sl, sl.d_cnt.p, sl.d_off.p, n_src * n_nb)) { ctx->err = sl.err; return 1; }
-    } else {
-        L3D_CUDA(cudaMemsetAsync(sl.d_off.p, 0, sizeof(int) * 2, st));
-    }
-    if (M_ub > 0) {
-        L3D_CUDA(sl.d_mids.ensure(M_ub)); L3D_CUDA(sl.d_mdep.ensure(M_ub)); L3D_CUDA(sl.d_score.ensure(M_ub));
-        const long warps = long(n_src) * n_nb;
-        L3D_CUDA(pdl_launch(k_fill, dim3(unsigned((warps * 32 + 255) / 256)), dim3(256), 0, st, sl.d_cams.p, n_nb, n_src, sl.d_off.p, pa.d_pa_off.p,
-                                                                  pa.d_stage_col.p, pa.d_stage_dep.p, pa.d_stage_ok.p, sl.d_mids.p, sl.d_mdep.p));
-        ctx->launches += 1;
-        L3D_CUDA(cudaGetLastError());
-    }
-    if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[3], st));
-
-    const bool scored = n_slots > 0;                  // cudawrapper.cu:877-878
-    const int* d_F = nullptr;                         // number of output records, on the device
-    L3D_CUDA(dfil.ensure(std::max<size_t>(M_ub, 1)));
-    // everything that has to start from zero lives in one buffer and is cleared with one memset per view
-    const bool delivering = n_deliver > 0 && scored;
-    const int stride = max_deliver_seg + 1;                         // one spare key per slot keeps t_start[n_seg] addressable
-    const int n_keys = delivering ? n_deliver * stride : 0;
-    const int ns = 2 * n_src;
-    const size_t z_items = 0, z_iters = 4, z_rank = 8, z_hist = z_rank + size_t(2 * ns) + 2, z_cursor = z_hist + size_t(n_keys) + 2, z_end = z_cursor + size_t(n_keys) + 2;
-    L3D_CUDA(sl.d_zero.ensure(z_end));
-    L3D_CUDA(cudaMemsetAsync(sl.d_zero.p, 0, sizeof(int) * z_end, st));
-    int* d_nitems = sl.d_zero.p + z_items;
-    unsigned long long* d_iters = reinterpret_cast<unsigned long long*>(sl.d_zero.p + z_iters);
-    int* d_hist = sl.d_zero.p + z_hist; int* d_cursor = sl.d_zero.p + z_cursor;
-    unsigned long long* d_best = reinterpret_cast<unsigned long long*>(sl.d_zero.p + z_rank);     // [n_src], 8-byte aligned (z_rank is even)
-    if (scored && M_ub > 0) {
-        // ---- score ------------------------------------------------------------------------
-        ScoreParams sp; sp.sigma_p = sigma_p; sp.sigma_a = sigma_a;
-        L3D_CUDA(sl.d_foff.ensure(4));
-        L3D_CUDA(sl.d_dsamples.ensure(size_t(n_src) * 2));
-        // Segments are grouped by depth and scored through windows; the tiled quadratic kernel takes everything when
-        // the 3-D gate is switched off, and segments with more matches than the window kernel's 20-bit index can hold.
-        const int SORT_MAX = 1 << 20;
-        const bool windowed = src.spatial_k > 0.0f;
+    // ---- per view: tables, bounds, buffers, hand-over records, kernel arguments ------------------------------
+    size_t zero_total = 0;
+    int mx_src = 1, mx_cams = 1, mx_items = 1, mx_cta = 1; long mx_warps = 1; size_t mx_M = 0, mx_smem = 0;
+    bool any_scored = false, any_window = false, any_quadratic = false, any_deliver = false;
+    struct Z { size_t items, iters, best, hist, cursor, end; } z[VG_MAX];
+    for (int g = 0; g < count; ++g) {
+        const int view = gv[g].view, n_nb = gv[g].n_nb; const l3d_neighbor* nb = gv[g].nb; const int first_job = gv[g].first_job;
+        ViewSlot& sl = gr.slot[g];
+        ViewJob& job = sl.job;
+        sl.plan_index = gv[g].plan_index;
+        const l3d_view& sv = ctx->views[view];
+        const int n_src = sv.n_segments;
+        CamTable* hc = gr.h_cams.p + gr.cam_off[g];
+        job.view = view; job.nb.assign(nb, nb + n_nb); job.sigma_p = sigma_p; job.sigma_a = sigma_a;
+        job.consumed.clear(); job.owner = -1;
+        int n_slots = 0, n_deliver = 0, max_deliver_seg = 1;
+        uint64_t pair_tests = 0, cand_ub = 0, raw_ub = 0, delivered_ub = 0;
+        size_t seg_ub = 0;                               // upper bound on the matches of one source segment
+        std::vector<int> consumed;                       // indices into ctx->delivered[view]
+        for (int c = 0; c < n_nb; ++c) {
+            const l3d_neighbor& n = nb[c];
+            const l3d_view& tv = ctx->views[n.view];
+            CamTable& ct = hc[c];
+            memcpy(ct.F, n.F, sizeof ct.F); memcpy(ct.RtKinv, tv.RtKinv, sizeof ct.RtKinv);
+            memcpy(ct.P, tv.P, sizeof ct.P); memcpy(ct.C, tv.C, sizeof ct.C);
+            ct.seg_off = ctx->seg_off[n.view]; ct.n_seg = tv.n_segments;
+            ct.t_start = nullptr; ct.t_tgt = nullptr; ct.t_dep = nullptr; ct.slot = -1; ct.deliver = -1; ct.row_off = 0;
+            if (n.to_be_matched) {
+                const int j = first_job + n_slots;
+                ct.mode = 0; ct.slot = n_slots++; ct.row_off = pa.jobs_host[j].row_off;
+                cand_ub += pa.job_cands[j]; raw_ub += pa.job_raw[j]; seg_ub += size_t(pa.job_raw_rowmax[j]);
+                pair_tests += uint64_t(n_src) * uint64_t(tv.n_segments);
+            } else {
+                ct.mode = 2;
+                std::vector<Delivered>& dl = ctx->delivered[view];
+                for (size_t k = 0; k < dl.size(); ++k)
+                    if (dl[k].from_view == n.view) {
+                        ct.mode = 1; ct.t_start = dl[k].t_start; ct.t_tgt = dl[k].t_tgt; ct.t_dep = dl[k].t_dep;
+                        delivered_ub += uint64_t(dl[k].count); seg_ub += size_t(dl[k].max_group);
+                        consumed.push_back(int(k)); job.consumed.push_back(std::make_pair(dl[k].owner, dl[k].slot));
+                        break;
+                    }
+            }
+            if (n.deliver) { ct.deliver = n_deliver++; max_deliver_seg = std::max(max_deliver_seg, tv.n_segments); }
+        }
+        if (n_deliver > VG_RES - 8) { ctx->err = "l3d_match_view: more than 64 neighbours ask for this view's matches"; return 1; }
+        job.pair_tests = pair_tests; job.cand_ub = cand_ub;
+        const size_t M_ub = size_t(raw_ub + delivered_ub);          // upper bound on the number of matches to score
+        const bool scored = n_slots > 0;                             // cudawrapper.cu:877-878
+        const bool delivering = n_deliver > 0 && scored;
+        const int stride = max_deliver_seg + 1;                      // one spare key per slot keeps t_start[n_seg] addressable
+        const int n_keys = delivering ? n_deliver * stride : 0;
+        const bool windowed = sv.spatial_k > 0.0f;
+        const int SORT_MAX = 1 << 20;                                // the window kernel's index has 20 bits
+        const bool quadratic = scored && (!windowed || seg_ub > size_t(SORT_MAX));
         const int max_items = int(M_ub / SC_T) + n_src + 1;
-        L3D_CUDA(sl.d_items.ensure(size_t(2 * max_items)));
+        const int n_cta = int(std::max<size_t>((M_ub + RM_T - 1) / RM_T, 1));
         const size_t sm_bytes = size_t(n_nb) * SC_T * sizeof(int);
         if (sm_bytes > 160 * 1024) { ctx->err = "l3d_match_view: too many neighbours for the scoring kernel's shared memory"; return 1; }
-        if (sm_bytes > ctx->score_smem) {
-            L3D_CUDA(cudaFuncSetAttribute(k_score, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_bytes)));
-            L3D_CUDA(cudaFuncSetAttribute(k_score_window, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sm_bytes)));
-            ctx->score_smem = sm_bytes;
+        // buffers of this view
+        L3D_CUDA(sl.d_cnt.ensure(size_t(n_src) * n_nb + 1)); L3D_CUDA(sl.d_off.ensure(size_t(n_src) * n_nb + 2));
+        L3D_CUDA(sl.d_mids.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_mdep.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_score.ensure(std::max<size_t>(M_ub, 1)));
+        L3D_CUDA(sl.d_filtered.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_cta.ensure(size_t(n_cta) + 1)); L3D_CUDA(sl.d_F.ensure(4));
+        L3D_CUDA(sl.d_dsamples.ensure(size_t(n_src) * 2 + 2)); L3D_CUDA(sl.d_items.ensure(size_t(2 * max_items)));
+        if (scored && windowed) {
+            L3D_CUDA(sl.d_sk.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_sd2.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_spl.ensure(std::max<size_t>(M_ub, 1)));
+            L3D_CUDA(sl.d_boff.ensure(size_t(n_src) * (BK_B + 1))); L3D_CUDA(sl.d_brange.ensure(size_t(std::max(n_src, 1))));
         }
-        if (windowed) {
-            L3D_CUDA(sl.d_sk.ensure(M_ub)); L3D_CUDA(sl.d_sd2.ensure(M_ub)); L3D_CUDA(sl.d_spl.ensure(M_ub));
-            L3D_CUDA(sl.d_boff.ensure(size_t(n_src) * (BK_B + 1))); L3D_CUDA(sl.d_brange.ensure(size_t(n_src)));
-            L3D_CUDA(pdl_launch(k_bucket_segments, dim3(n_src), dim3(BK_T), 0, st, sl.d_off.p, n_nb, sl.d_mids.p, sl.d_mdep.p, sl.d_sk.p, sl.d_sd2.p, sl.d_spl.p,
-                                sl.d_boff.p, sl.d_brange.p, SORT_MAX, SC_T, d_nitems, sl.d_items.p));
-            L3D_CUDA(pdl_launch(k_score_window, dim3(max_items), dim3(SC_T), sm_bytes, st, ctx->d_segs.p, sl.d_cams.p, n_nb, src, sl.d_off.p, sl.d_mids.p, sl.d_mdep.p,
-                                                             sl.d_sk.p, sl.d_sd2.p, sl.d_spl.p, sl.d_boff.p, sl.d_brange.p, sl.d_items.p, d_nitems, sp, sl.d_score.p));
-            ctx->launches += 2;
+        // what has to start from zero: one region per view in the group's zero buffer
+        z[g].items = zero_total; z[g].iters = z[g].items + 4; z[g].best = z[g].iters + 4; z[g].hist = z[g].best + 2 * size_t(n_src) + 2;
+        z[g].cursor = z[g].hist + size_t(n_keys) + 2; z[g].end = (z[g].cursor + size_t(n_keys) + 2 + 3) & ~size_t(3);
+        zero_total = z[g].end;
+        // hand-over buffers
+        DeliverBuf buf;
+        if (delivering) {
+            buf.refs = n_deliver;
+            L3D_CUDA(ctx->pool.get(sizeof(int) * (size_t(n_keys) + 2), reinterpret_cast<void**>(&buf.start)));
+            L3D_CUDA(ctx->pool.get(sizeof(int) * std::max<size_t>(M_ub, 1), reinterpret_cast<void**>(&buf.tgt)));
+            L3D_CUDA(ctx->pool.get(sizeof(float4) * std::max<size_t>(M_ub, 1), reinterpret_cast<void**>(&buf.dep)));
         }
-        if (!windowed || seg_ub > size_t(SORT_MAX)) {
-            L3D_CUDA(pdl_launch(k_score_items, dim3((n_src + 255) / 256), dim3(256), 0, st, sl.d_off.p, n_nb, n_src, windowed ? 0 : 0x7fffffff, windowed ? SORT_MAX : 0x7fffffff, 1,
-                                                              d_nitems + 1, sl.d_items.p + max_items));
-            L3D_CUDA(pdl_launch(k_score, dim3(max_items), dim3(SC_T), sm_bytes, st, ctx->d_segs.p, sl.d_cams.p, n_nb, src, sl.d_off.p, sl.d_mids.p, sl.d_mdep.p,
-                                                      sl.d_items.p + max_items, d_nitems + 1, sp, sl.d_score.p));
-            ctx->launches += 2;
+        job.M_ub = M_ub; job.scored = scored; job.delivering = delivering; job.n_deliver = n_deliver;
+        // kernel arguments (pointers into the zero buffer are filled in below, when it has its size)
+        VArgs& va = gr.h_args.p[g];
+        memset(&va, 0, sizeof va);
+        va.cams = gr.d_cams.p + gr.cam_off[g]; va.n_cams = n_nb; va.n_src = n_src;
+        memcpy(va.src.RtKinv, sv.RtKinv, sizeof va.src.RtKinv); memcpy(va.src.C, sv.C, sizeof va.src.C);
+        va.src.spatial_k = sv.spatial_k; va.src.cmax = std::max(std::fabs(sv.C[0]), std::max(std::fabs(sv.C[1]), std::fabs(sv.C[2])));
+        va.src.seg_off = ctx->seg_off[view]; va.src.n_seg = n_src;
+        va.sp.sigma_p = sigma_p; va.sp.sigma_a = sigma_a;
+        va.raw_cnt = pa.d_pa_raw.p; va.cand_off = pa.d_pa_off.p; va.stage_col = pa.d_stage_col.p; va.stage_dep = pa.d_stage_dep.p; va.stage_ok = pa.d_stage_ok.p;
+        va.cnt = sl.d_cnt.p; va.off = sl.d_off.p; va.mids = sl.d_mids.p; va.mdep = sl.d_mdep.p; va.score = sl.d_score.p;
+        va.sk = sl.d_sk.p; va.sd2 = sl.d_sd2.p; va.spl = sl.d_spl.p; va.boff = sl.d_boff.p; va.brange = sl.d_brange.p; va.items = sl.d_items.p; va.max_items = max_items;
+        va.scored = scored ? 1 : 0; va.windowed = windowed ? 1 : 0; va.quadratic = quadratic ? 1 : 0; va.m_hi = SORT_MAX;
+        va.cta_kept = sl.d_cta.p; va.n_cta = n_cta; va.Fout = sl.d_F.p; va.filtered = sl.d_filtered.p; va.dsamples = sl.d_dsamples.p;
+        va.delivering = delivering ? 1 : 0; va.stride = stride; va.n_keys = n_keys; va.n_deliver = n_deliver;
+        va.dl_start = buf.start; va.dl_tgt = buf.tgt; va.dl_dep = buf.dep;
+        va.vres = gr.d_vres.p + size_t(g) * VG_RES;
+        // the hand-over records exist from now on (stream order); until this view is collected their sizes are bounds
+        if (delivering) {
+            job.owner = int(ctx->deliver_bufs.size());
+            buf.counts.assign(size_t(n_deliver), 0); buf.maxg.assign(size_t(n_deliver), 0);
+            for (int c = 0; c < n_nb; ++c) {
+                const int d = hc[c].deliver;
+                if (d < 0) continue;
+                const uint64_t ub = std::min<uint64_t>(hc[c].slot >= 0 ? pa.job_raw[first_job + hc[c].slot] : uint64_t(M_ub), 0x7fffffffull);
+                Delivered dl; dl.from_view = view; dl.owner = job.owner; dl.slot = d;
+                dl.count = int(ub); dl.max_group = int(std::min<uint64_t>(ub, uint64_t(n_src)));      // a source segment matches a target segment once
+                dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
+                buf.counts[d] = dl.count; buf.maxg[d] = dl.max_group;
+                ctx->delivered[nb[c].view].push_back(dl);
+            }
+            ctx->deliver_bufs.push_back(buf);
         }
-        L3D_CUDA(cudaGetLastError());
-        if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[4], st));
-        // ---- reduce -----------------------------------------------------------------------
-        const unsigned n_cta = unsigned((M_ub + RM_T - 1) / RM_T);
-        L3D_CUDA(sl.d_fcnt.ensure(size_t(n_cta) + 1));                       // kept matches per CTA
-        L3D_CUDA(pdl_launch(k_reduce_matches, dim3(n_cta), dim3(RM_T), 0, st, d_M, sl.d_off.p, n_nb, sl.d_score.p, sl.d_mids.p, d_best, sl.d_fcnt.p, d_iters));
-        d_F = sl.d_foff.p;
-        L3D_CUDA(pdl_launch(k_filter_compact, dim3(n_cta), dim3(RM_T), 0, st, d_M, sl.d_score.p, sl.d_mids.p, sl.d_mdep.p, sl.d_fcnt.p, dfil.p, sl.d_foff.p,
-                            sl.d_cams.p, stride, delivering ? d_hist : nullptr));
-        ctx->launches += 2;
-        L3D_CUDA(cudaGetLastError());
-    } else {
-        if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[4], st));
-        d_F = d_M;
-        if (!scored && M_ub > 0) {
-            L3D_CUDA(pdl_launch(k_copy_unscored, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, sl.d_mids.p, sl.d_mdep.p, d_M, dfil.p));
-            ctx->launches += 1;
-            L3D_CUDA(cudaGetLastError());
+        // the consumed deliveries leave the list; their memory is given back when this view has been collected
+        {
+            std::vector<Delivered>& dl = ctx->delivered[view];
+            for (size_t k = 0; k < consumed.size(); ++k) dl[consumed[k]].from_view = -1;
+            std::vector<Delivered> keep;
+            for (size_t k = 0; k < dl.size(); ++k) if (dl[k].from_view >= 0) keep.push_back(dl[k]);
+            dl.swap(keep);
         }
+        job.active = true;
+        mx_src = std::max(mx_src, n_src); mx_cams = std::max(mx_cams, n_nb); mx_warps = std::max(mx_warps, long(n_src) * n_nb);
+        mx_M = std::max(mx_M, M_ub); mx_cta = std::max(mx_cta, n_cta);
+        if (scored) { any_scored = true; mx_items = std::max(mx_items, max_items); mx_smem = std::max(mx_smem, sm_bytes); }
+        any_window |= scored && windowed; any_quadratic |= quadratic; any_deliver |= delivering;
+    }
+    L3D_CUDA(gr.d_zero.ensure(zero_total + 4));
+    for (int g = 0; g < count; ++g) {
+        VArgs& va = gr.h_args.p[g];
+        va.nitems = gr.d_zero.p + z[g].items; va.iters = reinterpret_cast<unsigned long long*>(gr.d_zero.p + z[g].iters);
+        va.best = reinterpret_cast<unsigned long long*>(gr.d_zero.p + z[g].best); va.hist = gr.d_zero.p + z[g].hist; va.cursor = gr.d_zero.p + z[g].cursor;
+    }
+    if (mx_smem > ctx->score_smem) {
+        L3D_CUDA(cudaFuncSetAttribute(k_score, cudaFuncAttributeMaxDynamicSharedMemorySize, int(mx_smem)));
+        L3D_CUDA(cudaFuncSetAttribute(k_score_window, cudaFuncAttributeMaxDynamicSharedMemorySize, int(mx_smem)));
+        ctx->score_smem = mx_smem;
     }
 
-    // ---- hand-over to later views ---------------------------------------------------------
-    DeliverBuf buf;
-    if (delivering) {
-        buf.refs = n_deliver;
-        L3D_CUDA(cudaMallocAsync(&buf.start, sizeof(int) * (size_t(n_keys) + 2), st));
-        L3D_CUDA(cudaMallocAsync(&buf.tgt, sizeof(int) * std::max<size_t>(M_ub, 1), st));
-        L3D_CUDA(cudaMallocAsync(&buf.dep, sizeof(float4) * std::max<size_t>(M_ub, 1), st));
-        // (the group sizes were counted by k_filter_fill)
-        if (scan_exclusive(&sl, d_hist, buf.start, n_keys)) { ctx->err = sl.err; return 1; }
-        if (M_ub > 0) {
-            // records land in their group in the order of the atomics; the receiving view's k_fill orders them
-            L3D_CUDA(pdl_launch(k_deliver_scatter, dim3(unsigned((M_ub + 255) / 256)), dim3(256), 0, st, dfil.p, d_F, sl.d_cams.p, stride, buf.start, d_cursor, buf.tgt, buf.dep));
-            ctx->launches += 1;
-        }
-        L3D_CUDA(cudaGetLastError());
+    // ---- one upload, one memset, one launch of every kernel for the whole group ------------------------------
+    const unsigned G = unsigned(count);
+    const VArgs* A = gr.d_args.p;
+    L3D_CUDA(cudaMemcpyAsync(gr.d_cams.p, gr.h_cams.p, sizeof(CamTable) * cams_total, cudaMemcpyHostToDevice, st));
+    L3D_CUDA(cudaMemcpyAsync(gr.d_args.p, gr.h_args.p, sizeof(VArgs) * size_t(count), cudaMemcpyHostToDevice, st));
+    L3D_CUDA(cudaMemsetAsync(gr.d_zero.p, 0, sizeof(int) * zero_total, st));
+    if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[2], st));
+    L3D_CUDA(pdl_launch(k_gather_counts, dim3((mx_src + 255) / 256, mx_cams, G), dim3(256), 0, st, A));
+    L3D_CUDA(pdl_launch(k_scan_views, dim3(1, G), dim3(SCAN_T), 0, st, A, 0));
+    L3D_CUDA(pdl_launch(k_fill, dim3(unsigned((mx_warps * 32 + 255) / 256), G), dim3(256), 0, st, A, ctx->d_segs.p));
+    ctx->launches += 3;
+    if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[3], st));
+    if (any_window) {
+        L3D_CUDA(pdl_launch(k_bucket_segments, dim3(mx_src, G), dim3(BK_T), 0, st, A));
+        L3D_CUDA(pdl_launch(k_score_window, dim3(mx_items, G), dim3(SC_T), mx_smem, st, A, ctx->d_segs.p));
+        ctx->launches += 2;
     }
-    // ---- results: one kernel packs them, one copy; the host collects them in finish_view ----------------
-    const int n_res = 8 + std::max(n_deliver, 1);
-    L3D_CUDA(sl.d_vres.ensure(size_t(n_res))); L3D_CUDA(sl.h_vres.ensure(size_t(n_res)));
-    L3D_CUDA(pdl_launch(k_finish_view, dim3(1), dim3(MS_T), 0, st, sl.d_dsamples.p, (scored && M_ub > 0) ? ns : 0, d_best, sl.d_mdep.p, d_M, d_F, (scored && M_ub > 0) ? d_iters : nullptr,
-                        delivering ? buf.start : nullptr, stride, delivering ? n_deliver : 0, sl.d_vres.p));
+    if (any_quadratic) {
+        L3D_CUDA(pdl_launch(k_score_items, dim3((mx_src + 255) / 256, G), dim3(256), 0, st, A));
+        L3D_CUDA(pdl_launch(k_score, dim3(mx_items, G), dim3(SC_T), mx_smem, st, A, ctx->d_segs.p));
+        ctx->launches += 2;
+    }
+    if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[4], st));
+    if (any_scored) { L3D_CUDA(pdl_launch(k_reduce_matches, dim3(mx_cta, G), dim3(RM_T), 0, st, A)); ctx->launches += 1; }
+    L3D_CUDA(pdl_launch(k_filter_compact, dim3(mx_cta, G), dim3(RM_T), 0, st, A));
+    ctx->launches += 1;
+    if (any_deliver) {
+        L3D_CUDA(pdl_launch(k_scan_views, dim3(1, G), dim3(SCAN_T), 0, st, A, 1));
+        L3D_CUDA(pdl_launch(k_deliver_scatter, dim3(unsigned((std::max<size_t>(mx_M, 1) + 255) / 256), G), dim3(256), 0, st, A));
+        ctx->launches += 2;
+    }
+    L3D_CUDA(pdl_launch(k_finish_view, dim3(1, G), dim3(MS_T), 0, st, A));
     ctx->launches += 1;
     L3D_CUDA(cudaGetLastError());
-    if (ctx->stage_events) L3D_CUDA(cudaEventRecord(ev[5], st));
-    L3D_CUDA(cudaMemcpyAsync(sl.h_vres.p, sl.d_vres.p, sizeof(int) * size_t(n_res), cudaMemcpyDeviceToHost, st));
-    L3D_CUDA(cudaEventRecord(ev[0], st));
-    job.M_ub = M_ub; job.scored = scored; job.delivering = delivering; job.n_deliver = n_deliver;
-    // the hand-over records exist from now on (stream order); until this view is collected their sizes are bounds
-    if (delivering) {
-        job.owner = int(ctx->deliver_bufs.size());
-        buf.counts.assign(size_t(n_deliver), 0); buf.maxg.assign(size_t(n_deliver), 0);
-        for (int c = 0; c < n_nb; ++c) {
-            const int d = hc.p[c].deliver;
-            if (d < 0) continue;
-            const uint64_t ub = std::min<uint64_t>(hc.p[c].slot >= 0 ? pa.job_raw[first_job + hc.p[c].slot] : uint64_t(M_ub), 0x7fffffffull);
-            Delivered dl; dl.from_view = view; dl.owner = job.owner; dl.slot = d;
-            dl.count = int(ub); dl.max_group = int(std::min<uint64_t>(ub, uint64_t(n_src)));      // a source segment matches a target segment once
-            dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
-            buf.counts[d] = dl.count; buf.maxg[d] = dl.max_group;
-            ctx->delivered[nb[c].view].push_back(dl);
-        }
-        ctx->deliver_bufs.push_back(buf);
-    }
-    // the consumed deliveries leave the list; their memory is given back when this view has been collected
-    {
-        std::vector<Delivered>& dl = ctx->delivered[view];
-        for (size_t k = 0; k < consumed.size(); ++k) dl[consumed[k]].from_view = -1;
-        std::vector<Delivered> keep;
-        for (size_t k = 0; k < dl.size(); ++k) if (dl[k].from_view >= 0) keep.push_back(dl[k]);
-        dl.swap(keep);
-    }
-    ctx->inflight_slot[view] = int(&sl - ctx->vs);
-    job.active = true;
+    if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[5], st));
+    L3D_CUDA(cudaMemcpyAsync(gr.h_vres.p, gr.d_vres.p, sizeof(int) * size_t(count) * VG_RES, cudaMemcpyDeviceToHost, st));
+    L3D_CUDA(cudaEventRecord(gr.ev[0], st));
     return 0;
 }
 
@@ -1885,65 +1993,82 @@ int arena_take(l3d_ctx* ctx, size_t n, l3d_match** out)
     return 0;
 }
 
-int finish_view(l3d_ctx* ctx, ViewSlot& sl, l3d_match_result* res, bool copy_back)
+// Waits for a group, turns its result records into l3d_match_results (results[plan index], or *single for a view
+// matched outside a schedule) and fetches the output records of all its views with one synchronise.
+int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* single)
 {
-    ViewJob& job = sl.job;
-    job.active = false;
-    L3D_CUDA(cudaEventSynchronize(sl.ev[0]));
-    const int* hr = sl.h_vres.p;
-    memset(res, 0, sizeof *res);
-    res->pair_tests = job.pair_tests; res->n_candidates = job.cand_ub; res->scored = job.scored ? 1 : 0;
-    const int M = hr[0], F = (job.M_ub > 0) ? hr[1] : 0;
-    float median = 1.0f;                              // line3D.cc:811
-    if (job.scored && M > 0) {
-        memcpy(&median, &hr[2], sizeof(float));
-        const unsigned long long all = (unsigned long long)(unsigned)hr[4] | ((unsigned long long)(unsigned)hr[5] << 32);
-        const unsigned long long same = (unsigned long long)(unsigned)hr[6] | ((unsigned long long)(unsigned)hr[7] << 32);
-        res->score_iters = all; res->score_iters_other_cam = all - same;
-    }
-    if (job.delivering) {                              // exact sizes of what this view handed over
-        DeliverBuf& b = ctx->deliver_bufs[job.owner];
-        for (int d = 0; d < job.n_deliver; ++d) { b.counts[d] = hr[8 + d]; b.maxg[d] = std::min(b.maxg[d], hr[8 + d]); }
-        for (size_t c = 0; c < job.nb.size(); ++c) {
-            if (!job.nb[c].deliver) continue;
-            std::vector<Delivered>& dl = ctx->delivered[job.nb[c].view];
-            for (size_t k = 0; k < dl.size(); ++k)
-                if (dl[k].owner == job.owner) { dl[k].count = b.counts[dl[k].slot]; dl[k].max_group = b.maxg[dl[k].slot]; }
-        }
-    }
-    for (size_t k = 0; k < job.consumed.size(); ++k) {
-        DeliverBuf& b = ctx->deliver_bufs[job.consumed[k].first];
-        res->n_delivered += uint64_t(b.counts[job.consumed[k].second]);
-        if (--b.refs == 0) {                           // the last receiver has been collected: nothing on any stream reads it any more
-            cudaFreeAsync(b.start, ctx->stream); cudaFreeAsync(b.tgt, ctx->stream); cudaFreeAsync(b.dep, ctx->stream);
-            b.start = nullptr; b.tgt = nullptr; b.dep = nullptr;
-        }
-    }
-    ctx->inflight_slot[job.view] = -1;
-    ctx->launches += sl.launches; sl.launches = 0;
-    res->n_scored = uint64_t(M);
-    res->n_raw = uint64_t(M) - res->n_delivered;
-    res->median_depth = median;
-    res->n_filtered = uint64_t(F);
-    l3d_match* dst = nullptr;
-    if (copy_back && F > 0) {                          // on its own stream: the next view may already be running
-        if (ctx->retain || ctx->plan_started) { if (arena_take(ctx, size_t(F), &dst)) return 1; }     // results of a schedule are collected ahead of their calls
-        else { L3D_CUDA(ctx->h_filtered.ensure(size_t(F))); dst = ctx->h_filtered.p; }
-        L3D_CUDA(cudaMemcpyAsync(dst, sl.d_filtered.p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, ctx->copy_stream));
-        L3D_CUDA(cudaStreamSynchronize(ctx->copy_stream));
-    }
-    res->filtered = dst;
-    float ms;
-    ctx->last_ms[0] = ctx->last_ms[1] = 0.f;
+    L3D_CUDA(cudaEventSynchronize(gr.ev[0]));
     PhaseASet& pa = ctx->pa[ctx->cur];
+    float ms_a[2] = {0.f, 0.f};
     if (pa.pa_ms_pending) {                            // phase A of a whole batch is booked on the first view collected after it
-        ms = 0.f; cudaEventElapsedTime(&ms, pa.pa_ev[0], pa.pa_ev[1]); ctx->last_ms[0] = ms;
-        ms = 0.f; cudaEventElapsedTime(&ms, pa.pa_ev[1], pa.pa_ev[2]); ctx->last_ms[1] = ms;
-        for (int k = 0; k < 2; ++k) { ms = 0.f; if (pa.pa_kev_set[k]) cudaEventElapsedTime(&ms, pa.pa_kev[2 * k], pa.pa_kev[2 * k + 1]); ctx->pa_kernel_ms[k] = ms; }
+        cudaEventElapsedTime(&ms_a[0], pa.pa_ev[0], pa.pa_ev[1]); cudaEventElapsedTime(&ms_a[1], pa.pa_ev[1], pa.pa_ev[2]);
+        for (int k = 0; k < 2; ++k) { float ms = 0.f; if (pa.pa_kev_set[k]) cudaEventElapsedTime(&ms, pa.pa_kev[2 * k], pa.pa_kev[2 * k + 1]); ctx->pa_kernel_ms[k] = ms; }
         pa.pa_ms_pending = false;
+    } else ctx->pa_kernel_ms[0] = ctx->pa_kernel_ms[1] = 0.f;
+    float ms_b[3] = {0.f, 0.f, 0.f};
+    if (ctx->stage_events) for (int k = 0; k < 3; ++k) cudaEventElapsedTime(&ms_b[k], gr.ev[k + 2], gr.ev[k + 3]);
+    bool copies = false;
+    for (int g = 0; g < gr.count; ++g) {
+        ViewSlot& sl = gr.slot[g];
+        ViewJob& job = sl.job;
+        job.active = false;
+        const int* hr = gr.h_vres.p + size_t(g) * VG_RES;
+        l3d_match_result* res = single ? single : &ctx->results[sl.plan_index].res;
+        memset(res, 0, sizeof *res);
+        res->pair_tests = job.pair_tests; res->n_candidates = job.cand_ub; res->scored = job.scored ? 1 : 0;
+        const int M = hr[0], F = (job.M_ub > 0) ? hr[1] : 0;
+        float median = 1.0f;                              // line3D.cc:811
+        if (job.scored && M > 0) {
+            memcpy(&median, &hr[2], sizeof(float));
+            const unsigned long long all = (unsigned long long)(unsigned)hr[4] | ((unsigned long long)(unsigned)hr[5] << 32);
+            const unsigned long long same = (unsigned long long)(unsigned)hr[6] | ((unsigned long long)(unsigned)hr[7] << 32);
+            res->score_iters = all; res->score_iters_other_cam = all - same;
+        }
+        if (job.delivering) {                              // exact sizes of what this view handed over
+            DeliverBuf& b = ctx->deliver_bufs[job.owner];
+            for (int d = 0; d < job.n_deliver; ++d) { b.counts[d] = hr[8 + d]; b.maxg[d] = std::min(b.maxg[d], hr[8 + d]); }
+            for (size_t c = 0; c < job.nb.size(); ++c) {
+                if (!job.nb[c].deliver) continue;
+                std::vector<Delivered>& dl = ctx->delivered[job.nb[c].view];
+                for (size_t k = 0; k < dl.size(); ++k)
+                    if (dl[k].owner == job.owner) { dl[k].count = b.counts[dl[k].slot]; dl[k].max_group = b.maxg[dl[k].slot]; }
+            }
+        }
+        for (size_t k = 0; k < job.consumed.size(); ++k) {
+            DeliverBuf& b = ctx->deliver_bufs[job.consumed[k].first];
+            res->n_delivered += uint64_t(b.counts[job.consumed[k].second]);
+            if (--b.refs == 0) {                           // the last receiver has been collected: nothing on the GPU reads it any more
+                ctx->pool.put(b.start); ctx->pool.put(b.tgt); ctx->pool.put(b.dep);
+                b.start = nullptr; b.tgt = nullptr; b.dep = nullptr;
+            }
+        }
+        res->n_scored = uint64_t(M);
+        res->n_raw = uint64_t(M) - res->n_delivered;
+        res->median_depth = median;
+        res->n_filtered = uint64_t(F);
+        l3d_match* dst = nullptr;
+        if (copy_back && F > 0) {                          // on its own stream: the next group is already running
+            if (ctx->retain || !single) { if (arena_take(ctx, size_t(F), &dst)) return 1; }      // results of a schedule are collected ahead of their calls
+            else { L3D_CUDA(ctx->h_filtered.ensure(size_t(F))); dst = ctx->h_filtered.p; }
+            L3D_CUDA(cudaMemcpyAsync(dst, sl.d_filtered.p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, ctx->copy_stream));
+            copies = true;
+        }
+        res->filtered = dst;
+        if (!single) {
+            l3d_ctx::Stashed& stash = ctx->results[sl.plan_index];
+            memset(stash.ms, 0, sizeof stash.ms); stash.kms[0] = stash.kms[1] = 0.f;
+            if (g == 0) {                                  // the group's device times are booked on its first view
+                stash.ms[0] = ms_a[0]; stash.ms[1] = ms_a[1]; stash.ms[2] = ms_b[0]; stash.ms[3] = ms_b[1]; stash.ms[4] = ms_b[2];
+                stash.ms[5] = ms_a[0] + ms_a[1] + ms_b[0] + ms_b[1] + ms_b[2];
+                stash.kms[0] = ctx->pa_kernel_ms[0]; stash.kms[1] = ctx->pa_kernel_ms[1];
+            }
+            stash.ready = true;
+        } else {
+            ctx->last_ms[0] = ms_a[0]; ctx->last_ms[1] = ms_a[1]; ctx->last_ms[2] = ms_b[0]; ctx->last_ms[3] = ms_b[1]; ctx->last_ms[4] = ms_b[2];
+            ctx->last_ms[5] = ms_a[0] + ms_a[1] + ms_b[0] + ms_b[1] + ms_b[2];
+        }
     }
-    for (int k = 2; k < 5; ++k) { ms = 0.f; if (ctx->stage_events) cudaEventElapsedTime(&ms, sl.ev[k], sl.ev[k + 1]); ctx->last_ms[k] = ms; }
-    ctx->last_ms[5] = ctx->last_ms[0] + ctx->last_ms[1] + ctx->last_ms[2] + ctx->last_ms[3] + ctx->last_ms[4];
+    if (copies) L3D_CUDA(cudaStreamSynchronize(ctx->copy_stream));
     return 0;
 }
 
@@ -1953,8 +2078,8 @@ int join_worker(l3d_ctx* ctx);
 void drain_pending(l3d_ctx* ctx)
 {
     join_worker(ctx);
-    while (ctx->fly_begin < ctx->fly_end) { l3d_match_result dummy; finish_view(ctx, ctx->vs[ctx->fly_begin % VS_W], &dummy, false); ++ctx->fly_begin; }
-    ctx->fly_begin = ctx->fly_end = 0;
+    while (ctx->grp_begin < ctx->grp_end) { ViewGroup& gr = ctx->grp[ctx->grp_begin % 2]; finish_group(ctx, gr, false, nullptr); ctx->fly_begin += size_t(gr.count); ++ctx->grp_begin; }
+    ctx->fly_begin = ctx->fly_end = 0; ctx->grp_begin = ctx->grp_end = 0;
 }
 
 // The batch of the announced schedule that starts at position `from` of the execution order: its job list, and
@@ -2015,13 +2140,19 @@ int top_up(l3d_ctx* ctx)
         ctx->launches += set.launches; set.launches = 0;
         if (ctx->batch_end < ctx->order.size()) start_worker(ctx, ctx->batch_end);      // the following batch, meanwhile
     }
-    const size_t depth = ctx->stage_events ? 1 : size_t(VS_W);      // per-stage timing wants one view at a time
-    while (ctx->fly_end < ctx->batch_end && ctx->fly_end - ctx->fly_begin < depth) {
-        PlannedView& pv = ctx->plan[ctx->order[ctx->fly_end]];
-        ViewSlot& sl = ctx->vs[ctx->fly_end % VS_W];
-        sl.stream = ctx->vstream[ctx->fly_end % VS_S];
-        if (enqueue_view(ctx, pv.view, int(pv.nb.size()), pv.nb.data(), ctx->run_sigma_p, ctx->run_sigma_a, pv.first_job, sl)) return 1;
-        ++ctx->fly_end;
+    // the next groups: consecutive views of one dependency level, two groups in flight
+    while (ctx->fly_end < ctx->batch_end && ctx->grp_end - ctx->grp_begin < 2) {
+        GroupView gv[VG_MAX]; int count = 0;
+        const int lvl = ctx->level[ctx->order[ctx->fly_end]];
+        while (count < VG_MAX && ctx->fly_end + size_t(count) < ctx->batch_end && ctx->level[ctx->order[ctx->fly_end + size_t(count)]] == lvl) {
+            PlannedView& pv = ctx->plan[ctx->order[ctx->fly_end + size_t(count)]];
+            GroupView v = {pv.view, int(pv.nb.size()), pv.nb.data(), pv.first_job, ctx->order[ctx->fly_end + size_t(count)]};
+            gv[count++] = v;
+        }
+        ViewGroup& gr = ctx->grp[ctx->grp_end % 2];
+        gr.pos0 = ctx->fly_end;
+        if (enqueue_group(ctx, gr, gv, count, ctx->run_sigma_p, ctx->run_sigma_a)) return 1;
+        ctx->fly_end += size_t(count); ++ctx->grp_end;
     }
     return 0;
 }
@@ -2045,13 +2176,11 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         const size_t p = ctx->call_next;
         while (!ctx->results[p].ready) {
             if (top_up(ctx)) { drain_pending(ctx); return 1; }
-            if (ctx->fly_begin >= ctx->fly_end) { ctx->err = "l3d_match_view: internal error (schedule exhausted)"; return 1; }
-            const size_t q = ctx->order[ctx->fly_begin];
-            const int rc = finish_view(ctx, ctx->vs[ctx->fly_begin % VS_W], &ctx->results[q].res, ctx->run_copy_back);
-            ++ctx->fly_begin;
+            if (ctx->grp_begin >= ctx->grp_end) { ctx->err = "l3d_match_view: internal error (schedule exhausted)"; return 1; }
+            ViewGroup& gr = ctx->grp[ctx->grp_begin % 2];
+            const int rc = finish_group(ctx, gr, ctx->run_copy_back, nullptr);
+            ctx->fly_begin += size_t(gr.count); ++ctx->grp_begin;
             if (rc) { drain_pending(ctx); return 1; }
-            ctx->results[q].ready = true;
-            memcpy(ctx->results[q].ms, ctx->last_ms, sizeof ctx->last_ms); memcpy(ctx->results[q].kms, ctx->pa_kernel_ms, sizeof ctx->pa_kernel_ms);
         }
         *res = ctx->results[p].res;
         memcpy(ctx->last_ms, ctx->results[p].ms, sizeof ctx->last_ms); memcpy(ctx->pa_kernel_ms, ctx->results[p].kms, sizeof ctx->pa_kernel_ms);
@@ -2068,10 +2197,9 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     PhaseASet& set = ctx->pa[ctx->cur];
     if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
     ctx->launches += set.launches; set.launches = 0;
-    ViewSlot& sl = ctx->vs[0];
-    sl.stream = ctx->vstream[0];
-    if (enqueue_view(ctx, view, n_nb, nb, sigma_p, sigma_a, 0, sl)) return 1;
-    return finish_view(ctx, sl, res, copy_back);
+    GroupView one = {view, n_nb, nb, 0, 0};
+    if (enqueue_group(ctx, ctx->grp[0], &one, 1, sigma_p, sigma_a)) return 1;
+    return finish_group(ctx, ctx->grp[0], copy_back, res);
 }
 
 }  // namespace
@@ -2101,10 +2229,7 @@ int l3d_create(int device, l3d_ctx** out)
         if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
     }
     for (int k = 0; k < 8; ++k) cudaEventCreate(&ctx->ev[k]);
-    for (int q = 0; q < VS_S; ++q)
-        if ((e = cudaStreamCreateWithPriority(&ctx->vstream[q], cudaStreamNonBlocking, prio_hi)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); l3d_destroy(ctx); return 1; }
-    for (int q = 0; q < VS_W; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->vs[q].ev[k]);
-    cudaEventCreateWithFlags(&ctx->join_ev, cudaEventDisableTiming);
+    for (int q = 0; q < 2; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->grp[q].ev[k]);
     if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); cudaStreamDestroy(ctx->stream); delete ctx; return 1; }
     for (int q = 0; q < 2; ++q) {
         PhaseASet& set = ctx->pa[q];
@@ -2123,12 +2248,9 @@ int l3d_reset_matching(l3d_ctx* ctx)
     cudaSetDevice(ctx->device);
     drain_pending(ctx);
     for (size_t v = 0; v < ctx->delivered.size(); ++v) ctx->delivered[v].clear();
-    for (size_t k = 0; k < ctx->deliver_bufs.size(); ++k) {          // handed over and never taken, or not yet given back
-        DeliverBuf& b = ctx->deliver_bufs[k];
-        if (b.start) { cudaFreeAsync(b.start, ctx->stream); cudaFreeAsync(b.tgt, ctx->stream); cudaFreeAsync(b.dep, ctx->stream); }
-    }
     ctx->deliver_bufs.clear();
-    ctx->inflight_slot.assign(size_t(std::max(ctx->V, 0)), -1);
+    ctx->pool.put_all();                                 // hand-over buffers never taken, or not yet given back
+    ctx->level.clear();
     ctx->plan.clear(); ctx->order.clear(); ctx->results.clear(); ctx->call_next = 0; ctx->plan_started = false; ctx->batch_begin = ctx->batch_end = 0; ctx->fly_begin = ctx->fly_end = 0;
     ctx->arena_chunk = 0; ctx->arena_used = 0;           // retained results are given up, their memory is reused
     cudaStreamSynchronize(ctx->stream);
@@ -2142,9 +2264,7 @@ void l3d_destroy(l3d_ctx* ctx)
     l3d_reset_matching(ctx);
     ctx->d_segs.release(); ctx->d_viewd.release(); ctx->pa[0].release(); ctx->pa[1].release();
     ctx->d_tile_sums.release(); ctx->d_total.release();
-    for (int q = 0; q < VS_W; ++q) ctx->vs[q].release();
-    for (int q = 0; q < VS_S; ++q) if (ctx->vstream[q]) cudaStreamDestroy(ctx->vstream[q]);
-    if (ctx->join_ev) cudaEventDestroy(ctx->join_ev);
+    ctx->grp[0].release(); ctx->grp[1].release(); ctx->pool.release();
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (size_t k = 0; k < ctx->arena.size(); ++k) cudaFreeHost(ctx->arena[k].first);
     ctx->d_res.release(); ctx->d_zero.release();
@@ -2244,7 +2364,6 @@ int l3d_set_views(l3d_ctx* ctx, int n_views, const l3d_view* views)
     L3D_CUDA(cudaSetDevice(ctx->device));
     l3d_reset_matching(ctx);
     ctx->V = n_views;
-    ctx->inflight_slot.assign(size_t(n_views), -1);
     ctx->views.assign(views, views + n_views);
     ctx->seg_off.assign(size_t(n_views) + 1, 0);
     ctx->max_seg = 0;
@@ -2304,6 +2423,7 @@ int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
                 const int to = at[nbr.view];
                 if (nbr.deliver && to > int(k)) level[to] = std::max(level[to], level[k] + 1);
             }
+        ctx->level = level;
         ctx->order.resize(n);
         for (size_t k = 0; k < n; ++k) ctx->order[k] = k;
         std::stable_sort(ctx->order.begin(), ctx->order.end(), [&level](size_t a, size_t b) { return level[a] < level[b]; });
@@ -2471,11 +2591,7 @@ int l3d_mark(l3d_ctx* ctx, int which)
 {
     if (!ctx || which < 0 || which > 1) return 1;
     L3D_CUDA(cudaSetDevice(ctx->device));
-    for (int q = 0; q < VS_S; ++q) {                 // the mark comes after (before) everything on the view streams too
-        if (which == 1) { L3D_CUDA(cudaEventRecord(ctx->join_ev, ctx->vstream[q])); L3D_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->join_ev, 0)); }
-    }
     L3D_CUDA(cudaEventRecord(ctx->mark_ev[which], ctx->stream));
-    if (which == 0) for (int q = 0; q < VS_S; ++q) L3D_CUDA(cudaStreamWaitEvent(ctx->vstream[q], ctx->mark_ev[0], 0));
     return 0;
 }
 
