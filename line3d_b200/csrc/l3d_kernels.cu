@@ -2435,6 +2435,7 @@ int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
     uint64_t total = 0;
     for (size_t k = 0; k < ctx->plan.size(); ++k) total += ctx->plan[k].pair_tests;
     ctx->batch_pairs = ctx->batch_override ? ctx->batch_override : std::min<uint64_t>(ctx->pair_budget, std::max<uint64_t>(total / 8, 250000000ull));
+    if (ctx->stage_events && !ctx->batch_override) ctx->batch_pairs = ctx->pair_budget;      // per-stage timing: nothing runs beside anything else
     return 0;
 }
 
