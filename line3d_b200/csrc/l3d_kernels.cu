@@ -867,8 +867,10 @@ __device__ __forceinline__ void b_score_window(const float4* __restrict__ segs, 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int y = item.y * SC_T + tid;
     const bool live = y < M;
-    int my_cam = -1; float2 my_d = make_float2(0.f, 0.f);
-    if (live) { my_cam = m_ids[seg_start + y].y; float4 d = m_dep[seg_start + y]; my_d = make_float2(d.x, d.y); }
+    // thread y takes the y-th match in BUCKET order: the lanes of a warp then hold neighbouring depths, their windows
+    // overlap (coalesced loads) and are about equally long (little divergence in the scan below)
+    int my_cam = -1, my_idx = 0; float2 my_d = make_float2(0.f, 0.f);
+    if (live) { const unsigned pl = g_pl[seg_start + y]; my_cam = int(pl >> 20); my_idx = int(pl & 0xfffffu); my_d = make_float2(g_k[seg_start + y], g_d2[seg_start + y]); }
     s_yd[tid] = my_d;
     for (int c = 0; c < n_cams; ++c) s_max[c * SC_T + tid] = 0;
     const float4 sg = segs[src.seg_off + row];
@@ -917,7 +919,7 @@ __device__ __forceinline__ void b_score_window(const float4* __restrict__ segs, 
     if (live) {        // sum of the per-camera best confidences in camera order (cudawrapper.cu:677-687, 709)
         float total = 0.0f;
         for (int c = 0; c < n_cams; ++c) total = xa(total, __int_as_float(s_max[c * SC_T + tid]));
-        score[seg_start + y] = total;
+        score[seg_start + my_idx] = total;
     }
 }
 
