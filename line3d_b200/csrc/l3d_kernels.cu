@@ -1160,7 +1160,7 @@ __global__ void __launch_bounds__(BK_T) k_bucket_segments(const VArgs* __restric
     if (!va.scored || !va.windowed || int(blockIdx.x) >= va.n_src) return;
     b_bucket_segments(va.off, va.n_cams, va.mids, va.mdep, va.sk, va.sd2, va.spl, va.boff, va.brange, va.m_hi, SC_T, va.nitems, va.items);
 }
-__global__ void __launch_bounds__(SC_T) k_score_window(const VArgs* __restrict__ all, const float4* __restrict__ segs)
+__global__ void __launch_bounds__(SC_T, 12) k_score_window(const VArgs* __restrict__ all, const float4* __restrict__ segs)
 {
     L3D_VIEW(y);
     if (!va.scored || !va.windowed) return;
