@@ -1498,13 +1498,12 @@ struct ViewSlot {
         d_dsamples.release(); d_sk.release(); d_sd2.release(); d_spl.release(); d_items.release(); d_brange.release(); d_filtered.release();
     }
 };
-constexpr int VG_RES = 8 + 64;           // result ints per view: 8 scalars + one count per hand-over slot (checked against n_deliver)
 struct ViewGroup {
     int count = 0; size_t pos0 = 0;      // positions [pos0, pos0 + count) of the execution order
     ViewSlot slot[VG_MAX];
     HBuf<VArgs> h_args; DBuf<VArgs> d_args;
     HBuf<CamTable> h_cams; DBuf<CamTable> d_cams; size_t cam_off[VG_MAX + 1];
-    DBuf<int> d_zero; DBuf<int> d_vres; HBuf<int> h_vres;
+    DBuf<int> d_zero; DBuf<int> d_vres; HBuf<int> h_vres; int res_stride = 8;     // result ints per view: 8 scalars + one count per hand-over slot
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [0] results on the host, [2..5] stage boundaries
     void release()
     {
@@ -1788,7 +1787,10 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     PhaseASet& pa = ctx->pa[ctx->cur];
     gr.count = count;
     L3D_CUDA(gr.h_args.ensure(VG_MAX)); L3D_CUDA(gr.d_args.ensure(VG_MAX));
-    L3D_CUDA(gr.d_vres.ensure(size_t(VG_MAX) * VG_RES)); L3D_CUDA(gr.h_vres.ensure(size_t(VG_MAX) * VG_RES));
+    int res_stride = 8;
+    for (int g = 0; g < count; ++g) { int nd = 0; for (int c = 0; c < gv[g].n_nb; ++c) nd += gv[g].nb[c].deliver ? 1 : 0; res_stride = std::max(res_stride, 8 + nd); }
+    gr.res_stride = res_stride;
+    L3D_CUDA(gr.d_vres.ensure(size_t(VG_MAX) * res_stride)); L3D_CUDA(gr.h_vres.ensure(size_t(VG_MAX) * res_stride));
     size_t cams_total = 0;
     for (int g = 0; g < count; ++g) {
         if (gv[g].view < 0 || gv[g].view >= ctx->V) { ctx->err = "l3d_match_view: view index out of range"; return 1; }
@@ -1846,7 +1848,6 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
             }
             if (n.deliver) { ct.deliver = n_deliver++; max_deliver_seg = std::max(max_deliver_seg, tv.n_segments); }
         }
-        if (n_deliver > VG_RES - 8) { ctx->err = "l3d_match_view: more than 64 neighbours ask for this view's matches"; return 1; }
         job.pair_tests = pair_tests; job.cand_ub = cand_ub;
         const size_t M_ub = size_t(raw_ub + delivered_ub);          // upper bound on the number of matches to score
         const bool scored = n_slots > 0;                             // cudawrapper.cu:877-878
@@ -1897,7 +1898,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         va.cta_kept = sl.d_cta.p; va.n_cta = n_cta; va.Fout = sl.d_F.p; va.filtered = sl.d_filtered.p; va.dsamples = sl.d_dsamples.p;
         va.delivering = delivering ? 1 : 0; va.stride = stride; va.n_keys = n_keys; va.n_deliver = n_deliver;
         va.dl_start = buf.start; va.dl_tgt = buf.tgt; va.dl_dep = buf.dep;
-        va.vres = gr.d_vres.p + size_t(g) * VG_RES;
+        va.vres = gr.d_vres.p + size_t(g) * res_stride;
         // the hand-over records exist from now on (stream order); until this view is collected their sizes are bounds
         if (delivering) {
             job.owner = int(ctx->deliver_bufs.size());
@@ -1975,7 +1976,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     ctx->launches += 1;
     L3D_CUDA(cudaGetLastError());
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[5], st));
-    L3D_CUDA(cudaMemcpyAsync(gr.h_vres.p, gr.d_vres.p, sizeof(int) * size_t(count) * VG_RES, cudaMemcpyDeviceToHost, st));
+    L3D_CUDA(cudaMemcpyAsync(gr.h_vres.p, gr.d_vres.p, sizeof(int) * size_t(count) * res_stride, cudaMemcpyDeviceToHost, st));
     L3D_CUDA(cudaEventRecord(gr.ev[0], st));
     return 0;
 }
@@ -2014,7 +2015,7 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
         ViewSlot& sl = gr.slot[g];
         ViewJob& job = sl.job;
         job.active = false;
-        const int* hr = gr.h_vres.p + size_t(g) * VG_RES;
+        const int* hr = gr.h_vres.p + size_t(g) * gr.res_stride;
         l3d_match_result* res = single ? single : &ctx->results[sl.plan_index].res;
         memset(res, 0, sizeof *res);
         res->pair_tests = job.pair_tests; res->n_candidates = job.cand_ub; res->scored = job.scored ? 1 : 0;
