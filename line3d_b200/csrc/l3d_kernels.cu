@@ -2,20 +2,21 @@
 // Line3D matching-and-scoring path.  Written from scratch for B200; the reference's
 // cudawrapper.cu is cited only for the semantics each stage must reproduce.
 //
-// Per view v (l3d_match_view), everything stays on the device:
+// Everything stays on the device.  Pair tests (phase A) run per batch of views, the rest (phase B) per group of
+// views of one dependency level (see VArgs); DESIGN.md section 4 has the scheduling.
 //
-//   hoist      per neighbour, per segment: epipolar lines of the endpoints (FP64 -> FP32)
-//   pre-test   every (src, tgt) pair: conservative interval test on the four epipolar
-//              residuals q_m^T F p_n  -> 1 candidate bit per pair          [FP32-pipe bound]
+//   hoist      per pair-tested (view, neighbour), per segment: epipolar lines of the endpoints (FP64 -> FP32)
+//   pre-test   every (src, tgt) pair: conservative tests on the four epipolar residuals
+//              q_m^T F p_n  -> 1 candidate bit per pair                   [FP32 issue bound]
 //   exact      candidates only: the reference's arithmetic, bit for bit   (l3d_device.cuh)
 //   assemble   count -> scan -> fill: the view's match list in the reference's canonical
 //              (src, cam, tgt) order, new raw matches merged with the reversed records
 //              that earlier views delivered -- no sort, no host round trip
-//   score      every match against every other match of its source segment: a 2-compare
-//              depth gate that is a superset of the reference's 3-D gate, exact
-//              evaluation of the survivors through a per-warp queue   [LDS/ALU bound]
+//   score      matches of a segment are bucketed by depth; every match looks for supporters in the
+//              buckets its depth window touches: a 2-compare depth gate that is a superset of the
+//              reference's 3-D gate, exact evaluation of the survivors through a per-warp queue
 //   reduce     best match per segment, median depth, filter (score > 1), and the
-//              reversed hand-over lists for later views, transposed on the device
+//              reversed hand-over lists for later views, regrouped on the device
 //
 // Tensor cores are not used: nothing here is a dense contraction.
 #include "../../include/l3d_b200.h"
@@ -1598,7 +1599,6 @@ struct l3d_ctx {
     uint64_t batch_pairs = 24000000000ull;          // pair tests per batch of the announced schedule (l3d_plan_matching)
     uint64_t batch_override = 0;                    // l3d_debug_set_batch_pairs
     float pa_kernel_ms[2] = {0.f, 0.f};
-    DBuf<int> d_res, d_zero;
     // views in flight: positions [fly_begin, fly_end) of `order` are on the GPU, as the groups [grp_begin, grp_end)
     ViewGroup grp[2]; size_t grp_begin = 0, grp_end = 0;
     size_t fly_begin = 0, fly_end = 0; std::vector<int> level;
@@ -1609,8 +1609,7 @@ struct l3d_ctx {
     cudaEvent_t mark_ev[2] = {nullptr, nullptr};
     // retained results (l3d_retain_results): pinned chunks that are never moved, handed out front to back
     bool retain = false; std::vector<std::pair<l3d_match*, size_t> > arena; size_t arena_chunk = 0, arena_used = 0;
-    DBuf<int> d_hist, d_hstart, d_cursor;
-    HBuf<l3d_match> h_filtered; HBuf<int> h_ints; HBuf<float> h_floats; HBuf<unsigned long long> h_u64;
+    HBuf<l3d_match> h_filtered; HBuf<int> h_ints;
     // collinearity
     DBuf<float4> d_csegs; DBuf<unsigned> d_cbits; DBuf<int> d_ccnt, d_coff; DBuf<l3d_collin_pair> d_cpairs; HBuf<l3d_collin_pair> h_cpairs;
     // hypotheses
@@ -1618,7 +1617,7 @@ struct l3d_ctx {
     DBuf<l3d_pair> d_pairs; DBuf<float> d_aff, d_medians;
     DBuf<unsigned char> d_flush; int flush_value = 0;
     // timing
-    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[2] = {nullptr, nullptr};          // around the FP32 peak probe
     float last_ms[6] = {0, 0, 0, 0, 0, 0};
 };
 
@@ -2231,7 +2230,7 @@ int l3d_create(int device, l3d_ctx** out)
         cudaMemPool_t pool; unsigned long long keep = ~0ull;
         if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
     }
-    for (int k = 0; k < 8; ++k) cudaEventCreate(&ctx->ev[k]);
+    for (int k = 0; k < 2; ++k) cudaEventCreate(&ctx->ev[k]);
     for (int q = 0; q < 2; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->grp[q].ev[k]);
     if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); cudaStreamDestroy(ctx->stream); delete ctx; return 1; }
     for (int q = 0; q < 2; ++q) {
@@ -2270,13 +2269,11 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->grp[0].release(); ctx->grp[1].release(); ctx->pool.release();
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (size_t k = 0; k < ctx->arena.size(); ++k) cudaFreeHost(ctx->arena[k].first);
-    ctx->d_res.release(); ctx->d_zero.release();
     for (int k = 0; k < 2; ++k) if (ctx->mark_ev[k]) cudaEventDestroy(ctx->mark_ev[k]);
-    ctx->d_hist.release(); ctx->d_hstart.release(); ctx->d_cursor.release();
-    ctx->h_filtered.release(); ctx->h_ints.release(); ctx->h_floats.release(); ctx->h_u64.release();
+    ctx->h_filtered.release(); ctx->h_ints.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
     ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release();
-    for (int k = 0; k < 8; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+    for (int k = 0; k < 2; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -2637,11 +2634,11 @@ int l3d_measure_fp32_peak(l3d_ctx* ctx, float* tflops)
     k_fma_probe<<<blocks, threads, 0, ctx->stream>>>(d, 1024);
     float best = 0.f;
     for (int r = 0; r < 3; ++r) {
-        L3D_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
+        L3D_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
         k_fma_probe<<<blocks, threads, 0, ctx->stream>>>(d, iters);
-        L3D_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+        L3D_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
         L3D_CUDA(cudaStreamSynchronize(ctx->stream));
-        float ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[7]);
+        float ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
         double fl = double(blocks) * threads * double(iters) * 8.0 * 2.0;
         best = std::max(best, float(fl / (double(ms) * 1e-3) / 1e12));
     }
