@@ -810,12 +810,20 @@ struct Line3D::Impl
         std::map<unsigned, std::vector<int> > clusters; std::map<unsigned, std::set<unsigned> > cams;
         for (int n = 0; n < n_nodes; ++n) { unsigned cl = unsigned(find(n)); clusters[cl].push_back(hyp_of_node[n]); cams[cl].insert(hyps[hyp_of_node[n]].cam); }
         if (verbose) std::cout << prefix << "#clusters_total:  " << clusters.size() << std::endl;
+        // the clusters are independent (alignCluster only reads shared state): fitted on all cores, emitted in map order
         unsigned valid = 0;
-        for (std::map<unsigned, std::vector<int> >::iterator c = clusters.begin(); c != clusters.end(); ++c) {
-            if (cams[c->first].size() < 4) continue;
-            std::list<L3DSegment2D> s2; std::list<std::pair<V3, V3> > s3;
-            alignCluster(c->second, s3, s2);
-            if (!s3.empty()) { result.push_back(L3DFinalLine3D(s2, s3)); ++valid; }
+        {
+            std::vector<const std::vector<int>*> todo;
+            for (std::map<unsigned, std::vector<int> >::iterator c = clusters.begin(); c != clusters.end(); ++c)
+                if (cams[c->first].size() >= 4) todo.push_back(&c->second);
+            std::vector<std::list<L3DSegment2D> > s2(todo.size()); std::vector<std::list<std::pair<V3, V3> > > s3(todo.size());
+            auto work = [&](size_t t0, size_t step) { for (size_t k = t0; k < todo.size(); k += step) alignCluster(*todo[k], s3[k], s2[k]); };
+            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), todo.size()));
+            std::vector<std::thread> pool;
+            for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t, nt);
+            work(0, nt);
+            for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
+            for (size_t k = 0; k < todo.size(); ++k) if (!s3[k].empty()) { result.push_back(L3DFinalLine3D(s2[k], s3[k])); ++valid; }
         }
         if (verbose) std::cout << prefix << "#clusters_valid:  " << valid << std::endl;
         stats.t_lines += now_s() - tl;
