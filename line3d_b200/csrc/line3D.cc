@@ -656,74 +656,101 @@ struct Line3D::Impl
             if (seg >= view_at[vidx]->segs.size()) return false;
             out = view_base[vidx] + seg; return true;
         };
-        // Set of unordered segment pairs already looked at (line3D.cc:980, 1001-1005).  Pairs only ever join segments of
-        // two neighbouring views (or of one view), so the set is kept as one bit matrix per view pair, created on first
-        // use and dropped once the later of its two views has had its turns: a few MB are live at any time and the
-        // accesses are nearly sequential, where a hash set of 10^7..10^8 keys misses the caches on every probe.
-        struct PairBits { std::vector<uint64_t> w; size_t pitch; };
-        std::map<uint64_t, PairBits> bitmaps;                     // key = min view index * V + max view index
-        std::vector<std::vector<uint64_t> > drop_after(view_at.size());
-        std::vector<PairBits*> cur_bits(view_at.size(), (PairBits*)0);
-        int cur_view = -1;
-        const uint64_t nviews = view_at.size();
-        auto enter_view = [&](int v) {
-            if (v == cur_view) return;
-            if (cur_view >= 0) { for (size_t k = 0; k < drop_after[cur_view].size(); ++k) bitmaps.erase(drop_after[cur_view][k]); drop_after[cur_view].clear(); }
-            std::fill(cur_bits.begin(), cur_bits.end(), (PairBits*)0);
-            cur_view = v;
-        };
-        auto mark = [&](int sv, unsigned sseg, int tv, unsigned tseg) -> bool {   // true if the pair was new
-            PairBits*& pb = cur_bits[tv];
-            const int lo = std::min(sv, tv), hi = std::max(sv, tv);
-            if (!pb) {
-                const uint64_t key = uint64_t(lo) * nviews + uint64_t(hi);
-                std::map<uint64_t, PairBits>::iterator f = bitmaps.find(key);
-                if (f == bitmaps.end()) {
-                    PairBits nb; nb.pitch = (view_at[hi]->segs.size() + 63) / 64; nb.w.assign(view_at[lo]->segs.size() * nb.pitch, 0);
-                    f = bitmaps.insert(std::make_pair(key, PairBits())).first; f->second.w.swap(nb.w); f->second.pitch = nb.pitch;
-                    drop_after[hi].push_back(key);
-                }
-                pb = &f->second;
+        // Set of unordered segment pairs already looked at (line3D.cc:980, 1001-1005): a pair is dealt with at its first
+        // encounter, whether or not it passes.  Pairs only ever join a segment of the view whose turn it is (the source)
+        // with a segment of a neighbouring view or of the same view, so the set is one bit matrix per view pair, and the
+        // matrix of views (lo, hi) is written during lo's turns and again during hi's turns, by nobody else.  That makes
+        // the views' turns independent but for one thing -- what lo marked before hi starts:
+        //   phase 1  every view v, in parallel: its turns restricted to targets in LATER views w; the pairs it marks
+        //            there (on matrices that start empty) are kept as a list T(v, w);
+        //   phase 2  every view v, in parallel: all its turns in order with private matrices -- those of earlier views
+        //            w start from T(w, v), the others empty -- emitting the candidates.
+        // The per-view candidate lists, concatenated in view order, are the sequential loop's list.
+        const int nviews = int(view_at.size());
+        std::vector<size_t> h_begin(size_t(nviews) + 1, 0);
+        {   // hypotheses are ordered by (camera id, segment): one contiguous range per view, in view order
+            std::vector<size_t> cnt(size_t(nviews), 0), first(size_t(nviews), hyps.size());
+            for (size_t hidx = 0; hidx < hyps.size(); ++hidx) {
+                int svi; uint64_t d; if (!dense(hyps[hidx].cam, hyps[hidx].seg, svi, d)) continue;
+                if (cnt[svi]++ == 0) first[svi] = hidx;
             }
-            unsigned r, c;                                          // row: segment of the lower view, column: of the higher
-            if (sv < tv) { r = sseg; c = tseg; } else if (sv > tv) { r = tseg; c = sseg; } else { r = std::min(sseg, tseg); c = std::max(sseg, tseg); }
-            uint64_t& word = pb->w[size_t(r) * pb->pitch + (c >> 6)];
-            const uint64_t bit = uint64_t(1) << (c & 63);
-            if (word & bit) return false;
-            word |= bit; return true;
-        };
-        std::vector<size_t> cursor(view_at.size(), 0);
-        for (size_t hidx = 0; hidx < hyps.size(); ++hidx) {
-            const Hypothesis& C = hyps[hidx];
-            int svi; uint64_t dsrc; if (!dense(C.cam, C.seg, svi, dsrc)) continue;
-            enter_view(svi);
-            const std::vector<PC>& list = pc[svi];
-            size_t& cur = cursor[svi];
-            while (cur < list.size() && list[cur].seg < C.seg) ++cur;
-            for (size_t k = cur; k < list.size() && list[k].seg == C.seg; ++k) {                                                    // :996-1138
-                const unsigned tcam = list[k].tcam, tseg = list[k].tseg;
-                int tvi; uint64_t dt; if (!dense(tcam, tseg, tvi, dt)) continue;
-                if (!mark(svi, C.seg, tvi, tseg)) continue;
-                const int ht = hyp_of[tvi][tseg];
-                if (ht < 0) continue;                                                                                               // :1007
-                Cand c = {int(hidx), ht, 1.0f, L3D_MIN_AFFINITY}; cands.push_back(c);                                               // :1014-1016
-                const std::vector<CollinEntry>& cl = view_at[tvi]->collin[tseg];                                                    // :1065-1135
-                for (size_t e = 0; e < cl.size(); ++e) {
-                    if (!mark(svi, C.seg, tvi, cl[e].other)) continue;
-                    const int hc = hyp_of[tvi][cl[e].other];
-                    if (hc < 0) continue;
-                    Cand c3 = {int(hidx), hc, 1.0f, 0.01f}; cands.push_back(c3);                                                    // :1085-1087
-                }
-            }
-            const std::vector<CollinEntry>& cs = view_at[svi]->collin[C.seg];                                                       // :1141-1214
-            for (size_t e = 0; e < cs.size(); ++e) {
-                if (!mark(svi, C.seg, svi, cs[e].other)) continue;
-                const int hc = hyp_of[svi][cs[e].other];
-                if (hc < 0) continue;
-                Cand c2 = {int(hidx), hc, cs[e].w, 0.01f}; cands.push_back(c2);                                                     // :1163-1165
-            }
+            for (int v = 0; v < nviews; ++v) h_begin[v] = first[v];
+            h_begin[nviews] = hyps.size();
+            for (int v = nviews - 1; v >= 0; --v) if (cnt[v] == 0) h_begin[v] = h_begin[v + 1];
         }
-        bitmaps.clear();
+        std::vector<std::map<int, std::vector<uint32_t> > > touched(static_cast<size_t>(nviews));      // T(v, w), keys (seg of v) << 16 | seg of w
+        std::vector<std::vector<Cand> > cands_of(static_cast<size_t>(nviews));
+        auto run_pass = [&](int v, bool emit) {
+            std::vector<std::vector<uint64_t> > bm(static_cast<size_t>(nviews)); std::vector<size_t> pitch(size_t(nviews), 0);
+            auto mark = [&](unsigned sseg, int tv, unsigned tseg) -> bool {   // true if the pair was new
+                const int lo = std::min(v, tv), hi = std::max(v, tv);
+                std::vector<uint64_t>& w = bm[tv];
+                if (w.empty()) {
+                    pitch[tv] = (view_at[hi]->segs.size() + 63) / 64;
+                    w.assign(std::max<size_t>(view_at[lo]->segs.size() * pitch[tv], 1), 0);
+                    if (emit && tv < v) {                             // what the earlier view marked during its own turns
+                        std::map<int, std::vector<uint32_t> >::const_iterator f = touched[tv].find(v);
+                        if (f != touched[tv].end())
+                            for (size_t k = 0; k < f->second.size(); ++k) { const uint32_t key = f->second[k]; w[size_t(key >> 16) * pitch[tv] + ((key & 0xffffu) >> 6)] |= uint64_t(1) << (key & 63u); }
+                    }
+                }
+                unsigned r, c;                                          // row: segment of the lower view, column: of the higher
+                if (v < tv) { r = sseg; c = tseg; } else if (v > tv) { r = tseg; c = sseg; } else { r = std::min(sseg, tseg); c = std::max(sseg, tseg); }
+                uint64_t& word = w[size_t(r) * pitch[tv] + (c >> 6)];
+                const uint64_t bit = uint64_t(1) << (c & 63);
+                if (word & bit) return false;
+                word |= bit;
+                if (!emit) touched[v][tv].push_back((uint32_t(sseg) << 16) | uint32_t(tseg));
+                return true;
+            };
+            std::vector<Cand>& out = cands_of[v];
+            const std::vector<PC>& list = pc[v];
+            size_t cur = 0;
+            for (size_t hidx = h_begin[v]; hidx < h_begin[v + 1]; ++hidx) {
+                const Hypothesis& C = hyps[hidx];
+                int svi; uint64_t dsrc; if (!dense(C.cam, C.seg, svi, dsrc) || svi != v) continue;
+                while (cur < list.size() && list[cur].seg < C.seg) ++cur;
+                for (size_t k = cur; k < list.size() && list[k].seg == C.seg; ++k) {                                                // :996-1138
+                    const unsigned tcam = list[k].tcam, tseg = list[k].tseg;
+                    int tvi; uint64_t dt; if (!dense(tcam, tseg, tvi, dt)) continue;
+                    if (!emit && tvi <= v) continue;
+                    if (!mark(C.seg, tvi, tseg)) continue;
+                    const int ht = hyp_of[tvi][tseg];
+                    if (ht < 0) continue;                                                                                           // :1007
+                    if (emit) { Cand c = {int(hidx), ht, 1.0f, L3D_MIN_AFFINITY}; out.push_back(c); }                               // :1014-1016
+                    const std::vector<CollinEntry>& cl = view_at[tvi]->collin[tseg];                                                // :1065-1135
+                    for (size_t e = 0; e < cl.size(); ++e) {
+                        if (!mark(C.seg, tvi, cl[e].other)) continue;
+                        const int hc = hyp_of[tvi][cl[e].other];
+                        if (hc < 0) continue;
+                        if (emit) { Cand c3 = {int(hidx), hc, 1.0f, 0.01f}; out.push_back(c3); }                                    // :1085-1087
+                    }
+                }
+                if (!emit) continue;
+                const std::vector<CollinEntry>& cs = view_at[v]->collin[C.seg];                                                     // :1141-1214
+                for (size_t e = 0; e < cs.size(); ++e) {
+                    if (!mark(C.seg, v, cs[e].other)) continue;
+                    const int hc = hyp_of[v][cs[e].other];
+                    if (hc < 0) continue;
+                    Cand c2 = {int(hidx), hc, cs[e].w, 0.01f}; out.push_back(c2);                                                   // :1163-1165
+                }
+            }
+        };
+        for (int phase = 1; phase <= 2; ++phase) {
+            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), size_t(nviews)));
+            auto work = [&](size_t t0) { for (int v = int(t0); v < nviews; v += int(nt)) run_pass(v, phase == 2); };
+            std::vector<std::thread> pool;
+            for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t);
+            work(0);
+            for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
+        }
+        {
+            size_t total_c = 0;
+            for (int v = 0; v < nviews; ++v) total_c += cands_of[v].size();
+            cands.reserve(total_c);
+            for (int v = 0; v < nviews; ++v) { cands.insert(cands.end(), cands_of[v].begin(), cands_of[v].end()); std::vector<Cand>().swap(cands_of[v]); }
+        }
+        touched.clear();
         if (prof) { std::cerr << "[prof] enumerate " << now_s() - tp << " cands " << cands.size() << std::endl; tp = now_s(); }
         // similarities on the device (line3D.cc:1600-1691)
         std::vector<l3d_pair> pairs(cands.size());
