@@ -680,12 +680,13 @@ struct Line3D::Impl
         }
         std::vector<std::map<int, std::vector<uint32_t> > > touched(static_cast<size_t>(nviews));      // T(v, w), keys (seg of v) << 16 | seg of w
         std::vector<std::vector<Cand> > cands_of(static_cast<size_t>(nviews));
-        auto run_pass = [&](int v, bool emit) {
+        auto run_pass = [&](int v, bool emit, std::vector<std::vector<uint64_t> >& spare) {      // spare: this thread's retired matrices (no fresh pages per pass)
             std::vector<std::vector<uint64_t> > bm(static_cast<size_t>(nviews)); std::vector<size_t> pitch(size_t(nviews), 0);
             auto mark = [&](unsigned sseg, int tv, unsigned tseg) -> bool {   // true if the pair was new
                 const int lo = std::min(v, tv), hi = std::max(v, tv);
                 std::vector<uint64_t>& w = bm[tv];
                 if (w.empty()) {
+                    if (!spare.empty()) { w.swap(spare.back()); spare.pop_back(); }
                     pitch[tv] = (view_at[hi]->segs.size() + 63) / 64;
                     w.assign(std::max<size_t>(view_at[lo]->segs.size() * pitch[tv], 1), 0);
                     if (emit && tv < v) {                             // what the earlier view marked during its own turns
@@ -735,20 +736,28 @@ struct Line3D::Impl
                     Cand c2 = {int(hidx), hc, cs[e].w, 0.01f}; out.push_back(c2);                                                   // :1163-1165
                 }
             }
+            for (int t = 0; t < nviews; ++t) if (!bm[t].empty()) { spare.push_back(std::vector<uint64_t>()); spare.back().swap(bm[t]); }
         };
         for (int phase = 1; phase <= 2; ++phase) {
             const size_t nt = std::max<size_t>(1, std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), size_t(nviews)));
-            auto work = [&](size_t t0) { for (int v = int(t0); v < nviews; v += int(nt)) run_pass(v, phase == 2); };
+            auto work = [&](size_t t0) { std::vector<std::vector<uint64_t> > spare; for (int v = int(t0); v < nviews; v += int(nt)) run_pass(v, phase == 2, spare); };
             std::vector<std::thread> pool;
             for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t);
             work(0);
             for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
         }
-        {
-            size_t total_c = 0;
-            for (int v = 0; v < nviews; ++v) total_c += cands_of[v].size();
-            cands.reserve(total_c);
-            for (int v = 0; v < nviews; ++v) { cands.insert(cands.end(), cands_of[v].begin(), cands_of[v].end()); std::vector<Cand>().swap(cands_of[v]); }
+        {   // the views' lists, end to end (copied in parallel: 10^7..10^8 records)
+            std::vector<size_t> at(size_t(nviews) + 1, 0);
+            for (int v = 0; v < nviews; ++v) at[v + 1] = at[v] + cands_of[v].size();
+            cands.resize(at[nviews]);
+            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), size_t(nviews)));
+            auto work = [&](size_t t0) {
+                for (int v = int(t0); v < nviews; v += int(nt)) { if (!cands_of[v].empty()) memcpy(&cands[at[v]], cands_of[v].data(), sizeof(Cand) * cands_of[v].size()); std::vector<Cand>().swap(cands_of[v]); }
+            };
+            std::vector<std::thread> pool;
+            for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t);
+            work(0);
+            for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
         }
         touched.clear();
         if (prof) { std::cerr << "[prof] enumerate " << now_s() - tp << " cands " << cands.size() << std::endl; tp = now_s(); }
@@ -764,15 +773,31 @@ struct Line3D::Impl
         // edges and node ids in encounter order (line3D.cc:1018-1060)
         std::vector<Edge> A;
         std::vector<int> node_of(hyps.size(), -1); std::vector<int> hyp_of_node;
-        for (size_t k = 0; k < cands.size(); ++k) {
-            const Cand& c = cands[k];
-            // mult is the collinearity weight for same-image pairs (line3D.cc:1163) and exactly 1 otherwise
-            const float w = c.mult * 0.5f * (hyps[c.a].score + hyps[c.b].score) * sim[k];
-            if (!(w > c.thr)) continue;
-            if (node_of[c.a] < 0) { node_of[c.a] = int(hyp_of_node.size()); hyp_of_node.push_back(c.a); }
-            if (node_of[c.b] < 0) { node_of[c.b] = int(hyp_of_node.size()); hyp_of_node.push_back(c.b); }
-            Edge e = {node_of[c.a], node_of[c.b], w}; A.push_back(e);
-            Edge r = {node_of[c.b], node_of[c.a], w}; A.push_back(r);
+        {
+            // weights and the threshold test on all cores (each candidate on its own), the survivors in candidate order
+            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), 16));
+            std::vector<std::vector<std::pair<size_t, float> > > kept(nt);
+            auto work = [&](size_t t) {
+                const size_t k0 = cands.size() * t / nt, k1 = cands.size() * (t + 1) / nt;
+                for (size_t k = k0; k < k1; ++k) {
+                    const Cand& c = cands[k];
+                    // mult is the collinearity weight for same-image pairs (line3D.cc:1163) and exactly 1 otherwise
+                    const float w = c.mult * 0.5f * (hyps[c.a].score + hyps[c.b].score) * sim[k];
+                    if (w > c.thr) kept[t].push_back(std::make_pair(k, w));
+                }
+            };
+            std::vector<std::thread> pool;
+            for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t);
+            work(0);
+            for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
+            for (size_t t = 0; t < nt; ++t)
+                for (size_t q = 0; q < kept[t].size(); ++q) {
+                    const Cand& c = cands[kept[t][q].first]; const float w = kept[t][q].second;
+                    if (node_of[c.a] < 0) { node_of[c.a] = int(hyp_of_node.size()); hyp_of_node.push_back(c.a); }
+                    if (node_of[c.b] < 0) { node_of[c.b] = int(hyp_of_node.size()); hyp_of_node.push_back(c.b); }
+                    Edge e = {node_of[c.a], node_of[c.b], w}; A.push_back(e);
+                    Edge r = {node_of[c.b], node_of[c.a], w}; A.push_back(r);
+                }
         }
         if (prof) { std::cerr << "[prof] edges " << now_s() - tp << " A " << A.size() << std::endl; }
         stats.t_affinity += now_s() - t0;
