@@ -841,7 +841,22 @@ struct Line3D::Impl
         // Felzenszwalb-Huttenlocher as the reference runs it (clustering.cc:6-47, universe.h:59-115):
         // edges stably sorted by ascending weight, threshold w + c / size with c = 1
         std::vector<Edge> sorted(A);
-        std::stable_sort(sorted.begin(), sorted.end(), [](const Edge& a, const Edge& b) { return a.w < b.w; });
+        {
+            // stable sort by weight: positive floats order like their bit patterns, so four stable 8-bit counting passes
+            // do it (a comparison sort of 10^6..10^7 edges was most of this stage); anything else goes the general way
+            bool positive = true;
+            for (size_t k = 0; k < sorted.size() && positive; ++k) positive = sorted[k].w > 0.0f;
+            if (positive && sorted.size() > 256) {
+                std::vector<Edge> tmp(sorted.size());
+                for (int shift = 0; shift < 32; shift += 8) {
+                    size_t count[257] = {0};
+                    for (size_t k = 0; k < sorted.size(); ++k) { uint32_t b; memcpy(&b, &sorted[k].w, 4); ++count[((b >> shift) & 255u) + 1]; }
+                    for (int d = 0; d < 256; ++d) count[d + 1] += count[d];
+                    for (size_t k = 0; k < sorted.size(); ++k) { uint32_t b; memcpy(&b, &sorted[k].w, 4); tmp[count[(b >> shift) & 255u]++] = sorted[k]; }
+                    sorted.swap(tmp);
+                }
+            } else std::stable_sort(sorted.begin(), sorted.end(), [](const Edge& a, const Edge& b) { return a.w < b.w; });
+        }
         std::vector<int> parent(n_nodes), rank(n_nodes, 0), sz(n_nodes, 1);
         std::vector<float> thr(n_nodes, 1.0f);
         for (int i = 0; i < n_nodes; ++i) parent[i] = i;
