@@ -2108,7 +2108,11 @@ void start_worker(l3d_ctx* ctx, size_t from)
     std::vector<JobHost> jh;
     set->begin = from; set->end = plan_batch(ctx, from, jh);
     ctx->pa_worker_rc = 0;
-    ctx->pa_worker = std::thread([ctx, set, jh]() { ctx->pa_worker_rc = run_phase_a(ctx, set, jh); });
+    ctx->pa_worker = std::thread([ctx, set, jh]() {
+        try { ctx->pa_worker_rc = run_phase_a(ctx, set, jh); }
+        catch (const std::exception& e) { set->err = std::string("pair tests (helper thread): ") + e.what(); ctx->pa_worker_rc = 1; }
+        catch (...) { set->err = "pair tests (helper thread): unknown exception"; ctx->pa_worker_rc = 1; }
+    });
     ctx->pa_worker_active = true;
 }
 
@@ -2202,6 +2206,15 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     GroupView one = {view, n_nb, nb, 0, 0};
     if (enqueue_group(ctx, ctx->grp[0], &one, 1, sigma_p, sigma_a)) return 1;
     return finish_group(ctx, ctx->grp[0], copy_back, res);
+}
+
+// Nothing throws across the C ABI: the host-side containers can (out of memory).
+template <typename F>
+int guarded(l3d_ctx* ctx, F f)
+{
+    try { return f(); }
+    catch (const std::exception& e) { if (ctx) ctx->err = std::string("exception: ") + e.what(); return 1; }
+    catch (...) { if (ctx) ctx->err = "unknown exception"; return 1; }
 }
 
 }  // namespace
@@ -2455,11 +2468,11 @@ int l3d_retain_results(l3d_ctx* ctx, int on)
 
 int l3d_match_view(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors, float sigma_p, float sigma_a, l3d_match_result* result)
 {
-    return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, true);
+    return guarded(ctx, [&]() { return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, true); });
 }
 int l3d_match_view_resident(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors, float sigma_p, float sigma_a, l3d_match_result* result)
 {
-    return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, false);
+    return guarded(ctx, [&]() { return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, false); });
 }
 
 int l3d_unproject(l3d_ctx* ctx, size_t n, const l3d_hypothesis_in* in, l3d_segment3d* out)
