@@ -480,7 +480,7 @@ __global__ void k_expand(const JobDev* __restrict__ jobs, const int* __restrict_
 }
 
 constexpr int EF_T = 256;
-__global__ void __launch_bounds__(EF_T) k_exact_flat(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, const int* __restrict__ row_job, int n_cand,
+__global__ void __launch_bounds__(EF_T, 6) k_exact_flat(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, const int* __restrict__ row_job, int n_cand,
                                                      const int* __restrict__ c_col, const int* __restrict__ c_row,
                                                      unsigned char* __restrict__ c_ok, float4* __restrict__ c_dep, int* __restrict__ raw_cnt)
 {
