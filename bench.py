@@ -307,7 +307,7 @@ def ours(args) -> None:
                e2e=dict(value=tot_pairs / t_e2e_max, unit=UNIT, h2d_bytes_per_step=int(st_e["h2d_bytes"]), d2h_bytes_per_step=int(st_e["d2h_bytes"]),
                         ms_per_step=1e3 * t_e2e_max, inside_calls_ms=1e3 * float(st_e["t_upload"] + st_e["t_matching_calls"]),
                         timed="wall clock of the upload plus the whole matching loop of Line3D::compute3Dmodel, the host's bookkeeping between the calls included "
-                              "(the library runs one view ahead of the host, so the time inside the calls alone, inside_calls_ms, would flatter it)",
+                              "(the library works ahead of the host, so the time inside the calls alone, inside_calls_ms, would flatter it)",
                         api="Line3D::compute3Dmodel -> l3d_set_views + l3d_match_view per view (host buffers)",
                         compute3Dmodel_ms=1e3 * float(np.mean([tm["compute3Dmodel"] for tm, _ in e2e_stats])),
                         host_stages_ms={k[2:]: 1e3 * st_e[k] for k in ("t_neighbors", "t_upload", "t_matching", "t_hypotheses", "t_affinity", "t_diffusion", "t_clustering", "t_lines")}),
