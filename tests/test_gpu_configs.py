@@ -55,6 +55,16 @@ def test_urban_reduced_with_diffusion(tmp_path):
     _pipeline_equal(p, neighbors=6, diffusion=True)
 
 
+def test_ragged_and_empty_views(tmp_path):
+    """A view without segments, one with a single segment, one with 37 among views of 700: the whole pipeline against
+    the oracle (which equals the reference build on the same scene, tests/test_oracle_vs_ref.py)."""
+    from test_oracle_vs_ref import ragged_scene
+    p = str(tmp_path / "ragged.scn")
+    ragged_scene(p)
+    n, st = _pipeline_equal(p, neighbors=6)
+    assert n > 0
+
+
 def test_batched_equals_view_by_view_and_is_deterministic(tmp_path):
     """Larger urban slice (no oracle): the scaffold announces the schedule (batched pair tests), the plain C-ABI loop
     does not; both must give the same filtered matches, and a second run the same again."""

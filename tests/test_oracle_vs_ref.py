@@ -35,6 +35,22 @@ def test_other_seed_bit_identical(tmp_path):
     _both(p, neighbors=6)
 
 
+def ragged_scene(path):
+    """Views of very different sizes: one without any segment, one with a single segment, one with a few."""
+    sc = scenes.urban(n_views=12, n_seg=700, seed=5, blocks=(2, 1))
+    for k, n in ((3, 0), (5, 1), (7, 37)):
+        sc.views[k].segs = sc.views[k].segs[:n]
+    scenes.write_scene(sc, path)
+    return sc
+
+
+def test_ragged_and_empty_views_bit_identical(tmp_path):
+    p = str(tmp_path / "ragged.scn")
+    ragged_scene(p)
+    n, dm = _both(p, neighbors=6)
+    assert n > 0 and dm["filtered_matches"].shape[0] > 0
+
+
 def test_too_few_views_is_refused(tmp_path):
     # line3D.cc:347-351: fewer than 4 views -> error line, no result
     p = str(tmp_path / "s3.scn")
