@@ -140,3 +140,37 @@ def test_plan_run_ahead_and_retained_results(tmp_path):
     again = util.run_matching(ctx, ids, views, F, vn, plan=True)
     assert all(np.array_equal(again[v]["filtered"], plain[v]["filtered"]) for v in plain)
     ctx.close()
+
+
+def test_c2_full_size_properties():
+    """BASELINE.json's C2 at full size (200 views x ~2000 segments, 5.9e9 pair tests; the oracle would need hours):
+    properties that do not depend on the size.  Run-to-run identity of every record (the library runs views out of
+    order, in groups, beside the next batch's pair tests, with atomics in several kernels), work accounting, and the
+    mirror property of handed-over records: a match (v,i)->(n,j) kept by both views has mirrored depths."""
+    import bench
+    from line3d_b200 import host
+    s = host.Session(bench.scene_file("C2"), neighbors=12, collinearity=False)
+    n1, _, st1 = s.compute(keep_debug=True); d1 = s.dump()
+    n2, _, st2 = s.compute(keep_debug=True); d2 = s.dump()
+    s.close()
+    assert n1 == n2 and n1 > 0
+    for k in ("filtered_matches", "match_median", "match_log", "best_match", "edges_cluster", "lines_seg3d"):
+        assert np.array_equal(d1[k], d2[k]), k
+    assert st1["pair_tests"] == st2["pair_tests"] == 5875904553          # SURVEY 8.0: between V k N^2 / 2 and V k N^2
+    assert st1["raw_matches"] == st2["raw_matches"] and st1["score_iters"] == st2["score_iters"]
+    assert st1["raw_matches"] <= st1["candidates"] <= st1["pair_tests"] and st1["filtered_matches"] <= st1["scored_matches"]
+    f = d1["filtered_matches"]
+    assert f.shape[0] == st1["filtered_matches"]
+    assert np.all(f[:, 8] > 0.5)                                       # stored confidence = score / 2 with score > 1
+    fi = f[:, :4].astype(np.int64)
+    assert fi[:, 0].max() < 256 and fi[:, 2].max() < 256 and fi[:, 1].max() < 65536 and fi[:, 3].max() < 65536
+    key = ((fi[:, 0] * 65536 + fi[:, 1]) * 256 + fi[:, 2]) * 65536 + fi[:, 3]
+    srt = np.argsort(key, kind="stable"); skey = key[srt]
+    assert np.all(np.diff(skey) > 0)                                   # no record twice
+    back = np.nonzero(fi[:, 2] < fi[:, 0])[0]                          # records towards an earlier view ...
+    mirror = ((fi[back, 2] * 65536 + fi[back, 3]) * 256 + fi[back, 0]) * 65536 + fi[back, 1]
+    pos = np.searchsorted(skey, mirror)
+    hit = (pos < skey.size) & (skey[np.minimum(pos, skey.size - 1)] == mirror)
+    assert hit.sum() > 1000                                            # ... that this earlier view kept as well
+    a_rows = f[back[hit]]; b_rows = f[srt[pos[hit]]]
+    assert np.array_equal(a_rows[:, 4:8], b_rows[:, [6, 7, 4, 5]])
