@@ -10,5 +10,6 @@ for _ in range(2):
     print(n, tm, {k: round(v, 4) for k, v in st.items() if k.startswith('t_')})
 s.close()
 s = host.Session(p, neighbors=12, collinearity=True)
+s.compute()
 n, tm, st = s.compute()
 print('collin', n, tm, {k: round(v, 4) for k, v in st.items() if k.startswith('t_')}, st['affinity_pairs'], st['edges'])
