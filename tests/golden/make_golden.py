@@ -29,8 +29,22 @@ def golden_scene():
     return scenes.tiny(n_views=7, n_seg=70, seed=21, step_deg=10.0)
 
 
+def ragged_scene():
+    """Views of very different sizes: one without any segment, one with a single segment, one with a few."""
+    sc = scenes.urban(n_views=12, n_seg=700, seed=5, blocks=(2, 1))
+    for k, n in ((3, 0), (5, 1), (7, 37)):
+        sc.views[k].segs = sc.views[k].segs[:n]
+    return sc
+
+
 def main():
     assert refrun.available(), "build oracle/_ref first (make -C oracle ref)"
+    scn2 = os.path.join(HERE, "scene_g2.scn")
+    scenes.write_scene(ragged_scene(), scn2)
+    n, tm, dm = refrun.run_scene(scn2, tempfile.mkdtemp(), neighbors=6)
+    dm["n_lines"] = np.array([n])
+    np.savez_compressed(os.path.join(HERE, "ref_g2_k6.npz"), **dm)
+    print("g2 (ragged)", "lines", n, {k: v.shape for k, v in dm.items() if k in ("filtered_matches", "edges_cluster", "lines_seg3d")})
     scn = os.path.join(HERE, "scene_g1.scn")
     scenes.write_scene(golden_scene(), scn)
     for tag, params in CASES.items():

@@ -27,6 +27,18 @@ def test_pipeline_matches_reference_golden(tag):
     assert ct["raw"] > 0 and ct["pair_tests"] > ct["accepted"] >= ct["raw"]
 
 
+def test_ragged_scene_matches_reference_golden():
+    """scene_g2: views with 0, 1 and 37 segments among views of 700."""
+    gold = np.load(os.path.join(GOLD, "ref_g2_k6.npz"))
+    n, tm, ct, dm = oracle_py.run_scene(os.path.join(GOLD, "scene_g2.scn"), tempfile.mkdtemp(), neighbors=6)
+    assert n == int(gold["n_lines"][0]) and n > 0
+    for k in gold.files:
+        if k == "n_lines":
+            continue
+        assert dm[k].shape == gold[k].shape, k
+        assert np.array_equal(dm[k], gold[k]), k
+
+
 def test_collinearity_matches_reference_golden():
     g = np.load(os.path.join(GOLD, "ref_ops.npz"))
     rel = oracle_py.collinearity(g["collin_segs"], 2.0)
