@@ -30,6 +30,18 @@ namespace
 typedef Eigen::Matrix3d M3;
 typedef Eigen::Vector3d V3;
 
+// Worker threads for the host stages: up to 16, and a fair share of the cores when several processes of one job sit on
+// the machine (torchrun sets LOCAL_WORLD_SIZE; L3D_HOST_THREADS overrides).
+inline size_t host_threads()
+{
+    static const size_t n = [] {
+        if (const char* e = getenv("L3D_HOST_THREADS")) { const long v = atol(e); if (v > 0) return size_t(v); }
+        size_t hw = std::max<size_t>(1, std::thread::hardware_concurrency()), share = 1;
+        if (const char* e = getenv("LOCAL_WORLD_SIZE")) { const long v = atol(e); if (v > 0) share = size_t(v); }
+        return std::max<size_t>(1, std::min<size_t>(hw / share, 16));
+    }();
+    return n;
+}
 inline double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 inline uint64_t seg_key(unsigned cam, unsigned seg) { return (uint64_t(cam) << 32) | uint64_t(seg); }
 
@@ -561,7 +573,7 @@ struct Line3D::Impl
                 }
             }
         };
-        const size_t nt = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), 16));
+        const size_t nt = std::max<size_t>(1, host_threads());
         for (int pass = 1; pass <= 2; ++pass) {
             std::vector<std::thread> pool;
             for (size_t t = 1; t < nt; ++t) { if (pass == 1) pool.emplace_back(pass1, t, nt); else pool.emplace_back(pass2, t, nt); }
@@ -635,7 +647,7 @@ struct Line3D::Impl
                     std::vector<PC>().swap(f); std::vector<PC>().swap(r);
                 }
             };
-            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), 16));
+            const size_t nt = std::max<size_t>(1, host_threads());
             std::vector<std::thread> pool;
             for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t, nt);
             work(0, nt);
@@ -739,7 +751,7 @@ struct Line3D::Impl
             for (int t = 0; t < nviews; ++t) if (!bm[t].empty()) { spare.push_back(std::vector<uint64_t>()); spare.back().swap(bm[t]); }
         };
         for (int phase = 1; phase <= 2; ++phase) {
-            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), size_t(nviews)));
+            const size_t nt = std::max<size_t>(1, std::min<size_t>(host_threads(), size_t(nviews)));
             auto work = [&](size_t t0) { std::vector<std::vector<uint64_t> > spare; for (int v = int(t0); v < nviews; v += int(nt)) run_pass(v, phase == 2, spare); };
             std::vector<std::thread> pool;
             for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t);
@@ -750,7 +762,7 @@ struct Line3D::Impl
             std::vector<size_t> at(size_t(nviews) + 1, 0);
             for (int v = 0; v < nviews; ++v) at[v + 1] = at[v] + cands_of[v].size();
             cands.resize(at[nviews]);
-            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), size_t(nviews)));
+            const size_t nt = std::max<size_t>(1, std::min<size_t>(host_threads(), size_t(nviews)));
             auto work = [&](size_t t0) {
                 for (int v = int(t0); v < nviews; v += int(nt)) { if (!cands_of[v].empty()) memcpy(&cands[at[v]], cands_of[v].data(), sizeof(Cand) * cands_of[v].size()); std::vector<Cand>().swap(cands_of[v]); }
             };
@@ -775,7 +787,7 @@ struct Line3D::Impl
         std::vector<int> node_of(hyps.size(), -1); std::vector<int> hyp_of_node;
         {
             // weights and the threshold test on all cores (each candidate on its own), the survivors in candidate order
-            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), 16));
+            const size_t nt = std::max<size_t>(1, host_threads());
             std::vector<std::vector<std::pair<size_t, float> > > kept(nt);
             auto work = [&](size_t t) {
                 const size_t k0 = cands.size() * t / nt, k1 = cands.size() * (t + 1) / nt;
@@ -885,7 +897,7 @@ struct Line3D::Impl
                 if (cams[c->first].size() >= 4) todo.push_back(&c->second);
             std::vector<std::list<L3DSegment2D> > s2(todo.size()); std::vector<std::list<std::pair<V3, V3> > > s3(todo.size());
             auto work = [&](size_t t0, size_t step) { for (size_t k = t0; k < todo.size(); k += step) alignCluster(*todo[k], s3[k], s2[k]); };
-            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), todo.size()));
+            const size_t nt = std::max<size_t>(1, std::min<size_t>(host_threads(), todo.size()));
             std::vector<std::thread> pool;
             for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t, nt);
             work(0, nt);
