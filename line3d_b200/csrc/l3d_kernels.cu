@@ -1604,7 +1604,7 @@ struct l3d_ctx {
     size_t fly_begin = 0, fly_end = 0; std::vector<int> level;
     float run_sigma_p = 0.f, run_sigma_a = 0.f;
     DevPool pool;
-    cudaStream_t copy_stream = nullptr;
+    cudaStream_t copy_stream = nullptr, fin_stream = nullptr;
     bool stage_events = false;         // per-stage CUDA events inside a view (l3d_set_stage_timing): they separate kernels that otherwise overlap
     cudaEvent_t mark_ev[2] = {nullptr, nullptr};
     // retained results (l3d_retain_results): pinned chunks that are never moved, handed out front to back
@@ -1971,12 +1971,21 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         L3D_CUDA(pdl_launch(k_deliver_scatter, dim3(unsigned((std::max<size_t>(mx_M, 1) + 255) / 256), G), dim3(256), 0, st, A));
         ctx->launches += 2;
     }
-    L3D_CUDA(pdl_launch(k_finish_view, dim3(1, G), dim3(MS_T), 0, st, A));
+    // The last kernel (medians, result records) and the download of the records are needed by the host only: the next
+    // group does not wait for them.  They go to a side stream (this group's buffers are not touched again before the
+    // host has collected it), except when stages are being timed.
+    cudaStream_t fs = st;
+    if (!ctx->stage_events) {
+        fs = ctx->fin_stream;
+        L3D_CUDA(cudaEventRecord(gr.ev[1], st));
+        L3D_CUDA(cudaStreamWaitEvent(fs, gr.ev[1], 0));
+    }
+    L3D_CUDA(pdl_launch(k_finish_view, dim3(1, G), dim3(MS_T), 0, fs, A));
     ctx->launches += 1;
     L3D_CUDA(cudaGetLastError());
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[5], st));
-    L3D_CUDA(cudaMemcpyAsync(gr.h_vres.p, gr.d_vres.p, sizeof(int) * size_t(count) * res_stride, cudaMemcpyDeviceToHost, st));
-    L3D_CUDA(cudaEventRecord(gr.ev[0], st));
+    L3D_CUDA(cudaMemcpyAsync(gr.h_vres.p, gr.d_vres.p, sizeof(int) * size_t(count) * res_stride, cudaMemcpyDeviceToHost, fs));
+    L3D_CUDA(cudaEventRecord(gr.ev[0], fs));
     return 0;
 }
 
@@ -2246,6 +2255,7 @@ int l3d_create(int device, l3d_ctx** out)
     for (int k = 0; k < 2; ++k) cudaEventCreate(&ctx->ev[k]);
     for (int q = 0; q < 2; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->grp[q].ev[k]);
     if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); cudaStreamDestroy(ctx->stream); delete ctx; return 1; }
+    if ((e = cudaStreamCreateWithPriority(&ctx->fin_stream, cudaStreamNonBlocking, prio_hi)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); l3d_destroy(ctx); return 1; }
     for (int q = 0; q < 2; ++q) {
         PhaseASet& set = ctx->pa[q];
         if ((e = cudaStreamCreateWithPriority(&set.stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); l3d_destroy(ctx); return 1; }
@@ -2281,6 +2291,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->d_tile_sums.release(); ctx->d_total.release();
     ctx->grp[0].release(); ctx->grp[1].release(); ctx->pool.release();
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->fin_stream) cudaStreamDestroy(ctx->fin_stream);
     for (size_t k = 0; k < ctx->arena.size(); ++k) cudaFreeHost(ctx->arena[k].first);
     for (int k = 0; k < 2; ++k) if (ctx->mark_ev[k]) cudaEventDestroy(ctx->mark_ev[k]);
     ctx->h_filtered.release(); ctx->h_ints.release();
@@ -2605,6 +2616,10 @@ int l3d_mark(l3d_ctx* ctx, int which)
 {
     if (!ctx || which < 0 || which > 1) return 1;
     L3D_CUDA(cudaSetDevice(ctx->device));
+    if (which == 1) {            // the closing mark also comes after the side stream's last result records
+        L3D_CUDA(cudaEventRecord(ctx->ev[1], ctx->fin_stream));
+        L3D_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev[1], 0));
+    }
     L3D_CUDA(cudaEventRecord(ctx->mark_ev[which], ctx->stream));
     return 0;
 }
