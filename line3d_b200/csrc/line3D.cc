@@ -415,7 +415,9 @@ struct Line3D::Impl
             ViewData* v = it->second; v->index = idx; view_at[idx] = v; id2idx[it->first] = idx;
             l3d_view& o = lv[idx];
             memset(&o, 0, sizeof o);
-            o.id = int(v->id); o.n_segments = int(v->segs.size()); o.segments = reinterpret_cast<const float*>(v->segs.data());
+            // a rank only needs the segments of its own connected components (every neighbour of one of its views is in them)
+            const bool mine = shard_world <= 1 || my_views.count(it->first) != 0;
+            o.id = int(v->id); o.n_segments = mine ? int(v->segs.size()) : 0; o.segments = reinterpret_cast<const float*>(v->segs.data());
             for (int r = 0; r < 3; ++r) {
                 for (int c = 0; c < 3; ++c) { o.RtKinv[r * 3 + c] = float(v->RtKinv(r, c)); o.RtKinv_d[r * 3 + c] = v->RtKinv(r, c); }   // line3D.cc:746, 790
                 for (int c = 0; c < 4; ++c) o.P[r * 4 + c] = float(v->P(r, c));                                                            // line3D.cc:756
