@@ -56,18 +56,24 @@ int l3d_collinearity(l3d_ctx* ctx, const float* segments, int n, float collin_s,
  *      (about 2.1 MB of device memory on every GPU that loads the library, held until the
  *      process exits), and inputs and outputs are the caller's own DEVICE buffers.
  *
- *      d_segments  n x 4 floats on the device          d_pairs   room for `capacity` records
+ *      d_segments  n x 4 floats on the device, 16-byte aligned (it is read as float4; a
+ *                  misaligned pointer is refused with return code 1)
+ *      d_pairs     room for `capacity` records on the device (4-byte aligned)
  *      d_count     one int on the device: receives the number of collinear pairs found.  If
  *                  it exceeds `capacity`, only the first `capacity` records (in (i, j) order)
  *                  were written.
  *      cuda_stream a cudaStream_t (NULL = default stream); the work is enqueued, not waited for.
+ *                  The stream's device must be the CURRENT device (return code 7 otherwise):
+ *                  the built-in array is looked up on the current device.
  *      err/err_len optional buffer for a message when the return value is non-zero.
  *
  *      Limit: n <= 4096 segments per image; larger inputs are refused with return code 2
  *      (the reference's own detector cap is 3000, commons.h:44).
  *      The first call on each device looks up the device address of the built-in array
  *      (cudaGetSymbolAddress) with that device current; make that first call during
- *      start-up, before any stream capture is begun.  All calls on a device share the one
+ *      start-up, before any stream capture is begun (the look-up result is cached per
+ *      device in an atomic table: concurrent first calls are safe, both store the same
+ *      address).  All calls on a device share the one
  *      array and it keeps whatever the previous call left in it (the part that has to start
  *      from zero is cleared by each call); two calls whose GPU work overlaps in time -- on
  *      different streams or from different threads -- race on it and must be serialised by
@@ -161,8 +167,36 @@ int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans);
 /* Tests only: pair tests per batch of the next announced schedules (0 = automatic: about an eighth of the schedule,
  * at least 2.5e8, at most 2.4e10).  Small values force many batches on small scenes. */
 int l3d_debug_set_batch_pairs(l3d_ctx* ctx, uint64_t pairs);
+/* Tests only: mode 1 switches the conservative pre-tests off (every pair of a computed view pair goes to the exact
+ * test, as in cudawrapper.cu:538-611); mode 0 (default) switches them back on.  Results must be identical. */
+int l3d_debug_set_pretest(l3d_ctx* ctx, int mode);
+/* Tests only: candidates (pairs that survive the pre-tests) are indexed with 32 bits per batch of pair tests.  A batch
+ * with more than 2147418112 of them -- a candidate rate far above the usual 2 %, e.g. degenerate epipolar geometry --
+ * is cut in two and redone; if a single view alone exceeds the limit l3d_match_view fails with a message.  This call
+ * lowers the limit so that a test can reach that path with a small scene (0 = back to the default). */
+int l3d_debug_set_candidate_limit(l3d_ctx* ctx, uint64_t limit);
 /* Forget all delivered-but-unconsumed records and any plan (a new compute3Dmodel run, line3D.cc:356). */
 int l3d_reset_matching(l3d_ctx* ctx);
+
+/* ---- several GPUs on ONE scene.  No counterpart in the reference (single implicit device, cudawrapper.cu).
+ *      One process and one context per GPU.  After l3d_comm_init the contexts of the `world` ranks work on the same
+ *      scene together: the segments of every view are dealt out to the ranks in turn (segment s of a view belongs to
+ *      rank s mod world), each rank pair-tests, assembles and scores its rows of every view, and the views are still
+ *      processed in the reference's order of dependence.  What travels over NCCL (NVLink): the segment table from rank 0
+ *      at l3d_set_views (a rank other than 0 may pass segments = NULL); per group of independent views the ranks'
+ *      record counts, the depth samples for the median (min-all-reduce), the sizes of the hand-over groups
+ *      (sum-all-reduce) and the output records themselves (all-gather), from which every rank builds the hand-over
+ *      lists for its rows of later views.
+ *      Every rank must make the same calls in the same order with the same arguments (l3d_set_views, l3d_plan_matching,
+ *      l3d_match_view ...); a rank that fails leaves the others waiting.  Results: n_filtered, n_scored, n_raw, n_delivered,
+ *      median_depth and the score iteration counters describe the whole view on every rank; pair_tests and n_candidates
+ *      count this rank's rows; `filtered` holds the records of ALL ranks (grouped by rank, each group in (src, cam, tgt)
+ *      order) on rank result_root, or on every rank if result_root < 0, and is NULL elsewhere.
+ *      l3d_comm_unique_id: rank 0 obtains an id (ncclGetUniqueId) and hands it to the other ranks by any means. */
+#define L3D_COMM_ID_BYTES 128
+int l3d_comm_unique_id(void* id /* L3D_COMM_ID_BYTES bytes */);
+int l3d_comm_init(l3d_ctx* ctx, int rank, int world, const void* id, int result_root);
+int l3d_comm_destroy(l3d_ctx* ctx);
 
 /* Device-only variant used for measurement: same work, but nothing is copied back except
  * the counters; filtered is NULL. */
@@ -199,9 +233,10 @@ int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3
  * between the stages keep consecutive kernels from overlapping (programmatic dependent launch) and cost about
  * 13 % of a step, so they are off unless asked for. */
 int l3d_last_timings(l3d_ctx* ctx, float ms[6]);
-/* Duration in ms of the two large launches of the last batch of pair tests alone: [0] the pre-test kernel,
- * [1] the exact-test kernel (valid after the l3d_last_timings call that reported a non-zero ms[0]). */
-int l3d_last_kernel_timings(l3d_ctx* ctx, float ms[2]);
+/* Duration in ms of the three large launches of the last batch of pair tests alone: [0] the level-1 pre-test kernel
+ * (k_pretest), [1] the exact-test kernel, [2] the level-2 pre-test kernel (k_pretest2); valid after the
+ * l3d_last_timings call that reported a non-zero ms[0]. */
+int l3d_last_kernel_timings(l3d_ctx* ctx, float ms[3]);
 int l3d_set_stage_timing(l3d_ctx* ctx, int on);
 /* Two CUDA events on the context's stream for timing any span of calls on the device: l3d_mark(ctx, 0) before,
  * l3d_mark(ctx, 1) after, l3d_marks_elapsed waits for the second and returns the milliseconds between them. */
@@ -212,6 +247,8 @@ int l3d_flush_l2(l3d_ctx* ctx);
 /* FP32 FFMA throughput of the device in TFLOP/s (register-only FMA chains, CUDA events):
  * the measured denominator for the FP32-pipe roofline. */
 int l3d_measure_fp32_peak(l3d_ctx* ctx, float* tflops);
+/* The same with packed FFMA2 instructions (two FP32 FMAs per issue slot on sm_100). */
+int l3d_measure_fp32x2_peak(l3d_ctx* ctx, float* tflops);
 /* The device's float exp (which = 0) / acos (which = 1) as used inside the kernels, on an
  * array: they are written to agree bit for bit with glibc's expf / acosf, which the
  * reference's host build calls; tests compare them against libm. */

@@ -79,6 +79,12 @@ def lib():
         L.l3d_diffuse.restype = C.c_int; L.l3d_diffuse.argtypes = [vp, C.c_int, C.c_size_t, vp, vp]
         L.l3d_last_timings.restype = C.c_int; L.l3d_last_timings.argtypes = [vp, C.POINTER(C.c_float)]
         L.l3d_measure_fp32_peak.restype = C.c_int; L.l3d_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_float)]
+        L.l3d_measure_fp32x2_peak.restype = C.c_int; L.l3d_measure_fp32x2_peak.argtypes = [vp, C.POINTER(C.c_float)]
+        L.l3d_comm_unique_id.restype = C.c_int; L.l3d_comm_unique_id.argtypes = [C.c_char_p]
+        L.l3d_comm_init.restype = C.c_int; L.l3d_comm_init.argtypes = [vp, C.c_int, C.c_int, C.c_char_p, C.c_int]
+        L.l3d_comm_destroy.restype = C.c_int; L.l3d_comm_destroy.argtypes = [vp]
+        L.l3d_debug_set_pretest.restype = C.c_int; L.l3d_debug_set_pretest.argtypes = [vp, C.c_int]
+        L.l3d_debug_set_candidate_limit.restype = C.c_int; L.l3d_debug_set_candidate_limit.argtypes = [vp, C.c_uint64]
         L.l3d_flush_l2.restype = C.c_int; L.l3d_flush_l2.argtypes = [vp]
         L.l3d_debug_math.restype = C.c_int; L.l3d_debug_math.argtypes = [vp, C.c_int, C.c_int, vp, vp]
         L.l3d_kernel_launches.restype = C.c_uint64; L.l3d_kernel_launches.argtypes = [vp]
@@ -87,8 +93,19 @@ def lib():
 
 
 EXPORTS = ["l3d_create", "l3d_destroy", "l3d_last_error", "l3d_collinearity", "l3d_collinearity_prealloc", "l3d_set_views", "l3d_match_view",
-           "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_debug_set_batch_pairs", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
+           "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_debug_set_batch_pairs", "l3d_comm_unique_id", "l3d_comm_init", "l3d_comm_destroy", "l3d_debug_set_pretest", "l3d_debug_set_candidate_limit", "l3d_measure_fp32x2_peak", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
            "l3d_last_timings", "l3d_last_kernel_timings", "l3d_set_stage_timing", "l3d_mark", "l3d_marks_elapsed", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math", "l3d_flush_l2"]
+
+
+COMM_ID_BYTES = 128
+
+
+def comm_unique_id() -> bytes:
+    """An NCCL id for l3d_comm_init: made on rank 0, handed to the other ranks by the caller (e.g. a gloo broadcast)."""
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    if lib().l3d_comm_unique_id(buf) != 0:
+        raise L3DError(lib().l3d_last_error(None).decode())
+    return buf.raw
 
 
 class Context:
@@ -146,6 +163,9 @@ class Context:
         self._check(self._L.l3d_set_views(self._h, len(views), arr))
         self._n_views = len(views)
 
+    def comm_init(self, rank: int, world: int, nccl_id: bytes | None, result_root: int = -1):
+        self._check(self._L.l3d_comm_init(self._h, int(rank), int(world), nccl_id, int(result_root)))
+
     def set_stage_timing(self, on: bool):
         self._check(self._L.l3d_set_stage_timing(self._h, int(bool(on))))
 
@@ -171,6 +191,12 @@ class Context:
     def debug_set_batch_pairs(self, pairs: int):
         self._L.l3d_debug_set_batch_pairs.argtypes = [C.c_void_p, C.c_uint64]
         self._check(self._L.l3d_debug_set_batch_pairs(self._h, int(pairs)))
+
+    def debug_set_pretest(self, mode: int):
+        self._check(self._L.l3d_debug_set_pretest(self._h, int(mode)))
+
+    def debug_set_candidate_limit(self, limit: int):
+        self._check(self._L.l3d_debug_set_candidate_limit(self._h, int(limit)))
 
     def retain_results(self, on: bool):
         self._check(self._L.l3d_retain_results(self._h, int(bool(on))))
@@ -226,6 +252,11 @@ class Context:
     def fp32_peak_tflops(self) -> float:
         t = C.c_float()
         self._check(self._L.l3d_measure_fp32_peak(self._h, C.byref(t)))
+        return float(t.value)
+
+    def fp32x2_peak_tflops(self) -> float:
+        t = C.c_float()
+        self._check(self._L.l3d_measure_fp32x2_peak(self._h, C.byref(t)))
         return float(t.value)
 
     def flush_l2(self):

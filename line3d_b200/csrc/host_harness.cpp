@@ -85,7 +85,8 @@ int l3dhost_compute(void* session, int diffusion, int measure_only, int flush_l2
     if (!s || !s->l3d) return -1;
     Quiet q(s->verbose);
     try {
-        s->l3d->setMeasureOnly(measure_only != 0);
+        s->l3d->setMeasureOnly(measure_only == 1);
+        s->l3d->setMatchOnly(measure_only == 2);
         s->l3d->setFlushL2(flush_l2 != 0);
         s->l3d->setKeepDebug(keep_debug != 0);
         s->l3d->setStageTiming(stage_timing != 0);
@@ -99,7 +100,7 @@ int l3dhost_compute(void* session, int diffusion, int measure_only, int flush_l2
                                   double(st.score_iters), double(st.score_iters_other_cam), double(st.hypotheses), double(st.affinity_pairs), double(st.edges),
                                   double(st.kernel_launches), st.t_neighbors, st.t_upload, st.t_matching, st.t_matching_device, st.t_hypotheses, st.t_affinity,
                                   st.t_diffusion, st.t_clustering, st.t_lines, st.t_total, st.t_stage[0], st.t_stage[1], st.t_stage[2], st.t_stage[3], st.t_stage[4],
-                                  double(st.h2d_bytes), double(st.d2h_bytes), st.t_matching_calls, st.t_k_pretest, st.t_k_exact, 0.0};
+                                  double(st.h2d_bytes), double(st.d2h_bytes), st.t_matching_calls, st.t_k_pretest, st.t_k_exact, st.t_k_pretest2};
             std::memcpy(stats_out, v, sizeof v);
         }
         std::list<L3D::L3DFinalLine3D> result;
@@ -124,6 +125,14 @@ int l3dhost_set_shard(void* session, int rank, int world)
     Session* s = static_cast<Session*>(session);
     if (!s || !s->l3d) return -1;
     s->l3d->setShard(rank, world);
+    return 0;
+}
+
+int l3dhost_set_split(void* session, int rank, int world, const unsigned char* nccl_id)
+{
+    Session* s = static_cast<Session*>(session);
+    if (!s || !s->l3d) return -1;
+    try { s->l3d->setSplit(rank, world, nccl_id); } catch (const std::exception& e) { std::cerr << "l3dhost_set_split: " << e.what() << std::endl; return -2; }
     return 0;
 }
 

@@ -23,9 +23,13 @@
 #include "l3d_device.cuh"
 
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <thread>
@@ -39,6 +43,49 @@ using namespace l3d;
 namespace {
 
 std::string g_create_error;
+
+// NCCL is only needed when several GPUs work on one scene (l3d_comm_init): it is opened at run time, so that the
+// single-GPU path has no dependency on it (and a process that already holds a libnccl -- torch ships its own -- shares it).
+struct NcclApi {
+    void* lib = nullptr;
+    decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+    decltype(&ncclCommInitRank) CommInitRank = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclAllGather) AllGather = nullptr;
+    decltype(&ncclAllReduce) AllReduce = nullptr;
+    decltype(&ncclBroadcast) Broadcast = nullptr;
+    decltype(&ncclGroupStart) GroupStart = nullptr;
+    decltype(&ncclGroupEnd) GroupEnd = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+};
+NcclApi* nccl_api(std::string* err)
+{
+    static NcclApi api; static bool tried = false; static std::string why;
+    if (!tried) {
+        tried = true;
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (int k = 0; k < 2 && !api.lib; ++k) api.lib = dlopen(names[k], RTLD_NOW | RTLD_GLOBAL);
+        if (!api.lib) why = std::string("cannot open libnccl.so.2: ") + dlerror();
+        else {
+#define L3D_NCCL_SYM(name) api.name = reinterpret_cast<decltype(api.name)>(dlsym(api.lib, "nccl" #name)); if (!api.name) why = "libnccl has no nccl" #name;
+            L3D_NCCL_SYM(GetUniqueId) L3D_NCCL_SYM(CommInitRank) L3D_NCCL_SYM(CommDestroy) L3D_NCCL_SYM(AllGather) L3D_NCCL_SYM(AllReduce)
+            L3D_NCCL_SYM(Broadcast) L3D_NCCL_SYM(GroupStart) L3D_NCCL_SYM(GroupEnd) L3D_NCCL_SYM(GetErrorString)
+#undef L3D_NCCL_SYM
+        }
+    }
+    if (!why.empty()) { if (err) *err = why; return nullptr; }
+    return &api;
+}
+#define L3D_NCCL(call)                                                                              \
+    do {                                                                                            \
+        ncclResult_t r_ = (call);                                                                   \
+        if (r_ != ncclSuccess) {                                                                    \
+            char b_[512];                                                                           \
+            snprintf(b_, sizeof b_, "%s failed: %s (%s:%d)", #call, ctx->nccl->GetErrorString(r_), __FILE__, __LINE__); \
+            ctx->err = b_;                                                                          \
+            return 1;                                                                               \
+        }                                                                                           \
+    } while (0)
 
 #define L3D_CUDA(call)                                                                              \
     do {                                                                                            \
@@ -105,7 +152,10 @@ struct SrcTable {       // the source view
     float spatial_k;
     float cmax;         // max |C_k|
     int seg_off, n_seg;
+    int row_first, row_stride;   // row r of this process is segment row_first + r * row_stride of the view (one GPU: 0, 1;
+                                 // several GPUs on one scene: rank, number of ranks -- the view's segments are dealt out in turn)
 };
+__device__ __forceinline__ int row_segment(const SrcTable& s, int row) { return s.row_first + row * s.row_stride; }
 
 // ------------------------------------------------------------------------------------------
 // exclusive scan (int), three phases, any length up to 4096 * 4096
@@ -224,19 +274,24 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_add(int* __restrict__ out, cons
 //   tgt side:  q1, q2 and w_m = |(F^T q_m)_xy|
 // evaluated in FP64 from the FP32 tables, rounded once.
 // ------------------------------------------------------------------------------------------
-struct SrcHoist { float4 a; float4 b; };   // a = (A1x, A1y, A1z, T1)   b = (A2x, A2y, A2z, T2),  A_n = F p_n,  T_n = 2 eps |(A_n)_xy|
-struct TgtHoist { float4 q; float2 w; float2 pad; };   // w_m = 2 eps |(F^T q_m)_xy|
+struct SrcHoist { float4 a; float4 b; };   // a = (A1x, A1y, A1z, W1)   b = (A2x, A2y, A2z, W2),  A_n = F p_n / rho,  W_n = 2 eps |(F p_n)_xy|
+struct TgtHoist { float4 q; float2 w; float2 pad; };   // w_m = 2 eps kappa |(F^T q_m)_xy|
+struct SrcHoist1 { float4 p; float4 m; };  // level 1: p = (A_1 + A_2) / rho, m = (A_1 - A_2) / rho  (sum and difference of the residuals at the two endpoints)
 
 // one pair-tested (source view, neighbour) combination; phase A runs over an array of these
 struct JobDev {
     float F[9], RtKinv_s[9], RtKinv_t[9], C_s[3], C_t[3];
-    int src_off, n_src, tgt_off, n_tgt;      // segment ranges in the global segment array
+    int src_off, n_src, tgt_off, n_tgt;      // segment ranges in the global segment array (n_src: rows of this job)
+    int src_first, src_stride;               // row r of the job is segment src_off + src_first + r * src_stride of the view
     int sh_off, th_off;                      // first entry in the hoist arrays
     long long cand_off;                      // first word in the candidate bitmask
     int wpr;                                 // words per row
     int row_off;                             // first global row (= source segment of this job) in the per-row arrays
-    int blk_off, col_blocks;                 // pre-test blocks of this job: blk_off + rb * col_blocks + cb
+    int blk_off, col_blocks;                 // level-2 blocks of this job: blk_off + rb * col_blocks + cb
+    long long l1_off;                        // first word of the job's level-1 bits: [row group][target column]
+    int l1_blk_off;                          // level-1 blocks of this job start here
 };
+__device__ __forceinline__ int job_src_segment(const JobDev& jb, int row) { return jb.src_off + jb.src_first + row * jb.src_stride; }
 
 __device__ __forceinline__ int find_job_by_block(const JobDev* __restrict__ jobs, int n_jobs, int blk)
 {
@@ -245,47 +300,89 @@ __device__ __forceinline__ int find_job_by_block(const JobDev* __restrict__ jobs
     return lo;
 }
 
-#define L3D_PRETEST_EPS_PX 0.25f
+#define L3D_PRETEST_EPS_PX 0.25
 #define L3D_PRETEST_LO 0.09f
 #define L3D_PRETEST_HI 0.28f
+#define L3D_PRETEST_MAXABS 1e6f     // beyond this the float tests could overflow: the pre-test is switched off for the segment
 
-__global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, SrcHoist* __restrict__ sh, TgtHoist* __restrict__ th, int* __restrict__ row_job)
+// How far (in units of the 0.25 px allowance) the reference's own FP32 arithmetic can move the supporting line of the
+// segment (x1, y1)-(x2, y2) or an intersection with it, relative to coordinates around 2 kpx and long segments, for
+// which the allowance was validated:
+//   * cross(p1, p2).z = x1 y2 - y1 x2 is a difference of two rounded products (cudawrapper.cu:546-547): its error of up
+//     to 1.5 ulp(|x y|) moves the line by that much divided by the segment's length -- 0.06 px for a 12 px segment at
+//     2 kpx, but 1.5 px for a 3 px one, and 16 times more at 8 kpx;
+//   * the intersections are cross products of such lines: their error grows with the square of the coordinates.
+// The factor is >= 1; margins are multiplied by it (source side: the residuals are divided by it instead).
+__device__ __forceinline__ double pretest_noise_factor(double x1, double y1, double x2, double y2)
+{
+    const double c = fmax(fmax(fabs(x1), fabs(y1)), fmax(fabs(x2), fabs(y2)));
+    const double g = fmax(1.0, (c / 2048.0) * (c / 2048.0));
+    const double m = fmax(fmax(fabs(x1 * y2), fabs(y1 * x2)), 1.0);
+    const double ulp = scalbn(1.0, ilogb(m) - 23);
+    const double len = fmax(hypot(x1 - x2, y1 - y2), 1e-3);
+    return g * (1.0 + (3.0 * ulp / len) / L3D_PRETEST_EPS_PX);
+}
+
+// mode 0: normal; 1: the pre-test is switched off for every segment (all pairs go to the exact test; l3d_debug_set_pretest)
+__global__ void k_hoist(const float4* __restrict__ segs, const JobDev* __restrict__ jobs, SrcHoist* __restrict__ sh, SrcHoist1* __restrict__ sh1, TgtHoist* __restrict__ th, int* __restrict__ row_job, int mode)
 {
     const JobDev& jb = jobs[blockIdx.y];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= jb.n_src && idx >= jb.n_tgt) return;
-    double F[9];
+    // The tests are homogeneous in F: it is scaled by a power of two (exact) so that its largest entry lies in [1, 2)
+    // and squares of residuals stay far from the ends of the float range.
+    double F[9], fmaxabs = 0.0;
 #pragma unroll
-    for (int k = 0; k < 9; ++k) F[k] = double(jb.F[k]);
+    for (int k = 0; k < 9; ++k) { F[k] = double(jb.F[k]); fmaxabs = fmax(fmaxabs, fabs(F[k])); }
+    const bool f_ok = fmaxabs > 0.0 && fmaxabs < 1e300;      // (a NaN fails both comparisons)
+    if (f_ok) {
+        const double sc = scalbn(1.0, -ilogb(fmaxabs));
+#pragma unroll
+        for (int k = 0; k < 9; ++k) F[k] *= sc;
+    }
+    const float INF = __int_as_float(0x7f800000);
     if (idx < jb.n_src) {
-        float4 s = segs[jb.src_off + idx];
+        float4 s = segs[job_src_segment(jb, idx)];
         double p[2][2] = {{double(s.x), double(s.y)}, {double(s.z), double(s.w)}};
-        float o[2][4];
+        const double rho = pretest_noise_factor(p[0][0], p[0][1], p[1][0], p[1][1]);
+        float o[2][4]; double A[2][3];
+        bool ok = f_ok && mode == 0;
 #pragma unroll
         for (int n = 0; n < 2; ++n) {
             double ax = F[0] * p[n][0] + F[1] * p[n][1] + F[2];
             double ay = F[3] * p[n][0] + F[4] * p[n][1] + F[5];
             double az = F[6] * p[n][0] + F[7] * p[n][1] + F[8];
-            o[n][0] = float(ax); o[n][1] = float(ay); o[n][2] = float(az); o[n][3] = float(2.0 * L3D_PRETEST_EPS_PX * sqrt(ax * ax + ay * ay));
-            // values the float tests cannot handle (non-finite, or so large that products overflow) switch the
-            // pre-test off for this endpoint: zero residuals and an infinite margin keep every pair
-            if (!(fabsf(o[n][0]) < 1e15f && fabsf(o[n][1]) < 1e15f && fabsf(o[n][2]) < 1e15f)) { o[n][0] = o[n][1] = o[n][2] = 0.f; o[n][3] = __int_as_float(0x7f800000); }
+            A[n][0] = ax / rho; A[n][1] = ay / rho; A[n][2] = az / rho;
+            o[n][0] = float(A[n][0]); o[n][1] = float(A[n][1]); o[n][2] = float(A[n][2]); o[n][3] = float(2.0 * L3D_PRETEST_EPS_PX * sqrt(ax * ax + ay * ay));
+            ok = ok && fabsf(o[n][0]) < L3D_PRETEST_MAXABS && fabsf(o[n][1]) < L3D_PRETEST_MAXABS && fabsf(o[n][2]) < L3D_PRETEST_MAXABS && o[n][3] < L3D_PRETEST_MAXABS;
+        }
+        SrcHoist1 h1;
+        h1.p = make_float4(float(A[0][0] + A[1][0]), float(A[0][1] + A[1][1]), float(A[0][2] + A[1][2]), 0.f);
+        h1.m = make_float4(float(A[0][0] - A[1][0]), float(A[0][1] - A[1][1]), float(A[0][2] - A[1][2]), 0.f);
+        // Values the float tests cannot handle switch the pre-test off for this segment: residuals of +1 at one endpoint
+        // and -1 at the other ("the epipolar line crosses the segment") and infinite margins keep every pair at both levels.
+        if (!ok) {
+            o[0][0] = o[0][1] = o[1][0] = o[1][1] = 0.f; o[0][2] = 1.f; o[1][2] = -1.f; o[0][3] = o[1][3] = INF;
+            h1.p = make_float4(0.f, 0.f, 0.f, 0.f); h1.m = make_float4(0.f, 0.f, 2.f, 0.f);      // sum 0, difference 2
         }
         SrcHoist h; h.a = make_float4(o[0][0], o[0][1], o[0][2], o[0][3]); h.b = make_float4(o[1][0], o[1][1], o[1][2], o[1][3]);
-        sh[jb.sh_off + idx] = h;
+        sh[jb.sh_off + idx] = h; sh1[jb.sh_off + idx] = h1;
         row_job[jb.row_off + idx] = blockIdx.y;          // row -> job, so that later kernels need no search
     }
     if (idx < jb.n_tgt) {
         float4 t = segs[jb.tgt_off + idx];
         double q[2][2] = {{double(t.x), double(t.y)}, {double(t.z), double(t.w)}};
+        const double kappa = pretest_noise_factor(q[0][0], q[0][1], q[1][0], q[1][1]);
         float w[2];
+        bool ok = f_ok && mode == 0 && fabsf(t.x) < L3D_PRETEST_MAXABS && fabsf(t.y) < L3D_PRETEST_MAXABS && fabsf(t.z) < L3D_PRETEST_MAXABS && fabsf(t.w) < L3D_PRETEST_MAXABS;
 #pragma unroll
         for (int m = 0; m < 2; ++m) {
             double ex = F[0] * q[m][0] + F[3] * q[m][1] + F[6];
             double ey = F[1] * q[m][0] + F[4] * q[m][1] + F[7];
-            w[m] = float(2.0 * L3D_PRETEST_EPS_PX * sqrt(ex * ex + ey * ey));
+            w[m] = float(2.0 * L3D_PRETEST_EPS_PX * kappa * sqrt(ex * ex + ey * ey));
+            ok = ok && w[m] > 1e-12f && w[m] < L3D_PRETEST_MAXABS;      // (w / 2)^2 must be a normal float
         }
-        if (!(fabsf(t.x) < 1e15f && fabsf(t.y) < 1e15f && fabsf(t.z) < 1e15f && fabsf(t.w) < 1e15f)) { t = make_float4(0.f, 0.f, 0.f, 0.f); w[0] = w[1] = __int_as_float(0x7f800000); }
+        if (!ok) { t = make_float4(0.f, 0.f, 0.f, 0.f); w[0] = w[1] = INF; }
         TgtHoist h; h.q = t; h.w = make_float2(w[0], w[1]); h.pad = make_float2(0.f, 0.f);
         th[jb.th_off + idx] = h;
     }
@@ -320,34 +417,131 @@ __device__ __forceinline__ void side_bounds(float e1a, float e1b, float e2a, flo
     U_lo = fmaxf(hi, 1.0f) - fminf(lo, 0.0f) - err;
 }
 
-// Two levels inside the kernel.  Level 1 is a sign test on the four residuals: the src
-// segment lies entirely on one side of an epipolar line when E[m][1] and E[m][2] have the
-// same sign; if that holds for both target endpoints, by more than L3D_PRETEST_EPS_PX pixels,
-// and both intersections fall beyond the same end of the segment, the overlap is zero
-// whatever the rounding.  About 96 % of all pairs end here.
-// Survivors are compacted through a per-warp queue and get the interval test (level 2).
-constexpr int PT_ROWS = 128;        // source segments per block tile
-constexpr int PT_COLS = 256;        // target segments per block tile: 8 warps x 32 lanes
-constexpr int PT_BLOCK = 256;
-constexpr int PT_Q = 1024 + 32;     // a 32-row chunk can leave up to 1024 survivors on top of 31 waiting ones
+// Packed FP32 pairs (sm_100: FFMA2 / FADD2 work on 64-bit register pairs, one issue slot for two operations; an operand
+// given as pk2(x, x) is encoded as a scalar that is broadcast to both halves).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void up2(f32x2 v, unsigned& lo, unsigned& hi) { asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
 
-// Sign bit of the result set = the pair survives level 1.  With two residuals a, b of one epipolar line,
-// |a + b| - ||a| - |b|| is twice the smaller magnitude when they share a sign and zero when they do not, so one
-// subtraction of the margin T = 2 eps |.| tests "same side, by more than eps pixels"; |a| - |b| tells beyond which
-// end the intersection falls.  Everything but the final bit operation runs on the FMA pipe.  Only the source side
-// is tested here: on the frozen scenes it rejects 95.8 % of all pairs and the mirrored test on the target side
-// would add 0.4 % for as many instructions again -- level 2 covers both sides anyway.
-__device__ __forceinline__ int pretest_level1(float e11, float e12, float e21, float e22, float Tq1, float Tq2)
+// Two levels, two kernels.  Level 1 (k_pretest) is a sign test on the four residuals: the src segment lies entirely on
+// one side of the epipolar line of q_m when E[m][1] and E[m][2] have the same sign; if that holds for both target
+// endpoints, by more than the allowance (L3D_PRETEST_EPS_PX pixels), and both intersections fall beyond the same end of
+// the segment (|E[m][1]| - |E[m][2]| has the same sign for m = 1, 2), the overlap is zero whatever the rounding.  About
+// 96 % of all pairs end here.  It works on the sum and the difference of the two residuals of a line,
+//     S_m = E[m][1] + E[m][2] = q_m . (A_1 + A_2),      D_m = E[m][1] - E[m][2] = q_m . (A_1 - A_2),
+// which the hoisted source vectors give directly (packed over m: 2 FFMA2 each).  |S_m| - |D_m| is twice the smaller
+// magnitude when the residuals share a sign and negative when they do not, so
+//     x_m = |S_m| - |D_m| - w_m                   sign set: not on one side by more than the allowance
+// and, when they share a sign, |E[m][1]| - |E[m][2]| = sign(S_m) D_m, so the sign of (S_1 D_1)(S_2 D_2) tells whether
+// the two intersections lie beyond different ends.  The verdict is the sign bit of x_1 | x_2 | (S_1 D_1)(S_2 D_2):
+// 4 FFMA2 + 2 FADD + 1 FADD2 + 1 FMUL2 + 1 FMUL on the FMA pipe (15 of its cycles per warp and 32 pairs), one LOP3 and one
+// funnel shift on the ALU pipe (2 cycles each, and on this part they are cycles the FMA pipe loses), no branch.
+// Only the source side is tested: on the frozen scenes it rejects 95.8 % of all pairs and the mirrored test on the
+// target side would add 0.4 % for as many instructions again -- level 2 covers both sides anyway.
+// Its output is one bit per pair, 32 source rows of one target column per word (what a lane holds after 32 rows),
+// stored [row group][column]: a warp's store is one coalesced line.
+// Level 2 (k_pretest2) reads those words, compacts the ~4 % survivors through a per-warp queue, applies the interval
+// test on full warps and writes the candidate bitmask [row][column / 32] and the candidates per row.
+constexpr int P1_COLS = 256;        // target segments per block: 4 warps x 32 lanes x 2 columns per lane
+constexpr int P1_BLOCK = 128;
+constexpr int P1_CHUNK = 128;       // source rows staged in shared memory at a time
+constexpr int P1_ROWS = 512;        // source rows per block
+
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+
+// QX = (q_1.x, q_2.x), QY = (q_1.y, q_2.y), nW = (-w_1, -w_2); Ap, Am: the hoisted sum and difference vectors of the row
+__device__ __forceinline__ unsigned pretest_level1(f32x2 QX, f32x2 QY, f32x2 nW, const float4 Ap, const float4 Am)
 {
-    // along the src segment: endpoint m of the target gives (e_m1, e_m2)
-    const float da1 = fabsf(e11) - fabsf(e12), da2 = fabsf(e21) - fabsf(e22);
-    const float xa1 = (fabsf(e11 + e12) - fabsf(da1)) - Tq1, xa2 = (fabsf(e21 + e22) - fabsf(da2)) - Tq2;
-    return __float_as_int(xa1) | __float_as_int(xa2) | __float_as_int(da1 * da2);     // >= 0: surely no overlap on the src side
+    const f32x2 S = fma2(QX, pk2(Ap.x, Ap.x), fma2(QY, pk2(Ap.y, Ap.y), pk2(Ap.z, Ap.z)));      // (S_1, S_2)
+    const f32x2 D = fma2(QX, pk2(Am.x, Am.x), fma2(QY, pk2(Am.y, Am.y), pk2(Am.z, Am.z)));      // (D_1, D_2)
+    unsigned sl, sh_, dl, dh;
+    up2(S, sl, sh_); up2(D, dl, dh);
+    const float y1 = fabsf(__uint_as_float(sl)) - fabsf(__uint_as_float(dl)), y2 = fabsf(__uint_as_float(sh_)) - fabsf(__uint_as_float(dh));
+    const f32x2 X = add2(pk2(y1, y2), nW);
+    const f32x2 P = mul2(S, D);
+    unsigned xl, xh, pl, ph;
+    up2(X, xl, xh); up2(P, pl, ph);
+    const float pp = __uint_as_float(pl) * __uint_as_float(ph);
+    return xl | xh | __float_as_uint(pp);      // sign bit clear: surely no overlap on the src side
 }
 
-__global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict__ sh, const TgtHoist* __restrict__ th,
-                                                      const JobDev* __restrict__ jobs, int n_jobs,
-                                                      unsigned* __restrict__ cand, int* __restrict__ cand_cnt)
+template <int UNROLL, int MINB>
+__global__ void __launch_bounds__(P1_BLOCK, MINB) k_pretest(const SrcHoist1* __restrict__ sh, const TgtHoist* __restrict__ th,
+                                                            const JobDev* __restrict__ jobs, int n_jobs, unsigned* __restrict__ l1)
+{
+    __shared__ float4 s_a[P1_CHUNK], s_b[P1_CHUNK];
+    __shared__ int s_job;
+    if (threadIdx.x == 0) {      // the job this block belongs to: blocks are numbered job by job (l1 blocks: l1_blk_off)
+        int lo = 0, hi = n_jobs - 1;
+        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (jobs[mid].l1_blk_off <= int(blockIdx.x)) lo = mid; else hi = mid - 1; }
+        s_job = lo;
+    }
+    __syncthreads();
+    const JobDev& jb = jobs[s_job];
+    const int local = blockIdx.x - jb.l1_blk_off;
+    const int col_blocks = (jb.n_tgt + P1_COLS - 1) / P1_COLS;
+    const int rb = local / col_blocks, cb = local - rb * col_blocks;
+    const int row_begin = rb * P1_ROWS, row_end = min(jb.n_src, row_begin + P1_ROWS);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int c0 = cb * P1_COLS + warp * 64 + lane, c1 = c0 + 32;
+    f32x2 QX0 = 0, QY0 = 0, NT0 = 0, QX1 = 0, QY1 = 0, NT1 = 0;
+    if (c0 < jb.n_tgt) { const TgtHoist h = th[jb.th_off + c0]; QX0 = pk2(h.q.x, h.q.z); QY0 = pk2(h.q.y, h.q.w); NT0 = pk2(-h.w.x, -h.w.y); }
+    if (c1 < jb.n_tgt) { const TgtHoist h = th[jb.th_off + c1]; QX1 = pk2(h.q.x, h.q.z); QY1 = pk2(h.q.y, h.q.w); NT1 = pk2(-h.w.x, -h.w.y); }
+    unsigned* out = l1 + jb.l1_off;
+    // the rows of the next chunk travel through registers while the current chunk is computed
+    float4 na = make_float4(0.f, 0.f, 0.f, 0.f), nb = na;
+    if (row_begin + tid < row_end) { const SrcHoist1 h = sh[jb.sh_off + row_begin + tid]; na = h.p; nb = h.m; }
+    for (int r0 = row_begin; r0 < row_end; r0 += P1_CHUNK) {
+        __syncthreads();                                   // the previous chunk has been read by every warp
+        s_a[tid] = na; s_b[tid] = nb;
+        __syncthreads();
+        na = make_float4(0.f, 0.f, 0.f, 0.f); nb = na;
+        if (r0 + P1_CHUNK + tid < row_end) { const SrcHoist1 h = sh[jb.sh_off + r0 + P1_CHUNK + tid]; na = h.p; nb = h.m; }
+        const int groups = min(P1_CHUNK, row_end - r0 + 31) >> 5;
+        for (int g = 0; g < groups; ++g) {
+            unsigned acc0 = 0u, acc1 = 0u;
+#pragma unroll UNROLL
+            for (int rr = 0; rr < 32; ++rr) {
+                const float4 A1 = s_a[g * 32 + rr], A2 = s_b[g * 32 + rr];          // broadcast
+                acc0 = __funnelshift_l(pretest_level1(QX0, QY0, NT0, A1, A2), acc0, 1);      // row rr of the group ends at bit 31 - rr
+                acc1 = __funnelshift_l(pretest_level1(QX1, QY1, NT1, A1, A2), acc1, 1);
+            }
+            const int left = row_end - (r0 + g * 32);      // rows beyond the job's last (zero hoists) are masked out
+            if (left < 32) { const unsigned m = ~((1u << (32 - left)) - 1u); acc0 &= m; acc1 &= m; }
+            const size_t word = size_t((r0 >> 5) + g) * size_t(jb.n_tgt);
+            if (c0 < jb.n_tgt) out[word + c0] = acc0;
+            if (c1 < jb.n_tgt) out[word + c1] = acc1;
+        }
+    }
+}
+
+// level 2 for one pair: false = an overlap surely misses a threshold
+__device__ __forceinline__ bool pretest_level2(const float4 A1, const float4 A2, const float4 qq, const float2 ww)
+{
+    const float e11 = fmaf(qq.x, A1.x, fmaf(qq.y, A1.y, A1.z));
+    const float e12 = fmaf(qq.x, A2.x, fmaf(qq.y, A2.y, A2.z));
+    const float e21 = fmaf(qq.z, A1.x, fmaf(qq.w, A1.y, A1.z));
+    const float e22 = fmaf(qq.z, A2.x, fmaf(qq.w, A2.y, A2.z));
+    float Ia, Ua, Ib, Ub;
+    side_bounds(e11, e12, e21, e22, ww.x, ww.y, Ia, Ua);      // along the src segment
+    side_bounds(e11, e21, e12, e22, A1.w, A2.w, Ib, Ub);      // along the tgt segment
+    // keep unless an overlap surely misses a threshold; NaN/inf comparisons keep
+    const bool drop = (Ia < L3D_PRETEST_LO * Ua) || (Ib < L3D_PRETEST_LO * Ub) ||
+                      ((Ia < L3D_PRETEST_HI * Ua) && (Ib < L3D_PRETEST_HI * Ub));
+    return !drop;
+}
+
+constexpr int PT_ROWS = 128;        // level 2: source segments per block tile (4 words of level-1 bits per lane)
+constexpr int PT_COLS = 256;        // target segments per block tile: 8 warps x 32 lanes
+constexpr int PT_BLOCK = 256;
+constexpr int PT_Q = 320;           // per-warp queue.  A word of 32 rows leaves about 43 survivors in a warp; a word
+                                    // that would not fit (degenerate geometry) is evaluated without the queue
+
+__global__ void __launch_bounds__(PT_BLOCK) k_pretest2(const SrcHoist* __restrict__ sh, const TgtHoist* __restrict__ th,
+                                                       const JobDev* __restrict__ jobs, int n_jobs, const unsigned* __restrict__ l1,
+                                                       unsigned* __restrict__ cand, int* __restrict__ cand_cnt)
 {
     __shared__ float4 s_a[PT_ROWS], s_b[PT_ROWS];
     __shared__ float4 s_q[PT_COLS];
@@ -363,6 +557,13 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
     const int col0 = cb * PT_COLS, row0 = rb * PT_ROWS;
     const int ncol = min(PT_COLS, jb.n_tgt - col0), nrow = min(PT_ROWS, jb.n_src - row0);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // the level-1 words of this lane's column: row groups row0 / 32 .. of the job
+    unsigned words[PT_ROWS / 32];
+    {
+        const unsigned* in = l1 + jb.l1_off + size_t(row0 >> 5) * size_t(jb.n_tgt) + col0 + tid;
+#pragma unroll
+        for (int g = 0; g < PT_ROWS / 32; ++g) words[g] = (tid < ncol && g * 32 < nrow) ? in[size_t(g) * size_t(jb.n_tgt)] : 0u;
+    }
     {
         if (tid < ncol) { TgtHoist h = th[jb.th_off + col0 + tid]; s_q[tid] = h.q; s_w[tid] = h.w; }
         else { s_q[tid] = make_float4(0.f, 0.f, 0.f, 0.f); s_w[tid] = make_float2(0.f, 0.f); }
@@ -373,63 +574,38 @@ __global__ void __launch_bounds__(PT_BLOCK) k_pretest(const SrcHoist* __restrict
         for (int k = tid; k < PT_ROWS * (PT_COLS / 32); k += PT_BLOCK) (&s_bits[0][0])[k] = 0u;
     }
     __syncthreads();
-    const bool valid = tid < ncol;
-    const float4 q = s_q[tid];
-    const float2 wq = s_w[tid];
     unsigned short* queue = s_queue[warp];
     int qn = 0;
     auto level2 = [&](int first, int count) {
         if (lane < count) {
             const unsigned e = queue[first + lane];
-            const int r = int(e >> 5), l = int(e & 31u);
-            const float4 A1 = s_a[r], A2 = s_b[r];
-            const float4 qq = s_q[warp * 32 + l];
-            const float2 ww = s_w[warp * 32 + l];
-            float e11 = fmaf(qq.x, A1.x, fmaf(qq.y, A1.y, A1.z));
-            float e12 = fmaf(qq.x, A2.x, fmaf(qq.y, A2.y, A2.z));
-            float e21 = fmaf(qq.z, A1.x, fmaf(qq.w, A1.y, A1.z));
-            float e22 = fmaf(qq.z, A2.x, fmaf(qq.w, A2.y, A2.z));
-            float Ia, Ua, Ib, Ub;
-            side_bounds(e11, e12, e21, e22, ww.x, ww.y, Ia, Ua);      // along the src segment
-            side_bounds(e11, e21, e12, e22, A1.w, A2.w, Ib, Ub);      // along the tgt segment
-            // keep unless an overlap surely misses a threshold; NaN/inf comparisons keep
-            const bool drop = (Ia < L3D_PRETEST_LO * Ua) || (Ib < L3D_PRETEST_LO * Ub) ||
-                              ((Ia < L3D_PRETEST_HI * Ua) && (Ib < L3D_PRETEST_HI * Ub));
-            if (!drop) atomicOr(&s_bits[r][warp], 1u << l);
+            const int r = int(e >> 5), c = warp * 32 + int(e & 31u);
+            if (pretest_level2(s_a[r], s_b[r], s_q[c], s_w[c])) atomicOr(&s_bits[r][warp], 1u << (e & 31u));
         }
     };
-    // Level 1 over 32 rows at a time: every lane shifts its verdicts into a register (no vote, no branch in the
-    // loop); the warp then compacts its up to 1024 survivors into the queue and runs level 2 on full warps.
-    for (int c = 0; c < nrow; c += 32) {
-        unsigned acc = 0u;
-#pragma unroll 8
-        for (int rr = 0; rr < 32; ++rr) {
-            const float4 A1 = s_a[c + rr], A2 = s_b[c + rr];          // broadcast
-            // E[m][n] = q_m . A_n
-            const float e11 = fmaf(q.x, A1.x, fmaf(q.y, A1.y, A1.z));
-            const float e12 = fmaf(q.x, A2.x, fmaf(q.y, A2.y, A2.z));
-            const float e21 = fmaf(q.z, A1.x, fmaf(q.w, A1.y, A1.z));
-            const float e22 = fmaf(q.z, A2.x, fmaf(q.w, A2.y, A2.z));
-            acc = __funnelshift_l(unsigned(pretest_level1(e11, e12, e21, e22, wq.x, wq.y)), acc, 1);   // row c + rr ends at bit 31 - rr
-        }
-        const int left = nrow - c;
-        if (left < 32) acc &= ~((1u << (32 - left)) - 1u);
-        if (!valid) acc = 0u;
+#pragma unroll
+    for (int g = 0; g < PT_ROWS / 32; ++g) {
+        unsigned acc = words[g];                             // bit 31 - rr = row g * 32 + rr of the tile
         const int n = __popc(acc);
         int pre = n;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += t; }
         const int total = __shfl_sync(0xffffffffu, pre, 31);
-        pre += qn - n;
-        while (acc) {
-            const int bit = 31 - __clz(acc);
-            acc &= ~(1u << bit);
-            queue[pre++] = (unsigned short)(((c + 31 - bit) << 5) | lane);
+        if (total == 0) continue;
+        if (qn + total <= PT_Q) {
+            pre += qn - n;
+            while (acc) { const int bit = 31 - __clz(acc); acc &= ~(1u << bit); queue[pre++] = (unsigned short)(((g * 32 + 31 - bit) << 5) | lane); }
+            qn += total;
+            __syncwarp();
+            while (qn >= 32) { level2(qn - 32, 32); qn -= 32; }
+            __syncwarp();
+        } else {            // more survivors than the queue holds: every lane walks its own bits
+            while (acc) {
+                const int bit = 31 - __clz(acc); acc &= ~(1u << bit);
+                const int r = g * 32 + 31 - bit;
+                if (pretest_level2(s_a[r], s_b[r], s_q[tid], s_w[tid])) atomicOr(&s_bits[r][warp], 1u << lane);
+            }
         }
-        qn += total;
-        __syncwarp();
-        while (qn >= 32) { level2(qn - 32, 32); qn -= 32; }
-        __syncwarp();
     }
     if (qn > 0) level2(0, qn);
     __syncthreads();
@@ -494,7 +670,7 @@ __global__ void __launch_bounds__(EF_T, 6) k_exact_flat(const float4* __restrict
         const int grow = c_row[c];
         job = row_job[grow];
         const JobDev& jb = jobs[job];
-        ok1 = xpair_overlap(segs[jb.src_off + (grow - jb.row_off)], segs[jb.tgt_off + c_col[c]], jb.F, is);
+        ok1 = xpair_overlap(segs[job_src_segment(jb, grow - jb.row_off)], segs[jb.tgt_off + c_col[c]], jb.F, is);
         c_ok[c] = 0;
     }
     // block-wide ordered compaction of the survivors
@@ -519,7 +695,7 @@ __global__ void __launch_bounds__(EF_T, 6) k_exact_flat(const float4* __restrict
         i2.ax = s_is[0][tid]; i2.ay = s_is[1][tid]; i2.bx = s_is[2][tid]; i2.by = s_is[3][tid];
         i2.cx = s_is[4][tid]; i2.cy = s_is[5][tid]; i2.dx = s_is[6][tid]; i2.dy = s_is[7][tid];
         float4 dep;
-        const bool ok = xpair_depths(segs[jb.src_off + (grow - jb.row_off)], segs[jb.tgt_off + c_col[cc]], i2, jb.RtKinv_s, jb.RtKinv_t,
+        const bool ok = xpair_depths(segs[job_src_segment(jb, grow - jb.row_off)], segs[jb.tgt_off + c_col[cc]], i2, jb.RtKinv_s, jb.RtKinv_t,
                                      mk3(jb.C_s[0], jb.C_s[1], jb.C_s[2]), mk3(jb.C_t[0], jb.C_t[1], jb.C_t[2]), dep);
         if (ok) { c_ok[cc] = 1; c_dep[cc] = dep; atomicAdd(&raw_cnt[grow], 1); }
     }
@@ -565,6 +741,25 @@ __global__ void k_range_max(const int* __restrict__ v, const int* __restrict__ b
     }
 }
 
+// out[b] = sum over v[begin[b] .. begin[b] + len[b]) in 64 bits (the 32-bit scan of the same values may have wrapped)
+__global__ void k_range_sum64(const int* __restrict__ v, const int* __restrict__ begin, const int* __restrict__ len, unsigned long long* __restrict__ out)
+{
+    __shared__ unsigned long long sh[32];
+    const int b0 = begin[blockIdx.x], n = len[blockIdx.x];
+    unsigned long long s = 0ull;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += (unsigned long long)(unsigned)v[b0 + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        s = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (threadIdx.x == 0) out[blockIdx.x] = s;
+    }
+}
+
 // dst[k] = src[idx[k]]
 __global__ void k_gather_int(const int* __restrict__ src, const int* __restrict__ idx, int n, int* __restrict__ dst)
 {
@@ -573,7 +768,7 @@ __global__ void k_gather_int(const int* __restrict__ src, const int* __restrict_
 }
 
 // counts of the delivered records per (row, cam) for the cams in mode 1
-__device__ __forceinline__ void b_gather_counts(const CamTable* __restrict__ cams, int n_cams, int n_src, const int* __restrict__ raw_cnt, int* __restrict__ cnt)
+__device__ __forceinline__ void b_gather_counts(const CamTable* __restrict__ cams, int n_cams, int n_src, const SrcTable& src, const int* __restrict__ raw_cnt, int* __restrict__ cnt)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     const int cam = blockIdx.y;
@@ -581,12 +776,12 @@ __device__ __forceinline__ void b_gather_counts(const CamTable* __restrict__ cam
     const CamTable& ct = cams[cam];
     int c = 0;
     if (ct.mode == 0) c = raw_cnt[ct.row_off + row];
-    else if (ct.mode == 1) c = ct.t_start ? (ct.t_start[row + 1] - ct.t_start[row]) : 0;
+    else if (ct.mode == 1) { const int sg = row_segment(src, row); c = ct.t_start ? (ct.t_start[sg + 1] - ct.t_start[sg]) : 0; }
     cnt[row * n_cams + cam] = c;
 }
 
 // fill: one warp per (row, cam) copies the row's records to their final place
-__device__ __forceinline__ void b_fill(const CamTable* __restrict__ cams, int n_cams, int n_src,
+__device__ __forceinline__ void b_fill(const CamTable* __restrict__ cams, int n_cams, int n_src, const SrcTable& src,
                        const int* __restrict__ off, const int* __restrict__ cand_off,
                        const int* __restrict__ stage_col, const float4* __restrict__ stage_dep, const unsigned char* __restrict__ stage_ok,
                        int4* __restrict__ m_ids, float4* __restrict__ m_dep)
@@ -597,6 +792,7 @@ __device__ __forceinline__ void b_fill(const CamTable* __restrict__ cams, int n_
     const int o = off[gw], n = off[gw + 1] - o;
     if (n == 0) return;
     const CamTable& ct = cams[cam];
+    const int sg = row_segment(src, row);            // match ids carry the segment (x) and this process's row (w)
     if (ct.mode == 0) {
         const int b = cand_off[ct.row_off + row], e = cand_off[ct.row_off + row + 1];
         int w = o;
@@ -604,18 +800,18 @@ __device__ __forceinline__ void b_fill(const CamTable* __restrict__ cams, int n_
             const int k = k0 + lane;
             const bool ok = k < e && stage_ok[k] != 0;
             const unsigned m = __ballot_sync(0xffffffffu, ok);
-            if (ok) { const int r = w + __popc(m & ((1u << lane) - 1u)); m_ids[r] = make_int4(row, cam, stage_col[k], 0); m_dep[r] = stage_dep[k]; }
+            if (ok) { const int r = w + __popc(m & ((1u << lane) - 1u)); m_ids[r] = make_int4(sg, cam, stage_col[k], row); m_dep[r] = stage_dep[k]; }
             w += __popc(m);
         }
     } else if (ct.mode == 1) {
         // delivered records of one segment arrive in the order of the sender's atomics; they go out in ascending
         // target id (ids are unique within a group and groups are tiny: each record counts the smaller ones)
-        const int b = ct.t_start[row];
+        const int b = ct.t_start[sg];
         for (int k = lane; k < n; k += 32) {
             const int me = ct.t_tgt[b + k];
             int rank = 0;
             for (int i = 0; i < n; ++i) rank += (ct.t_tgt[b + i] < me);
-            m_ids[o + rank] = make_int4(row, cam, me, 0); m_dep[o + rank] = ct.t_dep[b + k];
+            m_ids[o + rank] = make_int4(sg, cam, me, row); m_dep[o + rank] = ct.t_dep[b + k];
         }
     }
 }
@@ -696,7 +892,7 @@ __device__ __forceinline__ void b_score(const float4* __restrict__ segs, const C
     s_yd[tid] = my_d;
     for (int c = 0; c < n_cams; ++c) s_max[c * SC_T + tid] = 0;
     // per-segment invariants (cudawrapper.cu:638-645)
-    const float4 sg = segs[src.seg_off + row];
+    const float4 sg = segs[src.seg_off + row_segment(src, row)];
     const V3 p1 = mk3(sg.x, sg.y, 1.0f), p2 = mk3(sg.z, sg.w, 1.0f);
     const V3 ray1 = xnormalize(xmat3(src.RtKinv, p1, false)), ray2 = xnormalize(xmat3(src.RtKinv, p2, false));
     const V3 C = mk3(src.C[0], src.C[1], src.C[2]);
@@ -874,7 +1070,7 @@ __device__ __forceinline__ void b_score_window(const float4* __restrict__ segs, 
     if (live) { const unsigned pl = g_pl[seg_start + y]; my_cam = int(pl >> 20); my_idx = int(pl & 0xfffffu); my_d = make_float2(g_k[seg_start + y], g_d2[seg_start + y]); }
     s_yd[tid] = my_d;
     for (int c = 0; c < n_cams; ++c) s_max[c * SC_T + tid] = 0;
-    const float4 sg = segs[src.seg_off + row];
+    const float4 sg = segs[src.seg_off + row_segment(src, row)];
     const V3 p1 = mk3(sg.x, sg.y, 1.0f), p2 = mk3(sg.z, sg.w, 1.0f);
     const V3 ray1 = xnormalize(xmat3(src.RtKinv, p1, false)), ray2 = xnormalize(xmat3(src.RtKinv, p2, false));
     const V3 C = mk3(src.C[0], src.C[1], src.C[2]);
@@ -945,12 +1141,12 @@ __device__ __forceinline__ void b_reduce_matches(const int* __restrict__ Mptr, c
     if (k < M) {
         const float c = score[k]; const int4 id = m_ids[k];
         keep = c > 1.0f;
-        const int* o = off + id.x * n_cams;
+        const int* o = off + id.w * n_cams;
         all = (unsigned long long)(o[n_cams] - o[0]);                 // sum over the matches of their segment's size = sum of squares
         same = (unsigned long long)(o[id.y + 1] - o[id.y]);
         if (c > 0.0f) {
             const unsigned long long key = ((unsigned long long)__float_as_uint(c) << 32) | (unsigned long long)(0xffffffffu - unsigned(k));
-            if (key > best[id.x]) atomicMax(&best[id.x], key);
+            if (key > best[id.w]) atomicMax(&best[id.w], key);
         }
     }
 #pragma unroll
@@ -1024,10 +1220,11 @@ __device__ float block_median_select(const float* __restrict__ dsamples, int n)
 __device__ __forceinline__ void b_finish_view(float* __restrict__ dsamples, int n_samples, const unsigned long long* __restrict__ best, const float4* __restrict__ m_dep,
                                                       const int* __restrict__ M, const int* __restrict__ F,
                                                       const unsigned long long* __restrict__ iters, const int* __restrict__ start, int stride, int n_deliver,
-                                                      int* __restrict__ out)
+                                                      int* __restrict__ out, bool samples_ready)
 {
     // depth samples: both depths of every segment's best match if its score exceeds 0.5 (cudawrapper.cu:1090-1110)
-    for (int row = threadIdx.x; 2 * row < n_samples; row += MS_T) {
+    // (with several GPUs on one scene they were written by k_mr_prepare and combined over the ranks already)
+    for (int row = threadIdx.x; !samples_ready && 2 * row < n_samples; row += MS_T) {
         const unsigned long long key = best[row];
         float a = INFINITY, b = INFINITY;
         if (__uint_as_float(unsigned(key >> 32)) > 0.5f) { const float4 d = m_dep[0xffffffffu - unsigned(key & 0xffffffffull)]; a = d.x; b = d.y; }
@@ -1133,6 +1330,20 @@ struct VArgs {
     // hand-over
     int delivering, stride, n_keys, n_deliver; int* dl_start; int* dl_tgt; float4* dl_dep;
     int* vres;
+    // several GPUs on one scene (l3d_comm_init): this process holds the rows row_first + r * row_stride of the view
+    int mr, n_seg_full;
+};
+
+// What one rank reports about one view of a group (all-gathered): its output records, its matches, its iteration counts.
+struct RankRec { int F, M; unsigned long long iters_all, iters_same; int pad[2]; };
+// Where the ranks' records of a group are: in the all-gather buffer (rank-major, every rank's records of the group's
+// views back to back) and in the group's view-major buffer, and where each view's hand-over records go.
+constexpr int MR_MAX_RANKS = 16;
+struct MrLayout {
+    int src_off[MR_MAX_RANKS][8], dst_off[MR_MAX_RANKS][8], cnt[MR_MAX_RANKS][8];      // [rank][view of the group], in records
+    int view_off[8], view_cnt[8];
+    int* dl_tgt[8]; float4* dl_dep[8];
+    int padded;                                                                          // records per rank in the all-gather buffer
 };
 #define L3D_VIEW(dim) L3D_PDL_PROLOGUE(); const VArgs& va = all[blockIdx.dim]
 
@@ -1140,7 +1351,7 @@ __global__ void k_gather_counts(const VArgs* __restrict__ all)
 {
     L3D_VIEW(z);
     if (int(blockIdx.y) >= va.n_cams) return;
-    b_gather_counts(va.cams, va.n_cams, va.n_src, va.raw_cnt, va.cnt);
+    b_gather_counts(va.cams, va.n_cams, va.n_src, va.src, va.raw_cnt, va.cnt);
 }
 // which = 0: count matrix -> offsets; 1: hand-over group sizes -> group starts.  One block per view.
 __global__ void __launch_bounds__(SCAN_T) k_scan_views(const VArgs* __restrict__ all, int which)
@@ -1153,7 +1364,7 @@ __global__ void k_fill(const VArgs* __restrict__ all, const float4* __restrict__
 {
     L3D_VIEW(y);
     (void)segs;
-    b_fill(va.cams, va.n_cams, va.n_src, va.off, va.cand_off, va.stage_col, va.stage_dep, va.stage_ok, va.mids, va.mdep);
+    b_fill(va.cams, va.n_cams, va.n_src, va.src, va.off, va.cand_off, va.stage_col, va.stage_dep, va.stage_ok, va.mids, va.mdep);
 }
 __global__ void __launch_bounds__(BK_T) k_bucket_segments(const VArgs* __restrict__ all)
 {
@@ -1205,8 +1416,77 @@ __global__ void __launch_bounds__(MS_T) k_finish_view(const VArgs* __restrict__ 
 {
     L3D_VIEW(y);
     const int* Mptr = va.off + va.n_src * va.n_cams;
-    b_finish_view(va.dsamples, va.scored ? 2 * va.n_src : 0, va.best, va.mdep, Mptr, va.scored ? va.Fout : Mptr, va.scored ? va.iters : nullptr,
-                  va.delivering ? va.dl_start : nullptr, va.stride, va.delivering ? va.n_deliver : 0, va.vres);
+    b_finish_view(va.dsamples, va.scored ? 2 * (va.mr ? va.n_seg_full : va.n_src) : 0, va.best, va.mdep, Mptr, va.scored ? va.Fout : Mptr, va.scored ? va.iters : nullptr,
+                  va.delivering ? va.dl_start : nullptr, va.stride, va.delivering ? va.n_deliver : 0, va.vres, va.mr != 0);
+}
+
+// ------------------------------------------------------------------------------------------
+// Several GPUs on ONE scene (l3d_comm_init).  The segments of every view are dealt out to the ranks in turn (segment
+// s belongs to rank s mod ranks), so each rank pair-tests, assembles and scores its rows of every view, and the views
+// are still processed level by level.  What a later view needs from an earlier one -- the reversed records, grouped by
+// ITS segments -- is put together from all ranks' output records of the group:
+//   k_mr_prepare   depth samples of all segments (infinity for other ranks' rows) and this rank's record of each view
+//   NCCL           all-gather of the records, min-all-reduce of the samples, sum-all-reduce of the hand-over group sizes
+//   (host: reads the counts, sizes the buffers)
+//   k_mr_pack      this rank's output records of the group's views back to back
+//   NCCL           all-gather of the packed records
+//   k_mr_unpack    all ranks' records, view by view: what is handed to the host, and what is handed over
+//   k_mr_deliver_scatter   as k_deliver_scatter, over all ranks' records
+// ------------------------------------------------------------------------------------------
+__global__ void k_mr_prepare(const VArgs* __restrict__ all, RankRec* __restrict__ rec)
+{
+    L3D_VIEW(y);
+    const int* Mptr = va.off + va.n_src * va.n_cams;
+    if (va.scored) {
+        for (int sg = blockIdx.x * blockDim.x + threadIdx.x; sg < va.n_seg_full; sg += gridDim.x * blockDim.x) {
+            float a = INFINITY, b = INFINITY;
+            const int d = sg - va.src.row_first;
+            if (d >= 0 && d % va.src.row_stride == 0) {
+                const unsigned long long key = va.best[d / va.src.row_stride];
+                if (__uint_as_float(unsigned(key >> 32)) > 0.5f) { const float4 dp = va.mdep[0xffffffffu - unsigned(key & 0xffffffffull)]; a = dp.x; b = dp.y; }
+            }
+            va.dsamples[2 * sg] = a; va.dsamples[2 * sg + 1] = b;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        RankRec r; r.M = *Mptr; r.F = va.scored ? *va.Fout : *Mptr;
+        r.iters_all = va.scored ? va.iters[0] : 0ull; r.iters_same = va.scored ? va.iters[1] : 0ull; r.pad[0] = r.pad[1] = 0;
+        rec[blockIdx.y] = r;
+    }
+}
+__global__ void k_mr_pack(const VArgs* __restrict__ all, const RankRec* __restrict__ rec, l3d_match* __restrict__ send)
+{
+    const VArgs& va = all[blockIdx.y];
+    int off = 0;
+    for (int v = 0; v < int(blockIdx.y); ++v) off += rec[v].F;
+    const int n = rec[blockIdx.y].F;
+    const uint4* src = reinterpret_cast<const uint4*>(va.filtered);
+    uint4* dst = reinterpret_cast<uint4*>(send + off);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * n; i += gridDim.x * blockDim.x) dst[i] = src[i];
+}
+__global__ void k_mr_unpack(const l3d_match* __restrict__ recv, l3d_match* __restrict__ allf, MrLayout lay)
+{
+    const int v = blockIdx.y, r = blockIdx.z;
+    const int n = lay.cnt[r][v];
+    const uint4* src = reinterpret_cast<const uint4*>(recv + size_t(r) * lay.padded + lay.src_off[r][v]);
+    uint4* dst = reinterpret_cast<uint4*>(allf + lay.dst_off[r][v]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * n; i += gridDim.x * blockDim.x) dst[i] = src[i];
+}
+__global__ void k_mr_deliver_scatter(const VArgs* __restrict__ all, const l3d_match* __restrict__ allf, MrLayout lay)
+{
+    const VArgs& va = all[blockIdx.y];
+    if (!va.delivering) return;
+    const int n = lay.view_cnt[blockIdx.y];
+    const l3d_match* f = allf + lay.view_off[blockIdx.y];
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const l3d_match m = f[k];
+        const int d = va.cams[m.cam].deliver;
+        if (d < 0) continue;
+        const int key = d * va.stride + m.tgt_seg;
+        const int pos = va.dl_start[key] + atomicAdd(&va.cursor[key], 1);
+        lay.dl_tgt[blockIdx.y][pos] = m.src_seg;
+        lay.dl_dep[blockIdx.y][pos] = make_float4(m.depths[2], m.depths[3], m.depths[0], m.depths[1]);     // line3D.cc:852-855
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1435,16 +1715,42 @@ __global__ void k_debug_math(int which, const float* __restrict__ in, float* __r
     out[k] = which == 0 ? xexpf(in[k]) : xacosf(in[k]);
 }
 
-// FP32 FFMA throughput probe
-__global__ void k_fma_probe(float* out, int iters)
+// FP32 throughput probes: register-only chains, operands in registers (not immediates), 16 independent chains per
+// thread, 8 steps unrolled: 128 FFMA (64 FFMA2) per loop trip against 3 loop instructions.
+__global__ void k_fma_probe(float* out, int iters, float b, float c)
 {
-    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
-    const float b = 1.0000001f, c = 1e-7f;
+    float a[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) a[k] = threadIdx.x * 1e-3f + float(k);
     for (int i = 0; i < iters; ++i) {
-        a0 = fmaf(a0, b, c); a1 = fmaf(a1, b, c); a2 = fmaf(a2, b, c); a3 = fmaf(a3, b, c);
-        a4 = fmaf(a4, b, c); a5 = fmaf(a5, b, c); a6 = fmaf(a6, b, c); a7 = fmaf(a7, b, c);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) a[k] = fmaf(a[k], b, c);
+        }
     }
-    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) s += a[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+__global__ void k_fma2_probe(float* out, int iters, float b, float c)
+{
+    f32x2 a[8];
+    const f32x2 B = pk2(b, b * 1.0000001f), C = pk2(c, c * 1.5f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = pk2(threadIdx.x * 1e-3f + float(k), threadIdx.x * 2e-3f + float(k));
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = fma2(a[k], B, C);
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { unsigned lo, hi; up2(a[k], lo, hi); s += __uint_as_float(lo) + __uint_as_float(hi); }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
 }  // namespace
@@ -1467,7 +1773,7 @@ struct DeliverBuf { int* start = nullptr; int* tgt = nullptr; float4* dep = null
 struct PlannedView {           // one entry of l3d_plan_matching
     int view = -1;
     std::vector<l3d_neighbor> nb;
-    uint64_t pair_tests = 0;
+    uint64_t pair_tests = 0;     // of this process; with several GPUs on one scene: of the rank with most rows (the same number on every rank)
     int first_job = -1;         // valid while the view's batch is resident
     uint64_t n_candidates = 0;
 };
@@ -1505,11 +1811,19 @@ struct ViewGroup {
     HBuf<VArgs> h_args; DBuf<VArgs> d_args;
     HBuf<CamTable> h_cams; DBuf<CamTable> d_cams; size_t cam_off[VG_MAX + 1];
     DBuf<int> d_zero; DBuf<int> d_vres; HBuf<int> h_vres; int res_stride = 8;     // result ints per view: 8 scalars + one count per hand-over slot
+    // several GPUs on one scene: depth samples of the group's views (one buffer: one all-reduce), the ranks' records,
+    // the packed records of this rank, all ranks' packed records, all ranks' records view by view
+    DBuf<float> d_samples; size_t samples_total = 0; size_t hist_off = 0, hist_total = 0;
+    DBuf<RankRec> d_myrec, d_allrec; HBuf<RankRec> h_allrec;
+    DBuf<l3d_match> d_send, d_recv, d_allf;
+    cudaEvent_t ev_x[2] = {nullptr, nullptr};      // [0] exchange done on the main stream, [1] this group's records copied to the host
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [0] results on the host, [2..5] stage boundaries
     void release()
     {
         for (int k = 0; k < VG_MAX; ++k) slot[k].release();
         h_args.release(); d_args.release(); h_cams.release(); d_cams.release(); d_zero.release(); d_vres.release(); h_vres.release();
+        d_samples.release(); d_myrec.release(); d_allrec.release(); h_allrec.release(); d_send.release(); d_recv.release(); d_allf.release();
+        for (int k = 0; k < 2; ++k) if (ev_x[k]) { cudaEventDestroy(ev_x[k]); ev_x[k] = nullptr; }
         for (int k = 0; k < 6; ++k) if (ev[k]) { cudaEventDestroy(ev[k]); ev[k] = nullptr; }
     }
 };
@@ -1547,24 +1861,25 @@ struct PhaseASet {
     std::string err;
     uint64_t launches = 0;
     size_t begin = 0, end = 0;                 // plan entries covered
-    DBuf<SrcHoist> d_sh; DBuf<TgtHoist> d_th; DBuf<int> d_row_job;
-    DBuf<unsigned> d_cand; DBuf<int> d_tile_sums, d_total;
+    DBuf<SrcHoist> d_sh; DBuf<SrcHoist1> d_sh1; DBuf<TgtHoist> d_th; DBuf<int> d_row_job;
+    DBuf<unsigned> d_cand, d_l1; DBuf<int> d_tile_sums, d_total;
     DBuf<int> d_stage_col, d_stage_row; DBuf<float4> d_stage_dep; DBuf<unsigned char> d_stage_ok;
     DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
     std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands, job_raw; std::vector<int> job_rowmax, job_raw_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
+    DBuf<unsigned long long> d_job_sum64; HBuf<unsigned long long> h_job_sum64;
     bool pa_ms_pending = false;
     cudaEvent_t pa_ev[3] = {nullptr, nullptr, nullptr};
-    cudaEvent_t pa_kev[4] = {nullptr, nullptr, nullptr, nullptr};   // around the k_pretest and k_exact_flat launches
+    cudaEvent_t pa_kev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // [0][1] around k_pretest, [1][4] around k_pretest2, [2][3] around k_exact_flat
     bool pa_kev_set[2] = {false, false};
     HBuf<int> h_res;
     void release()
     {
-        d_sh.release(); d_th.release(); d_row_job.release(); d_cand.release(); d_tile_sums.release(); d_total.release();
+        d_sh.release(); d_sh1.release(); d_th.release(); d_row_job.release(); d_cand.release(); d_l1.release(); d_tile_sums.release(); d_total.release();
         d_stage_col.release(); d_stage_row.release(); d_stage_dep.release(); d_stage_ok.release(); d_jobs.release();
         d_pa_cnt.release(); d_pa_off.release(); d_pa_raw.release(); d_pa_idx.release(); d_pa_tot.release();
-        d_rm_begin.release(); d_rm_len.release(); d_rm_out.release(); h_res.release();
+        d_rm_begin.release(); d_rm_len.release(); d_rm_out.release(); h_res.release(); d_job_sum64.release(); h_job_sum64.release();
         for (int k = 0; k < 3; ++k) if (pa_ev[k]) { cudaEventDestroy(pa_ev[k]); pa_ev[k] = nullptr; }
-        for (int k = 0; k < 4; ++k) if (pa_kev[k]) { cudaEventDestroy(pa_kev[k]); pa_kev[k] = nullptr; }
+        for (int k = 0; k < 5; ++k) if (pa_kev[k]) { cudaEventDestroy(pa_kev[k]); pa_kev[k] = nullptr; }
         if (stream) { cudaStreamDestroy(stream); stream = nullptr; }
     }
 };
@@ -1573,6 +1888,9 @@ struct l3d_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     std::string err;
+    // several GPUs on one scene (l3d_comm_init)
+    NcclApi* nccl = nullptr; ncclComm_t comm = nullptr; int rank = 0, world = 1, result_root = -1;
+    bool copies_pending = false;
     uint64_t launches = 0;
     // views
     int V = 0;
@@ -1591,14 +1909,16 @@ struct l3d_ctx {
     std::thread pa_worker; bool pa_worker_active = false; int pa_worker_rc = 0;
     std::vector<PlannedView> plan;                  // as announced (the order of the caller's calls)
     std::vector<size_t> order;                      // plan entries in the order they are executed: by dependency level
-    struct Stashed { l3d_match_result res; bool ready; float ms[6], kms[2]; };
+    struct Stashed { l3d_match_result res; bool ready; float ms[6], kms[3]; };
     std::vector<Stashed> results;                   // per plan entry, until the caller asks for it
     size_t call_next = 0; bool plan_started = false, run_copy_back = true;
     size_t batch_begin = 0, batch_end = 0;          // positions in `order` whose pair tests are resident
     uint64_t pair_budget = 24000000000ull;          // most pair tests of one batch (3 GB of candidate bits)
     uint64_t batch_pairs = 24000000000ull;          // pair tests per batch of the announced schedule (l3d_plan_matching)
     uint64_t batch_override = 0;                    // l3d_debug_set_batch_pairs
-    float pa_kernel_ms[2] = {0.f, 0.f};
+    int pretest_mode = 0;                           // l3d_debug_set_pretest
+    uint64_t cand_limit = 0x7fff0000ull;            // most candidates of one batch (32-bit candidate index); l3d_debug_set_candidate_limit
+    float pa_kernel_ms[3] = {0.f, 0.f, 0.f};
     // views in flight: positions [fly_begin, fly_end) of `order` are on the GPU, as the groups [grp_begin, grp_end)
     ViewGroup grp[2]; size_t grp_begin = 0, grp_end = 0;
     size_t fly_begin = 0, fly_end = 0; std::vector<int> level;
@@ -1657,6 +1977,9 @@ int scan_exclusive(C* ctx, const int* in, int* out /* n + 1 */, int n)
     return 0;
 }
 
+// rows of a view this process holds: all of them, or every world-th segment starting at its rank
+inline int local_rows(const l3d_ctx* ctx, int n_segments) { return ctx->world <= 1 ? n_segments : (n_segments > ctx->rank ? (n_segments - ctx->rank + ctx->world - 1) / ctx->world : 0); }
+
 int fetch_int(l3d_ctx* ctx, const int* dptr, int* out)
 {
     L3D_CUDA(ctx->h_ints.ensure(16));
@@ -1680,35 +2003,48 @@ int run_phase_a(l3d_ctx* cx, PhaseASet* ctx, const std::vector<JobHost>& jh)   /
     ctx->job_raw.assign(size_t(n_jobs), 0); ctx->job_raw_rowmax.assign(size_t(n_jobs), 0);
     ctx->pa_kev_set[0] = ctx->pa_kev_set[1] = false;
     if (n_jobs == 0) return 0;
-    long long sh_tot = 0, th_tot = 0, words = 0, rows = 0, blocks = 0;
+    long long sh_tot = 0, th_tot = 0, words = 0, rows = 0, blocks = 0, l1_words = 0, l1_blocks = 0;
     int max_n = 1;
     for (int j = 0; j < n_jobs; ++j) {
         const l3d_view& sv = cx->views[jh[j].src_view]; const l3d_view& tv = cx->views[jh[j].tgt_view];
         JobDev& d = ctx->jobs_host[j];
         memcpy(d.F, jh[j].F, sizeof d.F); memcpy(d.RtKinv_s, sv.RtKinv, sizeof d.RtKinv_s); memcpy(d.RtKinv_t, tv.RtKinv, sizeof d.RtKinv_t);
         memcpy(d.C_s, sv.C, sizeof d.C_s); memcpy(d.C_t, tv.C, sizeof d.C_t);
-        d.src_off = cx->seg_off[jh[j].src_view]; d.n_src = sv.n_segments; d.tgt_off = cx->seg_off[jh[j].tgt_view]; d.n_tgt = tv.n_segments;
+        d.src_off = cx->seg_off[jh[j].src_view]; d.n_src = local_rows(cx, sv.n_segments); d.src_first = cx->world > 1 ? cx->rank : 0; d.src_stride = cx->world > 1 ? cx->world : 1; d.tgt_off = cx->seg_off[jh[j].tgt_view]; d.n_tgt = tv.n_segments;
         d.sh_off = int(sh_tot); d.th_off = int(th_tot); d.cand_off = words; d.wpr = (d.n_tgt + 31) / 32;
         d.row_off = int(rows); d.blk_off = int(blocks); d.col_blocks = std::max((d.n_tgt + PT_COLS - 1) / PT_COLS, 1);
         sh_tot += d.n_src; th_tot += d.n_tgt; words += (long long)d.n_src * d.wpr; rows += d.n_src;
         blocks += (long long)((d.n_src + PT_ROWS - 1) / PT_ROWS) * d.col_blocks;
+        d.l1_off = l1_words; d.l1_blk_off = int(l1_blocks);
+        l1_words += (long long)((d.n_src + 31) / 32) * d.n_tgt;
+        l1_blocks += (long long)((d.n_src + P1_ROWS - 1) / P1_ROWS) * ((d.n_tgt + P1_COLS - 1) / P1_COLS);
         max_n = std::max(max_n, std::max(d.n_src, d.n_tgt));
-        if (sh_tot > 0x7fffffff || th_tot > 0x7fffffff || rows > 0x7ffffff0 || blocks > 0x7ffffff0) { ctx->err = "phase A: batch too large"; return 1; }
+        if (sh_tot > 0x7fffffff || th_tot > 0x7fffffff || rows > 0x7ffffff0 || blocks > 0x7ffffff0 || l1_blocks > 0x7ffffff0) { ctx->err = "phase A: batch too large"; return 1; }
     }
     L3D_CUDA(ctx->d_jobs.ensure(size_t(n_jobs)));
     L3D_CUDA(cudaMemcpyAsync(ctx->d_jobs.p, ctx->jobs_host.data(), sizeof(JobDev) * size_t(n_jobs), cudaMemcpyHostToDevice, st));
-    L3D_CUDA(ctx->d_sh.ensure(size_t(std::max<long long>(sh_tot, 1)))); L3D_CUDA(ctx->d_th.ensure(size_t(std::max<long long>(th_tot, 1))));
+    L3D_CUDA(ctx->d_sh.ensure(size_t(std::max<long long>(sh_tot, 1)))); L3D_CUDA(ctx->d_sh1.ensure(size_t(std::max<long long>(sh_tot, 1)))); L3D_CUDA(ctx->d_th.ensure(size_t(std::max<long long>(th_tot, 1))));
     L3D_CUDA(ctx->d_cand.ensure(size_t(std::max<long long>(words, 1)))); L3D_CUDA(ctx->d_row_job.ensure(size_t(rows) + 1));
+    L3D_CUDA(ctx->d_l1.ensure(size_t(std::max<long long>(l1_words, 1))));
     L3D_CUDA(ctx->d_pa_cnt.ensure(size_t(rows) + 1)); L3D_CUDA(ctx->d_pa_off.ensure(size_t(rows) + 2)); L3D_CUDA(ctx->d_pa_raw.ensure(size_t(rows) + 1));
     L3D_CUDA(cudaMemsetAsync(ctx->d_pa_cnt.p, 0, sizeof(int) * (size_t(rows) + 1), st));
     L3D_CUDA(cudaEventRecord(ctx->pa_ev[0], st));
     if (rows > 0 && blocks > 0) {
-        k_hoist<<<dim3((max_n + 127) / 128, n_jobs), 128, 0, st>>>(cx->d_segs.p, ctx->d_jobs.p, ctx->d_sh.p, ctx->d_th.p, ctx->d_row_job.p);
+        k_hoist<<<dim3((max_n + 127) / 128, n_jobs), 128, 0, st>>>(cx->d_segs.p, ctx->d_jobs.p, ctx->d_sh.p, ctx->d_sh1.p, ctx->d_th.p, ctx->d_row_job.p, cx->pretest_mode);
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[0], st));
-        k_pretest<<<unsigned(blocks), PT_BLOCK, 0, st>>>(ctx->d_sh.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_cand.p, ctx->d_pa_cnt.p);
+        {
+            static const int variant = getenv("L3D_P1_VARIANT") ? atoi(getenv("L3D_P1_VARIANT")) : 0;
+            if (variant == 1) k_pretest<4, 8><<<unsigned(l1_blocks), P1_BLOCK, 0, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p);
+            else if (variant == 2) k_pretest<8, 8><<<unsigned(l1_blocks), P1_BLOCK, 0, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p);
+            else if (variant == 3) k_pretest<8, 6><<<unsigned(l1_blocks), P1_BLOCK, 0, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p);
+            else if (variant == 4) k_pretest<2, 8><<<unsigned(l1_blocks), P1_BLOCK, 0, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p);
+            else k_pretest<4, 6><<<unsigned(l1_blocks), P1_BLOCK, 0, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p);
+        }
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[1], st));
+        k_pretest2<<<unsigned(blocks), PT_BLOCK, 0, st>>>(ctx->d_sh.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p, ctx->d_cand.p, ctx->d_pa_cnt.p);
+        L3D_CUDA(cudaEventRecord(ctx->pa_kev[4], st));
         ctx->pa_kev_set[0] = true;
-        ctx->launches += 2;
+        ctx->launches += 3;
         L3D_CUDA(cudaGetLastError());
     }
     if (scan_exclusive(ctx, ctx->d_pa_cnt.p, ctx->d_pa_off.p, int(rows))) return 1;
@@ -1730,9 +2066,22 @@ int run_phase_a(l3d_ctx* cx, PhaseASet* ctx, const std::vector<JobHost>& jh)   /
         L3D_CUDA(cudaMemcpyAsync(ctx->d_rm_begin.p, idx.data(), sizeof(int) * size_t(n_jobs), cudaMemcpyHostToDevice, st));
         L3D_CUDA(cudaMemcpyAsync(ctx->d_rm_len.p, lens.data(), sizeof(int) * size_t(n_jobs), cudaMemcpyHostToDevice, st));
         k_range_max<<<n_jobs, 256, 0, st>>>(ctx->d_pa_cnt.p, ctx->d_rm_begin.p, ctx->d_rm_len.p, 0, ctx->d_rm_out.p);
-        ctx->launches += 1;
+        L3D_CUDA(ctx->d_job_sum64.ensure(size_t(n_jobs))); L3D_CUDA(ctx->h_job_sum64.ensure(size_t(n_jobs)));
+        k_range_sum64<<<n_jobs, 256, 0, st>>>(ctx->d_pa_cnt.p, ctx->d_rm_begin.p, ctx->d_rm_len.p, ctx->d_job_sum64.p);
+        ctx->launches += 2;
         L3D_CUDA(cudaMemcpyAsync(ctx->h_res.p + n_jobs + 1, ctx->d_rm_out.p, sizeof(int) * size_t(n_jobs), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_job_sum64.p, ctx->d_job_sum64.p, sizeof(unsigned long long) * size_t(n_jobs), cudaMemcpyDeviceToHost, st));
         L3D_CUDA(cudaStreamSynchronize(st));        // idx / lens are stack vectors: must be consumed before they go away
+    }
+    {   // Candidate offsets are 32-bit: a batch whose candidates do not fit (a candidate rate far above the usual 2 %:
+        // degenerate epipolar geometry, or the pre-test switched off) is reported so that the caller can cut it smaller.
+        unsigned long long all = 0ull;
+        for (int j = 0; j < n_jobs; ++j) all += ctx->h_job_sum64.p[j];
+        if (all > cx->cand_limit) {
+            char b[200]; snprintf(b, sizeof b, "pair tests: %llu candidates in one batch exceed the limit of %llu (32-bit candidate index)", all, (unsigned long long)cx->cand_limit);
+            ctx->err = b;
+            return 2;
+        }
     }
     for (int j = 0; j < n_jobs; ++j) ctx->job_cands[j] = uint64_t(ctx->h_res.p[j + 1] - ctx->h_res.p[j]);
     for (int j = 0; j < n_jobs; ++j) ctx->job_rowmax[j] = ctx->h_res.p[n_jobs + 1 + j];
@@ -1784,8 +2133,14 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
 {
     cudaStream_t st = ctx->stream;
     PhaseASet& pa = ctx->pa[ctx->cur];
+    const bool mr = ctx->world > 1;
     gr.count = count;
     L3D_CUDA(gr.h_args.ensure(VG_MAX)); L3D_CUDA(gr.d_args.ensure(VG_MAX));
+    if (mr) {
+        L3D_CUDA(gr.d_myrec.ensure(VG_MAX)); L3D_CUDA(gr.d_allrec.ensure(size_t(VG_MAX) * ctx->world)); L3D_CUDA(gr.h_allrec.ensure(size_t(VG_MAX) * ctx->world));
+        // the records of the group two groups ago may still be on their way to the host out of this group's buffers
+        if (gr.ev_x[1]) L3D_CUDA(cudaStreamWaitEvent(st, gr.ev_x[1], 0));
+    }
     int res_stride = 8;
     for (int g = 0; g < count; ++g) { int nd = 0; for (int c = 0; c < gv[g].n_nb; ++c) nd += gv[g].nb[c].deliver ? 1 : 0; res_stride = std::max(res_stride, 8 + nd); }
     gr.res_stride = res_stride;
@@ -1806,14 +2161,16 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     size_t zero_total = 0;
     int mx_src = 1, mx_cams = 1, mx_items = 1, mx_cta = 1; long mx_warps = 1; size_t mx_M = 0, mx_smem = 0;
     bool any_scored = false, any_window = false, any_quadratic = false, any_deliver = false;
-    struct Z { size_t items, iters, best, hist, cursor, end; } z[VG_MAX];
+    struct Z { size_t items, iters, best, hist, cursor, end, samples; } z[VG_MAX];
+    size_t hist_total = 0, samples_total = 0;
     for (int g = 0; g < count; ++g) {
         const int view = gv[g].view, n_nb = gv[g].n_nb; const l3d_neighbor* nb = gv[g].nb; const int first_job = gv[g].first_job;
         ViewSlot& sl = gr.slot[g];
         ViewJob& job = sl.job;
         sl.plan_index = gv[g].plan_index;
         const l3d_view& sv = ctx->views[view];
-        const int n_src = sv.n_segments;
+        const int n_full = sv.n_segments;
+        const int n_src = local_rows(ctx, n_full);         // the rows of the view this process works on
         CamTable* hc = gr.h_cams.p + gr.cam_off[g];
         job.view = view; job.nb.assign(nb, nb + n_nb); job.sigma_p = sigma_p; job.sigma_a = sigma_a;
         job.consumed.clear(); job.owner = -1;
@@ -1864,22 +2221,28 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         L3D_CUDA(sl.d_cnt.ensure(size_t(n_src) * n_nb + 1)); L3D_CUDA(sl.d_off.ensure(size_t(n_src) * n_nb + 2));
         L3D_CUDA(sl.d_mids.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_mdep.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_score.ensure(std::max<size_t>(M_ub, 1)));
         L3D_CUDA(sl.d_filtered.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_cta.ensure(size_t(n_cta) + 1)); L3D_CUDA(sl.d_F.ensure(4));
-        L3D_CUDA(sl.d_dsamples.ensure(size_t(n_src) * 2 + 2)); L3D_CUDA(sl.d_items.ensure(size_t(2 * max_items)));
+        if (!mr) L3D_CUDA(sl.d_dsamples.ensure(size_t(n_src) * 2 + 2));
+        L3D_CUDA(sl.d_items.ensure(size_t(2 * max_items)));
         if (scored && windowed) {
             L3D_CUDA(sl.d_sk.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_sd2.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_spl.ensure(std::max<size_t>(M_ub, 1)));
             L3D_CUDA(sl.d_boff.ensure(size_t(n_src) * (BK_B + 1))); L3D_CUDA(sl.d_brange.ensure(size_t(std::max(n_src, 1))));
         }
-        // what has to start from zero: one region per view in the group's zero buffer
-        z[g].items = zero_total; z[g].iters = z[g].items + 4; z[g].best = z[g].iters + 4; z[g].hist = z[g].best + 2 * size_t(n_src) + 2;
-        z[g].cursor = z[g].hist + size_t(n_keys) + 2; z[g].end = (z[g].cursor + size_t(n_keys) + 2 + 3) & ~size_t(3);
+        // what has to start from zero: one region per view in the group's zero buffer, then the hand-over group sizes of
+        // all views (one block: with several GPUs on one scene they are summed over the ranks in one all-reduce)
+        z[g].items = zero_total; z[g].iters = z[g].items + 4; z[g].best = z[g].iters + 4;
+        z[g].cursor = z[g].best + 2 * size_t(n_src) + 2; z[g].end = (z[g].cursor + size_t(n_keys) + 2 + 3) & ~size_t(3);
         zero_total = z[g].end;
+        z[g].hist = hist_total; hist_total += (size_t(n_keys) + 2 + 3) & ~size_t(3);
+        z[g].samples = samples_total; samples_total += (size_t(n_full) * 2 + 2 + 3) & ~size_t(3);
         // hand-over buffers
         DeliverBuf buf;
         if (delivering) {
             buf.refs = n_deliver;
             L3D_CUDA(ctx->pool.get(sizeof(int) * (size_t(n_keys) + 2), reinterpret_cast<void**>(&buf.start)));
-            L3D_CUDA(ctx->pool.get(sizeof(int) * std::max<size_t>(M_ub, 1), reinterpret_cast<void**>(&buf.tgt)));
-            L3D_CUDA(ctx->pool.get(sizeof(float4) * std::max<size_t>(M_ub, 1), reinterpret_cast<void**>(&buf.dep)));
+            if (!mr) {          // (several GPUs on one scene: sized in finish_group, when all ranks' counts are known)
+                L3D_CUDA(ctx->pool.get(sizeof(int) * std::max<size_t>(M_ub, 1), reinterpret_cast<void**>(&buf.tgt)));
+                L3D_CUDA(ctx->pool.get(sizeof(float4) * std::max<size_t>(M_ub, 1), reinterpret_cast<void**>(&buf.dep)));
+            }
         }
         job.M_ub = M_ub; job.scored = scored; job.delivering = delivering; job.n_deliver = n_deliver;
         // kernel arguments (pointers into the zero buffer are filled in below, when it has its size)
@@ -1889,6 +2252,8 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         memcpy(va.src.RtKinv, sv.RtKinv, sizeof va.src.RtKinv); memcpy(va.src.C, sv.C, sizeof va.src.C);
         va.src.spatial_k = sv.spatial_k; va.src.cmax = std::max(std::fabs(sv.C[0]), std::max(std::fabs(sv.C[1]), std::fabs(sv.C[2])));
         va.src.seg_off = ctx->seg_off[view]; va.src.n_seg = n_src;
+        va.src.row_first = mr ? ctx->rank : 0; va.src.row_stride = mr ? ctx->world : 1;
+        va.mr = mr ? 1 : 0; va.n_seg_full = n_full;
         va.sp.sigma_p = sigma_p; va.sp.sigma_a = sigma_a;
         va.raw_cnt = pa.d_pa_raw.p; va.cand_off = pa.d_pa_off.p; va.stage_col = pa.d_stage_col.p; va.stage_dep = pa.d_stage_dep.p; va.stage_ok = pa.d_stage_ok.p;
         va.cnt = sl.d_cnt.p; va.off = sl.d_off.p; va.mids = sl.d_mids.p; va.mdep = sl.d_mdep.p; va.score = sl.d_score.p;
@@ -1908,6 +2273,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
                 const uint64_t ub = std::min<uint64_t>(hc[c].slot >= 0 ? pa.job_raw[first_job + hc[c].slot] : uint64_t(M_ub), 0x7fffffffull);
                 Delivered dl; dl.from_view = view; dl.owner = job.owner; dl.slot = d;
                 dl.count = int(ub); dl.max_group = int(std::min<uint64_t>(ub, uint64_t(n_src)));      // a source segment matches a target segment once
+                if (mr) { dl.count = 0; dl.max_group = n_full; }                                       // (exact count: finish_group)
                 dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
                 buf.counts[d] = dl.count; buf.maxg[d] = dl.max_group;
                 ctx->delivered[nb[c].view].push_back(dl);
@@ -1928,11 +2294,15 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         if (scored) { any_scored = true; mx_items = std::max(mx_items, max_items); mx_smem = std::max(mx_smem, sm_bytes); }
         any_window |= scored && windowed; any_quadratic |= quadratic; any_deliver |= delivering;
     }
+    gr.hist_off = zero_total; gr.hist_total = hist_total; gr.samples_total = samples_total;
+    zero_total += hist_total;
     L3D_CUDA(gr.d_zero.ensure(zero_total + 4));
+    if (mr) L3D_CUDA(gr.d_samples.ensure(samples_total + 4));
     for (int g = 0; g < count; ++g) {
         VArgs& va = gr.h_args.p[g];
         va.nitems = gr.d_zero.p + z[g].items; va.iters = reinterpret_cast<unsigned long long*>(gr.d_zero.p + z[g].iters);
-        va.best = reinterpret_cast<unsigned long long*>(gr.d_zero.p + z[g].best); va.hist = gr.d_zero.p + z[g].hist; va.cursor = gr.d_zero.p + z[g].cursor;
+        va.best = reinterpret_cast<unsigned long long*>(gr.d_zero.p + z[g].best); va.hist = gr.d_zero.p + gr.hist_off + z[g].hist; va.cursor = gr.d_zero.p + z[g].cursor;
+        if (mr) va.dsamples = gr.d_samples.p + z[g].samples;
     }
     if (mx_smem > ctx->score_smem) {
         L3D_CUDA(cudaFuncSetAttribute(k_score, cudaFuncAttributeMaxDynamicSharedMemorySize, int(mx_smem)));
@@ -1966,6 +2336,26 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     if (any_scored) { L3D_CUDA(pdl_launch(k_reduce_matches, dim3(mx_cta, G), dim3(RM_T), 0, st, A)); ctx->launches += 1; }
     L3D_CUDA(pdl_launch(k_filter_compact, dim3(mx_cta, G), dim3(RM_T), 0, st, A));
     ctx->launches += 1;
+    if (mr) {
+        // What the ranks exchange before the host looks at the group: their records of each view, the depth samples
+        // (minimum: every segment has a sample on one rank at most), the sizes of the hand-over groups (sum).
+        L3D_CUDA(pdl_launch(k_mr_prepare, dim3(8, G), dim3(256), 0, st, A, gr.d_myrec.p));
+        ctx->launches += 1;
+        L3D_NCCL(ctx->nccl->GroupStart());
+        L3D_NCCL(ctx->nccl->AllGather(gr.d_myrec.p, gr.d_allrec.p, sizeof(RankRec) * VG_MAX, ncclChar, ctx->comm, st));
+        if (any_scored) L3D_NCCL(ctx->nccl->AllReduce(gr.d_samples.p, gr.d_samples.p, gr.samples_total, ncclFloat, ncclMin, ctx->comm, st));
+        if (any_deliver) L3D_NCCL(ctx->nccl->AllReduce(gr.d_zero.p + gr.hist_off, gr.d_zero.p + gr.hist_off, gr.hist_total, ncclInt, ncclSum, ctx->comm, st));
+        L3D_NCCL(ctx->nccl->GroupEnd());
+        if (any_deliver) { L3D_CUDA(pdl_launch(k_scan_views, dim3(1, G), dim3(SCAN_T), 0, st, A, 1)); ctx->launches += 1; }
+        L3D_CUDA(pdl_launch(k_finish_view, dim3(1, G), dim3(MS_T), 0, st, A));
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+        if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[5], st));
+        L3D_CUDA(cudaMemcpyAsync(gr.h_vres.p, gr.d_vres.p, sizeof(int) * size_t(count) * res_stride, cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaMemcpyAsync(gr.h_allrec.p, gr.d_allrec.p, sizeof(RankRec) * VG_MAX * size_t(ctx->world), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaEventRecord(gr.ev[0], st));
+        return 0;               // the records themselves are exchanged in finish_group, when the host knows how many there are
+    }
     if (any_deliver) {
         L3D_CUDA(pdl_launch(k_scan_views, dim3(1, G), dim3(SCAN_T), 0, st, A, 1));
         L3D_CUDA(pdl_launch(k_deliver_scatter, dim3(unsigned((std::max<size_t>(mx_M, 1) + 255) / 256), G), dim3(256), 0, st, A));
@@ -2004,6 +2394,57 @@ int arena_take(l3d_ctx* ctx, size_t n, l3d_match** out)
     return 0;
 }
 
+// Several GPUs on one scene: the second half of a group's exchange, once the host knows every rank's record counts.
+// All ranks' output records of the group's views are gathered (packed: one all-gather of the largest rank's size),
+// laid out view by view, and the hand-over lists are built from them -- on every rank, so that each has the complete
+// lists for its rows of the later views.
+int mr_exchange(l3d_ctx* ctx, ViewGroup& gr, MrLayout& lay)
+{
+    cudaStream_t st = ctx->stream;
+    const int W = ctx->world, G = gr.count;
+    const RankRec* rec = gr.h_allrec.p;                 // [rank][VG_MAX]
+    memset(&lay, 0, sizeof lay);
+    long long padded = 0, total = 0; int max_cnt = 0;
+    for (int r = 0; r < W; ++r) {
+        long long t = 0;
+        for (int v = 0; v < G; ++v) { lay.src_off[r][v] = int(t); lay.cnt[r][v] = rec[size_t(r) * VG_MAX + v].F; t += lay.cnt[r][v]; max_cnt = std::max(max_cnt, lay.cnt[r][v]); }
+        padded = std::max(padded, t);
+    }
+    for (int v = 0; v < G; ++v) {
+        lay.view_off[v] = int(total);
+        for (int r = 0; r < W; ++r) { lay.dst_off[r][v] = int(total); total += lay.cnt[r][v]; }
+        lay.view_cnt[v] = int(total - lay.view_off[v]);
+    }
+    if (total > 0x7fffffffll || padded * W > 0x7fffffffll) { ctx->err = "l3d_match_view: too many output records in one group of views"; return 1; }
+    lay.padded = int(padded);
+    bool any_deliver = false;
+    for (int g = 0; g < G; ++g) {                       // the hand-over record buffers, now that their sizes are known
+        ViewJob& job = gr.slot[g].job;
+        if (!job.delivering) continue;
+        any_deliver = true;
+        DeliverBuf& b = ctx->deliver_bufs[job.owner];
+        const size_t n = size_t(std::max(lay.view_cnt[g], 1));
+        L3D_CUDA(ctx->pool.get(sizeof(int) * n, reinterpret_cast<void**>(&b.tgt)));
+        L3D_CUDA(ctx->pool.get(sizeof(float4) * n, reinterpret_cast<void**>(&b.dep)));
+        lay.dl_tgt[g] = b.tgt; lay.dl_dep[g] = b.dep;
+        for (size_t c = 0; c < job.nb.size(); ++c) {
+            if (!job.nb[c].deliver) continue;
+            std::vector<Delivered>& dl = ctx->delivered[job.nb[c].view];
+            for (size_t k = 0; k < dl.size(); ++k) if (dl[k].owner == job.owner) { dl[k].t_tgt = b.tgt; dl[k].t_dep = b.dep; }
+        }
+    }
+    if (total == 0) return 0;                           // (every rank sees the same counts and skips the same calls)
+    L3D_CUDA(gr.d_send.ensure(size_t(padded))); L3D_CUDA(gr.d_recv.ensure(size_t(padded) * W)); L3D_CUDA(gr.d_allf.ensure(size_t(total)));
+    const unsigned blocks = unsigned(std::min(std::max((2 * max_cnt + 255) / 256, 1), 4 * ctx->n_sm));
+    k_mr_pack<<<dim3(blocks, G), 256, 0, st>>>(gr.d_args.p, gr.d_myrec.p, gr.d_send.p);
+    L3D_NCCL(ctx->nccl->AllGather(gr.d_send.p, gr.d_recv.p, size_t(padded) * sizeof(l3d_match), ncclChar, ctx->comm, st));
+    k_mr_unpack<<<dim3(blocks, G, W), 256, 0, st>>>(gr.d_recv.p, gr.d_allf.p, lay);
+    ctx->launches += 2;
+    if (any_deliver) { k_mr_deliver_scatter<<<dim3(std::min(4u * blocks, unsigned(8 * ctx->n_sm)), G), 256, 0, st>>>(gr.d_args.p, gr.d_allf.p, lay); ctx->launches += 1; }
+    L3D_CUDA(cudaGetLastError());
+    return 0;
+}
+
 // Waits for a group, turns its result records into l3d_match_results (results[plan index], or *single for a view
 // matched outside a schedule) and fetches the output records of all its views with one synchronise.
 int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* single)
@@ -2014,10 +2455,19 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
     if (pa.pa_ms_pending) {                            // phase A of a whole batch is booked on the first view collected after it
         cudaEventElapsedTime(&ms_a[0], pa.pa_ev[0], pa.pa_ev[1]); cudaEventElapsedTime(&ms_a[1], pa.pa_ev[1], pa.pa_ev[2]);
         for (int k = 0; k < 2; ++k) { float ms = 0.f; if (pa.pa_kev_set[k]) cudaEventElapsedTime(&ms, pa.pa_kev[2 * k], pa.pa_kev[2 * k + 1]); ctx->pa_kernel_ms[k] = ms; }
+        { float ms = 0.f; if (pa.pa_kev_set[0]) cudaEventElapsedTime(&ms, pa.pa_kev[1], pa.pa_kev[4]); ctx->pa_kernel_ms[2] = ms; }
         pa.pa_ms_pending = false;
-    } else ctx->pa_kernel_ms[0] = ctx->pa_kernel_ms[1] = 0.f;
+    } else ctx->pa_kernel_ms[0] = ctx->pa_kernel_ms[1] = ctx->pa_kernel_ms[2] = 0.f;
     float ms_b[3] = {0.f, 0.f, 0.f};
     if (ctx->stage_events) for (int k = 0; k < 3; ++k) cudaEventElapsedTime(&ms_b[k], gr.ev[k + 2], gr.ev[k + 3]);
+    const bool mr = ctx->world > 1;
+    MrLayout lay;
+    if (mr) {
+        if (mr_exchange(ctx, gr, lay)) return 1;
+        L3D_CUDA(cudaEventRecord(gr.ev_x[0], ctx->stream));
+        copy_back = copy_back && (ctx->result_root < 0 || ctx->result_root == ctx->rank);      // who gets the records on the host
+        if (copy_back) L3D_CUDA(cudaStreamWaitEvent(ctx->copy_stream, gr.ev_x[0], 0));
+    }
     bool copies = false;
     for (int g = 0; g < gr.count; ++g) {
         ViewSlot& sl = gr.slot[g];
@@ -2027,9 +2477,14 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
         l3d_match_result* res = single ? single : &ctx->results[sl.plan_index].res;
         memset(res, 0, sizeof *res);
         res->pair_tests = job.pair_tests; res->n_candidates = job.cand_ub; res->scored = job.scored ? 1 : 0;
-        const int M = hr[0], F = (job.M_ub > 0) ? hr[1] : 0;
+        int M = hr[0], F = (job.M_ub > 0) ? hr[1] : 0;
         float median = 1.0f;                              // line3D.cc:811
-        if (job.scored && M > 0) {
+        if (mr) {                                          // the view as a whole: all ranks' rows
+            unsigned long long all = 0ull, same = 0ull; long long m = 0;
+            for (int r = 0; r < ctx->world; ++r) { const RankRec& rr = gr.h_allrec.p[size_t(r) * VG_MAX + g]; m += rr.M; all += rr.iters_all; same += rr.iters_same; }
+            M = int(m); F = lay.view_cnt[g];
+            if (job.scored && M > 0) { memcpy(&median, &hr[2], sizeof(float)); res->score_iters = all; res->score_iters_other_cam = all - same; }
+        } else if (job.scored && M > 0) {
             memcpy(&median, &hr[2], sizeof(float));
             const unsigned long long all = (unsigned long long)(unsigned)hr[4] | ((unsigned long long)(unsigned)hr[5] << 32);
             const unsigned long long same = (unsigned long long)(unsigned)hr[6] | ((unsigned long long)(unsigned)hr[7] << 32);
@@ -2061,17 +2516,18 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
         if (copy_back && F > 0) {                          // on its own stream: the next group is already running
             if (ctx->retain || !single) { if (arena_take(ctx, size_t(F), &dst)) return 1; }      // results of a schedule are collected ahead of their calls
             else { L3D_CUDA(ctx->h_filtered.ensure(size_t(F))); dst = ctx->h_filtered.p; }
-            L3D_CUDA(cudaMemcpyAsync(dst, sl.d_filtered.p, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, ctx->copy_stream));
+            const l3d_match* from = mr ? gr.d_allf.p + lay.view_off[g] : sl.d_filtered.p;
+            L3D_CUDA(cudaMemcpyAsync(dst, from, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, ctx->copy_stream));
             copies = true;
         }
         res->filtered = dst;
         if (!single) {
             l3d_ctx::Stashed& stash = ctx->results[sl.plan_index];
-            memset(stash.ms, 0, sizeof stash.ms); stash.kms[0] = stash.kms[1] = 0.f;
+            memset(stash.ms, 0, sizeof stash.ms); stash.kms[0] = stash.kms[1] = stash.kms[2] = 0.f;
             if (g == 0) {                                  // the group's device times are booked on its first view
                 stash.ms[0] = ms_a[0]; stash.ms[1] = ms_a[1]; stash.ms[2] = ms_b[0]; stash.ms[3] = ms_b[1]; stash.ms[4] = ms_b[2];
                 stash.ms[5] = ms_a[0] + ms_a[1] + ms_b[0] + ms_b[1] + ms_b[2];
-                stash.kms[0] = ctx->pa_kernel_ms[0]; stash.kms[1] = ctx->pa_kernel_ms[1];
+                stash.kms[0] = ctx->pa_kernel_ms[0]; stash.kms[1] = ctx->pa_kernel_ms[1]; stash.kms[2] = ctx->pa_kernel_ms[2];
             }
             stash.ready = true;
         } else {
@@ -2079,7 +2535,11 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
             ctx->last_ms[5] = ms_a[0] + ms_a[1] + ms_b[0] + ms_b[1] + ms_b[2];
         }
     }
-    if (copies) L3D_CUDA(cudaStreamSynchronize(ctx->copy_stream));
+    if (mr) {
+        // the next group can go onto the GPU before these copies have arrived: they are waited for when a result is
+        // handed to the caller (copies_pending), and before this group's buffers are used again (ev_x[1])
+        if (copies) { L3D_CUDA(cudaEventRecord(gr.ev_x[1], ctx->copy_stream)); ctx->copies_pending = true; }
+    } else if (copies) L3D_CUDA(cudaStreamSynchronize(ctx->copy_stream));
     return 0;
 }
 
@@ -2100,6 +2560,7 @@ size_t plan_batch(l3d_ctx* ctx, size_t from, std::vector<JobHost>& jh)
     size_t e = from; uint64_t pairs = 0;
     while (e < ctx->order.size() && (e == from || pairs + ctx->plan[ctx->order[e]].pair_tests <= ctx->batch_pairs)) {
         PlannedView& pv = ctx->plan[ctx->order[e]];
+        if (e > from && jh.size() + pv.nb.size() > 65535) break;        // one grid row per job in k_hoist
         pv.first_job = int(jh.size());
         for (size_t c = 0; c < pv.nb.size(); ++c)
             if (pv.nb[c].to_be_matched) { JobHost j; j.src_view = pv.view; j.tgt_view = pv.nb[c].view; memcpy(j.F, pv.nb[c].F, sizeof j.F); jh.push_back(j); }
@@ -2139,16 +2600,29 @@ int top_up(l3d_ctx* ctx)
 {
     if (ctx->fly_end >= ctx->batch_end) {
         if (ctx->fly_begin < ctx->fly_end || ctx->fly_end >= ctx->order.size()) return 0;
+        bool have = false;
         if (ctx->pa_worker_active) {                             // its pair tests were started while the previous batch was scored
             PhaseASet& nx = ctx->pa[ctx->cur ^ 1];
-            if (join_worker(ctx)) { ctx->err = nx.err; return 1; }
-            if (nx.begin != ctx->fly_end) { ctx->err = "l3d_match_view: internal error (batch out of step)"; return 1; }
-            ctx->cur ^= 1;
-        } else {
+            const int rc = join_worker(ctx);
+            if (rc == 0) {
+                if (nx.begin != ctx->fly_end) { ctx->err = "l3d_match_view: internal error (batch out of step)"; return 1; }
+                ctx->cur ^= 1; have = true;
+            } else if (rc != 2) { ctx->err = nx.err; return 1; }
+            // rc == 2: more candidates than a batch can index -- the batch is redone below, cut smaller
+        }
+        while (!have) {
             std::vector<JobHost> jh;
             PhaseASet& set = ctx->pa[ctx->cur];
             set.begin = ctx->fly_end; set.end = plan_batch(ctx, ctx->fly_end, jh);
-            if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
+            const int rc = run_phase_a(ctx, &set, jh);
+            if (rc == 2 && set.end - set.begin > 1 && ctx->world <= 1) {             // halve the batch and try again (one GPU only: ranks must cut alike)
+                uint64_t pairs = 0;
+                for (size_t e = set.begin; e < set.end; ++e) pairs += ctx->plan[ctx->order[e]].pair_tests;
+                ctx->batch_pairs = std::max<uint64_t>(pairs / 2, 1);
+                continue;
+            }
+            if (rc) { ctx->err = set.err + (rc == 2 ? " (a single view: not supported)" : ""); return 1; }
+            have = true;
         }
         PhaseASet& set = ctx->pa[ctx->cur];
         ctx->batch_begin = set.begin; ctx->batch_end = set.end;
@@ -2156,7 +2630,8 @@ int top_up(l3d_ctx* ctx)
         if (ctx->batch_end < ctx->order.size()) start_worker(ctx, ctx->batch_end);      // the following batch, meanwhile
     }
     // the next groups: consecutive views of one dependency level, two groups in flight
-    while (ctx->fly_end < ctx->batch_end && ctx->grp_end - ctx->grp_begin < 2) {
+    // (several GPUs on one scene: one, because a group's hand-over needs the ranks' counts on the host first)
+    while (ctx->fly_end < ctx->batch_end && ctx->grp_end - ctx->grp_begin < size_t(ctx->world > 1 ? 1 : 2)) {
         GroupView gv[VG_MAX]; int count = 0;
         const int lvl = ctx->level[ctx->order[ctx->fly_end]];
         while (count < VG_MAX && ctx->fly_end + size_t(count) < ctx->batch_end && ctx->level[ctx->order[ctx->fly_end + size_t(count)]] == lvl) {
@@ -2197,6 +2672,7 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
             ctx->fly_begin += size_t(gr.count); ++ctx->grp_begin;
             if (rc) { drain_pending(ctx); return 1; }
         }
+        if (ctx->copies_pending) { L3D_CUDA(cudaStreamSynchronize(ctx->copy_stream)); ctx->copies_pending = false; }
         *res = ctx->results[p].res;
         memcpy(ctx->last_ms, ctx->results[p].ms, sizeof ctx->last_ms); memcpy(ctx->pa_kernel_ms, ctx->results[p].kms, sizeof ctx->pa_kernel_ms);
         ++ctx->call_next;
@@ -2214,7 +2690,9 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     ctx->launches += set.launches; set.launches = 0;
     GroupView one = {view, n_nb, nb, 0, 0};
     if (enqueue_group(ctx, ctx->grp[0], &one, 1, sigma_p, sigma_a)) return 1;
-    return finish_group(ctx, ctx->grp[0], copy_back, res);
+    if (finish_group(ctx, ctx->grp[0], copy_back, res)) return 1;
+    if (ctx->copies_pending) { L3D_CUDA(cudaStreamSynchronize(ctx->copy_stream)); ctx->copies_pending = false; }
+    return 0;
 }
 
 // Nothing throws across the C ABI: the host-side containers can (out of memory).
@@ -2254,16 +2732,63 @@ int l3d_create(int device, l3d_ctx** out)
     }
     for (int k = 0; k < 2; ++k) cudaEventCreate(&ctx->ev[k]);
     for (int q = 0; q < 2; ++q) for (int k = 0; k < 6; ++k) cudaEventCreate(&ctx->grp[q].ev[k]);
+    for (int q = 0; q < 2; ++q) for (int k = 0; k < 2; ++k) cudaEventCreateWithFlags(&ctx->grp[q].ev_x[k], cudaEventDisableTiming);
     if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); cudaStreamDestroy(ctx->stream); delete ctx; return 1; }
     if ((e = cudaStreamCreateWithPriority(&ctx->fin_stream, cudaStreamNonBlocking, prio_hi)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); l3d_destroy(ctx); return 1; }
     for (int q = 0; q < 2; ++q) {
         PhaseASet& set = ctx->pa[q];
         if ((e = cudaStreamCreateWithPriority(&set.stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess) { g_create_error = std::string("l3d_create: stream: ") + cudaGetErrorString(e); l3d_destroy(ctx); return 1; }
         for (int k = 0; k < 3; ++k) cudaEventCreate(&set.pa_ev[k]);
-        for (int k = 0; k < 4; ++k) cudaEventCreate(&set.pa_kev[k]);
+        for (int k = 0; k < 5; ++k) cudaEventCreate(&set.pa_kev[k]);
     }
     for (int k = 0; k < 2; ++k) cudaEventCreate(&ctx->mark_ev[k]);
     *out = ctx;
+    return 0;
+}
+
+int l3d_comm_unique_id(void* id)
+{
+    std::string why;
+    NcclApi* api = nccl_api(&why);
+    if (!api || !id) { g_create_error = api ? "l3d_comm_unique_id: null argument" : "l3d_comm_unique_id: " + why; return 1; }
+    ncclUniqueId u;
+    static_assert(sizeof(ncclUniqueId) == L3D_COMM_ID_BYTES, "ncclUniqueId size");
+    const ncclResult_t r = api->GetUniqueId(&u);
+    if (r != ncclSuccess) { g_create_error = std::string("ncclGetUniqueId: ") + api->GetErrorString(r); return 1; }
+    memcpy(id, &u, sizeof u);
+    return 0;
+}
+
+int l3d_comm_init(l3d_ctx* ctx, int rank, int world, const void* id, int result_root)
+{
+    if (!ctx) return 1;
+    return guarded(ctx, [&]() -> int {
+        if (world < 1 || world > MR_MAX_RANKS || rank < 0 || rank >= world || (world > 1 && !id) || result_root >= world) { ctx->err = "l3d_comm_init: bad arguments (1 <= world <= 16)"; return 1; }
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        l3d_reset_matching(ctx);
+        if (l3d_comm_destroy(ctx)) return 1;
+        if (world == 1) return 0;
+        std::string why;
+        ctx->nccl = nccl_api(&why);
+        if (!ctx->nccl) { ctx->err = "l3d_comm_init: " + why; return 1; }
+        ncclUniqueId u; memcpy(&u, id, sizeof u);
+        L3D_NCCL(ctx->nccl->CommInitRank(&ctx->comm, world, u, rank));
+        ctx->rank = rank; ctx->world = world; ctx->result_root = result_root;
+        return 0;
+    });
+}
+
+int l3d_comm_destroy(l3d_ctx* ctx)
+{
+    if (!ctx) return 1;
+    if (ctx->comm) {
+        cudaSetDevice(ctx->device);
+        drain_pending(ctx);
+        cudaStreamSynchronize(ctx->stream);
+        ctx->nccl->CommDestroy(ctx->comm);
+        ctx->comm = nullptr;
+    }
+    ctx->rank = 0; ctx->world = 1; ctx->result_root = -1;
     return 0;
 }
 
@@ -2287,6 +2812,7 @@ void l3d_destroy(l3d_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     l3d_reset_matching(ctx);
+    l3d_comm_destroy(ctx);
     ctx->d_segs.release(); ctx->d_viewd.release(); ctx->pa[0].release(); ctx->pa[1].release();
     ctx->d_tile_sums.release(); ctx->d_total.release();
     ctx->grp[0].release(); ctx->grp[1].release(); ctx->pool.release();
@@ -2307,33 +2833,35 @@ uint64_t l3d_kernel_launches(const l3d_ctx* ctx) { return ctx ? ctx->launches : 
 
 int l3d_collinearity(l3d_ctx* ctx, const float* segments, int n, float collin_s, const l3d_collin_pair** pairs, size_t* count)
 {
-    if (!ctx) return 1;
-    if (!pairs || !count || (n > 0 && !segments)) { ctx->err = "l3d_collinearity: null argument"; return 1; }
-    *pairs = nullptr; *count = 0;
-    if (n <= 1) return 0;
-    L3D_CUDA(cudaSetDevice(ctx->device));
-    cudaStream_t st = ctx->stream;
-    const int wpr = (n + 31) / 32;
-    L3D_CUDA(ctx->d_csegs.ensure(size_t(n))); L3D_CUDA(ctx->d_cbits.ensure(size_t(n) * wpr));
-    L3D_CUDA(ctx->d_ccnt.ensure(size_t(n) + 1)); L3D_CUDA(ctx->d_coff.ensure(size_t(n) + 2));
-    L3D_CUDA(cudaMemcpyAsync(ctx->d_csegs.p, segments, sizeof(float4) * size_t(n), cudaMemcpyHostToDevice, st));
-    L3D_CUDA(cudaMemsetAsync(ctx->d_ccnt.p, 0, sizeof(int) * (size_t(n) + 1), st));
-    const float s2 = collin_s * collin_s;                                       // cudawrapper.cu:850
-    k_collin_count<<<dim3((wpr + 63) / 64, n), 64, 0, st>>>(ctx->d_csegs.p, n, s2, ctx->d_ccnt.p, ctx->d_cbits.p, wpr);
-    ctx->launches += 1;
-    L3D_CUDA(cudaGetLastError());
-    if (scan_exclusive(ctx, ctx->d_ccnt.p, ctx->d_coff.p, n)) return 1;
-    int total = 0;
-    if (fetch_int(ctx, ctx->d_coff.p + n, &total)) return 1;
-    if (total == 0) return 0;
-    L3D_CUDA(ctx->d_cpairs.ensure(size_t(total))); L3D_CUDA(ctx->h_cpairs.ensure(size_t(total)));
-    k_collin_fill<<<(n * 32 + 255) / 256, 256, 0, st>>>(ctx->d_csegs.p, n, s2, ctx->d_coff.p, ctx->d_cbits.p, wpr, ctx->d_cpairs.p);
-    ctx->launches += 1;
-    L3D_CUDA(cudaGetLastError());
-    L3D_CUDA(cudaMemcpyAsync(ctx->h_cpairs.p, ctx->d_cpairs.p, sizeof(l3d_collin_pair) * size_t(total), cudaMemcpyDeviceToHost, st));
-    L3D_CUDA(cudaStreamSynchronize(st));
-    *pairs = ctx->h_cpairs.p; *count = size_t(total);
-    return 0;
+    return guarded(ctx, [&]() -> int {
+        if (!ctx) return 1;
+        if (!pairs || !count || (n > 0 && !segments)) { ctx->err = "l3d_collinearity: null argument"; return 1; }
+        *pairs = nullptr; *count = 0;
+        if (n <= 1) return 0;
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        cudaStream_t st = ctx->stream;
+        const int wpr = (n + 31) / 32;
+        L3D_CUDA(ctx->d_csegs.ensure(size_t(n))); L3D_CUDA(ctx->d_cbits.ensure(size_t(n) * wpr));
+        L3D_CUDA(ctx->d_ccnt.ensure(size_t(n) + 1)); L3D_CUDA(ctx->d_coff.ensure(size_t(n) + 2));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_csegs.p, segments, sizeof(float4) * size_t(n), cudaMemcpyHostToDevice, st));
+        L3D_CUDA(cudaMemsetAsync(ctx->d_ccnt.p, 0, sizeof(int) * (size_t(n) + 1), st));
+        const float s2 = collin_s * collin_s;                                       // cudawrapper.cu:850
+        k_collin_count<<<dim3((wpr + 63) / 64, n), 64, 0, st>>>(ctx->d_csegs.p, n, s2, ctx->d_ccnt.p, ctx->d_cbits.p, wpr);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+        if (scan_exclusive(ctx, ctx->d_ccnt.p, ctx->d_coff.p, n)) return 1;
+        int total = 0;
+        if (fetch_int(ctx, ctx->d_coff.p + n, &total)) return 1;
+        if (total == 0) return 0;
+        L3D_CUDA(ctx->d_cpairs.ensure(size_t(total))); L3D_CUDA(ctx->h_cpairs.ensure(size_t(total)));
+        k_collin_fill<<<(n * 32 + 255) / 256, 256, 0, st>>>(ctx->d_csegs.p, n, s2, ctx->d_coff.p, ctx->d_cbits.p, wpr, ctx->d_cpairs.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_cpairs.p, ctx->d_cpairs.p, sizeof(l3d_collin_pair) * size_t(total), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaStreamSynchronize(st));
+        *pairs = ctx->h_cpairs.p; *count = size_t(total);
+        return 0;
+    });
 }
 
 int l3d_collinearity_prealloc(const float* d_segments, int n, float collin_s, l3d_collin_pair* d_pairs, int capacity,
@@ -2346,20 +2874,31 @@ int l3d_collinearity_prealloc(const float* d_segments, int n, float collin_s, l3
         char b[160]; snprintf(b, sizeof b, "%d segments exceed the built-in limit of %d (use l3d_collinearity, which allocates)", n, PREALLOC_MAX_SEGMENTS);
         return fail(2, b);
     }
+    // the kernels read the segments as float4 and write 12-byte records and an int: a misaligned pointer would raise a
+    // sticky device fault that takes the caller's whole CUDA context with it, so it is refused here
+    if ((reinterpret_cast<uintptr_t>(d_segments) & 15u) || (reinterpret_cast<uintptr_t>(d_pairs) & 3u) || (reinterpret_cast<uintptr_t>(d_count) & 3u))
+        return fail(1, "d_segments must be 16-byte aligned, d_pairs and d_count 4-byte aligned");
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
     // Set-up, once per device and with that device current: the array's name is only a host-side handle for the
-    // symbol, the kernels need its address in device memory.
-    static unsigned int* scratch_of_device[64] = {nullptr};
+    // symbol, the kernels need its address in device memory.  The per-device cache is a table of atomics: two threads
+    // that make their first call at the same time both look the address up and store the same value.
+    static std::atomic<unsigned int*> scratch_of_device[64];
     int dev = -1;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess || dev < 0 || dev >= 64) return fail(3, e != cudaSuccess ? cudaGetErrorString(e) : "device index out of range");
-    unsigned int* scratch = scratch_of_device[dev];
+    if (st != nullptr && st != cudaStreamLegacy && st != cudaStreamPerThread) {      // the work must go to the device whose array was looked up
+        int sdev = -1;
+        e = cudaStreamGetDevice(st, &sdev);
+        if (e != cudaSuccess) return fail(7, cudaGetErrorString(e));
+        if (sdev != dev) return fail(7, "cuda_stream belongs to another device than the current one (cudaSetDevice to the stream's device first)");
+    }
+    unsigned int* scratch = scratch_of_device[dev].load(std::memory_order_acquire);
     if (!scratch) {
         void* p = nullptr;
         e = cudaGetSymbolAddress(&p, g_prealloc_scratch);
         if (e != cudaSuccess || !p) return fail(4, e != cudaSuccess ? cudaGetErrorString(e) : "cudaGetSymbolAddress returned null");
         scratch = static_cast<unsigned int*>(p);
-        scratch_of_device[dev] = scratch;
+        scratch_of_device[dev].store(scratch, std::memory_order_release);
     }
     unsigned* bits = scratch;
     int* cnt = reinterpret_cast<int*>(scratch + PREALLOC_CNT_OFF);
@@ -2383,90 +2922,115 @@ int l3d_collinearity_prealloc(const float* d_segments, int n, float collin_s, l3
 
 int l3d_set_views(l3d_ctx* ctx, int n_views, const l3d_view* views)
 {
-    if (!ctx) return 1;
-    if (n_views <= 0 || !views) { ctx->err = "l3d_set_views: no views"; return 1; }
-    L3D_CUDA(cudaSetDevice(ctx->device));
-    l3d_reset_matching(ctx);
-    ctx->V = n_views;
-    ctx->views.assign(views, views + n_views);
-    ctx->seg_off.assign(size_t(n_views) + 1, 0);
-    ctx->max_seg = 0;
-    for (int v = 0; v < n_views; ++v) {
-        if (views[v].n_segments < 0 || (views[v].n_segments > 0 && !views[v].segments)) { ctx->err = "l3d_set_views: bad segment array"; return 1; }
-        if (views[v].n_segments > 65535) { ctx->err = "l3d_set_views: more than 65535 segments in a view"; return 1; }
-        ctx->seg_off[v + 1] = ctx->seg_off[v] + views[v].n_segments;
-        ctx->max_seg = std::max(ctx->max_seg, views[v].n_segments);
-    }
-    ctx->total_segs = ctx->seg_off[n_views];
-    L3D_CUDA(ctx->d_segs.ensure(size_t(std::max(ctx->total_segs, 1))));
-    L3D_CUDA(ctx->d_viewd.ensure(size_t(n_views)));
-    std::vector<ViewD> vd(n_views);
-    for (int v = 0; v < n_views; ++v) {
-        if (views[v].n_segments)
-            L3D_CUDA(cudaMemcpyAsync(ctx->d_segs.p + ctx->seg_off[v], views[v].segments, sizeof(float4) * size_t(views[v].n_segments), cudaMemcpyHostToDevice, ctx->stream));
-        memcpy(vd[v].RtKinv, views[v].RtKinv_d, sizeof vd[v].RtKinv); memcpy(vd[v].C, views[v].C_d, sizeof vd[v].C);
-        vd[v].k_lower = views[v].k_lower; vd[v].k_upper = views[v].k_upper; vd[v].seg_off = ctx->seg_off[v]; vd[v].n_seg = views[v].n_segments;
-        ctx->views[v].segments = nullptr;
-    }
-    L3D_CUDA(cudaMemcpyAsync(ctx->d_viewd.p, vd.data(), sizeof(ViewD) * size_t(n_views), cudaMemcpyHostToDevice, ctx->stream));
-    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
-    ctx->delivered.assign(size_t(n_views), std::vector<Delivered>());
-    ctx->n_hyp = 0;
-    return 0;
+    return guarded(ctx, [&]() -> int {
+        if (!ctx) return 1;
+        if (n_views <= 0 || !views) { ctx->err = "l3d_set_views: no views"; return 1; }
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        l3d_reset_matching(ctx);
+        ctx->V = n_views;
+        ctx->views.assign(views, views + n_views);
+        ctx->seg_off.assign(size_t(n_views) + 1, 0);
+        ctx->max_seg = 0;
+        for (int v = 0; v < n_views; ++v) {
+            if (views[v].n_segments < 0 || (views[v].n_segments > 0 && !views[v].segments && !(ctx->world > 1 && ctx->rank != 0))) { ctx->err = "l3d_set_views: bad segment array"; return 1; }
+            if (views[v].n_segments > 65535) { ctx->err = "l3d_set_views: more than 65535 segments in a view"; return 1; }
+            ctx->seg_off[v + 1] = ctx->seg_off[v] + views[v].n_segments;
+            ctx->max_seg = std::max(ctx->max_seg, views[v].n_segments);
+        }
+        ctx->total_segs = ctx->seg_off[n_views];
+        L3D_CUDA(ctx->d_segs.ensure(size_t(std::max(ctx->total_segs, 1))));
+        L3D_CUDA(ctx->d_viewd.ensure(size_t(n_views)));
+        std::vector<ViewD> vd(n_views);
+        for (int v = 0; v < n_views; ++v) {
+            // (several GPUs on one scene: a rank other than 0 may leave the segments out -- pointer NULL with n_segments
+            // set -- and gets them from rank 0 in the broadcast below)
+            if (views[v].n_segments && views[v].segments)
+                L3D_CUDA(cudaMemcpyAsync(ctx->d_segs.p + ctx->seg_off[v], views[v].segments, sizeof(float4) * size_t(views[v].n_segments), cudaMemcpyHostToDevice, ctx->stream));
+            memcpy(vd[v].RtKinv, views[v].RtKinv_d, sizeof vd[v].RtKinv); memcpy(vd[v].C, views[v].C_d, sizeof vd[v].C);
+            vd[v].k_lower = views[v].k_lower; vd[v].k_upper = views[v].k_upper; vd[v].seg_off = ctx->seg_off[v]; vd[v].n_seg = views[v].n_segments;
+            ctx->views[v].segments = nullptr;
+        }
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_viewd.p, vd.data(), sizeof(ViewD) * size_t(n_views), cudaMemcpyHostToDevice, ctx->stream));
+        // several GPUs on one scene: the segment table is replicated from rank 0 over NVLink (the camera tables are a few
+        // hundred bytes per view and every rank has computed them from the same input)
+        if (ctx->world > 1 && ctx->total_segs > 0)
+            L3D_NCCL(ctx->nccl->Broadcast(ctx->d_segs.p, ctx->d_segs.p, size_t(ctx->total_segs) * sizeof(float4), ncclChar, 0, ctx->comm, ctx->stream));
+        L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->delivered.assign(size_t(n_views), std::vector<Delivered>());
+        ctx->n_hyp = 0;
+        return 0;
+    });
 }
 
 int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
 {
-    if (!ctx) return 1;
-    cudaSetDevice(ctx->device);
-    drain_pending(ctx);
-    ctx->plan.clear(); ctx->order.clear(); ctx->results.clear(); ctx->call_next = 0; ctx->plan_started = false; ctx->batch_begin = ctx->batch_end = 0; ctx->fly_begin = ctx->fly_end = 0;
-    if (n_views <= 0) return 0;
-    if (!plans) { ctx->err = "l3d_plan_matching: null argument"; return 1; }
-    for (int k = 0; k < n_views; ++k) {
-        const l3d_view_plan& p = plans[k];
-        if (p.view < 0 || p.view >= ctx->V || p.n_neighbors <= 0 || !p.neighbors) { ctx->plan.clear(); ctx->err = "l3d_plan_matching: bad entry"; return 1; }
-        PlannedView pv; pv.view = p.view; pv.nb.assign(p.neighbors, p.neighbors + p.n_neighbors);
-        for (int c = 0; c < p.n_neighbors; ++c) {
-            if (p.neighbors[c].view < 0 || p.neighbors[c].view >= ctx->V || p.neighbors[c].view == p.view) { ctx->plan.clear(); ctx->err = "l3d_plan_matching: bad neighbour"; return 1; }
-            if (p.neighbors[c].to_be_matched) pv.pair_tests += uint64_t(ctx->views[p.view].n_segments) * uint64_t(ctx->views[p.neighbors[c].view].n_segments);
-        }
-        ctx->plan.push_back(pv);
-    }
-    // Execution order.  View b needs view a first only if a hands records over to b (a comes earlier and marks b
-    // "deliver"), so the schedule is a dependency graph, usually of a few independent chains (views along a street;
-    // C2: 200 views, longest chain 50).  The library works through it level by level -- the views of one level do not
-    // depend on each other and run side by side -- and hands the results out in the order of the calls.
-    {
-        const size_t n = ctx->plan.size();
-        std::vector<int> at(size_t(ctx->V), -1), level(n, 1);
-        for (size_t k = 0; k < n; ++k) at[ctx->plan[k].view] = int(k);
-        for (size_t k = 0; k < n; ++k)
-            for (size_t c = 0; c < ctx->plan[k].nb.size(); ++c) {
-                const l3d_neighbor& nbr = ctx->plan[k].nb[c];
-                const int to = at[nbr.view];
-                if (nbr.deliver && to > int(k)) level[to] = std::max(level[to], level[k] + 1);
+    return guarded(ctx, [&]() -> int {
+        if (!ctx) return 1;
+        cudaSetDevice(ctx->device);
+        drain_pending(ctx);
+        ctx->plan.clear(); ctx->order.clear(); ctx->results.clear(); ctx->call_next = 0; ctx->plan_started = false; ctx->batch_begin = ctx->batch_end = 0; ctx->fly_begin = ctx->fly_end = 0;
+        if (n_views <= 0) return 0;
+        if (!plans) { ctx->err = "l3d_plan_matching: null argument"; return 1; }
+        for (int k = 0; k < n_views; ++k) {
+            const l3d_view_plan& p = plans[k];
+            if (p.view < 0 || p.view >= ctx->V || p.n_neighbors <= 0 || !p.neighbors) { ctx->plan.clear(); ctx->err = "l3d_plan_matching: bad entry"; return 1; }
+            PlannedView pv; pv.view = p.view; pv.nb.assign(p.neighbors, p.neighbors + p.n_neighbors);
+            for (int c = 0; c < p.n_neighbors; ++c) {
+                if (p.neighbors[c].view < 0 || p.neighbors[c].view >= ctx->V || p.neighbors[c].view == p.view) { ctx->plan.clear(); ctx->err = "l3d_plan_matching: bad neighbour"; return 1; }
+                // (several GPUs on one scene: the rows of the rank with most of them -- the batches must be cut the same way on every rank)
+                if (p.neighbors[c].to_be_matched) pv.pair_tests += uint64_t((ctx->views[p.view].n_segments + ctx->world - 1) / ctx->world) * uint64_t(ctx->views[p.neighbors[c].view].n_segments);
             }
-        ctx->level = level;
-        ctx->order.resize(n);
-        for (size_t k = 0; k < n; ++k) ctx->order[k] = k;
-        std::stable_sort(ctx->order.begin(), ctx->order.end(), [&level](size_t a, size_t b) { return level[a] < level[b]; });
-        l3d_ctx::Stashed empty; memset(&empty, 0, sizeof empty);
-        ctx->results.assign(n, empty);
-    }
-    // Batches: the pair tests of batch i + 1 run beside the per-view work of batch i, so the schedule is cut into
-    // about eight of them (not smaller than 2.5e8 pair tests: a batch has fixed costs), none above the memory budget.
-    uint64_t total = 0;
-    for (size_t k = 0; k < ctx->plan.size(); ++k) total += ctx->plan[k].pair_tests;
-    ctx->batch_pairs = ctx->batch_override ? ctx->batch_override : std::min<uint64_t>(ctx->pair_budget, std::max<uint64_t>(total / 8, 250000000ull));
-    if (ctx->stage_events && !ctx->batch_override) ctx->batch_pairs = ctx->pair_budget;      // per-stage timing: nothing runs beside anything else
-    return 0;
+            ctx->plan.push_back(pv);
+        }
+        // Execution order.  View b needs view a first only if a hands records over to b (a comes earlier and marks b
+        // "deliver"), so the schedule is a dependency graph, usually of a few independent chains (views along a street;
+        // C2: 200 views, longest chain 50).  The library works through it level by level -- the views of one level do not
+        // depend on each other and run side by side -- and hands the results out in the order of the calls.
+        {
+            const size_t n = ctx->plan.size();
+            std::vector<int> at(size_t(ctx->V), -1), level(n, 1);
+            for (size_t k = 0; k < n; ++k) at[ctx->plan[k].view] = int(k);
+            for (size_t k = 0; k < n; ++k)
+                for (size_t c = 0; c < ctx->plan[k].nb.size(); ++c) {
+                    const l3d_neighbor& nbr = ctx->plan[k].nb[c];
+                    const int to = at[nbr.view];
+                    if (nbr.deliver && to > int(k)) level[to] = std::max(level[to], level[k] + 1);
+                }
+            ctx->level = level;
+            ctx->order.resize(n);
+            for (size_t k = 0; k < n; ++k) ctx->order[k] = k;
+            std::stable_sort(ctx->order.begin(), ctx->order.end(), [&level](size_t a, size_t b) { return level[a] < level[b]; });
+            l3d_ctx::Stashed empty; memset(&empty, 0, sizeof empty);
+            ctx->results.assign(n, empty);
+        }
+        // Batches: the pair tests of batch i + 1 run beside the per-view work of batch i, so the schedule is cut into
+        // about eight of them (not smaller than 2.5e8 pair tests: a batch has fixed costs), none above the memory budget.
+        uint64_t total = 0;
+        for (size_t k = 0; k < ctx->plan.size(); ++k) total += ctx->plan[k].pair_tests;
+        ctx->batch_pairs = ctx->batch_override ? ctx->batch_override : std::min<uint64_t>(ctx->pair_budget, std::max<uint64_t>(total / 8, 250000000ull));
+        if (ctx->stage_events && !ctx->batch_override) ctx->batch_pairs = ctx->pair_budget;      // per-stage timing: nothing runs beside anything else
+        return 0;
+    });
 }
 
 int l3d_debug_set_batch_pairs(l3d_ctx* ctx, uint64_t pairs)
 {
     if (!ctx) return 1;
     ctx->batch_override = pairs;
+    return 0;
+}
+
+int l3d_debug_set_pretest(l3d_ctx* ctx, int mode)
+{
+    if (!ctx || mode < 0 || mode > 1) return 1;
+    ctx->pretest_mode = mode;
+    return 0;
+}
+
+int l3d_debug_set_candidate_limit(l3d_ctx* ctx, uint64_t limit)
+{
+    if (!ctx) return 1;
+    ctx->cand_limit = (limit == 0 || limit > 0x7fff0000ull) ? 0x7fff0000ull : limit;
     return 0;
 }
 
@@ -2488,42 +3052,46 @@ int l3d_match_view_resident(l3d_ctx* ctx, int view, int n_neighbors, const l3d_n
 
 int l3d_unproject(l3d_ctx* ctx, size_t n, const l3d_hypothesis_in* in, l3d_segment3d* out)
 {
-    if (!ctx) return 1;
-    if (n == 0) { ctx->n_hyp = 0; return 0; }
-    if (!in || !out) { ctx->err = "l3d_unproject: null argument"; return 1; }
-    for (size_t k = 0; k < n; ++k)
-        if (in[k].view < 0 || in[k].view >= ctx->V || in[k].seg < 0 || in[k].seg >= ctx->views[in[k].view].n_segments) { ctx->err = "l3d_unproject: view/segment out of range"; return 1; }
-    L3D_CUDA(cudaSetDevice(ctx->device));
-    L3D_CUDA(ctx->d_hin.ensure(n)); L3D_CUDA(ctx->d_hout.ensure(n)); L3D_CUDA(ctx->d_hyp.ensure(n));
-    L3D_CUDA(cudaMemcpyAsync(ctx->d_hin.p, in, sizeof(l3d_hypothesis_in) * n, cudaMemcpyHostToDevice, ctx->stream));
-    k_unproject<<<unsigned((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_segs.p, ctx->d_viewd.p, ctx->d_hin.p, n, ctx->d_hyp.p, ctx->d_hout.p);
-    ctx->launches += 1;
-    L3D_CUDA(cudaGetLastError());
-    L3D_CUDA(cudaMemcpyAsync(out, ctx->d_hout.p, sizeof(l3d_segment3d) * n, cudaMemcpyDeviceToHost, ctx->stream));
-    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
-    ctx->n_hyp = n;
-    return 0;
+    return guarded(ctx, [&]() -> int {
+        if (!ctx) return 1;
+        if (n == 0) { ctx->n_hyp = 0; return 0; }
+        if (!in || !out) { ctx->err = "l3d_unproject: null argument"; return 1; }
+        for (size_t k = 0; k < n; ++k)
+            if (in[k].view < 0 || in[k].view >= ctx->V || in[k].seg < 0 || in[k].seg >= ctx->views[in[k].view].n_segments) { ctx->err = "l3d_unproject: view/segment out of range"; return 1; }
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        L3D_CUDA(ctx->d_hin.ensure(n)); L3D_CUDA(ctx->d_hout.ensure(n)); L3D_CUDA(ctx->d_hyp.ensure(n));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_hin.p, in, sizeof(l3d_hypothesis_in) * n, cudaMemcpyHostToDevice, ctx->stream));
+        k_unproject<<<unsigned((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_segs.p, ctx->d_viewd.p, ctx->d_hin.p, n, ctx->d_hyp.p, ctx->d_hout.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+        L3D_CUDA(cudaMemcpyAsync(out, ctx->d_hout.p, sizeof(l3d_segment3d) * n, cudaMemcpyDeviceToHost, ctx->stream));
+        L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->n_hyp = n;
+        return 0;
+    });
 }
 
 int l3d_affinity(l3d_ctx* ctx, const float* median_depth, size_t n_pairs, const l3d_pair* pairs, float sigma_a, float* out)
 {
-    if (!ctx) return 1;
-    if (n_pairs == 0) return 0;
-    if (!median_depth || !pairs || !out) { ctx->err = "l3d_affinity: null argument"; return 1; }
-    if (ctx->n_hyp == 0) { ctx->err = "l3d_affinity: no hypotheses resident (call l3d_unproject first)"; return 1; }
-    for (size_t k = 0; k < n_pairs; ++k)
-        if (pairs[k].a < 0 || size_t(pairs[k].a) >= ctx->n_hyp || pairs[k].b < 0 || size_t(pairs[k].b) >= ctx->n_hyp) { ctx->err = "l3d_affinity: pair index out of range"; return 1; }
-    L3D_CUDA(cudaSetDevice(ctx->device));
-    L3D_CUDA(ctx->d_pairs.ensure(n_pairs)); L3D_CUDA(ctx->d_aff.ensure(n_pairs)); L3D_CUDA(ctx->d_medians.ensure(size_t(ctx->V)));
-    L3D_CUDA(cudaMemcpyAsync(ctx->d_medians.p, median_depth, sizeof(float) * size_t(ctx->V), cudaMemcpyHostToDevice, ctx->stream));
-    L3D_CUDA(cudaMemcpyAsync(ctx->d_pairs.p, pairs, sizeof(l3d_pair) * n_pairs, cudaMemcpyHostToDevice, ctx->stream));
-    const float two_log = 2.0f * logf(0.01f);                                   // view.cc:376
-    k_affinity<<<unsigned((n_pairs + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_hyp.p, ctx->d_viewd.p, ctx->d_medians.p, ctx->d_pairs.p, n_pairs, sigma_a, two_log, ctx->d_aff.p);
-    ctx->launches += 1;
-    L3D_CUDA(cudaGetLastError());
-    L3D_CUDA(cudaMemcpyAsync(out, ctx->d_aff.p, sizeof(float) * n_pairs, cudaMemcpyDeviceToHost, ctx->stream));
-    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
-    return 0;
+    return guarded(ctx, [&]() -> int {
+        if (!ctx) return 1;
+        if (n_pairs == 0) return 0;
+        if (!median_depth || !pairs || !out) { ctx->err = "l3d_affinity: null argument"; return 1; }
+        if (ctx->n_hyp == 0) { ctx->err = "l3d_affinity: no hypotheses resident (call l3d_unproject first)"; return 1; }
+        for (size_t k = 0; k < n_pairs; ++k)
+            if (pairs[k].a < 0 || size_t(pairs[k].a) >= ctx->n_hyp || pairs[k].b < 0 || size_t(pairs[k].b) >= ctx->n_hyp) { ctx->err = "l3d_affinity: pair index out of range"; return 1; }
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        L3D_CUDA(ctx->d_pairs.ensure(n_pairs)); L3D_CUDA(ctx->d_aff.ensure(n_pairs)); L3D_CUDA(ctx->d_medians.ensure(size_t(ctx->V)));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_medians.p, median_depth, sizeof(float) * size_t(ctx->V), cudaMemcpyHostToDevice, ctx->stream));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_pairs.p, pairs, sizeof(l3d_pair) * n_pairs, cudaMemcpyHostToDevice, ctx->stream));
+        const float two_log = 2.0f * logf(0.01f);                                   // view.cc:376
+        k_affinity<<<unsigned((n_pairs + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_hyp.p, ctx->d_viewd.p, ctx->d_medians.p, ctx->d_pairs.p, n_pairs, sigma_a, two_log, ctx->d_aff.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+        L3D_CUDA(cudaMemcpyAsync(out, ctx->d_aff.p, sizeof(float) * n_pairs, cudaMemcpyDeviceToHost, ctx->stream));
+        L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+        return 0;
+    });
 }
 
 int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3d_edge* out)
@@ -2582,18 +3150,20 @@ int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3
 
 int l3d_debug_math(l3d_ctx* ctx, int which, int n, const float* in, float* out)
 {
-    if (!ctx) return 1;
-    if (n <= 0) return 0;
-    L3D_CUDA(cudaSetDevice(ctx->device));
-    float *d_in, *d_out;
-    L3D_CUDA(cudaMalloc(&d_in, sizeof(float) * n)); L3D_CUDA(cudaMalloc(&d_out, sizeof(float) * n));
-    L3D_CUDA(cudaMemcpyAsync(d_in, in, sizeof(float) * n, cudaMemcpyHostToDevice, ctx->stream));
-    k_debug_math<<<(n + 255) / 256, 256, 0, ctx->stream>>>(which, d_in, d_out, n);
-    ctx->launches += 1;
-    L3D_CUDA(cudaMemcpyAsync(out, d_out, sizeof(float) * n, cudaMemcpyDeviceToHost, ctx->stream));
-    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
-    cudaFree(d_in); cudaFree(d_out);
-    return 0;
+    return guarded(ctx, [&]() -> int {
+        if (!ctx) return 1;
+        if (n <= 0) return 0;
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        float *d_in, *d_out;
+        L3D_CUDA(cudaMalloc(&d_in, sizeof(float) * n)); L3D_CUDA(cudaMalloc(&d_out, sizeof(float) * n));
+        L3D_CUDA(cudaMemcpyAsync(d_in, in, sizeof(float) * n, cudaMemcpyHostToDevice, ctx->stream));
+        k_debug_math<<<(n + 255) / 256, 256, 0, ctx->stream>>>(which, d_in, d_out, n);
+        ctx->launches += 1;
+        L3D_CUDA(cudaMemcpyAsync(out, d_out, sizeof(float) * n, cudaMemcpyDeviceToHost, ctx->stream));
+        L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+        cudaFree(d_in); cudaFree(d_out);
+        return 0;
+    });
 }
 
 int l3d_last_timings(l3d_ctx* ctx, float ms[6])
@@ -2633,10 +3203,10 @@ int l3d_marks_elapsed(l3d_ctx* ctx, float* ms)
     return 0;
 }
 
-int l3d_last_kernel_timings(l3d_ctx* ctx, float ms[2])
+int l3d_last_kernel_timings(l3d_ctx* ctx, float ms[3])
 {
     if (!ctx || !ms) return 1;
-    ms[0] = ctx->pa_kernel_ms[0]; ms[1] = ctx->pa_kernel_ms[1];
+    ms[0] = ctx->pa_kernel_ms[0]; ms[1] = ctx->pa_kernel_ms[1]; ms[2] = ctx->pa_kernel_ms[2];
     return 0;
 }
 
@@ -2651,29 +3221,42 @@ int l3d_flush_l2(l3d_ctx* ctx)
     return 0;
 }
 
-int l3d_measure_fp32_peak(l3d_ctx* ctx, float* tflops)
+// which = 0: scalar FFMA chains, 1: packed FFMA2 chains.  Best of five launches.
+static int measure_fp32(l3d_ctx* ctx, int which, float* tflops)
 {
-    if (!ctx || !tflops) return 1;
     L3D_CUDA(cudaSetDevice(ctx->device));
     cudaDeviceProp prop; L3D_CUDA(cudaGetDeviceProperties(&prop, ctx->device));
-    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 16;
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 13;
     float* d = nullptr;
     L3D_CUDA(cudaMalloc(&d, sizeof(float) * size_t(blocks) * threads));
-    k_fma_probe<<<blocks, threads, 0, ctx->stream>>>(d, 1024);
+    const float b = 1.0000001f, c = 1e-7f;
     float best = 0.f;
-    for (int r = 0; r < 3; ++r) {
+    for (int r = 0; r < 6; ++r) {                       // the first launch warms up
         L3D_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
-        k_fma_probe<<<blocks, threads, 0, ctx->stream>>>(d, iters);
+        if (which == 0) k_fma_probe<<<blocks, threads, 0, ctx->stream>>>(d, iters, b, c);
+        else k_fma2_probe<<<blocks, threads, 0, ctx->stream>>>(d, iters, b, c);
         L3D_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
         L3D_CUDA(cudaStreamSynchronize(ctx->stream));
         float ms = 0.f; cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
-        double fl = double(blocks) * threads * double(iters) * 8.0 * 2.0;
-        best = std::max(best, float(fl / (double(ms) * 1e-3) / 1e12));
+        const double fl = double(blocks) * threads * double(iters) * 128.0 * 2.0;      // 128 FMAs per thread and loop trip in both variants
+        if (r > 0) best = std::max(best, float(fl / (double(ms) * 1e-3) / 1e12));
     }
-    ctx->launches += 4;
+    ctx->launches += 6;
     cudaFree(d);
     *tflops = best;
     return 0;
+}
+
+int l3d_measure_fp32_peak(l3d_ctx* ctx, float* tflops)
+{
+    if (!ctx || !tflops) return 1;
+    return measure_fp32(ctx, 0, tflops);
+}
+
+int l3d_measure_fp32x2_peak(l3d_ctx* ctx, float* tflops)
+{
+    if (!ctx || !tflops) return 1;
+    return measure_fp32(ctx, 1, tflops);
 }
 
 }  // extern "C"

@@ -124,7 +124,8 @@ std::string cacheName(const std::string& dir, unsigned id, unsigned w, unsigned 
 
 struct Line3D::Impl
 {
-    bool verbose, computation, use_collinearity, measure_only, flush_l2, keep_debug, stage_timing;
+    bool verbose, computation, use_collinearity, measure_only, match_only, flush_l2, keep_debug, stage_timing;
+    bool split; int split_rank, split_world;          // several GPUs on one scene (setSplit)
     std::string prefix, separator, data_directory;
     int matching_neighbors; float min_baseline, unc_upper, unc_lower, sigma_p, sigma_a;
     int shard_rank, shard_world; std::set<unsigned> my_views;
@@ -155,7 +156,7 @@ struct Line3D::Impl
     int cluster_nodes;
     L3DRunStats stats;
 
-    Impl() : shard_rank(0), shard_world(1), ctx(0), cluster_nodes(0) { memset(&stats, 0, sizeof stats); }
+    Impl() : match_only(false), split(false), split_rank(0), split_world(1), shard_rank(0), shard_world(1), ctx(0), cluster_nodes(0) { memset(&stats, 0, sizeof stats); }
 
     void fail(const char* what)
     {
@@ -307,6 +308,10 @@ struct Line3D::Impl
     void assignShard()
     {
         my_views.clear();
+        if (split) {                // every rank works on every view (its share of the view's segments)
+            for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) my_views.insert(it->first);
+            return;
+        }
         std::map<unsigned, std::set<unsigned> > adj;
         for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it)
             for (size_t k = 0; k < it->second.size(); ++k) { adj[it->first].insert(it->second[k]); adj[it->second[k]].insert(it->first); }
@@ -418,6 +423,7 @@ struct Line3D::Impl
             // a rank only needs the segments of its own connected components (every neighbour of one of its views is in them)
             const bool mine = shard_world <= 1 || my_views.count(it->first) != 0;
             o.id = int(v->id); o.n_segments = mine ? int(v->segs.size()) : 0; o.segments = reinterpret_cast<const float*>(v->segs.data());
+            if (split && split_rank != 0) o.segments = 0;      // replicated from rank 0 over NCCL (l3d_set_views)
             for (int r = 0; r < 3; ++r) {
                 for (int c = 0; c < 3; ++c) { o.RtKinv[r * 3 + c] = float(v->RtKinv(r, c)); o.RtKinv_d[r * 3 + c] = v->RtKinv(r, c); }   // line3D.cc:746, 790
                 for (int c = 0; c < 4; ++c) o.P[r * 4 + c] = float(v->P(r, c));                                                            // line3D.cc:756
@@ -427,7 +433,7 @@ struct Line3D::Impl
             o.k_lower = v->k_lower; o.k_upper = v->k_upper;
         }
         if (l3d_set_views(ctx, int(lv.size()), lv.data())) fail("l3d_set_views");
-        for (size_t k = 0; k < lv.size(); ++k) stats.h2d_bytes += size_t(lv[k].n_segments) * 16 + sizeof(l3d_view);
+        for (size_t k = 0; k < lv.size(); ++k) stats.h2d_bytes += (lv[k].segments ? size_t(lv[k].n_segments) * 16 : 0) + sizeof(l3d_view);
     }
 
     // line3D.cc:620-648 + 698-885
@@ -488,9 +494,9 @@ struct Line3D::Impl
             stats.t_matching_calls += now_s() - t0;
             float ms[6]; l3d_last_timings(ctx, ms);
             for (int k = 0; k < 5; ++k) stats.t_stage[k] += double(ms[k]) * 1e-3;
-            if (ms[0] > 0.f) { float km[2]; l3d_last_kernel_timings(ctx, km); stats.t_k_pretest += double(km[0]) * 1e-3; stats.t_k_exact += double(km[1]) * 1e-3; }
+            if (ms[0] > 0.f) { float km[3]; l3d_last_kernel_timings(ctx, km); stats.t_k_pretest += double(km[0]) * 1e-3; stats.t_k_exact += double(km[1]) * 1e-3; stats.t_k_pretest2 += double(km[2]) * 1e-3; }
             stats.score_iters_other_cam += res.score_iters_other_cam;
-            stats.h2d_bytes += nb.size() * 160; stats.d2h_bytes += (measure_only ? 0 : res.n_filtered * sizeof(l3d_match)) + 64;
+            stats.h2d_bytes += nb.size() * 160; stats.d2h_bytes += ((measure_only || !res.filtered) ? 0 : res.n_filtered * sizeof(l3d_match)) + 64;
             stats.pair_tests += res.pair_tests; stats.candidates += res.n_candidates; stats.raw_matches += res.n_raw;
             stats.scored_matches += res.n_scored; stats.filtered_matches += res.n_filtered; stats.score_iters += res.score_iters;
             if (verbose) {
@@ -504,7 +510,7 @@ struct Line3D::Impl
             match_median.push_back(res.median_depth);
             // the records stay in the library's pinned memory (l3d_retain_results) and are filed after the loop, on
             // all cores, while nothing else waits for them: the GPU is not held up by the host's bookkeeping
-            if (!measure_only) { ViewRecords vr = {vid, v->index, res.scored != 0, res.filtered, res.n_filtered, &it->second}; view_records.push_back(vr); }
+            if (!measure_only && !match_only && (res.filtered || res.n_filtered == 0)) { ViewRecords vr = {vid, v->index, res.scored != 0, res.filtered, res.n_filtered, &it->second}; view_records.push_back(vr); }
             else { std::vector<BestMatch>& bm = best[vid]; bm.assign(v->segs.size(), BestMatch()); for (size_t s = 0; s < bm.size(); ++s) bm[s].has = false; }
             for (size_t c = 0; c < it->second.size(); ++c) {                                                                        // :875-881
                 const unsigned n = it->second[c];
@@ -980,7 +986,7 @@ Line3D::Line3D(const std::string data_directory, const int matchingNeighbors, co
     d.verbose = verbose; d.prefix = "[L3D] "; d.separator = "----------------------------------------";
     d.data_directory = data_directory; d.matching_neighbors = matchingNeighbors;
     d.unc_upper = fabs(uncertainty_t_upper_2D); d.unc_lower = fabs(uncertainty_t_lower_2D);              // line3D.cc:18-28
-    d.computation = false; d.use_collinearity = useCollinearity; d.min_baseline = min_baseline; d.measure_only = false; d.flush_l2 = false; d.keep_debug = false; d.stage_timing = false;
+    d.computation = false; d.use_collinearity = useCollinearity; d.min_baseline = min_baseline; d.measure_only = false; d.match_only = false; d.flush_l2 = false; d.keep_debug = false; d.stage_timing = false;
     if (d.unc_lower < 1.0f) d.unc_lower = 1.0f;
     if (d.unc_upper <= d.unc_lower) d.unc_upper = d.unc_lower + 1.0f;
     d.sigma_a = sigma_a; d.sigma_p = sigma_p;
@@ -1063,7 +1069,8 @@ void Line3D::compute3Dmodel(bool perform_diffusion)                             
     d.stats.t_upload = now_s() - t1;
     if (d.flush_l2) l3d_flush_l2(d.ctx);
     d.matchViews();
-    if (!d.measure_only) {
+    // (several GPUs on one scene: the records are gathered on rank 0, which alone goes on to cluster them)
+    if (!d.measure_only && !d.match_only && (!d.split || d.split_rank == 0)) {
         t1 = now_s();
         d.buildHypotheses();
         d.stats.t_hypotheses = now_s() - t1;
@@ -1077,12 +1084,20 @@ void Line3D::getResult(std::list<L3D::L3DFinalLine3D>& result) { result.clear();
 unsigned int Line3D::numCameras() { return impl_->views.size(); }
 L3DRunStats Line3D::runStats() const { return impl_->stats; }
 void Line3D::setMeasureOnly(bool on) { impl_->measure_only = on; }
+void Line3D::setMatchOnly(bool on) { impl_->match_only = on; }
 void Line3D::setFlushL2(bool on) { impl_->flush_l2 = on; }
 void Line3D::setStageTiming(bool on) { impl_->stage_timing = on; }
 void Line3D::setKeepDebug(bool on) { impl_->keep_debug = on; }
 void Line3D::resetGeometry()
 {
     for (std::map<unsigned, ViewData*>::iterator it = impl_->views.begin(); it != impl_->views.end(); ++it) { it->second->R = it->second->R0; it->second->t = it->second->t0; it->second->init(); }
+}
+void Line3D::setSplit(int rank, int world, const unsigned char* nccl_id)
+{
+    Impl& d = *impl_;
+    if (l3d_comm_init(d.ctx, rank, world, nccl_id, 0)) d.fail("l3d_comm_init");
+    d.split = world > 1; d.split_rank = d.split ? rank : 0; d.split_world = d.split ? world : 1;
+    d.shard_rank = 0; d.shard_world = 1;
 }
 void Line3D::setShard(int rank, int world) { impl_->shard_world = world < 1 ? 1 : world; impl_->shard_rank = (rank < 0 || rank >= impl_->shard_world) ? 0 : rank; }
 

@@ -82,7 +82,8 @@ namespace L3D
         double t_neighbors, t_upload, t_matching, t_matching_device, t_hypotheses, t_affinity, t_diffusion, t_clustering, t_lines, t_total;
         double t_stage[5];   // device seconds: pre-test, exact test, assembly, scoring, reduce/filter/deliver
         unsigned long long h2d_bytes, d2h_bytes;
-        double t_k_pretest, t_k_exact;   // device seconds of the pre-test and exact-test kernels alone
+        double t_k_pretest, t_k_exact;   // device seconds of the level-1 pre-test and exact-test kernels alone
+        double t_k_pretest2;             // ... and of the level-2 pre-test kernel
         double t_matching_calls;   // part of t_matching spent inside l3d_match_view (the rest is the host's bookkeeping between the calls)
     };
 
@@ -142,6 +143,14 @@ namespace L3D
         // independent of each other, so they are dealt out whole (largest first, to the least loaded rank); all ranks
         // must have added the same images.  rank 0 / world 1 = everything.
         void setShard(int rank, int world);
+        // Multi-GPU, one connected scene: the `world` processes (one per GPU) have added the same images and make the
+        // same calls; every view's segments are dealt out to the ranks in turn and the ranks exchange what later views
+        // need over NCCL (include/l3d_b200.h, l3d_comm_init).  The matches are gathered on rank 0, which alone clusters
+        // them: getResult() is empty on the other ranks.  nccl_id: L3D_COMM_ID_BYTES bytes from l3d_comm_unique_id on
+        // rank 0, distributed by the caller.  world = 1 switches it off.
+        void setSplit(int rank, int world, const unsigned char* nccl_id);
+        // run matching with the records copied to the host, but stop there (measurement of the matching stage alone)
+        void setMatchOnly(bool on);
         // keep the per-match records debugDump() writes (off by default: they are large)
         void setKeepDebug(bool on);
         void setStageTiming(bool on);   // per-stage device times in runStats().t_stage (slows matching by about 13 %)

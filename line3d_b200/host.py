@@ -22,7 +22,7 @@ DEFAULTS = dict(neighbors=10, unc_upper=5.0, unc_lower=1.0, sigma_p=3.5, sigma_a
 STAT_NAMES = ["pair_tests", "candidates", "raw_matches", "scored_matches", "filtered_matches", "score_iters", "score_iters_other_cam",
               "hypotheses", "affinity_pairs", "edges", "kernel_launches", "t_neighbors", "t_upload", "t_matching", "t_matching_device",
               "t_hypotheses", "t_affinity", "t_diffusion", "t_clustering", "t_lines", "t_total", "t_pretest", "t_exact", "t_assemble",
-              "t_score", "t_reduce", "h2d_bytes", "d2h_bytes", "t_matching_calls", "t_k_pretest", "t_k_exact", "_r1"]
+              "t_score", "t_reduce", "h2d_bytes", "d2h_bytes", "t_matching_calls", "t_k_pretest", "t_k_exact", "t_k_pretest2"]
 
 _lib = None
 
@@ -40,6 +40,7 @@ def lib():
         L.l3dhost_compute.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.l3dhost_reset_geometry.restype = C.c_int; L.l3dhost_reset_geometry.argtypes = [C.c_void_p]
         L.l3dhost_set_shard.restype = C.c_int; L.l3dhost_set_shard.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.l3dhost_set_split.restype = C.c_int; L.l3dhost_set_split.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p]
         L.l3dhost_dump.restype = C.c_int; L.l3dhost_dump.argtypes = [C.c_void_p, C.c_char_p]
         L.l3dhost_close.restype = None; L.l3dhost_close.argtypes = [C.c_void_p]
         _lib = L
@@ -61,7 +62,7 @@ class Session:
             shutil.rmtree(self._data_dir, ignore_errors=True)
             raise capi.L3DError("l3dhost_open failed (no CUDA device, or unreadable scene)")
 
-    def compute(self, measure_only: bool = False, flush_l2: bool = False, diffusion: bool | None = None, keep_debug: bool = False, fresh: bool = True, stage_timing: bool = False):
+    def compute(self, measure_only: bool | int = False, flush_l2: bool = False, diffusion: bool | None = None, keep_debug: bool = False, fresh: bool = True, stage_timing: bool = False):
         """fresh: put the cameras back to their original poses first, so that every call sees the same input (a repeated
         compute3Dmodel otherwise re-normalises the normalised scene, as the reference does)."""
         if fresh:
@@ -76,6 +77,11 @@ class Session:
 
     def set_shard(self, rank: int, world: int):
         lib().l3dhost_set_shard(self._h, int(rank), int(world))
+
+    def set_split(self, rank: int, world: int, nccl_id: bytes | None):
+        """Several GPUs on ONE scene (Line3D::setSplit): nccl_id from capi.comm_unique_id() on rank 0, the same on all ranks."""
+        if lib().l3dhost_set_split(self._h, int(rank), int(world), nccl_id) != 0:
+            raise capi.L3DError("l3dhost_set_split failed (NCCL)")
 
     def dump(self) -> dict:
         d = tempfile.mkdtemp(prefix="l3d_dump_")

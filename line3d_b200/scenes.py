@@ -269,7 +269,11 @@ def _visible_wps(pts, nrm, K, R, t):
     return np.nonzero(ok)[0].astype(np.uint32)
 
 
-def _assemble(name, buildings, cams, n_seg, seed, n_wp=4000, win=2.4):
+def _assemble(name, buildings, cams, n_seg, seed, n_wp=4000, win=2.4, per_view_rng=False, view_range=None):
+    """per_view_rng: every view draws from its own generator seeded with (seed, view id) instead of one generator
+    for the whole scene, so that any range of views (view_range = (first, end)) can be generated on its own -- by
+    another process -- and the parts put together give the same scene."""
+    assert view_range is None or per_view_rng
     rng = np.random.default_rng(seed)
     E, N = [], []
     for (x0, y0, sx, sy, sz) in buildings:
@@ -280,6 +284,10 @@ def _assemble(name, buildings, cams, n_seg, seed, n_wp=4000, win=2.4):
     K = np.array([[FOCAL, 0, IMG_W / 2.0], [0, FOCAL, IMG_H / 2.0], [0, 0, 1.0]])
     sc = Scene(name=name)
     for vid, (C, target) in enumerate(cams):
+        if view_range is not None and not (view_range[0] <= vid < view_range[1]):
+            continue
+        if per_view_rng:
+            rng = np.random.default_rng([seed, vid])
         R, t = _look_at(C, target)
         lo, hi = int(round(n_seg * 0.95)), int(round(n_seg * 1.05))
         n_t = int(rng.integers(lo, hi + 1))
@@ -305,7 +313,7 @@ def wireframe_building(n_views=24, n_seg=800, seed=1001, radius=34.0, height=9.0
     return _assemble("wireframe_building", b, cams, n_seg, seed, n_wp=3000, win=1.9)
 
 
-def urban(n_views=200, n_seg=2000, seed=1002, blocks=(4, 3)):
+def urban(n_views=200, n_seg=2000, seed=1002, blocks=(4, 3), per_view_rng=False, view_range=None):
     """C2/C4-shaped: city blocks, cameras walking the streets between them."""
     rng = np.random.default_rng(seed + 7)
     bx, by = blocks
@@ -348,7 +356,7 @@ def urban(n_views=200, n_seg=2000, seed=1002, blocks=(4, 3)):
         sgn = 1.0 if dx >= 0 else -1.0
         tgt = (x + 12.0 * dx - sgn * side * 14.0 * dy, y + 12.0 * dy + sgn * side * 14.0 * dx, 9.0)
         cams.append(((x, y, 1.7 + 0.2 * np.sin(k)), tgt))
-    return _assemble("urban", buildings, cams, n_seg, seed, n_wp=20000, win=1.5)
+    return _assemble("urban", buildings, cams, n_seg, seed, n_wp=20000, win=1.5, per_view_rng=per_view_rng, view_range=view_range)
 
 
 def dense_dome(n_views=300, n_seg=3000, seed=1005, radius=60.0):
@@ -378,7 +386,7 @@ CONFIGS = {
     "C1": dict(fn=wireframe_building, kw=dict(n_views=24, n_seg=800, seed=1001), k=12, diffusion=False),
     "C2": dict(fn=urban, kw=dict(n_views=200, n_seg=2000, seed=1002), k=12, diffusion=False),
     "C3": dict(fn=urban, kw=dict(n_views=200, n_seg=2000, seed=1002), k=12, diffusion=True),
-    "C4": dict(fn=urban, kw=dict(n_views=1000, n_seg=4000, seed=1004, blocks=(8, 6)), k=20, diffusion=False),
+    "C4": dict(fn=urban, kw=dict(n_views=1000, n_seg=4000, seed=1004, blocks=(8, 6), per_view_rng=True), k=20, diffusion=False),
     "C5": dict(fn=dense_dome, kw=dict(n_views=300, n_seg=3000, seed=1005), k=-1, diffusion=False),
 }
 
@@ -404,3 +412,25 @@ def multi_district(config: str, n: int, spacing: float = 260.0) -> Scene:
 def make(config: str) -> Scene:
     c = CONFIGS[config]
     return c["fn"](**c["kw"])
+
+
+def _make_part(arg):
+    config, first, end = arg
+    c = CONFIGS[config]
+    return c["fn"](view_range=(first, end), **c["kw"]).views
+
+
+def make_parallel(config: str, processes: int | None = None) -> Scene:
+    """A configuration whose views have their own generators (per_view_rng), made by several processes at once."""
+    import multiprocessing as mp
+    import os
+    c = CONFIGS[config]
+    if not c["kw"].get("per_view_rng"):
+        return make(config)
+    n = c["kw"]["n_views"]
+    processes = processes or min(os.cpu_count() or 1, 32)
+    step = max((n + 4 * processes - 1) // (4 * processes), 1)
+    parts = [(config, a, min(a + step, n)) for a in range(0, n, step)]
+    with mp.get_context("fork").Pool(processes) as pool:
+        views = [v for part in pool.map(_make_part, parts) for v in part]
+    return Scene(views=views, name=config)

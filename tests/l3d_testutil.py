@@ -85,3 +85,43 @@ def filtered_as_rows(vid, res):
     rows[:, 2] = nbs[f["cam"]] if res["scored"] else f["cam"]
     rows[:, 3] = f["tgt_seg"]; rows[:, 4:8] = f["depths"]; rows[:, 8] = f["confidence"]
     return rows
+
+
+# ---- digests of a whole-pipeline dump (tests/golden/make_golden_big.py, tests/test_gpu_golden_big.py) --------------
+def _sha(a) -> np.ndarray:
+    import hashlib
+    return np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), dtype=np.uint8).copy()
+
+
+def pack_filtered(rows: np.ndarray) -> np.ndarray:
+    """filtered_matches.npy rows (vID, seg1, cam2, seg2, 4 depths, conf; float64) of ONE view as canonical bytes: sorted by
+    (seg1, cam2, seg2) -- the reference returns the records of an unscored view in delivery order (cudawrapper.cu:877-878),
+    the library in sorted order -- ids as int32, depths and confidence as the float32 they are."""
+    rec = np.zeros(rows.shape[0], dtype=[("ids", "<i4", (4,)), ("val", "<f4", (5,))])
+    if rows.shape[0]:
+        o = np.lexsort((rows[:, 3], rows[:, 2], rows[:, 1]))
+        rec["ids"] = rows[o, :4].astype(np.int32); rec["val"] = rows[o, 4:9].astype(np.float32)
+    return rec
+
+
+def digest_of_dumps(dm: dict, n_lines: int) -> dict:
+    """Compact, order-exact digest of everything a run dumps: a few hundred KB for a 200-view scene."""
+    out = dict(n_lines=np.array([n_lines], np.int64), match_log=dm["match_log"].astype(np.int32), match_median=dm["match_median"].astype(np.float32).reshape(-1),
+               cluster_nodes=dm["cluster_nodes"].astype(np.int32).reshape(-1), lines_seg3d=dm["lines_seg3d"].astype(np.float64))
+    f = dm["filtered_matches"]
+    log = out["match_log"]
+    sha = np.zeros((log.shape[0], 32), np.uint8)
+    # the rows of one view are contiguous, in the order of the match log
+    start = 0
+    for k in range(log.shape[0]):
+        n = int(log[k, 3])
+        rows = f[start:start + n]
+        assert n == 0 or (rows[:, 0] == log[k, 0]).all(), "filtered_matches is not grouped by view in match_log order"
+        sha[k] = _sha(pack_filtered(rows)); start += n
+    assert start == f.shape[0]
+    out["filtered_sha"] = sha
+    for name, dt in (("visual_neighbors", np.int32), ("best_match", np.float64), ("potential", np.int32), ("edges_pre_diffusion", np.float64),
+                     ("edges_cluster", np.float64), ("lines_seg2d", np.int32), ("collinearity", np.float64)):
+        a = dm[name].astype(dt)
+        out[name + "_sha"] = _sha(a); out[name + "_shape"] = np.array(a.shape, np.int64)
+    return out
