@@ -253,6 +253,10 @@ int l3d_measure_fp32x2_peak(l3d_ctx* ctx, float* tflops);
  * array: they are written to agree bit for bit with glibc's expf / acosf, which the
  * reference's host build calls; tests compare them against libm. */
 int l3d_debug_math(l3d_ctx* ctx, int which, int n, const float* in, float* out);
+/* Host seconds this context has spent since the last call of this function [0] putting groups of views on the GPU,
+ * [1] waiting for their results, [2] collecting them; [3] = number of groups.  For finding out whether the host or
+ * the GPU limits the per-view chain. */
+int l3d_debug_host_times(l3d_ctx* ctx, double out[4]);
 /* Number of kernels this library has launched on the context since creation. */
 uint64_t l3d_kernel_launches(const l3d_ctx* ctx);
 

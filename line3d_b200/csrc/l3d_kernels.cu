@@ -31,6 +31,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <chrono>
 #include <string>
 #include <thread>
 #include <vector>
@@ -1336,15 +1337,9 @@ struct VArgs {
 
 // What one rank reports about one view of a group (all-gathered): its output records, its matches, its iteration counts.
 struct RankRec { int F, M; unsigned long long iters_all, iters_same; int pad[2]; };
-// Where the ranks' records of a group are: in the all-gather buffer (rank-major, every rank's records of the group's
-// views back to back) and in the group's view-major buffer, and where each view's hand-over records go.
 constexpr int MR_MAX_RANKS = 16;
-struct MrLayout {
-    int src_off[MR_MAX_RANKS][8], dst_off[MR_MAX_RANKS][8], cnt[MR_MAX_RANKS][8];      // [rank][view of the group], in records
-    int view_off[8], view_cnt[8];
-    int* dl_tgt[8]; float4* dl_dep[8];
-    int padded;                                                                          // records per rank in the all-gather buffer
-};
+// The group's record window of every rank, as mapped into this process (CUDA IPC): [rank] -> base of that rank's window
+struct MrPeers { l3d_match* base[MR_MAX_RANKS]; };
 #define L3D_VIEW(dim) L3D_PDL_PROLOGUE(); const VArgs& va = all[blockIdx.dim]
 
 __global__ void k_gather_counts(const VArgs* __restrict__ all)
@@ -1427,11 +1422,11 @@ __global__ void __launch_bounds__(MS_T) k_finish_view(const VArgs* __restrict__ 
 // ITS segments -- is put together from all ranks' output records of the group:
 //   k_mr_prepare   depth samples of all segments (infinity for other ranks' rows) and this rank's record of each view
 //   NCCL           all-gather of the records, min-all-reduce of the samples, sum-all-reduce of the hand-over group sizes
-//   (host: reads the counts, sizes the buffers)
-//   k_mr_pack      this rank's output records of the group's views back to back
-//   NCCL           all-gather of the packed records
-//   k_mr_unpack    all ranks' records, view by view: what is handed to the host, and what is handed over
-//   k_mr_deliver_scatter   as k_deliver_scatter, over all ranks' records
+//   k_mr_push      this rank's output records of the group's views, stored straight into EVERY rank's record window
+//                  (peer memory over NVLink) at the place the gathered counts assign to them: view by view, rank by rank
+//   NCCL           a one-word all-reduce: every rank's stores have landed
+//   k_mr_deliver_scatter   as k_deliver_scatter, over all ranks' records in the window
+// The host is not in this loop: it reads the counts when it collects the group, with the next group already running.
 // ------------------------------------------------------------------------------------------
 __global__ void k_mr_prepare(const VArgs* __restrict__ all, RankRec* __restrict__ rec)
 {
@@ -1454,38 +1449,53 @@ __global__ void k_mr_prepare(const VArgs* __restrict__ all, RankRec* __restrict_
         rec[blockIdx.y] = r;
     }
 }
-__global__ void k_mr_pack(const VArgs* __restrict__ all, const RankRec* __restrict__ rec, l3d_match* __restrict__ send)
+// records of view v of the group start at mr_view_offset(v) in a window; inside a view the ranks follow each other
+__device__ __forceinline__ int mr_view_offset(const RankRec* __restrict__ allrec, int W, int v)
 {
-    const VArgs& va = all[blockIdx.y];
     int off = 0;
-    for (int v = 0; v < int(blockIdx.y); ++v) off += rec[v].F;
-    const int n = rec[blockIdx.y].F;
+    for (int vv = 0; vv < v; ++vv) for (int r = 0; r < W; ++r) off += allrec[r * 8 + vv].F;
+    return off;
+}
+__global__ void k_mr_push(const VArgs* __restrict__ all, const RankRec* __restrict__ allrec, MrPeers peers, int rank, int W)
+{
+    L3D_PDL_PROLOGUE();
+    __shared__ int s_off;
+    const int v = blockIdx.y;
+    const VArgs& va = all[v];
+    if (threadIdx.x == 0) {
+        int off = mr_view_offset(allrec, W, v);
+        for (int r = 0; r < rank; ++r) off += allrec[r * 8 + v].F;
+        s_off = off;
+    }
+    __syncthreads();
+    const int n = allrec[rank * 8 + v].F;
     const uint4* src = reinterpret_cast<const uint4*>(va.filtered);
-    uint4* dst = reinterpret_cast<uint4*>(send + off);
+    uint4* dst = reinterpret_cast<uint4*>(peers.base[blockIdx.z] + s_off);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * n; i += gridDim.x * blockDim.x) dst[i] = src[i];
 }
-__global__ void k_mr_unpack(const l3d_match* __restrict__ recv, l3d_match* __restrict__ allf, MrLayout lay)
+__global__ void k_mr_deliver_scatter(const VArgs* __restrict__ all, const l3d_match* __restrict__ window, const RankRec* __restrict__ allrec, int W)
 {
-    const int v = blockIdx.y, r = blockIdx.z;
-    const int n = lay.cnt[r][v];
-    const uint4* src = reinterpret_cast<const uint4*>(recv + size_t(r) * lay.padded + lay.src_off[r][v]);
-    uint4* dst = reinterpret_cast<uint4*>(allf + lay.dst_off[r][v]);
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * n; i += gridDim.x * blockDim.x) dst[i] = src[i];
-}
-__global__ void k_mr_deliver_scatter(const VArgs* __restrict__ all, const l3d_match* __restrict__ allf, MrLayout lay)
-{
+    L3D_PDL_PROLOGUE();
+    __shared__ int s_off, s_n;
     const VArgs& va = all[blockIdx.y];
     if (!va.delivering) return;
-    const int n = lay.view_cnt[blockIdx.y];
-    const l3d_match* f = allf + lay.view_off[blockIdx.y];
+    if (threadIdx.x == 0) {
+        s_off = mr_view_offset(allrec, W, blockIdx.y);
+        int n = 0;
+        for (int r = 0; r < W; ++r) n += allrec[r * 8 + blockIdx.y].F;
+        s_n = n;
+    }
+    __syncthreads();
+    const int n = s_n;
+    const l3d_match* f = window + s_off;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
         const l3d_match m = f[k];
         const int d = va.cams[m.cam].deliver;
         if (d < 0) continue;
         const int key = d * va.stride + m.tgt_seg;
         const int pos = va.dl_start[key] + atomicAdd(&va.cursor[key], 1);
-        lay.dl_tgt[blockIdx.y][pos] = m.src_seg;
-        lay.dl_dep[blockIdx.y][pos] = make_float4(m.depths[2], m.depths[3], m.depths[0], m.depths[1]);     // line3D.cc:852-855
+        va.dl_tgt[pos] = m.src_seg;
+        va.dl_dep[pos] = make_float4(m.depths[2], m.depths[3], m.depths[0], m.depths[1]);     // line3D.cc:852-855
     }
 }
 
@@ -1792,7 +1802,8 @@ struct ViewJob {                 // phase B of one view: on the stream, not yet 
 // The per-view work runs on groups of views (see VArgs): a slot holds one view's buffers, a group up to VG_MAX
 // slots plus what the group's views share (one upload of tables and arguments, one memset, one result download).
 // Two groups exist: the host prepares and launches the next one while the GPU works on the current one.
-constexpr int VG_MAX = 8;
+constexpr int VG_MAX = 8;          // (RankRec tables on the device are indexed [rank * 8 + view])
+static_assert(VG_MAX == 8, "the multi-GPU kernels index the record table with a stride of 8");
 struct ViewSlot {
     ViewJob job;
     size_t plan_index = 0;
@@ -1815,14 +1826,13 @@ struct ViewGroup {
     // the packed records of this rank, all ranks' packed records, all ranks' records view by view
     DBuf<float> d_samples; size_t samples_total = 0; size_t hist_off = 0, hist_total = 0;
     DBuf<RankRec> d_myrec, d_allrec; HBuf<RankRec> h_allrec;
-    DBuf<l3d_match> d_send, d_recv, d_allf;
     cudaEvent_t ev_x[2] = {nullptr, nullptr};      // [0] exchange done on the main stream, [1] this group's records copied to the host
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [0] results on the host, [2..5] stage boundaries
     void release()
     {
         for (int k = 0; k < VG_MAX; ++k) slot[k].release();
         h_args.release(); d_args.release(); h_cams.release(); d_cams.release(); d_zero.release(); d_vres.release(); h_vres.release();
-        d_samples.release(); d_myrec.release(); d_allrec.release(); h_allrec.release(); d_send.release(); d_recv.release(); d_allf.release();
+        d_samples.release(); d_myrec.release(); d_allrec.release(); h_allrec.release();
         for (int k = 0; k < 2; ++k) if (ev_x[k]) { cudaEventDestroy(ev_x[k]); ev_x[k] = nullptr; }
         for (int k = 0; k < 6; ++k) if (ev[k]) { cudaEventDestroy(ev[k]); ev[k] = nullptr; }
     }
@@ -1865,7 +1875,7 @@ struct PhaseASet {
     DBuf<unsigned> d_cand, d_l1; DBuf<int> d_tile_sums, d_total;
     DBuf<int> d_stage_col, d_stage_row; DBuf<float4> d_stage_dep; DBuf<unsigned char> d_stage_ok;
     DBuf<JobDev> d_jobs; DBuf<int> d_pa_cnt, d_pa_off, d_pa_raw, d_pa_idx, d_pa_tot;
-    std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands, job_raw; std::vector<int> job_rowmax, job_raw_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
+    std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands, job_raw, job_raw_all /* summed over the ranks (several GPUs on one scene) */; std::vector<int> job_rowmax, job_raw_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
     DBuf<unsigned long long> d_job_sum64; HBuf<unsigned long long> h_job_sum64;
     bool pa_ms_pending = false;
     cudaEvent_t pa_ev[3] = {nullptr, nullptr, nullptr};
@@ -1891,6 +1901,11 @@ struct l3d_ctx {
     // several GPUs on one scene (l3d_comm_init)
     NcclApi* nccl = nullptr; ncclComm_t comm = nullptr; int rank = 0, world = 1, result_root = -1;
     bool copies_pending = false;
+    double host_s[4] = {0, 0, 0, 0};      // host seconds in enqueue_group / finish_group (waiting) / finish_group (rest) / number of groups (l3d_debug_host_times)
+    // the record windows (one per group in flight): every rank's is mapped into every process, the ranks store their
+    // output records straight into each other's
+    l3d_match* win[2] = {nullptr, nullptr}; size_t win_cap = 0; MrPeers peers[2];
+    DBuf<int> d_bar; DBuf<unsigned long long> d_tot; HBuf<unsigned long long> h_tot; DBuf<unsigned char> d_ipc; HBuf<unsigned char> h_ipc;
     uint64_t launches = 0;
     // views
     int V = 0;
@@ -2129,6 +2144,26 @@ bool same_neighbors(const std::vector<l3d_neighbor>& a, int n, const l3d_neighbo
 // real counts stay on the device); finish_group waits for the group's result records and fetches the views' output.
 struct GroupView { int view; int n_nb; const l3d_neighbor* nb; int first_job; size_t plan_index; };
 
+// Several GPUs on one scene: how many records the views of a group can put out at most, all ranks together (what the
+// record window has to hold) -- the same bound enqueue_group computes, without touching anything.
+size_t mr_group_need(l3d_ctx* ctx, const GroupView* gv, int count)
+{
+    PhaseASet& pa = ctx->pa[ctx->cur];
+    size_t need = 0;
+    for (int g = 0; g < count; ++g) {
+        int n_slots = 0;
+        for (int c = 0; c < gv[g].n_nb; ++c) {
+            const l3d_neighbor& n = gv[g].nb[c];
+            if (n.to_be_matched) { const size_t j = size_t(gv[g].first_job + n_slots++); if (j < pa.job_raw_all.size()) need += size_t(pa.job_raw_all[j]); }
+            else if (gv[g].view >= 0 && gv[g].view < ctx->V) {
+                const std::vector<Delivered>& dl = ctx->delivered[gv[g].view];
+                for (size_t k = 0; k < dl.size(); ++k) if (dl[k].from_view == n.view) { need += size_t(dl[k].count); break; }
+            }
+        }
+    }
+    return need;
+}
+
 int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, float sigma_p, float sigma_a)
 {
     cudaStream_t st = ctx->stream;
@@ -2162,7 +2197,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     int mx_src = 1, mx_cams = 1, mx_items = 1, mx_cta = 1; long mx_warps = 1; size_t mx_M = 0, mx_smem = 0;
     bool any_scored = false, any_window = false, any_quadratic = false, any_deliver = false;
     struct Z { size_t items, iters, best, hist, cursor, end, samples; } z[VG_MAX];
-    size_t hist_total = 0, samples_total = 0;
+    size_t hist_total = 0, samples_total = 0, window_need = 0;
     for (int g = 0; g < count; ++g) {
         const int view = gv[g].view, n_nb = gv[g].n_nb; const l3d_neighbor* nb = gv[g].nb; const int first_job = gv[g].first_job;
         ViewSlot& sl = gr.slot[g];
@@ -2175,7 +2210,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         job.view = view; job.nb.assign(nb, nb + n_nb); job.sigma_p = sigma_p; job.sigma_a = sigma_a;
         job.consumed.clear(); job.owner = -1;
         int n_slots = 0, n_deliver = 0, max_deliver_seg = 1;
-        uint64_t pair_tests = 0, cand_ub = 0, raw_ub = 0, delivered_ub = 0;
+        uint64_t pair_tests = 0, cand_ub = 0, raw_ub = 0, raw_ub_all = 0, delivered_ub = 0;      // raw_ub_all: over all ranks' rows
         size_t seg_ub = 0;                               // upper bound on the matches of one source segment
         std::vector<int> consumed;                       // indices into ctx->delivered[view]
         for (int c = 0; c < n_nb; ++c) {
@@ -2189,7 +2224,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
             if (n.to_be_matched) {
                 const int j = first_job + n_slots;
                 ct.mode = 0; ct.slot = n_slots++; ct.row_off = pa.jobs_host[j].row_off;
-                cand_ub += pa.job_cands[j]; raw_ub += pa.job_raw[j]; seg_ub += size_t(pa.job_raw_rowmax[j]);
+                cand_ub += pa.job_cands[j]; raw_ub += pa.job_raw[j]; raw_ub_all += pa.job_raw_all[j]; seg_ub += size_t(pa.job_raw_rowmax[j]);
                 pair_tests += uint64_t(n_src) * uint64_t(tv.n_segments);
             } else {
                 ct.mode = 2;
@@ -2206,6 +2241,8 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         }
         job.pair_tests = pair_tests; job.cand_ub = cand_ub;
         const size_t M_ub = size_t(raw_ub + delivered_ub);          // upper bound on the number of matches to score
+        const size_t F_ub_all = size_t(raw_ub_all + delivered_ub);  // ... and on the output records of the view from all ranks together
+        window_need += F_ub_all;
         const bool scored = n_slots > 0;                             // cudawrapper.cu:877-878
         const bool delivering = n_deliver > 0 && scored;
         const int stride = max_deliver_seg + 1;                      // one spare key per slot keeps t_start[n_seg] addressable
@@ -2239,10 +2276,9 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         if (delivering) {
             buf.refs = n_deliver;
             L3D_CUDA(ctx->pool.get(sizeof(int) * (size_t(n_keys) + 2), reinterpret_cast<void**>(&buf.start)));
-            if (!mr) {          // (several GPUs on one scene: sized in finish_group, when all ranks' counts are known)
-                L3D_CUDA(ctx->pool.get(sizeof(int) * std::max<size_t>(M_ub, 1), reinterpret_cast<void**>(&buf.tgt)));
-                L3D_CUDA(ctx->pool.get(sizeof(float4) * std::max<size_t>(M_ub, 1), reinterpret_cast<void**>(&buf.dep)));
-            }
+            // (several GPUs on one scene: every rank holds the complete hand-over lists, all ranks' records)
+            L3D_CUDA(ctx->pool.get(sizeof(int) * std::max<size_t>(mr ? F_ub_all : M_ub, 1), reinterpret_cast<void**>(&buf.tgt)));
+            L3D_CUDA(ctx->pool.get(sizeof(float4) * std::max<size_t>(mr ? F_ub_all : M_ub, 1), reinterpret_cast<void**>(&buf.dep)));
         }
         job.M_ub = M_ub; job.scored = scored; job.delivering = delivering; job.n_deliver = n_deliver;
         // kernel arguments (pointers into the zero buffer are filled in below, when it has its size)
@@ -2270,10 +2306,10 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
             for (int c = 0; c < n_nb; ++c) {
                 const int d = hc[c].deliver;
                 if (d < 0) continue;
-                const uint64_t ub = std::min<uint64_t>(hc[c].slot >= 0 ? pa.job_raw[first_job + hc[c].slot] : uint64_t(M_ub), 0x7fffffffull);
+                const uint64_t ub = std::min<uint64_t>(hc[c].slot >= 0 ? pa.job_raw_all[first_job + hc[c].slot] : uint64_t(mr ? F_ub_all : M_ub), 0x7fffffffull);
                 Delivered dl; dl.from_view = view; dl.owner = job.owner; dl.slot = d;
                 dl.count = int(ub); dl.max_group = int(std::min<uint64_t>(ub, uint64_t(n_src)));      // a source segment matches a target segment once
-                if (mr) { dl.count = 0; dl.max_group = n_full; }                                       // (exact count: finish_group)
+                if (mr) dl.max_group = int(std::min<uint64_t>(ub, uint64_t(n_full)));
                 dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
                 buf.counts[d] = dl.count; buf.maxg[d] = dl.max_group;
                 ctx->delivered[nb[c].view].push_back(dl);
@@ -2354,7 +2390,21 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         L3D_CUDA(cudaMemcpyAsync(gr.h_vres.p, gr.d_vres.p, sizeof(int) * size_t(count) * res_stride, cudaMemcpyDeviceToHost, st));
         L3D_CUDA(cudaMemcpyAsync(gr.h_allrec.p, gr.d_allrec.p, sizeof(RankRec) * VG_MAX * size_t(ctx->world), cudaMemcpyDeviceToHost, st));
         L3D_CUDA(cudaEventRecord(gr.ev[0], st));
-        return 0;               // the records themselves are exchanged in finish_group, when the host knows how many there are
+        // The records themselves: every rank stores its own into all ranks' windows, at the places the gathered counts
+        // assign; a one-word all-reduce tells that everybody's stores have landed; then the hand-over lists are built.
+        if (window_need > ctx->win_cap) { ctx->err = "l3d_match_view: internal error (record window too small)"; return 1; }
+        const int q = int(&gr - ctx->grp);
+        const unsigned pb = unsigned(std::min<size_t>(std::max<size_t>((2 * mx_M + 255) / 256, 1), size_t(4 * ctx->n_sm)));
+        L3D_CUDA(pdl_launch(k_mr_push, dim3(pb, G, unsigned(ctx->world)), dim3(256), 0, st, A, (const RankRec*)gr.d_allrec.p, ctx->peers[q], ctx->rank, ctx->world));
+        L3D_NCCL(ctx->nccl->AllReduce(ctx->d_bar.p, ctx->d_bar.p, 1, ncclInt, ncclSum, ctx->comm, st));
+        ctx->launches += 1;
+        if (any_deliver) {
+            L3D_CUDA(pdl_launch(k_mr_deliver_scatter, dim3(unsigned(std::min<size_t>(size_t(ctx->world) * pb, size_t(8 * ctx->n_sm))), G), dim3(256), 0, st, A, (const l3d_match*)ctx->win[q], (const RankRec*)gr.d_allrec.p, ctx->world));
+            ctx->launches += 1;
+        }
+        L3D_CUDA(cudaGetLastError());
+        L3D_CUDA(cudaEventRecord(gr.ev_x[0], st));
+        return 0;
     }
     if (any_deliver) {
         L3D_CUDA(pdl_launch(k_scan_views, dim3(1, G), dim3(SCAN_T), 0, st, A, 1));
@@ -2394,54 +2444,76 @@ int arena_take(l3d_ctx* ctx, size_t n, l3d_match** out)
     return 0;
 }
 
-// Several GPUs on one scene: the second half of a group's exchange, once the host knows every rank's record counts.
-// All ranks' output records of the group's views are gathered (packed: one all-gather of the largest rank's size),
-// laid out view by view, and the hand-over lists are built from them -- on every rank, so that each has the complete
-// lists for its rows of the later views.
-int mr_exchange(l3d_ctx* ctx, ViewGroup& gr, MrLayout& lay)
+// Several GPUs on one scene: the record windows.  Every rank allocates two (one per group in flight), exports them
+// (CUDA IPC) and maps every other rank's; k_mr_push then stores a group's records into all of them.  Called by all
+// ranks at the same point with the same size, with no group in flight.
+int mr_ensure_window(l3d_ctx* ctx, size_t need)
 {
+    if (need <= ctx->win_cap) return 0;
     cudaStream_t st = ctx->stream;
-    const int W = ctx->world, G = gr.count;
-    const RankRec* rec = gr.h_allrec.p;                 // [rank][VG_MAX]
-    memset(&lay, 0, sizeof lay);
-    long long padded = 0, total = 0; int max_cnt = 0;
-    for (int r = 0; r < W; ++r) {
-        long long t = 0;
-        for (int v = 0; v < G; ++v) { lay.src_off[r][v] = int(t); lay.cnt[r][v] = rec[size_t(r) * VG_MAX + v].F; t += lay.cnt[r][v]; max_cnt = std::max(max_cnt, lay.cnt[r][v]); }
-        padded = std::max(padded, t);
+    const int W = ctx->world;
+    L3D_CUDA(ctx->d_bar.ensure(4)); L3D_CUDA(ctx->d_ipc.ensure(size_t(2) * sizeof(cudaIpcMemHandle_t) * W)); L3D_CUDA(ctx->h_ipc.ensure(size_t(2) * sizeof(cudaIpcMemHandle_t) * W));
+    L3D_CUDA(cudaStreamSynchronize(st));
+    for (int q = 0; q < 2; ++q)
+        for (int r = 0; r < W; ++r) { if (r != ctx->rank && ctx->peers[q].base[r]) cudaIpcCloseMemHandle(ctx->peers[q].base[r]); ctx->peers[q].base[r] = nullptr; }
+    // nobody frees a window that another rank still has mapped
+    L3D_CUDA(cudaMemsetAsync(ctx->d_bar.p, 0, sizeof(int), st));
+    L3D_NCCL(ctx->nccl->AllReduce(ctx->d_bar.p, ctx->d_bar.p, 1, ncclInt, ncclSum, ctx->comm, st));
+    L3D_CUDA(cudaStreamSynchronize(st));
+    const size_t cap = std::max<size_t>(need + need / 4, size_t(1) << 21);       // at least 64 MiB
+    cudaIpcMemHandle_t mine[2];
+    for (int q = 0; q < 2; ++q) {
+        if (ctx->win[q]) cudaFree(ctx->win[q]);
+        ctx->win[q] = nullptr;
+        L3D_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->win[q]), cap * sizeof(l3d_match)));
+        L3D_CUDA(cudaIpcGetMemHandle(&mine[q], ctx->win[q]));
     }
-    for (int v = 0; v < G; ++v) {
-        lay.view_off[v] = int(total);
-        for (int r = 0; r < W; ++r) { lay.dst_off[r][v] = int(total); total += lay.cnt[r][v]; }
-        lay.view_cnt[v] = int(total - lay.view_off[v]);
-    }
-    if (total > 0x7fffffffll || padded * W > 0x7fffffffll) { ctx->err = "l3d_match_view: too many output records in one group of views"; return 1; }
-    lay.padded = int(padded);
-    bool any_deliver = false;
-    for (int g = 0; g < G; ++g) {                       // the hand-over record buffers, now that their sizes are known
-        ViewJob& job = gr.slot[g].job;
-        if (!job.delivering) continue;
-        any_deliver = true;
-        DeliverBuf& b = ctx->deliver_bufs[job.owner];
-        const size_t n = size_t(std::max(lay.view_cnt[g], 1));
-        L3D_CUDA(ctx->pool.get(sizeof(int) * n, reinterpret_cast<void**>(&b.tgt)));
-        L3D_CUDA(ctx->pool.get(sizeof(float4) * n, reinterpret_cast<void**>(&b.dep)));
-        lay.dl_tgt[g] = b.tgt; lay.dl_dep[g] = b.dep;
-        for (size_t c = 0; c < job.nb.size(); ++c) {
-            if (!job.nb[c].deliver) continue;
-            std::vector<Delivered>& dl = ctx->delivered[job.nb[c].view];
-            for (size_t k = 0; k < dl.size(); ++k) if (dl[k].owner == job.owner) { dl[k].t_tgt = b.tgt; dl[k].t_dep = b.dep; }
+    ctx->win_cap = 0;
+    unsigned char* d_send = ctx->d_ipc.p; unsigned char* d_recv = ctx->d_ipc.p;      // in place: each rank's part at its own offset
+    L3D_CUDA(cudaMemcpyAsync(d_send + size_t(ctx->rank) * sizeof mine, mine, sizeof mine, cudaMemcpyHostToDevice, st));
+    L3D_NCCL(ctx->nccl->AllGather(d_send + size_t(ctx->rank) * sizeof mine, d_recv, sizeof mine, ncclChar, ctx->comm, st));
+    L3D_CUDA(cudaMemcpyAsync(ctx->h_ipc.p, d_recv, sizeof mine * size_t(W), cudaMemcpyDeviceToHost, st));
+    L3D_CUDA(cudaStreamSynchronize(st));
+    for (int r = 0; r < W; ++r)
+        for (int q = 0; q < 2; ++q) {
+            if (r == ctx->rank) { ctx->peers[q].base[r] = ctx->win[q]; continue; }
+            cudaIpcMemHandle_t h; memcpy(&h, ctx->h_ipc.p + (size_t(r) * 2 + q) * sizeof h, sizeof h);
+            void* ptr = nullptr;
+            L3D_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+            ctx->peers[q].base[r] = static_cast<l3d_match*>(ptr);
         }
+    ctx->win_cap = cap;
+    return 0;
+}
+
+void mr_release_window(l3d_ctx* ctx)
+{
+    for (int q = 0; q < 2; ++q) {
+        for (int r = 0; r < MR_MAX_RANKS; ++r) { if (r != ctx->rank && ctx->peers[q].base[r]) cudaIpcCloseMemHandle(ctx->peers[q].base[r]); ctx->peers[q].base[r] = nullptr; }
     }
-    if (total == 0) return 0;                           // (every rank sees the same counts and skips the same calls)
-    L3D_CUDA(gr.d_send.ensure(size_t(padded))); L3D_CUDA(gr.d_recv.ensure(size_t(padded) * W)); L3D_CUDA(gr.d_allf.ensure(size_t(total)));
-    const unsigned blocks = unsigned(std::min(std::max((2 * max_cnt + 255) / 256, 1), 4 * ctx->n_sm));
-    k_mr_pack<<<dim3(blocks, G), 256, 0, st>>>(gr.d_args.p, gr.d_myrec.p, gr.d_send.p);
-    L3D_NCCL(ctx->nccl->AllGather(gr.d_send.p, gr.d_recv.p, size_t(padded) * sizeof(l3d_match), ncclChar, ctx->comm, st));
-    k_mr_unpack<<<dim3(blocks, G, W), 256, 0, st>>>(gr.d_recv.p, gr.d_allf.p, lay);
-    ctx->launches += 2;
-    if (any_deliver) { k_mr_deliver_scatter<<<dim3(std::min(4u * blocks, unsigned(8 * ctx->n_sm)), G), 256, 0, st>>>(gr.d_args.p, gr.d_allf.p, lay); ctx->launches += 1; }
-    L3D_CUDA(cudaGetLastError());
+    if (ctx->comm && ctx->d_bar.p) {        // nobody frees a window that another rank still has mapped
+        cudaMemsetAsync(ctx->d_bar.p, 0, sizeof(int), ctx->stream);
+        ctx->nccl->AllReduce(ctx->d_bar.p, ctx->d_bar.p, 1, ncclInt, ncclSum, ctx->comm, ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
+    }
+    for (int q = 0; q < 2; ++q) { if (ctx->win[q]) cudaFree(ctx->win[q]); ctx->win[q] = nullptr; }
+    ctx->win_cap = 0;
+}
+
+// Raw matches per job summed over the ranks: the bounds every rank sizes the views' buffers with must cover what the
+// other ranks may hand over.  One small all-reduce per batch of pair tests, on the main stream.
+int mr_job_totals(l3d_ctx* ctx, PhaseASet& pa)
+{
+    const size_t n = pa.job_raw.size();
+    pa.job_raw_all = pa.job_raw;
+    if (ctx->world <= 1 || n == 0) return 0;
+    L3D_CUDA(ctx->d_tot.ensure(n)); L3D_CUDA(ctx->h_tot.ensure(n));
+    for (size_t j = 0; j < n; ++j) ctx->h_tot.p[j] = pa.job_raw[j];
+    L3D_CUDA(cudaMemcpyAsync(ctx->d_tot.p, ctx->h_tot.p, sizeof(unsigned long long) * n, cudaMemcpyHostToDevice, ctx->stream));
+    L3D_NCCL(ctx->nccl->AllReduce(ctx->d_tot.p, ctx->d_tot.p, n, ncclUint64, ncclSum, ctx->comm, ctx->stream));
+    L3D_CUDA(cudaMemcpyAsync(ctx->h_tot.p, ctx->d_tot.p, sizeof(unsigned long long) * n, cudaMemcpyDeviceToHost, ctx->stream));
+    L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (size_t j = 0; j < n; ++j) pa.job_raw_all[j] = ctx->h_tot.p[j];
     return 0;
 }
 
@@ -2449,7 +2521,11 @@ int mr_exchange(l3d_ctx* ctx, ViewGroup& gr, MrLayout& lay)
 // matched outside a schedule) and fetches the output records of all its views with one synchronise.
 int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* single)
 {
+    const auto t_in = std::chrono::steady_clock::now();
     L3D_CUDA(cudaEventSynchronize(gr.ev[0]));
+    const auto t_waited = std::chrono::steady_clock::now();
+    ctx->host_s[1] += std::chrono::duration<double>(t_waited - t_in).count();
+    struct Tail { l3d_ctx* c; std::chrono::steady_clock::time_point t; ~Tail() { c->host_s[2] += std::chrono::duration<double>(std::chrono::steady_clock::now() - t).count(); } } tail = {ctx, t_waited};
     PhaseASet& pa = ctx->pa[ctx->cur];
     float ms_a[2] = {0.f, 0.f};
     if (pa.pa_ms_pending) {                            // phase A of a whole batch is booked on the first view collected after it
@@ -2461,10 +2537,15 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
     float ms_b[3] = {0.f, 0.f, 0.f};
     if (ctx->stage_events) for (int k = 0; k < 3; ++k) cudaEventElapsedTime(&ms_b[k], gr.ev[k + 2], gr.ev[k + 3]);
     const bool mr = ctx->world > 1;
-    MrLayout lay;
+    int view_off[VG_MAX], view_cnt[VG_MAX];              // several GPUs: where each view's records are in this group's window
     if (mr) {
-        if (mr_exchange(ctx, gr, lay)) return 1;
-        L3D_CUDA(cudaEventRecord(gr.ev_x[0], ctx->stream));
+        long long total = 0;
+        for (int v = 0; v < gr.count; ++v) {
+            view_off[v] = int(total);
+            for (int r = 0; r < ctx->world; ++r) total += gr.h_allrec.p[size_t(r) * VG_MAX + v].F;
+            view_cnt[v] = int(total - view_off[v]);
+        }
+        if (size_t(total) > ctx->win_cap) { ctx->err = "l3d_match_view: internal error (record window overrun)"; return 1; }
         copy_back = copy_back && (ctx->result_root < 0 || ctx->result_root == ctx->rank);      // who gets the records on the host
         if (copy_back) L3D_CUDA(cudaStreamWaitEvent(ctx->copy_stream, gr.ev_x[0], 0));
     }
@@ -2482,7 +2563,7 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
         if (mr) {                                          // the view as a whole: all ranks' rows
             unsigned long long all = 0ull, same = 0ull; long long m = 0;
             for (int r = 0; r < ctx->world; ++r) { const RankRec& rr = gr.h_allrec.p[size_t(r) * VG_MAX + g]; m += rr.M; all += rr.iters_all; same += rr.iters_same; }
-            M = int(m); F = lay.view_cnt[g];
+            M = int(m); F = view_cnt[g];
             if (job.scored && M > 0) { memcpy(&median, &hr[2], sizeof(float)); res->score_iters = all; res->score_iters_other_cam = all - same; }
         } else if (job.scored && M > 0) {
             memcpy(&median, &hr[2], sizeof(float));
@@ -2516,7 +2597,7 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
         if (copy_back && F > 0) {                          // on its own stream: the next group is already running
             if (ctx->retain || !single) { if (arena_take(ctx, size_t(F), &dst)) return 1; }      // results of a schedule are collected ahead of their calls
             else { L3D_CUDA(ctx->h_filtered.ensure(size_t(F))); dst = ctx->h_filtered.p; }
-            const l3d_match* from = mr ? gr.d_allf.p + lay.view_off[g] : sl.d_filtered.p;
+            const l3d_match* from = mr ? ctx->win[int(&gr - ctx->grp)] + view_off[g] : sl.d_filtered.p;
             L3D_CUDA(cudaMemcpyAsync(dst, from, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, ctx->copy_stream));
             copies = true;
         }
@@ -2625,13 +2706,13 @@ int top_up(l3d_ctx* ctx)
             have = true;
         }
         PhaseASet& set = ctx->pa[ctx->cur];
+        if (mr_job_totals(ctx, set)) return 1;
         ctx->batch_begin = set.begin; ctx->batch_end = set.end;
         ctx->launches += set.launches; set.launches = 0;
-        if (ctx->batch_end < ctx->order.size()) start_worker(ctx, ctx->batch_end);      // the following batch, meanwhile
+        if (ctx->batch_end < ctx->order.size() && !ctx->stage_events) start_worker(ctx, ctx->batch_end);      // the following batch, meanwhile (not when stages are timed: nothing may run beside anything)
     }
     // the next groups: consecutive views of one dependency level, two groups in flight
-    // (several GPUs on one scene: one, because a group's hand-over needs the ranks' counts on the host first)
-    while (ctx->fly_end < ctx->batch_end && ctx->grp_end - ctx->grp_begin < size_t(ctx->world > 1 ? 1 : 2)) {
+    while (ctx->fly_end < ctx->batch_end && ctx->grp_end - ctx->grp_begin < 2) {
         GroupView gv[VG_MAX]; int count = 0;
         const int lvl = ctx->level[ctx->order[ctx->fly_end]];
         while (count < VG_MAX && ctx->fly_end + size_t(count) < ctx->batch_end && ctx->level[ctx->order[ctx->fly_end + size_t(count)]] == lvl) {
@@ -2641,7 +2722,18 @@ int top_up(l3d_ctx* ctx)
         }
         ViewGroup& gr = ctx->grp[ctx->grp_end % 2];
         gr.pos0 = ctx->fly_end;
+        if (ctx->world > 1) {
+            // the record windows must hold this group; growing them is a collective step with nothing in flight
+            // (every rank computes the same bound at the same point of the same schedule)
+            const size_t need = mr_group_need(ctx, gv, count);
+            if (need > ctx->win_cap) {
+                if (ctx->grp_begin < ctx->grp_end) return 0;          // collect what is in flight first; the caller's loop comes back
+                if (mr_ensure_window(ctx, need)) return 1;
+            }
+        }
+        const auto t0 = std::chrono::steady_clock::now();
         if (enqueue_group(ctx, gr, gv, count, ctx->run_sigma_p, ctx->run_sigma_a)) return 1;
+        ctx->host_s[0] += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); ctx->host_s[3] += 1.0;
         ctx->fly_end += size_t(count); ++ctx->grp_end;
     }
     return 0;
@@ -2687,8 +2779,10 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         if (nb[c].to_be_matched) { JobHost j; j.src_view = view; j.tgt_view = nb[c].view; memcpy(j.F, nb[c].F, sizeof j.F); jh.push_back(j); }
     PhaseASet& set = ctx->pa[ctx->cur];
     if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
+    if (mr_job_totals(ctx, set)) return 1;
     ctx->launches += set.launches; set.launches = 0;
     GroupView one = {view, n_nb, nb, 0, 0};
+    if (ctx->world > 1 && mr_ensure_window(ctx, mr_group_need(ctx, &one, 1))) return 1;
     if (enqueue_group(ctx, ctx->grp[0], &one, 1, sigma_p, sigma_a)) return 1;
     if (finish_group(ctx, ctx->grp[0], copy_back, res)) return 1;
     if (ctx->copies_pending) { L3D_CUDA(cudaStreamSynchronize(ctx->copy_stream)); ctx->copies_pending = false; }
@@ -2785,6 +2879,7 @@ int l3d_comm_destroy(l3d_ctx* ctx)
         cudaSetDevice(ctx->device);
         drain_pending(ctx);
         cudaStreamSynchronize(ctx->stream);
+        mr_release_window(ctx);
         ctx->nccl->CommDestroy(ctx->comm);
         ctx->comm = nullptr;
     }
@@ -3031,6 +3126,13 @@ int l3d_debug_set_candidate_limit(l3d_ctx* ctx, uint64_t limit)
 {
     if (!ctx) return 1;
     ctx->cand_limit = (limit == 0 || limit > 0x7fff0000ull) ? 0x7fff0000ull : limit;
+    return 0;
+}
+
+int l3d_debug_host_times(l3d_ctx* ctx, double out[4])
+{
+    if (!ctx || !out) return 1;
+    for (int k = 0; k < 4; ++k) { out[k] = ctx->host_s[k]; ctx->host_s[k] = 0.0; }
     return 0;
 }
 

@@ -520,6 +520,10 @@ struct Line3D::Impl
         }
         { float span = 0.f; if (l3d_mark(ctx, 1) || l3d_marks_elapsed(ctx, &span)) fail("l3d_mark"); stats.t_matching_device += double(span) * 1e-3; }   // CUDA events around the whole loop
         stats.t_matching += now_s() - t_match0;
+        if (getenv("L3D_PROFILE")) {
+            double hs[4]; l3d_debug_host_times(ctx, hs);
+            std::cerr << "[prof] matching " << (now_s() - t_match0) * 1e3 << " ms: host enqueue " << hs[0] * 1e3 << " ms, waiting " << hs[1] * 1e3 << " ms, collecting " << hs[2] * 1e3 << " ms, " << hs[3] << " groups" << std::endl;
+        }
     }
 
     // view.cc:162-224 (a view takes in its matches: best match per segment) and the potential-correspondence
