@@ -470,7 +470,7 @@ __device__ __forceinline__ unsigned pretest_level1(f32x2 QX, f32x2 QY, f32x2 nW,
 
 template <int UNROLL, int MINB>
 __global__ void __launch_bounds__(P1_BLOCK, MINB) k_pretest(const SrcHoist1* __restrict__ sh, const TgtHoist* __restrict__ th,
-                                                            const JobDev* __restrict__ jobs, int n_jobs, unsigned* __restrict__ l1)
+                                                            const JobDev* __restrict__ jobs, int n_jobs, unsigned* __restrict__ l1, int rows_per_block)
 {
     __shared__ float4 s_a[P1_CHUNK], s_b[P1_CHUNK];
     __shared__ int s_job;
@@ -484,7 +484,7 @@ __global__ void __launch_bounds__(P1_BLOCK, MINB) k_pretest(const SrcHoist1* __r
     const int local = blockIdx.x - jb.l1_blk_off;
     const int col_blocks = (jb.n_tgt + P1_COLS - 1) / P1_COLS;
     const int rb = local / col_blocks, cb = local - rb * col_blocks;
-    const int row_begin = rb * P1_ROWS, row_end = min(jb.n_src, row_begin + P1_ROWS);
+    const int row_begin = rb * rows_per_block, row_end = min(jb.n_src, row_begin + rows_per_block);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c0 = cb * P1_COLS + warp * 64 + lane, c1 = c0 + 32;
     f32x2 QX0 = 0, QY0 = 0, NT0 = 0, QX1 = 0, QY1 = 0, NT1 = 0;
@@ -1224,7 +1224,7 @@ __device__ __forceinline__ void b_finish_view(float* __restrict__ dsamples, int 
                                                       int* __restrict__ out, bool samples_ready)
 {
     // depth samples: both depths of every segment's best match if its score exceeds 0.5 (cudawrapper.cu:1090-1110)
-    // (with several GPUs on one scene they were written by k_mr_prepare and combined over the ranks already)
+    // (with several GPUs on one scene every rank's k_mr_push has written them into this rank's window already)
     for (int row = threadIdx.x; !samples_ready && 2 * row < n_samples; row += MS_T) {
         const unsigned long long key = best[row];
         float a = INFINITY, b = INFINITY;
@@ -1338,8 +1338,13 @@ struct VArgs {
 // What one rank reports about one view of a group (all-gathered): its output records, its matches, its iteration counts.
 struct RankRec { int F, M; unsigned long long iters_all, iters_same; int pad[2]; };
 constexpr int MR_MAX_RANKS = 16;
-// The group's record window of every rank, as mapped into this process (CUDA IPC): [rank] -> base of that rank's window
-struct MrPeers { l3d_match* base[MR_MAX_RANKS]; };
+// The group's window of every rank, as mapped into this process (CUDA IPC): [rank] -> base of that rank's window.
+// A window holds, for one group of views: the ranks' records of each view (RankRec[rank][8]), the depth samples of
+// every segment of each view, and the output records of each view -- one region per rank, sized by the bound all ranks
+// share, so that a rank knows where its records go in everybody's window without knowing the other ranks' counts.
+struct MrPeers { unsigned char* base[MR_MAX_RANKS]; };
+struct MrLayout { long long samp_off[8], rec_off[8], cap[8]; };      // per view of the group: bytes, bytes, records per rank
+constexpr size_t MR_COUNTS_BYTES = size_t(MR_MAX_RANKS) * 8 * 32;      // the RankRec table at the start of a window
 #define L3D_VIEW(dim) L3D_PDL_PROLOGUE(); const VArgs& va = all[blockIdx.dim]
 
 __global__ void k_gather_counts(const VArgs* __restrict__ all)
@@ -1396,7 +1401,7 @@ __global__ void __launch_bounds__(RM_T) k_filter_compact(const VArgs* __restrict
 {
     L3D_VIEW(y);
     if (int(blockIdx.x) >= va.n_cta) return;
-    if (va.scored) b_filter_compact(va.off + va.n_src * va.n_cams, va.score, va.mids, va.mdep, va.cta_kept, va.filtered, va.Fout, va.cams, va.stride, va.delivering ? va.hist : nullptr, va.n_cta);
+    if (va.scored) b_filter_compact(va.off + va.n_src * va.n_cams, va.score, va.mids, va.mdep, va.cta_kept, va.filtered, va.Fout, va.cams, va.stride, (va.delivering && !va.mr) ? va.hist : nullptr, va.n_cta);
     else {          // no neighbour was pair-tested (cudawrapper.cu:877-878): all records, unscored; RM_T / 256 chunks of 256 per block
         b_copy_unscored_at(va.mids, va.mdep, va.off + va.n_src * va.n_cams, va.filtered, blockIdx.x * RM_T + threadIdx.x);
     }
@@ -1420,82 +1425,96 @@ __global__ void __launch_bounds__(MS_T) k_finish_view(const VArgs* __restrict__ 
 // s belongs to rank s mod ranks), so each rank pair-tests, assembles and scores its rows of every view, and the views
 // are still processed level by level.  What a later view needs from an earlier one -- the reversed records, grouped by
 // ITS segments -- is put together from all ranks' output records of the group:
-//   k_mr_prepare   depth samples of all segments (infinity for other ranks' rows) and this rank's record of each view
-//   NCCL           all-gather of the records, min-all-reduce of the samples, sum-all-reduce of the hand-over group sizes
-//   k_mr_push      this rank's output records of the group's views, stored straight into EVERY rank's record window
-//                  (peer memory over NVLink) at the place the gathered counts assign to them: view by view, rank by rank
+//   k_mr_push      after the view's records have been filtered: this rank's output records, its depth samples (the
+//                  segments it owns) and its record of each view, stored straight into EVERY rank's window (peer memory
+//                  over NVLink); the regions are fixed by bounds all ranks share, so nothing has to be known of the others
 //   NCCL           a one-word all-reduce: every rank's stores have landed
-//   k_mr_deliver_scatter   as k_deliver_scatter, over all ranks' records in the window
+//   k_mr_hist, k_scan_views, k_mr_deliver_scatter   the hand-over lists, from all ranks' records in the own window
+//   k_finish_view  the median, from all ranks' samples in the own window
 // The host is not in this loop: it reads the counts when it collects the group, with the next group already running.
 // ------------------------------------------------------------------------------------------
-__global__ void k_mr_prepare(const VArgs* __restrict__ all, RankRec* __restrict__ rec)
+__global__ void k_mr_push(const VArgs* __restrict__ all, MrLayout lay, MrPeers peers, int rank)
 {
-    L3D_VIEW(y);
+    L3D_PDL_PROLOGUE();
+    const int v = blockIdx.y;
+    const VArgs& va = all[v];
+    unsigned char* base = peers.base[blockIdx.z];
     const int* Mptr = va.off + va.n_src * va.n_cams;
+    const int F = va.scored ? *va.Fout : *Mptr;
+    // the records
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(va.filtered);
+        uint4* dst = reinterpret_cast<uint4*>(base + lay.rec_off[v]) + size_t(2) * size_t(rank) * size_t(lay.cap[v]);
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * F; i += gridDim.x * blockDim.x) dst[i] = src[i];
+    }
+    // depth samples of the segments this rank owns: both depths of the segment's best match if its score exceeds 0.5,
+    // infinity otherwise (cudawrapper.cu:1090-1110); every segment is written by exactly one rank
     if (va.scored) {
-        for (int sg = blockIdx.x * blockDim.x + threadIdx.x; sg < va.n_seg_full; sg += gridDim.x * blockDim.x) {
-            float a = INFINITY, b = INFINITY;
-            const int d = sg - va.src.row_first;
-            if (d >= 0 && d % va.src.row_stride == 0) {
-                const unsigned long long key = va.best[d / va.src.row_stride];
-                if (__uint_as_float(unsigned(key >> 32)) > 0.5f) { const float4 dp = va.mdep[0xffffffffu - unsigned(key & 0xffffffffull)]; a = dp.x; b = dp.y; }
-            }
-            va.dsamples[2 * sg] = a; va.dsamples[2 * sg + 1] = b;
+        float2* smp = reinterpret_cast<float2*>(base + lay.samp_off[v]);
+        for (int row = blockIdx.x * blockDim.x + threadIdx.x; row < va.n_src; row += gridDim.x * blockDim.x) {
+            const unsigned long long key = va.best[row];
+            float2 ab = make_float2(INFINITY, INFINITY);
+            if (__uint_as_float(unsigned(key >> 32)) > 0.5f) { const float4 dp = va.mdep[0xffffffffu - unsigned(key & 0xffffffffull)]; ab = make_float2(dp.x, dp.y); }
+            smp[row_segment(va.src, row)] = ab;
         }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        RankRec r; r.M = *Mptr; r.F = va.scored ? *va.Fout : *Mptr;
+        RankRec r; r.M = *Mptr; r.F = F;
         r.iters_all = va.scored ? va.iters[0] : 0ull; r.iters_same = va.scored ? va.iters[1] : 0ull; r.pad[0] = r.pad[1] = 0;
-        rec[blockIdx.y] = r;
+        reinterpret_cast<RankRec*>(base)[rank * 8 + v] = r;
     }
 }
-// records of view v of the group start at mr_view_offset(v) in a window; inside a view the ranks follow each other
-__device__ __forceinline__ int mr_view_offset(const RankRec* __restrict__ allrec, int W, int v)
-{
-    int off = 0;
-    for (int vv = 0; vv < v; ++vv) for (int r = 0; r < W; ++r) off += allrec[r * 8 + vv].F;
-    return off;
-}
-__global__ void k_mr_push(const VArgs* __restrict__ all, const RankRec* __restrict__ allrec, MrPeers peers, int rank, int W)
+// sizes of the hand-over groups, from all ranks' records of the view
+__global__ void k_mr_hist(const VArgs* __restrict__ all, const unsigned char* __restrict__ window, MrLayout lay, int W)
 {
     L3D_PDL_PROLOGUE();
-    __shared__ int s_off;
     const int v = blockIdx.y;
     const VArgs& va = all[v];
-    if (threadIdx.x == 0) {
-        int off = mr_view_offset(allrec, W, v);
-        for (int r = 0; r < rank; ++r) off += allrec[r * 8 + v].F;
-        s_off = off;
+    if (!va.delivering) return;
+    const RankRec* rec = reinterpret_cast<const RankRec*>(window);
+    for (int r = 0; r < W; ++r) {
+        const int n = rec[r * 8 + v].F;
+        const l3d_match* f = reinterpret_cast<const l3d_match*>(window + lay.rec_off[v]) + size_t(r) * size_t(lay.cap[v]);
+        for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+            const int d = va.cams[f[k].cam].deliver;
+            if (d >= 0) atomicAdd(&va.hist[d * va.stride + f[k].tgt_seg], 1);
+        }
     }
-    __syncthreads();
-    const int n = allrec[rank * 8 + v].F;
-    const uint4* src = reinterpret_cast<const uint4*>(va.filtered);
-    uint4* dst = reinterpret_cast<uint4*>(peers.base[blockIdx.z] + s_off);
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * n; i += gridDim.x * blockDim.x) dst[i] = src[i];
 }
-__global__ void k_mr_deliver_scatter(const VArgs* __restrict__ all, const l3d_match* __restrict__ window, const RankRec* __restrict__ allrec, int W)
+__global__ void k_mr_deliver_scatter(const VArgs* __restrict__ all, const unsigned char* __restrict__ window, MrLayout lay, int W)
 {
     L3D_PDL_PROLOGUE();
-    __shared__ int s_off, s_n;
-    const VArgs& va = all[blockIdx.y];
+    const int v = blockIdx.y;
+    const VArgs& va = all[v];
     if (!va.delivering) return;
-    if (threadIdx.x == 0) {
-        s_off = mr_view_offset(allrec, W, blockIdx.y);
-        int n = 0;
-        for (int r = 0; r < W; ++r) n += allrec[r * 8 + blockIdx.y].F;
-        s_n = n;
+    const RankRec* rec = reinterpret_cast<const RankRec*>(window);
+    for (int r = 0; r < W; ++r) {
+        const int n = rec[r * 8 + v].F;
+        const l3d_match* f = reinterpret_cast<const l3d_match*>(window + lay.rec_off[v]) + size_t(r) * size_t(lay.cap[v]);
+        for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+            const l3d_match m = f[k];
+            const int d = va.cams[m.cam].deliver;
+            if (d < 0) continue;
+            const int key = d * va.stride + m.tgt_seg;
+            const int pos = va.dl_start[key] + atomicAdd(&va.cursor[key], 1);
+            va.dl_tgt[pos] = m.src_seg;
+            va.dl_dep[pos] = make_float4(m.depths[2], m.depths[3], m.depths[0], m.depths[1]);     // line3D.cc:852-855
+        }
     }
-    __syncthreads();
-    const int n = s_n;
-    const l3d_match* f = window + s_off;
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
-        const l3d_match m = f[k];
-        const int d = va.cams[m.cam].deliver;
-        if (d < 0) continue;
-        const int key = d * va.stride + m.tgt_seg;
-        const int pos = va.dl_start[key] + atomicAdd(&va.cursor[key], 1);
-        va.dl_tgt[pos] = m.src_seg;
-        va.dl_dep[pos] = make_float4(m.depths[2], m.depths[3], m.depths[0], m.depths[1]);     // line3D.cc:852-855
+}
+// the ranks' records of one group, view by view and rank by rank, into one contiguous buffer (for the copy to the host)
+__global__ void k_mr_gather(const unsigned char* __restrict__ window, MrLayout lay, int W, l3d_match* __restrict__ out)
+{
+    const int v = blockIdx.y;
+    const RankRec* rec = reinterpret_cast<const RankRec*>(window);
+    long long off = 0;
+    for (int vv = 0; vv < v; ++vv) for (int r = 0; r < W; ++r) off += rec[r * 8 + vv].F;
+    for (int r = 0; r < W; ++r) {
+        const int n = rec[r * 8 + v].F;
+        const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const l3d_match*>(window + lay.rec_off[v]) + size_t(r) * size_t(lay.cap[v]));
+        uint4* dst = reinterpret_cast<uint4*>(out + off);
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * n; i += gridDim.x * blockDim.x) dst[i] = src[i];
+        off += n;
     }
 }
 
@@ -1824,15 +1843,15 @@ struct ViewGroup {
     DBuf<int> d_zero; DBuf<int> d_vres; HBuf<int> h_vres; int res_stride = 8;     // result ints per view: 8 scalars + one count per hand-over slot
     // several GPUs on one scene: depth samples of the group's views (one buffer: one all-reduce), the ranks' records,
     // the packed records of this rank, all ranks' packed records, all ranks' records view by view
-    DBuf<float> d_samples; size_t samples_total = 0; size_t hist_off = 0, hist_total = 0;
-    DBuf<RankRec> d_myrec, d_allrec; HBuf<RankRec> h_allrec;
+    size_t hist_off = 0, hist_total = 0;
+    HBuf<RankRec> h_allrec; MrLayout lay; DBuf<l3d_match> d_gather;
     cudaEvent_t ev_x[2] = {nullptr, nullptr};      // [0] exchange done on the main stream, [1] this group's records copied to the host
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [0] results on the host, [2..5] stage boundaries
     void release()
     {
         for (int k = 0; k < VG_MAX; ++k) slot[k].release();
         h_args.release(); d_args.release(); h_cams.release(); d_cams.release(); d_zero.release(); d_vres.release(); h_vres.release();
-        d_samples.release(); d_myrec.release(); d_allrec.release(); h_allrec.release();
+        h_allrec.release(); d_gather.release();
         for (int k = 0; k < 2; ++k) if (ev_x[k]) { cudaEventDestroy(ev_x[k]); ev_x[k] = nullptr; }
         for (int k = 0; k < 6; ++k) if (ev[k]) { cudaEventDestroy(ev[k]); ev[k] = nullptr; }
     }
@@ -1878,6 +1897,7 @@ struct PhaseASet {
     std::vector<JobDev> jobs_host; std::vector<uint64_t> job_cands, job_raw, job_raw_all /* summed over the ranks (several GPUs on one scene) */; std::vector<int> job_rowmax, job_raw_rowmax; DBuf<int> d_rm_begin, d_rm_len, d_rm_out;
     DBuf<unsigned long long> d_job_sum64; HBuf<unsigned long long> h_job_sum64;
     bool pa_ms_pending = false;
+    bool background = false;      // this batch's pair tests run beside the per-view chain of the batch before (helper thread)
     cudaEvent_t pa_ev[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t pa_kev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // [0][1] around k_pretest, [1][4] around k_pretest2, [2][3] around k_exact_flat
     bool pa_kev_set[2] = {false, false};
@@ -1900,11 +1920,11 @@ struct l3d_ctx {
     std::string err;
     // several GPUs on one scene (l3d_comm_init)
     NcclApi* nccl = nullptr; ncclComm_t comm = nullptr; int rank = 0, world = 1, result_root = -1;
-    bool copies_pending = false;
+    bool copies_pending = false, want_records = true;      // want_records: the current calls copy the output records to the host
     double host_s[4] = {0, 0, 0, 0};      // host seconds in enqueue_group / finish_group (waiting) / finish_group (rest) / number of groups (l3d_debug_host_times)
     // the record windows (one per group in flight): every rank's is mapped into every process, the ranks store their
     // output records straight into each other's
-    l3d_match* win[2] = {nullptr, nullptr}; size_t win_cap = 0; MrPeers peers[2];
+    unsigned char* win[2] = {nullptr, nullptr}; size_t win_cap = 0 /* bytes */; MrPeers peers[2];
     DBuf<int> d_bar; DBuf<unsigned long long> d_tot; HBuf<unsigned long long> h_tot; DBuf<unsigned char> d_ipc; HBuf<unsigned char> h_ipc;
     uint64_t launches = 0;
     // views
@@ -2012,6 +2032,23 @@ int run_phase_a(l3d_ctx* cx, PhaseASet* ctx, const std::vector<JobHost>& jh)   /
     L3D_CUDA(cudaSetDevice(cx->device));
     cudaStream_t st = ctx->stream;
     const int n_jobs = int(jh.size());
+    // Pair tests that run beside the per-view chain must leave it room: the chain is a sequence of short dependent
+    // kernels whose blocks can only start when registers and shared memory are free, and kernels that fill every SM
+    // make each of them wait for blocks to retire.  In the background the large kernels therefore ask for unused
+    // dynamic shared memory, which caps them at 3-4 blocks per SM (about half of each SM stays free); alone they run
+    // at full occupancy.
+    static const bool bg_on = getenv("L3D_BG_SMEM") && atoi(getenv("L3D_BG_SMEM")) != 0;      // off by default: measured slower on one GPU
+    static const bool bg_ready = [] {
+        bool ok = true;
+        ok = ok && cudaFuncSetAttribute(k_pretest<4, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(k_pretest2, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(k_expand, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(k_exact_flat, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) == cudaSuccess;
+        return ok;
+    }();
+    const bool bgm = ctx->background && bg_on && bg_ready;
+    // per kernel: what leaves room for 4 / 3 / 4 / 3 blocks per SM (228 KB of shared memory, 1 KB reserved per block)
+    const size_t bg_p1 = bgm ? 51 * 1024 : 0, bg_p2 = bgm ? 55 * 1024 : 0, bg_ex = bgm ? 55 * 1024 : 0, bg_ef = bgm ? 65 * 1024 : 0;
     ctx->jobs_host.assign(size_t(n_jobs), JobDev());
     ctx->job_cands.assign(size_t(n_jobs), 0);
     ctx->job_rowmax.assign(size_t(n_jobs), 0);
@@ -2019,6 +2056,7 @@ int run_phase_a(l3d_ctx* cx, PhaseASet* ctx, const std::vector<JobHost>& jh)   /
     ctx->pa_kev_set[0] = ctx->pa_kev_set[1] = false;
     if (n_jobs == 0) return 0;
     long long sh_tot = 0, th_tot = 0, words = 0, rows = 0, blocks = 0, l1_words = 0, l1_blocks = 0;
+    static const int p1_rows = getenv("L3D_P1_ROWS") ? std::max(128, atoi(getenv("L3D_P1_ROWS")) / 128 * 128) : P1_ROWS;
     int max_n = 1;
     for (int j = 0; j < n_jobs; ++j) {
         const l3d_view& sv = cx->views[jh[j].src_view]; const l3d_view& tv = cx->views[jh[j].tgt_view];
@@ -2032,7 +2070,7 @@ int run_phase_a(l3d_ctx* cx, PhaseASet* ctx, const std::vector<JobHost>& jh)   /
         blocks += (long long)((d.n_src + PT_ROWS - 1) / PT_ROWS) * d.col_blocks;
         d.l1_off = l1_words; d.l1_blk_off = int(l1_blocks);
         l1_words += (long long)((d.n_src + 31) / 32) * d.n_tgt;
-        l1_blocks += (long long)((d.n_src + P1_ROWS - 1) / P1_ROWS) * ((d.n_tgt + P1_COLS - 1) / P1_COLS);
+        l1_blocks += (long long)((d.n_src + p1_rows - 1) / p1_rows) * ((d.n_tgt + P1_COLS - 1) / P1_COLS);
         max_n = std::max(max_n, std::max(d.n_src, d.n_tgt));
         if (sh_tot > 0x7fffffff || th_tot > 0x7fffffff || rows > 0x7ffffff0 || blocks > 0x7ffffff0 || l1_blocks > 0x7ffffff0) { ctx->err = "phase A: batch too large"; return 1; }
     }
@@ -2047,16 +2085,9 @@ int run_phase_a(l3d_ctx* cx, PhaseASet* ctx, const std::vector<JobHost>& jh)   /
     if (rows > 0 && blocks > 0) {
         k_hoist<<<dim3((max_n + 127) / 128, n_jobs), 128, 0, st>>>(cx->d_segs.p, ctx->d_jobs.p, ctx->d_sh.p, ctx->d_sh1.p, ctx->d_th.p, ctx->d_row_job.p, cx->pretest_mode);
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[0], st));
-        {
-            static const int variant = getenv("L3D_P1_VARIANT") ? atoi(getenv("L3D_P1_VARIANT")) : 0;
-            if (variant == 1) k_pretest<4, 8><<<unsigned(l1_blocks), P1_BLOCK, 0, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p);
-            else if (variant == 2) k_pretest<8, 8><<<unsigned(l1_blocks), P1_BLOCK, 0, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p);
-            else if (variant == 3) k_pretest<8, 6><<<unsigned(l1_blocks), P1_BLOCK, 0, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p);
-            else if (variant == 4) k_pretest<2, 8><<<unsigned(l1_blocks), P1_BLOCK, 0, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p);
-            else k_pretest<4, 6><<<unsigned(l1_blocks), P1_BLOCK, 0, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p);
-        }
+        k_pretest<4, 6><<<unsigned(l1_blocks), P1_BLOCK, bg_p1, st>>>(ctx->d_sh1.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p, p1_rows);
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[1], st));
-        k_pretest2<<<unsigned(blocks), PT_BLOCK, 0, st>>>(ctx->d_sh.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p, ctx->d_cand.p, ctx->d_pa_cnt.p);
+        k_pretest2<<<unsigned(blocks), PT_BLOCK, bg_p2, st>>>(ctx->d_sh.p, ctx->d_th.p, ctx->d_jobs.p, n_jobs, ctx->d_l1.p, ctx->d_cand.p, ctx->d_pa_cnt.p);
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[4], st));
         ctx->pa_kev_set[0] = true;
         ctx->launches += 3;
@@ -2105,9 +2136,9 @@ int run_phase_a(l3d_ctx* cx, PhaseASet* ctx, const std::vector<JobHost>& jh)   /
     L3D_CUDA(ctx->d_stage_row.ensure(size_t(std::max(n_cand, 1)))); L3D_CUDA(ctx->d_stage_ok.ensure(size_t(std::max(n_cand, 1))));
     L3D_CUDA(cudaMemsetAsync(ctx->d_pa_raw.p, 0, sizeof(int) * (size_t(rows) + 1), st));
     if (rows > 0 && n_cand > 0) {
-        k_expand<<<unsigned((rows * 32 + 255) / 256), 256, 0, st>>>(ctx->d_jobs.p, ctx->d_row_job.p, int(rows), ctx->d_cand.p, ctx->d_pa_off.p, ctx->d_stage_col.p, ctx->d_stage_row.p);
+        k_expand<<<unsigned((rows * 32 + 255) / 256), 256, bg_ex, st>>>(ctx->d_jobs.p, ctx->d_row_job.p, int(rows), ctx->d_cand.p, ctx->d_pa_off.p, ctx->d_stage_col.p, ctx->d_stage_row.p);
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[2], st));
-        k_exact_flat<<<unsigned((n_cand + EF_T - 1) / EF_T), EF_T, 0, st>>>(cx->d_segs.p, ctx->d_jobs.p, ctx->d_row_job.p, n_cand, ctx->d_stage_col.p, ctx->d_stage_row.p,
+        k_exact_flat<<<unsigned((n_cand + EF_T - 1) / EF_T), EF_T, bg_ef, st>>>(cx->d_segs.p, ctx->d_jobs.p, ctx->d_row_job.p, n_cand, ctx->d_stage_col.p, ctx->d_stage_row.p,
                                                                           ctx->d_stage_ok.p, ctx->d_stage_dep.p, ctx->d_pa_raw.p);
         L3D_CUDA(cudaEventRecord(ctx->pa_kev[3], st));
         ctx->pa_kev_set[1] = true;
@@ -2149,17 +2180,20 @@ struct GroupView { int view; int n_nb; const l3d_neighbor* nb; int first_job; si
 size_t mr_group_need(l3d_ctx* ctx, const GroupView* gv, int count)
 {
     PhaseASet& pa = ctx->pa[ctx->cur];
-    size_t need = 0;
+    size_t need = MR_COUNTS_BYTES;
     for (int g = 0; g < count; ++g) {
-        int n_slots = 0;
+        if (gv[g].view < 0 || gv[g].view >= ctx->V) continue;
+        int n_slots = 0; size_t f_ub = 0;
         for (int c = 0; c < gv[g].n_nb; ++c) {
             const l3d_neighbor& n = gv[g].nb[c];
-            if (n.to_be_matched) { const size_t j = size_t(gv[g].first_job + n_slots++); if (j < pa.job_raw_all.size()) need += size_t(pa.job_raw_all[j]); }
-            else if (gv[g].view >= 0 && gv[g].view < ctx->V) {
+            if (n.to_be_matched) { const size_t j = size_t(gv[g].first_job + n_slots++); if (j < pa.job_raw_all.size()) f_ub += size_t(pa.job_raw_all[j]); }
+            else {
                 const std::vector<Delivered>& dl = ctx->delivered[gv[g].view];
-                for (size_t k = 0; k < dl.size(); ++k) if (dl[k].from_view == n.view) { need += size_t(dl[k].count); break; }
+                for (size_t k = 0; k < dl.size(); ++k) if (dl[k].from_view == n.view) { f_ub += size_t(dl[k].count); break; }
             }
         }
+        need += (size_t(ctx->views[gv[g].view].n_segments) * 8 + 255) & ~size_t(255);
+        need += size_t(ctx->world) * std::max<size_t>(f_ub, 1) * sizeof(l3d_match);
     }
     return need;
 }
@@ -2172,7 +2206,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     gr.count = count;
     L3D_CUDA(gr.h_args.ensure(VG_MAX)); L3D_CUDA(gr.d_args.ensure(VG_MAX));
     if (mr) {
-        L3D_CUDA(gr.d_myrec.ensure(VG_MAX)); L3D_CUDA(gr.d_allrec.ensure(size_t(VG_MAX) * ctx->world)); L3D_CUDA(gr.h_allrec.ensure(size_t(VG_MAX) * ctx->world));
+        L3D_CUDA(gr.h_allrec.ensure(size_t(VG_MAX) * MR_MAX_RANKS));
         // the records of the group two groups ago may still be on their way to the host out of this group's buffers
         if (gr.ev_x[1]) L3D_CUDA(cudaStreamWaitEvent(st, gr.ev_x[1], 0));
     }
@@ -2196,8 +2230,10 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     size_t zero_total = 0;
     int mx_src = 1, mx_cams = 1, mx_items = 1, mx_cta = 1; long mx_warps = 1; size_t mx_M = 0, mx_smem = 0;
     bool any_scored = false, any_window = false, any_quadratic = false, any_deliver = false;
-    struct Z { size_t items, iters, best, hist, cursor, end, samples; } z[VG_MAX];
-    size_t hist_total = 0, samples_total = 0, window_need = 0;
+    struct Z { size_t items, iters, best, hist, cursor, end; } z[VG_MAX];
+    size_t hist_total = 0, window_need = MR_COUNTS_BYTES;
+    const int slot_q = int(&gr - ctx->grp);
+    memset(&gr.lay, 0, sizeof gr.lay);
     for (int g = 0; g < count; ++g) {
         const int view = gv[g].view, n_nb = gv[g].n_nb; const l3d_neighbor* nb = gv[g].nb; const int first_job = gv[g].first_job;
         ViewSlot& sl = gr.slot[g];
@@ -2242,7 +2278,11 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         job.pair_tests = pair_tests; job.cand_ub = cand_ub;
         const size_t M_ub = size_t(raw_ub + delivered_ub);          // upper bound on the number of matches to score
         const size_t F_ub_all = size_t(raw_ub_all + delivered_ub);  // ... and on the output records of the view from all ranks together
-        window_need += F_ub_all;
+        if (mr) {                                                    // the view's places in the group's window
+            gr.lay.samp_off[g] = (long long)window_need; window_need += (size_t(n_full) * 8 + 255) & ~size_t(255);
+            gr.lay.rec_off[g] = (long long)window_need; gr.lay.cap[g] = (long long)std::max<size_t>(F_ub_all, 1);
+            window_need += size_t(ctx->world) * size_t(gr.lay.cap[g]) * sizeof(l3d_match);
+        }
         const bool scored = n_slots > 0;                             // cudawrapper.cu:877-878
         const bool delivering = n_deliver > 0 && scored;
         const int stride = max_deliver_seg + 1;                      // one spare key per slot keeps t_start[n_seg] addressable
@@ -2270,7 +2310,6 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         z[g].cursor = z[g].best + 2 * size_t(n_src) + 2; z[g].end = (z[g].cursor + size_t(n_keys) + 2 + 3) & ~size_t(3);
         zero_total = z[g].end;
         z[g].hist = hist_total; hist_total += (size_t(n_keys) + 2 + 3) & ~size_t(3);
-        z[g].samples = samples_total; samples_total += (size_t(n_full) * 2 + 2 + 3) & ~size_t(3);
         // hand-over buffers
         DeliverBuf buf;
         if (delivering) {
@@ -2330,15 +2369,15 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         if (scored) { any_scored = true; mx_items = std::max(mx_items, max_items); mx_smem = std::max(mx_smem, sm_bytes); }
         any_window |= scored && windowed; any_quadratic |= quadratic; any_deliver |= delivering;
     }
-    gr.hist_off = zero_total; gr.hist_total = hist_total; gr.samples_total = samples_total;
+    gr.hist_off = zero_total; gr.hist_total = hist_total;
     zero_total += hist_total;
     L3D_CUDA(gr.d_zero.ensure(zero_total + 4));
-    if (mr) L3D_CUDA(gr.d_samples.ensure(samples_total + 4));
+    if (mr && window_need > ctx->win_cap) { ctx->err = "l3d_match_view: internal error (window too small)"; return 1; }
     for (int g = 0; g < count; ++g) {
         VArgs& va = gr.h_args.p[g];
         va.nitems = gr.d_zero.p + z[g].items; va.iters = reinterpret_cast<unsigned long long*>(gr.d_zero.p + z[g].iters);
         va.best = reinterpret_cast<unsigned long long*>(gr.d_zero.p + z[g].best); va.hist = gr.d_zero.p + gr.hist_off + z[g].hist; va.cursor = gr.d_zero.p + z[g].cursor;
-        if (mr) va.dsamples = gr.d_samples.p + z[g].samples;
+        if (mr) va.dsamples = reinterpret_cast<float*>(ctx->win[slot_q] + gr.lay.samp_off[g]);
     }
     if (mx_smem > ctx->score_smem) {
         L3D_CUDA(cudaFuncSetAttribute(k_score, cudaFuncAttributeMaxDynamicSharedMemorySize, int(mx_smem)));
@@ -2373,37 +2412,39 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     L3D_CUDA(pdl_launch(k_filter_compact, dim3(mx_cta, G), dim3(RM_T), 0, st, A));
     ctx->launches += 1;
     if (mr) {
-        // What the ranks exchange before the host looks at the group: their records of each view, the depth samples
-        // (minimum: every segment has a sample on one rank at most), the sizes of the hand-over groups (sum).
-        L3D_CUDA(pdl_launch(k_mr_prepare, dim3(8, G), dim3(256), 0, st, A, gr.d_myrec.p));
+        // Every rank stores its records, depth samples and counts into all ranks' windows (regions fixed by shared
+        // bounds), a one-word all-reduce tells that everybody's stores have landed, and the hand-over lists and the
+        // medians are made from the own window.
+        const unsigned pb = unsigned(std::min<size_t>(std::max<size_t>((2 * mx_M + 255) / 256, 1), size_t(2 * ctx->n_sm)));
+        L3D_CUDA(pdl_launch(k_mr_push, dim3(pb, G, unsigned(ctx->world)), dim3(256), 0, st, A, gr.lay, ctx->peers[slot_q], ctx->rank));
+        L3D_NCCL(ctx->nccl->AllReduce(ctx->d_bar.p, ctx->d_bar.p, 1, ncclInt, ncclSum, ctx->comm, st));
         ctx->launches += 1;
-        L3D_NCCL(ctx->nccl->GroupStart());
-        L3D_NCCL(ctx->nccl->AllGather(gr.d_myrec.p, gr.d_allrec.p, sizeof(RankRec) * VG_MAX, ncclChar, ctx->comm, st));
-        if (any_scored) L3D_NCCL(ctx->nccl->AllReduce(gr.d_samples.p, gr.d_samples.p, gr.samples_total, ncclFloat, ncclMin, ctx->comm, st));
-        if (any_deliver) L3D_NCCL(ctx->nccl->AllReduce(gr.d_zero.p + gr.hist_off, gr.d_zero.p + gr.hist_off, gr.hist_total, ncclInt, ncclSum, ctx->comm, st));
-        L3D_NCCL(ctx->nccl->GroupEnd());
-        if (any_deliver) { L3D_CUDA(pdl_launch(k_scan_views, dim3(1, G), dim3(SCAN_T), 0, st, A, 1)); ctx->launches += 1; }
+        const unsigned char* window = ctx->win[slot_q];
+        if (any_deliver) {
+            const unsigned hb = unsigned(std::min<size_t>(size_t(ctx->world) * pb, size_t(8 * ctx->n_sm)));
+            L3D_CUDA(pdl_launch(k_mr_hist, dim3(hb, G), dim3(256), 0, st, A, window, gr.lay, ctx->world));
+            L3D_CUDA(pdl_launch(k_scan_views, dim3(1, G), dim3(SCAN_T), 0, st, A, 1));
+            L3D_CUDA(pdl_launch(k_mr_deliver_scatter, dim3(hb, G), dim3(256), 0, st, A, window, gr.lay, ctx->world));
+            ctx->launches += 3;
+        }
         L3D_CUDA(pdl_launch(k_finish_view, dim3(1, G), dim3(MS_T), 0, st, A));
         ctx->launches += 1;
+        if (ctx->want_records && (ctx->result_root < 0 || ctx->result_root == ctx->rank)) {
+            // for the copy to the host: the ranks' regions of each view put end to end.  On this stream, so that the
+            // window is only ever read in stream order (the other ranks write the group after next into it as soon as
+            // this rank has joined the next group's all-reduce).
+            size_t bound = 0;
+            for (int g = 0; g < count; ++g) bound += size_t(gr.lay.cap[g]);
+            L3D_CUDA(gr.d_gather.ensure(bound));
+            k_mr_gather<<<dim3(pb, G), 256, 0, st>>>(window, gr.lay, ctx->world, gr.d_gather.p);
+            ctx->launches += 1;
+        }
+        L3D_CUDA(cudaEventRecord(gr.ev_x[0], st));      // the gathered records are complete
         L3D_CUDA(cudaGetLastError());
         if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[5], st));
         L3D_CUDA(cudaMemcpyAsync(gr.h_vres.p, gr.d_vres.p, sizeof(int) * size_t(count) * res_stride, cudaMemcpyDeviceToHost, st));
-        L3D_CUDA(cudaMemcpyAsync(gr.h_allrec.p, gr.d_allrec.p, sizeof(RankRec) * VG_MAX * size_t(ctx->world), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaMemcpyAsync(gr.h_allrec.p, window, sizeof(RankRec) * 8 * size_t(ctx->world), cudaMemcpyDeviceToHost, st));
         L3D_CUDA(cudaEventRecord(gr.ev[0], st));
-        // The records themselves: every rank stores its own into all ranks' windows, at the places the gathered counts
-        // assign; a one-word all-reduce tells that everybody's stores have landed; then the hand-over lists are built.
-        if (window_need > ctx->win_cap) { ctx->err = "l3d_match_view: internal error (record window too small)"; return 1; }
-        const int q = int(&gr - ctx->grp);
-        const unsigned pb = unsigned(std::min<size_t>(std::max<size_t>((2 * mx_M + 255) / 256, 1), size_t(4 * ctx->n_sm)));
-        L3D_CUDA(pdl_launch(k_mr_push, dim3(pb, G, unsigned(ctx->world)), dim3(256), 0, st, A, (const RankRec*)gr.d_allrec.p, ctx->peers[q], ctx->rank, ctx->world));
-        L3D_NCCL(ctx->nccl->AllReduce(ctx->d_bar.p, ctx->d_bar.p, 1, ncclInt, ncclSum, ctx->comm, st));
-        ctx->launches += 1;
-        if (any_deliver) {
-            L3D_CUDA(pdl_launch(k_mr_deliver_scatter, dim3(unsigned(std::min<size_t>(size_t(ctx->world) * pb, size_t(8 * ctx->n_sm))), G), dim3(256), 0, st, A, (const l3d_match*)ctx->win[q], (const RankRec*)gr.d_allrec.p, ctx->world));
-            ctx->launches += 1;
-        }
-        L3D_CUDA(cudaGetLastError());
-        L3D_CUDA(cudaEventRecord(gr.ev_x[0], st));
         return 0;
     }
     if (any_deliver) {
@@ -2460,12 +2501,12 @@ int mr_ensure_window(l3d_ctx* ctx, size_t need)
     L3D_CUDA(cudaMemsetAsync(ctx->d_bar.p, 0, sizeof(int), st));
     L3D_NCCL(ctx->nccl->AllReduce(ctx->d_bar.p, ctx->d_bar.p, 1, ncclInt, ncclSum, ctx->comm, st));
     L3D_CUDA(cudaStreamSynchronize(st));
-    const size_t cap = std::max<size_t>(need + need / 4, size_t(1) << 21);       // at least 64 MiB
+    const size_t cap = std::max<size_t>(need + need / 4, size_t(64) << 20);      // bytes; at least 64 MiB
     cudaIpcMemHandle_t mine[2];
     for (int q = 0; q < 2; ++q) {
         if (ctx->win[q]) cudaFree(ctx->win[q]);
         ctx->win[q] = nullptr;
-        L3D_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->win[q]), cap * sizeof(l3d_match)));
+        L3D_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->win[q]), cap));
         L3D_CUDA(cudaIpcGetMemHandle(&mine[q], ctx->win[q]));
     }
     ctx->win_cap = 0;
@@ -2480,7 +2521,7 @@ int mr_ensure_window(l3d_ctx* ctx, size_t need)
             cudaIpcMemHandle_t h; memcpy(&h, ctx->h_ipc.p + (size_t(r) * 2 + q) * sizeof h, sizeof h);
             void* ptr = nullptr;
             L3D_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
-            ctx->peers[q].base[r] = static_cast<l3d_match*>(ptr);
+            ctx->peers[q].base[r] = static_cast<unsigned char*>(ptr);
         }
     ctx->win_cap = cap;
     return 0;
@@ -2539,15 +2580,20 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
     const bool mr = ctx->world > 1;
     int view_off[VG_MAX], view_cnt[VG_MAX];              // several GPUs: where each view's records are in this group's window
     if (mr) {
-        long long total = 0;
+        long long total = 0; int max_cnt = 0;
         for (int v = 0; v < gr.count; ++v) {
             view_off[v] = int(total);
-            for (int r = 0; r < ctx->world; ++r) total += gr.h_allrec.p[size_t(r) * VG_MAX + v].F;
+            for (int r = 0; r < ctx->world; ++r) {
+                const int f = gr.h_allrec.p[size_t(r) * VG_MAX + v].F;
+                if (f < 0 || (long long)f > gr.lay.cap[v]) { ctx->err = "l3d_match_view: internal error (record window overrun)"; return 1; }
+                total += f; max_cnt = std::max(max_cnt, f);
+            }
             view_cnt[v] = int(total - view_off[v]);
         }
-        if (size_t(total) > ctx->win_cap) { ctx->err = "l3d_match_view: internal error (record window overrun)"; return 1; }
+        if (total > 0x7fffffffll) { ctx->err = "l3d_match_view: too many output records in one group of views"; return 1; }
         copy_back = copy_back && (ctx->result_root < 0 || ctx->result_root == ctx->rank);      // who gets the records on the host
-        if (copy_back) L3D_CUDA(cudaStreamWaitEvent(ctx->copy_stream, gr.ev_x[0], 0));
+        (void)max_cnt;
+        if (copy_back && total > 0) L3D_CUDA(cudaStreamWaitEvent(ctx->copy_stream, gr.ev_x[0], 0));
     }
     bool copies = false;
     for (int g = 0; g < gr.count; ++g) {
@@ -2597,7 +2643,7 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
         if (copy_back && F > 0) {                          // on its own stream: the next group is already running
             if (ctx->retain || !single) { if (arena_take(ctx, size_t(F), &dst)) return 1; }      // results of a schedule are collected ahead of their calls
             else { L3D_CUDA(ctx->h_filtered.ensure(size_t(F))); dst = ctx->h_filtered.p; }
-            const l3d_match* from = mr ? ctx->win[int(&gr - ctx->grp)] + view_off[g] : sl.d_filtered.p;
+            const l3d_match* from = mr ? gr.d_gather.p + view_off[g] : sl.d_filtered.p;
             L3D_CUDA(cudaMemcpyAsync(dst, from, sizeof(l3d_match) * size_t(F), cudaMemcpyDeviceToHost, ctx->copy_stream));
             copies = true;
         }
@@ -2659,6 +2705,7 @@ void start_worker(l3d_ctx* ctx, size_t from)
     std::vector<JobHost> jh;
     set->begin = from; set->end = plan_batch(ctx, from, jh);
     ctx->pa_worker_rc = 0;
+    set->background = true;
     ctx->pa_worker = std::thread([ctx, set, jh]() {
         try { ctx->pa_worker_rc = run_phase_a(ctx, set, jh); }
         catch (const std::exception& e) { set->err = std::string("pair tests (helper thread): ") + e.what(); ctx->pa_worker_rc = 1; }
@@ -2695,6 +2742,7 @@ int top_up(l3d_ctx* ctx)
             std::vector<JobHost> jh;
             PhaseASet& set = ctx->pa[ctx->cur];
             set.begin = ctx->fly_end; set.end = plan_batch(ctx, ctx->fly_end, jh);
+            set.background = false;
             const int rc = run_phase_a(ctx, &set, jh);
             if (rc == 2 && set.end - set.begin > 1 && ctx->world <= 1) {             // halve the batch and try again (one GPU only: ranks must cut alike)
                 uint64_t pairs = 0;
@@ -2709,7 +2757,8 @@ int top_up(l3d_ctx* ctx)
         if (mr_job_totals(ctx, set)) return 1;
         ctx->batch_begin = set.begin; ctx->batch_end = set.end;
         ctx->launches += set.launches; set.launches = 0;
-        if (ctx->batch_end < ctx->order.size() && !ctx->stage_events) start_worker(ctx, ctx->batch_end);      // the following batch, meanwhile (not when stages are timed: nothing may run beside anything)
+        static const bool no_overlap = getenv("L3D_NO_OVERLAP") != nullptr;
+        if (ctx->batch_end < ctx->order.size() && !ctx->stage_events && !no_overlap) start_worker(ctx, ctx->batch_end);      // the following batch, meanwhile (not when stages are timed: nothing may run beside anything)
     }
     // the next groups: consecutive views of one dependency level, two groups in flight
     while (ctx->fly_end < ctx->batch_end && ctx->grp_end - ctx->grp_begin < 2) {
@@ -2755,6 +2804,7 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
         // ---- the next view of the announced schedule: the library works through the schedule in its own order
         // (by dependency level) and ahead of the caller; wait until this view's result has been collected
         if (!ctx->plan_started) { ctx->plan_started = true; ctx->run_sigma_p = sigma_p; ctx->run_sigma_a = sigma_a; ctx->run_copy_back = copy_back; }
+        ctx->want_records = ctx->run_copy_back;
         const size_t p = ctx->call_next;
         while (!ctx->results[p].ready) {
             if (top_up(ctx)) { drain_pending(ctx); return 1; }
@@ -2778,6 +2828,8 @@ int match_view_impl(l3d_ctx* ctx, int view, int n_nb, const l3d_neighbor* nb, fl
     for (int c = 0; c < n_nb; ++c)
         if (nb[c].to_be_matched) { JobHost j; j.src_view = view; j.tgt_view = nb[c].view; memcpy(j.F, nb[c].F, sizeof j.F); jh.push_back(j); }
     PhaseASet& set = ctx->pa[ctx->cur];
+    set.background = false;
+    ctx->want_records = copy_back;
     if (run_phase_a(ctx, &set, jh)) { ctx->err = set.err; return 1; }
     if (mr_job_totals(ctx, set)) return 1;
     ctx->launches += set.launches; set.launches = 0;
