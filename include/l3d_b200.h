@@ -217,6 +217,24 @@ typedef struct { int32_t a, b; } l3d_pair;
 int l3d_affinity(l3d_ctx* ctx, const float* median_depth, size_t n_pairs, const l3d_pair* pairs,
                  float sigma_a, float* out);
 
+/* ---- candidate pairs -> affinity edges, thresholded on the device: the similarity of l3d_affinity followed by the
+ *      reference's edge weight and acceptance test (line3D.cc:1014-1016, 1085-1087, 1163-1165)
+ *          w = mult * 0.5 * (score[a] + score[b]) * sim,     kept if w > thr
+ *      (mult: the collinearity weight for pairs inside one image, 1 otherwise; thr: 0.25 for a direct correspondence,
+ *      0.01 for the others).  Only the kept candidates come back, in candidate order, as (index into cands, w) -- for
+ *      the urban scene 2.4e6 of 2.2e7.  l3d_candidate_buffer hands out pinned host memory (context-owned, valid until
+ *      the next call) to build the candidate list in; any host pointer is accepted by l3d_affinity_edges, pinned
+ *      memory just travels faster.  hyp_score: one value per hypothesis of the last l3d_unproject.
+ *      order (optional, may be NULL): receives the kept candidates' positions in the order the clustering takes its
+ *      edges -- a stable sort by ascending weight (clustering.cc:12) -- sorted on the device: order[t] is the index
+ *      into kept[] of the t-th lightest edge (equal weights in candidate order).
+ *      The result buffers belong to the context and stay valid until the next l3d_affinity_edges call. */
+typedef struct { int32_t a, b; float mult, thr; } l3d_candidate;
+typedef struct { uint32_t index; float w; } l3d_kept_edge;
+int l3d_candidate_buffer(l3d_ctx* ctx, size_t n, l3d_candidate** buf);
+int l3d_affinity_edges(l3d_ctx* ctx, const float* median_depth, const float* hyp_score, size_t n, const l3d_candidate* cands,
+                       float sigma_a, const l3d_kept_edge** kept, size_t* n_kept, const uint32_t** order);
+
 /* ---- diffusion: replaces SparseMatrix construction (sparsematrix.cc:63-191) and
  *      replicator_dynamics_diffusion (cudawrapper.h:74, cudawrapper.cu:1131-1191).
  *      edges: nnz directed entries (i, j, w), unique (i, j), structurally symmetric, every

@@ -1699,6 +1699,104 @@ __global__ void k_affinity(const Hyp* __restrict__ hyp, const ViewD* __restrict_
     out[k] = (sim <= 0.01f) ? 0.0f : sim;
 }
 
+// Candidate pairs -> affinity edges on the device (line3D.cc:1014-1016, 1085-1087, 1163-1165): the similarity of the two
+// hypotheses, the edge weight  mult * 0.5 * (score_a + score_b) * sim  in the host code's order of operations, the
+// threshold of the candidate's kind, and an ordered compaction of the survivors -- only they travel back to the host.
+constexpr int AE_T = 256;
+__device__ __forceinline__ float affinity_of(const Hyp& a, const Hyp& b, const ViewD* __restrict__ views, const float* __restrict__ median, float sigma_a, float two_log001)
+{
+    const ViewD& va = views[a.view]; const ViewD& vb = views[b.view];
+    const float ma = median[a.view], mb = median[b.view];
+    float s1 = d_sim_term(d_point_line(b, a.P1), a.d1, va.k_lower, va.k_upper, ma, two_log001);
+    float s2 = d_sim_term(d_point_line(b, a.P2), a.d2, va.k_lower, va.k_upper, ma, two_log001);
+    float s3 = d_sim_term(d_point_line(a, b.P1), b.d1, vb.k_lower, vb.k_upper, mb, two_log001);
+    float s4 = d_sim_term(d_point_line(a, b.P2), b.d2, vb.k_lower, vb.k_upper, mb, two_log001);
+    float w_d = fminf(fminf(s1, s2), fminf(s3, s4));
+    double dt = __dadd_rn(__dadd_rn(__dmul_rn(a.dir[0], b.dir[0]), __dmul_rn(a.dir[1], b.dir[1])), __dmul_rn(a.dir[2], b.dir[2]));
+    float angle = float(acos(fmax(fmin(dt, 1.0), -1.0)) / 3.14159265358979323846 * 180.0);
+    if (angle > 90.0f) angle = xs(180.0f, angle);
+    float w_a = xexpf(xd(xm(-angle, angle), xm(xm(2.0f, sigma_a), sigma_a)));
+    float sim = fminf(w_d, w_a);
+    return (sim <= 0.01f) ? 0.0f : sim;
+}
+__global__ void __launch_bounds__(AE_T) k_affinity_edges(const Hyp* __restrict__ hyp, const ViewD* __restrict__ views, const float* __restrict__ median, const float* __restrict__ score,
+                                                         const l3d_candidate* __restrict__ cands, size_t n, float sigma_a, float two_log001,
+                                                         float* __restrict__ w_out, int* __restrict__ cta_kept)
+{
+    __shared__ int s_n[AE_T / 32];
+    const size_t k = size_t(blockIdx.x) * AE_T + threadIdx.x;
+    float w = 0.0f; bool keep = false;
+    if (k < n) {
+        const l3d_candidate c = cands[k];
+        const float sim = affinity_of(hyp[c.a], hyp[c.b], views, median, sigma_a, two_log001);
+        w = xm(xm(xm(c.mult, 0.5f), xa(score[c.a], score[c.b])), sim);
+        keep = w > c.thr;
+        w_out[k] = keep ? w : 0.0f;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    if ((threadIdx.x & 31) == 0) s_n[threadIdx.x >> 5] = __popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0) { int t = 0; for (int q = 0; q < AE_T / 32; ++q) t += s_n[q]; cta_kept[blockIdx.x] = t; }
+}
+__global__ void __launch_bounds__(AE_T) k_affinity_compact(const float* __restrict__ w_in, size_t n, const int* __restrict__ cta_off, l3d_kept_edge* __restrict__ out)
+{
+    __shared__ int s_n[AE_T / 32];
+    const size_t k = size_t(blockIdx.x) * AE_T + threadIdx.x;
+    const float w = (k < n) ? w_in[k] : 0.0f;
+    const bool keep = w != 0.0f;                       // (a kept weight exceeds a positive threshold)
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) s_n[warp] = __popc(m);
+    __syncthreads();
+    int before = 0;
+    for (int q = 0; q < warp; ++q) before += s_n[q];
+    if (keep) { l3d_kept_edge e; e.index = unsigned(k); e.w = w; out[cta_off[blockIdx.x] + before + __popc(m & ((1u << lane) - 1u))] = e; }
+}
+
+// The order in which the clustering takes the edges (clustering.cc:12: a stable sort by ascending weight): the kept
+// candidates sorted by the 64-bit key (weight bits, position) -- weights are positive, so their bit patterns order like
+// the values, and the position makes every key unique, so any sort gives the stable order.  Bitonic network over a
+// power of two of keys (padding: all ones); strides below the tile size run in shared memory.
+constexpr int BS_TILE = 2048;
+__global__ void k_edge_keys(const l3d_kept_edge* __restrict__ kept, int n, int n_pad, unsigned long long* __restrict__ keys)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_pad) return;
+    keys[k] = (k < n) ? (((unsigned long long)__float_as_uint(kept[k].w) << 32) | (unsigned long long)unsigned(k)) : ~0ull;
+}
+__global__ void k_bitonic_global(unsigned long long* __restrict__ keys, int j, int k)
+{
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned p = i ^ unsigned(j);
+    if (p > i) {
+        const unsigned long long a = keys[i], b = keys[p];
+        const bool up = (i & unsigned(k)) == 0;
+        if ((a > b) == up) { keys[i] = b; keys[p] = a; }
+    }
+}
+__global__ void __launch_bounds__(BS_TILE / 2) k_bitonic_shared(unsigned long long* __restrict__ keys, int j_first, int k)
+{
+    __shared__ unsigned long long s[BS_TILE];
+    const unsigned base = blockIdx.x * BS_TILE;
+    s[threadIdx.x] = keys[base + threadIdx.x]; s[threadIdx.x + BS_TILE / 2] = keys[base + threadIdx.x + BS_TILE / 2];
+    __syncthreads();
+    for (int j = j_first; j > 0; j >>= 1) {
+        const unsigned t = threadIdx.x;
+        const unsigned i = ((t & ~unsigned(j - 1)) << 1) | (t & unsigned(j - 1));      // the lower index of the t-th pair at stride j
+        const unsigned p = i | unsigned(j);
+        const bool up = ((base + i) & unsigned(k)) == 0;
+        const unsigned long long a = s[i], b = s[p];
+        if ((a > b) == up) { s[i] = b; s[p] = a; }
+        __syncthreads();
+    }
+    keys[base + threadIdx.x] = s[threadIdx.x]; keys[base + threadIdx.x + BS_TILE / 2] = s[threadIdx.x + BS_TILE / 2];
+}
+__global__ void k_edge_order(const unsigned long long* __restrict__ keys, int n, unsigned* __restrict__ order)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) order[k] = unsigned(keys[k] & 0xffffffffull);
+}
+
 // ------------------------------------------------------------------------------------------
 // diffusion (cudawrapper.cu:717-829, 1131-1191)
 // ------------------------------------------------------------------------------------------
@@ -1970,6 +2068,7 @@ struct l3d_ctx {
     // hypotheses
     DBuf<Hyp> d_hyp; size_t n_hyp = 0; DBuf<l3d_hypothesis_in> d_hin; DBuf<l3d_segment3d> d_hout;
     DBuf<l3d_pair> d_pairs; DBuf<float> d_aff, d_medians;
+    HBuf<l3d_candidate> h_cands; DBuf<l3d_candidate> d_cands; DBuf<float> d_hscore, d_ew; DBuf<int> d_ecnt, d_eoff; DBuf<l3d_kept_edge> d_kept; HBuf<l3d_kept_edge> h_kept; DBuf<unsigned long long> d_ekeys; DBuf<unsigned> d_eorder; HBuf<unsigned> h_eorder;
     DBuf<unsigned char> d_flush; int flush_value = 0;
     // timing
     cudaEvent_t ev[2] = {nullptr, nullptr};          // around the FP32 peak probe
@@ -2969,6 +3068,7 @@ void l3d_destroy(l3d_ctx* ctx)
     for (int k = 0; k < 2; ++k) if (ctx->mark_ev[k]) cudaEventDestroy(ctx->mark_ev[k]);
     ctx->h_filtered.release(); ctx->h_ints.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
+    ctx->h_cands.release(); ctx->d_cands.release(); ctx->d_hscore.release(); ctx->d_ew.release(); ctx->d_ecnt.release(); ctx->d_eoff.release(); ctx->d_kept.release(); ctx->h_kept.release(); ctx->d_ekeys.release(); ctx->d_eorder.release(); ctx->h_eorder.release();
     ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release();
     for (int k = 0; k < 2; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -3244,6 +3344,73 @@ int l3d_affinity(l3d_ctx* ctx, const float* median_depth, size_t n_pairs, const 
         L3D_CUDA(cudaGetLastError());
         L3D_CUDA(cudaMemcpyAsync(out, ctx->d_aff.p, sizeof(float) * n_pairs, cudaMemcpyDeviceToHost, ctx->stream));
         L3D_CUDA(cudaStreamSynchronize(ctx->stream));
+        return 0;
+    });
+}
+
+int l3d_candidate_buffer(l3d_ctx* ctx, size_t n, l3d_candidate** buf)
+{
+    if (!ctx || !buf) return 1;
+    return guarded(ctx, [&]() -> int {
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        L3D_CUDA(ctx->h_cands.ensure(std::max<size_t>(n, 1)));
+        *buf = ctx->h_cands.p;
+        return 0;
+    });
+}
+
+int l3d_affinity_edges(l3d_ctx* ctx, const float* median_depth, const float* hyp_score, size_t n, const l3d_candidate* cands, float sigma_a,
+                       const l3d_kept_edge** kept, size_t* n_kept, const uint32_t** order)
+{
+    if (!ctx) return 1;
+    return guarded(ctx, [&]() -> int {
+        if (!kept || !n_kept) { ctx->err = "l3d_affinity_edges: null argument"; return 1; }
+        *kept = nullptr; *n_kept = 0;
+        if (order) *order = nullptr;
+        if (n == 0) return 0;
+        if (!median_depth || !hyp_score || !cands) { ctx->err = "l3d_affinity_edges: null argument"; return 1; }
+        if (ctx->n_hyp == 0) { ctx->err = "l3d_affinity_edges: no hypotheses resident (call l3d_unproject first)"; return 1; }
+        if (n > size_t(0x7fffffff) - AE_T) { ctx->err = "l3d_affinity_edges: too many candidates"; return 1; }
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        cudaStream_t st = ctx->stream;
+        const int blocks = int((n + AE_T - 1) / AE_T);
+        L3D_CUDA(ctx->d_cands.ensure(n)); L3D_CUDA(ctx->d_ew.ensure(n)); L3D_CUDA(ctx->d_hscore.ensure(ctx->n_hyp)); L3D_CUDA(ctx->d_medians.ensure(size_t(ctx->V)));
+        L3D_CUDA(ctx->d_ecnt.ensure(size_t(blocks) + 1)); L3D_CUDA(ctx->d_eoff.ensure(size_t(blocks) + 2));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_medians.p, median_depth, sizeof(float) * size_t(ctx->V), cudaMemcpyHostToDevice, st));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_hscore.p, hyp_score, sizeof(float) * ctx->n_hyp, cudaMemcpyHostToDevice, st));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_cands.p, cands, sizeof(l3d_candidate) * n, cudaMemcpyHostToDevice, st));
+        const float two_log = 2.0f * logf(0.01f);                                   // view.cc:376
+        k_affinity_edges<<<blocks, AE_T, 0, st>>>(ctx->d_hyp.p, ctx->d_viewd.p, ctx->d_medians.p, ctx->d_hscore.p, ctx->d_cands.p, n, sigma_a, two_log, ctx->d_ew.p, ctx->d_ecnt.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+        if (scan_exclusive(ctx, ctx->d_ecnt.p, ctx->d_eoff.p, blocks)) return 1;
+        int total = 0;
+        if (fetch_int(ctx, ctx->d_eoff.p + blocks, &total)) return 1;
+        if (total == 0) return 0;
+        L3D_CUDA(ctx->d_kept.ensure(size_t(total))); L3D_CUDA(ctx->h_kept.ensure(size_t(total)));
+        k_affinity_compact<<<blocks, AE_T, 0, st>>>(ctx->d_ew.p, n, ctx->d_eoff.p, ctx->d_kept.p);
+        ctx->launches += 1;
+        L3D_CUDA(cudaGetLastError());
+        L3D_CUDA(cudaMemcpyAsync(ctx->h_kept.p, ctx->d_kept.p, sizeof(l3d_kept_edge) * size_t(total), cudaMemcpyDeviceToHost, st));
+        if (order) {                                        // the clustering's edge order, while the records travel
+            int n_pad = BS_TILE; while (n_pad < total) n_pad <<= 1;
+            L3D_CUDA(ctx->d_ekeys.ensure(size_t(n_pad))); L3D_CUDA(ctx->d_eorder.ensure(size_t(total))); L3D_CUDA(ctx->h_eorder.ensure(size_t(total)));
+            k_edge_keys<<<(n_pad + 255) / 256, 256, 0, st>>>(ctx->d_kept.p, total, n_pad, ctx->d_ekeys.p);
+            ctx->launches += 1;
+            for (int k = 2; k <= n_pad; k <<= 1) {
+                int j = k >> 1;
+                for (; j >= BS_TILE; j >>= 1) { k_bitonic_global<<<n_pad / 256, 256, 0, st>>>(ctx->d_ekeys.p, j, k); ctx->launches += 1; }
+                k_bitonic_shared<<<n_pad / BS_TILE, BS_TILE / 2, 0, st>>>(ctx->d_ekeys.p, j, k);
+                ctx->launches += 1;
+            }
+            k_edge_order<<<(total + 255) / 256, 256, 0, st>>>(ctx->d_ekeys.p, total, ctx->d_eorder.p);
+            ctx->launches += 1;
+            L3D_CUDA(cudaGetLastError());
+            L3D_CUDA(cudaMemcpyAsync(ctx->h_eorder.p, ctx->d_eorder.p, sizeof(unsigned) * size_t(total), cudaMemcpyDeviceToHost, st));
+        }
+        L3D_CUDA(cudaStreamSynchronize(st));
+        *kept = ctx->h_kept.p; *n_kept = size_t(total);
+        if (order) *order = ctx->h_eorder.p;
         return 0;
     });
 }

@@ -285,22 +285,45 @@ struct Line3D::Impl
                 if (sim > L3D_EPS) view_sim[it->first][n->first] = sim;
             }
         }
-        for (std::map<unsigned, std::map<unsigned, float> >::iterator s = view_sim.begin(); s != view_sim.end(); ++s) {
-            std::cout << prefix << "setting VNs for image [" << s->first << "]" << std::endl;
-            std::vector<std::pair<unsigned, float> > cand;
-            for (std::map<unsigned, float>::iterator n = s->second.begin(); n != s->second.end(); ++n) {
-                if (views.find(n->first) == views.end() || views.find(s->first) == views.end()) continue;
-                if (!(baseline(s->first, n->first) > min_baseline)) continue;
-                bool ok = true;                          // baseline against the neighbours accepted so far, in id order (:514-522)
-                for (size_t e = 0; e < cand.size() && ok; ++e) if (baseline(cand[e].first, n->first) <= min_baseline) ok = false;
-                if (ok) cand.push_back(std::make_pair(n->first, n->second));
+        // The views' neighbour lists are independent of each other: worked out on all cores (camera centres in a flat
+        // table instead of a map look-up per baseline -- the accepted-so-far test is quadratic in the co-visible views),
+        // reported in view order afterwards.
+        std::vector<std::map<unsigned, std::map<unsigned, float> >::iterator> todo;
+        for (std::map<unsigned, std::map<unsigned, float> >::iterator s = view_sim.begin(); s != view_sim.end(); ++s) { vn[s->first]; todo.push_back(s); }
+        const unsigned max_id = views.empty() ? 0u : views.rbegin()->first;
+        std::vector<V3> centre(size_t(max_id) + 1); std::vector<char> present(size_t(max_id) + 1, 0);
+        for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) { centre[it->first] = it->second->C; present[it->first] = 1; }
+        std::vector<size_t> found(todo.size(), 0);
+        auto work = [&](size_t t0, size_t step) {
+            for (size_t q = t0; q < todo.size(); q += step) {
+                const unsigned sid = todo[q]->first;
+                if (sid > max_id || !present[sid]) continue;
+                std::vector<std::pair<unsigned, float> > cand;
+                for (std::map<unsigned, float>::iterator n = todo[q]->second.begin(); n != todo[q]->second.end(); ++n) {
+                    if (n->first > max_id || !present[n->first]) continue;
+                    if (!(float((centre[sid] - centre[n->first]).norm()) > min_baseline)) continue;
+                    bool ok = true;                          // baseline against the neighbours accepted so far, in id order (:514-522)
+                    for (size_t e = 0; e < cand.size() && ok; ++e) if (float((centre[cand[e].first] - centre[n->first]).norm()) <= min_baseline) ok = false;
+                    if (ok) cand.push_back(std::make_pair(n->first, n->second));
+                }
+                std::stable_sort(cand.begin(), cand.end(), [](const std::pair<unsigned, float>& a, const std::pair<unsigned, float>& b) { return a.second > b.second; });
+                if (matching_neighbors > 0 && int(cand.size()) > matching_neighbors) cand.resize(matching_neighbors);
+                std::vector<unsigned>& out = vn.find(sid)->second;
+                for (size_t e = 0; e < cand.size(); ++e) out.push_back(cand[e].first);
+                std::sort(out.begin(), out.end());
+                found[q] = cand.size();
             }
-            std::stable_sort(cand.begin(), cand.end(), [](const std::pair<unsigned, float>& a, const std::pair<unsigned, float>& b) { return a.second > b.second; });
-            if (matching_neighbors > 0 && int(cand.size()) > matching_neighbors) cand.resize(matching_neighbors);
-            std::vector<unsigned>& out = vn[s->first];
-            for (size_t e = 0; e < cand.size(); ++e) out.push_back(cand[e].first);
-            std::sort(out.begin(), out.end());
-            if (verbose) std::cout << prefix << cand.size() << " visual neighbors found" << std::endl;
+        };
+        {
+            const size_t nt = std::max<size_t>(1, std::min<size_t>(host_threads(), todo.size()));
+            std::vector<std::thread> pool;
+            for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t, nt);
+            work(0, nt);
+            for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
+        }
+        for (size_t q = 0; q < todo.size(); ++q) {
+            std::cout << prefix << "setting VNs for image [" << todo[q]->first << "]" << std::endl;
+            if (verbose) std::cout << prefix << found[q] << " visual neighbors found" << std::endl;
         }
     }
 
@@ -666,8 +689,8 @@ struct Line3D::Impl
             for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
         }
         if (prof) { std::cerr << "[prof] pc merge " << now_s() - tp << std::endl; tp = now_s(); }
-        struct Cand { int a, b; float mult; float thr; };
-        std::vector<Cand> cands;
+        typedef l3d_candidate Cand;                   // { a, b, mult, thr }
+        Cand* cands = 0; size_t n_cands = 0;          // the views' lists end to end, in the library's pinned memory
         // dense numbering of every segment, for the "used" pair set
         std::vector<uint64_t> view_base(view_at.size() + 1, 0);
         for (size_t k = 0; k < view_at.size(); ++k) view_base[k + 1] = view_base[k] + view_at[k]->segs.size();
@@ -773,7 +796,8 @@ struct Line3D::Impl
         {   // the views' lists, end to end (copied in parallel: 10^7..10^8 records)
             std::vector<size_t> at(size_t(nviews) + 1, 0);
             for (int v = 0; v < nviews; ++v) at[v + 1] = at[v] + cands_of[v].size();
-            cands.resize(at[nviews]);
+            n_cands = at[nviews];
+            if (l3d_candidate_buffer(ctx, n_cands, &cands)) fail("l3d_candidate_buffer");
             const size_t nt = std::max<size_t>(1, std::min<size_t>(host_threads(), size_t(nviews)));
             auto work = [&](size_t t0) {
                 for (int v = int(t0); v < nviews; v += int(nt)) { if (!cands_of[v].empty()) memcpy(&cands[at[v]], cands_of[v].data(), sizeof(Cand) * cands_of[v].size()); std::vector<Cand>().swap(cands_of[v]); }
@@ -784,44 +808,26 @@ struct Line3D::Impl
             for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
         }
         touched.clear();
-        if (prof) { std::cerr << "[prof] enumerate " << now_s() - tp << " cands " << cands.size() << std::endl; tp = now_s(); }
-        // similarities on the device (line3D.cc:1600-1691)
-        std::vector<l3d_pair> pairs(cands.size());
-        for (size_t k = 0; k < cands.size(); ++k) { pairs[k].a = cands[k].a; pairs[k].b = cands[k].b; }
-        std::vector<float> sim(cands.size());
-        std::vector<float> medians(views.size());
+        if (prof) { std::cerr << "[prof] enumerate " << now_s() - tp << " cands " << n_cands << std::endl; tp = now_s(); }
+        // similarities, edge weights and thresholds on the device (line3D.cc:1600-1691, 1014-1016, 1085-1087, 1163-1165):
+        // only the accepted candidates come back
+        std::vector<float> medians(views.size()), scores(hyps.size());
         for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) medians[it->second->index] = it->second->median_depth;
-        if (!cands.empty() && l3d_affinity(ctx, medians.data(), pairs.size(), pairs.data(), sigma_a, sim.data())) fail("l3d_affinity");
-        stats.affinity_pairs = cands.size();
-        if (prof) { std::cerr << "[prof] l3d_affinity " << now_s() - tp << std::endl; tp = now_s(); }
+        for (size_t k = 0; k < hyps.size(); ++k) scores[k] = hyps[k].score;
+        const l3d_kept_edge* kept = 0; size_t n_kept = 0; const uint32_t* kept_order = 0;
+        if (n_cands && l3d_affinity_edges(ctx, medians.data(), scores.data(), n_cands, cands, sigma_a, &kept, &n_kept, perform_diffusion ? (const uint32_t**)0 : &kept_order)) fail("l3d_affinity_edges");
+        stats.affinity_pairs = n_cands;
+        if (prof) { std::cerr << "[prof] l3d_affinity_edges " << now_s() - tp << " kept " << n_kept << std::endl; tp = now_s(); }
         // edges and node ids in encounter order (line3D.cc:1018-1060)
         std::vector<Edge> A;
         std::vector<int> node_of(hyps.size(), -1); std::vector<int> hyp_of_node;
-        {
-            // weights and the threshold test on all cores (each candidate on its own), the survivors in candidate order
-            const size_t nt = std::max<size_t>(1, host_threads());
-            std::vector<std::vector<std::pair<size_t, float> > > kept(nt);
-            auto work = [&](size_t t) {
-                const size_t k0 = cands.size() * t / nt, k1 = cands.size() * (t + 1) / nt;
-                for (size_t k = k0; k < k1; ++k) {
-                    const Cand& c = cands[k];
-                    // mult is the collinearity weight for same-image pairs (line3D.cc:1163) and exactly 1 otherwise
-                    const float w = c.mult * 0.5f * (hyps[c.a].score + hyps[c.b].score) * sim[k];
-                    if (w > c.thr) kept[t].push_back(std::make_pair(k, w));
-                }
-            };
-            std::vector<std::thread> pool;
-            for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t);
-            work(0);
-            for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
-            for (size_t t = 0; t < nt; ++t)
-                for (size_t q = 0; q < kept[t].size(); ++q) {
-                    const Cand& c = cands[kept[t][q].first]; const float w = kept[t][q].second;
-                    if (node_of[c.a] < 0) { node_of[c.a] = int(hyp_of_node.size()); hyp_of_node.push_back(c.a); }
-                    if (node_of[c.b] < 0) { node_of[c.b] = int(hyp_of_node.size()); hyp_of_node.push_back(c.b); }
-                    Edge e = {node_of[c.a], node_of[c.b], w}; A.push_back(e);
-                    Edge r = {node_of[c.b], node_of[c.a], w}; A.push_back(r);
-                }
+        A.reserve(2 * n_kept);
+        for (size_t q = 0; q < n_kept; ++q) {
+            const Cand& c = cands[kept[q].index]; const float w = kept[q].w;
+            if (node_of[c.a] < 0) { node_of[c.a] = int(hyp_of_node.size()); hyp_of_node.push_back(c.a); }
+            if (node_of[c.b] < 0) { node_of[c.b] = int(hyp_of_node.size()); hyp_of_node.push_back(c.b); }
+            Edge e = {node_of[c.a], node_of[c.b], w}; A.push_back(e);
+            Edge r = {node_of[c.b], node_of[c.a], w}; A.push_back(r);
         }
         if (prof) { std::cerr << "[prof] edges " << now_s() - tp << " A " << A.size() << std::endl; }
         stats.t_affinity += now_s() - t0;
@@ -864,8 +870,14 @@ struct Line3D::Impl
         const double tc = now_s();
         // Felzenszwalb-Huttenlocher as the reference runs it (clustering.cc:6-47, universe.h:59-115):
         // edges stably sorted by ascending weight, threshold w + c / size with c = 1
-        std::vector<Edge> sorted(A);
-        {
+        std::vector<Edge> sorted;
+        if (kept_order && A.size() == 2 * n_kept) {
+            // sorted on the device (l3d_affinity_edges): the two directions of a candidate carry the same weight and
+            // follow each other in A, so they stay together, in order, in the stable order by weight
+            sorted.resize(A.size());
+            for (size_t t = 0; t < n_kept; ++t) { sorted[2 * t] = A[2 * size_t(kept_order[t])]; sorted[2 * t + 1] = A[2 * size_t(kept_order[t]) + 1]; }
+        } else {
+            sorted = A;
             // stable sort by weight: positive floats order like their bit patterns, so four stable 8-bit counting passes
             // do it (a comparison sort of 10^6..10^7 edges was most of this stage); anything else goes the general way
             bool positive = true;
