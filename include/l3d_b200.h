@@ -146,6 +146,13 @@ typedef struct {
 } l3d_match_result;
 int l3d_match_view(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors,
                    float sigma_p, float sigma_a, l3d_match_result* result);
+/* Hands records to a view from outside: what the reference's host does when it loads the matches earlier views have
+ * filed for a view and passes them into compute_pairwise_matches through its in/out list (view.cc:200-224,
+ * line3D.cc:806).  `records` are in the RECEIVING view's frame: src_seg = its segment, tgt_seg = the segment of
+ * from_view, depths as l3d_match lists them (cam and confidence are ignored).  The next l3d_match_view of to_view that
+ * lists from_view with to_be_matched = 0 consumes them like records delivered inside the library.  Used by the
+ * operator-level binding (integration/cudawrapper_b200.cc). */
+int l3d_deliver(l3d_ctx* ctx, int to_view, int from_view, size_t n, const l3d_match* records);
 /* Optional: with on != 0, l3d_match_result::filtered of every following l3d_match_view call stays valid until
  * l3d_reset_matching / l3d_set_views / l3d_destroy instead of until the next call (the records of all views are kept
  * in pinned host memory, 32 bytes each, reused after a reset).  A caller that files the records into its own

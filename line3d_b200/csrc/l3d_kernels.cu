@@ -3209,6 +3209,45 @@ int l3d_set_views(l3d_ctx* ctx, int n_views, const l3d_view* views)
     });
 }
 
+int l3d_deliver(l3d_ctx* ctx, int to_view, int from_view, size_t n, const l3d_match* records)
+{
+    if (!ctx) return 1;
+    return guarded(ctx, [&]() -> int {
+        if (to_view < 0 || to_view >= ctx->V || from_view < 0 || from_view >= ctx->V || to_view == from_view) { ctx->err = "l3d_deliver: view index out of range"; return 1; }
+        if (n > 0 && !records) { ctx->err = "l3d_deliver: null argument"; return 1; }
+        if (n > size_t(0x7fffffff)) { ctx->err = "l3d_deliver: too many records"; return 1; }
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        drain_pending(ctx);
+        const int n_to = ctx->views[to_view].n_segments, n_from = ctx->views[from_view].n_segments;
+        // grouped by the receiving view's segment (counting sort), as k_deliver_scatter leaves them
+        std::vector<int> start(size_t(n_to) + 2, 0), tgt(std::max<size_t>(n, 1)); std::vector<float4> dep(std::max<size_t>(n, 1));
+        for (size_t k = 0; k < n; ++k) {
+            if (records[k].src_seg < 0 || records[k].src_seg >= n_to || records[k].tgt_seg < 0 || records[k].tgt_seg >= n_from) { ctx->err = "l3d_deliver: segment index out of range"; return 1; }
+            ++start[size_t(records[k].src_seg) + 1];
+        }
+        int max_group = 0;
+        for (int q = 0; q < n_to; ++q) { max_group = std::max(max_group, start[size_t(q) + 1]); start[size_t(q) + 1] += start[q]; }
+        start[size_t(n_to) + 1] = start[n_to];
+        { std::vector<int> cur(start.begin(), start.begin() + n_to);
+          for (size_t k = 0; k < n; ++k) { const int pos = cur[records[k].src_seg]++; tgt[pos] = records[k].tgt_seg; dep[pos] = make_float4(records[k].depths[0], records[k].depths[1], records[k].depths[2], records[k].depths[3]); } }
+        DeliverBuf buf; buf.refs = 1; buf.counts.assign(1, int(n)); buf.maxg.assign(1, max_group);
+        L3D_CUDA(ctx->pool.get(sizeof(int) * (size_t(n_to) + 2), reinterpret_cast<void**>(&buf.start)));
+        L3D_CUDA(ctx->pool.get(sizeof(int) * std::max<size_t>(n, 1), reinterpret_cast<void**>(&buf.tgt)));
+        L3D_CUDA(ctx->pool.get(sizeof(float4) * std::max<size_t>(n, 1), reinterpret_cast<void**>(&buf.dep)));
+        L3D_CUDA(cudaMemcpyAsync(buf.start, start.data(), sizeof(int) * (size_t(n_to) + 2), cudaMemcpyHostToDevice, ctx->stream));
+        if (n) {
+            L3D_CUDA(cudaMemcpyAsync(buf.tgt, tgt.data(), sizeof(int) * n, cudaMemcpyHostToDevice, ctx->stream));
+            L3D_CUDA(cudaMemcpyAsync(buf.dep, dep.data(), sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
+        }
+        L3D_CUDA(cudaStreamSynchronize(ctx->stream));          // the host vectors go away
+        Delivered dl; dl.from_view = from_view; dl.count = int(n); dl.max_group = max_group; dl.t_start = buf.start; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
+        dl.owner = int(ctx->deliver_bufs.size()); dl.slot = 0;
+        ctx->deliver_bufs.push_back(buf);
+        ctx->delivered[to_view].push_back(dl);
+        return 0;
+    });
+}
+
 int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
 {
     return guarded(ctx, [&]() -> int {
