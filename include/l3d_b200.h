@@ -182,6 +182,10 @@ int l3d_debug_set_pretest(l3d_ctx* ctx, int mode);
  * is cut in two and redone; if a single view alone exceeds the limit l3d_match_view fails with a message.  This call
  * lowers the limit so that a test can reach that path with a small scene (0 = back to the default). */
 int l3d_debug_set_candidate_limit(l3d_ctx* ctx, uint64_t limit);
+/* Tests only: the scoring kernels hold one maximum per (camera, hypothesis) in shared memory and therefore take 128
+ * hypotheses per block for up to 192 neighbours, 64 up to 384 and 32 up to 1600 (more are refused).  This call forces
+ * 32 or 64 (0 = automatic) so that a small scene exercises the blocks a view with hundreds of neighbours gets. */
+int l3d_debug_set_score_block(l3d_ctx* ctx, int hypotheses);
 /* Forget all delivered-but-unconsumed records and any plan (a new compute3Dmodel run, line3D.cc:356). */
 int l3d_reset_matching(l3d_ctx* ctx);
 
@@ -249,6 +253,10 @@ int l3d_affinity_edges(l3d_ctx* ctx, const float* median_depth, const float* hyp
  *      stored order (sorted by row, then column). */
 typedef struct { int32_t i, j; float w; } l3d_edge;
 int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3d_edge* out);
+/* Measurement: of the last l3d_diffuse call, [0] the duration in ms of one step kernel (the second of the ten
+ * iterations, CUDA events), [1] the algorithmic bytes one iteration moves -- per entry 16 bytes plus 32 bytes per
+ * lock-step pair, min(row length, column length) of them --, [2] the number of entries. */
+int l3d_diffuse_stats(l3d_ctx* ctx, double out[3]);
 
 /* ---- measurement helpers -------------------------------------------------------------- */
 /* Device time in ms of the kernels of the last l3d_match_view[_resident] call, by stage:

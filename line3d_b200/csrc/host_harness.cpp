@@ -77,7 +77,7 @@ void* l3dhost_open(const char* scene_path, const char* data_dir, int neighbors, 
     return s;
 }
 
-// compute3Dmodel + getResult.  stats_out: 32 doubles (see line3d_b200/host.py STAT_NAMES).
+// compute3Dmodel + getResult.  stats_out: 40 doubles (see line3d_b200/host.py STAT_NAMES).
 // Returns the number of 3-D lines or < 0.
 int l3dhost_compute(void* session, int diffusion, int measure_only, int flush_l2, int keep_debug, int stage_timing, double* wall_out, double* stats_out)
 {
@@ -96,11 +96,12 @@ int l3dhost_compute(void* session, int diffusion, int measure_only, int flush_l2
         if (wall_out) { wall_out[0] = s->t_add; wall_out[1] = t1 - t0; }
         if (stats_out) {
             L3D::L3DRunStats st = s->l3d->runStats();
-            const double v[32] = {double(st.pair_tests), double(st.candidates), double(st.raw_matches), double(st.scored_matches), double(st.filtered_matches),
+            const double v[40] = {double(st.pair_tests), double(st.candidates), double(st.raw_matches), double(st.scored_matches), double(st.filtered_matches),
                                   double(st.score_iters), double(st.score_iters_other_cam), double(st.hypotheses), double(st.affinity_pairs), double(st.edges),
                                   double(st.kernel_launches), st.t_neighbors, st.t_upload, st.t_matching, st.t_matching_device, st.t_hypotheses, st.t_affinity,
                                   st.t_diffusion, st.t_clustering, st.t_lines, st.t_total, st.t_stage[0], st.t_stage[1], st.t_stage[2], st.t_stage[3], st.t_stage[4],
-                                  double(st.h2d_bytes), double(st.d2h_bytes), st.t_matching_calls, st.t_k_pretest, st.t_k_exact, st.t_k_pretest2};
+                                  double(st.h2d_bytes), double(st.d2h_bytes), st.t_matching_calls, st.t_k_pretest, st.t_k_exact, st.t_k_pretest2,
+                                  st.rdd_step_ms, st.rdd_step_bytes, st.rdd_entries, 0.0, 0.0, 0.0, 0.0, 0.0};
             std::memcpy(stats_out, v, sizeof v);
         }
         std::list<L3D::L3DFinalLine3D> result;

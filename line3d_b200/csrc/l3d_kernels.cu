@@ -834,14 +834,14 @@ constexpr int SC_QCAP = 128;       // per-warp queue of gate survivors
 struct ScoreParams { float sigma_p, sigma_a; };
 
 // work items: (source segment, chunk of SC_T matches); order is irrelevant to the result
-__device__ __forceinline__ void b_score_items(const int* __restrict__ off, int n_cams, int n_src, int m_lo, int m_hi, int outside, int* __restrict__ counter, int2* __restrict__ items)
+__device__ __forceinline__ void b_score_items(const int* __restrict__ off, int n_cams, int n_src, int m_lo, int m_hi, int outside, int* __restrict__ counter, int2* __restrict__ items, int chunk)
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n_src) return;
     int m = off[(row + 1) * n_cams] - off[row * n_cams];
     const bool inside = m > m_lo && m <= m_hi;
     if (inside == (outside != 0)) m = 0;     // this list takes the segments inside (m_lo, m_hi], or those outside it
-    const int n = (m + SC_T - 1) / SC_T;
+    const int n = (m + chunk - 1) / chunk;
     if (n == 0) return;
     const int base = atomicAdd(counter, n);
     for (int k = 0; k < n; ++k) items[base + k] = make_int2(row, k);
@@ -851,7 +851,7 @@ __device__ __forceinline__ void b_score_items(const int* __restrict__ off, int n
 __device__ __forceinline__ void score_drain(int count, const unsigned* q, int lane, const float2* s_yd, int seg_start,
                                             const int4* __restrict__ m_ids, const float4* __restrict__ m_dep,
                                             V3 ray1, V3 ray2, V3 C, float spatial_k, const CamTable* __restrict__ cams,
-                                            const float4* __restrict__ segs, float sigma_p, float sigma_a, int* s_max, int stride = SC_T)
+                                            const float4* __restrict__ segs, float sigma_p, float sigma_a, int* s_max, int stride)
 {
     if (lane < count) {
         const unsigned e = q[lane];
@@ -875,7 +875,8 @@ __device__ __forceinline__ void b_score(const float4* __restrict__ segs, const C
                                                 const int2* __restrict__ items, const int* __restrict__ n_items,
                                                 ScoreParams sp, float* __restrict__ score)
 {
-    extern __shared__ int s_max[];                 // [n_cams][SC_T] best confidence per (camera, hypothesis), as int bits
+    extern __shared__ int s_max[];                 // [n_cams][H] best confidence per (camera, hypothesis), as int bits; H = blockDim.x hypotheses per block
+    const int H = blockDim.x;
     __shared__ float2 s_d[SC_TILE];
     __shared__ float2 s_yd[SC_T];
     __shared__ unsigned s_q[SC_WARPS][SC_QCAP];
@@ -884,14 +885,14 @@ __device__ __forceinline__ void b_score(const float4* __restrict__ segs, const C
     const int row = item.x;
     const int seg_start = off[row * n_cams], seg_end = off[(row + 1) * n_cams];
     const int M = seg_end - seg_start;
-    const int y0 = item.y * SC_T;
+    const int y0 = item.y * H;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int y = y0 + tid;
     const bool live = y < M;
     int my_cam = -1; float2 my_d = make_float2(0.f, 0.f);
     if (live) { my_cam = m_ids[seg_start + y].y; float4 d = m_dep[seg_start + y]; my_d = make_float2(d.x, d.y); }
     s_yd[tid] = my_d;
-    for (int c = 0; c < n_cams; ++c) s_max[c * SC_T + tid] = 0;
+    for (int c = 0; c < n_cams; ++c) s_max[c * H + tid] = 0;
     // per-segment invariants (cudawrapper.cu:638-645)
     const float4 sg = segs[src.seg_off + row_segment(src, row)];
     const V3 p1 = mk3(sg.x, sg.y, 1.0f), p2 = mk3(sg.z, sg.w, 1.0f);
@@ -910,7 +911,7 @@ __device__ __forceinline__ void b_score(const float4* __restrict__ segs, const C
     for (int t0 = 0; t0 < M; t0 += SC_TILE) {
         const int tn = min(SC_TILE, M - t0);
         __syncthreads();
-        for (int i = tid; i < tn; i += SC_T) { float4 d = m_dep[seg_start + t0 + i]; s_d[i] = make_float2(d.x, d.y); }
+        for (int i = tid; i < tn; i += H) { float4 d = m_dep[seg_start + t0 + i]; s_d[i] = make_float2(d.x, d.y); }
         __syncthreads();
         for (int i0 = 0; i0 < tn; i0 += 32) {
             unsigned hits = 0;
@@ -949,18 +950,18 @@ __device__ __forceinline__ void b_score(const float4* __restrict__ segs, const C
                 qn += tot;
                 __syncwarp();
                 while (qn >= 32) {
-                    score_drain(32, q + (qn - 32), lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, k, cams, segs, sp.sigma_p, sp.sigma_a, s_max);
+                    score_drain(32, q + (qn - 32), lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, k, cams, segs, sp.sigma_p, sp.sigma_a, s_max, H);
                     qn -= 32;
                     __syncwarp();
                 }
             }
         }
     }
-    if (qn > 0) score_drain(qn, q, lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, k, cams, segs, sp.sigma_p, sp.sigma_a, s_max);
+    if (qn > 0) score_drain(qn, q, lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, k, cams, segs, sp.sigma_p, sp.sigma_a, s_max, H);
     __syncwarp();
     // sum of the per-camera best confidences in camera order (cudawrapper.cu:677-687, 709)
     float total = 0.0f;
-    for (int c = 0; c < n_cams; ++c) total = xa(total, __int_as_float(s_max[c * SC_T + tid]));
+    for (int c = 0; c < n_cams; ++c) total = xa(total, __int_as_float(s_max[c * H + tid]));
     if (live) score[seg_start + y] = total;
 }
 
@@ -1055,7 +1056,8 @@ __device__ __forceinline__ void b_score_window(const float4* __restrict__ segs, 
                                                        const int2* __restrict__ items, const int* __restrict__ n_items,
                                                        ScoreParams sp, float* __restrict__ score)
 {
-    extern __shared__ int s_max[];                 // [n_cams][SC_T]
+    extern __shared__ int s_max[];                 // [n_cams][H], H = blockDim.x hypotheses per block
+    const int H = blockDim.x;
     __shared__ float2 s_yd[SC_T];
     __shared__ unsigned s_q[SC_WARPS][SC_QCAP];
     if (int(blockIdx.x) >= *n_items) return;
@@ -1063,14 +1065,14 @@ __device__ __forceinline__ void b_score_window(const float4* __restrict__ segs, 
     const int row = item.x;
     const int seg_start = off[row * n_cams], M = off[(row + 1) * n_cams] - seg_start;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int y = item.y * SC_T + tid;
+    const int y = item.y * H + tid;
     const bool live = y < M;
     // thread y takes the y-th match in BUCKET order: the lanes of a warp then hold neighbouring depths, their windows
     // overlap (coalesced loads) and are about equally long (little divergence in the scan below)
     int my_cam = -1, my_idx = 0; float2 my_d = make_float2(0.f, 0.f);
     if (live) { const unsigned pl = g_pl[seg_start + y]; my_cam = int(pl >> 20); my_idx = int(pl & 0xfffffu); my_d = make_float2(g_k[seg_start + y], g_d2[seg_start + y]); }
     s_yd[tid] = my_d;
-    for (int c = 0; c < n_cams; ++c) s_max[c * SC_T + tid] = 0;
+    for (int c = 0; c < n_cams; ++c) s_max[c * H + tid] = 0;
     const float4 sg = segs[src.seg_off + row_segment(src, row)];
     const V3 p1 = mk3(sg.x, sg.y, 1.0f), p2 = mk3(sg.z, sg.w, 1.0f);
     const V3 ray1 = xnormalize(xmat3(src.RtKinv, p1, false)), ray2 = xnormalize(xmat3(src.RtKinv, p2, false));
@@ -1106,17 +1108,17 @@ __device__ __forceinline__ void b_score_window(const float4* __restrict__ segs, 
             qn += __popc(m);
             __syncwarp();
             if (qn >= 32) {
-                score_drain(32, q + (qn - 32), lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, kk, cams, segs, sp.sigma_p, sp.sigma_a, s_max);
+                score_drain(32, q + (qn - 32), lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, kk, cams, segs, sp.sigma_p, sp.sigma_a, s_max, H);
                 qn -= 32;
                 __syncwarp();
             }
         }
     }
-    if (qn > 0) score_drain(qn, q, lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, kk, cams, segs, sp.sigma_p, sp.sigma_a, s_max);
+    if (qn > 0) score_drain(qn, q, lane, s_yd, seg_start, m_ids, m_dep, ray1, ray2, C, kk, cams, segs, sp.sigma_p, sp.sigma_a, s_max, H);
     __syncwarp();
     if (live) {        // sum of the per-camera best confidences in camera order (cudawrapper.cu:677-687, 709)
         float total = 0.0f;
-        for (int c = 0; c < n_cams; ++c) total = xa(total, __int_as_float(s_max[c * SC_T + tid]));
+        for (int c = 0; c < n_cams; ++c) total = xa(total, __int_as_float(s_max[c * H + tid]));
         score[seg_start + my_idx] = total;
     }
 }
@@ -1333,6 +1335,7 @@ struct VArgs {
     int* vres;
     // several GPUs on one scene (l3d_comm_init): this process holds the rows row_first + r * row_stride of the view
     int mr, n_seg_full;
+    int sc_h;          // hypotheses per block of the scoring kernels (their shared memory holds cameras x sc_h maxima)
 };
 
 // What one rank reports about one view of a group (all-gathered): its output records, its matches, its iteration counts.
@@ -1370,7 +1373,7 @@ __global__ void __launch_bounds__(BK_T) k_bucket_segments(const VArgs* __restric
 {
     L3D_VIEW(y);
     if (!va.scored || !va.windowed || int(blockIdx.x) >= va.n_src) return;
-    b_bucket_segments(va.off, va.n_cams, va.mids, va.mdep, va.sk, va.sd2, va.spl, va.boff, va.brange, va.m_hi, SC_T, va.nitems, va.items);
+    b_bucket_segments(va.off, va.n_cams, va.mids, va.mdep, va.sk, va.sd2, va.spl, va.boff, va.brange, va.m_hi, va.sc_h, va.nitems, va.items);
 }
 __global__ void __launch_bounds__(SC_T, 12) k_score_window(const VArgs* __restrict__ all, const float4* __restrict__ segs)
 {
@@ -1383,7 +1386,7 @@ __global__ void k_score_items(const VArgs* __restrict__ all)
 {
     L3D_VIEW(y);
     if (!va.scored || !va.quadratic) return;
-    b_score_items(va.off, va.n_cams, va.n_src, va.windowed ? 0 : 0x7fffffff, va.windowed ? va.m_hi : 0x7fffffff, 1, va.nitems + 1, va.items + va.max_items);
+    b_score_items(va.off, va.n_cams, va.n_src, va.windowed ? 0 : 0x7fffffff, va.windowed ? va.m_hi : 0x7fffffff, 1, va.nitems + 1, va.items + va.max_items, va.sc_h);
 }
 __global__ void __launch_bounds__(SC_T) k_score(const VArgs* __restrict__ all, const float4* __restrict__ segs)
 {
@@ -2050,6 +2053,7 @@ struct l3d_ctx {
     uint64_t batch_pairs = 24000000000ull;          // pair tests per batch of the announced schedule (l3d_plan_matching)
     uint64_t batch_override = 0;                    // l3d_debug_set_batch_pairs
     int pretest_mode = 0;                           // l3d_debug_set_pretest
+    int score_block = 0;                            // l3d_debug_set_score_block
     uint64_t cand_limit = 0x7fff0000ull;            // most candidates of one batch (32-bit candidate index); l3d_debug_set_candidate_limit
     float pa_kernel_ms[3] = {0.f, 0.f, 0.f};
     // views in flight: positions [fly_begin, fly_end) of `order` are on the GPU, as the groups [grp_begin, grp_end)
@@ -2070,6 +2074,8 @@ struct l3d_ctx {
     DBuf<l3d_pair> d_pairs; DBuf<float> d_aff, d_medians;
     HBuf<l3d_candidate> h_cands; DBuf<l3d_candidate> d_cands; DBuf<float> d_hscore, d_ew; DBuf<int> d_ecnt, d_eoff; DBuf<l3d_kept_edge> d_kept; HBuf<l3d_kept_edge> h_kept; DBuf<unsigned long long> d_ekeys; DBuf<unsigned> d_eorder; HBuf<unsigned> h_eorder;
     DBuf<unsigned char> d_flush; int flush_value = 0;
+    // diffusion: one device and one pinned buffer for all its arrays; the step kernel's duration and algorithmic bytes of the last call
+    DBuf<int> d_rdd; HBuf<int> h_rdd; float rdd_step_ms = 0.f; double rdd_step_bytes = 0.0; int rdd_nnz = 0;
     // timing
     cudaEvent_t ev[2] = {nullptr, nullptr};          // around the FP32 peak probe
     float last_ms[6] = {0, 0, 0, 0, 0, 0};
@@ -2327,7 +2333,9 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
 
     // ---- per view: tables, bounds, buffers, hand-over records, kernel arguments ------------------------------
     size_t zero_total = 0;
-    int mx_src = 1, mx_cams = 1, mx_items = 1, mx_cta = 1; long mx_warps = 1; size_t mx_M = 0, mx_smem = 0;
+    int mx_src = 1, mx_cams = 1, mx_items = 1, mx_cta = 1, mn_sc_h = SC_T; long mx_warps = 1; size_t mx_M = 0, mx_smem = 0;
+    for (int g = 0; g < count; ++g) mn_sc_h = std::min(mn_sc_h, gv[g].n_nb <= 192 ? 128 : (gv[g].n_nb <= 384 ? 64 : 32));
+    if (ctx->score_block) mn_sc_h = std::min(mn_sc_h, ctx->score_block);
     bool any_scored = false, any_window = false, any_quadratic = false, any_deliver = false;
     struct Z { size_t items, iters, best, hist, cursor, end; } z[VG_MAX];
     size_t hist_total = 0, window_need = MR_COUNTS_BYTES;
@@ -2389,10 +2397,13 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         const bool windowed = sv.spatial_k > 0.0f;
         const int SORT_MAX = 1 << 20;                                // the window kernel's index has 20 bits
         const bool quadratic = scored && (!windowed || seg_ub > size_t(SORT_MAX));
-        const int max_items = int(M_ub / SC_T) + n_src + 1;
+        // hypotheses per scoring block: the per-(camera, hypothesis) maxima must fit in shared memory whatever the number
+        // of neighbours (k = -1: every co-visible view)
+        const int sc_h = mn_sc_h;                        // (one launch covers the group: the same for all its views)
+        const int max_items = int(M_ub / size_t(sc_h)) + n_src + 1;
         const int n_cta = int(std::max<size_t>((M_ub + RM_T - 1) / RM_T, 1));
-        const size_t sm_bytes = size_t(n_nb) * SC_T * sizeof(int);
-        if (sm_bytes > 160 * 1024) { ctx->err = "l3d_match_view: too many neighbours for the scoring kernel's shared memory"; return 1; }
+        const size_t sm_bytes = size_t(n_nb) * size_t(sc_h) * sizeof(int);
+        if (sm_bytes > 200 * 1024) { ctx->err = "l3d_match_view: more than 1600 neighbours in one view"; return 1; }
         // buffers of this view
         L3D_CUDA(sl.d_cnt.ensure(size_t(n_src) * n_nb + 1)); L3D_CUDA(sl.d_off.ensure(size_t(n_src) * n_nb + 2));
         L3D_CUDA(sl.d_mids.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_mdep.ensure(std::max<size_t>(M_ub, 1))); L3D_CUDA(sl.d_score.ensure(std::max<size_t>(M_ub, 1)));
@@ -2432,6 +2443,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         va.raw_cnt = pa.d_pa_raw.p; va.cand_off = pa.d_pa_off.p; va.stage_col = pa.d_stage_col.p; va.stage_dep = pa.d_stage_dep.p; va.stage_ok = pa.d_stage_ok.p;
         va.cnt = sl.d_cnt.p; va.off = sl.d_off.p; va.mids = sl.d_mids.p; va.mdep = sl.d_mdep.p; va.score = sl.d_score.p;
         va.sk = sl.d_sk.p; va.sd2 = sl.d_sd2.p; va.spl = sl.d_spl.p; va.boff = sl.d_boff.p; va.brange = sl.d_brange.p; va.items = sl.d_items.p; va.max_items = max_items;
+        va.sc_h = sc_h;
         va.scored = scored ? 1 : 0; va.windowed = windowed ? 1 : 0; va.quadratic = quadratic ? 1 : 0; va.m_hi = SORT_MAX;
         va.cta_kept = sl.d_cta.p; va.n_cta = n_cta; va.Fout = sl.d_F.p; va.filtered = sl.d_filtered.p; va.dsamples = sl.d_dsamples.p;
         va.delivering = delivering ? 1 : 0; va.stride = stride; va.n_keys = n_keys; va.n_deliver = n_deliver;
@@ -2498,12 +2510,12 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[3], st));
     if (any_window) {
         L3D_CUDA(pdl_launch(k_bucket_segments, dim3(mx_src, G), dim3(BK_T), 0, st, A));
-        L3D_CUDA(pdl_launch(k_score_window, dim3(mx_items, G), dim3(SC_T), mx_smem, st, A, ctx->d_segs.p));
+        L3D_CUDA(pdl_launch(k_score_window, dim3(mx_items, G), dim3(mn_sc_h), mx_smem, st, A, ctx->d_segs.p));
         ctx->launches += 2;
     }
     if (any_quadratic) {
         L3D_CUDA(pdl_launch(k_score_items, dim3((mx_src + 255) / 256, G), dim3(256), 0, st, A));
-        L3D_CUDA(pdl_launch(k_score, dim3(mx_items, G), dim3(SC_T), mx_smem, st, A, ctx->d_segs.p));
+        L3D_CUDA(pdl_launch(k_score, dim3(mx_items, G), dim3(mn_sc_h), mx_smem, st, A, ctx->d_segs.p));
         ctx->launches += 2;
     }
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[4], st));
@@ -3069,7 +3081,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->h_filtered.release(); ctx->h_ints.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
     ctx->h_cands.release(); ctx->d_cands.release(); ctx->d_hscore.release(); ctx->d_ew.release(); ctx->d_ecnt.release(); ctx->d_eoff.release(); ctx->d_kept.release(); ctx->h_kept.release(); ctx->d_ekeys.release(); ctx->d_eorder.release(); ctx->h_eorder.release();
-    ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release();
+    ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release(); ctx->d_rdd.release(); ctx->h_rdd.release();
     for (int k = 0; k < 2; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -3313,6 +3325,13 @@ int l3d_debug_set_pretest(l3d_ctx* ctx, int mode)
     return 0;
 }
 
+int l3d_debug_set_score_block(l3d_ctx* ctx, int hypotheses)
+{
+    if (!ctx || !(hypotheses == 0 || hypotheses == 32 || hypotheses == 64 || hypotheses == 128)) return 1;
+    ctx->score_block = hypotheses;
+    return 0;
+}
+
 int l3d_debug_set_candidate_limit(l3d_ctx* ctx, uint64_t limit)
 {
     if (!ctx) return 1;
@@ -3457,54 +3476,100 @@ int l3d_affinity_edges(l3d_ctx* ctx, const float* median_depth, const float* hyp
 int l3d_diffuse(l3d_ctx* ctx, int n_nodes, size_t nnz, const l3d_edge* edges, l3d_edge* out)
 {
     if (!ctx) return 1;
-    if (nnz == 0 || n_nodes <= 0) return 0;
-    if (!edges || !out) { ctx->err = "l3d_diffuse: null argument"; return 1; }
-    L3D_CUDA(cudaSetDevice(ctx->device));
-    cudaStream_t st = ctx->stream;
-    const int N = int(nnz);
-    for (int k = 0; k < N; ++k)
-        if (edges[k].i < 0 || edges[k].i >= n_nodes || edges[k].j < 0 || edges[k].j >= n_nodes) { ctx->err = "l3d_diffuse: node id out of range"; return 1; }
-    // W column-sorted (sparsematrix.cc:81-85), P row-sorted (sparsematrix.cc:158-161); the comparators order by the
-    // integer ids only, stable, so equal keys (none for a valid input) keep their list order
-    std::vector<int> wi(N), pi(N);
-    for (int k = 0; k < N; ++k) wi[k] = k;
-    std::stable_sort(wi.begin(), wi.end(), [&](int a, int b) { return edges[a].j < edges[b].j || (edges[a].j == edges[b].j && edges[a].i < edges[b].i); });
-    for (int k = 0; k < N; ++k) pi[k] = k;                                       // P is built from W's stored order
-    std::stable_sort(pi.begin(), pi.end(), [&](int a, int b) { const l3d_edge& x = edges[wi[a]]; const l3d_edge& y = edges[wi[b]]; return x.i < y.i || (x.i == y.i && x.j < y.j); });
-    std::vector<int> prow(N), pcol(N), wcol(N), rstart(n_nodes, -1), cstart(n_nodes, -1), tpos(N, -1);
-    std::vector<float> pval(N), wval(N);
-    for (int k = 0; k < N; ++k) { const l3d_edge& e = edges[wi[k]]; wcol[k] = e.j; wval[k] = e.w; if (cstart[e.j] < 0) cstart[e.j] = k; }
-    for (int k = 0; k < N; ++k) { const l3d_edge& e = edges[wi[pi[k]]]; prow[k] = e.i; pcol[k] = e.j; pval[k] = e.w; if (rstart[e.i] < 0) rstart[e.i] = k; }
-    for (int y = 0; y < N; ++y) {                                               // cudawrapper.cu:809-827: first entry (r, c) of row r = col_y with col == row_y
-        const int r = pcol[y], c = prow[y];
-        for (int s = rstart[r]; s >= 0 && s < N && prow[s] == r; ++s) if (pcol[s] == c) { tpos[y] = s; break; }
-    }
-    int *d_prow, *d_pcol, *d_wcol, *d_rstart, *d_cstart, *d_tpos; float *d_pa, *d_pb, *d_wval;
-    L3D_CUDA(cudaMallocAsync(&d_prow, sizeof(int) * N, st)); L3D_CUDA(cudaMallocAsync(&d_pcol, sizeof(int) * N, st)); L3D_CUDA(cudaMallocAsync(&d_wcol, sizeof(int) * N, st));
-    L3D_CUDA(cudaMallocAsync(&d_tpos, sizeof(int) * N, st)); L3D_CUDA(cudaMallocAsync(&d_rstart, sizeof(int) * n_nodes, st)); L3D_CUDA(cudaMallocAsync(&d_cstart, sizeof(int) * n_nodes, st));
-    L3D_CUDA(cudaMallocAsync(&d_pa, sizeof(float) * N, st)); L3D_CUDA(cudaMallocAsync(&d_pb, sizeof(float) * N, st)); L3D_CUDA(cudaMallocAsync(&d_wval, sizeof(float) * N, st));
-    L3D_CUDA(cudaMemcpyAsync(d_prow, prow.data(), sizeof(int) * N, cudaMemcpyHostToDevice, st)); L3D_CUDA(cudaMemcpyAsync(d_pcol, pcol.data(), sizeof(int) * N, cudaMemcpyHostToDevice, st));
-    L3D_CUDA(cudaMemcpyAsync(d_wcol, wcol.data(), sizeof(int) * N, cudaMemcpyHostToDevice, st)); L3D_CUDA(cudaMemcpyAsync(d_tpos, tpos.data(), sizeof(int) * N, cudaMemcpyHostToDevice, st));
-    L3D_CUDA(cudaMemcpyAsync(d_rstart, rstart.data(), sizeof(int) * n_nodes, cudaMemcpyHostToDevice, st)); L3D_CUDA(cudaMemcpyAsync(d_cstart, cstart.data(), sizeof(int) * n_nodes, cudaMemcpyHostToDevice, st));
-    L3D_CUDA(cudaMemcpyAsync(d_pa, pval.data(), sizeof(float) * N, cudaMemcpyHostToDevice, st)); L3D_CUDA(cudaMemcpyAsync(d_pb, pval.data(), sizeof(float) * N, cudaMemcpyHostToDevice, st));
-    L3D_CUDA(cudaMemcpyAsync(d_wval, wval.data(), sizeof(float) * N, cudaMemcpyHostToDevice, st));
-    const int rb = (n_nodes + 255) / 256, eb = (N + 255) / 256;
-    k_rdd_normalise<<<rb, 256, 0, st>>>(d_prow, d_pa, d_rstart, n_nodes, N);
-    ctx->launches += 1;
-    float* P = d_pa; float* Pn = d_pb;
-    for (int it = 0; it < 10; ++it) {                                           // L3D_RDD_MAX_ITER, cudawrapper.h:35
-        k_rdd_step<<<eb, 256, 0, st>>>(d_prow, d_pcol, P, d_wcol, d_wval, d_rstart, d_cstart, d_tpos, Pn, N);
-        std::swap(P, Pn);
+    return guarded(ctx, [&]() -> int {
+        if (nnz == 0 || n_nodes <= 0) return 0;
+        if (!edges || !out) { ctx->err = "l3d_diffuse: null argument"; return 1; }
+        if (nnz > size_t(0x7ffffff0)) { ctx->err = "l3d_diffuse: more than 2^31 entries"; return 1; }
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        cudaStream_t st = ctx->stream;
+        const int N = int(nnz);
+        for (int k = 0; k < N; ++k)
+            if (edges[k].i < 0 || edges[k].i >= n_nodes || edges[k].j < 0 || edges[k].j >= n_nodes) { ctx->err = "l3d_diffuse: node id out of range"; return 1; }
+        // W column-sorted (sparsematrix.cc:81-85), P row-sorted (sparsematrix.cc:158-161); the comparators order by the
+        // integer ids only, stable, so equal keys (none for a valid input) keep their list order.  Two stable counting
+        // passes per order (secondary key first) instead of comparison sorts: O(nnz + nodes).
+        auto order_by = [&](const std::vector<int>& in, bool by_col_then_row, std::vector<int>& outv) {
+            std::vector<int> tmp(N), cnt(size_t(n_nodes) + 1);
+            for (int pass = 0; pass < 2; ++pass) {
+                const bool use_i = by_col_then_row ? (pass == 0) : (pass == 1);          // secondary key first
+                const std::vector<int>& src = pass == 0 ? in : tmp;
+                std::vector<int>& dst = pass == 0 ? tmp : outv;
+                std::fill(cnt.begin(), cnt.end(), 0);
+                for (int k = 0; k < N; ++k) { const l3d_edge& e = edges[src[k]]; ++cnt[size_t(use_i ? e.i : e.j) + 1]; }
+                for (int d = 0; d < n_nodes; ++d) cnt[size_t(d) + 1] += cnt[d];
+                for (int k = 0; k < N; ++k) { const l3d_edge& e = edges[src[k]]; dst[cnt[use_i ? e.i : e.j]++] = src[k]; }
+            }
+        };
+        std::vector<int> ident(N), wi(N), pi(N);
+        for (int k = 0; k < N; ++k) ident[k] = k;
+        order_by(ident, true, wi);                                                  // W: by (col, row)
+        order_by(wi, false, pi);                                                    // P is built from W's stored order: by (row, col); pi holds input indices
+        // pinned staging, one buffer: prow pcol wcol tpos (N ints each), rstart cstart (n_nodes each), pval wval (N floats each)
+        const size_t n_int = size_t(4) * N + size_t(2) * n_nodes, n_all = n_int + size_t(2) * N;
+        L3D_CUDA(ctx->h_rdd.ensure(n_all)); L3D_CUDA(ctx->d_rdd.ensure(n_all + size_t(N)));
+        int* prow = ctx->h_rdd.p; int* pcol = prow + N; int* wcol = pcol + N; int* tpos = wcol + N; int* rstart = tpos + N; int* cstart = rstart + n_nodes;
+        float* pval = reinterpret_cast<float*>(cstart + n_nodes); float* wval = pval + N;
+        for (int d = 0; d < n_nodes; ++d) { rstart[d] = -1; cstart[d] = -1; }
+        for (int k = 0; k < N; ++k) { const l3d_edge& e = edges[wi[k]]; wcol[k] = e.j; wval[k] = e.w; if (cstart[e.j] < 0) cstart[e.j] = k; }
+        for (int k = 0; k < N; ++k) { const l3d_edge& e = edges[pi[k]]; prow[k] = e.i; pcol[k] = e.j; pval[k] = e.w; if (rstart[e.i] < 0) rstart[e.i] = k; }
+        // cudawrapper.cu:809-827: first entry (r, c) of row r = col_y with col == row_y (the transposed entry's place);
+        // the rows are sorted by column, so it is found by bisection; and the algorithmic traffic of one iteration:
+        // per entry the lock-step walk reads min(row length, column length) pairs of 16 bytes from each operand
+        double walk = 0.0;
+        {
+            std::vector<int> rlen(size_t(n_nodes), 0), clen(size_t(n_nodes), 0);
+            for (int k = 0; k < N; ++k) { ++rlen[prow[k]]; ++clen[wcol[k]]; }
+            const size_t nt = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), 16));
+            std::vector<double> part(nt, 0.0);
+            auto work = [&](size_t t) {
+                const int y0 = int(size_t(N) * t / nt), y1 = int(size_t(N) * (t + 1) / nt);
+                for (int y = y0; y < y1; ++y) {
+                    const int r = pcol[y], c = prow[y];
+                    int lo = rstart[r], hi = lo < 0 ? -1 : lo + rlen[r];
+                    int found = -1;
+                    while (lo >= 0 && lo < hi) { const int mid = (lo + hi) >> 1; if (pcol[mid] < c) lo = mid + 1; else hi = mid; }
+                    if (lo >= 0 && lo < rstart[r] + rlen[r] && prow[lo] == r && pcol[lo] == c) found = lo;
+                    tpos[y] = found;
+                    part[t] += double(std::min(rlen[r], clen[c]));
+                }
+            };
+            std::vector<std::thread> pool;
+            for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t);
+            work(0);
+            for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
+            for (size_t t = 0; t < nt; ++t) walk += part[t];
+        }
+        int* d_prow = ctx->d_rdd.p; int* d_pcol = d_prow + N; int* d_wcol = d_pcol + N; int* d_tpos = d_wcol + N; int* d_rstart = d_tpos + N; int* d_cstart = d_rstart + n_nodes;
+        float* d_pa = reinterpret_cast<float*>(d_cstart + n_nodes); float* d_wval = d_pa + N; float* d_pb = d_wval + N;
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_rdd.p, ctx->h_rdd.p, sizeof(int) * n_all, cudaMemcpyHostToDevice, st));
+        L3D_CUDA(cudaMemcpyAsync(d_pb, d_pa, sizeof(float) * N, cudaMemcpyDeviceToDevice, st));
+        const int rb = (n_nodes + 255) / 256, eb = (N + 255) / 256;
+        k_rdd_normalise<<<rb, 256, 0, st>>>(d_prow, d_pa, d_rstart, n_nodes, N);
         ctx->launches += 1;
-        if (it < 9) { k_rdd_normalise<<<rb, 256, 0, st>>>(d_prow, P, d_rstart, n_nodes, N); ctx->launches += 1; }
-    }
-    L3D_CUDA(cudaGetLastError());
-    L3D_CUDA(cudaMemcpyAsync(pval.data(), P, sizeof(float) * N, cudaMemcpyDeviceToHost, st));
-    L3D_CUDA(cudaStreamSynchronize(st));
-    for (int k = 0; k < N; ++k) { out[k].i = prow[k]; out[k].j = pcol[k]; out[k].w = pval[k]; }
-    cudaFreeAsync(d_prow, st); cudaFreeAsync(d_pcol, st); cudaFreeAsync(d_wcol, st); cudaFreeAsync(d_tpos, st); cudaFreeAsync(d_rstart, st);
-    cudaFreeAsync(d_cstart, st); cudaFreeAsync(d_pa, st); cudaFreeAsync(d_pb, st); cudaFreeAsync(d_wval, st);
-    L3D_CUDA(cudaStreamSynchronize(st));
+        float* P = d_pa; float* Pn = d_pb;
+        float step_ms = 0.f;
+        for (int it = 0; it < 10; ++it) {                                           // L3D_RDD_MAX_ITER, cudawrapper.h:35
+            if (it == 1) L3D_CUDA(cudaEventRecord(ctx->ev[0], st));                 // the step kernel's own duration: iteration 2 (warm)
+            k_rdd_step<<<eb, 256, 0, st>>>(d_prow, d_pcol, P, d_wcol, d_wval, d_rstart, d_cstart, d_tpos, Pn, N);
+            if (it == 1) L3D_CUDA(cudaEventRecord(ctx->ev[1], st));
+            std::swap(P, Pn);
+            ctx->launches += 1;
+            if (it < 9) { k_rdd_normalise<<<rb, 256, 0, st>>>(d_prow, P, d_rstart, n_nodes, N); ctx->launches += 1; }
+        }
+        L3D_CUDA(cudaGetLastError());
+        L3D_CUDA(cudaMemcpyAsync(pval, P, sizeof(float) * N, cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaStreamSynchronize(st));
+        cudaEventElapsedTime(&step_ms, ctx->ev[0], ctx->ev[1]);
+        ctx->rdd_step_ms = step_ms; ctx->rdd_step_bytes = 32.0 * walk + 16.0 * double(N); ctx->rdd_nnz = N;
+        for (int k = 0; k < N; ++k) { out[k].i = prow[k]; out[k].j = pcol[k]; out[k].w = pval[k]; }
+        return 0;
+    });
+}
+
+int l3d_diffuse_stats(l3d_ctx* ctx, double out[3])
+{
+    if (!ctx || !out) return 1;
+    out[0] = ctx->rdd_step_ms; out[1] = ctx->rdd_step_bytes; out[2] = double(ctx->rdd_nnz);
     return 0;
 }
 

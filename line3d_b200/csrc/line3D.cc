@@ -842,25 +842,39 @@ struct Line3D::Impl
             const double td = now_s();
             std::vector<l3d_edge> in(A.size()), out(A.size());
             for (size_t k = 0; k < A.size(); ++k) { in[k].i = A[k].i; in[k].j = A[k].j; in[k].w = A[k].w; }
-            {   // W as the reference stores it (column-sorted) for the dump
+            if (keep_debug) {   // W as the reference stores it (column-sorted) for the dump
                 std::vector<l3d_edge> w(in);
                 std::stable_sort(w.begin(), w.end(), [](const l3d_edge& a, const l3d_edge& b) { return a.j < b.j || (a.j == b.j && a.i < b.i); });
-                if (keep_debug) for (size_t k = 0; k < w.size(); ++k) { edges_pre.push_back(w[k].i); edges_pre.push_back(w[k].j); edges_pre.push_back(w[k].w); }
+                for (size_t k = 0; k < w.size(); ++k) { edges_pre.push_back(w[k].i); edges_pre.push_back(w[k].j); edges_pre.push_back(w[k].w); }
             }
             if (l3d_diffuse(ctx, n_nodes, in.size(), in.data(), out.data())) fail("l3d_diffuse");
-            // symmetrise with min(w_ij, w_ji) in stored order, then (i, j) order (line3D.cc:1267-1299)
-            std::map<int, std::map<int, float> > entries;
-            for (size_t k = 0; k < out.size(); ++k) {
-                const int s1 = out[k].i, s2 = out[k].j; float w12 = out[k].w, w21 = w12;
-                std::map<int, float>& row2 = entries[s2];
-                std::map<int, float>::iterator f = row2.find(s1);
-                if (f != row2.end()) w21 = f->second;
-                const float w = fminf(w12, w21);
-                entries[s1][s2] = w; entries[s2][s1] = w;
+            { double ds[3]; if (!l3d_diffuse_stats(ctx, ds)) { stats.rdd_step_ms = ds[0]; stats.rdd_step_bytes = ds[1]; stats.rdd_entries = ds[2]; } }
+            // symmetrise with min(w_ij, w_ji), then (i, j) order (line3D.cc:1267-1299).  The reference walks the result in
+            // stored order (sorted by row, then column) and keeps, per unordered pair, the smaller of the two directions
+            // in a map of maps, which it then reads out in (i, j) order -- the stored order again.  Here: every entry
+            // looks its transposed entry up by bisection in that entry's row.
+            {
+                const size_t n = out.size();
+                std::vector<size_t> row_begin(size_t(n_nodes) + 1, 0);
+                for (size_t k = 0; k < n; ++k) ++row_begin[size_t(out[k].i) + 1];
+                for (int r = 0; r < n_nodes; ++r) row_begin[size_t(r) + 1] += row_begin[r];
+                A.resize(n);
+                auto work = [&](size_t t0, size_t nt) {
+                    for (size_t k = n * t0 / nt; k < n * (t0 + 1) / nt; ++k) {
+                        const int s1 = out[k].i, s2 = out[k].j;
+                        size_t lo = row_begin[s2], hi = row_begin[size_t(s2) + 1];
+                        while (lo < hi) { const size_t mid = (lo + hi) >> 1; if (out[mid].j < s1) lo = mid + 1; else hi = mid; }
+                        float w = out[k].w;
+                        if (lo < row_begin[size_t(s2) + 1] && out[lo].j == s1) w = fminf(w, out[lo].w);
+                        Edge e = {s1, s2, w}; A[k] = e;
+                    }
+                };
+                const size_t nt = std::max<size_t>(1, host_threads());
+                std::vector<std::thread> pool;
+                for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t, nt);
+                work(0, nt);
+                for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
             }
-            A.clear();
-            for (std::map<int, std::map<int, float> >::iterator a = entries.begin(); a != entries.end(); ++a)
-                for (std::map<int, float>::iterator b = a->second.begin(); b != a->second.end(); ++b) { Edge e = {a->first, b->first, b->second}; A.push_back(e); }
             stats.t_diffusion += now_s() - td;
         }
         stats.edges = A.size();

@@ -84,6 +84,7 @@ namespace L3D
         unsigned long long h2d_bytes, d2h_bytes;
         double t_k_pretest, t_k_exact;   // device seconds of the level-1 pre-test and exact-test kernels alone
         double t_k_pretest2;             // ... and of the level-2 pre-test kernel
+        double rdd_step_ms, rdd_step_bytes, rdd_entries;   // diffusion: one step kernel's duration, its algorithmic bytes, the matrix entries
         double t_matching_calls;   // part of t_matching spent inside l3d_match_view (the rest is the host's bookkeeping between the calls)
     };
 

@@ -22,7 +22,7 @@ DEFAULTS = dict(neighbors=10, unc_upper=5.0, unc_lower=1.0, sigma_p=3.5, sigma_a
 STAT_NAMES = ["pair_tests", "candidates", "raw_matches", "scored_matches", "filtered_matches", "score_iters", "score_iters_other_cam",
               "hypotheses", "affinity_pairs", "edges", "kernel_launches", "t_neighbors", "t_upload", "t_matching", "t_matching_device",
               "t_hypotheses", "t_affinity", "t_diffusion", "t_clustering", "t_lines", "t_total", "t_pretest", "t_exact", "t_assemble",
-              "t_score", "t_reduce", "h2d_bytes", "d2h_bytes", "t_matching_calls", "t_k_pretest", "t_k_exact", "t_k_pretest2"]
+              "t_score", "t_reduce", "h2d_bytes", "d2h_bytes", "t_matching_calls", "t_k_pretest", "t_k_exact", "t_k_pretest2", "rdd_step_ms", "rdd_step_bytes", "rdd_entries", "_r1", "_r2", "_r3", "_r4", "_r5"]
 
 _lib = None
 
@@ -67,7 +67,7 @@ class Session:
         compute3Dmodel otherwise re-normalises the normalised scene, as the reference does)."""
         if fresh:
             lib().l3dhost_reset_geometry(self._h)
-        wall = (C.c_double * 2)(); st = (C.c_double * 32)()
+        wall = (C.c_double * 2)(); st = (C.c_double * 40)()
         dif = self.params["diffusion"] if diffusion is None else diffusion
         n = lib().l3dhost_compute(self._h, int(bool(dif)), int(measure_only), int(flush_l2), int(keep_debug), int(stage_timing), wall, st)
         if n < 0:

@@ -174,3 +174,38 @@ def test_c2_full_size_properties():
     assert hit.sum() > 1000                                            # ... that this earlier view kept as well
     a_rows = f[back[hit]]; b_rows = f[srt[pos[hit]]]
     assert np.array_equal(a_rows[:, 4:8], b_rows[:, [6, 7, 4, 5]])
+
+
+@pytest.mark.parametrize("hyp", [32, 64])
+def test_small_scoring_blocks(small_scene, hyp):
+    """The scoring kernels keep one maximum per (camera, hypothesis) in shared memory, so a view with hundreds of
+    neighbours (k = -1) gets fewer hypotheses per block: 128 up to 192 cameras, 64 up to 384, 32 up to 1600 (the first
+    version failed above 320).  Forced here on a small scene, with and without the 3-D gate's window kernel: records,
+    scores and medians must equal the oracle's."""
+    from line3d_b200 import capi, scenes
+    sc = scenes.read_scene(small_scene)
+    dm = util.oracle_dump(small_scene, neighbors=-1, collinearity=False, threads=8)
+    ids, views, F, vn = util.tables_from_dump(dm, sc)
+    ctx = capi.Context(0)
+    ctx.debug_set_score_block(hyp)
+    for gate in (True, False):
+        vv = [dict(v) for v in views]
+        if not gate:
+            for v in vv:
+                v["spatial_k"] = np.float32(0.0)             # no 3-D gate: the quadratic kernel (k_score)
+        got = util.run_matching(ctx, ids, vv, F, vn, plan=True)
+        if gate:
+            rows = np.concatenate([util.filtered_as_rows(v, got[v]) for v in sorted(got)])
+            key = lambda a: np.lexsort((a[:, 3], a[:, 2], a[:, 1], a[:, 0]))
+            ref = dm["filtered_matches"]
+            assert ref.shape[0] > 1000 and rows.shape == ref.shape and np.array_equal(rows[key(rows)], ref[key(ref)])
+            for r, m in zip(dm["match_log"], dm["match_median"].ravel()):
+                assert got[int(r[0])]["median_depth"] == float(m)
+        else:
+            ctx.debug_set_score_block(0)
+            base = util.run_matching(ctx, ids, vv, F, vn, plan=True)      # the same without the gate at 128 per block
+            ctx.debug_set_score_block(hyp)
+            for v in base:
+                assert np.array_equal(base[v]["filtered"], got[v]["filtered"]) and base[v]["median_depth"] == got[v]["median_depth"]
+    ctx.debug_set_score_block(0)
+    ctx.close()
