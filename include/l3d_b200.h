@@ -190,19 +190,22 @@ int l3d_debug_set_score_block(l3d_ctx* ctx, int hypotheses);
 int l3d_reset_matching(l3d_ctx* ctx);
 
 /* ---- several GPUs on ONE scene.  No counterpart in the reference (single implicit device, cudawrapper.cu).
- *      One process and one context per GPU.  After l3d_comm_init the contexts of the `world` ranks work on the same
- *      scene together: the segments of every view are dealt out to the ranks in turn (segment s of a view belongs to
- *      rank s mod world), each rank pair-tests, assembles and scores its rows of every view, and the views are still
- *      processed in the reference's order of dependence.  What travels over NCCL (NVLink): the segment table from rank 0
- *      at l3d_set_views (a rank other than 0 may pass segments = NULL); per group of independent views the ranks'
- *      record counts, the depth samples for the median (min-all-reduce), the sizes of the hand-over groups
- *      (sum-all-reduce) and the output records themselves (all-gather), from which every rank builds the hand-over
- *      lists for its rows of later views.
+ *      One process and one context per GPU of one node.  After l3d_comm_init the contexts of the `world` ranks work
+ *      on the same scene together: the segments of every view are dealt out to the ranks in turn (segment s of a view
+ *      belongs to rank s mod world), each rank pair-tests, assembles and scores its rows of every view, and the views
+ *      are still processed in the reference's order of dependence.  What travels between the GPUs: over NCCL (from the
+ *      process's libnccl.so.2, opened at run time) the segment table from rank 0 at l3d_set_views (a rank other than 0
+ *      may pass segments = NULL), the raw-match totals per batch of pair tests (the bounds all ranks size their buffers
+ *      with) and the handshake when the exchange windows are (re)allocated; per group of independent views, by stores
+ *      into CUDA-IPC-mapped windows of the other ranks (NVLink) and an arrival flag per rank, every output record that
+ *      a later view consumes (to the rank that holds the target segment), the depth samples for the median and the
+ *      ranks' counts -- and all output records to the rank(s) that hand them to the host.
  *      Every rank must make the same calls in the same order with the same arguments (l3d_set_views, l3d_plan_matching,
- *      l3d_match_view ...); a rank that fails leaves the others waiting.  Results: n_filtered, n_scored, n_raw, n_delivered,
- *      median_depth and the score iteration counters describe the whole view on every rank; pair_tests and n_candidates
- *      count this rank's rows; `filtered` holds the records of ALL ranks (grouped by rank, each group in (src, cam, tgt)
- *      order) on rank result_root, or on every rank if result_root < 0, and is NULL elsewhere.
+ *      l3d_match_view ...); a rank that fails leaves the others waiting (ten seconds inside a group, then they fail too).
+ *      Results: n_filtered, median_depth and `filtered` describe the whole view -- `filtered` holds the records of ALL
+ *      ranks (grouped by rank, each group in (src, cam, tgt) order) on rank result_root, or on every rank if
+ *      result_root < 0, and is NULL elsewhere; pair_tests, n_candidates, n_raw, n_delivered, n_scored and the score
+ *      iteration counters count this rank's rows (their sums over the ranks are the single-GPU values).
  *      l3d_comm_unique_id: rank 0 obtains an id (ncclGetUniqueId) and hands it to the other ranks by any means. */
 #define L3D_COMM_ID_BYTES 128
 int l3d_comm_unique_id(void* id /* L3D_COMM_ID_BYTES bytes */);
@@ -288,8 +291,13 @@ int l3d_measure_fp32x2_peak(l3d_ctx* ctx, float* tflops);
 int l3d_debug_math(l3d_ctx* ctx, int which, int n, const float* in, float* out);
 /* Host seconds this context has spent since the last call of this function [0] putting groups of views on the GPU,
  * [1] waiting for their results, [2] collecting them; [3] = number of groups.  For finding out whether the host or
- * the GPU limits the per-view chain. */
-int l3d_debug_host_times(l3d_ctx* ctx, double out[4]);
+ * the GPU limits the per-view chain.  [4] waiting for the helper thread's pair tests of the next batch, [5] pair tests
+ * run in the foreground (first batch), [6] the per-batch totals over the ranks (several GPUs); [7] unused. */
+int l3d_debug_host_times(l3d_ctx* ctx, double out[8]);
+/* With on != 0 and l3d_set_stage_timing, a CUDA event follows every kernel of the per-view chain; out (may be NULL)
+ * receives the device ms since the last call, summed over the groups: [1] gather_counts [2] scan [3] fill [4] bucket
+ * [5] score [6] reduce [7] filter [8] push [9] all-reduce [10] hist [11] scan [12] scatter [13] finish [14] gather. */
+int l3d_debug_chain_times(l3d_ctx* ctx, int on, double out[24]);
 /* Number of kernels this library has launched on the context since creation. */
 uint64_t l3d_kernel_launches(const l3d_ctx* ctx);
 

@@ -93,7 +93,7 @@ def lib():
 
 
 EXPORTS = ["l3d_create", "l3d_destroy", "l3d_last_error", "l3d_collinearity", "l3d_collinearity_prealloc", "l3d_set_views", "l3d_match_view",
-           "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_debug_set_batch_pairs", "l3d_comm_unique_id", "l3d_comm_init", "l3d_comm_destroy", "l3d_debug_host_times", "l3d_debug_set_score_block", "l3d_diffuse_stats", "l3d_deliver", "l3d_candidate_buffer", "l3d_affinity_edges", "l3d_debug_set_pretest", "l3d_debug_set_candidate_limit", "l3d_measure_fp32x2_peak", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
+           "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_debug_set_batch_pairs", "l3d_comm_unique_id", "l3d_comm_init", "l3d_comm_destroy", "l3d_debug_host_times", "l3d_debug_chain_times", "l3d_debug_set_score_block", "l3d_diffuse_stats", "l3d_deliver", "l3d_candidate_buffer", "l3d_affinity_edges", "l3d_debug_set_pretest", "l3d_debug_set_candidate_limit", "l3d_measure_fp32x2_peak", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
            "l3d_last_timings", "l3d_last_kernel_timings", "l3d_set_stage_timing", "l3d_mark", "l3d_marks_elapsed", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math", "l3d_flush_l2"]
 
 

@@ -52,6 +52,7 @@ struct NcclApi {
     decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
     decltype(&ncclCommInitRank) CommInitRank = nullptr;
     decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclCommAbort) CommAbort = nullptr;
     decltype(&ncclAllGather) AllGather = nullptr;
     decltype(&ncclAllReduce) AllReduce = nullptr;
     decltype(&ncclBroadcast) Broadcast = nullptr;
@@ -69,7 +70,7 @@ NcclApi* nccl_api(std::string* err)
         if (!api.lib) why = std::string("cannot open libnccl.so.2: ") + dlerror();
         else {
 #define L3D_NCCL_SYM(name) api.name = reinterpret_cast<decltype(api.name)>(dlsym(api.lib, "nccl" #name)); if (!api.name) why = "libnccl has no nccl" #name;
-            L3D_NCCL_SYM(GetUniqueId) L3D_NCCL_SYM(CommInitRank) L3D_NCCL_SYM(CommDestroy) L3D_NCCL_SYM(AllGather) L3D_NCCL_SYM(AllReduce)
+            L3D_NCCL_SYM(GetUniqueId) L3D_NCCL_SYM(CommInitRank) L3D_NCCL_SYM(CommDestroy) L3D_NCCL_SYM(CommAbort) L3D_NCCL_SYM(AllGather) L3D_NCCL_SYM(AllReduce)
             L3D_NCCL_SYM(Broadcast) L3D_NCCL_SYM(GroupStart) L3D_NCCL_SYM(GroupEnd) L3D_NCCL_SYM(GetErrorString)
 #undef L3D_NCCL_SYM
         }
@@ -1338,16 +1339,19 @@ struct VArgs {
     int sc_h;          // hypotheses per block of the scoring kernels (their shared memory holds cameras x sc_h maxima)
 };
 
+constexpr int VG_MAX = 32;         // most views in one group (l3d_ctx::group_views is how many are used)
 // What one rank reports about one view of a group (all-gathered): its output records, its matches, its iteration counts.
-struct RankRec { int F, M; unsigned long long iters_all, iters_same; int pad[2]; };
+struct RankRec { int F, M; unsigned long long iters_all, iters_same; int routed; int pad; };      // routed: records sent to the rank that holds this table
 constexpr int MR_MAX_RANKS = 16;
 // The group's window of every rank, as mapped into this process (CUDA IPC): [rank] -> base of that rank's window.
-// A window holds, for one group of views: the ranks' records of each view (RankRec[rank][8]), the depth samples of
+// A window holds, for one group of views: the ranks' records of each view (RankRec[rank][VG_MAX]), the depth samples of
 // every segment of each view, and the output records of each view -- one region per rank, sized by the bound all ranks
 // share, so that a rank knows where its records go in everybody's window without knowing the other ranks' counts.
 struct MrPeers { unsigned char* base[MR_MAX_RANKS]; };
-struct MrLayout { long long samp_off[8], rec_off[8], cap[8]; };      // per view of the group: bytes, bytes, records per rank
-constexpr size_t MR_COUNTS_BYTES = size_t(MR_MAX_RANKS) * 8 * 32;      // the RankRec table at the start of a window
+struct MrLayout { long long samp_off[VG_MAX], rec_off[VG_MAX], full_off[VG_MAX], cap[VG_MAX]; };      // per view of the group: bytes, bytes, bytes, records per rank
+constexpr size_t MR_COUNTS_BYTES = size_t(MR_MAX_RANKS) * VG_MAX * 32;      // the RankRec table at the start of a window ...
+constexpr size_t MR_FLAGS_OFF = MR_COUNTS_BYTES;                       // ... then one arrival flag per sending rank (unsigned) ...
+constexpr size_t MR_HEADER_BYTES = MR_COUNTS_BYTES + 256;             // ... and the views' regions
 #define L3D_VIEW(dim) L3D_PDL_PROLOGUE(); const VArgs& va = all[blockIdx.dim]
 
 __global__ void k_gather_counts(const VArgs* __restrict__ all)
@@ -1428,46 +1432,107 @@ __global__ void __launch_bounds__(MS_T) k_finish_view(const VArgs* __restrict__ 
 // s belongs to rank s mod ranks), so each rank pair-tests, assembles and scores its rows of every view, and the views
 // are still processed level by level.  What a later view needs from an earlier one -- the reversed records, grouped by
 // ITS segments -- is put together from all ranks' output records of the group:
-//   k_mr_push      after the view's records have been filtered: this rank's output records, its depth samples (the
-//                  segments it owns) and its record of each view, stored straight into EVERY rank's window (peer memory
-//                  over NVLink); the regions are fixed by bounds all ranks share, so nothing has to be known of the others
-//   NCCL           a one-word all-reduce: every rank's stores have landed
-//   k_mr_hist, k_scan_views, k_mr_deliver_scatter   the hand-over lists, from all ranks' records in the own window
+//   k_mr_push      after the view's records have been filtered: every record that a later view will consume goes to
+//                  the rank that holds the target segment (peer store over NVLink into that rank's window, into this
+//                  rank's region of the view, appended through a counter); the depth samples of the segments this rank
+//                  owns go to every rank; and, if a rank collects the records for the host, all records go to it as well
+//   k_mr_signal    this rank's counts of each view into every rank's window, then -- after a system-wide fence -- its
+//                  arrival flag
+//   k_mr_wait      spins until every rank's flag for this group has arrived (no collective call, no host)
+//   k_mr_hist, k_scan_views, k_mr_deliver_scatter   the hand-over lists for the segments this rank holds, from the
+//                  records all ranks routed to it
 //   k_finish_view  the median, from all ranks' samples in the own window
-// The host is not in this loop: it reads the counts when it collects the group, with the next group already running.
+// The regions of a window are fixed by bounds all ranks share, so nothing has to be known of the others to store into it.
 // ------------------------------------------------------------------------------------------
-__global__ void k_mr_push(const VArgs* __restrict__ all, MrLayout lay, MrPeers peers, int rank)
+__global__ void k_mr_push(const VArgs* __restrict__ all, MrLayout lay, MrPeers peers, int rank, int W, int root, int* __restrict__ routed /* [VG_MAX][MR_MAX_RANKS], zeroed */)
 {
     L3D_PDL_PROLOGUE();
     const int v = blockIdx.y;
     const VArgs& va = all[v];
-    unsigned char* base = peers.base[blockIdx.z];
     const int* Mptr = va.off + va.n_src * va.n_cams;
     const int F = va.scored ? *va.Fout : *Mptr;
-    // the records
-    {
+    const int lane = threadIdx.x & 31;
+    // records a later view consumes: to the owner of the target segment
+    if (va.delivering) {
+        for (int k0 = blockIdx.x * blockDim.x; k0 < F; k0 += gridDim.x * blockDim.x) {
+            const int k = k0 + threadIdx.x;
+            int dest = -1; uint4 lo, hi;
+            if (k < F) {
+                const uint4* src = reinterpret_cast<const uint4*>(va.filtered + k);
+                lo = src[0]; hi = src[1];
+                const int cam = int(lo.y), tgt = int(lo.z);                 // l3d_match: src_seg, cam, tgt_seg, confidence | depths
+                if (va.cams[cam].deliver >= 0) dest = tgt % W;
+            }
+            // one counter bump per destination and warp
+            const unsigned active = __ballot_sync(0xffffffffu, dest >= 0);
+            if (dest >= 0) {
+                const unsigned peers_same = __match_any_sync(active, dest);
+                const int leader = __ffs(peers_same) - 1;
+                int base = 0;
+                if (lane == leader) base = atomicAdd(&routed[v * MR_MAX_RANKS + dest], __popc(peers_same));
+                base = __shfl_sync(peers_same, base, leader);
+                const int pos = base + __popc(peers_same & ((1u << lane) - 1u));
+                uint4* dst = reinterpret_cast<uint4*>(peers.base[dest] + lay.rec_off[v]) + size_t(2) * (size_t(rank) * size_t(lay.cap[v]) + size_t(pos));
+                dst[0] = lo; dst[1] = hi;
+            }
+        }
+    }
+    // all records, in order, to the rank that hands them to its host
+    for (int r = (root == -2 ? 0 : root); r >= 0 && r < W; r = (root == -2 ? r + 1 : W)) {      // root: one rank, -2: every rank, -1: nobody
         const uint4* src = reinterpret_cast<const uint4*>(va.filtered);
-        uint4* dst = reinterpret_cast<uint4*>(base + lay.rec_off[v]) + size_t(2) * size_t(rank) * size_t(lay.cap[v]);
+        uint4* dst = reinterpret_cast<uint4*>(peers.base[r] + lay.full_off[v]) + size_t(2) * size_t(rank) * size_t(lay.cap[v]);
         for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * F; i += gridDim.x * blockDim.x) dst[i] = src[i];
     }
     // depth samples of the segments this rank owns: both depths of the segment's best match if its score exceeds 0.5,
-    // infinity otherwise (cudawrapper.cu:1090-1110); every segment is written by exactly one rank
+    // infinity otherwise (cudawrapper.cu:1090-1110); every segment is written by exactly one rank, to every rank
     if (va.scored) {
-        float2* smp = reinterpret_cast<float2*>(base + lay.samp_off[v]);
-        for (int row = blockIdx.x * blockDim.x + threadIdx.x; row < va.n_src; row += gridDim.x * blockDim.x) {
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < va.n_src * W; i += gridDim.x * blockDim.x) {
+            const int row = i / W, r = i - row * W;
             const unsigned long long key = va.best[row];
             float2 ab = make_float2(INFINITY, INFINITY);
             if (__uint_as_float(unsigned(key >> 32)) > 0.5f) { const float4 dp = va.mdep[0xffffffffu - unsigned(key & 0xffffffffull)]; ab = make_float2(dp.x, dp.y); }
-            smp[row_segment(va.src, row)] = ab;
+            reinterpret_cast<float2*>(peers.base[r] + lay.samp_off[v])[row_segment(va.src, row)] = ab;
         }
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        RankRec r; r.M = *Mptr; r.F = F;
-        r.iters_all = va.scored ? va.iters[0] : 0ull; r.iters_same = va.scored ? va.iters[1] : 0ull; r.pad[0] = r.pad[1] = 0;
-        reinterpret_cast<RankRec*>(base)[rank * 8 + v] = r;
+}
+// one thread per (view, destination rank): this rank's records of the group's views, then the flags
+__global__ void k_mr_signal(const VArgs* __restrict__ all, int n_views, MrPeers peers, int rank, int W, const int* __restrict__ routed, unsigned seq)
+{
+    L3D_PDL_PROLOGUE();
+    const int t = threadIdx.x;
+    if (t < n_views * W) {
+        const int v = t / W, r = t - v * W;
+        const VArgs& va = all[v];
+        const int* Mptr = va.off + va.n_src * va.n_cams;
+        RankRec rec; rec.M = *Mptr; rec.F = va.scored ? *va.Fout : *Mptr;
+        rec.iters_all = va.scored ? va.iters[0] : 0ull; rec.iters_same = va.scored ? va.iters[1] : 0ull;
+        rec.routed = routed[v * MR_MAX_RANKS + r]; rec.pad = 0;
+        reinterpret_cast<RankRec*>(peers.base[r])[rank * VG_MAX + v] = rec;
+    }
+    __threadfence_system();                 // the push kernel's stores (complete: it has ended) and the table, before the flags
+    __syncthreads();
+    if (t < W) {
+        __threadfence_system();
+        volatile unsigned* flag = reinterpret_cast<volatile unsigned*>(peers.base[t] + MR_FLAGS_OFF) + rank;
+        *flag = seq;
     }
 }
-// sizes of the hand-over groups, from all ranks' records of the view
+// waits for the flags of all ranks; gives up after about ten seconds and says so in *fault (the host reports it)
+__global__ void k_mr_wait(const unsigned char* __restrict__ window, int W, unsigned seq, int* __restrict__ fault)
+{
+    L3D_PDL_PROLOGUE();
+    const int r = threadIdx.x;
+    if (r < W) {
+        const volatile unsigned* flag = reinterpret_cast<const volatile unsigned*>(window + MR_FLAGS_OFF) + r;
+        const long long t0 = clock64();
+        while (int(*flag - seq) < 0) {
+            if (clock64() - t0 > 20000000000ll) { atomicExch(fault, 1 + r); break; }
+            __nanosleep(200);
+        }
+    }
+    __threadfence_system();
+}
+// sizes of the hand-over groups, from the records all ranks routed here
 __global__ void k_mr_hist(const VArgs* __restrict__ all, const unsigned char* __restrict__ window, MrLayout lay, int W)
 {
     L3D_PDL_PROLOGUE();
@@ -1476,7 +1541,7 @@ __global__ void k_mr_hist(const VArgs* __restrict__ all, const unsigned char* __
     if (!va.delivering) return;
     const RankRec* rec = reinterpret_cast<const RankRec*>(window);
     for (int r = 0; r < W; ++r) {
-        const int n = rec[r * 8 + v].F;
+        const int n = rec[r * VG_MAX + v].routed;
         const l3d_match* f = reinterpret_cast<const l3d_match*>(window + lay.rec_off[v]) + size_t(r) * size_t(lay.cap[v]);
         for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
             const int d = va.cams[f[k].cam].deliver;
@@ -1492,7 +1557,7 @@ __global__ void k_mr_deliver_scatter(const VArgs* __restrict__ all, const unsign
     if (!va.delivering) return;
     const RankRec* rec = reinterpret_cast<const RankRec*>(window);
     for (int r = 0; r < W; ++r) {
-        const int n = rec[r * 8 + v].F;
+        const int n = rec[r * VG_MAX + v].routed;
         const l3d_match* f = reinterpret_cast<const l3d_match*>(window + lay.rec_off[v]) + size_t(r) * size_t(lay.cap[v]);
         for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
             const l3d_match m = f[k];
@@ -1511,10 +1576,10 @@ __global__ void k_mr_gather(const unsigned char* __restrict__ window, MrLayout l
     const int v = blockIdx.y;
     const RankRec* rec = reinterpret_cast<const RankRec*>(window);
     long long off = 0;
-    for (int vv = 0; vv < v; ++vv) for (int r = 0; r < W; ++r) off += rec[r * 8 + vv].F;
+    for (int vv = 0; vv < v; ++vv) for (int r = 0; r < W; ++r) off += rec[r * VG_MAX + vv].F;
     for (int r = 0; r < W; ++r) {
-        const int n = rec[r * 8 + v].F;
-        const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const l3d_match*>(window + lay.rec_off[v]) + size_t(r) * size_t(lay.cap[v]));
+        const int n = rec[r * VG_MAX + v].F;
+        const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const l3d_match*>(window + lay.full_off[v]) + size_t(r) * size_t(lay.cap[v]));
         uint4* dst = reinterpret_cast<uint4*>(out + off);
         for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * n; i += gridDim.x * blockDim.x) dst[i] = src[i];
         off += n;
@@ -1524,16 +1589,33 @@ __global__ void k_mr_gather(const unsigned char* __restrict__ window, MrLayout l
 // ------------------------------------------------------------------------------------------
 // collinearity (cudawrapper.cu:476-535): upper triangle, compacted on the device
 // ------------------------------------------------------------------------------------------
+// A pair can only pass if all four endpoint-to-line distances stay below sigma * sqrt(2 ln 2) (affinity > 0.5).  Two of
+// them -- the other segment's endpoints against THIS row's line -- are tested first in plain FP32 with the line
+// normalised once per row: 4 FMAs per pair, and all but about 1 % of the pairs end there.  The bound is widened by
+// 0.5 px plus what the reference's own FP32 line through the row's endpoints can be off by (the cross product's
+// rounding divided by the segment's length), so that no pair the exact evaluation accepts is dropped.
 __global__ void k_collin_count(const float4* __restrict__ segs, int n, float sigma_sqr, int* __restrict__ cnt, unsigned* __restrict__ bits, int wpr)
 {
     const int i = blockIdx.y;
     const int w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= wpr) return;
     const float4 a = segs[i];
+    const float lx = a.y - a.w, ly = a.z - a.x, lz = a.x * a.w - a.y * a.z;          // p1 x p2
+    const float len2 = lx * lx + ly * ly;
+    const float inv = rsqrtf(fmaxf(len2, 1e-30f));
+    const float nx = lx * inv, ny = ly * inv, nz = lz * inv;
+    const float big = fmaxf(fmaxf(fabsf(a.x * a.w), fabsf(a.y * a.z)), 1.0f);
+    const float ulp = __int_as_float((__float_as_int(big) & 0x7f800000) - (23 << 23));      // 2^(exponent - 23)
+    float thr = 1.1775f * sqrtf(sigma_sqr) * 1.0001f + 0.5f + 2.0f * ulp * inv;
+    if (!(len2 > 1e-12f) || !(thr < 1e30f)) thr = __int_as_float(0x7f800000);             // degenerate row: no pre-test
     unsigned m = 0;
     for (int b = 0; b < 32; ++b) {
         const int j = w * 32 + b;
-        if (j > i && j < n && xcollinearity(a, segs[j], sigma_sqr) > 0.0f) m |= 1u << b;
+        if (j > i && j < n) {
+            const float4 q = segs[j];
+            const float t1 = fabsf(fmaf(nx, q.x, fmaf(ny, q.y, nz))), t2 = fabsf(fmaf(nx, q.z, fmaf(ny, q.w, nz)));
+            if (!(t1 > thr || t2 > thr) && xcollinearity(a, q, sigma_sqr) > 0.0f) m |= 1u << b;
+        }
     }
     bits[size_t(i) * wpr + w] = m;
     if (m) atomicAdd(&cnt[i], __popc(m));
@@ -1890,7 +1972,8 @@ __global__ void k_fma2_probe(float* out, int iters, float b, float c)
 // ==========================================================================================
 struct Delivered {            // records a source view handed to a later view
     int from_view = -1;
-    int count = 0;
+    int count = 0;            // records (a bound until the sending view has been collected; several GPUs: this rank's share)
+    long long count_all = 0;  // several GPUs: a bound on all ranks' records together, the same number on every rank (it fixes the window layout)
     int* t_start = nullptr;   // n_seg(to) + 1, points into the owning buffer
     int* t_tgt = nullptr;
     float4* t_dep = nullptr;
@@ -1922,8 +2005,6 @@ struct ViewJob {                 // phase B of one view: on the stream, not yet 
 // The per-view work runs on groups of views (see VArgs): a slot holds one view's buffers, a group up to VG_MAX
 // slots plus what the group's views share (one upload of tables and arguments, one memset, one result download).
 // Two groups exist: the host prepares and launches the next one while the GPU works on the current one.
-constexpr int VG_MAX = 8;          // (RankRec tables on the device are indexed [rank * 8 + view])
-static_assert(VG_MAX == 8, "the multi-GPU kernels index the record table with a stride of 8");
 struct ViewSlot {
     ViewJob job;
     size_t plan_index = 0;
@@ -1945,8 +2026,9 @@ struct ViewGroup {
     // several GPUs on one scene: depth samples of the group's views (one buffer: one all-reduce), the ranks' records,
     // the packed records of this rank, all ranks' packed records, all ranks' records view by view
     size_t hist_off = 0, hist_total = 0;
-    HBuf<RankRec> h_allrec; MrLayout lay; DBuf<l3d_match> d_gather;
+    HBuf<RankRec> h_allrec; MrLayout lay; DBuf<l3d_match> d_gather; int* d_fault = nullptr;
     cudaEvent_t ev_x[2] = {nullptr, nullptr};      // [0] exchange done on the main stream, [1] this group's records copied to the host
+    cudaEvent_t kev[24] = {}; int kev_slot[24] = {}; int n_kev = 0;      // per-kernel events of the chain (l3d_debug_chain_times)
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [0] results on the host, [2..5] stage boundaries
     void release()
     {
@@ -1954,6 +2036,7 @@ struct ViewGroup {
         h_args.release(); d_args.release(); h_cams.release(); d_cams.release(); d_zero.release(); d_vres.release(); h_vres.release();
         h_allrec.release(); d_gather.release();
         for (int k = 0; k < 2; ++k) if (ev_x[k]) { cudaEventDestroy(ev_x[k]); ev_x[k] = nullptr; }
+        for (int k = 0; k < 24; ++k) if (kev[k]) { cudaEventDestroy(kev[k]); kev[k] = nullptr; }
         for (int k = 0; k < 6; ++k) if (ev[k]) { cudaEventDestroy(ev[k]); ev[k] = nullptr; }
     }
 };
@@ -2021,11 +2104,19 @@ struct l3d_ctx {
     std::string err;
     // several GPUs on one scene (l3d_comm_init)
     NcclApi* nccl = nullptr; ncclComm_t comm = nullptr; int rank = 0, world = 1, result_root = -1;
+    bool comm_broken = false;          // a call failed while several ranks were at work: no collective step is attempted any more (the others may be gone)
     bool copies_pending = false, want_records = true;      // want_records: the current calls copy the output records to the host
-    double host_s[4] = {0, 0, 0, 0};      // host seconds in enqueue_group / finish_group (waiting) / finish_group (rest) / number of groups (l3d_debug_host_times)
+    bool chain_prof = false; double chain_ms[24] = {};      // device ms per kernel of the per-view chain, summed over the groups (with stage timing)
+    double host_s[8] = {0, 0, 0, 0, 0, 0, 0, 0};      // host seconds in enqueue_group / finish_group (waiting) / finish_group (rest) / number of groups / waiting for the helper thread / pair tests in the foreground / totals over the ranks (l3d_debug_host_times)
+    // how the pair tests of the next batch share the GPU with the per-view chain (read from the environment by l3d_plan_matching)
+    int bg_blocks = 0;                              // L3D_BG_BLOCKS: blocks per SM the large pair-test kernels may take in the background (0: no cap)
+    int p1_rows = 0;                                // L3D_P1_ROWS: source rows per block of k_pretest (0: P1_ROWS)
+    bool no_overlap = false;                        // L3D_NO_OVERLAP: pair tests never run beside the chain
+    int batch_div = 8;                              // L3D_BATCH_DIV: the schedule is cut into about this many batches
+    int group_views = 8;                            // L3D_GROUP_VIEWS: views per group of the per-view chain (at most VG_MAX)
     // the record windows (one per group in flight): every rank's is mapped into every process, the ranks store their
     // output records straight into each other's
-    unsigned char* win[2] = {nullptr, nullptr}; size_t win_cap = 0 /* bytes */; MrPeers peers[2];
+    unsigned char* win[2] = {nullptr, nullptr}; size_t win_cap = 0 /* bytes */; MrPeers peers[2]; unsigned win_seq[2] = {0u, 0u};
     DBuf<int> d_bar; DBuf<unsigned long long> d_tot; HBuf<unsigned long long> h_tot; DBuf<unsigned char> d_ipc; HBuf<unsigned char> h_ipc;
     uint64_t launches = 0;
     // views
@@ -2142,18 +2233,20 @@ int run_phase_a(l3d_ctx* cx, PhaseASet* ctx, const std::vector<JobHost>& jh)   /
     // make each of them wait for blocks to retire.  In the background the large kernels therefore ask for unused
     // dynamic shared memory, which caps them at 3-4 blocks per SM (about half of each SM stays free); alone they run
     // at full occupancy.
-    static const bool bg_on = getenv("L3D_BG_SMEM") && atoi(getenv("L3D_BG_SMEM")) != 0;      // off by default: measured slower on one GPU
-    static const bool bg_ready = [] {
-        bool ok = true;
-        ok = ok && cudaFuncSetAttribute(k_pretest<4, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) == cudaSuccess;
-        ok = ok && cudaFuncSetAttribute(k_pretest2, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) == cudaSuccess;
-        ok = ok && cudaFuncSetAttribute(k_expand, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) == cudaSuccess;
-        ok = ok && cudaFuncSetAttribute(k_exact_flat, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) == cudaSuccess;
-        return ok;
-    }();
-    const bool bgm = ctx->background && bg_on && bg_ready;
-    // per kernel: what leaves room for 4 / 3 / 4 / 3 blocks per SM (228 KB of shared memory, 1 KB reserved per block)
-    const size_t bg_p1 = bgm ? 51 * 1024 : 0, bg_p2 = bgm ? 55 * 1024 : 0, bg_ex = bgm ? 55 * 1024 : 0, bg_ef = bgm ? 65 * 1024 : 0;
+    size_t bg_p1 = 0, bg_p2 = 0, bg_ex = 0, bg_ef = 0;
+    if (ctx->background && cx->bg_blocks > 0) {
+        // what leaves room for bg_blocks blocks per SM: 228 KB of shared memory, 1 KB reserved per block
+        auto cap = [&](const void* fn, size_t* dyn) -> cudaError_t {
+            cudaFuncAttributes a; cudaError_t e = cudaFuncGetAttributes(&a, fn); if (e != cudaSuccess) return e;
+            const long long per = (228ll * 1024) / (cx->bg_blocks + 1) + 1024;      // one block more would not fit
+            long long d = per - 1024 - (long long)a.sharedSizeBytes;
+            d = std::max(0ll, std::min(d, 227ll * 1024 - (long long)a.sharedSizeBytes));
+            *dyn = size_t(d);
+            return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(d));
+        };
+        L3D_CUDA(cap(reinterpret_cast<const void*>(&k_pretest<4, 6>), &bg_p1)); L3D_CUDA(cap(reinterpret_cast<const void*>(&k_pretest2), &bg_p2));
+        L3D_CUDA(cap(reinterpret_cast<const void*>(&k_expand), &bg_ex)); L3D_CUDA(cap(reinterpret_cast<const void*>(&k_exact_flat), &bg_ef));
+    }
     ctx->jobs_host.assign(size_t(n_jobs), JobDev());
     ctx->job_cands.assign(size_t(n_jobs), 0);
     ctx->job_rowmax.assign(size_t(n_jobs), 0);
@@ -2161,7 +2254,7 @@ int run_phase_a(l3d_ctx* cx, PhaseASet* ctx, const std::vector<JobHost>& jh)   /
     ctx->pa_kev_set[0] = ctx->pa_kev_set[1] = false;
     if (n_jobs == 0) return 0;
     long long sh_tot = 0, th_tot = 0, words = 0, rows = 0, blocks = 0, l1_words = 0, l1_blocks = 0;
-    static const int p1_rows = getenv("L3D_P1_ROWS") ? std::max(128, atoi(getenv("L3D_P1_ROWS")) / 128 * 128) : P1_ROWS;
+    const int p1_rows = cx->p1_rows > 0 ? cx->p1_rows : P1_ROWS;
     int max_n = 1;
     for (int j = 0; j < n_jobs; ++j) {
         const l3d_view& sv = cx->views[jh[j].src_view]; const l3d_view& tv = cx->views[jh[j].tgt_view];
@@ -2285,7 +2378,7 @@ struct GroupView { int view; int n_nb; const l3d_neighbor* nb; int first_job; si
 size_t mr_group_need(l3d_ctx* ctx, const GroupView* gv, int count)
 {
     PhaseASet& pa = ctx->pa[ctx->cur];
-    size_t need = MR_COUNTS_BYTES;
+    size_t need = MR_HEADER_BYTES;
     for (int g = 0; g < count; ++g) {
         if (gv[g].view < 0 || gv[g].view >= ctx->V) continue;
         int n_slots = 0; size_t f_ub = 0;
@@ -2294,11 +2387,11 @@ size_t mr_group_need(l3d_ctx* ctx, const GroupView* gv, int count)
             if (n.to_be_matched) { const size_t j = size_t(gv[g].first_job + n_slots++); if (j < pa.job_raw_all.size()) f_ub += size_t(pa.job_raw_all[j]); }
             else {
                 const std::vector<Delivered>& dl = ctx->delivered[gv[g].view];
-                for (size_t k = 0; k < dl.size(); ++k) if (dl[k].from_view == n.view) { f_ub += size_t(dl[k].count); break; }
+                for (size_t k = 0; k < dl.size(); ++k) if (dl[k].from_view == n.view) { f_ub += size_t(dl[k].count_all); break; }
             }
         }
         need += (size_t(ctx->views[gv[g].view].n_segments) * 8 + 255) & ~size_t(255);
-        need += size_t(ctx->world) * std::max<size_t>(f_ub, 1) * sizeof(l3d_match);
+        need += 2 * size_t(ctx->world) * std::max<size_t>(f_ub, 1) * sizeof(l3d_match);
     }
     return need;
 }
@@ -2338,7 +2431,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     if (ctx->score_block) mn_sc_h = std::min(mn_sc_h, ctx->score_block);
     bool any_scored = false, any_window = false, any_quadratic = false, any_deliver = false;
     struct Z { size_t items, iters, best, hist, cursor, end; } z[VG_MAX];
-    size_t hist_total = 0, window_need = MR_COUNTS_BYTES;
+    size_t hist_total = 0, window_need = MR_HEADER_BYTES;
     const int slot_q = int(&gr - ctx->grp);
     memset(&gr.lay, 0, sizeof gr.lay);
     for (int g = 0; g < count; ++g) {
@@ -2353,7 +2446,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         job.view = view; job.nb.assign(nb, nb + n_nb); job.sigma_p = sigma_p; job.sigma_a = sigma_a;
         job.consumed.clear(); job.owner = -1;
         int n_slots = 0, n_deliver = 0, max_deliver_seg = 1;
-        uint64_t pair_tests = 0, cand_ub = 0, raw_ub = 0, raw_ub_all = 0, delivered_ub = 0;      // raw_ub_all: over all ranks' rows
+        uint64_t pair_tests = 0, cand_ub = 0, raw_ub = 0, raw_ub_all = 0, delivered_ub = 0, delivered_ub_all = 0;      // raw_ub_all: over all ranks' rows
         size_t seg_ub = 0;                               // upper bound on the matches of one source segment
         std::vector<int> consumed;                       // indices into ctx->delivered[view]
         for (int c = 0; c < n_nb; ++c) {
@@ -2375,7 +2468,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
                 for (size_t k = 0; k < dl.size(); ++k)
                     if (dl[k].from_view == n.view) {
                         ct.mode = 1; ct.t_start = dl[k].t_start; ct.t_tgt = dl[k].t_tgt; ct.t_dep = dl[k].t_dep;
-                        delivered_ub += uint64_t(dl[k].count); seg_ub += size_t(dl[k].max_group);
+                        delivered_ub += uint64_t(dl[k].count); delivered_ub_all += uint64_t(dl[k].count_all); seg_ub += size_t(dl[k].max_group);
                         consumed.push_back(int(k)); job.consumed.push_back(std::make_pair(dl[k].owner, dl[k].slot));
                         break;
                     }
@@ -2384,11 +2477,12 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         }
         job.pair_tests = pair_tests; job.cand_ub = cand_ub;
         const size_t M_ub = size_t(raw_ub + delivered_ub);          // upper bound on the number of matches to score
-        const size_t F_ub_all = size_t(raw_ub_all + delivered_ub);  // ... and on the output records of the view from all ranks together
+        const size_t F_ub_all = size_t(raw_ub_all + (mr ? delivered_ub_all : delivered_ub));  // ... and on the output records of any rank (the same number on every rank)
         if (mr) {                                                    // the view's places in the group's window
             gr.lay.samp_off[g] = (long long)window_need; window_need += (size_t(n_full) * 8 + 255) & ~size_t(255);
-            gr.lay.rec_off[g] = (long long)window_need; gr.lay.cap[g] = (long long)std::max<size_t>(F_ub_all, 1);
-            window_need += size_t(ctx->world) * size_t(gr.lay.cap[g]) * sizeof(l3d_match);
+            gr.lay.cap[g] = (long long)std::max<size_t>(F_ub_all, 1);
+            gr.lay.rec_off[g] = (long long)window_need; window_need += size_t(ctx->world) * size_t(gr.lay.cap[g]) * sizeof(l3d_match);
+            gr.lay.full_off[g] = (long long)window_need; window_need += size_t(ctx->world) * size_t(gr.lay.cap[g]) * sizeof(l3d_match);
         }
         const bool scored = n_slots > 0;                             // cudawrapper.cu:877-878
         const bool delivering = n_deliver > 0 && scored;
@@ -2459,6 +2553,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
                 const uint64_t ub = std::min<uint64_t>(hc[c].slot >= 0 ? pa.job_raw_all[first_job + hc[c].slot] : uint64_t(mr ? F_ub_all : M_ub), 0x7fffffffull);
                 Delivered dl; dl.from_view = view; dl.owner = job.owner; dl.slot = d;
                 dl.count = int(ub); dl.max_group = int(std::min<uint64_t>(ub, uint64_t(n_src)));      // a source segment matches a target segment once
+                dl.count_all = (long long)ub;
                 if (mr) dl.max_group = int(std::min<uint64_t>(ub, uint64_t(n_full)));
                 dl.t_start = buf.start + size_t(d) * stride; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
                 buf.counts[d] = dl.count; buf.maxg[d] = dl.max_group;
@@ -2482,6 +2577,8 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     }
     gr.hist_off = zero_total; gr.hist_total = hist_total;
     zero_total += hist_total;
+    const size_t routed_off = zero_total;                     // several GPUs: records routed per (view, destination rank), and a fault word
+    zero_total += size_t(VG_MAX) * MR_MAX_RANKS + 4;
     L3D_CUDA(gr.d_zero.ensure(zero_total + 4));
     if (mr && window_need > ctx->win_cap) { ctx->err = "l3d_match_view: internal error (window too small)"; return 1; }
     for (int g = 0; g < count; ++g) {
@@ -2502,14 +2599,22 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     L3D_CUDA(cudaMemcpyAsync(gr.d_cams.p, gr.h_cams.p, sizeof(CamTable) * cams_total, cudaMemcpyHostToDevice, st));
     L3D_CUDA(cudaMemcpyAsync(gr.d_args.p, gr.h_args.p, sizeof(VArgs) * size_t(count), cudaMemcpyHostToDevice, st));
     L3D_CUDA(cudaMemsetAsync(gr.d_zero.p, 0, sizeof(int) * zero_total, st));
+    gr.n_kev = 0;
+    // (per-kernel events, only when asked for: l3d_debug_chain_times)
+#define L3D_KEV(slot) do { if (ctx->chain_prof && ctx->stage_events && gr.n_kev < 24) { if (!gr.kev[gr.n_kev]) cudaEventCreate(&gr.kev[gr.n_kev]); cudaEventRecord(gr.kev[gr.n_kev], st); gr.kev_slot[gr.n_kev] = (slot); ++gr.n_kev; } } while (0)
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[2], st));
+    L3D_KEV(0);
     L3D_CUDA(pdl_launch(k_gather_counts, dim3((mx_src + 255) / 256, mx_cams, G), dim3(256), 0, st, A));
+    L3D_KEV(1);
     L3D_CUDA(pdl_launch(k_scan_views, dim3(1, G), dim3(SCAN_T), 0, st, A, 0));
+    L3D_KEV(2);
     L3D_CUDA(pdl_launch(k_fill, dim3(unsigned((mx_warps * 32 + 255) / 256), G), dim3(256), 0, st, A, ctx->d_segs.p));
     ctx->launches += 3;
+    L3D_KEV(3);
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[3], st));
     if (any_window) {
         L3D_CUDA(pdl_launch(k_bucket_segments, dim3(mx_src, G), dim3(BK_T), 0, st, A));
+        L3D_KEV(4);
         L3D_CUDA(pdl_launch(k_score_window, dim3(mx_items, G), dim3(mn_sc_h), mx_smem, st, A, ctx->d_segs.p));
         ctx->launches += 2;
     }
@@ -2518,43 +2623,60 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         L3D_CUDA(pdl_launch(k_score, dim3(mx_items, G), dim3(mn_sc_h), mx_smem, st, A, ctx->d_segs.p));
         ctx->launches += 2;
     }
+    L3D_KEV(5);
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[4], st));
     if (any_scored) { L3D_CUDA(pdl_launch(k_reduce_matches, dim3(mx_cta, G), dim3(RM_T), 0, st, A)); ctx->launches += 1; }
+    L3D_KEV(6);
     L3D_CUDA(pdl_launch(k_filter_compact, dim3(mx_cta, G), dim3(RM_T), 0, st, A));
     ctx->launches += 1;
+    L3D_KEV(7);
     if (mr) {
         // Every rank stores its records, depth samples and counts into all ranks' windows (regions fixed by shared
         // bounds), a one-word all-reduce tells that everybody's stores have landed, and the hand-over lists and the
         // medians are made from the own window.
-        const unsigned pb = unsigned(std::min<size_t>(std::max<size_t>((2 * mx_M + 255) / 256, 1), size_t(2 * ctx->n_sm)));
-        L3D_CUDA(pdl_launch(k_mr_push, dim3(pb, G, unsigned(ctx->world)), dim3(256), 0, st, A, gr.lay, ctx->peers[slot_q], ctx->rank));
-        L3D_NCCL(ctx->nccl->AllReduce(ctx->d_bar.p, ctx->d_bar.p, 1, ncclInt, ncclSum, ctx->comm, st));
-        ctx->launches += 1;
+        const unsigned pb = unsigned(std::min<size_t>(std::max<size_t>((mx_M + 255) / 256, 1), size_t(4 * ctx->n_sm)));
+        const bool collect = ctx->want_records;
+        const int root = !collect ? -1 : (ctx->result_root < 0 ? -2 : ctx->result_root);
+        int* routed = gr.d_zero.p + routed_off; int* fault = routed + VG_MAX * MR_MAX_RANKS;
+        const unsigned seq = ++ctx->win_seq[slot_q];
         const unsigned char* window = ctx->win[slot_q];
+        L3D_CUDA(pdl_launch(k_mr_push, dim3(pb, G), dim3(256), 0, st, A, gr.lay, ctx->peers[slot_q], ctx->rank, ctx->world, root, routed));
+        L3D_KEV(8);
+        L3D_CUDA(pdl_launch(k_mr_signal, dim3(1), dim3(VG_MAX * MR_MAX_RANKS), 0, st, A, int(count), ctx->peers[slot_q], ctx->rank, ctx->world, (const int*)routed, seq));
+        L3D_CUDA(pdl_launch(k_mr_wait, dim3(1), dim3(32), 0, st, window, ctx->world, seq, fault));
+        ctx->launches += 3;
+        L3D_KEV(9);
+        gr.d_fault = fault;
         if (any_deliver) {
-            const unsigned hb = unsigned(std::min<size_t>(size_t(ctx->world) * pb, size_t(8 * ctx->n_sm)));
+            const unsigned hb = unsigned(std::min<size_t>(std::max<size_t>(pb, 1), size_t(4 * ctx->n_sm)));
             L3D_CUDA(pdl_launch(k_mr_hist, dim3(hb, G), dim3(256), 0, st, A, window, gr.lay, ctx->world));
+            L3D_KEV(10);
             L3D_CUDA(pdl_launch(k_scan_views, dim3(1, G), dim3(SCAN_T), 0, st, A, 1));
+            L3D_KEV(11);
             L3D_CUDA(pdl_launch(k_mr_deliver_scatter, dim3(hb, G), dim3(256), 0, st, A, window, gr.lay, ctx->world));
             ctx->launches += 3;
+            L3D_KEV(12);
         }
         L3D_CUDA(pdl_launch(k_finish_view, dim3(1, G), dim3(MS_T), 0, st, A));
         ctx->launches += 1;
-        if (ctx->want_records && (ctx->result_root < 0 || ctx->result_root == ctx->rank)) {
+        L3D_KEV(13);
+        if (collect && (ctx->result_root < 0 || ctx->result_root == ctx->rank)) {
             // for the copy to the host: the ranks' regions of each view put end to end.  On this stream, so that the
             // window is only ever read in stream order (the other ranks write the group after next into it as soon as
             // this rank has joined the next group's all-reduce).
             size_t bound = 0;
             for (int g = 0; g < count; ++g) bound += size_t(gr.lay.cap[g]);
             L3D_CUDA(gr.d_gather.ensure(bound));
-            k_mr_gather<<<dim3(pb, G), 256, 0, st>>>(window, gr.lay, ctx->world, gr.d_gather.p);
+            k_mr_gather<<<dim3(std::min(2 * pb, unsigned(4 * ctx->n_sm)), G), 256, 0, st>>>(window, gr.lay, ctx->world, gr.d_gather.p);
             ctx->launches += 1;
+            L3D_KEV(14);
         }
         L3D_CUDA(cudaEventRecord(gr.ev_x[0], st));      // the gathered records are complete
         L3D_CUDA(cudaGetLastError());
         if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[5], st));
         L3D_CUDA(cudaMemcpyAsync(gr.h_vres.p, gr.d_vres.p, sizeof(int) * size_t(count) * res_stride, cudaMemcpyDeviceToHost, st));
-        L3D_CUDA(cudaMemcpyAsync(gr.h_allrec.p, window, sizeof(RankRec) * 8 * size_t(ctx->world), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaMemcpyAsync(gr.h_allrec.p, window, sizeof(RankRec) * VG_MAX * size_t(ctx->world), cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaMemcpyAsync(&gr.h_allrec.p[size_t(VG_MAX) * MR_MAX_RANKS - 1].pad, gr.d_fault, sizeof(int), cudaMemcpyDeviceToHost, st));      // (a spare word of the pinned table)
         L3D_CUDA(cudaEventRecord(gr.ev[0], st));
         return 0;
     }
@@ -2562,6 +2684,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
         L3D_CUDA(pdl_launch(k_scan_views, dim3(1, G), dim3(SCAN_T), 0, st, A, 1));
         L3D_CUDA(pdl_launch(k_deliver_scatter, dim3(unsigned((std::max<size_t>(mx_M, 1) + 255) / 256), G), dim3(256), 0, st, A));
         ctx->launches += 2;
+        L3D_KEV(12);
     }
     // The last kernel (medians, result records) and the download of the records are needed by the host only: the next
     // group does not wait for them.  They go to a side stream (this group's buffers are not touched again before the
@@ -2574,6 +2697,7 @@ int enqueue_group(l3d_ctx* ctx, ViewGroup& gr, const GroupView* gv, int count, f
     }
     L3D_CUDA(pdl_launch(k_finish_view, dim3(1, G), dim3(MS_T), 0, fs, A));
     ctx->launches += 1;
+    L3D_KEV(13);
     L3D_CUDA(cudaGetLastError());
     if (ctx->stage_events) L3D_CUDA(cudaEventRecord(gr.ev[5], st));
     L3D_CUDA(cudaMemcpyAsync(gr.h_vres.p, gr.d_vres.p, sizeof(int) * size_t(count) * res_stride, cudaMemcpyDeviceToHost, fs));
@@ -2618,6 +2742,7 @@ int mr_ensure_window(l3d_ctx* ctx, size_t need)
         if (ctx->win[q]) cudaFree(ctx->win[q]);
         ctx->win[q] = nullptr;
         L3D_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->win[q]), cap));
+        L3D_CUDA(cudaMemsetAsync(ctx->win[q], 0, MR_HEADER_BYTES, st));          // the arrival flags start below every sequence number
         L3D_CUDA(cudaIpcGetMemHandle(&mine[q], ctx->win[q]));
     }
     ctx->win_cap = 0;
@@ -2643,7 +2768,7 @@ void mr_release_window(l3d_ctx* ctx)
     for (int q = 0; q < 2; ++q) {
         for (int r = 0; r < MR_MAX_RANKS; ++r) { if (r != ctx->rank && ctx->peers[q].base[r]) cudaIpcCloseMemHandle(ctx->peers[q].base[r]); ctx->peers[q].base[r] = nullptr; }
     }
-    if (ctx->comm && ctx->d_bar.p) {        // nobody frees a window that another rank still has mapped
+    if (ctx->comm && ctx->d_bar.p && !ctx->comm_broken) {        // nobody frees a window that another rank still has mapped
         cudaMemsetAsync(ctx->d_bar.p, 0, sizeof(int), ctx->stream);
         ctx->nccl->AllReduce(ctx->d_bar.p, ctx->d_bar.p, 1, ncclInt, ncclSum, ctx->comm, ctx->stream);
         cudaStreamSynchronize(ctx->stream);
@@ -2688,6 +2813,8 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
     } else ctx->pa_kernel_ms[0] = ctx->pa_kernel_ms[1] = ctx->pa_kernel_ms[2] = 0.f;
     float ms_b[3] = {0.f, 0.f, 0.f};
     if (ctx->stage_events) for (int k = 0; k < 3; ++k) cudaEventElapsedTime(&ms_b[k], gr.ev[k + 2], gr.ev[k + 3]);
+    for (int k = 1; k < gr.n_kev; ++k) { float ms = 0.f; cudaEventElapsedTime(&ms, gr.kev[k - 1], gr.kev[k]); ctx->chain_ms[gr.kev_slot[k]] += double(ms); }
+    gr.n_kev = 0;
     const bool mr = ctx->world > 1;
     int view_off[VG_MAX], view_cnt[VG_MAX];              // several GPUs: where each view's records are in this group's window
     if (mr) {
@@ -2702,6 +2829,7 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
             view_cnt[v] = int(total - view_off[v]);
         }
         if (total > 0x7fffffffll) { ctx->err = "l3d_match_view: too many output records in one group of views"; return 1; }
+        if (gr.h_allrec.p[size_t(VG_MAX) * MR_MAX_RANKS - 1].pad != 0) { ctx->err = "l3d_match_view: a rank did not deliver its records of a group of views within ten seconds"; return 1; }
         copy_back = copy_back && (ctx->result_root < 0 || ctx->result_root == ctx->rank);      // who gets the records on the host
         (void)max_cnt;
         if (copy_back && total > 0) L3D_CUDA(cudaStreamWaitEvent(ctx->copy_stream, gr.ev_x[0], 0));
@@ -2717,11 +2845,13 @@ int finish_group(l3d_ctx* ctx, ViewGroup& gr, bool copy_back, l3d_match_result* 
         res->pair_tests = job.pair_tests; res->n_candidates = job.cand_ub; res->scored = job.scored ? 1 : 0;
         int M = hr[0], F = (job.M_ub > 0) ? hr[1] : 0;
         float median = 1.0f;                              // line3D.cc:811
-        if (mr) {                                          // the view as a whole: all ranks' rows
-            unsigned long long all = 0ull, same = 0ull; long long m = 0;
-            for (int r = 0; r < ctx->world; ++r) { const RankRec& rr = gr.h_allrec.p[size_t(r) * VG_MAX + g]; m += rr.M; all += rr.iters_all; same += rr.iters_same; }
-            M = int(m); F = view_cnt[g];
-            if (job.scored && M > 0) { memcpy(&median, &hr[2], sizeof(float)); res->score_iters = all; res->score_iters_other_cam = all - same; }
+        if (mr) {                                          // counters: this rank's rows; records and median: the whole view
+            long long m_all = 0;
+            for (int r = 0; r < ctx->world; ++r) m_all += gr.h_allrec.p[size_t(r) * VG_MAX + g].M;
+            const RankRec& mine = gr.h_allrec.p[size_t(ctx->rank) * VG_MAX + g];
+            M = mine.M; F = view_cnt[g];
+            if (job.scored && m_all > 0) memcpy(&median, &hr[2], sizeof(float));
+            if (job.scored) { res->score_iters = mine.iters_all; res->score_iters_other_cam = mine.iters_all - mine.iters_same; }
         } else if (job.scored && M > 0) {
             memcpy(&median, &hr[2], sizeof(float));
             const unsigned long long all = (unsigned long long)(unsigned)hr[4] | ((unsigned long long)(unsigned)hr[5] << 32);
@@ -2842,7 +2972,9 @@ int top_up(l3d_ctx* ctx)
         bool have = false;
         if (ctx->pa_worker_active) {                             // its pair tests were started while the previous batch was scored
             PhaseASet& nx = ctx->pa[ctx->cur ^ 1];
+            const auto tj = std::chrono::steady_clock::now();
             const int rc = join_worker(ctx);
+            ctx->host_s[4] += std::chrono::duration<double>(std::chrono::steady_clock::now() - tj).count();
             if (rc == 0) {
                 if (nx.begin != ctx->fly_end) { ctx->err = "l3d_match_view: internal error (batch out of step)"; return 1; }
                 ctx->cur ^= 1; have = true;
@@ -2854,7 +2986,9 @@ int top_up(l3d_ctx* ctx)
             PhaseASet& set = ctx->pa[ctx->cur];
             set.begin = ctx->fly_end; set.end = plan_batch(ctx, ctx->fly_end, jh);
             set.background = false;
+            const auto tf = std::chrono::steady_clock::now();
             const int rc = run_phase_a(ctx, &set, jh);
+            ctx->host_s[5] += std::chrono::duration<double>(std::chrono::steady_clock::now() - tf).count();
             if (rc == 2 && set.end - set.begin > 1 && ctx->world <= 1) {             // halve the batch and try again (one GPU only: ranks must cut alike)
                 uint64_t pairs = 0;
                 for (size_t e = set.begin; e < set.end; ++e) pairs += ctx->plan[ctx->order[e]].pair_tests;
@@ -2865,17 +2999,18 @@ int top_up(l3d_ctx* ctx)
             have = true;
         }
         PhaseASet& set = ctx->pa[ctx->cur];
+        const auto tt = std::chrono::steady_clock::now();
         if (mr_job_totals(ctx, set)) return 1;
+        ctx->host_s[6] += std::chrono::duration<double>(std::chrono::steady_clock::now() - tt).count();
         ctx->batch_begin = set.begin; ctx->batch_end = set.end;
         ctx->launches += set.launches; set.launches = 0;
-        static const bool no_overlap = getenv("L3D_NO_OVERLAP") != nullptr;
-        if (ctx->batch_end < ctx->order.size() && !ctx->stage_events && !no_overlap) start_worker(ctx, ctx->batch_end);      // the following batch, meanwhile (not when stages are timed: nothing may run beside anything)
+        if (ctx->batch_end < ctx->order.size() && !ctx->stage_events && !ctx->no_overlap) start_worker(ctx, ctx->batch_end);      // the following batch, meanwhile (not when stages are timed: nothing may run beside anything)
     }
     // the next groups: consecutive views of one dependency level, two groups in flight
     while (ctx->fly_end < ctx->batch_end && ctx->grp_end - ctx->grp_begin < 2) {
         GroupView gv[VG_MAX]; int count = 0;
         const int lvl = ctx->level[ctx->order[ctx->fly_end]];
-        while (count < VG_MAX && ctx->fly_end + size_t(count) < ctx->batch_end && ctx->level[ctx->order[ctx->fly_end + size_t(count)]] == lvl) {
+        while (count < ctx->group_views && ctx->fly_end + size_t(count) < ctx->batch_end && ctx->level[ctx->order[ctx->fly_end + size_t(count)]] == lvl) {
             PlannedView& pv = ctx->plan[ctx->order[ctx->fly_end + size_t(count)]];
             GroupView v = {pv.view, int(pv.nb.size()), pv.nb.data(), pv.first_job, ctx->order[ctx->fly_end + size_t(count)]};
             gv[count++] = v;
@@ -3040,13 +3175,12 @@ int l3d_comm_destroy(l3d_ctx* ctx)
     if (!ctx) return 1;
     if (ctx->comm) {
         cudaSetDevice(ctx->device);
-        drain_pending(ctx);
-        cudaStreamSynchronize(ctx->stream);
+        if (!ctx->comm_broken) { drain_pending(ctx); cudaStreamSynchronize(ctx->stream); }
         mr_release_window(ctx);
-        ctx->nccl->CommDestroy(ctx->comm);
+        if (ctx->comm_broken) ctx->nccl->CommAbort(ctx->comm); else ctx->nccl->CommDestroy(ctx->comm);
         ctx->comm = nullptr;
     }
-    ctx->rank = 0; ctx->world = 1; ctx->result_root = -1;
+    ctx->rank = 0; ctx->world = 1; ctx->result_root = -1; ctx->comm_broken = false;
     return 0;
 }
 
@@ -3252,7 +3386,7 @@ int l3d_deliver(l3d_ctx* ctx, int to_view, int from_view, size_t n, const l3d_ma
             L3D_CUDA(cudaMemcpyAsync(buf.dep, dep.data(), sizeof(float4) * n, cudaMemcpyHostToDevice, ctx->stream));
         }
         L3D_CUDA(cudaStreamSynchronize(ctx->stream));          // the host vectors go away
-        Delivered dl; dl.from_view = from_view; dl.count = int(n); dl.max_group = max_group; dl.t_start = buf.start; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
+        Delivered dl; dl.from_view = from_view; dl.count = int(n); dl.count_all = (long long)n; dl.max_group = max_group; dl.t_start = buf.start; dl.t_tgt = buf.tgt; dl.t_dep = buf.dep;
         dl.owner = int(ctx->deliver_bufs.size()); dl.slot = 0;
         ctx->deliver_bufs.push_back(buf);
         ctx->delivered[to_view].push_back(dl);
@@ -3305,7 +3439,16 @@ int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans)
         // about eight of them (not smaller than 2.5e8 pair tests: a batch has fixed costs), none above the memory budget.
         uint64_t total = 0;
         for (size_t k = 0; k < ctx->plan.size(); ++k) total += ctx->plan[k].pair_tests;
-        ctx->batch_pairs = ctx->batch_override ? ctx->batch_override : std::min<uint64_t>(ctx->pair_budget, std::max<uint64_t>(total / 8, 250000000ull));
+        {   // tuning knobs, read once per schedule
+            const char* e;
+            ctx->bg_blocks = (e = getenv("L3D_BG_BLOCKS")) ? std::max(0, std::min(atoi(e), 16)) : 0;
+            ctx->p1_rows = (e = getenv("L3D_P1_ROWS")) ? std::max(128, atoi(e) / 128 * 128) : 0;
+            ctx->no_overlap = (e = getenv("L3D_NO_OVERLAP")) != nullptr && atoi(e) != 0;
+            ctx->batch_div = (e = getenv("L3D_BATCH_DIV")) ? std::max(1, std::min(atoi(e), 256)) : 8;
+            // (one scene on several GPUs: a rank's share of a view is small and every group costs an exchange, so larger groups)
+            ctx->group_views = (e = getenv("L3D_GROUP_VIEWS")) ? std::max(1, std::min(atoi(e), VG_MAX)) : (ctx->world > 1 ? 16 : 8);
+        }
+        ctx->batch_pairs = ctx->batch_override ? ctx->batch_override : std::min<uint64_t>(ctx->pair_budget, std::max<uint64_t>(total / uint64_t(ctx->batch_div), 250000000ull));
         if (ctx->stage_events && !ctx->batch_override) ctx->batch_pairs = ctx->pair_budget;      // per-stage timing: nothing runs beside anything else
         return 0;
     });
@@ -3339,10 +3482,18 @@ int l3d_debug_set_candidate_limit(l3d_ctx* ctx, uint64_t limit)
     return 0;
 }
 
+int l3d_debug_chain_times(l3d_ctx* ctx, int on, double out[24])
+{
+    if (!ctx) return 1;
+    if (out) for (int k = 0; k < 24; ++k) { out[k] = ctx->chain_ms[k]; ctx->chain_ms[k] = 0.0; }
+    ctx->chain_prof = on != 0;
+    return 0;
+}
+
 int l3d_debug_host_times(l3d_ctx* ctx, double out[4])
 {
     if (!ctx || !out) return 1;
-    for (int k = 0; k < 4; ++k) { out[k] = ctx->host_s[k]; ctx->host_s[k] = 0.0; }
+    for (int k = 0; k < 8; ++k) { out[k] = ctx->host_s[k]; ctx->host_s[k] = 0.0; }
     return 0;
 }
 
@@ -3355,11 +3506,15 @@ int l3d_retain_results(l3d_ctx* ctx, int on)
 
 int l3d_match_view(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors, float sigma_p, float sigma_a, l3d_match_result* result)
 {
-    return guarded(ctx, [&]() { return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, true); });
+    const int rc = guarded(ctx, [&]() { return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, true); });
+    if (rc && ctx && ctx->world > 1) ctx->comm_broken = true;
+    return rc;
 }
 int l3d_match_view_resident(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors, float sigma_p, float sigma_a, l3d_match_result* result)
 {
-    return guarded(ctx, [&]() { return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, false); });
+    const int rc = guarded(ctx, [&]() { return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, false); });
+    if (rc && ctx && ctx->world > 1) ctx->comm_broken = true;
+    return rc;
 }
 
 int l3d_unproject(l3d_ctx* ctx, size_t n, const l3d_hypothesis_in* in, l3d_segment3d* out)

@@ -468,6 +468,7 @@ struct Line3D::Impl
         // spent inside the calls alone (t_matching_calls) would leave out the host's own share of the loop
         const double t_match0 = now_s();
         if (l3d_set_stage_timing(ctx, stage_timing ? 1 : 0) || l3d_mark(ctx, 0)) fail("l3d_set_stage_timing");
+        if (getenv("L3D_PROFILE")) l3d_debug_chain_times(ctx, stage_timing ? 1 : 0, 0);
         // Which neighbours a view pair-tests and to which it hands its matches depends only on the
         // neighbour graph and the view order (line3D.cc:732-736, 844-845, 875-881): work the whole
         // schedule out first and announce it, so the library can batch the pair tests.
@@ -505,7 +506,7 @@ struct Line3D::Impl
         }
         for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it) {
             const unsigned vid = it->first;
-            std::cout << prefix << "matching image [" << vid << "] with " << it->second.size() << " VNs" << std::endl;
+            std::cout << prefix << "matching image [" << vid << "] with " << it->second.size() << " VNs\n";      // (no flush per view: the loop runs beside the GPU)
             if (it->second.empty() || !my_views.count(vid)) continue;
             ViewData* v = views[vid];
             std::vector<l3d_neighbor>& nb = schedule[vid];
@@ -534,7 +535,7 @@ struct Line3D::Impl
             // the records stay in the library's pinned memory (l3d_retain_results) and are filed after the loop, on
             // all cores, while nothing else waits for them: the GPU is not held up by the host's bookkeeping
             if (!measure_only && !match_only && (res.filtered || res.n_filtered == 0)) { ViewRecords vr = {vid, v->index, res.scored != 0, res.filtered, res.n_filtered, &it->second}; view_records.push_back(vr); }
-            else { std::vector<BestMatch>& bm = best[vid]; bm.assign(v->segs.size(), BestMatch()); for (size_t s = 0; s < bm.size(); ++s) bm[s].has = false; }
+            else if (!measure_only && !match_only) { std::vector<BestMatch>& bm = best[vid]; bm.assign(v->segs.size(), BestMatch()); for (size_t s = 0; s < bm.size(); ++s) bm[s].has = false; }      // (the later stages do not run in the measuring modes)
             for (size_t c = 0; c < it->second.size(); ++c) {                                                                        // :875-881
                 const unsigned n = it->second[c];
                 matched[vid].insert(n);
@@ -544,8 +545,15 @@ struct Line3D::Impl
         { float span = 0.f; if (l3d_mark(ctx, 1) || l3d_marks_elapsed(ctx, &span)) fail("l3d_mark"); stats.t_matching_device += double(span) * 1e-3; }   // CUDA events around the whole loop
         stats.t_matching += now_s() - t_match0;
         if (getenv("L3D_PROFILE")) {
-            double hs[4]; l3d_debug_host_times(ctx, hs);
-            std::cerr << "[prof] matching " << (now_s() - t_match0) * 1e3 << " ms: host enqueue " << hs[0] * 1e3 << " ms, waiting " << hs[1] * 1e3 << " ms, collecting " << hs[2] * 1e3 << " ms, " << hs[3] << " groups" << std::endl;
+            double hs[8]; l3d_debug_host_times(ctx, hs);
+            if (stage_timing) {
+                double cm[24]; l3d_debug_chain_times(ctx, 0, cm);
+                static const char* nm[15] = {"", "gather_counts", "scan", "fill", "bucket", "score", "reduce", "filter", "push", "allreduce", "hist", "scan2", "scatter", "finish", "gather"};
+                std::cerr << "[prof] chain ms:";
+                for (int k = 1; k < 15; ++k) std::cerr << " " << nm[k] << " " << cm[k];
+                std::cerr << std::endl;
+            }
+            std::cerr << "[prof] matching " << (now_s() - t_match0) * 1e3 << " ms: host enqueue " << hs[0] * 1e3 << " ms, waiting " << hs[1] * 1e3 << " ms, collecting " << hs[2] * 1e3 << " ms, helper " << hs[4] * 1e3 << " ms, foreground pair tests " << hs[5] * 1e3 << " ms, totals " << hs[6] * 1e3 << " ms, " << hs[3] << " groups" << std::endl;
         }
     }
 
