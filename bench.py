@@ -51,9 +51,30 @@ UNIT = "pairs/s"
 # (0.125 B) and reads the hoisted segments once per tile; bench.py scales the captured figure to the launch it times.
 PRETEST_TRAFFIC_PER_PAIR = (23.44e6 + 35.02e6) / 7.345e8
 
-# bounded CPU samples of the named workloads: the first views of the scene, all neighbours of each other
-CPU_SAMPLE = {"C1": dict(views=24, neighbors=12), "C2": dict(views=5, neighbors=4), "C3": dict(views=5, neighbors=4),
-              "C4": dict(views=4, neighbors=3), "C5": dict(views=4, neighbors=-1)}
+# bounded CPU samples of the named workloads: the first views of the scene, all neighbours of each other.  C2/C3 keep
+# the configuration's k = 12 (13 views) and take every second segment of each view (they are sorted by length, so the
+# length distribution stays): 13 whole views are 80 s per step on 8 cores, and with every view a neighbour of every
+# other they have 5.5 scoring iterations per pair test against 2.55 in the whole scene -- the thinned sample has about
+# the whole scene's ratio.  C4's k = 20 would need 21 views, so its sample has k = 7 and says so.
+CPU_SAMPLE = {"C1": dict(views=24, neighbors=12, stride=1), "C2": dict(views=13, neighbors=12, stride=2), "C3": dict(views=13, neighbors=12, stride=2),
+              "C4": dict(views=8, neighbors=7, stride=2), "C5": dict(views=4, neighbors=-1, stride=1)}
+_SAMPLE_COUNTERS: dict = {}
+
+
+def full_config_reference(config: str):
+    """The reference's CPU build on the WHOLE configuration, timed once when the benchmark-size golden digests were made
+    (tests/golden/make_golden_big.py, in the build container): read from the digest file, not measured here."""
+    path = os.path.join(ROOT, "tests", "golden", f"big_{config.lower()}.npz")
+    if not os.path.exists(path):
+        return None
+    try:
+        d = np.load(path)
+        secs, thr = d["ref_seconds"], int(d["ref_threads"][0])
+        out = dict(seconds_matching=float(secs[0]), seconds_compute3Dmodel=float(secs[1]), threads=thr,
+                   where="build container, once, with the golden digests (tests/golden/make_golden_big.py)")
+        return out
+    except Exception:      # an older digest without timings
+        return None
 
 
 def scene_file(config: str, rank: int = 0) -> str:
@@ -113,12 +134,13 @@ def multi_scene_file(config: str, n: int) -> str:
 def sample_scene_file(config: str) -> tuple[str, dict]:
     s = CPU_SAMPLE[config]
     full = scenes.read_scene(scene_file(config))
-    sub = scenes.Scene(views=full.views[: s["views"]], name=f"{config}-sample")
-    path = os.path.join(tempfile.gettempdir(), f"l3d_scene_{config}_sample{s['views']}.scn")
+    sub = scenes.Scene(views=[scenes.View(v.id, v.width, v.height, v.K, v.R, v.t, np.ascontiguousarray(v.segs[:: s["stride"]]), v.wps) for v in full.views[: s["views"]]],
+                       name=f"{config}-sample")
+    path = os.path.join(tempfile.gettempdir(), f"l3d_scene_{config}_sample{s['views']}s{s['stride']}.scn")
     if not os.path.exists(path):
         scenes.write_scene(sub, path)
     n = [v.segs.shape[0] for v in sub.views]
-    desc = dict(views=len(sub.views), segments_per_view=int(np.mean(n)), neighbors=s["neighbors"])
+    desc = dict(views=len(sub.views), segments_per_view=int(np.mean(n)), neighbors=s["neighbors"], stride=s["stride"])
     return path, desc
 
 
@@ -173,15 +195,18 @@ def run_cpu(config: str, threads: int, prefer_ref: bool = True) -> dict:
         t0 = time.perf_counter()
         n, tm, _ = refrun.run_scene(path, None, threads=threads, **params)
         wall = time.perf_counter() - t0
-        _, _, ct, _ = oracle_py.run_scene(path, None, threads=threads, **params)
+        if path not in _SAMPLE_COUNTERS:           # (once per sample: the counters do not change between steps)
+            _SAMPLE_COUNTERS[path] = oracle_py.run_scene(path, None, threads=threads, **params)[2]
+        ct = _SAMPLE_COUNTERS[path]
         kind, secs = "reference", tm["matching"]
     else:
         t0 = time.perf_counter()
         n, tm, ct, _ = oracle_py.run_scene(path, None, threads=threads, **params)
         wall = time.perf_counter() - t0
         kind, secs = "port", tm["matching"]
-    return dict(value=ct["pair_tests"] / max(secs, 1e-9), unit=UNIT, cores=threads, kind=kind,
-                sample=f"first {desc['views']} views of {config} (~{desc['segments_per_view']} segments/view, k={desc['neighbors']}): "
+    k_full = scenes.CONFIGS[config]["k"]
+    return dict(value=ct["pair_tests"] / max(secs, 1e-9), unit=UNIT, cores=threads, kind=kind, same_k=desc["neighbors"] == k_full,
+                sample=f"first {desc['views']} views of {config}" + (f", every {desc['stride']}. segment" if desc["stride"] > 1 else "") + f" (~{desc['segments_per_view']} segments/view, k={desc['neighbors']}): "
                        f"{int(ct['pair_tests'])} pair tests, {int(ct['score_iters'])} scoring iterations, {secs:.2f} s in matching+scoring",
                 pair_tests=int(ct["pair_tests"]), seconds=secs, wall_seconds=wall)
 
@@ -208,7 +233,10 @@ def reference_arm(args) -> None:
         per_step.append(cb["seconds"])
     ms = 1e3 * float(np.mean(per_step))
     value = cb["pair_tests"] / (ms * 1e-3)
-    cb = dict(value=value, unit=UNIT, cores=cb["cores"], kind=cb["kind"], sample=cb["sample"])
+    cb = dict(value=value, unit=UNIT, cores=cb["cores"], kind=cb["kind"], sample=cb["sample"], same_k=cb["same_k"])
+    full = full_config_reference(args.config)
+    if full:
+        cb["full_config"] = full
     c = scenes.CONFIGS[args.config]
     out = dict(impl="reference", metric=METRIC, value=value, unit=UNIT, n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
                ms_per_step=ms, higher_is_better=True, scaling="weak" if (args.gpus <= 1 or args.weak) else "strong", vs_baseline=None, dtype="f32", data="synthetic",
@@ -359,7 +387,8 @@ def ours(args) -> None:
                     traffic_note="ncu dram bytes of one captured batch (profiles/r2_kernels.md) scaled by pair tests to this launch",
                     peak_source="FFMA-chain microkernel run in this process (l3d_measure_fp32_peak: 16 chains per thread, operands in registers); MEASURED_PEAKS.json has no FP32 figure",
                     peak_fp32x2=fp32x2_peak, peak_nominal=fp32_nominal, frac_of_nominal=achieved / fp32_nominal,
-                    algorithmic_flops_per_launch=PRETEST_FLOPS * st_prof["pair_tests"], launches_per_step=1, kernel_ms_per_launch=1e3 * t_kp,
+                    algorithmic_flops_per_launch=PRETEST_FLOPS * st_prof["pair_tests"], launches_per_step=1, launches_note="the timing pass runs the whole step's pair tests as ONE batch (one k_pretest launch); the timed steps cut them into about eight",
+                    kernel_ms_per_launch=1e3 * t_kp,
                     fma_pipe_instr_per_pair=PRETEST_INSTR,
                     exact_kernel_ms=1e3 * t_ke, pretest2_kernel_ms=1e3 * float(st_prof["t_k_pretest2"]), kernel_ms_overlapped=dict(k_pretest=1e3 * t_kp_ov, k_exact_flat=1e3 * t_ke_ov), stages_ms={k[2:]: 1e3 * v for k, v in stage.items()},
                     stages_note="device ms per stage, and the kernels' own times, from one extra pass with CUDA events between the stages and "
@@ -370,7 +399,12 @@ def ours(args) -> None:
                     hbm_peak_gbs=peaks.get("hbm_gbs"))
     cb = run_cpu(args.config, os.cpu_count() or 1) if world == 1 else None
     if cb:
-        cb = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        cb = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "same_k")}
+        full = full_config_reference(args.config)
+        if full:                                     # the whole configuration, timed once in the build container (not on this box)
+            full["value"] = float(tot_pairs / max(world, 1)) / full["seconds_matching"] if not strong and world == 1 else None
+            full["unit"] = UNIT
+            cb["full_config"] = full
 
     value = tot_pairs / t_max
     out = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * t_max,

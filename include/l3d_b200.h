@@ -144,6 +144,10 @@ typedef struct {
     float median_depth;      /* cudawrapper.cu:1066-1076                                  */
     const l3d_match* filtered;
 } l3d_match_result;
+/* Limits: at most 1600 neighbours per view (the scoring kernel keeps one maximum per (camera, hypothesis) in shared
+ * memory); a batch of pair tests holds at most 65 535 (view, neighbour) jobs and 2^31 - 65 536 candidates (batches are
+ * cut accordingly, see l3d_debug_set_candidate_limit); segments, matches and records of one view are counted with
+ * 32 bits.  Anything beyond fails with a message in l3d_last_error, never silently. */
 int l3d_match_view(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors,
                    float sigma_p, float sigma_a, l3d_match_result* result);
 /* Hands records to a view from outside: what the reference's host does when it loads the matches earlier views have
@@ -169,6 +173,11 @@ int l3d_retain_results(l3d_ctx* ctx, int on);
  * announced views must then be asked for in order, with the announced neighbours and the same sigmas throughout:
  * a call that deviates before the schedule has started voids the schedule, one that deviates while a view is
  * already running ahead fails (l3d_last_error says so; l3d_reset_matching starts over). */
+/* Tuning, read from the environment once per schedule (defaults are what bench.py measures): L3D_BATCH_DIV (about how
+ * many batches of pair tests a schedule is cut into, 8), L3D_GROUP_VIEWS (views of one dependency level per launch of
+ * the per-view kernels: 8, with several GPUs on one scene 16, at most 32), L3D_NO_OVERLAP=1 (pair tests of the next
+ * batch do not run beside the per-view work), L3D_BG_BLOCKS (blocks per SM the pair-test kernels may take while they
+ * run beside it, 0 = no cap), L3D_P1_ROWS (source rows per block of the level-1 pre-test, 512). */
 typedef struct { int32_t view; int32_t n_neighbors; const l3d_neighbor* neighbors; } l3d_view_plan;
 int l3d_plan_matching(l3d_ctx* ctx, int n_views, const l3d_view_plan* plans);
 /* Tests only: pair tests per batch of the next announced schedules (0 = automatic: about an eighth of the schedule,
@@ -296,7 +305,7 @@ int l3d_debug_math(l3d_ctx* ctx, int which, int n, const float* in, float* out);
 int l3d_debug_host_times(l3d_ctx* ctx, double out[8]);
 /* With on != 0 and l3d_set_stage_timing, a CUDA event follows every kernel of the per-view chain; out (may be NULL)
  * receives the device ms since the last call, summed over the groups: [1] gather_counts [2] scan [3] fill [4] bucket
- * [5] score [6] reduce [7] filter [8] push [9] all-reduce [10] hist [11] scan [12] scatter [13] finish [14] gather. */
+ * [5] score [6] reduce [7] filter [8] push [9] signal + waiting for the other ranks' flags [10] hist [11] scan [12] scatter [13] finish [14] gather. */
 int l3d_debug_chain_times(l3d_ctx* ctx, int on, double out[24]);
 /* Number of kernels this library has launched on the context since creation. */
 uint64_t l3d_kernel_launches(const l3d_ctx* ctx);

@@ -1520,7 +1520,9 @@ __global__ void k_mr_signal(const VArgs* __restrict__ all, int n_views, MrPeers 
 // waits for the flags of all ranks; gives up after about ten seconds and says so in *fault (the host reports it)
 __global__ void k_mr_wait(const unsigned char* __restrict__ window, int W, unsigned seq, int* __restrict__ fault)
 {
-    L3D_PDL_PROLOGUE();
+    // The next kernel's blocks are let onto the SMs only when the flags have arrived (at the end of this kernel): while
+    // this rank waits for the slowest one they would sit there idle, in the way of the next batch's pair tests.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int r = threadIdx.x;
     if (r < W) {
         const volatile unsigned* flag = reinterpret_cast<const volatile unsigned*>(window + MR_FLAGS_OFF) + r;

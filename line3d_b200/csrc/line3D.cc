@@ -548,7 +548,7 @@ struct Line3D::Impl
             double hs[8]; l3d_debug_host_times(ctx, hs);
             if (stage_timing) {
                 double cm[24]; l3d_debug_chain_times(ctx, 0, cm);
-                static const char* nm[15] = {"", "gather_counts", "scan", "fill", "bucket", "score", "reduce", "filter", "push", "allreduce", "hist", "scan2", "scatter", "finish", "gather"};
+                static const char* nm[15] = {"", "gather_counts", "scan", "fill", "bucket", "score", "reduce", "filter", "push", "wait", "hist", "scan2", "scatter", "finish", "gather"};
                 std::cerr << "[prof] chain ms:";
                 for (int k = 1; k < 15; ++k) std::cerr << " " << nm[k] << " " << cm[k];
                 std::cerr << std::endl;
