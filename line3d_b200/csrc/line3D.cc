@@ -932,17 +932,38 @@ struct Line3D::Impl
         stats.t_clustering += now_s() - tc;
         // line3D.cc:1306-1368
         const double tl = now_s();
-        std::map<unsigned, std::vector<int> > clusters; std::map<unsigned, std::set<unsigned> > cams;
-        for (int n = 0; n < n_nodes; ++n) { unsigned cl = unsigned(find(n)); clusters[cl].push_back(hyp_of_node[n]); cams[cl].insert(hyps[hyp_of_node[n]].cam); }
-        if (verbose) std::cout << prefix << "#clusters_total:  " << clusters.size() << std::endl;
-        // the clusters are independent (alignCluster only reads shared state): fitted on all cores, emitted in map order
+        // the clusters as ranges of one array, in ascending order of their root node (the reference's std::map order),
+        // members in node order; no per-node map or set operations
+        std::vector<int> root(static_cast<size_t>(n_nodes));
+        for (int n = 0; n < n_nodes; ++n) root[n] = find(n);
+        std::vector<size_t> cbeg(size_t(n_nodes) + 1, 0);
+        for (int n = 0; n < n_nodes; ++n) ++cbeg[size_t(root[n]) + 1];
+        for (int r = 0; r < n_nodes; ++r) cbeg[size_t(r) + 1] += cbeg[r];
+        std::vector<int> members(static_cast<size_t>(n_nodes));
+        {
+            std::vector<size_t> cur(cbeg.begin(), cbeg.end() - 1);
+            for (int n = 0; n < n_nodes; ++n) members[cur[root[n]]++] = hyp_of_node[n];
+        }
+        std::vector<int> todo;                                   // roots of the non-empty clusters
+        for (int r = 0; r < n_nodes; ++r) if (cbeg[size_t(r) + 1] > cbeg[r]) todo.push_back(r);
+        if (verbose) std::cout << prefix << "#clusters_total:  " << todo.size() << std::endl;
+        // the clusters are independent (alignCluster only reads shared state): fitted on all cores, emitted in order.
+        // Only clusters seen by at least four cameras are fitted (line3D.cc:1334).
         unsigned valid = 0;
         {
-            std::vector<const std::vector<int>*> todo;
-            for (std::map<unsigned, std::vector<int> >::iterator c = clusters.begin(); c != clusters.end(); ++c)
-                if (cams[c->first].size() >= 4) todo.push_back(&c->second);
             std::vector<std::list<L3DSegment2D> > s2(todo.size()); std::vector<std::list<std::pair<V3, V3> > > s3(todo.size());
-            auto work = [&](size_t t0, size_t step) { for (size_t k = t0; k < todo.size(); k += step) alignCluster(*todo[k], s3[k], s2[k]); };
+            auto work = [&](size_t t0, size_t step) {
+                std::vector<unsigned> seen;
+                for (size_t k = t0; k < todo.size(); k += step) {
+                    const int* mem = members.data() + cbeg[todo[k]]; const size_t m = cbeg[size_t(todo[k]) + 1] - cbeg[todo[k]];
+                    if (m < 4) continue;
+                    seen.clear();
+                    for (size_t q = 0; q < m; ++q) seen.push_back(hyps[mem[q]].cam);
+                    std::sort(seen.begin(), seen.end());
+                    if (std::unique(seen.begin(), seen.end()) - seen.begin() < 4) continue;
+                    alignCluster(mem, m, s3[k], s2[k]);
+                }
+            };
             const size_t nt = std::max<size_t>(1, std::min<size_t>(host_threads(), todo.size()));
             std::vector<std::thread> pool;
             for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t, nt);
@@ -956,10 +977,10 @@ struct Line3D::Impl
     }
 
     // line3D.cc:1371-1389, 1392-1451, 1454-1476, 1479-1597
-    void alignCluster(const std::vector<int>& members, std::list<std::pair<V3, V3> >& seg3D, std::list<L3DSegment2D>& seg2D)
+    void alignCluster(const int* members, size_t n_members, std::list<std::pair<V3, V3> >& seg3D, std::list<L3DSegment2D>& seg2D)
     {
         // the reference keys the cluster's segments by (cam, seg); equal keys cannot occur
-        std::vector<int> order(members);
+        std::vector<int> order(members, members + n_members);
         std::sort(order.begin(), order.end(), [&](int a, int b) { return seg_key(hyps[a].cam, hyps[a].seg) < seg_key(hyps[b].cam, hyps[b].seg); });
         const int m = int(order.size());
         if (m == 0) return;
