@@ -226,6 +226,31 @@ int l3d_comm_destroy(l3d_ctx* ctx);
 int l3d_match_view_resident(l3d_ctx* ctx, int view, int n_neighbors, const l3d_neighbor* neighbors,
                             float sigma_p, float sigma_a, l3d_match_result* result);
 
+/* ---- in front of the pair tests: the neighbour graph and the fundamental matrices.
+ *      l3d_camera is a view's calibration as the host holds it (FP64, row-major; C = -R^T t as the host computed it).
+ *      Both calls evaluate the host code's formulas in the host code's order of operations with individually rounded
+ *      FP64 operations, so the results are the host code's, bit for bit.
+ *
+ *      l3d_visual_neighbors replaces the selection loop of Line3D::findVisualNeighbors (line3D.cc:498-546): for every
+ *      view the co-visible views (ascending view index) and their similarities (line3D.cc:483-495) are passed in CSR
+ *      form; a co-visible view is kept if its camera centre is farther than min_baseline from the view's and from that
+ *      of every view kept before it, the kept ones are ranked by similarity (descending, stable), cut to k (k <= 0:
+ *      all) and returned in ascending order: count[v] of them at neighbors[start[v]...].
+ *
+ *      l3d_fundamentals replaces Line3D::fundamental (line3D.cc:1949-1993) for a list of (source, neighbour) index
+ *      pairs: R = R2 R1^T, t = t2 - R t1, F = K2^-T [t]x R K1^-1; 9 doubles per pair, row-major. */
+typedef struct { double K[9]; double R[9]; double t[3]; double C[3]; } l3d_camera;
+int l3d_visual_neighbors(l3d_ctx* ctx, int n_views, const l3d_camera* cameras, const int32_t* start /* n_views + 1 */,
+                         const int32_t* other, const float* similarity, float min_baseline, int k,
+                         int32_t* count /* n_views */, int32_t* neighbors /* start[n_views] */);
+int l3d_fundamentals(l3d_ctx* ctx, int n_views, const l3d_camera* cameras, size_t n_pairs, const int32_t* pairs /* 2 per pair */,
+                     double* F /* 9 per pair */);
+/* Tests only: the same source compiled for the host (no GPU needed), so that the arithmetic can be checked against the
+ * reference's numbers in the CPU test suite.  Not used by the product. */
+int l3d_debug_visual_neighbors_host(int n_views, const l3d_camera* cameras, const int32_t* start, const int32_t* other,
+                                    const float* similarity, float min_baseline, int k, int32_t* count, int32_t* neighbors);
+int l3d_debug_fundamentals_host(int n_views, const l3d_camera* cameras, size_t n_pairs, const int32_t* pairs, double* F);
+
 /* ---- hypotheses: replaces L3DView::unprojectSegment (view.cc:302-342), FP64 on device.
  *      The n hypotheses stay resident for l3d_affinity. */
 typedef struct { int32_t view; int32_t seg; float depth1, depth2; } l3d_hypothesis_in;

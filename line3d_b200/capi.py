@@ -75,6 +75,10 @@ def lib():
             f.restype = C.c_int; f.argtypes = [vp, C.c_int, C.c_int, C.POINTER(Neighbor), C.c_float, C.c_float, C.POINTER(MatchResult)]
         L.l3d_reset_matching.restype = C.c_int; L.l3d_reset_matching.argtypes = [vp]
         L.l3d_unproject.restype = C.c_int; L.l3d_unproject.argtypes = [vp, C.c_size_t, vp, vp]
+        L.l3d_visual_neighbors.restype = C.c_int; L.l3d_visual_neighbors.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_float, C.c_int, vp, vp]
+        L.l3d_fundamentals.restype = C.c_int; L.l3d_fundamentals.argtypes = [vp, C.c_int, vp, C.c_size_t, vp, vp]
+        L.l3d_debug_visual_neighbors_host.restype = C.c_int; L.l3d_debug_visual_neighbors_host.argtypes = [C.c_int, vp, vp, vp, vp, C.c_float, C.c_int, vp, vp]
+        L.l3d_debug_fundamentals_host.restype = C.c_int; L.l3d_debug_fundamentals_host.argtypes = [C.c_int, vp, C.c_size_t, vp, vp]
         L.l3d_affinity.restype = C.c_int; L.l3d_affinity.argtypes = [vp, vp, C.c_size_t, vp, C.c_float, vp]
         L.l3d_diffuse.restype = C.c_int; L.l3d_diffuse.argtypes = [vp, C.c_int, C.c_size_t, vp, vp]
         L.l3d_last_timings.restype = C.c_int; L.l3d_last_timings.argtypes = [vp, C.POINTER(C.c_float)]
@@ -93,11 +97,42 @@ def lib():
 
 
 EXPORTS = ["l3d_create", "l3d_destroy", "l3d_last_error", "l3d_collinearity", "l3d_collinearity_prealloc", "l3d_set_views", "l3d_match_view",
-           "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_debug_set_batch_pairs", "l3d_comm_unique_id", "l3d_comm_init", "l3d_comm_destroy", "l3d_debug_host_times", "l3d_debug_chain_times", "l3d_debug_set_score_block", "l3d_diffuse_stats", "l3d_deliver", "l3d_candidate_buffer", "l3d_affinity_edges", "l3d_debug_set_pretest", "l3d_debug_set_candidate_limit", "l3d_measure_fp32x2_peak", "l3d_reset_matching", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
+           "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_debug_set_batch_pairs", "l3d_comm_unique_id", "l3d_comm_init", "l3d_comm_destroy", "l3d_debug_host_times", "l3d_debug_chain_times", "l3d_debug_set_score_block", "l3d_diffuse_stats", "l3d_deliver", "l3d_candidate_buffer", "l3d_affinity_edges", "l3d_debug_set_pretest", "l3d_debug_set_candidate_limit", "l3d_measure_fp32x2_peak", "l3d_reset_matching", "l3d_visual_neighbors", "l3d_fundamentals", "l3d_debug_visual_neighbors_host", "l3d_debug_fundamentals_host", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
            "l3d_last_timings", "l3d_last_kernel_timings", "l3d_set_stage_timing", "l3d_mark", "l3d_marks_elapsed", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math", "l3d_flush_l2"]
 
 
 COMM_ID_BYTES = 128
+
+
+CAMERA_DOUBLES = 24        # l3d_camera: K[9], R[9], t[3], C[3]
+
+
+def _geometry_args(cameras, start, other, similarity):
+    cams = np.ascontiguousarray(cameras, dtype=np.float64).reshape(-1, CAMERA_DOUBLES)
+    start = np.ascontiguousarray(start, dtype=np.int32); other = np.ascontiguousarray(other, dtype=np.int32)
+    sim = np.ascontiguousarray(similarity, dtype=np.float32)
+    assert start.shape[0] == cams.shape[0] + 1 and other.shape[0] == sim.shape[0] == int(start[-1])
+    return cams, start, other, sim
+
+
+def visual_neighbors_host(cameras, start, other, similarity, min_baseline: float, k: int):
+    """l3d_debug_visual_neighbors_host: the neighbour selection compiled for the host (tests; no GPU needed).  Returns a
+    list of int32 arrays, one per view."""
+    cams, start, other, sim = _geometry_args(cameras, start, other, similarity)
+    count = np.zeros(cams.shape[0], np.int32); out = np.zeros(max(other.shape[0], 1), np.int32)
+    if lib().l3d_debug_visual_neighbors_host(cams.shape[0], cams.ctypes.data, start.ctypes.data, other.ctypes.data, sim.ctypes.data, min_baseline, k, count.ctypes.data, out.ctypes.data) != 0:
+        raise L3DError("l3d_debug_visual_neighbors_host: bad arguments")
+    return [out[start[v]: start[v] + count[v]].copy() for v in range(cams.shape[0])]
+
+
+def fundamentals_host(cameras, pairs) -> np.ndarray:
+    """l3d_debug_fundamentals_host: F (n, 3, 3) float64 for (source, neighbour) index pairs, on the host (tests)."""
+    cams = np.ascontiguousarray(cameras, dtype=np.float64).reshape(-1, CAMERA_DOUBLES)
+    pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+    F = np.zeros((pairs.shape[0], 3, 3), np.float64)
+    if lib().l3d_debug_fundamentals_host(cams.shape[0], cams.ctypes.data, pairs.shape[0], pairs.ctypes.data, F.ctypes.data) != 0:
+        raise L3DError("l3d_debug_fundamentals_host: bad arguments")
+    return F
 
 
 def comm_unique_id() -> bytes:
@@ -133,6 +168,20 @@ class Context:
     def _check(self, rc):
         if rc != 0:
             raise L3DError(self._L.l3d_last_error(self._h).decode())
+
+    # ---- neighbour graph and fundamental matrices ------------------------------------------
+    def visual_neighbors(self, cameras, start, other, similarity, min_baseline: float, k: int):
+        cams, start, other, sim = _geometry_args(cameras, start, other, similarity)
+        count = np.zeros(cams.shape[0], np.int32); out = np.zeros(max(other.shape[0], 1), np.int32)
+        self._check(self._L.l3d_visual_neighbors(self._h, cams.shape[0], cams.ctypes.data, start.ctypes.data, other.ctypes.data, sim.ctypes.data, min_baseline, k, count.ctypes.data, out.ctypes.data))
+        return [out[start[v]: start[v] + count[v]].copy() for v in range(cams.shape[0])]
+
+    def fundamentals(self, cameras, pairs) -> np.ndarray:
+        cams = np.ascontiguousarray(cameras, dtype=np.float64).reshape(-1, CAMERA_DOUBLES)
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+        F = np.zeros((pairs.shape[0], 3, 3), np.float64)
+        self._check(self._L.l3d_fundamentals(self._h, cams.shape[0], cams.ctypes.data, pairs.shape[0], pairs.ctypes.data, F.ctypes.data))
+        return F
 
     # ---- collinearity ----------------------------------------------------------------
     def collinearity(self, segs: np.ndarray, s: float = 2.0) -> np.ndarray:

@@ -46,6 +46,7 @@ using namespace l3d;
 #include "l3d_multigpu.cuh"
 #include "l3d_collinearity.cuh"
 #include "l3d_postprocess.cuh"
+#include "l3d_geometry.cuh"
 
 // ---- host side: state, phase A, phase B, schedule ----
 #include "l3d_context.h"
@@ -170,6 +171,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->h_filtered.release(); ctx->h_ints.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
     ctx->h_cands.release(); ctx->d_cands.release(); ctx->d_hscore.release(); ctx->d_ew.release(); ctx->d_ecnt.release(); ctx->d_eoff.release(); ctx->d_kept.release(); ctx->h_kept.release(); ctx->d_ekeys.release(); ctx->d_eorder.release(); ctx->h_eorder.release();
+    ctx->d_geo_cams.release(); ctx->d_geo_start.release(); ctx->d_geo_other.release(); ctx->d_geo_ids.release(); ctx->d_geo_count.release(); ctx->d_geo_sim.release(); ctx->d_geo_sims.release(); ctx->d_geo_pairs.release(); ctx->d_geo_F.release();
     ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release(); ctx->d_rdd.release(); ctx->h_rdd.release();
     for (int k = 0; k < 2; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -470,6 +472,96 @@ int l3d_match_view_resident(l3d_ctx* ctx, int view, int n_neighbors, const l3d_n
     const int rc = guarded(ctx, [&]() { return match_view_impl(ctx, view, n_neighbors, neighbors, sigma_p, sigma_a, result, false); });
     if (rc && ctx && ctx->world > 1) ctx->comm_broken = true;
     return rc;
+}
+
+// ---- the neighbour graph and the fundamental matrices (l3d_geometry.cuh) ----
+static const char* geometry_args_ok(int n_views, const l3d_camera* cams, const int32_t* start, const int32_t* other, const float* sim, const int32_t* count, const int32_t* out)
+{
+    if (n_views < 0 || (n_views > 0 && (!cams || !start || !count))) return "null argument";
+    if (n_views > 0 && start[0] != 0) return "start[0] must be 0";
+    for (int v = 0; v < n_views; ++v) if (start[v + 1] < start[v]) return "start must not decrease";
+    const int nnz = n_views > 0 ? start[n_views] : 0;
+    if (nnz > 0 && (!other || !sim || !out)) return "null argument";
+    for (int v = 0; v < n_views; ++v)
+        for (int q = start[v]; q < start[v + 1]; ++q) {
+            if (other[q] < 0 || other[q] >= n_views || other[q] == v) return "co-visible view index out of range";
+            if (q > start[v] && other[q - 1] >= other[q]) return "co-visible views must be in ascending order";
+        }
+    return nullptr;
+}
+
+int l3d_visual_neighbors(l3d_ctx* ctx, int n_views, const l3d_camera* cams, const int32_t* start, const int32_t* other, const float* similarity,
+                         float min_baseline, int k, int32_t* count, int32_t* neighbors)
+{
+    if (!ctx) return 1;
+    return guarded(ctx, [&]() -> int {
+        if (const char* bad = geometry_args_ok(n_views, cams, start, other, similarity, count, neighbors)) { ctx->err = std::string("l3d_visual_neighbors: ") + bad; return 1; }
+        if (n_views == 0) return 0;
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        cudaStream_t st = ctx->stream;
+        const size_t nnz = size_t(start[n_views]);
+        L3D_CUDA(ctx->d_geo_cams.ensure(size_t(n_views))); L3D_CUDA(ctx->d_geo_start.ensure(size_t(n_views) + 1)); L3D_CUDA(ctx->d_geo_count.ensure(size_t(n_views)));
+        L3D_CUDA(ctx->d_geo_other.ensure(std::max<size_t>(nnz, 1))); L3D_CUDA(ctx->d_geo_ids.ensure(std::max<size_t>(nnz, 1)));
+        L3D_CUDA(ctx->d_geo_sim.ensure(std::max<size_t>(nnz, 1))); L3D_CUDA(ctx->d_geo_sims.ensure(std::max<size_t>(nnz, 1)));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_geo_cams.p, cams, sizeof(l3d_camera) * size_t(n_views), cudaMemcpyHostToDevice, st));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_geo_start.p, start, sizeof(int) * (size_t(n_views) + 1), cudaMemcpyHostToDevice, st));
+        if (nnz) {
+            L3D_CUDA(cudaMemcpyAsync(ctx->d_geo_other.p, other, sizeof(int) * nnz, cudaMemcpyHostToDevice, st));
+            L3D_CUDA(cudaMemcpyAsync(ctx->d_geo_sim.p, similarity, sizeof(float) * nnz, cudaMemcpyHostToDevice, st));
+        }
+        k_visual_neighbors<<<(n_views + 63) / 64, 64, 0, st>>>(ctx->d_geo_cams.p, n_views, ctx->d_geo_start.p, ctx->d_geo_other.p, ctx->d_geo_sim.p, min_baseline, k,
+                                                            ctx->d_geo_count.p, ctx->d_geo_ids.p, ctx->d_geo_sims.p);
+        L3D_CUDA(cudaGetLastError());
+        ctx->launches += 1;
+        L3D_CUDA(cudaMemcpyAsync(count, ctx->d_geo_count.p, sizeof(int) * size_t(n_views), cudaMemcpyDeviceToHost, st));
+        if (nnz) L3D_CUDA(cudaMemcpyAsync(neighbors, ctx->d_geo_ids.p, sizeof(int) * nnz, cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaStreamSynchronize(st));
+        return 0;
+    });
+}
+
+int l3d_fundamentals(l3d_ctx* ctx, int n_views, const l3d_camera* cams, size_t n_pairs, const int32_t* pairs, double* F)
+{
+    if (!ctx) return 1;
+    return guarded(ctx, [&]() -> int {
+        if (n_pairs == 0) return 0;
+        if (n_views <= 0 || !cams || !pairs || !F) { ctx->err = "l3d_fundamentals: null argument"; return 1; }
+        for (size_t p = 0; p < 2 * n_pairs; ++p) if (pairs[p] < 0 || pairs[p] >= n_views) { ctx->err = "l3d_fundamentals: view index out of range"; return 1; }
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        cudaStream_t st = ctx->stream;
+        L3D_CUDA(ctx->d_geo_cams.ensure(size_t(n_views))); L3D_CUDA(ctx->d_geo_pairs.ensure(n_pairs)); L3D_CUDA(ctx->d_geo_F.ensure(9 * n_pairs));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_geo_cams.p, cams, sizeof(l3d_camera) * size_t(n_views), cudaMemcpyHostToDevice, st));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_geo_pairs.p, pairs, sizeof(int2) * n_pairs, cudaMemcpyHostToDevice, st));
+        k_fundamentals<<<unsigned((n_pairs + 127) / 128), 128, 0, st>>>(ctx->d_geo_cams.p, ctx->d_geo_pairs.p, n_pairs, ctx->d_geo_F.p);
+        L3D_CUDA(cudaGetLastError());
+        ctx->launches += 1;
+        L3D_CUDA(cudaMemcpyAsync(F, ctx->d_geo_F.p, sizeof(double) * 9 * n_pairs, cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaStreamSynchronize(st));
+        return 0;
+    });
+}
+
+int l3d_debug_visual_neighbors_host(int n_views, const l3d_camera* cams, const int32_t* start, const int32_t* other, const float* similarity,
+                                    float min_baseline, int k, int32_t* count, int32_t* neighbors)
+{
+    try {
+        if (geometry_args_ok(n_views, cams, start, other, similarity, count, neighbors)) return 1;
+        std::vector<float> sims(n_views > 0 ? size_t(start[n_views]) + 1 : 1);
+        for (int v = 0; v < n_views; ++v)
+            count[v] = geo_select_neighbors(cams, v, start[v + 1] - start[v], other + start[v], similarity + start[v], min_baseline, k, neighbors + start[v], sims.data() + start[v]);
+        return 0;
+    } catch (...) { return 1; }
+}
+
+int l3d_debug_fundamentals_host(int n_views, const l3d_camera* cams, size_t n_pairs, const int32_t* pairs, double* F)
+{
+    if (n_pairs == 0) return 0;
+    if (n_views <= 0 || !cams || !pairs || !F) return 1;
+    for (size_t p = 0; p < n_pairs; ++p) {
+        if (pairs[2 * p] < 0 || pairs[2 * p] >= n_views || pairs[2 * p + 1] < 0 || pairs[2 * p + 1] >= n_views) return 1;
+        geo_fundamental(cams[pairs[2 * p]], cams[pairs[2 * p + 1]], F + 9 * p);
+    }
+    return 0;
 }
 
 int l3d_unproject(l3d_ctx* ctx, size_t n, const l3d_hypothesis_in* in, l3d_segment3d* out)

@@ -285,41 +285,39 @@ struct Line3D::Impl
                 if (sim > L3D_EPS) view_sim[it->first][n->first] = sim;
             }
         }
-        // The views' neighbour lists are independent of each other: worked out on all cores (camera centres in a flat
-        // table instead of a map look-up per baseline -- the accepted-so-far test is quadratic in the co-visible views),
-        // reported in view order afterwards.
+        // The selection itself (baseline against the view and against the neighbours accepted so far, ranking by
+        // similarity, cut to k; line3D.cc:498-546) runs on the device for all views at once: l3d_visual_neighbors gets
+        // every view's co-visible views in ascending order with their similarities, in CSR form.
         std::vector<std::map<unsigned, std::map<unsigned, float> >::iterator> todo;
         for (std::map<unsigned, std::map<unsigned, float> >::iterator s = view_sim.begin(); s != view_sim.end(); ++s) { vn[s->first]; todo.push_back(s); }
-        const unsigned max_id = views.empty() ? 0u : views.rbegin()->first;
-        std::vector<V3> centre(size_t(max_id) + 1); std::vector<char> present(size_t(max_id) + 1, 0);
-        for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) { centre[it->first] = it->second->C; present[it->first] = 1; }
         std::vector<size_t> found(todo.size(), 0);
-        auto work = [&](size_t t0, size_t step) {
-            for (size_t q = t0; q < todo.size(); q += step) {
-                const unsigned sid = todo[q]->first;
-                if (sid > max_id || !present[sid]) continue;
-                std::vector<std::pair<unsigned, float> > cand;
-                for (std::map<unsigned, float>::iterator n = todo[q]->second.begin(); n != todo[q]->second.end(); ++n) {
-                    if (n->first > max_id || !present[n->first]) continue;
-                    if (!(float((centre[sid] - centre[n->first]).norm()) > min_baseline)) continue;
-                    bool ok = true;                          // baseline against the neighbours accepted so far, in id order (:514-522)
-                    for (size_t e = 0; e < cand.size() && ok; ++e) if (float((centre[cand[e].first] - centre[n->first]).norm()) <= min_baseline) ok = false;
-                    if (ok) cand.push_back(std::make_pair(n->first, n->second));
-                }
-                std::stable_sort(cand.begin(), cand.end(), [](const std::pair<unsigned, float>& a, const std::pair<unsigned, float>& b) { return a.second > b.second; });
-                if (matching_neighbors > 0 && int(cand.size()) > matching_neighbors) cand.resize(matching_neighbors);
-                std::vector<unsigned>& out = vn.find(sid)->second;
-                for (size_t e = 0; e < cand.size(); ++e) out.push_back(cand[e].first);
-                std::sort(out.begin(), out.end());
-                found[q] = cand.size();
-            }
-        };
         {
-            const size_t nt = std::max<size_t>(1, std::min<size_t>(host_threads(), todo.size()));
-            std::vector<std::thread> pool;
-            for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t, nt);
-            work(0, nt);
-            for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
+            std::map<unsigned, int> idx_of; std::vector<unsigned> id_of; std::vector<l3d_camera> cams;
+            for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) {
+                idx_of[it->first] = int(id_of.size()); id_of.push_back(it->first);
+                cams.push_back(camera_of(it->second));
+            }
+            const int nv = int(id_of.size());
+            std::vector<int32_t> start(size_t(nv) + 1, 0), other, count(static_cast<size_t>(nv), 0); std::vector<float> sim;
+            std::vector<int> todo_of(static_cast<size_t>(nv), -1);
+            for (size_t q = 0; q < todo.size(); ++q) { std::map<unsigned, int>::iterator f = idx_of.find(todo[q]->first); if (f != idx_of.end()) todo_of[f->second] = int(q); }
+            for (int v = 0; v < nv; ++v) {
+                if (todo_of[v] >= 0)
+                    for (std::map<unsigned, float>::iterator n = todo[todo_of[v]]->second.begin(); n != todo[todo_of[v]]->second.end(); ++n) {
+                        std::map<unsigned, int>::iterator f = idx_of.find(n->first);
+                        if (f == idx_of.end() || f->second == v) continue;          // a view that was never added has no camera
+                        other.push_back(f->second); sim.push_back(n->second);
+                    }
+                start[size_t(v) + 1] = int32_t(other.size());
+            }
+            std::vector<int32_t> out(std::max<size_t>(other.size(), 1));
+            if (l3d_visual_neighbors(ctx, nv, cams.data(), start.data(), other.data(), sim.data(), min_baseline, matching_neighbors, count.data(), out.data())) fail("l3d_visual_neighbors");
+            for (int v = 0; v < nv; ++v) {
+                if (todo_of[v] < 0) continue;
+                std::vector<unsigned>& lst = vn.find(id_of[v])->second;
+                for (int e = 0; e < count[v]; ++e) lst.push_back(id_of[out[size_t(start[v]) + e]]);      // ascending index = ascending id
+                found[todo_of[v]] = size_t(count[v]);
+            }
         }
         for (size_t q = 0; q < todo.size(); ++q) {
             std::cout << prefix << "setting VNs for image [" << todo[q]->first << "]" << std::endl;
@@ -419,17 +417,39 @@ struct Line3D::Impl
     V3 inverseTransform(const V3& P) { return tr_Rinv * (P * tr_scale_inv + tr_tneg); }              // line3D.cc:1782-1786
 
     // line3D.cc:1968-1993
-    M3 fundamental(unsigned a, unsigned b)
+    static l3d_camera camera_of(const ViewData* v)
     {
-        ViewData* v1 = views[a]; ViewData* v2 = views[b];
-        M3 R = v2->R * v1->R.transpose();
-        V3 t = v2->t - R * v1->t;
-        M3 T;
-        T(0,0) = 0.0; T(0,1) = -t.z(); T(0,2) = t.y();
-        T(1,0) = t.z(); T(1,1) = 0.0; T(1,2) = -t.x();
-        T(2,0) = -t.y(); T(2,1) = t.x(); T(2,2) = 0.0;
-        M3 E = T * R;
-        return v2->K.transpose().inverse() * E * v1->K.inverse();
+        l3d_camera c;
+        for (int r = 0; r < 3; ++r) { for (int k = 0; k < 3; ++k) { c.K[r * 3 + k] = v->K(r, k); c.R[r * 3 + k] = v->R(r, k); } c.t[r] = v->t(r); c.C[r] = v->C(r); }
+        return c;
+    }
+
+    // line3D.cc:1949-1993 for every pair the schedule needs and that is not known yet, in one call: the pair a view
+    // meets first is computed, the reverse pair gets the transpose (:1959-1962)
+    void prepareFundamentals()
+    {
+        std::vector<l3d_camera> cams; std::map<unsigned, int> idx_of;
+        for (std::map<unsigned, ViewData*>::iterator it = views.begin(); it != views.end(); ++it) { idx_of[it->first] = int(cams.size()); cams.push_back(camera_of(it->second)); }
+        std::vector<int32_t> pairs; std::vector<std::pair<unsigned, unsigned> > ids; std::set<std::pair<unsigned, unsigned> > fresh;
+        for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it) {
+            const unsigned vid = it->first;
+            if (it->second.empty() || !my_views.count(vid)) continue;
+            for (size_t c = 0; c < it->second.size(); ++c) {
+                const unsigned n = it->second[c];
+                if (fund[vid].find(n) != fund[vid].end() || fresh.count(std::make_pair(vid, n))) continue;
+                fresh.insert(std::make_pair(vid, n)); fresh.insert(std::make_pair(n, vid));
+                ids.push_back(std::make_pair(vid, n)); pairs.push_back(idx_of[vid]); pairs.push_back(idx_of[n]);
+            }
+        }
+        if (ids.empty()) return;
+        std::vector<double> F(9 * ids.size());
+        if (l3d_fundamentals(ctx, int(cams.size()), cams.data(), ids.size(), pairs.data(), F.data())) fail("l3d_fundamentals");
+        for (size_t p = 0; p < ids.size(); ++p) {
+            M3 Fm;
+            for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) Fm(r, c) = F[9 * p + size_t(r) * 3 + c];
+            M3 Ft = Fm.transpose();
+            fund[ids[p].first][ids[p].second] = Fm; fund[ids[p].second][ids[p].first] = Ft;
+        }
     }
 
     void uploadViews()
@@ -472,6 +492,7 @@ struct Line3D::Impl
         // Which neighbours a view pair-tests and to which it hands its matches depends only on the
         // neighbour graph and the view order (line3D.cc:732-736, 844-845, 875-881): work the whole
         // schedule out first and announce it, so the library can batch the pair tests.
+        prepareFundamentals();
         std::map<unsigned, std::vector<l3d_neighbor> > schedule;
         {
             std::map<unsigned, std::set<unsigned> > done;
@@ -482,7 +503,7 @@ struct Line3D::Impl
                 nb.resize(it->second.size());
                 for (size_t c = 0; c < it->second.size(); ++c) {
                     const unsigned n = it->second[c];
-                    if (fund[vid].find(n) == fund[vid].end()) { M3 F = fundamental(vid, n); M3 Ft = F.transpose(); fund[vid][n] = F; fund[n][vid] = Ft; }   // :1949-1965
+                    if (fund[vid].find(n) == fund[vid].end()) fail("fundamental matrix missing");                                          // (prepareFundamentals, :1949-1965)
                     const M3& F = fund[vid][n];
                     nb[c].view = views[n]->index;
                     for (int r = 0; r < 3; ++r) for (int cc = 0; cc < 3; ++cc) nb[c].F[r * 3 + cc] = float(F(r, cc));                    // :745

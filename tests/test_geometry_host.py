@@ -1,0 +1,139 @@
+"""The neighbour graph and the fundamental matrices (l3d_visual_neighbors, l3d_fundamentals) are one
+source compiled twice: for the device (the product) and for the host (l3d_debug_*_host).  Here, without a GPU, the host
+build is pinned against the oracle's dumps -- which are pinned against the reference's own sources: the fundamental
+matrices must come out bit for bit in FP64, the neighbour lists identical.  tests/test_gpu_end_to_end.py then checks the
+device build against the same dumps through Line3D."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from line3d_b200 import capi, scenes  # noqa: E402
+from oracle import oracle_py  # noqa: E402
+
+
+def cameras_from_dump(views):
+    """views.npy rows: id, median, k_upper, k_lower, spatial_k, C[3], RtKinv[9], P[12], K[9], R[9], t[3] (after the scene
+    normalisation, as the fundamental matrices see them)."""
+    cams = np.zeros((views.shape[0], capi.CAMERA_DOUBLES))
+    cams[:, 0:9] = views[:, 29:38]; cams[:, 9:18] = views[:, 38:47]; cams[:, 18:21] = views[:, 47:50]; cams[:, 21:24] = views[:, 5:8]
+    return cams
+
+
+@pytest.mark.parametrize("maker,kw,params", [
+    (scenes.tiny, dict(), dict(neighbors=5)),
+    (scenes.urban, dict(n_views=14, n_seg=60, seed=31, blocks=(2, 2)), dict(neighbors=4)),
+    (scenes.dense_dome, dict(n_views=12, n_seg=50, seed=5), dict(neighbors=-1)),
+])
+def test_fundamentals_host_build_equals_the_oracle_bit_for_bit(tmp_path, maker, kw, params):
+    scn = str(tmp_path / "s.scn")
+    scenes.write_scene(maker(**kw), scn)
+    d = str(tmp_path / "dump"); os.makedirs(d)
+    _, _, _, dm = oracle_py.run_scene(scn, d, **params)
+    views, fund = dm["views"], dm["fundamentals"]
+    assert fund.shape[0] > 0
+    index = {int(v): k for k, v in enumerate(views[:, 0])}
+    # the host computes F for (view, neighbour) when it first meets the pair, in view order, and files the transpose
+    # for the reverse pair (line3D.cc:1949-1965): which direction was computed follows from the neighbour lists
+    computed, have = [], set()
+    for a, b in dm["visual_neighbors"]:
+        a, b = int(a), int(b)
+        if (a, b) not in have:
+            computed.append((a, b)); have.add((a, b)); have.add((b, a))
+    assert len(have) == fund.shape[0]
+    F = capi.fundamentals_host(cameras_from_dump(views), np.array([[index[a], index[b]] for a, b in computed], np.int32))
+    got = {}
+    for (a, b), f in zip(computed, F):
+        got[(a, b)] = f; got[(b, a)] = f.T
+    for row in fund:
+        assert np.array_equal(got[(int(row[0]), int(row[1]))].ravel(), row[2:11])          # FP64, every bit
+
+
+def _centre(R, t):
+    """C = R^T (-t): the product accumulates from zero with ascending inner index (python floats are IEEE doubles)."""
+    out = []
+    for i in range(3):
+        s = 0.0
+        for k in range(3):
+            s = s + float(R[k][i]) * (-float(t[k]))
+        out.append(s)
+    return out
+
+
+def _similarities(sc):
+    """Line3D::processWorldpoints + the similarity of findVisualNeighbors (line3D.cc:236-281, 483-495), restated: the
+    counts are built incrementally in the order the images are added, and a worldpoint starts to count when its second
+    view arrives."""
+    wp2views, common, num = {}, {}, {}
+    def bump(a, b):
+        common.setdefault(a, {}); common.setdefault(b, {})
+        common[a][b] = common[a].get(b, 0) + 1; common[b][a] = common[b].get(a, 0) + 1
+    for v in sc.views:
+        num[v.id] = 0
+        for wp in v.wps.tolist():
+            seen = wp2views.setdefault(wp, {})
+            if len(seen) == 2:
+                v1, v2 = sorted(seen)
+                bump(v1, v2); num[v1] += 1; num[v2] += 1
+            if len(seen) >= 2:
+                for w in sorted(seen):
+                    bump(w, v.id)
+                num[v.id] += 1
+            seen[v.id] = True
+    sims = {}
+    for a in sorted(common):
+        for b in sorted(common[a]):
+            s = np.float32(2.0) * np.float32(common[a][b]) / np.float32(num[a] + num[b])
+            if s > 1e-12:
+                sims.setdefault(a, {})[b] = s
+    return sims
+
+
+@pytest.mark.parametrize("maker,kw,k,min_baseline", [
+    (scenes.tiny, dict(), 5, 0.25),
+    (scenes.urban, dict(n_views=14, n_seg=60, seed=31, blocks=(2, 2)), 4, 0.25),
+    (scenes.dense_dome, dict(n_views=12, n_seg=50, seed=5), -1, 0.25),
+    (scenes.urban, dict(n_views=16, n_seg=60, seed=9, blocks=(2, 2)), 6, 25.0),          # a baseline limit that actually rejects views
+    (scenes.dense_dome, dict(n_views=14, n_seg=50, seed=6), 5, 50.0),
+])
+def test_neighbour_selection_host_build_equals_the_oracle(tmp_path, maker, kw, k, min_baseline):
+    sc = maker(**kw)
+    scn = str(tmp_path / "s.scn")
+    scenes.write_scene(sc, scn)
+    d = str(tmp_path / "dump"); os.makedirs(d)
+    _, _, _, dm = oracle_py.run_scene(scn, d, neighbors=k, min_baseline=min_baseline)
+    want = {}
+    for a, b in dm["visual_neighbors"]:
+        want.setdefault(int(a), []).append(int(b))
+    ids = sorted(v.id for v in sc.views)
+    index = {vid: i for i, vid in enumerate(ids)}
+    by_id = {v.id: v for v in sc.views}
+    cams = np.zeros((len(ids), capi.CAMERA_DOUBLES))
+    for vid in ids:
+        v = by_id[vid]
+        cams[index[vid], 0:9] = np.asarray(v.K, np.float64).ravel(); cams[index[vid], 9:18] = np.asarray(v.R, np.float64).ravel()
+        cams[index[vid], 18:21] = np.asarray(v.t, np.float64).ravel(); cams[index[vid], 21:24] = _centre(np.asarray(v.R, np.float64), np.asarray(v.t, np.float64))
+    sims = _similarities(sc)
+    start, other, sim = [0], [], []
+    for vid in ids:
+        for o in sorted(sims.get(vid, {})):
+            other.append(index[o]); sim.append(sims[vid][o])
+        start.append(len(other))
+    got = capi.visual_neighbors_host(cams, start, other, sim, min_baseline, k)
+    got_by_id = {ids[i]: [ids[j] for j in lst] for i, lst in enumerate(got) if len(lst)}
+    assert got_by_id == want
+    if min_baseline > 1.0:                                    # the limit did something
+        unlimited = capi.visual_neighbors_host(cams, start, other, sim, 0.0, k)
+        assert any(len(a) != len(b) or (a != b).any() for a, b in zip(got, unlimited))
+
+
+def test_bad_arguments_are_refused():
+    cams = np.zeros((2, capi.CAMERA_DOUBLES))
+    with pytest.raises(capi.L3DError):
+        capi.visual_neighbors_host(cams, [0, 1, 2], [0, 0], [0.5, 0.5], 0.1, 3)       # a view listed as its own neighbour
+    with pytest.raises(capi.L3DError):
+        capi.fundamentals_host(cams, [[0, 2]])
