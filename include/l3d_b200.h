@@ -245,8 +245,20 @@ int l3d_visual_neighbors(l3d_ctx* ctx, int n_views, const l3d_camera* cameras, c
                          int32_t* count /* n_views */, int32_t* neighbors /* start[n_views] */);
 int l3d_fundamentals(l3d_ctx* ctx, int n_views, const l3d_camera* cameras, size_t n_pairs, const int32_t* pairs /* 2 per pair */,
                      double* F /* 9 per pair */);
+/* ---- after the clustering: the 3-D line of every cluster (line3D.cc:1306-1368, 1392-1451, 1479-1597).
+ *      A cluster is a list of hypotheses (indices into the array of the last l3d_unproject, which is still resident), in
+ *      (camera, segment) order, with the camera id of each; clusters are given in CSR form.  Per cluster: the end
+ *      points go back to world coordinates (`back`, line3D.cc:1782-1786), the line runs through their centroid along
+ *      the dominant direction of their scatter matrix, and a sweep along it emits every stretch over which at least
+ *      three cameras see the line.  seg_count[c] segments of 6 doubles (start, end) are written at segments +
+ *      6 * start[c]; a cluster of m hypotheses yields at most m.  FP64, the host code's order of operations. */
+typedef struct { double scale_inv; double Rinv[9]; double tneg[3]; } l3d_similarity;      /* P -> Rinv (P * scale_inv + tneg) */
+int l3d_fit_lines(l3d_ctx* ctx, const l3d_similarity* back, int n_clusters, const int32_t* start /* n_clusters + 1 */,
+                  const int32_t* member, const uint32_t* member_camera, int32_t* seg_count /* n_clusters */, double* segments /* 6 * start[n_clusters] */);
 /* Tests only: the same source compiled for the host (no GPU needed), so that the arithmetic can be checked against the
  * reference's numbers in the CPU test suite.  Not used by the product. */
+int l3d_debug_fit_lines_host(const l3d_similarity* back, int n_clusters, const int32_t* start, const double* points /* 6 per member: P1, P2 */,
+                             const uint32_t* member_camera, int32_t* seg_count, double* segments);
 int l3d_debug_visual_neighbors_host(int n_views, const l3d_camera* cameras, const int32_t* start, const int32_t* other,
                                     const float* similarity, float min_baseline, int k, int32_t* count, int32_t* neighbors);
 int l3d_debug_fundamentals_host(int n_views, const l3d_camera* cameras, size_t n_pairs, const int32_t* pairs, double* F);

@@ -78,6 +78,8 @@ def lib():
         L.l3d_visual_neighbors.restype = C.c_int; L.l3d_visual_neighbors.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_float, C.c_int, vp, vp]
         L.l3d_fundamentals.restype = C.c_int; L.l3d_fundamentals.argtypes = [vp, C.c_int, vp, C.c_size_t, vp, vp]
         L.l3d_debug_visual_neighbors_host.restype = C.c_int; L.l3d_debug_visual_neighbors_host.argtypes = [C.c_int, vp, vp, vp, vp, C.c_float, C.c_int, vp, vp]
+        L.l3d_fit_lines.restype = C.c_int; L.l3d_fit_lines.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, vp]
+        L.l3d_debug_fit_lines_host.restype = C.c_int; L.l3d_debug_fit_lines_host.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp]
         L.l3d_debug_fundamentals_host.restype = C.c_int; L.l3d_debug_fundamentals_host.argtypes = [C.c_int, vp, C.c_size_t, vp, vp]
         L.l3d_affinity.restype = C.c_int; L.l3d_affinity.argtypes = [vp, vp, C.c_size_t, vp, C.c_float, vp]
         L.l3d_diffuse.restype = C.c_int; L.l3d_diffuse.argtypes = [vp, C.c_int, C.c_size_t, vp, vp]
@@ -97,7 +99,7 @@ def lib():
 
 
 EXPORTS = ["l3d_create", "l3d_destroy", "l3d_last_error", "l3d_collinearity", "l3d_collinearity_prealloc", "l3d_set_views", "l3d_match_view",
-           "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_debug_set_batch_pairs", "l3d_comm_unique_id", "l3d_comm_init", "l3d_comm_destroy", "l3d_debug_host_times", "l3d_debug_chain_times", "l3d_debug_set_score_block", "l3d_diffuse_stats", "l3d_deliver", "l3d_candidate_buffer", "l3d_affinity_edges", "l3d_debug_set_pretest", "l3d_debug_set_candidate_limit", "l3d_measure_fp32x2_peak", "l3d_reset_matching", "l3d_visual_neighbors", "l3d_fundamentals", "l3d_debug_visual_neighbors_host", "l3d_debug_fundamentals_host", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
+           "l3d_match_view_resident", "l3d_retain_results", "l3d_plan_matching", "l3d_debug_set_batch_pairs", "l3d_comm_unique_id", "l3d_comm_init", "l3d_comm_destroy", "l3d_debug_host_times", "l3d_debug_chain_times", "l3d_debug_set_score_block", "l3d_diffuse_stats", "l3d_deliver", "l3d_candidate_buffer", "l3d_affinity_edges", "l3d_debug_set_pretest", "l3d_debug_set_candidate_limit", "l3d_measure_fp32x2_peak", "l3d_reset_matching", "l3d_visual_neighbors", "l3d_fundamentals", "l3d_debug_visual_neighbors_host", "l3d_debug_fundamentals_host", "l3d_fit_lines", "l3d_debug_fit_lines_host", "l3d_unproject", "l3d_affinity", "l3d_diffuse",
            "l3d_last_timings", "l3d_last_kernel_timings", "l3d_set_stage_timing", "l3d_mark", "l3d_marks_elapsed", "l3d_measure_fp32_peak", "l3d_kernel_launches", "l3d_debug_math", "l3d_flush_l2"]
 
 
@@ -133,6 +135,27 @@ def fundamentals_host(cameras, pairs) -> np.ndarray:
     if lib().l3d_debug_fundamentals_host(cams.shape[0], cams.ctypes.data, pairs.shape[0], pairs.ctypes.data, F.ctypes.data) != 0:
         raise L3DError("l3d_debug_fundamentals_host: bad arguments")
     return F
+
+
+def similarity_back(scale: float, R, t) -> np.ndarray:
+    """l3d_similarity for the way back from the normalised scene (line3D.cc:1782-1786): 1 / scale, R^T, -t."""
+    R = np.asarray(R, np.float64).reshape(3, 3); t = np.asarray(t, np.float64).reshape(3)
+    return np.concatenate([[1.0 / float(scale)], R.T.ravel(), -t]).astype(np.float64)
+
+
+def _split_segments(start, count, seg):
+    return [seg[start[c]: start[c] + count[c]].copy() for c in range(len(count))]
+
+
+def fit_lines_host(back, start, points, member_camera):
+    """l3d_debug_fit_lines_host: per cluster an (n, 6) float64 array of 3-D segments (tests; no GPU needed)."""
+    back = np.ascontiguousarray(back, np.float64); start = np.ascontiguousarray(start, np.int32)
+    points = np.ascontiguousarray(points, np.float64).reshape(-1, 6); cam = np.ascontiguousarray(member_camera, np.uint32)
+    assert points.shape[0] == cam.shape[0] == int(start[-1])
+    count = np.zeros(start.shape[0] - 1, np.int32); seg = np.zeros((max(points.shape[0], 1), 6), np.float64)
+    if lib().l3d_debug_fit_lines_host(back.ctypes.data, count.shape[0], start.ctypes.data, points.ctypes.data, cam.ctypes.data, count.ctypes.data, seg.ctypes.data) != 0:
+        raise L3DError("l3d_debug_fit_lines_host: bad arguments")
+    return _split_segments(start, count, seg)
 
 
 def comm_unique_id() -> bytes:
@@ -175,6 +198,14 @@ class Context:
         count = np.zeros(cams.shape[0], np.int32); out = np.zeros(max(other.shape[0], 1), np.int32)
         self._check(self._L.l3d_visual_neighbors(self._h, cams.shape[0], cams.ctypes.data, start.ctypes.data, other.ctypes.data, sim.ctypes.data, min_baseline, k, count.ctypes.data, out.ctypes.data))
         return [out[start[v]: start[v] + count[v]].copy() for v in range(cams.shape[0])]
+
+    def fit_lines(self, back, start, member, member_camera):
+        """l3d_fit_lines on the hypotheses of the last unproject(): per cluster an (n, 6) float64 array of 3-D segments."""
+        back = np.ascontiguousarray(back, np.float64); start = np.ascontiguousarray(start, np.int32)
+        member = np.ascontiguousarray(member, np.int32); cam = np.ascontiguousarray(member_camera, np.uint32)
+        count = np.zeros(start.shape[0] - 1, np.int32); seg = np.zeros((max(member.shape[0], 1), 6), np.float64)
+        self._check(self._L.l3d_fit_lines(self._h, back.ctypes.data, count.shape[0], start.ctypes.data, member.ctypes.data, cam.ctypes.data, count.ctypes.data, seg.ctypes.data))
+        return _split_segments(start, count, seg)
 
     def fundamentals(self, cameras, pairs) -> np.ndarray:
         cams = np.ascontiguousarray(cameras, dtype=np.float64).reshape(-1, CAMERA_DOUBLES)

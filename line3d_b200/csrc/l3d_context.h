@@ -139,6 +139,8 @@ struct l3d_ctx {
     bool comm_broken = false;          // a call failed while several ranks were at work: no collective step is attempted any more (the others may be gone)
     bool copies_pending = false, want_records = true;      // want_records: the current calls copy the output records to the host
     bool chain_prof = false; double chain_ms[24] = {};      // device ms per kernel of the per-view chain, summed over the groups (with stage timing)
+    // the clusters' 3-D lines (l3d_fit_lines): CSR of the clusters, and per member scratch (points, centred products, sweep state)
+    DBuf<int> d_fit_start, d_fit_count, d_fit_member, d_fit_camopen, d_fit_order; DBuf<unsigned> d_fit_cam; DBuf<unsigned char> d_fit_open; DBuf<double> d_fit_dbl; DBuf<float> d_fit_dist;
     // the neighbour graph and the fundamental matrices (l3d_visual_neighbors, l3d_fundamentals)
     DBuf<l3d_camera> d_geo_cams; DBuf<int> d_geo_start, d_geo_other, d_geo_ids, d_geo_count; DBuf<float> d_geo_sim, d_geo_sims; DBuf<int2> d_geo_pairs; DBuf<double> d_geo_F;
     double host_s[8] = {0, 0, 0, 0, 0, 0, 0, 0};      // host seconds in enqueue_group / finish_group (waiting) / finish_group (rest) / number of groups / waiting for the helper thread / pair tests in the foreground / totals over the ranks (l3d_debug_host_times)

@@ -171,6 +171,7 @@ void l3d_destroy(l3d_ctx* ctx)
     ctx->h_filtered.release(); ctx->h_ints.release();
     ctx->d_csegs.release(); ctx->d_cbits.release(); ctx->d_ccnt.release(); ctx->d_coff.release(); ctx->d_cpairs.release(); ctx->h_cpairs.release();
     ctx->h_cands.release(); ctx->d_cands.release(); ctx->d_hscore.release(); ctx->d_ew.release(); ctx->d_ecnt.release(); ctx->d_eoff.release(); ctx->d_kept.release(); ctx->h_kept.release(); ctx->d_ekeys.release(); ctx->d_eorder.release(); ctx->h_eorder.release();
+    ctx->d_fit_start.release(); ctx->d_fit_count.release(); ctx->d_fit_member.release(); ctx->d_fit_cam.release(); ctx->d_fit_camopen.release(); ctx->d_fit_open.release(); ctx->d_fit_dbl.release(); ctx->d_fit_order.release(); ctx->d_fit_dist.release();
     ctx->d_geo_cams.release(); ctx->d_geo_start.release(); ctx->d_geo_other.release(); ctx->d_geo_ids.release(); ctx->d_geo_count.release(); ctx->d_geo_sim.release(); ctx->d_geo_sims.release(); ctx->d_geo_pairs.release(); ctx->d_geo_F.release();
     ctx->d_hyp.release(); ctx->d_hin.release(); ctx->d_hout.release(); ctx->d_pairs.release(); ctx->d_aff.release(); ctx->d_medians.release(); ctx->d_flush.release(); ctx->d_rdd.release(); ctx->h_rdd.release();
     for (int k = 0; k < 2; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
@@ -539,6 +540,65 @@ int l3d_fundamentals(l3d_ctx* ctx, int n_views, const l3d_camera* cams, size_t n
         L3D_CUDA(cudaStreamSynchronize(st));
         return 0;
     });
+}
+
+static const char* clusters_ok(const l3d_similarity* tr, int n_clusters, const int32_t* start, const void* a, const uint32_t* cam, const int32_t* count, const double* seg)
+{
+    if (n_clusters < 0 || !tr || (n_clusters > 0 && (!start || !count))) return "null argument";
+    if (n_clusters > 0 && start[0] != 0) return "start[0] must be 0";
+    for (int c = 0; c < n_clusters; ++c) if (start[c + 1] < start[c]) return "start must not decrease";
+    if (n_clusters > 0 && start[n_clusters] > 0 && (!a || !cam || !seg)) return "null argument";
+    for (int c = 0; c < n_clusters; ++c)
+        for (int q = start[c] + 1; q < start[c + 1]; ++q) if (cam[q - 1] > cam[q]) return "the members of a cluster must be in (camera, segment) order";
+    return nullptr;
+}
+
+int l3d_fit_lines(l3d_ctx* ctx, const l3d_similarity* back, int n_clusters, const int32_t* start, const int32_t* member, const uint32_t* member_camera,
+                  int32_t* seg_count, double* segments)
+{
+    if (!ctx) return 1;
+    return guarded(ctx, [&]() -> int {
+        if (const char* bad = clusters_ok(back, n_clusters, start, member, member_camera, seg_count, segments)) { ctx->err = std::string("l3d_fit_lines: ") + bad; return 1; }
+        if (n_clusters == 0) return 0;
+        const size_t total = size_t(start[n_clusters]);
+        for (size_t q = 0; q < total; ++q) if (member[q] < 0 || size_t(member[q]) >= ctx->n_hyp) { ctx->err = "l3d_fit_lines: hypothesis index out of range (indices refer to the last l3d_unproject)"; return 1; }
+        L3D_CUDA(cudaSetDevice(ctx->device));
+        cudaStream_t st = ctx->stream;
+        const size_t t1 = std::max<size_t>(total, 1);
+        L3D_CUDA(ctx->d_fit_start.ensure(size_t(n_clusters) + 1)); L3D_CUDA(ctx->d_fit_count.ensure(size_t(n_clusters)));
+        L3D_CUDA(ctx->d_fit_member.ensure(t1)); L3D_CUDA(ctx->d_fit_cam.ensure(t1)); L3D_CUDA(ctx->d_fit_camopen.ensure(t1)); L3D_CUDA(ctx->d_fit_open.ensure(t1));
+        L3D_CUDA(ctx->d_fit_dbl.ensure(4 * 6 * t1)); L3D_CUDA(ctx->d_fit_order.ensure(2 * t1)); L3D_CUDA(ctx->d_fit_dist.ensure(2 * t1));
+        L3D_CUDA(cudaMemcpyAsync(ctx->d_fit_start.p, start, sizeof(int) * (size_t(n_clusters) + 1), cudaMemcpyHostToDevice, st));
+        if (total) {
+            L3D_CUDA(cudaMemcpyAsync(ctx->d_fit_member.p, member, sizeof(int) * total, cudaMemcpyHostToDevice, st));
+            L3D_CUDA(cudaMemcpyAsync(ctx->d_fit_cam.p, member_camera, sizeof(unsigned) * total, cudaMemcpyHostToDevice, st));
+        }
+        double* pts = ctx->d_fit_dbl.p; double* A = pts + 6 * t1; double* G = A + 6 * t1; double* seg = G + 6 * t1;
+        k_fit_lines<<<n_clusters, FIT_T, 0, st>>>(*back, n_clusters, ctx->d_fit_start.p, ctx->d_fit_member.p, ctx->d_fit_cam.p, ctx->d_hyp.p, pts, A, G,
+                                                        ctx->d_fit_order.p, ctx->d_fit_dist.p, ctx->d_fit_open.p, ctx->d_fit_camopen.p, ctx->d_fit_count.p, seg);
+        L3D_CUDA(cudaGetLastError());
+        ctx->launches += 1;
+        L3D_CUDA(cudaMemcpyAsync(seg_count, ctx->d_fit_count.p, sizeof(int) * size_t(n_clusters), cudaMemcpyDeviceToHost, st));
+        if (total) L3D_CUDA(cudaMemcpyAsync(segments, seg, sizeof(double) * 6 * total, cudaMemcpyDeviceToHost, st));
+        L3D_CUDA(cudaStreamSynchronize(st));
+        return 0;
+    });
+}
+
+int l3d_debug_fit_lines_host(const l3d_similarity* back, int n_clusters, const int32_t* start, const double* points, const uint32_t* member_camera,
+                             int32_t* seg_count, double* segments)
+{
+    try {
+        if (clusters_ok(back, n_clusters, start, points, member_camera, seg_count, segments)) return 1;
+        for (int c = 0; c < n_clusters; ++c) {
+            const int b = start[c], m = start[c + 1] - b;
+            std::vector<double> A(size_t(m) * 6 + 1), G(size_t(m) * 6 + 1); std::vector<int> order(size_t(m) * 2 + 1), cam_open(size_t(m) + 1);
+            std::vector<float> dist(size_t(m) * 2 + 1); std::vector<unsigned char> open_line(size_t(m) + 1);
+            seg_count[c] = geo_fit_cluster(*back, m, points + size_t(b) * 6, member_camera + b, A.data(), G.data(), order.data(), dist.data(), open_line.data(), cam_open.data(),
+                                           segments + size_t(b) * 6);
+        }
+        return 0;
+    } catch (...) { return 1; }
 }
 
 int l3d_debug_visual_neighbors_host(int n_views, const l3d_camera* cams, const int32_t* start, const int32_t* other, const float* similarity,

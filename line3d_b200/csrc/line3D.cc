@@ -968,11 +968,12 @@ struct Line3D::Impl
         std::vector<int> todo;                                   // roots of the non-empty clusters
         for (int r = 0; r < n_nodes; ++r) if (cbeg[size_t(r) + 1] > cbeg[r]) todo.push_back(r);
         if (verbose) std::cout << prefix << "#clusters_total:  " << todo.size() << std::endl;
-        // the clusters are independent (alignCluster only reads shared state): fitted on all cores, emitted in order.
-        // Only clusters seen by at least four cameras are fitted (line3D.cc:1334).
+        // Only clusters seen by at least four cameras are fitted (line3D.cc:1334).  The host puts each one's hypotheses in
+        // (camera, segment) order (the reference's key order; equal keys cannot occur), on all cores; the fits themselves
+        // run on the device, all clusters in one call (l3d_fit_lines, on the hypotheses l3d_unproject left there).
         unsigned valid = 0;
         {
-            std::vector<std::list<L3DSegment2D> > s2(todo.size()); std::vector<std::list<std::pair<V3, V3> > > s3(todo.size());
+            std::vector<std::vector<int> > sorted(todo.size());
             auto work = [&](size_t t0, size_t step) {
                 std::vector<unsigned> seen;
                 for (size_t k = t0; k < todo.size(); k += step) {
@@ -982,7 +983,8 @@ struct Line3D::Impl
                     for (size_t q = 0; q < m; ++q) seen.push_back(hyps[mem[q]].cam);
                     std::sort(seen.begin(), seen.end());
                     if (std::unique(seen.begin(), seen.end()) - seen.begin() < 4) continue;
-                    alignCluster(mem, m, s3[k], s2[k]);
+                    sorted[k].assign(mem, mem + m);
+                    std::sort(sorted[k].begin(), sorted[k].end(), [&](int a, int b) { return seg_key(hyps[a].cam, hyps[a].seg) < seg_key(hyps[b].cam, hyps[b].seg); });
                 }
             };
             const size_t nt = std::max<size_t>(1, std::min<size_t>(host_threads(), todo.size()));
@@ -990,67 +992,32 @@ struct Line3D::Impl
             for (size_t t = 1; t < nt; ++t) pool.emplace_back(work, t, nt);
             work(0, nt);
             for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
-            for (size_t k = 0; k < todo.size(); ++k) if (!s3[k].empty()) { result.push_back(L3DFinalLine3D(s2[k], s3[k])); ++valid; }
+            std::vector<size_t> fitted;                         // indices into todo
+            std::vector<int32_t> start(1, 0), member; std::vector<uint32_t> member_cam;
+            for (size_t k = 0; k < todo.size(); ++k) {
+                if (sorted[k].empty()) continue;
+                fitted.push_back(k);
+                for (size_t q = 0; q < sorted[k].size(); ++q) { member.push_back(sorted[k][q]); member_cam.push_back(hyps[sorted[k][q]].cam); }
+                start.push_back(int32_t(member.size()));
+            }
+            std::vector<int32_t> count(fitted.size(), 0); std::vector<double> segs(6 * std::max<size_t>(member.size(), 1));
+            l3d_similarity back;
+            back.scale_inv = tr_scale_inv;
+            for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) back.Rinv[r * 3 + c] = tr_Rinv(r, c); back.tneg[r] = tr_tneg(r); }
+            if (!fitted.empty() && l3d_fit_lines(ctx, &back, int(fitted.size()), start.data(), member.data(), member_cam.data(), count.data(), segs.data())) fail("l3d_fit_lines");
+            for (size_t f = 0; f < fitted.size(); ++f) {
+                if (count[f] <= 0) continue;
+                std::list<std::pair<V3, V3> > s3; std::list<L3DSegment2D> s2;
+                const double* sg = segs.data() + 6 * size_t(start[f]);
+                for (int e = 0; e < count[f]; ++e) s3.push_back(std::make_pair(V3(sg[6 * e], sg[6 * e + 1], sg[6 * e + 2]), V3(sg[6 * e + 3], sg[6 * e + 4], sg[6 * e + 5])));
+                const std::vector<int>& ord = sorted[fitted[f]];
+                for (size_t q = 0; q < ord.size(); ++q) s2.push_back(L3DSegment2D(hyps[ord[q]].cam, hyps[ord[q]].seg));
+                result.push_back(L3DFinalLine3D(s2, s3)); ++valid;
+            }
         }
         if (verbose) std::cout << prefix << "#clusters_valid:  " << valid << std::endl;
         stats.t_lines += now_s() - tl;
         std::cout << prefix << result.size() << " 3D lines found!" << std::endl;
-    }
-
-    // line3D.cc:1371-1389, 1392-1451, 1454-1476, 1479-1597
-    void alignCluster(const int* members, size_t n_members, std::list<std::pair<V3, V3> >& seg3D, std::list<L3DSegment2D>& seg2D)
-    {
-        // the reference keys the cluster's segments by (cam, seg); equal keys cannot occur
-        std::vector<int> order(members, members + n_members);
-        std::sort(order.begin(), order.end(), [&](int a, int b) { return seg_key(hyps[a].cam, hyps[a].seg) < seg_key(hyps[b].cam, hyps[b].seg); });
-        const int m = int(order.size());
-        if (m == 0) return;
-        std::vector<V3> A1(m), A2(m);
-        for (int k = 0; k < m; ++k) { A1[k] = inverseTransform(hyps[order[k]].P1); A2[k] = inverseTransform(hyps[order[k]].P2); }
-        V3 P(0, 0, 0);
-        const int n = m * 2;
-        Eigen::MatrixXd g(3, n);
-        double szd = 0.0;
-        for (int k = 0; k < m; ++k) {
-            P += A1[k]; P += A2[k];
-            for (int r = 0; r < 3; ++r) { g(r, 2 * k) = A1[k](r); g(r, 2 * k + 1) = A2[k](r); }
-            szd += 2.0;
-        }
-        P /= szd;
-        Eigen::MatrixXd Cm = Eigen::MatrixXd::Identity(n, n) - (1.0 / double(n)) * Eigen::MatrixXd::Constant(n, n, 1.0);
-        Eigen::MatrixXd Scat = g * Cm * g.transpose();
-        Eigen::JacobiSVD<Eigen::MatrixXd> svd(Scat, Eigen::ComputeThinU);
-        Eigen::MatrixXd U = svd.matrixU(); Eigen::VectorXd S = svd.singularValues();
-        int mp; S.maxCoeff(&mp);
-        V3 dir(U(0, mp), U(1, mp), U(2, mp)); dir.normalize();
-        struct Pt { V3 P; unsigned seg3, cam; float dist; };
-        std::vector<Pt> pts;
-        V3 min_point(0.0, 0.0, 0.0), max_point(0.0, 0.0, 0.0);
-        double min_len = 0.0, max_len = 0.0;
-        for (int k = 0; k < m; ++k) {
-            V3 pr1 = P + (dir.dot(A1[k] - P) / (dir.norm() * dir.norm())) * dir;
-            V3 pr2 = P + (dir.dot(A2[k] - P) / (dir.norm() * dir.norm())) * dir;
-            double loc1 = dir.dot(P - pr1);
-            if (loc1 <= min_len) { min_len = loc1; min_point = pr1; }
-            if (loc1 >= max_len) { max_len = loc1; max_point = pr1; }
-            double loc2 = dir.dot(P - pr2);
-            if (loc2 <= min_len) { min_len = loc2; min_point = pr2; }
-            if (loc2 >= max_len) { max_len = loc2; max_point = pr2; }
-            Pt a; a.P = A1[k]; a.seg3 = unsigned(k); a.cam = hyps[order[k]].cam; a.dist = 0; Pt b = a; b.P = A2[k];
-            pts.push_back(a); pts.push_back(b);
-        }
-        for (size_t k = 0; k < pts.size(); ++k) pts[k].dist = float((pts[k].P - min_point).norm());
-        std::stable_sort(pts.begin(), pts.end(), [](const Pt& a, const Pt& b) { return a.dist < b.dist; });
-        std::map<unsigned, unsigned> open; std::set<unsigned> open_lines;
-        bool opened = false; V3 start(0, 0, 0);
-        for (size_t k = 0; k < pts.size(); ++k) {
-            const Pt& p = pts[k];
-            if (!open_lines.count(p.seg3)) { open_lines.insert(p.seg3); ++open[p.cam]; }
-            else { open_lines.erase(p.seg3); if (--open[p.cam] == 0) open.erase(p.cam); }
-            if (opened && open.size() < 3) { seg3D.push_back(std::make_pair(start, p.P)); opened = false; }
-            else if (!opened && open.size() >= 3) { start = p.P; opened = true; }
-        }
-        for (int k = 0; k < m; ++k) seg2D.push_back(L3DSegment2D(hyps[order[k]].cam, hyps[order[k]].seg));
     }
 };
 

@@ -131,6 +131,39 @@ def test_neighbour_selection_host_build_equals_the_oracle(tmp_path, maker, kw, k
         assert any(len(a) != len(b) or (a != b).any() for a, b in zip(got, unlimited))
 
 
+@pytest.mark.parametrize("maker,kw,params", [
+    (scenes.tiny, dict(), dict(neighbors=5)),
+    (scenes.tiny, dict(n_views=10, n_seg=200, seed=3), dict(neighbors=6, diffusion=True)),
+    (scenes.urban, dict(n_views=16, n_seg=150, seed=31, blocks=(2, 2)), dict(neighbors=6)),
+    (scenes.wireframe_building, dict(n_views=12, n_seg=200, seed=2), dict(neighbors=8)),
+    (scenes.wireframe_building, dict(n_views=24, n_seg=400, seed=4), dict(neighbors=12, threads=8)),      # clusters of up to 87 hypotheses, 11 segments on a line
+])
+def test_line_fit_host_build_equals_the_oracle_bit_for_bit(tmp_path, maker, kw, params):
+    """Every 3-D line the oracle emits, recomputed from its cluster (lines_seg2d), the hypotheses' end points
+    (best_match) and the scene normalisation (transform): same number of segments, every FP64 coordinate identical."""
+    scn = str(tmp_path / "s.scn")
+    scenes.write_scene(maker(**kw), scn)
+    d = str(tmp_path / "dump"); os.makedirs(d)
+    n_lines, _, _, dm = oracle_py.run_scene(scn, d, **params)
+    assert n_lines > 0
+    hyp = {(int(r[0]), int(r[1])): r[6:12] for r in dm["best_match"]}
+    tr = dm["transform"].ravel()
+    back = capi.similarity_back(tr[0], tr[1:10], tr[10:13])
+    start, pts, cams = [0], [], []
+    for li in range(n_lines):
+        rows = dm["lines_seg2d"][dm["lines_seg2d"][:, 0] == li]
+        for _, cam, seg in rows:
+            pts.append(hyp[(int(cam), int(seg))]); cams.append(int(cam))
+        start.append(len(cams))
+    got = capi.fit_lines_host(back, start, np.array(pts), cams)
+    total = 0
+    for li in range(n_lines):
+        want = dm["lines_seg3d"][dm["lines_seg3d"][:, 0] == li][:, 1:7]
+        assert got[li].shape == want.shape and np.array_equal(got[li].view(np.uint64), np.ascontiguousarray(want).view(np.uint64)), li
+        total += want.shape[0]
+    assert total == dm["lines_seg3d"].shape[0] > 0
+
+
 def test_bad_arguments_are_refused():
     cams = np.zeros((2, capi.CAMERA_DOUBLES))
     with pytest.raises(capi.L3DError):

@@ -66,6 +66,46 @@ def test_neighbour_selection_device_equals_host_build(n, k, baseline, seed):
         assert max(len(a) for a in got) <= k
 
 
+def _resident_hypotheses(ctx, rng, n_views, n_seg):
+    """Synthetic views and one hypothesis per segment, unprojected on the device (they stay resident); returns the
+    end points as l3d_unproject reports them and the camera of each hypothesis."""
+    views = []
+    for v in range(n_views):
+        q, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+        f = rng.uniform(900.0, 2000.0)
+        Kinv = np.linalg.inv(np.array([[f, 0.0, 640.0], [0.0, f, 480.0], [0.0, 0.0, 1.0]]))
+        segs = rng.uniform(0.0, 1200.0, size=(n_seg, 4)).astype(np.float32)
+        views.append(dict(id=v, segs=segs, RtKinv=q.T @ Kinv, C=rng.uniform(-2.0, 2.0, 3), P=np.zeros((3, 4)), spatial_k=0.01, k_lower=0.001, k_upper=0.002))
+    ctx.set_views(views)
+    hin = np.zeros(n_views * n_seg, capi.HYP_IN_DTYPE)
+    hin["view"] = np.repeat(np.arange(n_views), n_seg); hin["seg"] = np.tile(np.arange(n_seg), n_views)
+    hin["depth1"] = rng.uniform(1.0, 4.0, hin.shape[0]).astype(np.float32); hin["depth2"] = rng.uniform(1.0, 4.0, hin.shape[0]).astype(np.float32)
+    out = ctx.unproject(hin)
+    pts = np.concatenate([out["P1"], out["P2"]], axis=1)
+    return pts, hin["view"].astype(np.uint32)
+
+
+@pytest.mark.parametrize("n_views,n_seg,sizes,seed", [(6, 40, [4, 5, 9, 17, 30], 1), (12, 300, [4, 64, 200, 777, 1500, 33, 4], 2), (40, 50, [40] * 45 + [400], 3)])
+def test_line_fit_device_equals_host_build(n_views, n_seg, sizes, seed):
+    rng = np.random.default_rng(seed)
+    ctx = capi.Context(0)
+    try:
+        pts, cams = _resident_hypotheses(ctx, rng, n_views, n_seg)
+        start, member = [0], []
+        for m in sizes:                                   # clusters: random hypotheses, put in (camera, segment) order = index order
+            member += np.sort(rng.choice(pts.shape[0], size=m, replace=False)).tolist()
+            start.append(len(member))
+        back = capi.similarity_back(rng.uniform(0.05, 0.3), np.linalg.qr(rng.normal(size=(3, 3)))[0], rng.normal(size=3))
+        got = ctx.fit_lines(back, start, member, cams[member])
+    finally:
+        ctx.close()
+    want = capi.fit_lines_host(back, start, pts[member], cams[member])
+    assert len(got) == len(want) == len(sizes)
+    assert sum(w.shape[0] for w in want) > 0
+    for a, b in zip(got, want):
+        assert a.shape == b.shape and np.array_equal(a.view(np.uint64), b.view(np.uint64))
+
+
 def test_bad_arguments_are_reported():
     ctx = capi.Context(0)
     try:
