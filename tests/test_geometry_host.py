@@ -164,9 +164,34 @@ def test_line_fit_host_build_equals_the_oracle_bit_for_bit(tmp_path, maker, kw, 
     assert total == dm["lines_seg3d"].shape[0] > 0
 
 
+def test_line_fit_degenerate_clusters():
+    """No cluster at all; a cluster that fewer than three cameras see; hypotheses that are all the same point (zero
+    scatter: the direction falls back to the first axis); three cameras seeing one stretch give exactly one segment."""
+    back = capi.similarity_back(1.0, np.eye(3), np.zeros(3))
+    assert capi.fit_lines_host(back, [0], np.zeros((0, 6)), []) == []
+    two_cams = np.array([[0, 0, 0, 1, 0, 0], [0, 0.1, 0, 1, 0.1, 0]], float)
+    assert capi.fit_lines_host(back, [0, 2], two_cams, [0, 1])[0].shape == (0, 6)
+    same = np.tile(np.array([[1.0, 2.0, 3.0, 1.0, 2.0, 3.0]]), (4, 1))
+    got = capi.fit_lines_host(back, [0, 4], same, [0, 1, 2, 3])[0]
+    assert got.shape[0] <= 4 and np.isfinite(got).all()
+    three = np.array([[0, 0, 0, 4, 0, 0], [1, 0.01, 0, 3, 0.01, 0], [0.5, -0.01, 0, 3.5, -0.01, 0]], float)
+    seg = capi.fit_lines_host(back, [0, 3], three, [0, 1, 2])[0]
+    assert seg.shape == (1, 6)
+    # the stretch where all three are open: from x = 1 (the last to open) to the first to close, whichever end the sweep starts from
+    xs = sorted([seg[0, 0], seg[0, 3]])
+    assert xs == [1.0, 3.0]
+    # scaling and rotating the scene back changes the coordinates, not the structure
+    R = np.array([[0.0, -1.0, 0.0], [1.0, 0.0, 0.0], [0.0, 0.0, 1.0]])
+    seg2 = capi.fit_lines_host(capi.similarity_back(0.5, R, [1.0, 0.0, 0.0]), [0, 3], three, [0, 1, 2])[0]
+    assert seg2.shape == (1, 6)
+    assert np.allclose(np.linalg.norm(seg2[0, :3] - seg2[0, 3:]), 2.0 * np.linalg.norm(seg[0, :3] - seg[0, 3:]))
+
+
 def test_bad_arguments_are_refused():
     cams = np.zeros((2, capi.CAMERA_DOUBLES))
     with pytest.raises(capi.L3DError):
         capi.visual_neighbors_host(cams, [0, 1, 2], [0, 0], [0.5, 0.5], 0.1, 3)       # a view listed as its own neighbour
     with pytest.raises(capi.L3DError):
         capi.fundamentals_host(cams, [[0, 2]])
+    with pytest.raises(capi.L3DError):                      # members not in camera order
+        capi.fit_lines_host(capi.similarity_back(1.0, np.eye(3), np.zeros(3)), [0, 2], np.zeros((2, 6)), [3, 1])
