@@ -208,7 +208,10 @@ def run_cpu(config: str, threads: int, prefer_ref: bool = True) -> dict:
     return dict(value=ct["pair_tests"] / max(secs, 1e-9), unit=UNIT, cores=threads, kind=kind, same_k=desc["neighbors"] == k_full,
                 sample=f"first {desc['views']} views of {config}" + (f", every {desc['stride']}. segment" if desc["stride"] > 1 else "") + f" (~{desc['segments_per_view']} segments/view, k={desc['neighbors']}): "
                        f"{int(ct['pair_tests'])} pair tests, {int(ct['score_iters'])} scoring iterations, {secs:.2f} s in matching+scoring",
-                pair_tests=int(ct["pair_tests"]), seconds=secs, wall_seconds=wall)
+                pair_tests=int(ct["pair_tests"]), seconds=secs, wall_seconds=wall,
+                # the reference's host stages on the same sample (line3D.cc, sparsematrix.cc, clustering.cc: everything of
+                # compute3Dmodel that is not compute_pairwise_matches), same cores
+                compute3Dmodel_seconds=float(tm["compute3Dmodel"]), host_stages_seconds=max(float(tm["compute3Dmodel"]) - float(secs), 0.0))
 
 
 def default_config(args) -> str:
@@ -233,7 +236,8 @@ def reference_arm(args) -> None:
         per_step.append(cb["seconds"])
     ms = 1e3 * float(np.mean(per_step))
     value = cb["pair_tests"] / (ms * 1e-3)
-    cb = dict(value=value, unit=UNIT, cores=cb["cores"], kind=cb["kind"], sample=cb["sample"], same_k=cb["same_k"])
+    cb = dict(value=value, unit=UNIT, cores=cb["cores"], kind=cb["kind"], sample=cb["sample"], same_k=cb["same_k"],
+              compute3Dmodel_seconds=cb["compute3Dmodel_seconds"], host_stages_seconds=cb["host_stages_seconds"])
     full = full_config_reference(args.config)
     if full:
         cb["full_config"] = full
@@ -399,7 +403,7 @@ def ours(args) -> None:
                     hbm_peak_gbs=peaks.get("hbm_gbs"))
     cb = run_cpu(args.config, os.cpu_count() or 1) if world == 1 else None
     if cb:
-        cb = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "same_k")}
+        cb = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "same_k", "compute3Dmodel_seconds", "host_stages_seconds")}
         full = full_config_reference(args.config)
         if full:                                     # the whole configuration, timed once in the build container (not on this box)
             full["value"] = float(tot_pairs / max(world, 1)) / full["seconds_matching"] if not strong and world == 1 else None
