@@ -187,6 +187,94 @@ def test_line_fit_degenerate_clusters():
     assert np.allclose(np.linalg.norm(seg2[0, :3] - seg2[0, 3:]), 2.0 * np.linalg.norm(seg[0, :3] - seg[0, 3:]))
 
 
+# ---- an independent restatement in plain Python floats (IEEE doubles, no contraction), on random inputs -------------
+def _mul33(a, b):
+    return [[sum_from_zero(a[i][k] * b[k][j] for k in range(3)) for j in range(3)] for i in range(3)]
+
+
+def sum_from_zero(terms):
+    s = 0.0
+    for t in terms:
+        s = s + t
+    return s
+
+
+def _inv33(m):
+    c00 = m[1][1] * m[2][2] - m[1][2] * m[2][1]
+    c01 = m[1][2] * m[2][0] - m[1][0] * m[2][2]
+    c02 = m[1][0] * m[2][1] - m[1][1] * m[2][0]
+    det = m[0][0] * c00 + m[0][1] * c01 + m[0][2] * c02
+    i = 1.0 / det
+    return [[c00 * i, (m[0][2] * m[2][1] - m[0][1] * m[2][2]) * i, (m[0][1] * m[1][2] - m[0][2] * m[1][1]) * i],
+            [c01 * i, (m[0][0] * m[2][2] - m[0][2] * m[2][0]) * i, (m[0][2] * m[1][0] - m[0][0] * m[1][2]) * i],
+            [c02 * i, (m[0][1] * m[2][0] - m[0][0] * m[2][1]) * i, (m[0][0] * m[1][1] - m[0][1] * m[1][0]) * i]]
+
+
+def _fundamental_py(c1, c2):
+    K1, R1, t1 = [c1[0:9].reshape(3, 3).tolist(), c1[9:18].reshape(3, 3).tolist(), c1[18:21].tolist()]
+    K2, R2, t2 = [c2[0:9].reshape(3, 3).tolist(), c2[9:18].reshape(3, 3).tolist(), c2[18:21].tolist()]
+    T_ = lambda m: [[m[j][i] for j in range(3)] for i in range(3)]
+    R = _mul33(R2, T_(R1))
+    t = [t2[i] - sum_from_zero(R[i][k] * t1[k] for k in range(3)) for i in range(3)]
+    T = [[0.0, -t[2], t[1]], [t[2], 0.0, -t[0]], [-t[1], t[0], 0.0]]
+    return _mul33(_mul33(_inv33(T_(K2)), _mul33(T, R)), _inv33(K1))
+
+
+def _random_cameras(n, rng, spread):
+    cams = np.zeros((n, capi.CAMERA_DOUBLES))
+    for v in range(n):
+        q, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+        f = rng.uniform(500.0, 3000.0)
+        K = np.array([[f, rng.normal(0, 0.5), rng.uniform(300, 2000)], [0.0, f * rng.uniform(0.9, 1.1), rng.uniform(200, 1500)], [0.0, 0.0, 1.0]])
+        C = rng.uniform(-spread, spread, 3)
+        cams[v, 0:9] = K.ravel(); cams[v, 9:18] = q.ravel(); cams[v, 18:21] = -q @ C; cams[v, 21:24] = C
+    return cams
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_fundamentals_host_build_equals_a_plain_python_restatement(seed):
+    rng = np.random.default_rng(seed)
+    cams = _random_cameras(12, rng, 25.0)
+    pairs = [(a, b) for a in range(12) for b in range(12) if a != b]
+    F = capi.fundamentals_host(cams, pairs)
+    for (a, b), f in zip(pairs, F):
+        want = np.array(_fundamental_py(cams[a], cams[b]))
+        assert np.array_equal(f.view(np.uint64), want.view(np.uint64)), (a, b)
+
+
+def _select_py(cams, v, other, sim, min_baseline, k):
+    def base(a, b):
+        s = 0.0
+        for i in range(3):
+            d = float(cams[a, 21 + i]) - float(cams[b, 21 + i])
+            s = s + d * d
+        return np.float32(np.sqrt(s))
+    mb = np.float32(min_baseline)
+    kept = []
+    for o, s in zip(other, sim):
+        if not base(v, o) > mb:
+            continue
+        if all(base(e, o) > mb for e, _ in kept):
+            kept.append((o, np.float32(s)))
+    kept.sort(key=lambda e: -e[1])               # python's sort is stable
+    if k > 0:
+        kept = kept[:k]
+    return sorted(o for o, _ in kept)
+
+
+@pytest.mark.parametrize("n,k,baseline,seed", [(10, 3, 5.0, 1), (40, 8, 9.0, 2), (40, -1, 0.0, 3), (25, 5, 30.0, 4)])
+def test_neighbour_selection_host_build_equals_a_plain_python_restatement(n, k, baseline, seed):
+    rng = np.random.default_rng(seed)
+    cams = _random_cameras(n, rng, 20.0)
+    start, other, sim = [0], [], []
+    for v in range(n):
+        o = np.sort(rng.choice([x for x in range(n) if x != v], size=int(rng.integers(0, n)), replace=False))
+        other += o.tolist(); sim += (rng.integers(1, 12, size=o.shape[0]).astype(np.float32) / np.float32(12.0)).tolist(); start.append(len(other))
+    got = capi.visual_neighbors_host(cams, start, other, sim, baseline, k)
+    for v in range(n):
+        assert got[v].tolist() == _select_py(cams, v, other[start[v]: start[v + 1]], sim[start[v]: start[v + 1]], baseline, k), v
+
+
 def test_bad_arguments_are_refused():
     cams = np.zeros((2, capi.CAMERA_DOUBLES))
     with pytest.raises(capi.L3DError):
