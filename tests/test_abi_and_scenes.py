@@ -55,6 +55,19 @@ def test_product_does_not_import_the_oracle():
             assert "oracle_py" not in txt and "liboracle" not in txt and "refrun" not in txt and "oracle/" not in txt.replace("oracle/ref_harness.cpp writes", ""), path
 
 
+def test_product_never_calls_the_host_builds_of_the_geometry_stages():
+    """l3d_debug_*_host (the FP64 geometry stages compiled for the host) exist for the CPU tests only: the C++ scaffold,
+    the operator binding and the Python driver call the device entry points."""
+    callers = [os.path.join(ROOT, "line3d_b200", "csrc", f) for f in ("line3D.cc", "line3D.h", "host_harness.cpp")]
+    callers += glob.glob(os.path.join(ROOT, "integration", "*")) + [os.path.join(ROOT, "line3d_b200", "host.py"), os.path.join(ROOT, "bench.py"), os.path.join(ROOT, "__graft_entry__.py")]
+    for path in callers:
+        txt = open(path, errors="ignore").read()
+        assert "_host(" not in txt.replace("host_threads(", "") or "l3d_debug_" not in txt, path
+    src = open(os.path.join(ROOT, "line3d_b200", "csrc", "line3D.cc")).read()
+    for name in ("l3d_visual_neighbors(ctx", "l3d_fundamentals(ctx", "l3d_fit_lines(ctx"):
+        assert name in src
+
+
 def test_scene_roundtrip_and_determinism(tmp_path):
     from line3d_b200 import scenes
     a = scenes.tiny(); b = scenes.tiny()
