@@ -138,7 +138,6 @@ struct Line3D::Impl
     std::map<unsigned, std::map<unsigned, bool> > wp2views;
     std::map<unsigned, std::vector<unsigned> > vn;                 // visual neighbours, ascending
     std::map<unsigned, std::map<unsigned, M3> > fund;
-    std::map<unsigned, std::set<unsigned> > matched;
 
     std::map<unsigned, std::vector<BestMatch> > best;              // per view, per segment
     struct PC { unsigned seg, tcam, tseg; };                          // (this view, seg) <-> (tcam, tseg), line3D.cc:861-865
@@ -163,11 +162,6 @@ struct Line3D::Impl
         std::string msg = std::string(what) + ": " + l3d_last_error(ctx);
         std::cerr << prefix << msg << std::endl;
         throw std::runtime_error(msg);
-    }
-    bool neighbour_of(unsigned a, unsigned b)      // b in VN(a)
-    {
-        std::map<unsigned, std::vector<unsigned> >::iterator it = vn.find(a);
-        return it != vn.end() && std::binary_search(it->second.begin(), it->second.end(), b);
     }
 
     // line3D.cc:1874-1935
@@ -495,25 +489,37 @@ struct Line3D::Impl
         prepareFundamentals();
         std::map<unsigned, std::vector<l3d_neighbor> > schedule;
         {
-            std::map<unsigned, std::set<unsigned> > done;
+            // done[x]: the views x has been paired with so far -- a std::set per view in the reference (matched_); here a
+            // sorted vector per view id, and the neighbour lists reachable by view id, so that the 10^4..10^5 membership
+            // tests of a large scene need no tree walks (the schedule is part of every step's matching time)
+            const size_t n_ids = id2idx.size();
+            std::vector<std::vector<unsigned> > done(n_ids);
+            std::vector<const std::vector<unsigned>*> vn_of(n_ids, (const std::vector<unsigned>*)0);
+            for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it) if (it->first < n_ids) vn_of[it->first] = &it->second;
+            auto has = [](const std::vector<unsigned>& s, unsigned x) { return std::binary_search(s.begin(), s.end(), x); };
+            auto put = [](std::vector<unsigned>& s, unsigned x) { std::vector<unsigned>::iterator p = std::lower_bound(s.begin(), s.end(), x); if (p == s.end() || *p != x) s.insert(p, x); };
+            auto nb_of = [&](unsigned a, unsigned b) { return a < n_ids && vn_of[a] && std::binary_search(vn_of[a]->begin(), vn_of[a]->end(), b); };      // b in VN(a)
             for (std::map<unsigned, std::vector<unsigned> >::iterator it = vn.begin(); it != vn.end(); ++it) {
                 const unsigned vid = it->first;
                 if (it->second.empty() || !my_views.count(vid)) continue;
+                if (vid >= n_ids) fail("matching: a view with neighbours that was never added");
                 std::vector<l3d_neighbor>& nb = schedule[vid];
                 nb.resize(it->second.size());
+                std::map<unsigned, M3>& fv = fund[vid];
                 for (size_t c = 0; c < it->second.size(); ++c) {
                     const unsigned n = it->second[c];
-                    if (fund[vid].find(n) == fund[vid].end()) fail("fundamental matrix missing");                                          // (prepareFundamentals, :1949-1965)
-                    const M3& F = fund[vid][n];
-                    nb[c].view = views[n]->index;
+                    std::map<unsigned, M3>::iterator f = fv.find(n);
+                    if (f == fv.end() || n >= n_ids || id2idx[n] < 0) fail("fundamental matrix missing");                                  // (prepareFundamentals, :1949-1965)
+                    const M3& F = f->second;
+                    nb[c].view = id2idx[n];
                     for (int r = 0; r < 3; ++r) for (int cc = 0; cc < 3; ++cc) nb[c].F[r * 3 + cc] = float(F(r, cc));                    // :745
-                    nb[c].to_be_matched = done[vid].count(n) ? 0 : 1;                                                                    // :732-736
-                    nb[c].deliver = (neighbour_of(n, vid) && !done[n].count(vid)) ? 1 : 0;                                               // :844-845
+                    nb[c].to_be_matched = has(done[vid], n) ? 0 : 1;                                                                     // :732-736
+                    nb[c].deliver = (nb_of(n, vid) && !has(done[n], vid)) ? 1 : 0;                                                       // :844-845
                 }
                 for (size_t c = 0; c < it->second.size(); ++c) {                                                                         // :875-881
                     const unsigned n = it->second[c];
-                    done[vid].insert(n);
-                    if (neighbour_of(n, vid)) done[n].insert(vid);
+                    put(done[vid], n);
+                    if (nb_of(n, vid)) put(done[n], vid);
                 }
             }
             std::vector<l3d_view_plan> plans;
@@ -557,11 +563,6 @@ struct Line3D::Impl
             // all cores, while nothing else waits for them: the GPU is not held up by the host's bookkeeping
             if (!measure_only && !match_only && (res.filtered || res.n_filtered == 0)) { ViewRecords vr = {vid, v->index, res.scored != 0, res.filtered, res.n_filtered, &it->second}; view_records.push_back(vr); }
             else if (!measure_only && !match_only) { std::vector<BestMatch>& bm = best[vid]; bm.assign(v->segs.size(), BestMatch()); for (size_t s = 0; s < bm.size(); ++s) bm[s].has = false; }      // (the later stages do not run in the measuring modes)
-            for (size_t c = 0; c < it->second.size(); ++c) {                                                                        // :875-881
-                const unsigned n = it->second[c];
-                matched[vid].insert(n);
-                if (neighbour_of(n, vid)) matched[n].insert(vid);
-            }
         }
         { float span = 0.f; if (l3d_mark(ctx, 1) || l3d_marks_elapsed(ctx, &span)) fail("l3d_mark"); stats.t_matching_device += double(span) * 1e-3; }   // CUDA events around the whole loop
         stats.t_matching += now_s() - t_match0;
@@ -1069,7 +1070,7 @@ void Line3D::reset()                                                            
 {
     Impl& d = *impl_;
     d.num_wps.clear(); d.common_wps.clear(); d.view_sim.clear(); d.wp2views.clear(); d.vn.clear(); d.fund.clear();
-    d.matched.clear(); d.best.clear(); d.pc_fwd.clear(); d.pc_rev.clear(); d.pc.clear(); d.hyps.clear(); d.hyp_of.clear(); d.result.clear();
+    d.best.clear(); d.pc_fwd.clear(); d.pc_rev.clear(); d.pc.clear(); d.hyps.clear(); d.hyp_of.clear(); d.result.clear();
     for (std::map<unsigned, ViewData*>::iterator it = d.views.begin(); it != d.views.end(); ++it) delete it->second;
     d.views.clear();
     d.computation = false;
@@ -1102,7 +1103,7 @@ void Line3D::compute3Dmodel(bool perform_diffusion)                             
     Impl& d = *impl_;
     if (d.views.size() < 4) { std::cerr << d.prefix << "not enough images! can't compute 3D model..." << std::endl; return; }
     d.computation = true;
-    d.matched.clear(); d.best.clear(); d.result.clear();
+    d.best.clear(); d.result.clear();
     d.match_log.clear(); d.match_median.clear(); d.filtered_dump.clear(); d.edges_pre.clear(); d.edges_cluster.clear(); d.cluster_nodes = 0;
     memset(&d.stats, 0, sizeof d.stats);
     const uint64_t launches0 = l3d_kernel_launches(d.ctx);
