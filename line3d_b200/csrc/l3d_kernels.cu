@@ -448,7 +448,7 @@ int l3d_debug_chain_times(l3d_ctx* ctx, int on, double out[24])
     return 0;
 }
 
-int l3d_debug_host_times(l3d_ctx* ctx, double out[4])
+int l3d_debug_host_times(l3d_ctx* ctx, double out[8])
 {
     if (!ctx || !out) return 1;
     for (int k = 0; k < 8; ++k) { out[k] = ctx->host_s[k]; ctx->host_s[k] = 0.0; }
